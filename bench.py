@@ -1,0 +1,370 @@
+#!/usr/bin/env python
+"""bench.py -- 31-mer FM-index query throughput on B200 (BASELINE.json metric).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+A step = one pass of the hot path (findInterval, src/bwt/query.cpp:24-41) over one batch of Q
+synthetic 31-mers against one BWT shard per GPU.
+
+N = 1     workload = BASELINE.json configs[1]: 50M x 100bp reads from a random 10 Mbp diploid genome,
+          de-duplicated, one RLBWT; 1M 31-mers (90% cut from the genome).
+N > 1     weak scaling: every rank holds its OWN shard of that size (a different read sample of the same
+          genome -- the reference shards by read, and every query visits every shard: SURVEY.md 8(e)),
+          all ranks search the same Q k-mers and the per-shard counts are summed with one NCCL all-reduce
+          inside the timed region (the reference's ZMQ fan-in + sum, server.cpp:184-197, 404-410).
+          The unit is therefore one 31-mer searched in one shard; value = N*Q*K / max-over-ranks time.
+
+Prints ONE JSON line on rank 0.  `--impl reference` times the reference's own CPU code (oracle/_ref, or
+the oracle port when that library is absent) on the host cores for the same workload.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import sys
+import tempfile
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "31-mer count queries/s (findInterval, one shard per GPU)"
+UNIT = "queries/s"
+BYTES_PER_RANK = 128          # one 128-byte block per getOcc
+FALLBACK_HBM_GBS = 6650.0     # /opt/skills/guides/B200_PROFILING.md
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    # workload overrides (debugging only; the defaults are BASELINE.json configs[1])
+    ap.add_argument("--genome", type=int, default=10_000_000)
+    ap.add_argument("--reads", type=int, default=50_000_000)
+    ap.add_argument("--read-len", type=int, default=100)
+    ap.add_argument("--queries", type=int, default=1_000_000)
+    ap.add_argument("--k", type=int, default=31)
+    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--locate-queries", type=int, default=100_000, help="k-mers of the count+locate side measurement")
+    return ap.parse_args()
+
+
+def dist_env():
+    return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
+
+
+# ------------------------------------------------------------------------------------------------
+# workload
+# ------------------------------------------------------------------------------------------------
+def build_shard(args, device, rank):
+    """configs[1] for shard `rank`: (runs u8 [R] numpy, num_strings, num_symbols, sai numpy, queries [Q,k] tensor)."""
+    import torch
+    from readserver_b200 import datagen as dg
+    t0 = time.time()
+    h1 = dg.random_genome(args.genome, seed=2, device=device)
+    h2 = dg.mutate_snps(h1, 1e-3, seed=20)
+    for attempt in range(4):  # re-seed until the reference would not read m_vSum out of bounds
+        reads, lens = dg.sample_reads([h1, h2], args.reads, args.read_len, seed=21 + 100 * rank + 7919 * attempt)
+        reads, lens, _, _ = dg.dedupe_rlo(reads, lens)
+        built = dg.build_bwt(reads, lens)
+        del reads, lens
+        if dg.q2_safe(built.runs, built.num_symbols):
+            break
+    queries = dg.make_queries(h1, args.queries, args.k, seed=3).contiguous()
+    runs = built.runs.cpu().numpy()
+    sai = built.sai.cpu().numpy().astype(np.uint64)
+    ns, nsym = built.num_strings, built.num_symbols
+    del built, h2
+    if device != "cpu":
+        torch.cuda.empty_cache()
+    return dict(runs=runs, num_strings=ns, num_symbols=nsym, sai=sai, queries=queries, genome=h1,
+                build_seconds=time.time() - t0)
+
+
+def workload_name(args):
+    return (f"configs[1]: {args.reads // 1_000_000}M x {args.read_len}bp reads, random {args.genome / 1e6:g} Mbp diploid "
+            f"genome (SNPs 1/kb), de-duplicated, single RLBWT per GPU; {args.queries} random {args.k}-mers (90% present)")
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    REASONS = {0x8: "hw_slowdown", 0x40: "hw_thermal_slowdown", 0x20: "sw_thermal_slowdown", 0x4: "sw_power_cap",
+               0x80: "hw_power_brake_slowdown"}
+
+    def __init__(self, index):
+        self.samples, self.reasons, self.max_mhz = [], set(), None
+        self._stop = threading.Event()
+        self._t = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            # CUDA_VISIBLE_DEVICES may remap; use the UUID of the torch device
+            import torch
+            uuid = str(torch.cuda.get_device_properties(index).uuid)
+            h = None
+            for i in range(pynvml.nvmlDeviceGetCount()):
+                hh = pynvml.nvmlDeviceGetHandleByIndex(i)
+                u = pynvml.nvmlDeviceGetUUID(hh)
+                u = u.decode() if isinstance(u, bytes) else u
+                if uuid in u:
+                    h = hh
+            self.h = h if h is not None else pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _run(self):
+        nv = self.nv
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                for bit, name in self.REASONS.items():
+                    if r & bit:
+                        self.reasons.add(name)
+            except Exception:
+                pass
+            self._stop.wait(0.02)
+
+    def start(self):
+        if self.nv:
+            self._t = threading.Thread(target=self._run, daemon=True)
+            self._t.start()
+
+    def stop(self):
+        self._stop.set()
+        if self._t:
+            self._t.join()
+        med = float(np.median(self.samples)) if self.samples else None
+        return {"sm_mhz": med, "sm_max_mhz": self.max_mhz, "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU legs (the ONLY place bench.py touches oracle/)
+# ------------------------------------------------------------------------------------------------
+def cpu_find_interval(shard, queries_np, k, nthreads, target_seconds, steps=1, warmup=0):
+    """Times findInterval of the reference's CPU implementation on a bounded sample of the queries."""
+    import oracle
+    import torch
+    from readserver_b200 import datagen as dg
+    with tempfile.TemporaryDirectory() as d:
+        path = os.path.join(d, "shard.bwt")
+        dg.write_bwt(path, torch.from_numpy(shard["runs"]), shard["num_strings"], shard["num_symbols"])
+        t0 = time.time()
+        ix = oracle.open_best(path)
+        load_s = time.time() - t0
+    probe = min(len(queries_np), 20_000)
+    ix.find_interval_batch(queries_np[:probe], k, nthreads=nthreads)
+    rate = probe / max(ix.last_seconds, 1e-9)
+    n = int(min(len(queries_np), max(probe, rate * target_seconds / max(1, steps + warmup))))
+    sample = np.ascontiguousarray(queries_np[:n])
+    for _ in range(warmup):
+        ix.find_interval_batch(sample, k, nthreads=nthreads)
+    secs = []
+    for _ in range(steps):
+        lo, up = ix.find_interval_batch(sample, k, nthreads=nthreads)
+        secs.append(ix.last_seconds)
+    return dict(kind=ix.kind, n=n, seconds=secs, value=n * len(secs) / sum(secs), load_seconds=load_s,
+                lower=lo, upper=up)
+
+
+def run_reference(args):
+    rank, local_rank, world = dist_env()
+    if rank != 0:
+        return
+    import torch
+    device = "cuda:0" if torch.cuda.is_available() else "cpu"
+    shard = build_shard(args, device, 0)
+    q = shard["queries"].cpu().numpy()
+    cores = os.cpu_count() or 1
+    r = cpu_find_interval(shard, q, args.k, cores, target_seconds=60.0, steps=args.steps, warmup=args.warmup)
+    ms = 1e3 * sum(r["seconds"]) / len(r["seconds"])
+    sample = f"first {r['n']} of {len(q)} queries per step, {cores} threads striding the array"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+        "config": {"workload": workload_name(args), "bwt_symbols": shard["num_symbols"], "bwt_runs": int(shard["runs"].size),
+                   "queries_per_step": r["n"]},
+        "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": cores, "kind": r["kind"], "sample": sample},
+        "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------
+# our arm
+# ------------------------------------------------------------------------------------------------
+def hbm_peak():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs, streaming copy)"
+    except Exception:
+        return FALLBACK_HBM_GBS, "fallback (B200_PROFILING.md)"
+
+
+def pinned_array(engine, nbytes, dtype, shape):
+    import ctypes as C
+    p = C.c_void_p()
+    rc = engine.lib().rs_host_alloc(C.byref(p), nbytes)
+    assert rc == 0
+    buf = (C.c_uint8 * nbytes).from_address(p.value)
+    return np.frombuffer(buf, dtype=dtype).reshape(shape), p
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    rank, local_rank, world = dist_env()
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (there is no CPU path)"
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local_rank}"))
+    torch.cuda.set_device(local_rank)
+    dev = f"cuda:{local_rank}"
+    from readserver_b200 import engine
+
+    shard = build_shard(args, dev, rank)
+    B = engine.GpuBWT(runs=shard["runs"], num_strings=shard["num_strings"], num_symbols=shard["num_symbols"],
+                      device=local_rank)
+    B.set_sai(shard["sai"])
+    B.enable_stats(True)
+    Q, k = args.queries, args.k
+    dq = shard["queries"]
+    dlo = torch.empty(Q, dtype=torch.int64, device=dev)
+    dup = torch.empty(Q, dtype=torch.int64, device=dev)
+    dcnt = torch.empty(Q, dtype=torch.int64, device=dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
+    stream = torch.cuda.current_stream().cuda_stream
+
+    def step():
+        if world > 1:
+            B.count_dev(dq, k, Q, 0, dcnt, stream)
+            dist.all_reduce(dcnt)  # per-shard counts -> population counts (C1)
+        else:
+            B.find_interval_dev(dq, k, Q, dlo, dup, stream)
+
+    for _ in range(max(3, args.warmup)):
+        step()
+    torch.cuda.synchronize()
+    B.read_stats(reset=True)
+    if world > 1:
+        dist.barrier()
+    clocks = ClockSampler(local_rank)
+    clocks.start()
+    torch.cuda.synchronize()
+    evs = []
+    for _ in range(args.steps):
+        flush.fill_(1)  # evict the index and the queries from L2 between timed steps (untimed)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        step()
+        e1.record()
+        evs.append((e0, e1))
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    clk = clocks.stop()
+    step_ms = [a.elapsed_time(b) for a, b in evs]
+    total_ms = torch.tensor([sum(step_ms)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
+    total_ms = float(total_ms.item())
+    interval_steps, _ = B.read_stats(reset=True)
+
+    # ---- e2e: the host-pointer C-ABI call, pinned host buffers, copies inside the timed region ----
+    hq, _p1 = pinned_array(engine, Q * k, np.uint8, (Q, k))
+    hlo, _p2 = pinned_array(engine, Q * 8, np.uint64, (Q,))
+    hup, _p3 = pinned_array(engine, Q * 8, np.uint64, (Q,))
+    hq[:] = dq.cpu().numpy()
+    L = engine.lib()
+    for _ in range(3):
+        assert L.rs_find_interval_batch(B._h, hq.ctypes.data, k, Q, hlo.ctypes.data, hup.ctypes.data) == 0
+    if world > 1:
+        dist.barrier()
+    e2e_s = 0.0
+    for _ in range(args.steps):
+        flush.fill_(1)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        rc = L.rs_find_interval_batch(B._h, hq.ctypes.data, k, Q, hlo.ctypes.data, hup.ctypes.data)
+        e2e_s += time.perf_counter() - t0
+        assert rc == 0
+    e2e_t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
+    e2e_s = float(e2e_t.item())
+
+    # results of the device path and of the host path agree (and, below, with the CPU reference)
+    if world == 1:
+        assert np.array_equal(dlo.cpu().numpy().view(np.uint64), hlo) and np.array_equal(dup.cpu().numpy().view(np.uint64), hup)
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    value = world * Q * args.steps / (total_ms / 1e3)
+    peak, peak_src = hbm_peak()
+    kern_ms = sum(step_ms) / len(step_ms)  # at N = 1 the step IS the kernel launch
+    ranks_per_launch = 2.0 * interval_steps / args.steps
+    achieved = ranks_per_launch * BYTES_PER_RANK / (kern_ms / 1e3) / 1e9
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": max(3, args.warmup), "ms_per_step": total_ms / args.steps, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+        "config": {
+            "workload": workload_name(args), "k": k, "queries_per_step": Q, "shards_per_gpu": 1,
+            "bwt_symbols": shard["num_symbols"], "bwt_runs": int(shard["runs"].size), "reads_unique": shard["num_strings"],
+            "index_hbm_bytes": int(B.info.hbm_bytes), "index_fits_l2": bool(B.info.hbm_bytes < 126e6),
+            "l2": "256 MiB buffer written between timed steps (untimed) -> index and queries start cold",
+            "timing": "CUDA events around each step on the launching stream, summed; max over ranks",
+            "collective": "none" if world == 1 else "NCCL all-reduce of per-shard counts inside the timed step",
+            "data_build_seconds": round(shard["build_seconds"], 1),
+        },
+        "roofline": {
+            "bound": "hbm", "kernel": "k_find_interval", "achieved": achieved, "peak": peak, "unit": "GB/s",
+            "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+            "algorithmic_bytes": "executed getOcc calls x 128 B (SURVEY.md 8(d)); lower/upper of a step usually share a block",
+            "getocc_per_launch": ranks_per_launch,
+        },
+        "e2e": {"value": world * Q * args.steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": Q * k,
+                "d2h_bytes_per_step": 2 * Q * 8, "api": "rs_find_interval_batch (host pointers, pinned)"},
+        "gpu_launches": args.steps,
+        "clocks": clk,
+    }
+    if world == 1 and not args.no_cpu_baseline:
+        cores = os.cpu_count() or 1
+        r = cpu_find_interval(shard, hq, k, cores, target_seconds=args.cpu_seconds, steps=1)
+        ok = bool(np.array_equal(r["lower"], hlo[: r["n"]]) and np.array_equal(r["upper"], hup[: r["n"]]))
+        line["cpu_baseline"] = {"value": r["value"], "unit": UNIT, "cores": cores, "kind": r["kind"],
+                                "sample": f"first {r['n']} of {Q} queries, {cores} threads striding the array",
+                                "gpu_results_bit_exact_on_sample": ok}
+        assert ok, "GPU results differ from the CPU reference"
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

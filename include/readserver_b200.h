@@ -1,0 +1,131 @@
+/* readserver_b200 -- C ABI of the B200-native FM-index query engine.
+ *
+ * Drop-in boundary for ReadServer's BWT hot path.  The reference has no FFI: its seam is the C++
+ * static library libbwt.a (/root/reference/src/bwt/Makefile:11) with the abstract `class BWT`
+ * (include/bwt/bwt.h:6-15) and the free functions of include/bwt/query.h:18-32, consumed by the
+ * query worker (src/service/service.cpp).  Each entry point below names the reference interface it
+ * replaces.  All calls are batched; plain pointers and sizes only.
+ *
+ * Conventions
+ *  - every function returns an rs_status (0 = OK); rs_last_error() gives the thread's last message;
+ *  - symbols are the reference's characters '$','A','C','G','T'; any other byte ranks as '$'
+ *    (include/bwt/alphabet.h:11-32);
+ *  - results are bit-exact with the reference's CPU path INCLUDING its tail behaviour in
+ *    BPTree::rank/access (include/bwt/BPTree.h:74-94,135-157) unless rs_index_set_tail_emulation(ix, 0);
+ *  - "_dev" variants take device pointers and a cudaStream_t (as void*), are asynchronous and
+ *    stream-ordered; the others take host pointers and return when the results are in them;
+ *  - an rs_index is immutable after its tables are attached and may be shared by any number of
+ *    threads (the reference shares one `const BWT*` between 8 + 64 threads, service.cpp:88-89,1505-1513);
+ *    host-pointer calls on one index are serialised internally, "_dev" calls are not;
+ *  - there is NO CPU fallback: without a CUDA device every compute call fails with RS_ERR_CUDA.
+ */
+#ifndef READSERVER_B200_H
+#define READSERVER_B200_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct rs_index rs_index;
+
+typedef enum rs_status {
+  RS_STATUS_OK = 0,
+  RS_STATUS_OPEN = 1,      /* cannot open file (the reference silently yields an empty index)          */
+  RS_STATUS_MAGIC = 2,     /* bad magic: the reference prints and exit(EXIT_FAILURE)s, rlebwt_reader.cpp:31-34 */
+  RS_STATUS_SHORT = 3,     /* truncated file                                                            */
+  RS_STATUS_RUNBYTE = 4,   /* run byte with symbol > 4 or length 0                                      */
+  RS_STATUS_ARG = 5,       /* null / empty / inconsistent argument (e.g. empty query)     */
+  RS_STATUS_CUDA = 6,      /* CUDA runtime error                                                        */
+  RS_STATUS_TOO_LARGE = 7, /* more than 2^32 blocks in one shard                                        */
+  RS_STATUS_NO_TABLE = 8   /* locate / sample call before the table it needs was attached              */
+} rs_status;
+
+typedef struct rs_index_info {
+  uint64_t bwlen;        /* getBWLen(), rlebwt.cpp:303-305                                   */
+  uint64_t num_strings;  /* reads in the shard                                                */
+  uint64_t num_runs;     /* run bytes of the .bwt                                             */
+  uint64_t num_blocks;   /* 128-byte blocks in HBM                                            */
+  uint64_t hbm_bytes;    /* blocks + directories + attached tables                            */
+  uint64_t pc[5];        /* getPC for $,A,C,G,T                                               */
+  uint64_t total[5];     /* occurrences of each symbol                                        */
+  uint64_t ref_depth;    /* depth of the BP-tree the reference would build (rlebwt.cpp:51-72) */
+  uint64_t ref_clamp_c;  /* first position of the reference's tail region      */
+  uint64_t ref_vlast;    /* index of the last m_vSum hint                                     */
+  int32_t q2_safe;       /* 0: the reference would read m_vSum out of bounds   */
+  int32_t device;        /* CUDA device ordinal                                               */
+} rs_index_info;
+
+/* ---- lifecycle -------------------------------------------------------------------------------- */
+/* RLEBWT::RLEBWT(filename) (src/bwt/rlebwt.cpp:11-32) + BWTReaderRLE (src/bwt/rlebwt_reader.cpp:21-48):
+ * read an SGA binary RLE .bwt, re-encode it into 128-byte blocks and upload it to `device`. */
+int rs_index_open(const char* bwt_path, int device, rs_index** out);
+/* Same from run bytes already in memory (sym<<5 | len, include/bwt/rlunit.h:8-16). */
+int rs_index_from_runs(const uint8_t* runs, uint64_t num_runs, uint64_t num_strings, uint64_t num_symbols,
+                       int device, rs_index** out);
+void rs_index_close(rs_index* ix);
+int rs_index_get_info(const rs_index* ix, rs_index_info* info);
+/* 1 (default): bit-exact with the reference; 0: exact rank/access everywhere. */
+int rs_index_set_tail_emulation(rs_index* ix, int on);
+/* Work counters for the *_dev calls (kept on the device, off by default): executed updateInterval
+ * steps of findInterval (2 getOcc each) and executed LF steps of extractPrefix.  Used by bench.py
+ * to turn a kernel time into achieved bytes/s; no reference counterpart. */
+int rs_index_enable_stats(rs_index* ix, int on);
+int rs_index_read_stats(rs_index* ix, uint64_t* interval_steps, uint64_t* walk_steps, int reset);
+const char* rs_last_error(void);
+/* pinned host memory for the host-pointer calls (optional; any host memory is accepted) */
+int rs_host_alloc(void** p, size_t bytes);
+void rs_host_free(void* p);
+
+/* ---- class BWT (include/bwt/bwt.h:6-15), batched ------------------------------------------------- */
+uint64_t rs_get_pc(const rs_index* ix, char b);   /* RLEBWT::getPC,    rlebwt.cpp:229-231 */
+uint64_t rs_get_bwlen(const rs_index* ix);        /* RLEBWT::getBWLen, rlebwt.cpp:303-305 */
+/* RLEBWT::getOcc(b, index), rlebwt.cpp:268-301: out[i] = occurrences of b[i] in BWT[0..index[i]] */
+int rs_get_occ_batch(const rs_index* ix, const char* b, const uint64_t* index, size_t n, uint64_t* out);
+/* RLEBWT::getChar(index), rlebwt.cpp:202-227 */
+int rs_get_char_batch(const rs_index* ix, const uint64_t* index, size_t n, char* out);
+/* RLEBWT::getF(index), rlebwt.cpp:307-314 */
+int rs_get_f_batch(const rs_index* ix, const uint64_t* index, size_t n, char* out);
+
+/* ---- include/bwt/query.h:18-32, batched ---------------------------------------------------------- */
+/* findInterval (src/bwt/query.cpp:24-41) for Q k-mers of one length k stored back to back.
+ * lower/upper are the reference's BWTInterval, including the value at the step where the search
+ * stopped early (query.cpp:35-37). */
+int rs_find_interval_batch(const rs_index* ix, const char* kmers, int k, size_t Q, uint64_t* lower, uint64_t* upper);
+/* findInterval for Q strings of any length: string q = text[offsets[q] .. offsets[q+1]).
+ * An empty string (undefined behaviour in the reference) yields lower = 1, upper = 0. */
+int rs_find_interval_var_batch(const rs_index* ix, const char* text, const uint64_t* offsets, size_t Q,
+                               uint64_t* lower, uint64_t* upper);
+int rs_find_interval_batch_dev(const rs_index* ix, const void* d_kmers, int k, size_t Q, void* d_lower,
+                               void* d_upper, void* stream);
+int rs_find_interval_var_batch_dev(const rs_index* ix, const void* d_text, const void* d_offsets, size_t Q,
+                                   void* d_lower, void* d_upper, void* stream);
+
+/* count_reads (src/service/service.cpp:279-315): per k-mer, the number of BWT rows matching it on the
+ * forward strand (strand = 0) or its reverse complement (strand = 1); a k-mer with any byte outside
+ * ACGT counts 0 (service.cpp:299-301). */
+int rs_count_batch(const rs_index* ix, const char* kmers, int k, size_t Q, int strand, uint64_t* counts);
+int rs_count_batch_dev(const rs_index* ix, const void* d_kmers, int k, size_t Q, int strand, void* d_counts,
+                       void* stream);
+
+/* ---- locate -------------------------------------------------------------------------------------- */
+/* Attach the lexicographic-rank -> read-index table (SGA's .sai, written by `sga index` next to the
+ * .bwt: submodules/sga/src/SuffixTools/SampledSuffixArray.cpp:171-189).  sai has num_strings entries. */
+int rs_index_set_sai(rs_index* ix, const uint64_t* sai, uint64_t num_strings);
+/* extractPrefix (src/bwt/query.cpp:43-63) for n BWT rows: LF-walk to the '$'.
+ *   lexrank[i]  terminal row = lexicographic rank of the read (UINT64_MAX if the walk did not end
+ *               within max_steps bases: inside the reference's tail region it can cycle forever)
+ *   steps[i]    bases walked (UINT32_MAX on cut-off)            -- may be NULL
+ *   read_index[i]  sai[lexrank[i]]                               -- may be NULL; needs rs_index_set_sai
+ *   bases       n x max_steps chars, the extracted prefix in reading order, NUL padded -- may be NULL */
+int rs_extract_prefix_batch(const rs_index* ix, const uint64_t* rows, size_t n, uint32_t max_steps,
+                            uint64_t* lexrank, uint32_t* steps, uint64_t* read_index, char* bases);
+int rs_extract_prefix_batch_dev(const rs_index* ix, const void* d_rows, size_t n, uint32_t max_steps,
+                                void* d_lexrank, void* d_steps, void* d_read_index, void* d_bases, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -133,15 +133,17 @@ static inline uint64_t prefix_terminal(const BWT* p, uint64_t row, uint32_t* ste
   return idx;
 }
 
-// Replay of the extractPostfix loop (src/bwt/query.cpp:65-85); terminal idx = input-order read index.
+// Replay of the extractPostfix loop (src/bwt/query.cpp:65-85); reports the row (< num_strings) at which
+// getF returned '$' = the read's input-order index (the select of that last step is still performed).
 static inline uint64_t postfix_terminal(const BWT* p, uint64_t row, uint32_t* steps, uint32_t max_steps) {
   uint64_t idx = row;
   uint32_t s = 0;
   while (1) {
     char f = p->getF(idx);
     uint64_t fc = idx - p->getPC(f) + 1;
+    const uint64_t at = idx;  // row in F: when f == '$' it is the read's input-order index
     idx = p->getOccAt(f, fc);
-    if (f == '$') break;
+    if (f == '$') { idx = at; break; }
     if (++s > max_steps) { s = UINT32_MAX; idx = UINT64_MAX; break; }
   }
   if (steps) *steps = s;

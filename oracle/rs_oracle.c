@@ -473,13 +473,15 @@ uint64_t rso_get_occ(const rso_index* ix, char b, uint64_t index) {
   if (end >= length) end = length - 1;
   for (uint64_t i = begin; i <= end; ++i) {
     const uint64_t count = ix->runs[i] & 31u;
-    const unsigned rs = ix->runs[i] >> 5;
+    /* rlebwt.cpp:286,293 compare CHARACTERS (b == unit.getChar()): a byte outside "$ACGT" takes the
+     * '$' counters in the tree (alphabet.h getRank) but matches no run here. */
+    const char rc = RANK_ALPHABET[ix->runs[i] >> 5];
     if (offset <= count) {
-      if (sym == rs) occ += offset;
+      if (b == rc) occ += offset;
       break;
     } else {
       offset -= count;
-      if (sym == rs) occ += count;
+      if (b == rc) occ += count;
     }
   }
   return occ;
@@ -496,7 +498,7 @@ uint64_t rso_get_occ_at(const rso_index* ix, char b, uint64_t bc) {
   uint64_t index = mk.sum;
   for (uint64_t i = begin; i <= end; ++i) {
     const uint64_t count = ix->runs[i] & 31u;
-    if (sym != (unsigned)(ix->runs[i] >> 5)) {
+    if (b != RANK_ALPHABET[ix->runs[i] >> 5]) { /* rlebwt.cpp:251 compares characters */
       index += count;
       continue;
     }
@@ -590,8 +592,12 @@ size_t rso_extract_postfix(const rso_index* ix, uint64_t row, char* out, size_t 
   while (1) {
     char f = rso_get_f(ix, idx);
     uint64_t fc = idx - rso_get_pc(ix, f) + 1;
+    const uint64_t at = idx; /* row in F: when f == '$' this row IS the read's input-order index */
     idx = rso_get_occ_at(ix, f, fc);
-    if (f == '$') break;
+    if (f == '$') {
+      idx = at;
+      break;
+    }
     if (out && n + 1 < cap) out[n] = f;
     ++n;
     if (n > max_steps) {

@@ -52,7 +52,9 @@ void rso_find_interval(const rso_index* ix, const char* w, size_t len, uint64_t*
  * NUL), returns its length; *terminal = idx after the '$' step = lexicographic rank of the read. */
 size_t rso_extract_prefix(const rso_index* ix, uint64_t row, char* out, size_t cap, uint64_t* terminal,
                           size_t max_steps);
-/* query.cpp:65-85: *terminal = idx after the '$' step = input-order read index. */
+/* query.cpp:65-85: *terminal = the row (< num_strings) at which getF returned '$' = the read's index in
+ * builder input order ($_i < $_j <=> i < j).  The reference also performs the select of that step
+ * (query.cpp:73-74) before it breaks; so does this port, but the row reported is the one before it. */
 size_t rso_extract_postfix(const rso_index* ix, uint64_t row, char* out, size_t cap, uint64_t* terminal,
                            size_t max_steps);
 /* NOTE: a walk that enters the reference's tail-clamp region can cycle forever; the

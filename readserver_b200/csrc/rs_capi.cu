@@ -1,0 +1,401 @@
+/* C ABI of the engine (include/readserver_b200.h): index lifecycle, host<->device staging and
+ * kernel launches.  No torch types, no CPU compute path. */
+#include "../../include/readserver_b200.h"
+
+#include <cuda_runtime.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "rs_build.h"
+#include "rs_kernels.h"
+
+static thread_local std::string g_err;
+
+static int fail(int code, const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof(buf), fmt, ap);
+  va_end(ap);
+  g_err = buf;
+  return code;
+}
+
+#define CU(call)                                                                                  \
+  do {                                                                                            \
+    cudaError_t e_ = (call);                                                                      \
+    if (e_ != cudaSuccess) return fail(RS_STATUS_CUDA, "%s: %s", #call, cudaGetErrorString(e_));  \
+  } while (0)
+
+namespace {
+/* grow-on-demand device scratch buffer */
+struct Scratch {
+  void* p = nullptr;
+  size_t cap = 0;
+  cudaError_t need(size_t bytes) {
+    if (bytes <= cap) return cudaSuccess;
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+    size_t want = bytes + bytes / 4 + 256;
+    cudaError_t e = cudaMalloc(&p, want);
+    if (e == cudaSuccess) cap = want;
+    return e;
+  }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+  }
+};
+}  // namespace
+
+struct rs_index {
+  int device = 0;
+  rs_index_dev dev;
+  uint64_t num_runs = 0, depth = 0;
+  bool q2_safe = true;
+  uint64_t hbm_bytes = 0;
+  uint64_t init_occ_ref[RS_NSYM] = {0, 0, 0, 0, 0}; /* the reference's getOcc(c, n-1) */
+  void* d_blocks = nullptr;
+  void* d_dir = nullptr;
+  void* d_sel[RS_NSYM] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+  uint64_t* d_sai = nullptr;
+  uint64_t* d_samp_off = nullptr;
+  uint8_t* d_samp_codes = nullptr;
+  int size_of_sample = 0;
+  uint64_t* d_stats = nullptr; /* [0] updateInterval steps, [1] LF-walk steps; null unless profiling is on */
+  cudaStream_t stream = nullptr;
+  mutable std::mutex mu; /* serialises the host-pointer calls (they share the scratch buffers) */
+  mutable Scratch s_in, s_in2, s_out, s_out2, s_out3, s_out4;
+};
+
+const char* rs_last_error(void) { return g_err.c_str(); }
+
+static int upload(rs_index* ix, const RsHostIndex& h) {
+  CU(cudaSetDevice(ix->device));
+  CU(cudaStreamCreateWithFlags(&ix->stream, cudaStreamNonBlocking));
+  const size_t bb = h.blocks.size() * sizeof(rs_block), db = h.dir.size() * sizeof(uint64_t);
+  CU(cudaMalloc(&ix->d_blocks, bb));
+  CU(cudaMalloc(&ix->d_dir, db));
+  CU(cudaMemcpy(ix->d_blocks, h.blocks.data(), bb, cudaMemcpyHostToDevice));
+  CU(cudaMemcpy(ix->d_dir, h.dir.data(), db, cudaMemcpyHostToDevice));
+  ix->hbm_bytes = bb + db;
+  memset(&ix->dev, 0, sizeof(ix->dev));
+  for (int c = 0; c < RS_NSYM; ++c) {
+    const size_t sb = h.sel[c].size() * sizeof(uint32_t);
+    CU(cudaMalloc(&ix->d_sel[c], sb));
+    CU(cudaMemcpy(ix->d_sel[c], h.sel[c].data(), sb, cudaMemcpyHostToDevice));
+    ix->dev.sel[c] = (const uint32_t*)ix->d_sel[c];
+    ix->hbm_bytes += sb;
+    ix->dev.pc[c] = h.pc[c];
+    ix->dev.tot[c] = h.tot[c];
+    ix->dev.init_occ[c] = h.init_occ[c];
+    ix->init_occ_ref[c] = h.init_occ[c];
+  }
+  ix->dev.blocks = ix->d_blocks;
+  ix->dev.dir = (const uint64_t*)ix->d_dir;
+  ix->dev.n = h.n;
+  ix->dev.nblocks = h.blocks.size();
+  ix->dev.num_strings = h.num_strings;
+  ix->dev.clamp_c = h.clamp_c;
+  ix->dev.clamp_char = h.clamp_char;
+  ix->dev.vlast = h.vlast;
+  ix->dev.emulate_tail = 1;
+  ix->num_runs = h.num_runs;
+  ix->depth = h.depth;
+  ix->q2_safe = h.q2_safe;
+  return RS_STATUS_OK;
+}
+
+int rs_index_from_runs(const uint8_t* runs, uint64_t num_runs, uint64_t num_strings, uint64_t num_symbols, int device,
+                       rs_index** out) {
+  if (!out) return fail(RS_STATUS_ARG, "out is null");
+  *out = nullptr;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev)
+    return fail(RS_STATUS_CUDA, "CUDA device %d not available (%d devices): this engine has no CPU path", device, ndev);
+  RsHostIndex h;
+  const int rc = rs_build_host_index(runs, num_runs, num_strings, num_symbols, h);
+  if (rc != RS_OK) return fail(rc, "cannot build index from run bytes (status %d)", rc);
+  rs_index* ix = new rs_index;
+  ix->device = device;
+  const int st = upload(ix, h);
+  if (st != RS_STATUS_OK) {
+    rs_index_close(ix);
+    return st;
+  }
+  *out = ix;
+  return RS_STATUS_OK;
+}
+
+int rs_index_open(const char* bwt_path, int device, rs_index** out) {
+  if (!bwt_path || !out) return fail(RS_STATUS_ARG, "null argument");
+  std::vector<uint8_t> runs;
+  uint64_t ns = 0, nsym = 0;
+  const int rc = rs_read_bwt_file(bwt_path, runs, ns, nsym);
+  if (rc != RS_OK) return fail(rc, "%s: cannot read SGA .bwt (status %d)", bwt_path, rc);
+  return rs_index_from_runs(runs.data(), runs.size(), ns, nsym, device, out);
+}
+
+void rs_index_close(rs_index* ix) {
+  if (!ix) return;
+  cudaSetDevice(ix->device);
+  if (ix->stream) cudaStreamSynchronize(ix->stream);
+  if (ix->d_blocks) cudaFree(ix->d_blocks);
+  if (ix->d_dir) cudaFree(ix->d_dir);
+  for (int c = 0; c < RS_NSYM; ++c)
+    if (ix->d_sel[c]) cudaFree(ix->d_sel[c]);
+  if (ix->d_sai) cudaFree(ix->d_sai);
+  if (ix->d_samp_off) cudaFree(ix->d_samp_off);
+  if (ix->d_samp_codes) cudaFree(ix->d_samp_codes);
+  if (ix->d_stats) cudaFree(ix->d_stats);
+  ix->s_in.release();
+  ix->s_in2.release();
+  ix->s_out.release();
+  ix->s_out2.release();
+  ix->s_out3.release();
+  ix->s_out4.release();
+  if (ix->stream) cudaStreamDestroy(ix->stream);
+  delete ix;
+}
+
+int rs_index_get_info(const rs_index* ix, rs_index_info* info) {
+  if (!ix || !info) return fail(RS_STATUS_ARG, "null argument");
+  memset(info, 0, sizeof(*info));
+  info->bwlen = ix->dev.n;
+  info->num_strings = ix->dev.num_strings;
+  info->num_runs = ix->num_runs;
+  info->num_blocks = ix->dev.nblocks;
+  info->hbm_bytes = ix->hbm_bytes;
+  for (int c = 0; c < RS_NSYM; ++c) {
+    info->pc[c] = ix->dev.pc[c];
+    info->total[c] = ix->dev.tot[c];
+  }
+  info->ref_depth = ix->depth;
+  info->ref_clamp_c = ix->dev.clamp_c;
+  info->ref_vlast = ix->dev.vlast;
+  info->q2_safe = ix->q2_safe ? 1 : 0;
+  info->device = ix->device;
+  return RS_STATUS_OK;
+}
+
+int rs_index_set_tail_emulation(rs_index* ix, int on) {
+  if (!ix) return fail(RS_STATUS_ARG, "null index");
+  std::lock_guard<std::mutex> lk(ix->mu);
+  ix->dev.emulate_tail = on ? 1u : 0u;
+  /* initInterval's constant (query.cpp:18-21) follows the same switch */
+  for (int c = 0; c < RS_NSYM; ++c) ix->dev.init_occ[c] = on ? ix->init_occ_ref[c] : ix->dev.tot[c];
+  return RS_STATUS_OK;
+}
+
+int rs_index_enable_stats(rs_index* ix, int on) {
+  if (!ix) return fail(RS_STATUS_ARG, "null index");
+  std::lock_guard<std::mutex> lk(ix->mu);
+  CU(cudaSetDevice(ix->device));
+  if (on && !ix->d_stats) {
+    CU(cudaMalloc((void**)&ix->d_stats, 2 * sizeof(uint64_t)));
+    CU(cudaMemset(ix->d_stats, 0, 2 * sizeof(uint64_t)));
+  } else if (!on && ix->d_stats) {
+    CU(cudaDeviceSynchronize());
+    cudaFree(ix->d_stats);
+    ix->d_stats = nullptr;
+  }
+  return RS_STATUS_OK;
+}
+
+int rs_index_read_stats(rs_index* ix, uint64_t* interval_steps, uint64_t* walk_steps, int reset) {
+  if (!ix) return fail(RS_STATUS_ARG, "null index");
+  if (!ix->d_stats) return fail(RS_STATUS_NO_TABLE, "statistics are not enabled");
+  CU(cudaSetDevice(ix->device));
+  CU(cudaDeviceSynchronize());
+  uint64_t v[2] = {0, 0};
+  CU(cudaMemcpy(v, ix->d_stats, sizeof(v), cudaMemcpyDeviceToHost));
+  if (interval_steps) *interval_steps = v[0];
+  if (walk_steps) *walk_steps = v[1];
+  if (reset) CU(cudaMemset(ix->d_stats, 0, sizeof(v)));
+  return RS_STATUS_OK;
+}
+
+int rs_host_alloc(void** p, size_t bytes) {
+  if (!p) return fail(RS_STATUS_ARG, "null argument");
+  CU(cudaMallocHost(p, bytes ? bytes : 1));
+  return RS_STATUS_OK;
+}
+
+void rs_host_free(void* p) {
+  if (p) cudaFreeHost(p);
+}
+
+static inline uint32_t code_of(char b) { return b == 'A' ? 1u : b == 'C' ? 2u : b == 'G' ? 3u : b == 'T' ? 4u : 0u; }
+
+uint64_t rs_get_pc(const rs_index* ix, char b) { return ix ? ix->dev.pc[code_of(b)] : 0; }
+uint64_t rs_get_bwlen(const rs_index* ix) { return ix ? ix->dev.n : 0; }
+
+/* ---- host-pointer calls: stage in, launch, stage out on the index's own stream ---- */
+int rs_get_occ_batch(const rs_index* ix, const char* b, const uint64_t* index, size_t n, uint64_t* out) {
+  if (!ix || (n && (!b || !index || !out))) return fail(RS_STATUS_ARG, "null argument");
+  if (!n) return RS_STATUS_OK;
+  std::lock_guard<std::mutex> lk(ix->mu);
+  CU(cudaSetDevice(ix->device));
+  CU(ix->s_in.need(n));
+  CU(ix->s_in2.need(n * 8));
+  CU(ix->s_out.need(n * 8));
+  cudaStream_t st = ix->stream;
+  CU(cudaMemcpyAsync(ix->s_in.p, b, n, cudaMemcpyHostToDevice, st));
+  CU(cudaMemcpyAsync(ix->s_in2.p, index, n * 8, cudaMemcpyHostToDevice, st));
+  CU(rs_launch_occ(ix->dev, (const uint8_t*)ix->s_in.p, (const uint64_t*)ix->s_in2.p, n, (uint64_t*)ix->s_out.p, st));
+  CU(cudaMemcpyAsync(out, ix->s_out.p, n * 8, cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  return RS_STATUS_OK;
+}
+
+static int char_like(const rs_index* ix, const uint64_t* index, size_t n, char* out, bool f) {
+  if (!ix || (n && (!index || !out))) return fail(RS_STATUS_ARG, "null argument");
+  if (!n) return RS_STATUS_OK;
+  std::lock_guard<std::mutex> lk(ix->mu);
+  CU(cudaSetDevice(ix->device));
+  CU(ix->s_in.need(n * 8));
+  CU(ix->s_out.need(n));
+  cudaStream_t st = ix->stream;
+  CU(cudaMemcpyAsync(ix->s_in.p, index, n * 8, cudaMemcpyHostToDevice, st));
+  if (f) CU(rs_launch_getf(ix->dev, (const uint64_t*)ix->s_in.p, n, (uint8_t*)ix->s_out.p, st));
+  else CU(rs_launch_char(ix->dev, (const uint64_t*)ix->s_in.p, n, (uint8_t*)ix->s_out.p, st));
+  CU(cudaMemcpyAsync(out, ix->s_out.p, n, cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  return RS_STATUS_OK;
+}
+
+int rs_get_char_batch(const rs_index* ix, const uint64_t* index, size_t n, char* out) {
+  return char_like(ix, index, n, out, false);
+}
+int rs_get_f_batch(const rs_index* ix, const uint64_t* index, size_t n, char* out) {
+  return char_like(ix, index, n, out, true);
+}
+
+static int find_host(const rs_index* ix, const char* text, const uint64_t* offsets, int k, size_t Q, uint64_t* lower,
+                     uint64_t* upper, int mode, int strand) {
+  if (!ix || (Q && (!text || !lower || (mode == 0 && !upper)))) return fail(RS_STATUS_ARG, "null argument");
+  if (!offsets && k < 1) return fail(RS_STATUS_ARG, "k must be >= 1 (empty query: SURVEY.md Q3)");
+  if (!Q) return RS_STATUS_OK;
+  std::lock_guard<std::mutex> lk(ix->mu);
+  CU(cudaSetDevice(ix->device));
+  const size_t tbytes = offsets ? (size_t)offsets[Q] : Q * (size_t)k;
+  CU(ix->s_in.need(tbytes ? tbytes : 1));
+  if (offsets) CU(ix->s_in2.need((Q + 1) * 8));
+  CU(ix->s_out.need(Q * 8));
+  if (mode == 0) CU(ix->s_out2.need(Q * 8));
+  cudaStream_t st = ix->stream;
+  CU(cudaMemcpyAsync(ix->s_in.p, text, tbytes, cudaMemcpyHostToDevice, st));
+  if (offsets) CU(cudaMemcpyAsync(ix->s_in2.p, offsets, (Q + 1) * 8, cudaMemcpyHostToDevice, st));
+  CU(rs_launch_find_interval(ix->dev, (const uint8_t*)ix->s_in.p, offsets ? (const uint64_t*)ix->s_in2.p : nullptr,
+                             (uint32_t)k, Q, (uint64_t*)ix->s_out.p, (uint64_t*)ix->s_out2.p, mode, strand, nullptr, st));
+  CU(cudaMemcpyAsync(lower, ix->s_out.p, Q * 8, cudaMemcpyDeviceToHost, st));
+  if (mode == 0) CU(cudaMemcpyAsync(upper, ix->s_out2.p, Q * 8, cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  return RS_STATUS_OK;
+}
+
+int rs_find_interval_batch(const rs_index* ix, const char* kmers, int k, size_t Q, uint64_t* lower, uint64_t* upper) {
+  return find_host(ix, kmers, nullptr, k, Q, lower, upper, 0, 0);
+}
+
+int rs_find_interval_var_batch(const rs_index* ix, const char* text, const uint64_t* offsets, size_t Q,
+                               uint64_t* lower, uint64_t* upper) {
+  if (Q && !offsets) return fail(RS_STATUS_ARG, "null offsets");
+  return find_host(ix, text, offsets, 0, Q, lower, upper, 0, 0);
+}
+
+int rs_count_batch(const rs_index* ix, const char* kmers, int k, size_t Q, int strand, uint64_t* counts) {
+  if (strand != 0 && strand != 1) return fail(RS_STATUS_ARG, "strand must be 0 (forward) or 1 (reverse complement)");
+  return find_host(ix, kmers, nullptr, k, Q, counts, nullptr, 1, strand);
+}
+
+/* ---- device-pointer calls ---- */
+int rs_find_interval_batch_dev(const rs_index* ix, const void* d_kmers, int k, size_t Q, void* d_lower, void* d_upper,
+                               void* stream) {
+  if (!ix || (Q && (!d_kmers || !d_lower || !d_upper))) return fail(RS_STATUS_ARG, "null argument");
+  if (k < 1) return fail(RS_STATUS_ARG, "k must be >= 1 (empty query: SURVEY.md Q3)");
+  CU(rs_launch_find_interval(ix->dev, (const uint8_t*)d_kmers, nullptr, (uint32_t)k, Q, (uint64_t*)d_lower,
+                             (uint64_t*)d_upper, 0, 0, (unsigned long long*)ix->d_stats, (cudaStream_t)stream));
+  return RS_STATUS_OK;
+}
+
+int rs_find_interval_var_batch_dev(const rs_index* ix, const void* d_text, const void* d_offsets, size_t Q,
+                                   void* d_lower, void* d_upper, void* stream) {
+  if (!ix || (Q && (!d_text || !d_offsets || !d_lower || !d_upper))) return fail(RS_STATUS_ARG, "null argument");
+  CU(rs_launch_find_interval(ix->dev, (const uint8_t*)d_text, (const uint64_t*)d_offsets, 0, Q, (uint64_t*)d_lower,
+                             (uint64_t*)d_upper, 0, 0, (unsigned long long*)ix->d_stats, (cudaStream_t)stream));
+  return RS_STATUS_OK;
+}
+
+int rs_count_batch_dev(const rs_index* ix, const void* d_kmers, int k, size_t Q, int strand, void* d_counts,
+                       void* stream) {
+  if (!ix || (Q && (!d_kmers || !d_counts))) return fail(RS_STATUS_ARG, "null argument");
+  if (k < 1) return fail(RS_STATUS_ARG, "k must be >= 1");
+  if (strand != 0 && strand != 1) return fail(RS_STATUS_ARG, "strand must be 0 or 1");
+  CU(rs_launch_find_interval(ix->dev, (const uint8_t*)d_kmers, nullptr, (uint32_t)k, Q, (uint64_t*)d_counts, nullptr, 1,
+                             strand, (unsigned long long*)ix->d_stats, (cudaStream_t)stream));
+  return RS_STATUS_OK;
+}
+
+/* ---- locate ---- */
+int rs_index_set_sai(rs_index* ix, const uint64_t* sai, uint64_t num_strings) {
+  if (!ix || !sai) return fail(RS_STATUS_ARG, "null argument");
+  if (num_strings != ix->dev.num_strings)
+    return fail(RS_STATUS_ARG, "sai has %llu entries, the index holds %llu strings", (unsigned long long)num_strings,
+                (unsigned long long)ix->dev.num_strings);
+  std::lock_guard<std::mutex> lk(ix->mu);
+  CU(cudaSetDevice(ix->device));
+  if (ix->d_sai) {
+    cudaFree(ix->d_sai);
+    ix->hbm_bytes -= num_strings * 8;
+    ix->d_sai = nullptr;
+  }
+  CU(cudaMalloc((void**)&ix->d_sai, num_strings ? num_strings * 8 : 8));
+  CU(cudaMemcpy(ix->d_sai, sai, num_strings * 8, cudaMemcpyHostToDevice));
+  ix->hbm_bytes += num_strings * 8;
+  return RS_STATUS_OK;
+}
+
+int rs_extract_prefix_batch_dev(const rs_index* ix, const void* d_rows, size_t n, uint32_t max_steps, void* d_lexrank,
+                                void* d_steps, void* d_read_index, void* d_bases, void* stream) {
+  if (!ix || (n && !d_rows)) return fail(RS_STATUS_ARG, "null argument");
+  if (d_read_index && !ix->d_sai) return fail(RS_STATUS_NO_TABLE, "read_index requested but no .sai table attached");
+  if (max_steps < 1) return fail(RS_STATUS_ARG, "max_steps must be >= 1");
+  CU(rs_launch_extract_prefix(ix->dev, (const uint64_t*)d_rows, n, max_steps, (uint64_t*)d_lexrank, (uint32_t*)d_steps,
+                              ix->d_sai, (uint64_t*)d_read_index, (uint8_t*)d_bases, (unsigned long long*)ix->d_stats,
+                              (cudaStream_t)stream));
+  return RS_STATUS_OK;
+}
+
+int rs_extract_prefix_batch(const rs_index* ix, const uint64_t* rows, size_t n, uint32_t max_steps, uint64_t* lexrank,
+                            uint32_t* steps, uint64_t* read_index, char* bases) {
+  if (!ix || (n && !rows)) return fail(RS_STATUS_ARG, "null argument");
+  if (read_index && !ix->d_sai) return fail(RS_STATUS_NO_TABLE, "read_index requested but no .sai table attached");
+  if (max_steps < 1) return fail(RS_STATUS_ARG, "max_steps must be >= 1");
+  if (!n) return RS_STATUS_OK;
+  std::lock_guard<std::mutex> lk(ix->mu);
+  CU(cudaSetDevice(ix->device));
+  CU(ix->s_in.need(n * 8));
+  CU(ix->s_out.need(n * 8));
+  CU(ix->s_out2.need(n * 4));
+  if (read_index) CU(ix->s_out3.need(n * 8));
+  if (bases) CU(ix->s_out4.need(n * (size_t)max_steps));
+  cudaStream_t st = ix->stream;
+  CU(cudaMemcpyAsync(ix->s_in.p, rows, n * 8, cudaMemcpyHostToDevice, st));
+  CU(rs_launch_extract_prefix(ix->dev, (const uint64_t*)ix->s_in.p, n, max_steps, (uint64_t*)ix->s_out.p,
+                              (uint32_t*)ix->s_out2.p, ix->d_sai, read_index ? (uint64_t*)ix->s_out3.p : nullptr,
+                              bases ? (uint8_t*)ix->s_out4.p : nullptr, nullptr, st));
+  if (lexrank) CU(cudaMemcpyAsync(lexrank, ix->s_out.p, n * 8, cudaMemcpyDeviceToHost, st));
+  if (steps) CU(cudaMemcpyAsync(steps, ix->s_out2.p, n * 4, cudaMemcpyDeviceToHost, st));
+  if (read_index) CU(cudaMemcpyAsync(read_index, ix->s_out3.p, n * 8, cudaMemcpyDeviceToHost, st));
+  if (bases) CU(cudaMemcpyAsync(bases, ix->s_out4.p, n * (size_t)max_steps, cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  return RS_STATUS_OK;
+}

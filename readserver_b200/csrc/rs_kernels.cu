@@ -1,0 +1,259 @@
+/* sm_100a kernels of the FM-index hot path.  One lane group (8 lanes) per query / walker; each rank
+ * is one coalesced 128-byte block load + SWAR decode + shuffle scan (rs_device.cuh).
+ *
+ *   k_find_interval   findInterval            src/bwt/query.cpp:24-41   (K1)
+ *   k_extract_prefix  extractPrefix           src/bwt/query.cpp:43-63   (K2)
+ *   k_occ / k_char    RLEBWT::getOcc/getChar  src/bwt/rlebwt.cpp:202-301
+ */
+#include "rs_kernels.h"
+
+#include "rs_device.cuh"
+
+#define RS_FULL 0xFFFFFFFFu
+
+/* alphabet.h:11-32: A,C,G,T -> 1..4, every other byte -> 0 ('$') */
+__device__ __forceinline__ uint32_t rs_code(uint32_t ch) {
+  return ch == 'A' ? 1u : ch == 'C' ? 2u : ch == 'G' ? 3u : ch == 'T' ? 4u : 0u;
+}
+__device__ __forceinline__ char rs_ascii(uint32_t code) { return "$ACGT"[code]; }
+
+__global__ void __launch_bounds__(RS_THREADS) k_occ(const __grid_constant__ rs_index_dev ix, const uint8_t* __restrict__ syms,
+                                                    const uint64_t* __restrict__ idx, uint64_t n,
+                                                    uint64_t* __restrict__ out) {
+  const rs_grp G = rs_grp_init();
+  const uint64_t ngroups = (uint64_t)gridDim.x * (RS_THREADS / RS_GROUP);
+  for (uint64_t i = (uint64_t)blockIdx.x * (RS_THREADS / RS_GROUP) + threadIdx.x / RS_GROUP; i < n; i += ngroups) {
+    const uint64_t r = rs_grp_occ(ix, G, rs_code(syms[i]), idx[i]);
+    if (G.g == 0) out[i] = r;
+  }
+}
+
+__global__ void __launch_bounds__(RS_THREADS) k_char(const __grid_constant__ rs_index_dev ix, const uint64_t* __restrict__ idx,
+                                                     uint64_t n, uint8_t* __restrict__ out) {
+  const rs_grp G = rs_grp_init();
+  const uint64_t ngroups = (uint64_t)gridDim.x * (RS_THREADS / RS_GROUP);
+  for (uint64_t i = (uint64_t)blockIdx.x * (RS_THREADS / RS_GROUP) + threadIdx.x / RS_GROUP; i < n; i += ngroups) {
+    const uint32_t s = rs_grp_char(ix, G, idx[i]);
+    if (G.g == 0) out[i] = (uint8_t)rs_ascii(s);
+  }
+}
+
+/* getF (rlebwt.cpp:307-314): last symbol whose C[] value is <= index. One thread per item. */
+__global__ void k_getf(const __grid_constant__ rs_index_dev ix, const uint64_t* __restrict__ idx, uint64_t n,
+                       uint8_t* __restrict__ out) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  const uint64_t v = idx[i];
+  uint32_t ci = 0;
+  while (ci < RS_NSYM && ix.pc[ci] <= v) ++ci;
+  out[i] = (uint8_t)rs_ascii(ci - 1);
+}
+
+/* K1.  Each group owns one query at a time and all groups of a warp advance one backward-search
+ * step per loop trip, whatever query they are on: a group whose query ends (all characters consumed,
+ * or the interval went empty: query.cpp:35-37) picks up its next query on the following trip, so
+ * lanes never idle behind a longer neighbour.
+ *   mode 0: write lower/upper.   mode 1: write counts (count_reads, service.cpp:279-315), strand as given. */
+__global__ void __launch_bounds__(RS_THREADS)
+    k_find_interval(const __grid_constant__ rs_index_dev ix, const uint8_t* __restrict__ text,
+                    const uint64_t* __restrict__ offs, uint32_t k, uint64_t Q, uint64_t* __restrict__ lower,
+                    uint64_t* __restrict__ upper, int mode, int strand, unsigned long long* __restrict__ stats) {
+  const rs_grp G = rs_grp_init();
+  const uint64_t ngroups = (uint64_t)gridDim.x * (RS_THREADS / RS_GROUP);
+  uint64_t next_q = (uint64_t)blockIdx.x * (RS_THREADS / RS_GROUP) + threadIdx.x / RS_GROUP;
+  uint64_t q = 0, base = 0, lo = 0, hi = 0;
+  int64_t j = -1;     /* characters still to consume (index of the next one in search order) */
+  uint32_t len = 0;
+  bool active = false;
+  const bool rc = (mode == 1 && strand == 1);
+  unsigned long long nsteps = 0; /* updateInterval calls executed by this group (2 ranks each) */
+
+  while (true) {
+    if (!active && next_q < Q) {
+      q = next_q;
+      next_q += ngroups;
+      if (offs) {
+        base = offs[q];
+        len = (uint32_t)(offs[q + 1] - base);
+      } else {
+        base = q * (uint64_t)k;
+        len = k;
+      }
+      active = true;
+      bool bad = (len == 0);
+      if (mode == 1) { /* any byte outside ACGT -> count 0 (service.cpp:299-301) */
+        for (uint32_t t = G.g; t < len; t += RS_GROUP) bad |= (rs_code(text[base + t]) == 0);
+        bad = __ballot_sync(G.mask, bad) & G.mask;
+      }
+      if (bad) {
+        if (G.g == 0) {
+          if (mode == 1) lower[q] = 0;
+          else { lower[q] = 1; upper[q] = 0; }
+        }
+        active = false;
+      } else {
+        /* initInterval (query.cpp:18-21) on the last character of the searched string */
+        const uint32_t ch = rc ? text[base] : text[base + len - 1];
+        const uint32_t c = rc ? (5u - rs_code(ch)) : rs_code(ch);
+        lo = ix.pc[c];
+        hi = lo + ix.init_occ[c] - 1;
+        j = (int64_t)len - 2;
+        if (j < 0) {
+          if (G.g == 0) {
+            if (mode == 1) lower[q] = hi >= lo ? hi - lo + 1 : 0;
+            else { lower[q] = lo; upper[q] = hi; }
+          }
+          active = false;
+        }
+      }
+    }
+    if (__all_sync(RS_FULL, !active)) {
+      if (__all_sync(RS_FULL, next_q >= Q)) break;
+      continue;
+    }
+    if (active) {
+      /* updateInterval (query.cpp:11-15).  Reverse complement: the searched string is
+       * revcomp(w), whose character at search index j is the complement of w[len-1-j]. */
+      const uint32_t ch = rc ? text[base + (len - 1 - j)] : text[base + j];
+      const uint32_t c = rc ? (5u - rs_code(ch)) : rs_code(ch);
+      uint64_t r1, r2;
+      rs_grp_occ2(ix, G, c, lo - 1, hi, &r1, &r2);
+      ++nsteps;
+      const uint64_t pb = ix.pc[c];
+      lo = pb + r1;
+      hi = pb + r2 - 1;
+      --j;
+      if (lo > hi || j < 0) {
+        if (G.g == 0) {
+          if (mode == 1) lower[q] = hi >= lo ? hi - lo + 1 : 0;
+          else { lower[q] = lo; upper[q] = hi; }
+        }
+        active = false;
+      }
+    }
+  }
+  if (stats && G.g == 0 && nsteps) atomicAdd(stats, nsteps);
+}
+
+/* K2.  extractPrefix (query.cpp:43-63): LF-walk from each row to its '$'.  Same step-interleaved
+ * scheme as K1: a group whose walk ends takes its next row on the following trip. */
+__global__ void __launch_bounds__(RS_THREADS)
+    k_extract_prefix(const __grid_constant__ rs_index_dev ix, const uint64_t* __restrict__ rows, uint64_t n,
+                     uint32_t max_steps, uint64_t* __restrict__ lexrank, uint32_t* __restrict__ steps,
+                     const uint64_t* __restrict__ sai, uint64_t* __restrict__ read_index, uint8_t* __restrict__ bases,
+                     unsigned long long* __restrict__ stats) {
+  const rs_grp G = rs_grp_init();
+  const uint64_t ngroups = (uint64_t)gridDim.x * (RS_THREADS / RS_GROUP);
+  unsigned long long lf_steps = 0;
+  uint64_t next_i = (uint64_t)blockIdx.x * (RS_THREADS / RS_GROUP) + threadIdx.x / RS_GROUP;
+  uint64_t i = 0, idx = 0;
+  uint32_t s = 0;
+  bool active = false;
+  while (true) {
+    if (!active && next_i < n) {
+      i = next_i;
+      next_i += ngroups;
+      idx = rows[i];
+      s = 0;
+      active = true;
+    }
+    if (__all_sync(RS_FULL, !active)) break;
+    if (active) {
+      uint64_t nxt;
+      const uint32_t sym = rs_grp_lf_step(ix, G, idx, &nxt);
+      ++lf_steps;
+      idx = nxt;
+      bool done = false;
+      uint64_t term = 0;
+      uint32_t nsteps = 0;
+      if (sym == 0) {
+        done = true;
+        term = idx;
+        nsteps = s;
+      } else {
+        if (bases && s < max_steps && G.g == 0) bases[i * (uint64_t)max_steps + s] = (uint8_t)rs_ascii(sym);
+        ++s;
+        if (s > max_steps) { /* the reference would never return (walk cycling in its tail region) */
+          done = true;
+          term = ~0ull;
+          nsteps = 0xFFFFFFFFu;
+        }
+      }
+      if (done) {
+        if (G.g == 0) {
+          if (lexrank) lexrank[i] = term;
+          if (steps) steps[i] = nsteps;
+          if (read_index) read_index[i] = (term != ~0ull && term < ix.num_strings) ? sai[term] : ~0ull;
+        }
+        if (bases) { /* std::reverse (query.cpp:60): the walk produced the prefix back to front */
+          uint8_t* p = bases + i * (uint64_t)max_steps;
+          const uint32_t m = nsteps == 0xFFFFFFFFu ? 0u : nsteps;
+          __syncwarp(G.mask);
+          for (uint32_t a = G.g; a < m / 2; a += RS_GROUP) {
+            const uint8_t t = p[a];
+            p[a] = p[m - 1 - a];
+            p[m - 1 - a] = t;
+          }
+          for (uint32_t a = m + G.g; a < max_steps; a += RS_GROUP) p[a] = 0;
+        }
+        active = false;
+      }
+    }
+  }
+  if (stats && G.g == 0 && lf_steps) atomicAdd(stats + 1, lf_steps);
+}
+
+/* ---- launchers ---- */
+static int rs_grid_for(const void* kernel, uint64_t work_groups) {
+  static int sms = 0;
+  if (!sms) {
+    int dev = 0;
+    cudaGetDevice(&dev);
+    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+    if (sms <= 0) sms = 148;
+  }
+  int per_sm = 0;
+  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, RS_THREADS, 0);
+  if (per_sm < 1) per_sm = 1;
+  uint64_t grid = (uint64_t)sms * per_sm; /* one resident wave, a multiple of the SM count */
+  const uint64_t need = (work_groups + (RS_THREADS / RS_GROUP) - 1) / (RS_THREADS / RS_GROUP);
+  if (need < grid) grid = need;
+  return grid ? (int)grid : 1;
+}
+
+cudaError_t rs_launch_occ(const rs_index_dev& ix, const uint8_t* syms, const uint64_t* idx, uint64_t n, uint64_t* out,
+                          cudaStream_t st) {
+  if (!n) return cudaSuccess;
+  k_occ<<<rs_grid_for((const void*)k_occ, n), RS_THREADS, 0, st>>>(ix, syms, idx, n, out);
+  return cudaGetLastError();
+}
+
+cudaError_t rs_launch_char(const rs_index_dev& ix, const uint64_t* idx, uint64_t n, uint8_t* out, cudaStream_t st) {
+  if (!n) return cudaSuccess;
+  k_char<<<rs_grid_for((const void*)k_char, n), RS_THREADS, 0, st>>>(ix, idx, n, out);
+  return cudaGetLastError();
+}
+
+cudaError_t rs_launch_getf(const rs_index_dev& ix, const uint64_t* idx, uint64_t n, uint8_t* out, cudaStream_t st) {
+  if (!n) return cudaSuccess;
+  k_getf<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(ix, idx, n, out);
+  return cudaGetLastError();
+}
+
+cudaError_t rs_launch_find_interval(const rs_index_dev& ix, const uint8_t* text, const uint64_t* offs, uint32_t k,
+                                    uint64_t Q, uint64_t* lower, uint64_t* upper, int mode, int strand,
+                                    unsigned long long* stats, cudaStream_t st) {
+  if (!Q) return cudaSuccess;
+  k_find_interval<<<rs_grid_for((const void*)k_find_interval, Q), RS_THREADS, 0, st>>>(ix, text, offs, k, Q, lower,
+                                                                                      upper, mode, strand, stats);
+  return cudaGetLastError();
+}
+
+cudaError_t rs_launch_extract_prefix(const rs_index_dev& ix, const uint64_t* rows, uint64_t n, uint32_t max_steps,
+                                     uint64_t* lexrank, uint32_t* steps, const uint64_t* sai, uint64_t* read_index,
+                                     uint8_t* bases, unsigned long long* stats, cudaStream_t st) {
+  if (!n) return cudaSuccess;
+  k_extract_prefix<<<rs_grid_for((const void*)k_extract_prefix, n), RS_THREADS, 0, st>>>(
+      ix, rows, n, max_steps, lexrank, steps, sai, read_index, bases, stats);
+  return cudaGetLastError();
+}

@@ -1,0 +1,25 @@
+/* Launchers of the sm_100a kernels (rs_kernels.cu); device pointers, stream-ordered. */
+#ifndef RS_KERNELS_H
+#define RS_KERNELS_H
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "rs_layout.h"
+
+#define RS_THREADS 256 /* 8 warps = 32 lane groups per CTA */
+
+cudaError_t rs_launch_occ(const rs_index_dev& ix, const uint8_t* syms, const uint64_t* idx, uint64_t n, uint64_t* out,
+                          cudaStream_t st);
+cudaError_t rs_launch_char(const rs_index_dev& ix, const uint64_t* idx, uint64_t n, uint8_t* out, cudaStream_t st);
+cudaError_t rs_launch_getf(const rs_index_dev& ix, const uint64_t* idx, uint64_t n, uint8_t* out, cudaStream_t st);
+/* mode 0: lower/upper; mode 1: counts into `lower` (strand 0 forward, 1 reverse complement);
+ * stats (nullable): += number of updateInterval steps executed (2 ranks each) */
+cudaError_t rs_launch_find_interval(const rs_index_dev& ix, const uint8_t* text, const uint64_t* offs, uint32_t k,
+                                    uint64_t Q, uint64_t* lower, uint64_t* upper, int mode, int strand,
+                                    unsigned long long* stats, cudaStream_t st);
+cudaError_t rs_launch_extract_prefix(const rs_index_dev& ix, const uint64_t* rows, uint64_t n, uint32_t max_steps,
+                                     uint64_t* lexrank, uint32_t* steps, const uint64_t* sai, uint64_t* read_index,
+                                     uint8_t* bases, unsigned long long* stats, cudaStream_t st);
+
+#endif

@@ -1,0 +1,70 @@
+/* HBM layout of one population-BWT shard (shared by the host builder and the sm_100a kernels).
+ *
+ * Replaces the reference's RLVector + multi-level BP-tree (include/bwt/rlunit.h:8-89,
+ * include/bwt/BPTree.h:20-206, BPNodes.h:34-241, built by src/bwt/rlebwt.cpp:34-148) with a flat
+ * array of 128-byte blocks -- one L2 line / one coalesced 8 x 16 B lane-group load per rank -- and a
+ * position directory that resolves "symbol position -> block" in one 8-byte read.
+ *
+ *   block (128 B, 128-B aligned)
+ *     +0   u64 start            symbols before this block
+ *     +8   u64 cnt[4]           occurrences of A,C,G,T before this block ('$' = start - sum)
+ *     +40  u8  runs[88]         SGA run bytes  sym<<5 | len  (rlunit.h:8-16), 0x00 = padding
+ *
+ *   position directory: one u64 per 2^RS_SLOT_SHIFT symbols
+ *     bits  0..31  index of the block holding the slot's first symbol
+ *     bits 32..41  b1  offset inside the slot at which block +1 starts (0 = no such boundary)
+ *     bits 42..51  b2  ... block +2
+ *     bits 52..61  b3  ... block +3
+ *     bit  62      more than three block boundaries fall inside the slot (walk forward from +3)
+ *
+ *   select directory (per symbol c): one u32 per 2^RS_SEL_SHIFT occurrences of c
+ *     entry k = index of the block holding the (k << RS_SEL_SHIFT | 1)-th occurrence of c,
+ *     i.e. the last block whose cnt[c] <= k << RS_SEL_SHIFT.
+ */
+#ifndef RS_LAYOUT_H
+#define RS_LAYOUT_H
+
+#include <stdint.h>
+
+#define RS_BLOCK_BYTES 128
+#define RS_HDR_BYTES 40
+#define RS_PAYLOAD 88
+#define RS_SLOT_SHIFT 10
+#define RS_SLOT_SIZE (1u << RS_SLOT_SHIFT)
+#define RS_SLOT_MASK (RS_SLOT_SIZE - 1u)
+#define RS_DIR_MORE (1ull << 62)
+#define RS_SEL_SHIFT 10
+#define RS_NSYM 5
+#define RS_GROUP 8 /* lanes per query: 8 x 16 B = one block */
+#define RS_NO_ROW 0xFFFFFFFFFFFFFFFFull
+
+typedef struct rs_block {
+  uint64_t start;
+  uint64_t cnt[4];
+  uint8_t runs[RS_PAYLOAD];
+} rs_block;
+
+/* Everything a kernel needs, passed by value as a __grid_constant__ parameter. */
+typedef struct rs_index_dev {
+  const void* blocks;        /* rs_block[nblocks]                                              */
+  const uint64_t* dir;       /* position directory, ndir entries                                */
+  const uint32_t* sel[RS_NSYM]; /* select directories                                           */
+  uint64_t n;                /* BWT length in symbols (getBWLen)                                */
+  uint64_t nblocks;
+  uint64_t num_strings;
+  uint64_t pc[RS_NSYM];      /* C[] array: getPC (rlebwt.cpp:229-231)                           */
+  uint64_t tot[RS_NSYM];     /* occurrences of each symbol in the whole BWT                     */
+  uint64_t init_occ[RS_NSYM];/* what the reference's getOcc(c, n-1) returns (initInterval)      */
+  /* Reference tail behaviour (BPTree.h:74-94, 135-157): for positions i with
+   * ((i+1) >> 16) >= vlast and i >= clamp the reference answers as if i were clamp - 1.
+   * rank (getOcc) is confined to the top-level bucket of the last m_vSum hint; access (getChar)
+   * to the first bucket on that hint's path whose index is non-zero (BPTree.h:148-151 tests
+   * `offset == 0`), which is a deeper, smaller bucket when the top-level index is 0. */
+  uint64_t clamp_c;          /* getOcc  */
+  uint64_t clamp_char;       /* getChar */
+  uint64_t vlast;
+  uint32_t emulate_tail;     /* 1 = bit-exact with the reference (default), 0 = true rank       */
+  uint32_t pad_;
+} rs_index_dev;
+
+#endif

@@ -1,0 +1,254 @@
+"""Host-side mirror of the reference's BWT interface over the C-ABI library (``librs_b200.so``).
+
+``GpuBWT`` mirrors ``class BWT`` / ``RLEBWT`` (``/root/reference/include/bwt/bwt.h:6-15``,
+``rlebwt.h:15-61``) and the free functions of ``include/bwt/query.h:18-32`` -- same names (snake
+case), argument meaning and results -- in batched form.  Every call goes through the C ABI declared
+in ``include/readserver_b200.h``; nothing here computes on the CPU and there is no fallback: if the
+library is missing or no CUDA device is present, construction raises.
+
+torch is used only as plumbing (device buffers and streams for the ``*_dev`` calls).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import build as _build
+
+_u8p = np.ctypeslib.ndpointer(dtype=np.uint8, flags="C_CONTIGUOUS")
+_u32p = np.ctypeslib.ndpointer(dtype=np.uint32, flags="C_CONTIGUOUS")
+_u64p = np.ctypeslib.ndpointer(dtype=np.uint64, flags="C_CONTIGUOUS")
+
+STATUS = {0: "OK", 1: "OPEN", 2: "MAGIC", 3: "SHORT", 4: "RUNBYTE", 5: "ARG", 6: "CUDA", 7: "TOO_LARGE", 8: "NO_TABLE"}
+
+
+class RsError(RuntimeError):
+    def __init__(self, status: int, msg: str):
+        super().__init__(f"readserver_b200: status {status} ({STATUS.get(status, '?')}): {msg}")
+        self.status = status
+
+
+class Info(C.Structure):
+    _fields_ = [("bwlen", C.c_uint64), ("num_strings", C.c_uint64), ("num_runs", C.c_uint64),
+                ("num_blocks", C.c_uint64), ("hbm_bytes", C.c_uint64), ("pc", C.c_uint64 * 5),
+                ("total", C.c_uint64 * 5), ("ref_depth", C.c_uint64), ("ref_clamp_c", C.c_uint64),
+                ("ref_vlast", C.c_uint64), ("q2_safe", C.c_int32), ("device", C.c_int32)]
+
+
+_LIB = None
+
+
+def lib() -> C.CDLL:
+    """Loads (building if stale and nvcc is present) the C-ABI library. Raises if it cannot."""
+    global _LIB
+    if _LIB is not None:
+        return _LIB
+    path = _build.LIB
+    if not os.path.exists(path):
+        path = _build.build()
+    L = C.CDLL(path)
+    vp, sz, u64, i32 = C.c_void_p, C.c_size_t, C.c_uint64, C.c_int
+    sig = {
+        "rs_index_open": (i32, [C.c_char_p, i32, C.POINTER(vp)]),
+        "rs_index_from_runs": (i32, [vp, u64, u64, u64, i32, C.POINTER(vp)]),
+        "rs_index_close": (None, [vp]),
+        "rs_index_get_info": (i32, [vp, C.POINTER(Info)]),
+        "rs_index_set_tail_emulation": (i32, [vp, i32]),
+        "rs_index_enable_stats": (i32, [vp, i32]),
+        "rs_index_read_stats": (i32, [vp, C.POINTER(u64), C.POINTER(u64), i32]),
+        "rs_last_error": (C.c_char_p, []),
+        "rs_host_alloc": (i32, [C.POINTER(vp), sz]),
+        "rs_host_free": (None, [vp]),
+        "rs_get_pc": (u64, [vp, C.c_char]),
+        "rs_get_bwlen": (u64, [vp]),
+        "rs_get_occ_batch": (i32, [vp, vp, vp, sz, vp]),
+        "rs_get_char_batch": (i32, [vp, vp, sz, vp]),
+        "rs_get_f_batch": (i32, [vp, vp, sz, vp]),
+        "rs_find_interval_batch": (i32, [vp, vp, i32, sz, vp, vp]),
+        "rs_find_interval_var_batch": (i32, [vp, vp, vp, sz, vp, vp]),
+        "rs_find_interval_batch_dev": (i32, [vp, vp, i32, sz, vp, vp, vp]),
+        "rs_find_interval_var_batch_dev": (i32, [vp, vp, vp, sz, vp, vp, vp]),
+        "rs_count_batch": (i32, [vp, vp, i32, sz, i32, vp]),
+        "rs_count_batch_dev": (i32, [vp, vp, i32, sz, i32, vp, vp]),
+        "rs_index_set_sai": (i32, [vp, vp, u64]),
+        "rs_extract_prefix_batch": (i32, [vp, vp, sz, C.c_uint32, vp, vp, vp, vp]),
+        "rs_extract_prefix_batch_dev": (i32, [vp, vp, sz, C.c_uint32, vp, vp, vp, vp, vp]),
+    }
+    for name, (res, args) in sig.items():
+        f = getattr(L, name)
+        f.restype = res
+        f.argtypes = args
+    _LIB = L
+    return L
+
+
+def _check(rc: int):
+    if rc != 0:
+        raise RsError(rc, (lib().rs_last_error() or b"").decode("utf-8", "replace"))
+
+
+def _ptr(a) -> int:
+    """Address of a numpy array / torch tensor / None."""
+    if a is None:
+        return None
+    if isinstance(a, np.ndarray):
+        return a.ctypes.data
+    return a.data_ptr()  # torch tensor
+
+
+def _ascii(a) -> np.ndarray:
+    if isinstance(a, str):
+        a = a.encode()
+    if isinstance(a, (bytes, bytearray)):
+        return np.frombuffer(bytes(a), dtype=np.uint8)
+    return np.ascontiguousarray(a, dtype=np.uint8)
+
+
+class GpuBWT:
+    """One BWT shard resident in the HBM of one B200 (``RLEBWT``, rlebwt.cpp:11-32)."""
+
+    def __init__(self, bwt_path: str | None = None, *, runs=None, num_strings: int = 0, num_symbols: int = 0,
+                 device: int = 0):
+        L = lib()
+        h = C.c_void_p()
+        if bwt_path is not None:
+            _check(L.rs_index_open(os.fsencode(bwt_path), device, C.byref(h)))
+        else:
+            runs = np.ascontiguousarray(runs, dtype=np.uint8)
+            _check(L.rs_index_from_runs(runs.ctypes.data, runs.size, num_strings, num_symbols, device, C.byref(h)))
+        self._h = h
+        self.device = device
+        info = Info()
+        _check(L.rs_index_get_info(h, C.byref(info)))
+        self.info = info
+
+    # -- lifecycle -------------------------------------------------------------------------------
+    def close(self):
+        h = getattr(self, "_h", None)
+        if h:
+            lib().rs_index_close(h)
+            self._h = None
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def set_tail_emulation(self, on: bool):
+        _check(lib().rs_index_set_tail_emulation(self._h, int(on)))
+
+    def enable_stats(self, on: bool = True):
+        _check(lib().rs_index_enable_stats(self._h, int(on)))
+
+    def read_stats(self, reset: bool = True) -> tuple[int, int]:
+        """(updateInterval steps, LF-walk steps) executed by the *_dev calls since the last reset."""
+        a, b = C.c_uint64(), C.c_uint64()
+        _check(lib().rs_index_read_stats(self._h, C.byref(a), C.byref(b), int(reset)))
+        return int(a.value), int(b.value)
+
+    def set_sai(self, sai):
+        sai = np.ascontiguousarray(sai, dtype=np.uint64)
+        _check(lib().rs_index_set_sai(self._h, sai.ctypes.data, sai.size))
+
+    # -- class BWT -------------------------------------------------------------------------------
+    def get_bwlen(self) -> int:
+        return int(lib().rs_get_bwlen(self._h))
+
+    def get_pc(self, b) -> int:
+        b = b.encode() if isinstance(b, str) else bytes([b]) if isinstance(b, int) else b
+        return int(lib().rs_get_pc(self._h, b))
+
+    def get_occ(self, b, index) -> np.ndarray:
+        b = _ascii(b)
+        index = np.ascontiguousarray(index, dtype=np.uint64)
+        if b.size == 1 and index.size != 1:
+            b = np.full(index.size, b[0], dtype=np.uint8)
+        assert b.size == index.size
+        out = np.empty(index.size, dtype=np.uint64)
+        _check(lib().rs_get_occ_batch(self._h, b.ctypes.data, index.ctypes.data, index.size, out.ctypes.data))
+        return out
+
+    def get_char(self, index) -> np.ndarray:
+        index = np.ascontiguousarray(index, dtype=np.uint64)
+        out = np.empty(index.size, dtype=np.uint8)
+        _check(lib().rs_get_char_batch(self._h, index.ctypes.data, index.size, out.ctypes.data))
+        return out
+
+    def get_f(self, index) -> np.ndarray:
+        index = np.ascontiguousarray(index, dtype=np.uint64)
+        out = np.empty(index.size, dtype=np.uint8)
+        _check(lib().rs_get_f_batch(self._h, index.ctypes.data, index.size, out.ctypes.data))
+        return out
+
+    # -- query.h ---------------------------------------------------------------------------------
+    def find_interval(self, kmers, k: int | None = None):
+        """findInterval for a [Q, k] uint8 ASCII array (or a single str). Returns (lower, upper) uint64."""
+        if isinstance(kmers, str):
+            k = len(kmers)
+        kmers = _ascii(kmers)
+        if k is None:
+            k = kmers.shape[-1]
+        flat = kmers.reshape(-1)
+        if k < 1 or flat.size % k:
+            raise RsError(5, "k-mer array size is not a multiple of k")
+        q = flat.size // k
+        lo = np.empty(q, dtype=np.uint64)
+        up = np.empty(q, dtype=np.uint64)
+        _check(lib().rs_find_interval_batch(self._h, flat.ctypes.data, k, q, lo.ctypes.data, up.ctypes.data))
+        return lo, up
+
+    def find_interval_var(self, strings: list[str]):
+        text = np.frombuffer("".join(strings).encode(), dtype=np.uint8)
+        offs = np.zeros(len(strings) + 1, dtype=np.uint64)
+        np.cumsum([len(s) for s in strings], out=offs[1:])
+        lo = np.empty(len(strings), dtype=np.uint64)
+        up = np.empty(len(strings), dtype=np.uint64)
+        text = np.ascontiguousarray(text) if text.size else np.zeros(1, dtype=np.uint8)
+        _check(lib().rs_find_interval_var_batch(self._h, text.ctypes.data, offs.ctypes.data, len(strings),
+                                                lo.ctypes.data, up.ctypes.data))
+        return lo, up
+
+    def count(self, kmers, k: int | None = None, strand: int = 0) -> np.ndarray:
+        """count_reads (service.cpp:279-315): matching rows per k-mer on one strand."""
+        kmers = _ascii(kmers)
+        if k is None:
+            k = kmers.shape[-1]
+        flat = kmers.reshape(-1)
+        q = flat.size // k
+        out = np.empty(q, dtype=np.uint64)
+        _check(lib().rs_count_batch(self._h, flat.ctypes.data, k, q, strand, out.ctypes.data))
+        return out
+
+    def extract_prefix(self, rows, max_steps: int = 1024, want_bases: bool = False, want_read_index: bool = False):
+        """extractPrefix (query.cpp:43-63) per row: (lexrank, steps[, read_index][, bases [n, max_steps]])."""
+        rows = np.ascontiguousarray(rows, dtype=np.uint64)
+        n = rows.size
+        lex = np.empty(n, dtype=np.uint64)
+        st = np.empty(n, dtype=np.uint32)
+        ri = np.empty(n, dtype=np.uint64) if want_read_index else None
+        bases = np.zeros((n, max_steps), dtype=np.uint8) if want_bases else None
+        _check(lib().rs_extract_prefix_batch(self._h, rows.ctypes.data, n, max_steps, lex.ctypes.data, st.ctypes.data,
+                                             _ptr(ri), _ptr(bases)))
+        out = [lex, st]
+        if want_read_index:
+            out.append(ri)
+        if want_bases:
+            out.append(bases)
+        return tuple(out)
+
+    # -- device-pointer forms (torch tensors on self.device; asynchronous on `stream`) -------------
+    def find_interval_dev(self, d_kmers, k: int, q: int, d_lower, d_upper, stream: int = 0):
+        _check(lib().rs_find_interval_batch_dev(self._h, _ptr(d_kmers), k, q, _ptr(d_lower), _ptr(d_upper), stream))
+
+    def count_dev(self, d_kmers, k: int, q: int, strand: int, d_counts, stream: int = 0):
+        _check(lib().rs_count_batch_dev(self._h, _ptr(d_kmers), k, q, strand, _ptr(d_counts), stream))
+
+    def extract_prefix_dev(self, d_rows, n: int, max_steps: int, d_lexrank=None, d_steps=None, d_read_index=None,
+                           d_bases=None, stream: int = 0):
+        _check(lib().rs_extract_prefix_batch_dev(self._h, _ptr(d_rows), n, max_steps, _ptr(d_lexrank), _ptr(d_steps),
+                                                 _ptr(d_read_index), _ptr(d_bases), stream))

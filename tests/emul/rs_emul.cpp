@@ -1,0 +1,263 @@
+// TEST INFRASTRUCTURE ONLY -- never part of the product library.
+//
+// Lane-by-lane host replay of the device lane-group code (readserver_b200/csrc/rs_device.cuh) on top
+// of the REAL host builder (rs_build.cpp) and the REAL per-lane SWAR arithmetic (rs_swar.h): the
+// eight lanes of a group are looped over and warp shuffles become array reads.  It lets the CPU test
+// suite (-m "not gpu") check the HBM layout, the directory logic, the in-block rank/access/select
+// arithmetic and the reference-tail emulation against the oracle without a GPU.  The product never
+// loads this file: librs_b200.so has no CPU compute path.
+#include <stdint.h>
+#include <string.h>
+
+#include <vector>
+
+#include "rs_build.h"
+#include "rs_layout.h"
+#include "rs_swar.h"
+
+namespace {
+struct Emul {
+  RsHostIndex h;
+  bool emulate_tail = true;
+};
+
+struct Hit {
+  rs_lane L[RS_GROUP];
+  uint32_t lane_base[RS_GROUP];
+  uint32_t off;
+  uint64_t start;
+  const rs_block* blk;
+};
+
+inline uint64_t ref_pos(const Emul& e, uint64_t i) {
+  if (e.emulate_tail && ((i + 1) >> 16) >= e.h.vlast && i >= e.h.clamp_c) i = e.h.clamp_c - 1;
+  return i;
+}
+
+inline uint64_t ref_pos_char(const Emul& e, uint64_t i) {
+  if (e.emulate_tail && ((i + 1) >> 16) >= e.h.vlast && i >= e.h.clamp_char) i = e.h.clamp_char - 1;
+  return i;
+}
+
+uint64_t dir_block(uint64_t e, uint32_t o, bool* more) {
+  const uint32_t b1 = (uint32_t)(e >> 32) & RS_SLOT_MASK;
+  const uint32_t b2 = (uint32_t)(e >> 42) & RS_SLOT_MASK;
+  const uint32_t b3 = (uint32_t)(e >> 52) & RS_SLOT_MASK;
+  const uint32_t add = (uint32_t)(b1 != 0 && o >= b1) + (uint32_t)(b2 != 0 && o >= b2) + (uint32_t)(b3 != 0 && o >= b3);
+  *more = (e & RS_DIR_MORE) != 0 && add == 3;
+  return (uint64_t)(uint32_t)e + add;
+}
+
+void fetch(const Emul& e, uint64_t pos, Hit* H) {
+  bool more;
+  uint64_t b = dir_block(e.h.dir[pos >> RS_SLOT_SHIFT], (uint32_t)pos & RS_SLOT_MASK, &more);
+  while (true) {
+    const rs_block* blk = &e.h.blocks[b];
+    uint32_t words[32];
+    memcpy(words, blk, RS_BLOCK_BYTES);
+    uint32_t run = 0;
+    for (int g = 0; g < RS_GROUP; ++g) {
+      rs_lane_prepare(words[4 * g], words[4 * g + 1], words[4 * g + 2], words[4 * g + 3], g, &H->L[g]);
+      H->lane_base[g] = run;
+      run += H->L[g].total;
+    }
+    H->start = blk->start;
+    H->blk = blk;
+    const uint64_t off = pos - blk->start + 1;
+    if (more && off > run) {
+      ++b;
+      continue;
+    }
+    H->off = (uint32_t)off;
+    return;
+  }
+}
+
+uint64_t hit_rank(const Hit& H, uint32_t c) {
+  uint64_t before;
+  if (c)
+    before = H.blk->cnt[c - 1];
+  else
+    before = H.start - (H.blk->cnt[0] + H.blk->cnt[1] + H.blk->cnt[2] + H.blk->cnt[3]);
+  uint32_t sum = 0;
+  for (int g = 0; g < RS_GROUP; ++g) sum += rs_lane_count(&H.L[g], c, (int32_t)H.off - (int32_t)H.lane_base[g]);
+  return before + sum;
+}
+
+uint32_t hit_symbol(const Hit& H) {
+  uint32_t sym = 0xFF;
+  int owners = 0;
+  for (int g = 0; g < RS_GROUP; ++g) {
+    const uint32_t s = rs_lane_symbol(&H.L[g], (int32_t)H.off - (int32_t)H.lane_base[g]);
+    if (s != 0xFF) {
+      sym = s;
+      ++owners;
+    }
+  }
+  return owners == 1 ? sym : 0xFE; /* exactly one lane must own the position */
+}
+
+uint64_t occ(const Emul& e, uint32_t c, uint64_t i) {
+  if (i == ~0ull) return 0;
+  uint64_t pos = ref_pos(e, i);
+  if (pos >= e.h.n) pos = e.h.n - 1;
+  Hit H;
+  fetch(e, pos, &H);
+  return hit_rank(H, c);
+}
+
+uint32_t chr(const Emul& e, uint64_t i) {
+  uint64_t pos = ref_pos_char(e, i);
+  if (pos >= e.h.n) pos = e.h.n - 1;
+  Hit H;
+  fetch(e, pos, &H);
+  return hit_symbol(H);
+}
+
+uint32_t lf_step(const Emul& e, uint64_t idx, uint64_t* next) {
+  uint64_t pc = ref_pos_char(e, idx);
+  if (pc >= e.h.n) pc = e.h.n - 1;
+  Hit H;
+  fetch(e, pc, &H);
+  uint32_t sym = hit_symbol(H);
+  if (sym > 4) sym = 0;
+  const bool none = idx == 0;
+  const uint64_t pp = none ? 0 : ref_pos(e, idx - 1);
+  uint64_t o;
+  if (!none && pp + 1 == pc)
+    o = hit_rank(H, sym) - 1;
+  else
+    o = occ(e, sym, idx - 1);
+  *next = e.h.pc[sym] + o;
+  return sym;
+}
+
+/* select inside the block replay: position of the r-th (1-based) occurrence of c */
+uint64_t occ_at(const Emul& e, uint32_t c, uint64_t r) {
+  const RsHostIndex& h = e.h;
+  if (r == 0 || r > h.tot[c]) return ~0ull;
+  uint64_t b = h.sel[c][(r - 1) >> RS_SEL_SHIFT];
+  while (true) {
+    const rs_block* blk = &h.blocks[b];
+    uint32_t words[32];
+    memcpy(words, blk, RS_BLOCK_BYTES);
+    rs_lane L[RS_GROUP];
+    uint32_t lane_base[RS_GROUP], cbase[RS_GROUP], run = 0, crun = 0;
+    for (int g = 0; g < RS_GROUP; ++g) {
+      rs_lane_prepare(words[4 * g], words[4 * g + 1], words[4 * g + 2], words[4 * g + 3], g, &L[g]);
+      lane_base[g] = run;
+      cbase[g] = crun;
+      run += L[g].total;
+      crun += rs_lane_count_all(&L[g], c);
+    }
+    const uint64_t before = c ? blk->cnt[c - 1] : blk->start - (blk->cnt[0] + blk->cnt[1] + blk->cnt[2] + blk->cnt[3]);
+    const uint64_t want = r - before;
+    if (want > crun) {
+      ++b;
+      continue;
+    }
+    for (int g = 0; g < RS_GROUP; ++g) {
+      const uint32_t p = rs_lane_select(&L[g], c, (int32_t)want - (int32_t)cbase[g]);
+      if (p) return blk->start + lane_base[g] + p - 1;
+    }
+    return ~0ull - 1;
+  }
+}
+
+inline uint32_t code_of(uint8_t b) { return b == 'A' ? 1u : b == 'C' ? 2u : b == 'G' ? 3u : b == 'T' ? 4u : 0u; }
+}  // namespace
+
+extern "C" {
+
+void* emul_open(const uint8_t* runs, uint64_t nruns, uint64_t num_strings, uint64_t num_symbols, int* status) {
+  Emul* e = new Emul;
+  const int rc = rs_build_host_index(runs, nruns, num_strings, num_symbols, e->h);
+  if (status) *status = rc;
+  if (rc != RS_OK) {
+    delete e;
+    return nullptr;
+  }
+  return e;
+}
+
+void* emul_open_file(const char* path, int* status) {
+  std::vector<uint8_t> runs;
+  uint64_t ns = 0, nsym = 0;
+  int rc = rs_read_bwt_file(path, runs, ns, nsym);
+  if (rc != RS_OK) {
+    if (status) *status = rc;
+    return nullptr;
+  }
+  return emul_open(runs.data(), runs.size(), ns, nsym, status);
+}
+
+void emul_close(void* p) { delete (Emul*)p; }
+void emul_set_tail(void* p, int on) { ((Emul*)p)->emulate_tail = on != 0; }
+
+/* out[0..] = n, nblocks, ndir, clamp_c, vlast, depth, q2_safe, pc[5], tot[5], init_occ[5], clamp_char */
+void emul_info(void* p, uint64_t* out) {
+  const RsHostIndex& h = ((Emul*)p)->h;
+  out[0] = h.n; out[1] = h.blocks.size(); out[2] = h.dir.size(); out[3] = h.clamp_c; out[4] = h.vlast;
+  out[5] = h.depth; out[6] = h.q2_safe; out[22] = h.clamp_char;
+  for (int c = 0; c < 5; ++c) { out[7 + c] = h.pc[c]; out[12 + c] = h.tot[c]; out[17 + c] = h.init_occ[c]; }
+}
+
+void emul_occ_batch(void* p, const uint8_t* b, const uint64_t* idx, uint64_t n, uint64_t* out) {
+  const Emul& e = *(Emul*)p;
+  for (uint64_t i = 0; i < n; ++i) out[i] = occ(e, code_of(b[i]), idx[i]);
+}
+
+void emul_char_batch(void* p, const uint64_t* idx, uint64_t n, uint8_t* out) {
+  const Emul& e = *(Emul*)p;
+  for (uint64_t i = 0; i < n; ++i) {
+    const uint32_t s = chr(e, idx[i]);
+    out[i] = s <= 4 ? (uint8_t)"$ACGT"[s] : (uint8_t)'?';
+  }
+}
+
+void emul_occ_at_batch(void* p, const uint8_t* b, const uint64_t* cnt, uint64_t n, uint64_t* out) {
+  const Emul& e = *(Emul*)p;
+  for (uint64_t i = 0; i < n; ++i) out[i] = occ_at(e, code_of(b[i]), cnt[i]);
+}
+
+void emul_find_interval_batch(void* p, const uint8_t* kmers, int k, uint64_t Q, uint64_t* lower, uint64_t* upper) {
+  const Emul& e = *(Emul*)p;
+  for (uint64_t q = 0; q < Q; ++q) {
+    const uint8_t* w = kmers + q * (uint64_t)k;
+    uint32_t c = code_of(w[k - 1]);
+    uint64_t lo = e.h.pc[c];
+    uint64_t hi = lo + (e.emulate_tail ? e.h.init_occ[c] : e.h.tot[c]) - 1;
+    for (int j = k - 2; j >= 0; --j) {
+      c = code_of(w[j]);
+      lo = e.h.pc[c] + occ(e, c, lo - 1);
+      hi = e.h.pc[c] + occ(e, c, hi) - 1;
+      if (lo > hi) break;
+    }
+    lower[q] = lo;
+    upper[q] = hi;
+  }
+}
+
+void emul_prefix_walk_batch(void* p, const uint64_t* rows, uint64_t n, uint32_t max_steps, uint64_t* lexrank,
+                            uint32_t* steps) {
+  const Emul& e = *(Emul*)p;
+  for (uint64_t i = 0; i < n; ++i) {
+    uint64_t idx = rows[i];
+    uint32_t s = 0;
+    while (true) {
+      uint64_t nxt;
+      const uint32_t sym = lf_step(e, idx, &nxt);
+      idx = nxt;
+      if (sym == 0) break;
+      if (++s > max_steps) {
+        s = 0xFFFFFFFFu;
+        idx = ~0ull;
+        break;
+      }
+    }
+    lexrank[i] = idx;
+    steps[i] = s;
+  }
+}
+
+}  // extern "C"

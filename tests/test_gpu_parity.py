@@ -1,0 +1,180 @@
+"""Parity tests proper: the CUDA path, called through the C ABI, against the CPU oracle on the same
+seeded inputs and against the golden vectors generated from the unmodified reference.  Bit-exact."""
+import hashlib
+import os
+
+import numpy as np
+import pytest
+
+import oracle
+from tests import common
+from tests.golden.make_golden import random_runs
+
+pytestmark = pytest.mark.gpu
+U64MAX = np.iinfo(np.uint64).max
+
+
+@pytest.fixture(scope="module")
+def engine():
+    import torch
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    from readserver_b200 import engine as e
+    return e
+
+
+def _gpu(engine, case):
+    return engine.GpuBWT(runs=case.runs, num_strings=case.num_strings, num_symbols=case.num_symbols)
+
+
+@pytest.mark.parametrize("name", ["tiny", "small", "clean", "mid", "deep"])
+def test_bwt_interface_matches_oracle(name, datasets, engine):
+    case, P = datasets.case(name), datasets.port(name)
+    with _gpu(engine, case) as B:
+        assert B.get_bwlen() == P.bwlen and B.info.ref_depth == P.depth and B.info.q2_safe == 1
+        assert [B.get_pc(c) for c in "$ACGT"] == [P.get_pc(c) for c in "$ACGT"]
+        idx = np.concatenate([common.positions(P.bwlen), np.array([U64MAX], dtype=np.uint64)])
+        for c in b"$ACGT":
+            s = np.full(idx.size, c, dtype=np.uint8)
+            assert np.array_equal(B.get_occ(s, idx), P.get_occ_batch(s, idx)), chr(c)
+        assert np.array_equal(B.get_char(idx[:-1]), P.get_char_batch(idx[:-1]))
+        f = B.get_f(idx[:2000])
+        assert [chr(x) for x in f] == [P.get_f(int(i)) for i in idx[:2000]]
+
+
+@pytest.mark.parametrize("name", ["tiny", "small", "clean", "mid", "deep"])
+def test_find_interval_matches_oracle(name, datasets, engine):
+    case, P = datasets.case(name), datasets.port(name)
+    with _gpu(engine, case) as B:
+        for k in (1, 2, 12, 31, 73):
+            q = case.queries(20000 if k == 31 else 3000, k, seed=40 + k)
+            lo, up = B.find_interval(q, k)
+            lo2, up2 = P.find_interval_batch(q, k, nthreads=4)
+            assert np.array_equal(lo, lo2) and np.array_equal(up, up2), k
+        # ragged batch (lengths of demo/test.in plus the extremes), one of them empty
+        strs = [bytes(case.queries(1, L, seed=90 + L)[0]).decode() for L in (37, 41, 46, 41, 100, 100, 1, 200)] + [""]
+        lo, up = B.find_interval_var(strs)
+        for s, a, b in zip(strs[:-1], lo, up):
+            assert (int(a), int(b)) == P.find_interval(s), s
+        assert (int(lo[-1]), int(up[-1])) == (1, 0)
+
+
+@pytest.mark.parametrize("name", ["small", "clean", "deep"])
+def test_count_reads_both_strands(name, datasets, engine):
+    case, P = datasets.case(name), datasets.port(name)
+    comp = np.zeros(256, dtype=np.uint8)
+    for a, b in zip(b"ACGT", b"TGCA"):
+        comp[a] = b
+    with _gpu(engine, case) as B:
+        q = case.queries(5000, 31, seed=77)
+        q[7, 3] = ord("N")      # count_reads answers 0 for anything outside ACGT (service.cpp:299-301)
+        q[9, 30] = ord("$")
+        ok = np.ones(len(q), dtype=bool)
+        ok[[7, 9]] = False
+        for strand, qq in ((0, q), (1, comp[q[:, ::-1]])):
+            lo, up = P.find_interval_batch(np.ascontiguousarray(qq), 31, nthreads=4)
+            want = np.where(ok & (up >= lo), up - lo + 1, 0)
+            assert np.array_equal(B.count(q, 31, strand=strand), want)
+
+
+@pytest.mark.parametrize("name", ["tiny", "small", "clean", "mid", "deep"])
+def test_extract_prefix_matches_oracle(name, datasets, engine):
+    case, P = datasets.case(name), datasets.port(name)
+    with _gpu(engine, case) as B:
+        B.set_sai(case.sai)
+        rows = np.random.default_rng(2).integers(0, P.bwlen, 20000).astype(np.uint64)
+        lex, st, ri, bases = B.extract_prefix(rows, max_steps=128, want_bases=True, want_read_index=True)
+        lex2, st2, ri2, _ = P.locate_batch(rows, nthreads=4, max_steps=128)
+        assert np.array_equal(lex, lex2) and np.array_equal(st, st2)
+        done = st != 0xFFFFFFFF
+        assert np.array_equal(ri[done], case.sai[lex[done].astype(np.int64)])
+        if name in ("clean", "deep"):   # empty tail region: every walk ends and .sai[lexrank] is the read index
+            assert done.all() and np.array_equal(ri, ri2)
+        for i in np.nonzero(done)[0][:200]:
+            s, _, n = P.extract_prefix(int(rows[i]))
+            assert bytes(bases[i, :n]).decode() == s and not bases[i, n:].any()
+
+
+def test_tail_emulation_switch(datasets, engine):
+    import torch
+    from readserver_b200 import datagen as dg
+    case = datasets.case("small")
+    bwt = dg.rle_decode(torch.from_numpy(case.runs)).numpy()
+    with _gpu(engine, case) as B:
+        assert B.info.ref_clamp_c < B.info.bwlen
+        B.set_tail_emulation(False)
+        idx = np.arange(bwt.size, dtype=np.uint64)
+        for code, c in enumerate(b"$ACGT"):
+            assert np.array_equal(B.get_occ(np.full(idx.size, c, np.uint8), idx), np.cumsum(bwt == code).astype(np.uint64))
+        q = case.queries(300, 31, seed=17)
+        lo, up = B.find_interval(q, 31)
+        cnt = np.where(up >= lo, up - lo + 1, 0)
+        assert list(cnt) == [common.brute_count(case.reads, bytes(k).decode()) for k in q]
+        B.set_tail_emulation(True)
+        lo2, up2 = datasets.port("small").find_interval_batch(q, 31)
+        lo, up = B.find_interval(q, 31)
+        assert np.array_equal(lo, lo2) and np.array_equal(up, up2)
+
+
+@pytest.mark.parametrize("name", ["small", "clean", "deep_rand"])
+def test_against_reference_golden(name, engine):
+    z = np.load(os.path.join(common.GOLDEN, name + ".npz"))
+    if name == "deep_rand":
+        runs, nsym = random_runs(int(z["seed"]), int(z["nruns"]))
+        assert hashlib.sha256(runs.tobytes()).hexdigest() == str(z["runs_sha256"])
+        B = engine.GpuBWT(runs=runs, num_strings=1, num_symbols=nsym)
+    else:
+        B = engine.GpuBWT(os.path.join(common.GOLDEN, name + ".bwt"))
+    with B:
+        for c in b"$ACGT":
+            assert np.array_equal(B.get_occ(np.full(z["pos"].size, c, np.uint8), z["pos"]), z["occ_" + chr(c)])
+        assert np.array_equal(B.get_char(z["pos_in"]), z["char"])
+        assert np.array_equal(B.get_f(z["pos_in"][:500]), z["f"])
+        lo, up = B.find_interval(z["kmers"], z["kmers"].shape[1])
+        assert np.array_equal(lo, z["lower"]) and np.array_equal(up, z["upper"])
+        if name != "deep_rand":
+            lo, up = B.find_interval_var([str(s) for s in z["var_queries"]])
+            assert np.array_equal(lo, z["var_lower"]) and np.array_equal(up, z["var_upper"])
+            B.set_sai(z["sai"])
+            lex, st, ri = B.extract_prefix(z["rows"], max_steps=300, want_read_index=True)
+            assert np.array_equal(lex, z["lexrank"]) and np.array_equal(st, z["pre_steps"])
+            if name == "clean":
+                assert np.array_equal(ri, z["read_index"])
+
+
+def test_degenerate_blocks_on_gpu(engine):
+    rng = np.random.default_rng(5)
+    shapes = [((rng.integers(0, 5, 5000).astype(np.uint8) << 5) | 1),
+              ((rng.integers(1, 5, 3000).astype(np.uint8) << 5) | 31),
+              np.array([(2 << 5) | 7], dtype=np.uint8),
+              np.concatenate([(rng.integers(0, 5, 4000).astype(np.uint8) << 5) | 1,
+                              (rng.integers(0, 5, 70000).astype(np.uint8) << 5) | rng.integers(1, 4, 70000).astype(np.uint8)])]
+    for runs in shapes:
+        runs = np.ascontiguousarray(runs, dtype=np.uint8)
+        n = int((runs & 31).astype(np.int64).sum())
+        P = oracle.PortIndex(runs=runs, num_strings=1, num_symbols=n)
+        with engine.GpuBWT(runs=runs, num_strings=1, num_symbols=n) as B:
+            if not B.info.q2_safe:
+                continue
+            idx = np.concatenate([np.arange(n, dtype=np.uint64), np.array([U64MAX], dtype=np.uint64)])
+            for c in b"$ACGT":
+                s = np.full(idx.size, c, dtype=np.uint8)
+                assert np.array_equal(B.get_occ(s, idx), P.get_occ_batch(s, idx))
+            assert np.array_equal(B.get_char(idx[:-1]), P.get_char_batch(idx[:-1]))
+
+
+def test_error_behaviour(engine, tmp_path):
+    p = tmp_path / "bad.bwt"
+    p.write_bytes(b"\x00" * 64)
+    with pytest.raises(engine.RsError) as e:
+        engine.GpuBWT(str(p))
+    assert e.value.status == 2      # the reference prints and exits (rlebwt_reader.cpp:31-34)
+    with pytest.raises(engine.RsError) as e:
+        engine.GpuBWT(str(tmp_path / "missing.bwt"))
+    assert e.value.status == 1
+    runs = np.array([(1 << 5) | 3, (0 << 5) | 1], dtype=np.uint8)
+    with engine.GpuBWT(runs=runs, num_strings=1, num_symbols=4) as B:
+        with pytest.raises(engine.RsError) as e:
+            B.extract_prefix(np.zeros(1, np.uint64), want_read_index=True)
+        assert e.value.status == 8
+        lo, up = B.find_interval(np.zeros((0, 31), dtype=np.uint8), 31)
+        assert lo.size == 0
