@@ -74,6 +74,10 @@ int rs_index_set_tail_emulation(rs_index* ix, int on);
  * to turn a kernel time into achieved bytes/s; no reference counterpart. */
 int rs_index_enable_stats(rs_index* ix, int on);
 int rs_index_read_stats(rs_index* ix, uint64_t* interval_steps, uint64_t* walk_steps, int reset);
+/* Tuning knob, no reference counterpart: lanes of a warp that cooperate on one query / walker
+ * (1, 2, 4 or 8; also settable as RS_B200_LANES in the environment).  Results do not depend on it. */
+int rs_config_set_lanes(int lanes);
+int rs_config_get_lanes(void);
 const char* rs_last_error(void);
 /* pinned host memory for the host-pointer calls (optional; any host memory is accepted) */
 int rs_host_alloc(void** p, size_t bytes);

@@ -77,6 +77,23 @@ struct rs_index {
 
 const char* rs_last_error(void) { return g_err.c_str(); }
 
+int rs_config_set_lanes(int lanes) {
+  if (lanes != 1 && lanes != 2 && lanes != 4 && lanes != 8) return fail(RS_STATUS_ARG, "lanes must be 1, 2, 4 or 8");
+  rs_set_lanes(lanes);
+  return RS_STATUS_OK;
+}
+int rs_config_get_lanes(void) { return rs_get_lanes(); }
+
+/* fold "last m_vSum window and at/after the clamp" into one threshold per lookup kind */
+static void set_tail(rs_index* ix, bool on) {
+  rs_index_dev& d = ix->dev;
+  d.emulate_tail = on ? 1u : 0u;
+  const uint64_t win = d.vlast ? (d.vlast << 16) - 1 : 0; /* (i + 1) >> 16 >= vlast  <=>  i >= win (i != 2^64-1) */
+  d.tail_from = on ? (win > d.clamp_c ? win : d.clamp_c) : ~0ull;
+  d.tail_from_char = on ? (win > d.clamp_char ? win : d.clamp_char) : ~0ull;
+  for (int c = 0; c < RS_NSYM; ++c) d.init_occ[c] = on ? ix->init_occ_ref[c] : d.tot[c];
+}
+
 static int upload(rs_index* ix, const RsHostIndex& h) {
   CU(cudaSetDevice(ix->device));
   CU(cudaStreamCreateWithFlags(&ix->stream, cudaStreamNonBlocking));
@@ -107,6 +124,7 @@ static int upload(rs_index* ix, const RsHostIndex& h) {
   ix->dev.clamp_char = h.clamp_char;
   ix->dev.vlast = h.vlast;
   ix->dev.emulate_tail = 1;
+  set_tail(ix, true);
   ix->num_runs = h.num_runs;
   ix->depth = h.depth;
   ix->q2_safe = h.q2_safe;
@@ -188,9 +206,7 @@ int rs_index_get_info(const rs_index* ix, rs_index_info* info) {
 int rs_index_set_tail_emulation(rs_index* ix, int on) {
   if (!ix) return fail(RS_STATUS_ARG, "null index");
   std::lock_guard<std::mutex> lk(ix->mu);
-  ix->dev.emulate_tail = on ? 1u : 0u;
-  /* initInterval's constant (query.cpp:18-21) follows the same switch */
-  for (int c = 0; c < RS_NSYM; ++c) ix->dev.init_occ[c] = on ? ix->init_occ_ref[c] : ix->dev.tot[c];
+  set_tail(ix, on != 0); /* initInterval's constant (query.cpp:18-21) follows the same switch */
   return RS_STATUS_OK;
 }
 

@@ -1,5 +1,4 @@
-/* sm_100a kernels of the FM-index hot path.  One lane group (8 lanes) per query / walker; each rank
- * is one coalesced 128-byte block load + SWAR decode + shuffle scan (rs_device.cuh).
+/* sm_100a kernels of the FM-index hot path.  LANES lanes per query / walker (rs_device.cuh).
  *
  *   k_find_interval   findInterval            src/bwt/query.cpp:24-41   (K1)
  *   k_extract_prefix  extractPrefix           src/bwt/query.cpp:43-63   (K2)
@@ -7,32 +6,43 @@
  */
 #include "rs_kernels.h"
 
+#include <stdlib.h>
+
 #include "rs_device.cuh"
 
 #define RS_FULL 0xFFFFFFFFu
 
-/* alphabet.h:11-32: A,C,G,T -> 1..4, every other byte -> 0 ('$') */
+/* alphabet.h:11-32: A,C,G,T -> 1..4, every other byte -> 0 ('$'); branch-free:
+ * (ch >> 1) & 3 separates A,C,T,G (0,1,2,3); the byte must also equal the letter it selects. */
 __device__ __forceinline__ uint32_t rs_code(uint32_t ch) {
-  return ch == 'A' ? 1u : ch == 'C' ? 2u : ch == 'G' ? 3u : ch == 'T' ? 4u : 0u;
+  const uint32_t sel = ((ch >> 1) & 3u) * 8u;
+  const uint32_t letter = (0x47544341u >> sel) & 0xFFu; /* 'A','C','T','G' */
+  const uint32_t code = (0x03040201u >> sel) & 0xFFu;   /*  1 , 2 , 4 , 3  */
+  return ch == letter ? code : 0u;
 }
-__device__ __forceinline__ char rs_ascii(uint32_t code) { return "$ACGT"[code]; }
+__device__ __forceinline__ uint32_t rs_ascii(uint32_t code) { return (0x5447434124ull >> (8 * code)) & 0xFFu; }
 
+template <int LANES>
 __global__ void __launch_bounds__(RS_THREADS) k_occ(const __grid_constant__ rs_index_dev ix, const uint8_t* __restrict__ syms,
                                                     const uint64_t* __restrict__ idx, uint64_t n,
                                                     uint64_t* __restrict__ out) {
-  const rs_grp G = rs_grp_init();
-  const uint64_t ngroups = (uint64_t)gridDim.x * (RS_THREADS / RS_GROUP);
-  for (uint64_t i = (uint64_t)blockIdx.x * (RS_THREADS / RS_GROUP) + threadIdx.x / RS_GROUP; i < n; i += ngroups) {
+  const rs_grp<LANES> G;
+  constexpr int GPB = RS_THREADS / LANES;
+  const uint64_t ngroups = (uint64_t)gridDim.x * GPB;
+  /* a group leaves the loop as a whole, so the group-masked shuffles inside stay well formed */
+  for (uint64_t i = (uint64_t)blockIdx.x * GPB + threadIdx.x / LANES; i < n; i += ngroups) {
     const uint64_t r = rs_grp_occ(ix, G, rs_code(syms[i]), idx[i]);
     if (G.g == 0) out[i] = r;
   }
 }
 
+template <int LANES>
 __global__ void __launch_bounds__(RS_THREADS) k_char(const __grid_constant__ rs_index_dev ix, const uint64_t* __restrict__ idx,
                                                      uint64_t n, uint8_t* __restrict__ out) {
-  const rs_grp G = rs_grp_init();
-  const uint64_t ngroups = (uint64_t)gridDim.x * (RS_THREADS / RS_GROUP);
-  for (uint64_t i = (uint64_t)blockIdx.x * (RS_THREADS / RS_GROUP) + threadIdx.x / RS_GROUP; i < n; i += ngroups) {
+  const rs_grp<LANES> G;
+  constexpr int GPB = RS_THREADS / LANES;
+  const uint64_t ngroups = (uint64_t)gridDim.x * GPB;
+  for (uint64_t i = (uint64_t)blockIdx.x * GPB + threadIdx.x / LANES; i < n; i += ngroups) {
     const uint32_t s = rs_grp_char(ix, G, idx[i]);
     if (G.g == 0) out[i] = (uint8_t)rs_ascii(s);
   }
@@ -54,15 +64,18 @@ __global__ void k_getf(const __grid_constant__ rs_index_dev ix, const uint64_t* 
  * or the interval went empty: query.cpp:35-37) picks up its next query on the following trip, so
  * lanes never idle behind a longer neighbour.
  *   mode 0: write lower/upper.   mode 1: write counts (count_reads, service.cpp:279-315), strand as given. */
+template <int LANES>
 __global__ void __launch_bounds__(RS_THREADS)
     k_find_interval(const __grid_constant__ rs_index_dev ix, const uint8_t* __restrict__ text,
                     const uint64_t* __restrict__ offs, uint32_t k, uint64_t Q, uint64_t* __restrict__ lower,
                     uint64_t* __restrict__ upper, int mode, int strand, unsigned long long* __restrict__ stats) {
-  const rs_grp G = rs_grp_init();
-  const uint64_t ngroups = (uint64_t)gridDim.x * (RS_THREADS / RS_GROUP);
-  uint64_t next_q = (uint64_t)blockIdx.x * (RS_THREADS / RS_GROUP) + threadIdx.x / RS_GROUP;
-  uint64_t q = 0, base = 0, lo = 0, hi = 0;
-  int64_t j = -1;     /* characters still to consume (index of the next one in search order) */
+  const rs_grp<LANES> G;
+  constexpr int GPB = RS_THREADS / LANES;
+  const uint64_t ngroups = (uint64_t)gridDim.x * GPB;
+  uint64_t next_q = (uint64_t)blockIdx.x * GPB + threadIdx.x / LANES;
+  uint64_t q = 0, lo = 0, hi = 0;
+  const uint8_t* w = text; /* the query's characters */
+  int32_t j = -1;          /* index of the next character in search order */
   uint32_t len = 0;
   bool active = false;
   const bool rc = (mode == 1 && strand == 1);
@@ -72,6 +85,7 @@ __global__ void __launch_bounds__(RS_THREADS)
     if (!active && next_q < Q) {
       q = next_q;
       next_q += ngroups;
+      uint64_t base;
       if (offs) {
         base = offs[q];
         len = (uint32_t)(offs[q + 1] - base);
@@ -79,11 +93,12 @@ __global__ void __launch_bounds__(RS_THREADS)
         base = q * (uint64_t)k;
         len = k;
       }
+      w = text + base;
       active = true;
       bool bad = (len == 0);
       if (mode == 1) { /* any byte outside ACGT -> count 0 (service.cpp:299-301) */
-        for (uint32_t t = G.g; t < len; t += RS_GROUP) bad |= (rs_code(text[base + t]) == 0);
-        bad = __ballot_sync(G.mask, bad) & G.mask;
+        for (uint32_t t = G.g; t < len; t += LANES) bad |= (rs_code(w[t]) == 0);
+        if (LANES > 1) bad = (__ballot_sync(G.mask, bad) & G.mask) != 0;
       }
       if (bad) {
         if (G.g == 0) {
@@ -93,11 +108,10 @@ __global__ void __launch_bounds__(RS_THREADS)
         active = false;
       } else {
         /* initInterval (query.cpp:18-21) on the last character of the searched string */
-        const uint32_t ch = rc ? text[base] : text[base + len - 1];
-        const uint32_t c = rc ? (5u - rs_code(ch)) : rs_code(ch);
+        const uint32_t c = rc ? 5u - rs_code(w[0]) : rs_code(w[len - 1]);
         lo = ix.pc[c];
         hi = lo + ix.init_occ[c] - 1;
-        j = (int64_t)len - 2;
+        j = (int32_t)len - 2;
         if (j < 0) {
           if (G.g == 0) {
             if (mode == 1) lower[q] = hi >= lo ? hi - lo + 1 : 0;
@@ -114,8 +128,7 @@ __global__ void __launch_bounds__(RS_THREADS)
     if (active) {
       /* updateInterval (query.cpp:11-15).  Reverse complement: the searched string is
        * revcomp(w), whose character at search index j is the complement of w[len-1-j]. */
-      const uint32_t ch = rc ? text[base + (len - 1 - j)] : text[base + j];
-      const uint32_t c = rc ? (5u - rs_code(ch)) : rs_code(ch);
+      const uint32_t c = rc ? 5u - rs_code(w[len - 1 - j]) : rs_code(w[j]);
       uint64_t r1, r2;
       rs_grp_occ2(ix, G, c, lo - 1, hi, &r1, &r2);
       ++nsteps;
@@ -136,16 +149,19 @@ __global__ void __launch_bounds__(RS_THREADS)
 }
 
 /* K2.  extractPrefix (query.cpp:43-63): LF-walk from each row to its '$'.  Same step-interleaved
- * scheme as K1: a group whose walk ends takes its next row on the following trip. */
+ * scheme as K1: a group whose walk ends takes its next row on the following trip, so the set of
+ * live walkers stays dense in every warp without a separate compaction pass. */
+template <int LANES>
 __global__ void __launch_bounds__(RS_THREADS)
     k_extract_prefix(const __grid_constant__ rs_index_dev ix, const uint64_t* __restrict__ rows, uint64_t n,
                      uint32_t max_steps, uint64_t* __restrict__ lexrank, uint32_t* __restrict__ steps,
                      const uint64_t* __restrict__ sai, uint64_t* __restrict__ read_index, uint8_t* __restrict__ bases,
                      unsigned long long* __restrict__ stats) {
-  const rs_grp G = rs_grp_init();
-  const uint64_t ngroups = (uint64_t)gridDim.x * (RS_THREADS / RS_GROUP);
+  const rs_grp<LANES> G;
+  constexpr int GPB = RS_THREADS / LANES;
+  const uint64_t ngroups = (uint64_t)gridDim.x * GPB;
   unsigned long long lf_steps = 0;
-  uint64_t next_i = (uint64_t)blockIdx.x * (RS_THREADS / RS_GROUP) + threadIdx.x / RS_GROUP;
+  uint64_t next_i = (uint64_t)blockIdx.x * GPB + threadIdx.x / LANES;
   uint64_t i = 0, idx = 0;
   uint32_t s = 0;
   bool active = false;
@@ -189,12 +205,12 @@ __global__ void __launch_bounds__(RS_THREADS)
           uint8_t* p = bases + i * (uint64_t)max_steps;
           const uint32_t m = nsteps == 0xFFFFFFFFu ? 0u : nsteps;
           __syncwarp(G.mask);
-          for (uint32_t a = G.g; a < m / 2; a += RS_GROUP) {
+          for (uint32_t a = G.g; a < m / 2; a += LANES) {
             const uint8_t t = p[a];
             p[a] = p[m - 1 - a];
             p[m - 1 - a] = t;
           }
-          for (uint32_t a = m + G.g; a < max_steps; a += RS_GROUP) p[a] = 0;
+          for (uint32_t a = m + G.g; a < max_steps; a += LANES) p[a] = 0;
         }
         active = false;
       }
@@ -204,7 +220,22 @@ __global__ void __launch_bounds__(RS_THREADS)
 }
 
 /* ---- launchers ---- */
-static int rs_grid_for(const void* kernel, uint64_t work_groups) {
+static int g_lanes = 0;
+
+int rs_get_lanes() {
+  if (!g_lanes) {
+    const char* e = getenv("RS_B200_LANES");
+    const int v = e ? atoi(e) : 0;
+    g_lanes = (v == 1 || v == 2 || v == 4 || v == 8) ? v : RS_DEFAULT_LANES;
+  }
+  return g_lanes;
+}
+
+void rs_set_lanes(int lanes) {
+  if (lanes == 1 || lanes == 2 || lanes == 4 || lanes == 8) g_lanes = lanes;
+}
+
+static int rs_grid_for(const void* kernel, int lanes, uint64_t items) {
   static int sms = 0;
   if (!sms) {
     int dev = 0;
@@ -216,21 +247,32 @@ static int rs_grid_for(const void* kernel, uint64_t work_groups) {
   cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, RS_THREADS, 0);
   if (per_sm < 1) per_sm = 1;
   uint64_t grid = (uint64_t)sms * per_sm; /* one resident wave, a multiple of the SM count */
-  const uint64_t need = (work_groups + (RS_THREADS / RS_GROUP) - 1) / (RS_THREADS / RS_GROUP);
+  const uint64_t gpb = RS_THREADS / lanes;
+  const uint64_t need = (items + gpb - 1) / gpb;
   if (need < grid) grid = need;
   return grid ? (int)grid : 1;
 }
 
+#define RS_DISPATCH(KERNEL, ITEMS, ST, ...)                                                                       \
+  do {                                                                                                            \
+    switch (rs_get_lanes()) {                                                                                     \
+      case 1: KERNEL<1><<<rs_grid_for((const void*)KERNEL<1>, 1, ITEMS), RS_THREADS, 0, ST>>>(__VA_ARGS__); break; \
+      case 2: KERNEL<2><<<rs_grid_for((const void*)KERNEL<2>, 2, ITEMS), RS_THREADS, 0, ST>>>(__VA_ARGS__); break; \
+      case 4: KERNEL<4><<<rs_grid_for((const void*)KERNEL<4>, 4, ITEMS), RS_THREADS, 0, ST>>>(__VA_ARGS__); break; \
+      default: KERNEL<8><<<rs_grid_for((const void*)KERNEL<8>, 8, ITEMS), RS_THREADS, 0, ST>>>(__VA_ARGS__); break; \
+    }                                                                                                             \
+  } while (0)
+
 cudaError_t rs_launch_occ(const rs_index_dev& ix, const uint8_t* syms, const uint64_t* idx, uint64_t n, uint64_t* out,
                           cudaStream_t st) {
   if (!n) return cudaSuccess;
-  k_occ<<<rs_grid_for((const void*)k_occ, n), RS_THREADS, 0, st>>>(ix, syms, idx, n, out);
+  RS_DISPATCH(k_occ, n, st, ix, syms, idx, n, out);
   return cudaGetLastError();
 }
 
 cudaError_t rs_launch_char(const rs_index_dev& ix, const uint64_t* idx, uint64_t n, uint8_t* out, cudaStream_t st) {
   if (!n) return cudaSuccess;
-  k_char<<<rs_grid_for((const void*)k_char, n), RS_THREADS, 0, st>>>(ix, idx, n, out);
+  RS_DISPATCH(k_char, n, st, ix, idx, n, out);
   return cudaGetLastError();
 }
 
@@ -244,8 +286,7 @@ cudaError_t rs_launch_find_interval(const rs_index_dev& ix, const uint8_t* text,
                                     uint64_t Q, uint64_t* lower, uint64_t* upper, int mode, int strand,
                                     unsigned long long* stats, cudaStream_t st) {
   if (!Q) return cudaSuccess;
-  k_find_interval<<<rs_grid_for((const void*)k_find_interval, Q), RS_THREADS, 0, st>>>(ix, text, offs, k, Q, lower,
-                                                                                      upper, mode, strand, stats);
+  RS_DISPATCH(k_find_interval, Q, st, ix, text, offs, k, Q, lower, upper, mode, strand, stats);
   return cudaGetLastError();
 }
 
@@ -253,7 +294,6 @@ cudaError_t rs_launch_extract_prefix(const rs_index_dev& ix, const uint64_t* row
                                      uint64_t* lexrank, uint32_t* steps, const uint64_t* sai, uint64_t* read_index,
                                      uint8_t* bases, unsigned long long* stats, cudaStream_t st) {
   if (!n) return cudaSuccess;
-  k_extract_prefix<<<rs_grid_for((const void*)k_extract_prefix, n), RS_THREADS, 0, st>>>(
-      ix, rows, n, max_steps, lexrank, steps, sai, read_index, bases, stats);
+  RS_DISPATCH(k_extract_prefix, n, st, ix, rows, n, max_steps, lexrank, steps, sai, read_index, bases, stats);
   return cudaGetLastError();
 }

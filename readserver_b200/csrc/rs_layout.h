@@ -35,7 +35,7 @@
 #define RS_DIR_MORE (1ull << 62)
 #define RS_SEL_SHIFT 10
 #define RS_NSYM 5
-#define RS_GROUP 8 /* lanes per query: 8 x 16 B = one block */
+#define RS_GROUP 8 /* widest lane group: 8 x 16 B = one block */
 #define RS_NO_ROW 0xFFFFFFFFFFFFFFFFull
 
 typedef struct rs_block {
@@ -63,6 +63,10 @@ typedef struct rs_index_dev {
   uint64_t clamp_c;          /* getOcc  */
   uint64_t clamp_char;       /* getChar */
   uint64_t vlast;
+  /* the same rule folded into one compare per lookup: i >= tail_from  <=>  the clamp applies
+   * (max(vlast * 65536 - 1, clamp) when emulating the reference, 2^64-1 = never otherwise) */
+  uint64_t tail_from;        /* getOcc  */
+  uint64_t tail_from_char;   /* getChar */
   uint32_t emulate_tail;     /* 1 = bit-exact with the reference (default), 0 = true rank       */
   uint32_t pad_;
 } rs_index_dev;

@@ -1,10 +1,15 @@
 /* Per-lane arithmetic of the in-block rank / access / select over SGA run bytes.
  *
- * One lane owns 16 bytes (four 32-bit words) of a 128-byte block.  Everything here is pure 32-bit
- * integer SWAR over four run bytes at a time, so the same source compiles for the sm_100a kernels
- * (video-SIMD + dp4a instructions) and for the host (portable fall-backs) where tests/ replays it
- * lane by lane against the oracle.  The cross-lane glue (scan / reduce / broadcast) lives with the
- * caller: warp shuffles on the device.
+ * A lane owns NW consecutive 32-bit words (4 run bytes each) of a 128-byte block: 22 payload words
+ * when one thread handles a whole block, fewer when 2, 4 or 8 lanes share it.  Everything here is
+ * branch-free 32-bit SWAR so the same source compiles for the sm_100a kernels and for the host,
+ * where tests/ replays it lane by lane against the oracle.  The cross-lane glue (scan / reduce /
+ * broadcast) lives with the caller: warp shuffles on the device.
+ *
+ * Byte-SIMD without the video intrinsics (on sm_100a __vminu4 / __vsubus4 / __vcmpeq4 expand to 5-8
+ * ALU instructions each): every quantity a byte holds here is < 128 (a word spans at most 4 x 31 =
+ * 124 symbols), so bit 7 of each byte is free to act as a guard bit for compares, and byte sums are
+ * taken with dp4a.
  *
  * Replaces the byte-at-a-time run scans of the reference: RLEBWT::getOcc (src/bwt/rlebwt.cpp:281-298),
  * getChar (:213-225) and getOccAt (:247-264).
@@ -23,146 +28,147 @@
 #define RS_LEN_MASK 0x1F1F1F1Fu
 #define RS_SYM_MASK 0xE0E0E0E0u
 #define RS_ONES 0x01010101u
+#define RS_HIGH 0x80808080u
 
-/* ---- byte-SIMD primitives ---- */
+/* sum over bytes of a_j * b_j (unsigned) + acc */
+RS_HD uint32_t rs_dot(uint32_t a, uint32_t b, uint32_t acc) {
 #if defined(__CUDA_ARCH__)
-RS_HD uint32_t rs_vsubus4(uint32_t a, uint32_t b) { return __vsubus4(a, b); }
-RS_HD uint32_t rs_vminu4(uint32_t a, uint32_t b) { return __vminu4(a, b); }
-RS_HD uint32_t rs_vcmpeq4(uint32_t a, uint32_t b) { return __vcmpeq4(a, b); }
-RS_HD uint32_t rs_vcmpgeu4(uint32_t a, uint32_t b) { return __vcmpgeu4(a, b); }
-RS_HD uint32_t rs_bytesum(uint32_t a, uint32_t acc) { return __dp4a(a, RS_ONES, acc); }
-RS_HD int rs_ffs(uint32_t a) { return __ffs((int)a); }
+  return __dp4a(a, b, acc);
 #else
-RS_HD uint32_t rs_vsubus4(uint32_t a, uint32_t b) {
-  uint32_t r = 0;
-  for (int i = 0; i < 4; ++i) {
-    uint32_t x = (a >> (8 * i)) & 255u, y = (b >> (8 * i)) & 255u;
-    r |= (x > y ? x - y : 0u) << (8 * i);
-  }
-  return r;
-}
-RS_HD uint32_t rs_vminu4(uint32_t a, uint32_t b) {
-  uint32_t r = 0;
-  for (int i = 0; i < 4; ++i) {
-    uint32_t x = (a >> (8 * i)) & 255u, y = (b >> (8 * i)) & 255u;
-    r |= (x < y ? x : y) << (8 * i);
-  }
-  return r;
-}
-RS_HD uint32_t rs_vcmpeq4(uint32_t a, uint32_t b) {
-  uint32_t r = 0;
-  for (int i = 0; i < 4; ++i)
-    if (((a >> (8 * i)) & 255u) == ((b >> (8 * i)) & 255u)) r |= 255u << (8 * i);
-  return r;
-}
-RS_HD uint32_t rs_vcmpgeu4(uint32_t a, uint32_t b) {
-  uint32_t r = 0;
-  for (int i = 0; i < 4; ++i)
-    if (((a >> (8 * i)) & 255u) >= ((b >> (8 * i)) & 255u)) r |= 255u << (8 * i);
-  return r;
-}
-RS_HD uint32_t rs_bytesum(uint32_t a, uint32_t acc) {
-  return acc + (a & 255u) + ((a >> 8) & 255u) + ((a >> 16) & 255u) + (a >> 24);
-}
-RS_HD int rs_ffs(uint32_t a) { return a ? __builtin_ffs((int)a) : 0; }
+  for (int i = 0; i < 4; ++i) acc += ((a >> (8 * i)) & 255u) * ((b >> (8 * i)) & 255u);
+  return acc;
 #endif
-
-/* Decoded view of one lane's 16 bytes. */
-typedef struct rs_lane {
-  uint32_t w[4];    /* run bytes (header bytes zeroed)                     */
-  uint32_t incl[4]; /* byte j = sum of lengths of bytes 0..j of the word   */
-  uint32_t base[4]; /* symbols in the lane before word k                    */
-  uint32_t total;   /* symbols in the lane                                   */
-} rs_lane;
-
-/* g = lane position in its group (0..7); x,y,z,w = the lane's 16 bytes of the block.
- * Lanes 0,1 hold header only, lane 2 holds cnt[T] in x,y and run bytes in z,w. */
-RS_HD void rs_lane_prepare(uint32_t x, uint32_t y, uint32_t z, uint32_t w, int g, rs_lane* d) {
-  d->w[0] = g >= 3 ? x : 0u;
-  d->w[1] = g >= 3 ? y : 0u;
-  d->w[2] = g >= 2 ? z : 0u;
-  d->w[3] = g >= 2 ? w : 0u;
-  uint32_t run = 0;
-#pragma unroll
-  for (int k = 0; k < 4; ++k) {
-    const uint32_t p = d->w[k] & RS_LEN_MASK;
-    d->incl[k] = p * RS_ONES; /* no byte overflows: 4 x 31 = 124 */
-    d->base[k] = run;
-    run += d->incl[k] >> 24;
-  }
-  d->total = run;
 }
 
-/* Occurrences of symbol c among the first t symbols of the lane (t may be <= 0 or > total). */
-RS_HD uint32_t rs_lane_count(const rs_lane* d, uint32_t c, int32_t t) {
+RS_HD int rs_ffs(uint32_t a) {
+#if defined(__CUDA_ARCH__)
+  return __ffs((int)a);
+#else
+  return a ? __builtin_ffs((int)a) : 0;
+#endif
+}
+
+/* 8 in every byte whose run symbol equals c (cpat = c * 0x20202020), else 0 */
+RS_HD uint32_t rs_w_match8(uint32_t w, uint32_t cpat) {
+  const uint32_t x = (w ^ cpat) & RS_SYM_MASK;            /* 0 in the symbol bits where equal      */
+  return ~((x >> 5) + 0x07070707u) & 0x08080808u;         /* bit 3 stays clear only for x == 0     */
+}
+
+/* byte j = number of symbols of run j that lie among the first tt symbols of the word;
+ * p = run lengths (w & RS_LEN_MASK), 0 <= tt <= 127 */
+RS_HD uint32_t rs_w_take(uint32_t p, uint32_t tt) {
+  const uint32_t incl = p * RS_ONES;                      /* byte j = len_0 + .. + len_j (<= 124)  */
+  const uint32_t ttr = tt * RS_ONES;
+  const uint32_t d = (incl | RS_HIGH) - ttr;              /* bit 7 of byte j set iff incl_j >= tt  */
+  const uint32_t ge = ((d >> 7) & RS_ONES) * 0xFFu;       /* 0xFF where incl_j >= tt               */
+  const uint32_t m = (ttr & ge) | (incl & ~ge);           /* min(incl_j, tt)                       */
+  return m * 0xFFFFFF01u;                                 /* m_j - m_{j-1}: no borrows, m ascends  */
+}
+
+/* index (0..3) of the first byte whose inclusive length prefix reaches tt, 1 <= tt <= word total */
+RS_HD uint32_t rs_w_byte_of(uint32_t p, uint32_t tt) {
+  const uint32_t incl = p * RS_ONES;
+  const uint32_t d = ((incl | RS_HIGH) - tt * RS_ONES) & RS_HIGH;
+  return (uint32_t)(rs_ffs(d) - 1) >> 3;
+}
+
+/* Symbols held by the NW words. */
+template <int NW>
+RS_HD uint32_t rs_words_total(const uint32_t (&w)[NW]) {
+  uint32_t tot = 0;
+#pragma unroll
+  for (int j = 0; j < NW; ++j) tot = rs_dot(w[j] & RS_LEN_MASK, RS_ONES, tot);
+  return tot;
+}
+
+/* Occurrences of symbol c among the first t1 (resp. t2) symbols of the words.  t may be <= 0
+ * (nothing) or >= the total (everything).  One pass: whole words before the target are added with
+ * one dp4a; the single word the target falls into is kept aside and resolved once after the loop. */
+template <int NW, bool TWO>
+RS_HD void rs_words_rank(const uint32_t (&w)[NW], uint32_t c, int32_t t1, int32_t t2, uint32_t* r1, uint32_t* r2) {
+  const uint32_t cpat = c * 0x20202020u;
+  int32_t run = 0;
+  uint32_t acc1 = 0, acc2 = 0;   /* 8 x count over fully included words           */
+  uint32_t bw1 = w[0], bw2 = w[0]; /* first word that is not fully included        */
+  int32_t rb1 = 0, rb2 = 0;      /* symbols before that word                       */
+#pragma unroll
+  for (int j = 0; j < NW; ++j) {
+    const uint32_t p = w[j] & RS_LEN_MASK;
+    const uint32_t cw = rs_dot(p, rs_w_match8(w[j], cpat), 0);
+    const int32_t end = run + (int32_t)rs_dot(p, RS_ONES, 0);
+    const uint32_t nxt = (j + 1 < NW) ? w[j + 1] : 0u;
+    if (end <= t1) { acc1 += cw; bw1 = nxt; rb1 = end; }
+    if (TWO && end <= t2) { acc2 += cw; bw2 = nxt; rb2 = end; }
+    run = end;
+  }
+  {
+    int32_t tt = t1 - rb1;
+    tt = tt < 0 ? 0 : (tt > 127 ? 127 : tt);
+    acc1 = rs_dot(rs_w_take(bw1 & RS_LEN_MASK, (uint32_t)tt), rs_w_match8(bw1, cpat), acc1);
+    *r1 = acc1 >> 3;
+  }
+  if (TWO) {
+    int32_t tt = t2 - rb2;
+    tt = tt < 0 ? 0 : (tt > 127 ? 127 : tt);
+    acc2 = rs_dot(rs_w_take(bw2 & RS_LEN_MASK, (uint32_t)tt), rs_w_match8(bw2, cpat), acc2);
+    *r2 = acc2 >> 3;
+  }
+}
+
+/* Symbol (0..4) of the t-th symbol of the words, 1 <= t <= total; 0xFF when t is outside. */
+template <int NW>
+RS_HD uint32_t rs_words_symbol(const uint32_t (&w)[NW], int32_t t) {
+  int32_t run = 0, rb = 0;
+  uint32_t bw = w[0];
+#pragma unroll
+  for (int j = 0; j < NW; ++j) {
+    const int32_t end = run + (int32_t)rs_dot(w[j] & RS_LEN_MASK, RS_ONES, 0);
+    const uint32_t nxt = (j + 1 < NW) ? w[j + 1] : 0u;
+    if (end < t) { bw = nxt; rb = end; }   /* word lies wholly before the t-th symbol */
+    run = end;
+  }
+  if (t < 1 || t > run) return 0xFFu;
+  const uint32_t byte = rs_w_byte_of(bw & RS_LEN_MASK, (uint32_t)(t - rb));
+  return (bw >> (8 * byte + 5)) & 7u;
+}
+
+/* Occurrences of c in all the words. */
+template <int NW>
+RS_HD uint32_t rs_words_count_all(const uint32_t (&w)[NW], uint32_t c) {
   const uint32_t cpat = c * 0x20202020u;
   uint32_t acc = 0;
 #pragma unroll
-  for (int k = 0; k < 4; ++k) {
-    int32_t tk = t - (int32_t)d->base[k];
-    tk = tk < 0 ? 0 : (tk > 255 ? 255 : tk);
-    const uint32_t p = d->w[k] & RS_LEN_MASK;
-    const uint32_t excl = d->incl[k] - p;
-    const uint32_t take = rs_vminu4(p, rs_vsubus4((uint32_t)tk * RS_ONES, excl));
-    const uint32_t match = rs_vcmpeq4(d->w[k] & RS_SYM_MASK, cpat);
-    acc = rs_bytesum(take & match, acc);
-  }
-  return acc;
+  for (int j = 0; j < NW; ++j) acc = rs_dot(w[j] & RS_LEN_MASK, rs_w_match8(w[j], cpat), acc);
+  return acc >> 3;
 }
 
-/* Occurrences of symbol c in the whole lane. */
-RS_HD uint32_t rs_lane_count_all(const rs_lane* d, uint32_t c) {
+/* Select inside the words: 1-based position (counted in symbols from the first word) of the r-th
+ * occurrence of c, 1 <= r <= rs_words_count_all; 0 when r is outside. */
+template <int NW>
+RS_HD uint32_t rs_words_select(const uint32_t (&w)[NW], uint32_t c, int32_t r) {
   const uint32_t cpat = c * 0x20202020u;
-  uint32_t acc = 0;
+  int32_t run = 0, rb = 0, seen = 0, sb = 0;
+  uint32_t bw = w[0];
 #pragma unroll
-  for (int k = 0; k < 4; ++k) {
-    const uint32_t match = rs_vcmpeq4(d->w[k] & RS_SYM_MASK, cpat);
-    acc = rs_bytesum(d->w[k] & RS_LEN_MASK & match, acc);
+  for (int j = 0; j < NW; ++j) {
+    const uint32_t p = w[j] & RS_LEN_MASK;
+    const int32_t cend = seen + (int32_t)(rs_dot(p, rs_w_match8(w[j], cpat), 0) >> 3);
+    const int32_t end = run + (int32_t)rs_dot(p, RS_ONES, 0);
+    const uint32_t nxt = (j + 1 < NW) ? w[j + 1] : 0u;
+    if (cend < r) { bw = nxt; rb = end; sb = cend; }   /* word holds none of the r-th occurrence */
+    run = end;
+    seen = cend;
   }
-  return acc;
-}
-
-/* Symbol (0..4) of the t-th symbol of the lane, 1 <= t <= total; 0xFF if t is outside the lane. */
-RS_HD uint32_t rs_lane_symbol(const rs_lane* d, int32_t t) {
-  uint32_t sym = 0xFFu;
-#pragma unroll
-  for (int k = 0; k < 4; ++k) {
-    const int32_t tk = t - (int32_t)d->base[k];
-    const int32_t wt = (int32_t)(d->incl[k] >> 24);
-    if (tk >= 1 && tk <= wt) {
-      const uint32_t ge = rs_vcmpgeu4(d->incl[k], (uint32_t)tk * RS_ONES) & 0x80808080u;
-      const int byte = (rs_ffs(ge) - 1) >> 3;
-      sym = (d->w[k] >> (8 * byte + 5)) & 7u;
-    }
-  }
-  return sym;
-}
-
-/* Select inside a lane: position (1-based count of symbols from the lane start) of the r-th
- * occurrence of c in the lane, 1 <= r <= rs_lane_count_all; 0 if r is outside. */
-RS_HD uint32_t rs_lane_select(const rs_lane* d, uint32_t c, int32_t r) {
-  const uint32_t cpat = c * 0x20202020u;
-  uint32_t pos = 0;
-  int32_t seen = 0;
-#pragma unroll
-  for (int k = 0; k < 4; ++k) {
-    const uint32_t match = rs_vcmpeq4(d->w[k] & RS_SYM_MASK, cpat);
-    const uint32_t p = d->w[k] & RS_LEN_MASK;
-    const uint32_t mp = p & match;           /* lengths of matching runs               */
-    const uint32_t mincl = mp * RS_ONES;     /* inclusive prefix of matching lengths   */
-    const int32_t mt = (int32_t)(mincl >> 24);
-    const int32_t rk = r - seen;
-    if (rk >= 1 && rk <= mt) {
-      const uint32_t ge = rs_vcmpgeu4(mincl, (uint32_t)rk * RS_ONES) & 0x80808080u;
-      const int byte = (rs_ffs(ge) - 1) >> 3;
-      /* symbols before that run inside the word + offset inside the run */
-      const uint32_t before = ((d->incl[k] - p) >> (8 * byte)) & 255u;
-      const uint32_t mbefore = ((mincl - mp) >> (8 * byte)) & 255u;
-      pos = d->base[k] + before + ((uint32_t)rk - mbefore);
-    }
-    seen += mt;
-  }
-  return pos;
+  if (r < 1 || r > seen) return 0u;
+  /* inside bw: lengths of the matching runs only, then the byte whose matching prefix reaches rk */
+  const uint32_t p = bw & RS_LEN_MASK;
+  const uint32_t m8 = rs_w_match8(bw, cpat);
+  const uint32_t mp = p & ((m8 >> 3) * 0xFFu);
+  const uint32_t rk = (uint32_t)(r - sb);
+  const uint32_t byte = rs_w_byte_of(mp, rk);
+  const uint32_t before = ((p * RS_ONES - p) >> (8 * byte)) & 255u;      /* symbols before that run in the word  */
+  const uint32_t mbefore = ((mp * RS_ONES - mp) >> (8 * byte)) & 255u;   /* matching symbols before that run     */
+  return (uint32_t)rb + before + (rk - mbefore);
 }
 
 #endif

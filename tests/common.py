@@ -115,6 +115,7 @@ class Emul:
             L.emul_open_file.argtypes = [C.c_char_p, C.POINTER(C.c_int)]
             L.emul_close.argtypes = [C.c_void_p]
             L.emul_set_tail.argtypes = [C.c_void_p, C.c_int]
+            L.emul_set_lanes.argtypes = [C.c_void_p, C.c_int]
             L.emul_info.argtypes = [C.c_void_p, _u64p]
             L.emul_occ_batch.argtypes = [C.c_void_p, _u8p, _u64p, C.c_uint64, _u64p]
             L.emul_char_batch.argtypes = [C.c_void_p, _u64p, C.c_uint64, _u8p]
@@ -124,7 +125,7 @@ class Emul:
             cls._lib = L
         return cls._lib
 
-    def __init__(self, case: Case | None = None, path: str | None = None):
+    def __init__(self, case: Case | None = None, path: str | None = None, lanes: int = 8):
         L = self.lib()
         st = C.c_int()
         if path is not None:
@@ -140,6 +141,7 @@ class Emul:
             self.tot = [int(x) for x in info[12:17]]
             self.init_occ = [int(x) for x in info[17:22]]
             self.clamp_char = int(info[22])
+            L.emul_set_lanes(self._h, lanes)
 
     def __del__(self):
         if getattr(self, "_h", None):
@@ -148,6 +150,10 @@ class Emul:
 
     def set_tail(self, on: bool):
         self.lib().emul_set_tail(self._h, int(on))
+
+    def set_lanes(self, lanes: int):
+        """lanes per query of the replayed device code: 1, 2, 4 or 8"""
+        self.lib().emul_set_lanes(self._h, lanes)
 
     def occ(self, syms, idx):
         idx = np.ascontiguousarray(idx, dtype=np.uint64)

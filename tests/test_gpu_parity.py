@@ -14,11 +14,14 @@ pytestmark = pytest.mark.gpu
 U64MAX = np.iinfo(np.uint64).max
 
 
-@pytest.fixture(scope="module")
-def engine():
+@pytest.fixture(scope="module", params=[8, 4, 2, 1], ids=lambda l: f"lanes{l}")
+def engine(request):
+    """The C-ABI engine, once per lane-group width (a tuning knob: results must not depend on it)."""
     import torch
     assert torch.cuda.is_available(), "GPU tests need a CUDA device"
     from readserver_b200 import engine as e
+    e.set_lanes(request.param)
+    assert e.get_lanes() == request.param
     return e
 
 
