@@ -93,6 +93,10 @@ int rs_get_char_batch(const rs_index* ix, const uint64_t* index, size_t n, char*
 /* RLEBWT::getF(index), rlebwt.cpp:307-314 */
 int rs_get_f_batch(const rs_index* ix, const uint64_t* index, size_t n, char* out);
 
+/* RLEBWT::getOccAt(b, count), rlebwt.cpp:233-266: position of the count-th occurrence of b
+ * (count outside [1, occurrences of b] yields UINT64_MAX; undefined in the reference) */
+int rs_get_occ_at_batch(const rs_index* ix, const char* b, const uint64_t* count, size_t n, uint64_t* out);
+
 /* ---- include/bwt/query.h:18-32, batched ---------------------------------------------------------- */
 /* findInterval (src/bwt/query.cpp:24-41) for Q k-mers of one length k stored back to back.
  * lower/upper are the reference's BWTInterval, including the value at the step where the search
@@ -128,6 +132,16 @@ int rs_extract_prefix_batch(const rs_index* ix, const uint64_t* rows, size_t n, 
                             uint64_t* lexrank, uint32_t* steps, uint64_t* read_index, char* bases);
 int rs_extract_prefix_batch_dev(const rs_index* ix, const void* d_rows, size_t n, uint32_t max_steps,
                                 void* d_lexrank, void* d_steps, void* d_read_index, void* d_bases, void* stream);
+
+/* extractPostfix (src/bwt/query.cpp:65-85) for n BWT rows: forward walk by getF / getOccAt to the '$'.
+ *   read_index[i] the row (< num_strings) at which getF returned '$' = the read's index in builder
+ *                 input order (UINT64_MAX if the walk did not end within max_steps bases)
+ *   steps[i]      bases walked (UINT32_MAX on cut-off)                -- may be NULL
+ *   bases         n x max_steps chars in reading order, NUL padded    -- may be NULL */
+int rs_extract_postfix_batch(const rs_index* ix, const uint64_t* rows, size_t n, uint32_t max_steps,
+                             uint64_t* read_index, uint32_t* steps, char* bases);
+int rs_extract_postfix_batch_dev(const rs_index* ix, const void* d_rows, size_t n, uint32_t max_steps,
+                                 void* d_read_index, void* d_steps, void* d_bases, void* stream);
 
 #ifdef __cplusplus
 }

@@ -162,18 +162,18 @@ int rs_build_host_index(const uint8_t* runs, uint64_t R, uint64_t num_strings, u
     }
   }
 
-  /* select directories */
+  /* select directories: about one entry per two blocks for every symbol */
   for (int c = 0; c < RS_NSYM; ++c) {
-    const uint64_t nent = (cnt[c] >> RS_SEL_SHIFT) + 2;
+    uint32_t sh = 0;
+    while (sh < RS_SEL_SHIFT_MAX && (cnt[c] >> (sh + 1)) >= nblocks / 2 + 1) ++sh;
+    out.sel_shift[c] = sh;
+    const uint64_t nent = (cnt[c] >> sh) + 2;
     out.sel[c].assign(nent, (uint32_t)(nblocks - 1));
   }
   {
     uint64_t k[RS_NSYM] = {0, 0, 0, 0, 0};
     for (uint64_t b = 0; b < nblocks; ++b) {
-      uint64_t before[RS_NSYM], after[RS_NSYM];
-      const rs_block& B = out.blocks[b];
-      before[0] = B.start - (B.cnt[0] + B.cnt[1] + B.cnt[2] + B.cnt[3]);
-      for (int c = 1; c < RS_NSYM; ++c) before[c] = B.cnt[c - 1];
+      uint64_t after[RS_NSYM];
       if (b + 1 < nblocks) {
         const rs_block& N = out.blocks[b + 1];
         after[0] = N.start - (N.cnt[0] + N.cnt[1] + N.cnt[2] + N.cnt[3]);
@@ -182,8 +182,7 @@ int rs_build_host_index(const uint8_t* runs, uint64_t R, uint64_t num_strings, u
         memcpy(after, cnt, sizeof(after));
       }
       for (int c = 0; c < RS_NSYM; ++c) {
-        (void)before;
-        while ((k[c] << RS_SEL_SHIFT) < after[c]) {
+        while ((k[c] << out.sel_shift[c]) < after[c]) {
           out.sel[c][k[c]] = (uint32_t)b;
           ++k[c];
         }

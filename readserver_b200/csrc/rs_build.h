@@ -15,6 +15,7 @@ struct RsHostIndex {
   std::vector<rs_block> blocks;
   std::vector<uint64_t> dir;
   std::vector<uint32_t> sel[RS_NSYM];
+  uint32_t sel_shift[RS_NSYM] = {0, 0, 0, 0, 0};
   uint64_t n = 0, num_strings = 0, num_runs = 0;
   uint64_t pc[RS_NSYM] = {0, 0, 0, 0, 0};
   uint64_t tot[RS_NSYM] = {0, 0, 0, 0, 0};

@@ -109,6 +109,7 @@ static int upload(rs_index* ix, const RsHostIndex& h) {
     CU(cudaMalloc(&ix->d_sel[c], sb));
     CU(cudaMemcpy(ix->d_sel[c], h.sel[c].data(), sb, cudaMemcpyHostToDevice));
     ix->dev.sel[c] = (const uint32_t*)ix->d_sel[c];
+    ix->dev.sel_shift[c] = h.sel_shift[c];
     ix->hbm_bytes += sb;
     ix->dev.pc[c] = h.pc[c];
     ix->dev.tot[c] = h.tot[c];
@@ -411,6 +412,55 @@ int rs_extract_prefix_batch(const rs_index* ix, const uint64_t* rows, size_t n, 
   if (lexrank) CU(cudaMemcpyAsync(lexrank, ix->s_out.p, n * 8, cudaMemcpyDeviceToHost, st));
   if (steps) CU(cudaMemcpyAsync(steps, ix->s_out2.p, n * 4, cudaMemcpyDeviceToHost, st));
   if (read_index) CU(cudaMemcpyAsync(read_index, ix->s_out3.p, n * 8, cudaMemcpyDeviceToHost, st));
+  if (bases) CU(cudaMemcpyAsync(bases, ix->s_out4.p, n * (size_t)max_steps, cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  return RS_STATUS_OK;
+}
+
+/* ---- select / extractPostfix ---- */
+int rs_get_occ_at_batch(const rs_index* ix, const char* b, const uint64_t* count, size_t n, uint64_t* out) {
+  if (!ix || (n && (!b || !count || !out))) return fail(RS_STATUS_ARG, "null argument");
+  if (!n) return RS_STATUS_OK;
+  std::lock_guard<std::mutex> lk(ix->mu);
+  CU(cudaSetDevice(ix->device));
+  CU(ix->s_in.need(n));
+  CU(ix->s_in2.need(n * 8));
+  CU(ix->s_out.need(n * 8));
+  cudaStream_t st = ix->stream;
+  CU(cudaMemcpyAsync(ix->s_in.p, b, n, cudaMemcpyHostToDevice, st));
+  CU(cudaMemcpyAsync(ix->s_in2.p, count, n * 8, cudaMemcpyHostToDevice, st));
+  CU(rs_launch_occ_at(ix->dev, (const uint8_t*)ix->s_in.p, (const uint64_t*)ix->s_in2.p, n, (uint64_t*)ix->s_out.p, st));
+  CU(cudaMemcpyAsync(out, ix->s_out.p, n * 8, cudaMemcpyDeviceToHost, st));
+  CU(cudaStreamSynchronize(st));
+  return RS_STATUS_OK;
+}
+
+int rs_extract_postfix_batch_dev(const rs_index* ix, const void* d_rows, size_t n, uint32_t max_steps,
+                                 void* d_read_index, void* d_steps, void* d_bases, void* stream) {
+  if (!ix || (n && !d_rows)) return fail(RS_STATUS_ARG, "null argument");
+  if (max_steps < 1) return fail(RS_STATUS_ARG, "max_steps must be >= 1");
+  CU(rs_launch_extract_postfix(ix->dev, (const uint64_t*)d_rows, n, max_steps, (uint64_t*)d_read_index,
+                               (uint32_t*)d_steps, (uint8_t*)d_bases, (cudaStream_t)stream));
+  return RS_STATUS_OK;
+}
+
+int rs_extract_postfix_batch(const rs_index* ix, const uint64_t* rows, size_t n, uint32_t max_steps,
+                             uint64_t* read_index, uint32_t* steps, char* bases) {
+  if (!ix || (n && !rows)) return fail(RS_STATUS_ARG, "null argument");
+  if (max_steps < 1) return fail(RS_STATUS_ARG, "max_steps must be >= 1");
+  if (!n) return RS_STATUS_OK;
+  std::lock_guard<std::mutex> lk(ix->mu);
+  CU(cudaSetDevice(ix->device));
+  CU(ix->s_in.need(n * 8));
+  CU(ix->s_out.need(n * 8));
+  CU(ix->s_out2.need(n * 4));
+  if (bases) CU(ix->s_out4.need(n * (size_t)max_steps));
+  cudaStream_t st = ix->stream;
+  CU(cudaMemcpyAsync(ix->s_in.p, rows, n * 8, cudaMemcpyHostToDevice, st));
+  CU(rs_launch_extract_postfix(ix->dev, (const uint64_t*)ix->s_in.p, n, max_steps, (uint64_t*)ix->s_out.p,
+                               (uint32_t*)ix->s_out2.p, bases ? (uint8_t*)ix->s_out4.p : nullptr, st));
+  if (read_index) CU(cudaMemcpyAsync(read_index, ix->s_out.p, n * 8, cudaMemcpyDeviceToHost, st));
+  if (steps) CU(cudaMemcpyAsync(steps, ix->s_out2.p, n * 4, cudaMemcpyDeviceToHost, st));
   if (bases) CU(cudaMemcpyAsync(bases, ix->s_out4.p, n * (size_t)max_steps, cudaMemcpyDeviceToHost, st));
   CU(cudaStreamSynchronize(st));
   return RS_STATUS_OK;

@@ -242,28 +242,24 @@ __device__ __forceinline__ void rs_grp_occ2(const rs_index_dev& ix, const rs_grp
   const bool split = (b1 != b2) || m1 || m2 || p2 < p1; /* group-uniform */
   rs_blk_load(ix, b1, G, &H.B);
   if (split) rs_blk_load(ix, b2, G, &B2);
-  if (!split) {
-    /* common case: one block serves both positions */
-    rs_grp_settle(ix, G, p1, b1, false, &H);
-    const int32_t t1 = (int32_t)H.off - (int32_t)H.lane_base;
-    const int32_t t2 = t1 + (int32_t)(uint32_t)(p2 - p1);
-    uint32_t a1, a2;
-    rs_words_rank<rs_grp<LANES>::NW, true>(H.B.w, c, t1, t2, &a1, &a2);
-    const uint64_t before = rs_blk_count_before(G, H.B, c, H.start);
-    if (LANES > 1) {
-      a1 = rs_grp_sum(G, a1);
-      a2 = rs_grp_sum(G, a2);
-    }
-    *r1 = none1 ? 0 : before + a1;
-    *r2 = none2 ? 0 : before + a2;
-    return;
-  }
+  /* block of p1: one scan answers p1 and, when it lives in the same block, p2 */
   rs_grp_settle(ix, G, p1, b1, m1, &H);
-  const uint64_t x1 = rs_hit_rank(G, H, c);
-  H.B = B2;
-  rs_grp_settle(ix, G, p2, b2, m2, &H);
-  const uint64_t x2 = rs_hit_rank(G, H, c);
-  *r1 = none1 ? 0 : x1;
+  const int32_t t1 = (int32_t)H.off - (int32_t)H.lane_base;
+  const int32_t t2 = split ? -1 : t1 + (int32_t)(uint32_t)(p2 - p1);
+  uint32_t a1, a2;
+  rs_words_rank<rs_grp<LANES>::NW, true>(H.B.w, c, t1, t2, &a1, &a2);
+  const uint64_t before = rs_blk_count_before(G, H.B, c, H.start);
+  if (LANES > 1) {
+    a1 = rs_grp_sum(G, a1);
+    a2 = rs_grp_sum(G, a2);
+  }
+  uint64_t x2 = before + a2;
+  if (split) { /* group-uniform: p2 sits in another block */
+    H.B = B2;
+    rs_grp_settle(ix, G, p2, b2, m2, &H);
+    x2 = rs_hit_rank(G, H, c);
+  }
+  *r1 = none1 ? 0 : before + a1;
   *r2 = none2 ? 0 : x2;
 }
 
@@ -288,6 +284,59 @@ __device__ __forceinline__ uint32_t rs_grp_lf_step(const rs_index_dev& ix, const
   }
   *next = ix.pc[sym] + occ;
   return sym;
+}
+
+/* occurrences of c before block b, read straight from its header (no decode) */
+__device__ __forceinline__ uint64_t rs_hdr_count_before(const rs_index_dev& ix, uint64_t b, uint32_t c) {
+  const uint64_t* h = reinterpret_cast<const uint64_t*>(ix.blocks) + b * (RS_BLOCK_BYTES / 8);
+  if (c != 0) return __ldg(h + c);
+  return __ldg(h) - (__ldg(h + 1) + __ldg(h + 2) + __ldg(h + 3) + __ldg(h + 4));
+}
+
+/* getOccAt(c, r) (rlebwt.cpp:233-266): position of the r-th occurrence of c, 1 <= r <= tot[c].
+ * The reference's select never consults m_vSum, so there is no tail behaviour to reproduce
+ * (SURVEY.md A8).  r outside [1, tot[c]] yields 2^64-1. */
+template <int LANES>
+__device__ __forceinline__ uint64_t rs_grp_occ_at(const rs_index_dev& ix, const rs_grp<LANES>& G, uint32_t c, uint64_t r) {
+  const bool bad = (r == 0 || r > ix.tot[c]);
+  if (bad) r = 1;
+  if (ix.tot[c] == 0) return ~0ull; /* uniform: symbol absent from the BWT */
+  uint64_t b = __ldg(ix.sel[c] + ((r - 1) >> ix.sel_shift[c]));
+  /* skip blocks that end before the r-th occurrence: their successor's header says so */
+  while (b + 1 < ix.nblocks && rs_hdr_count_before(ix, b + 1, c) < r) ++b;
+  rs_hit<LANES> H;
+  rs_blk_load(ix, b, G, &H.B);
+  rs_blk_words(G, &H.B);
+  H.start = rs_blk_field(G, H.B, 0);
+  const uint64_t before = rs_blk_count_before(G, H.B, c, H.start);
+  const uint32_t want = (uint32_t)(r - before);
+  uint32_t span, ctot;
+  const uint32_t lane_base = rs_grp_exscan(G, rs_words_total(H.B.w), &span);
+  const uint32_t cbase = rs_grp_exscan(G, rs_words_count_all(H.B.w, c), &ctot);
+  const uint32_t p = rs_words_select(H.B.w, c, (int32_t)want - (int32_t)cbase);
+  uint32_t in_block = p ? lane_base + p : 0u; /* 1-based position inside the block, from the owning lane */
+  if (LANES > 1) {
+    const unsigned owners = __ballot_sync(G.mask, p != 0) & G.mask;
+    in_block = __shfl_sync(G.mask, in_block, (__ffs(owners) - 1) & (LANES - 1), LANES);
+  }
+  return bad ? ~0ull : H.start + in_block - 1;
+}
+
+/* getF(i) (rlebwt.cpp:307-314) as a symbol code */
+__device__ __forceinline__ uint32_t rs_f_code(const rs_index_dev& ix, uint64_t i) {
+  uint32_t ci = 0;
+#pragma unroll
+  for (int c = 1; c < RS_NSYM; ++c) ci += (ix.pc[c] <= i) ? 1u : 0u;
+  return ci;
+}
+
+/* One step of extractPostfix (src/bwt/query.cpp:69-75): f = getF(idx); idx' = getOccAt(f, idx - PC(f) + 1). */
+template <int LANES>
+__device__ __forceinline__ uint32_t rs_grp_fl_step(const rs_index_dev& ix, const rs_grp<LANES>& G, uint64_t idx,
+                                                   uint64_t* next) {
+  const uint32_t f = rs_f_code(ix, idx);
+  *next = rs_grp_occ_at(ix, G, f, idx - ix.pc[f] + 1);
+  return f;
 }
 
 #endif

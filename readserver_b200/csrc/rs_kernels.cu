@@ -219,6 +219,81 @@ __global__ void __launch_bounds__(RS_THREADS)
   if (stats && G.g == 0 && lf_steps) atomicAdd(stats + 1, lf_steps);
 }
 
+template <int LANES>
+__global__ void __launch_bounds__(RS_THREADS) k_occ_at(const __grid_constant__ rs_index_dev ix, const uint8_t* __restrict__ syms,
+                                                       const uint64_t* __restrict__ cnt, uint64_t n,
+                                                       uint64_t* __restrict__ out) {
+  const rs_grp<LANES> G;
+  constexpr int GPB = RS_THREADS / LANES;
+  const uint64_t ngroups = (uint64_t)gridDim.x * GPB;
+  for (uint64_t i = (uint64_t)blockIdx.x * GPB + threadIdx.x / LANES; i < n; i += ngroups) {
+    const uint64_t r = rs_grp_occ_at(ix, G, rs_code(syms[i]), cnt[i]);
+    if (G.g == 0) out[i] = r;
+  }
+}
+
+/* extractPostfix (query.cpp:65-85): forward walk by getF / getOccAt from each row to the '$' row of
+ * its read.  read_index = the row at which getF returned '$' (the read's index in builder input
+ * order); the select of that last step is still performed, as the reference does. */
+template <int LANES>
+__global__ void __launch_bounds__(RS_THREADS)
+    k_extract_postfix(const __grid_constant__ rs_index_dev ix, const uint64_t* __restrict__ rows, uint64_t n,
+                      uint32_t max_steps, uint64_t* __restrict__ read_index, uint32_t* __restrict__ steps,
+                      uint8_t* __restrict__ bases) {
+  const rs_grp<LANES> G;
+  constexpr int GPB = RS_THREADS / LANES;
+  const uint64_t ngroups = (uint64_t)gridDim.x * GPB;
+  uint64_t next_i = (uint64_t)blockIdx.x * GPB + threadIdx.x / LANES;
+  uint64_t i = 0, idx = 0;
+  uint32_t s = 0;
+  bool active = false;
+  while (true) {
+    if (!active && next_i < n) {
+      i = next_i;
+      next_i += ngroups;
+      idx = rows[i];
+      s = 0;
+      active = true;
+    }
+    if (__all_sync(RS_FULL, !active)) break;
+    if (active) {
+      uint64_t nxt;
+      const uint64_t at = idx;
+      const uint32_t f = rs_grp_fl_step(ix, G, idx < ix.n ? idx : ix.n - 1, &nxt);
+      idx = nxt;
+      bool done = false;
+      uint64_t term = 0;
+      uint32_t nsteps = 0;
+      if (f == 0) {
+        done = true;
+        term = at;
+        nsteps = s;
+      } else {
+        if (bases && s < max_steps && G.g == 0) bases[i * (uint64_t)max_steps + s] = (uint8_t)rs_ascii(f);
+        ++s;
+        if (s > max_steps || idx == ~0ull) {
+          done = true;
+          term = ~0ull;
+          nsteps = 0xFFFFFFFFu;
+        }
+      }
+      if (done) {
+        if (G.g == 0) {
+          if (read_index) read_index[i] = term;
+          if (steps) steps[i] = nsteps;
+        }
+        if (bases) {
+          uint8_t* p = bases + i * (uint64_t)max_steps;
+          const uint32_t m = nsteps == 0xFFFFFFFFu ? 0u : nsteps;
+          __syncwarp(G.mask);
+          for (uint32_t a = m + G.g; a < max_steps; a += LANES) p[a] = 0;
+        }
+        active = false;
+      }
+    }
+  }
+}
+
 /* ---- launchers ---- */
 static int g_lanes = 0;
 
@@ -295,5 +370,19 @@ cudaError_t rs_launch_extract_prefix(const rs_index_dev& ix, const uint64_t* row
                                      uint8_t* bases, unsigned long long* stats, cudaStream_t st) {
   if (!n) return cudaSuccess;
   RS_DISPATCH(k_extract_prefix, n, st, ix, rows, n, max_steps, lexrank, steps, sai, read_index, bases, stats);
+  return cudaGetLastError();
+}
+
+cudaError_t rs_launch_occ_at(const rs_index_dev& ix, const uint8_t* syms, const uint64_t* cnt, uint64_t n, uint64_t* out,
+                             cudaStream_t st) {
+  if (!n) return cudaSuccess;
+  RS_DISPATCH(k_occ_at, n, st, ix, syms, cnt, n, out);
+  return cudaGetLastError();
+}
+
+cudaError_t rs_launch_extract_postfix(const rs_index_dev& ix, const uint64_t* rows, uint64_t n, uint32_t max_steps,
+                                      uint64_t* read_index, uint32_t* steps, uint8_t* bases, cudaStream_t st) {
+  if (!n) return cudaSuccess;
+  RS_DISPATCH(k_extract_postfix, n, st, ix, rows, n, max_steps, read_index, steps, bases);
   return cudaGetLastError();
 }

@@ -26,4 +26,9 @@ cudaError_t rs_launch_extract_prefix(const rs_index_dev& ix, const uint64_t* row
                                      uint64_t* lexrank, uint32_t* steps, const uint64_t* sai, uint64_t* read_index,
                                      uint8_t* bases, unsigned long long* stats, cudaStream_t st);
 
+cudaError_t rs_launch_occ_at(const rs_index_dev& ix, const uint8_t* syms, const uint64_t* cnt, uint64_t n, uint64_t* out,
+                             cudaStream_t st);
+cudaError_t rs_launch_extract_postfix(const rs_index_dev& ix, const uint64_t* rows, uint64_t n, uint32_t max_steps,
+                                      uint64_t* read_index, uint32_t* steps, uint8_t* bases, cudaStream_t st);
+
 #endif

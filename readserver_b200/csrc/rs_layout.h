@@ -17,9 +17,10 @@
  *     bits 52..61  b3  ... block +3
  *     bit  62      more than three block boundaries fall inside the slot (walk forward from +3)
  *
- *   select directory (per symbol c): one u32 per 2^RS_SEL_SHIFT occurrences of c
- *     entry k = index of the block holding the (k << RS_SEL_SHIFT | 1)-th occurrence of c,
- *     i.e. the last block whose cnt[c] <= k << RS_SEL_SHIFT.
+ *   select directory (per symbol c): one u32 per 2^s occurrences of c, s = sel_shift[c] chosen so
+ *     that a directory slot spans about two blocks (a sparse symbol such as '$' gets a small s)
+ *     entry k = index of the block holding the ((k << s) + 1)-th occurrence of c,
+ *     i.e. the block with cnt_before[c] <= k << s < cnt_before_next[c].
  */
 #ifndef RS_LAYOUT_H
 #define RS_LAYOUT_H
@@ -33,7 +34,7 @@
 #define RS_SLOT_SIZE (1u << RS_SLOT_SHIFT)
 #define RS_SLOT_MASK (RS_SLOT_SIZE - 1u)
 #define RS_DIR_MORE (1ull << 62)
-#define RS_SEL_SHIFT 10
+#define RS_SEL_SHIFT_MAX 10
 #define RS_NSYM 5
 #define RS_GROUP 8 /* widest lane group: 8 x 16 B = one block */
 #define RS_NO_ROW 0xFFFFFFFFFFFFFFFFull
@@ -68,7 +69,7 @@ typedef struct rs_index_dev {
   uint64_t tail_from;        /* getOcc  */
   uint64_t tail_from_char;   /* getChar */
   uint32_t emulate_tail;     /* 1 = bit-exact with the reference (default), 0 = true rank       */
-  uint32_t pad_;
+  uint32_t sel_shift[RS_NSYM]; /* select directory of c: one entry per 2^sel_shift[c] occurrences */
 } rs_index_dev;
 
 #endif

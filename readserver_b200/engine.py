@@ -68,6 +68,9 @@ def lib() -> C.CDLL:
         "rs_get_occ_batch": (i32, [vp, vp, vp, sz, vp]),
         "rs_get_char_batch": (i32, [vp, vp, sz, vp]),
         "rs_get_f_batch": (i32, [vp, vp, sz, vp]),
+        "rs_get_occ_at_batch": (i32, [vp, vp, vp, sz, vp]),
+        "rs_extract_postfix_batch": (i32, [vp, vp, sz, C.c_uint32, vp, vp, vp]),
+        "rs_extract_postfix_batch_dev": (i32, [vp, vp, sz, C.c_uint32, vp, vp, vp, vp]),
         "rs_find_interval_batch": (i32, [vp, vp, i32, sz, vp, vp]),
         "rs_find_interval_var_batch": (i32, [vp, vp, vp, sz, vp, vp]),
         "rs_find_interval_batch_dev": (i32, [vp, vp, i32, sz, vp, vp, vp]),
@@ -196,6 +199,16 @@ class GpuBWT:
         _check(lib().rs_get_f_batch(self._h, index.ctypes.data, index.size, out.ctypes.data))
         return out
 
+    def get_occ_at(self, b, count) -> np.ndarray:
+        b = _ascii(b)
+        count = np.ascontiguousarray(count, dtype=np.uint64)
+        if b.size == 1 and count.size != 1:
+            b = np.full(count.size, b[0], dtype=np.uint8)
+        assert b.size == count.size
+        out = np.empty(count.size, dtype=np.uint64)
+        _check(lib().rs_get_occ_at_batch(self._h, b.ctypes.data, count.ctypes.data, count.size, out.ctypes.data))
+        return out
+
     # -- query.h ---------------------------------------------------------------------------------
     def find_interval(self, kmers, k: int | None = None):
         """findInterval for a [Q, k] uint8 ASCII array (or a single str). Returns (lower, upper) uint64."""
@@ -251,6 +264,29 @@ class GpuBWT:
         if want_bases:
             out.append(bases)
         return tuple(out)
+
+    def extract_postfix(self, rows, max_steps: int = 1024, want_bases: bool = False):
+        """extractPostfix (query.cpp:65-85) per row: (read_index, steps[, bases [n, max_steps]])."""
+        rows = np.ascontiguousarray(rows, dtype=np.uint64)
+        n = rows.size
+        ri = np.empty(n, dtype=np.uint64)
+        st = np.empty(n, dtype=np.uint32)
+        bases = np.zeros((n, max_steps), dtype=np.uint8) if want_bases else None
+        _check(lib().rs_extract_postfix_batch(self._h, rows.ctypes.data, n, max_steps, ri.ctypes.data, st.ctypes.data,
+                                              _ptr(bases)))
+        return (ri, st, bases) if want_bases else (ri, st)
+
+    def extract_read(self, rows, max_steps: int = 1024) -> list[str]:
+        """extractPrefix(row) + extractPostfix(row): the read each row belongs to (query(), query.cpp:93-97)."""
+        _, ps, pb = self.extract_prefix(rows, max_steps, want_bases=True)
+        _, qs, qb = self.extract_postfix(rows, max_steps, want_bases=True)
+        out = []
+        for i in range(len(ps)):
+            if ps[i] == 0xFFFFFFFF or qs[i] == 0xFFFFFFFF:
+                out.append(None)
+            else:
+                out.append(bytes(pb[i, :ps[i]]).decode() + bytes(qb[i, :qs[i]]).decode())
+        return out
 
     # -- device-pointer forms (torch tensors on self.device; asynchronous on `stream`) -------------
     def find_interval_dev(self, d_kmers, k: int, q: int, d_lower, d_upper, stream: int = 0):

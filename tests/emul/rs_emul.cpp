@@ -191,7 +191,7 @@ uint64_t occ_at_t(const Emul& e, uint32_t c, uint64_t r) {
   constexpr int NW = 32 / LANES;
   const RsHostIndex& h = e.h;
   if (r == 0 || r > h.tot[c]) return ~0ull;
-  uint64_t b = h.sel[c][(r - 1) >> RS_SEL_SHIFT];
+  uint64_t b = h.sel[c][(r - 1) >> h.sel_shift[c]];
   while (true) {
     Hit<LANES> H;
     split_block(&h.blocks[b], &H);

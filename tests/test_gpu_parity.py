@@ -97,6 +97,32 @@ def test_extract_prefix_matches_oracle(name, datasets, engine):
             assert bytes(bases[i, :n]).decode() == s and not bases[i, n:].any()
 
 
+@pytest.mark.parametrize("name", ["tiny", "small", "clean", "mid", "deep"])
+def test_select_and_extract_postfix_match_oracle(name, datasets, engine):
+    case, P = datasets.case(name), datasets.port(name)
+    rng = np.random.default_rng(8)
+    with _gpu(engine, case) as B:
+        for ci, c in enumerate(b"$ACGT"):
+            tot = int(B.info.total[ci])
+            cnt = np.arange(1, tot + 1, dtype=np.uint64) if tot <= 300_000 else np.concatenate(
+                [rng.integers(1, tot + 1, 300_000).astype(np.uint64), np.array([1, tot], dtype=np.uint64)])
+            s = np.full(cnt.size, c, dtype=np.uint8)
+            assert np.array_equal(B.get_occ_at(s, cnt), P.get_occ_at_batch(s, cnt)), chr(c)
+        rows = rng.integers(0, P.bwlen, 20000).astype(np.uint64)
+        ri, st, bases = B.extract_postfix(rows, max_steps=128, want_bases=True)
+        _, _, ri2, st2 = P.locate_batch(rows, nthreads=4, prefix=False, max_steps=128)
+        assert np.array_equal(ri, ri2) and np.array_equal(st, st2)
+        assert (st != 0xFFFFFFFF).all()       # select is exact in the reference: every forward walk ends
+        for i in range(150):
+            s, _, n = P.extract_postfix(int(rows[i]))
+            assert bytes(bases[i, :n]).decode() == s and not bases[i, n:].any()
+        # query() (query.cpp:87-100): reads rebuilt from rows = extractPrefix + extractPostfix
+        if name == "clean":
+            reads = B.extract_read(rows[:300], max_steps=128)
+            assert reads == [P.extract_read(int(r)) for r in rows[:300]]
+            assert all(r == case.reads[int(i)] for r, i in zip(reads, ri[:300]))
+
+
 def test_tail_emulation_switch(datasets, engine):
     import torch
     from readserver_b200 import datagen as dg
