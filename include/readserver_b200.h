@@ -40,7 +40,8 @@ typedef enum rs_status {
   RS_STATUS_ARG = 5,       /* null / empty / inconsistent argument (e.g. empty query)     */
   RS_STATUS_CUDA = 6,      /* CUDA runtime error                                                        */
   RS_STATUS_TOO_LARGE = 7, /* more than 2^32 blocks in one shard                                        */
-  RS_STATUS_NO_TABLE = 8   /* locate / sample call before the table it needs was attached              */
+  RS_STATUS_NO_TABLE = 8,  /* locate / sample call before the table it needs was attached              */
+  RS_STATUS_CAPACITY = 9   /* an output buffer is too small; the sizes needed have been written          */
 } rs_status;
 
 typedef struct rs_index_info {
@@ -142,6 +143,37 @@ int rs_extract_postfix_batch(const rs_index* ix, const uint64_t* rows, size_t n,
                              uint64_t* read_index, uint32_t* steps, char* bases);
 int rs_extract_postfix_batch_dev(const rs_index* ix, const void* d_rows, size_t n, uint32_t max_steps,
                                  void* d_read_index, void* d_steps, void* d_bases, void* stream);
+
+/* ---- count + locate: the per-row loop of query() (src/bwt/query.cpp:87-100) without the strings ---- */
+/* For Q k-mers: findInterval, then for every row of each interval (at most max_hits rows per k-mer)
+ * extractPrefix's walk to the '$' and the .sai lookup.
+ *   hit_offsets[Q+1]   CSR offsets of each k-mer's hits (always written)
+ *   capacity           entries available in rows / lexrank / read_index / steps; if the hits do not
+ *                      fit, only hit_offsets is written and RS_STATUS_CAPACITY is returned
+ *   rows, lexrank, read_index, steps   per hit, any of them may be NULL (read_index needs the .sai) */
+int rs_locate_batch(const rs_index* ix, const char* kmers, int k, size_t Q, uint64_t max_hits, uint32_t max_steps,
+                    uint64_t* hit_offsets, uint64_t capacity, uint64_t* rows, uint64_t* lexrank,
+                    uint64_t* read_index, uint32_t* steps);
+/* Same with device buffers; *total_hits (host) receives hit_offsets[Q]. Synchronises `stream` once. */
+int rs_locate_batch_dev(const rs_index* ix, const void* d_kmers, int k, size_t Q, uint64_t max_hits,
+                        uint32_t max_steps, void* d_hit_offsets, uint64_t capacity, void* d_rows, void* d_lexrank,
+                        void* d_read_index, void* d_steps, uint64_t* total_hits, void* stream);
+
+/* ---- sample sets --------------------------------------------------------------------------------- */
+/* Attach the read-index -> sample-codes table that stands in for the 64 RocksDB stores on this path
+ * (key = read string, value = concatenated codes: src/service/service.cpp:816-845; the table is the
+ * same values addressed by read index instead of read string).  Read r owns codes
+ * [offsets[r], offsets[r+1]) of size_of_sample bytes each; offsets has num_strings+1 entries. */
+int rs_index_set_samples(rs_index* ix, const uint64_t* offsets, const uint8_t* codes, uint64_t num_strings,
+                         int size_of_sample);
+/* Sample codes of n reads, order and duplicates preserved (service.cpp:829-843):
+ * out_offsets[n+1] in codes (always written); out_codes holds `capacity` codes, else RS_STATUS_CAPACITY. */
+int rs_samples_batch(const rs_index* ix, const uint64_t* read_index, size_t n, uint64_t* out_offsets,
+                     uint64_t capacity, uint8_t* out_codes);
+/* Carrier sets: for each of Q k-mers whose hits are read_index[hit_offsets[q] .. hit_offsets[q+1]),
+ * the distinct sample codes over those reads in ascending order. */
+int rs_carriers_batch(const rs_index* ix, const uint64_t* hit_offsets, const uint64_t* read_index, size_t Q,
+                      uint64_t* out_offsets, uint64_t capacity, uint8_t* out_codes);
 
 #ifdef __cplusplus
 }

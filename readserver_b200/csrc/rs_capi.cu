@@ -1,22 +1,10 @@
 /* C ABI of the engine (include/readserver_b200.h): index lifecycle, host<->device staging and
  * kernel launches.  No torch types, no CPU compute path. */
-#include "../../include/readserver_b200.h"
-
-#include <cuda_runtime.h>
-#include <stdarg.h>
-#include <stdio.h>
-#include <string.h>
-
-#include <mutex>
-#include <string>
-#include <vector>
-
-#include "rs_build.h"
-#include "rs_kernels.h"
+#include "rs_internal.h"
 
 static thread_local std::string g_err;
 
-static int fail(int code, const char* fmt, ...) {
+int rs_fail(int code, const char* fmt, ...) {
   char buf[512];
   va_list ap;
   va_start(ap, fmt);
@@ -25,55 +13,6 @@ static int fail(int code, const char* fmt, ...) {
   g_err = buf;
   return code;
 }
-
-#define CU(call)                                                                                  \
-  do {                                                                                            \
-    cudaError_t e_ = (call);                                                                      \
-    if (e_ != cudaSuccess) return fail(RS_STATUS_CUDA, "%s: %s", #call, cudaGetErrorString(e_));  \
-  } while (0)
-
-namespace {
-/* grow-on-demand device scratch buffer */
-struct Scratch {
-  void* p = nullptr;
-  size_t cap = 0;
-  cudaError_t need(size_t bytes) {
-    if (bytes <= cap) return cudaSuccess;
-    if (p) cudaFree(p);
-    p = nullptr;
-    cap = 0;
-    size_t want = bytes + bytes / 4 + 256;
-    cudaError_t e = cudaMalloc(&p, want);
-    if (e == cudaSuccess) cap = want;
-    return e;
-  }
-  void release() {
-    if (p) cudaFree(p);
-    p = nullptr;
-    cap = 0;
-  }
-};
-}  // namespace
-
-struct rs_index {
-  int device = 0;
-  rs_index_dev dev;
-  uint64_t num_runs = 0, depth = 0;
-  bool q2_safe = true;
-  uint64_t hbm_bytes = 0;
-  uint64_t init_occ_ref[RS_NSYM] = {0, 0, 0, 0, 0}; /* the reference's getOcc(c, n-1) */
-  void* d_blocks = nullptr;
-  void* d_dir = nullptr;
-  void* d_sel[RS_NSYM] = {nullptr, nullptr, nullptr, nullptr, nullptr};
-  uint64_t* d_sai = nullptr;
-  uint64_t* d_samp_off = nullptr;
-  uint8_t* d_samp_codes = nullptr;
-  int size_of_sample = 0;
-  uint64_t* d_stats = nullptr; /* [0] updateInterval steps, [1] LF-walk steps; null unless profiling is on */
-  cudaStream_t stream = nullptr;
-  mutable std::mutex mu; /* serialises the host-pointer calls (they share the scratch buffers) */
-  mutable Scratch s_in, s_in2, s_out, s_out2, s_out3, s_out4;
-};
 
 const char* rs_last_error(void) { return g_err.c_str(); }
 

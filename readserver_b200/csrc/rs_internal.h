@@ -1,0 +1,69 @@
+/* Internals shared by the C-ABI translation units (not part of the public interface). */
+#ifndef RS_INTERNAL_H
+#define RS_INTERNAL_H
+
+#include <cuda_runtime.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <mutex>
+#include <string>
+#include <vector>
+
+#include "../../include/readserver_b200.h"
+#include "rs_build.h"
+#include "rs_kernels.h"
+
+int rs_fail(int code, const char* fmt, ...); /* records the thread's last error message */
+#define fail rs_fail
+
+#define CU(call)                                                                                  \
+  do {                                                                                            \
+    cudaError_t e_ = (call);                                                                      \
+    if (e_ != cudaSuccess) return fail(RS_STATUS_CUDA, "%s: %s", #call, cudaGetErrorString(e_));  \
+  } while (0)
+
+/* grow-on-demand device scratch buffer */
+struct Scratch {
+  void* p = nullptr;
+  size_t cap = 0;
+  cudaError_t need(size_t bytes) {
+    if (bytes <= cap) return cudaSuccess;
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+    size_t want = bytes + bytes / 4 + 256;
+    cudaError_t e = cudaMalloc(&p, want);
+    if (e == cudaSuccess) cap = want;
+    return e;
+  }
+  void release() {
+    if (p) cudaFree(p);
+    p = nullptr;
+    cap = 0;
+  }
+};
+
+struct rs_index {
+  int device = 0;
+  rs_index_dev dev;
+  uint64_t num_runs = 0, depth = 0;
+  bool q2_safe = true;
+  uint64_t hbm_bytes = 0;
+  uint64_t init_occ_ref[RS_NSYM] = {0, 0, 0, 0, 0}; /* the reference's getOcc(c, n-1) */
+  void* d_blocks = nullptr;
+  void* d_dir = nullptr;
+  void* d_sel[RS_NSYM] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+  uint64_t* d_sai = nullptr;
+  uint64_t* d_samp_off = nullptr;
+  uint8_t* d_samp_codes = nullptr;
+  int size_of_sample = 0;
+  uint32_t num_samples = 0; /* 1 + largest sample number that occurs in the table */
+  uint64_t* d_stats = nullptr; /* [0] updateInterval steps, [1] LF-walk steps; null unless profiling is on */
+  cudaStream_t stream = nullptr;
+  mutable std::mutex mu; /* serialises the host-pointer calls (they share the scratch buffers) */
+  mutable Scratch s_in, s_in2, s_out, s_out2, s_out3, s_out4;
+};
+
+#endif

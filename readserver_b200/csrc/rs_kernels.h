@@ -31,4 +31,22 @@ cudaError_t rs_launch_occ_at(const rs_index_dev& ix, const uint8_t* syms, const 
 cudaError_t rs_launch_extract_postfix(const rs_index_dev& ix, const uint64_t* rows, uint64_t n, uint32_t max_steps,
                                       uint64_t* read_index, uint32_t* steps, uint8_t* bases, cudaStream_t st);
 
+/* rs_pipeline.cu */
+cudaError_t rs_scan_bytes(uint64_t n, size_t* bytes);
+cudaError_t rs_exclusive_scan(const uint64_t* counts, uint64_t* offsets, uint64_t n, void* tmp, size_t tmp_bytes,
+                              cudaStream_t st);
+cudaError_t rs_launch_hit_counts(const uint64_t* lower, const uint64_t* upper, uint64_t Q, uint64_t max_hits,
+                                 uint64_t* counts, cudaStream_t st);
+cudaError_t rs_launch_expand_rows(const uint64_t* lower, const uint64_t* offsets, uint64_t Q, uint64_t capacity,
+                                  uint64_t* rows, uint32_t* owner, cudaStream_t st);
+cudaError_t rs_launch_sample_counts(const uint64_t* samp_off, uint64_t num_strings, const uint64_t* read_index,
+                                    uint64_t n, uint64_t* counts, cudaStream_t st);
+cudaError_t rs_launch_sample_gather(const uint64_t* samp_off, const uint8_t* samp_codes, uint32_t sos,
+                                    uint64_t num_strings, const uint64_t* read_index, uint64_t n,
+                                    const uint64_t* out_off, uint8_t* out_codes, cudaStream_t st);
+cudaError_t rs_launch_carriers(const uint64_t* samp_off, const uint8_t* samp_codes, uint32_t sos, uint64_t num_strings,
+                               uint32_t num_samples, const uint64_t* hit_off, const uint64_t* read_index, uint64_t Q,
+                               int emit, uint64_t* counts, const uint64_t* out_off, uint8_t* out_codes,
+                               cudaStream_t st);
+
 #endif

@@ -21,7 +21,7 @@ _u8p = np.ctypeslib.ndpointer(dtype=np.uint8, flags="C_CONTIGUOUS")
 _u32p = np.ctypeslib.ndpointer(dtype=np.uint32, flags="C_CONTIGUOUS")
 _u64p = np.ctypeslib.ndpointer(dtype=np.uint64, flags="C_CONTIGUOUS")
 
-STATUS = {0: "OK", 1: "OPEN", 2: "MAGIC", 3: "SHORT", 4: "RUNBYTE", 5: "ARG", 6: "CUDA", 7: "TOO_LARGE", 8: "NO_TABLE"}
+STATUS = {0: "OK", 1: "OPEN", 2: "MAGIC", 3: "SHORT", 4: "RUNBYTE", 5: "ARG", 6: "CUDA", 7: "TOO_LARGE", 8: "NO_TABLE", 9: "CAPACITY"}
 
 
 class RsError(RuntimeError):
@@ -71,6 +71,11 @@ def lib() -> C.CDLL:
         "rs_get_occ_at_batch": (i32, [vp, vp, vp, sz, vp]),
         "rs_extract_postfix_batch": (i32, [vp, vp, sz, C.c_uint32, vp, vp, vp]),
         "rs_extract_postfix_batch_dev": (i32, [vp, vp, sz, C.c_uint32, vp, vp, vp, vp]),
+        "rs_locate_batch": (i32, [vp, vp, i32, sz, u64, C.c_uint32, vp, u64, vp, vp, vp, vp]),
+        "rs_locate_batch_dev": (i32, [vp, vp, i32, sz, u64, C.c_uint32, vp, u64, vp, vp, vp, vp, C.POINTER(u64), vp]),
+        "rs_index_set_samples": (i32, [vp, vp, vp, u64, i32]),
+        "rs_samples_batch": (i32, [vp, vp, sz, vp, u64, vp]),
+        "rs_carriers_batch": (i32, [vp, vp, vp, sz, vp, u64, vp]),
         "rs_find_interval_batch": (i32, [vp, vp, i32, sz, vp, vp]),
         "rs_find_interval_var_batch": (i32, [vp, vp, vp, sz, vp, vp]),
         "rs_find_interval_batch_dev": (i32, [vp, vp, i32, sz, vp, vp, vp]),
@@ -288,12 +293,86 @@ class GpuBWT:
                 out.append(bytes(pb[i, :ps[i]]).decode() + bytes(qb[i, :qs[i]]).decode())
         return out
 
+    # -- count + locate, sample sets -------------------------------------------------------------
+    def locate(self, kmers, k: int | None = None, max_hits: int = 100_000, max_steps: int = 1024,
+               want_read_index: bool = True):
+        """Per k-mer: the rows of its interval (<= max_hits), each walked to its read (query(), query.cpp:87-100,
+        without rebuilding strings).  Returns dict(hit_offsets, rows, lexrank, steps[, read_index])."""
+        kmers = _ascii(kmers)
+        if k is None:
+            k = kmers.shape[-1]
+        flat = kmers.reshape(-1)
+        q = flat.size // k
+        off = np.empty(q + 1, dtype=np.uint64)
+        L = lib()
+        rc = L.rs_locate_batch(self._h, flat.ctypes.data, k, q, max_hits, max_steps, off.ctypes.data, 0, None, None, None, None)
+        if rc not in (0, 9):
+            _check(rc)
+        h = int(off[q])
+        rows = np.empty(h, dtype=np.uint64)
+        lex = np.empty(h, dtype=np.uint64)
+        st = np.empty(h, dtype=np.uint32)
+        ri = np.empty(h, dtype=np.uint64) if want_read_index else None
+        if h:
+            _check(L.rs_locate_batch(self._h, flat.ctypes.data, k, q, max_hits, max_steps, off.ctypes.data, h,
+                                     rows.ctypes.data, lex.ctypes.data, _ptr(ri), st.ctypes.data))
+        out = dict(hit_offsets=off, rows=rows, lexrank=lex, steps=st)
+        if want_read_index:
+            out["read_index"] = ri
+        return out
+
+    def set_samples(self, offsets, codes, size_of_sample: int):
+        offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
+        codes = np.ascontiguousarray(codes, dtype=np.uint8).reshape(-1)
+        _check(lib().rs_index_set_samples(self._h, offsets.ctypes.data, codes.ctypes.data if codes.size else None,
+                                          offsets.size - 1, size_of_sample))
+        self._sos = size_of_sample
+
+    def samples(self, read_index):
+        """(offsets [n+1], codes [total, size_of_sample]) for n reads, order and duplicates preserved."""
+        ri = np.ascontiguousarray(read_index, dtype=np.uint64)
+        off = np.empty(ri.size + 1, dtype=np.uint64)
+        L = lib()
+        rc = L.rs_samples_batch(self._h, ri.ctypes.data, ri.size, off.ctypes.data, 0, None)
+        if rc not in (0, 9):
+            _check(rc)
+        tot = int(off[ri.size])
+        codes = np.empty((tot, self._sos), dtype=np.uint8)
+        if tot:
+            _check(L.rs_samples_batch(self._h, ri.ctypes.data, ri.size, off.ctypes.data, tot, codes.ctypes.data))
+        return off, codes
+
+    def carriers(self, hit_offsets, read_index):
+        """Per k-mer the sorted distinct sample codes over its hit reads: (offsets [Q+1], codes [total, sos])."""
+        ho = np.ascontiguousarray(hit_offsets, dtype=np.uint64)
+        ri = np.ascontiguousarray(read_index, dtype=np.uint64)
+        q = ho.size - 1
+        off = np.empty(q + 1, dtype=np.uint64)
+        L = lib()
+        rc = L.rs_carriers_batch(self._h, ho.ctypes.data, ri.ctypes.data if ri.size else None, q, off.ctypes.data, 0, None)
+        if rc not in (0, 9):
+            _check(rc)
+        tot = int(off[q])
+        codes = np.empty((tot, self._sos), dtype=np.uint8)
+        if tot:
+            _check(L.rs_carriers_batch(self._h, ho.ctypes.data, ri.ctypes.data, q, off.ctypes.data, tot, codes.ctypes.data))
+        return off, codes
+
     # -- device-pointer forms (torch tensors on self.device; asynchronous on `stream`) -------------
     def find_interval_dev(self, d_kmers, k: int, q: int, d_lower, d_upper, stream: int = 0):
         _check(lib().rs_find_interval_batch_dev(self._h, _ptr(d_kmers), k, q, _ptr(d_lower), _ptr(d_upper), stream))
 
     def count_dev(self, d_kmers, k: int, q: int, strand: int, d_counts, stream: int = 0):
         _check(lib().rs_count_batch_dev(self._h, _ptr(d_kmers), k, q, strand, _ptr(d_counts), stream))
+
+    def locate_dev(self, d_kmers, k: int, q: int, max_hits: int, max_steps: int, d_hit_offsets, capacity: int,
+                   d_rows=None, d_lexrank=None, d_read_index=None, d_steps=None, stream: int = 0) -> int:
+        """count + locate on device buffers; returns the total number of hits (raises RsError(9) if > capacity)."""
+        tot = C.c_uint64()
+        _check(lib().rs_locate_batch_dev(self._h, _ptr(d_kmers), k, q, max_hits, max_steps, _ptr(d_hit_offsets), capacity,
+                                         _ptr(d_rows), _ptr(d_lexrank), _ptr(d_read_index), _ptr(d_steps), C.byref(tot),
+                                         stream))
+        return int(tot.value)
 
     def extract_prefix_dev(self, d_rows, n: int, max_steps: int, d_lexrank=None, d_steps=None, d_read_index=None,
                            d_bases=None, stream: int = 0):

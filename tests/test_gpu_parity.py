@@ -123,6 +123,60 @@ def test_select_and_extract_postfix_match_oracle(name, datasets, engine):
             assert all(r == case.reads[int(i)] for r, i in zip(reads, ri[:300]))
 
 
+def _sample_table(num_reads, nsamples, sos, seed):
+    """Synthetic sample store in the reference's value format (service.cpp:829-843): per read a list of
+    1..4 sample codes in merge order, duplicates allowed (rlosort...cpp:47-53)."""
+    rng = np.random.default_rng(seed)
+    cnt = rng.integers(1, 5, num_reads)
+    off = np.zeros(num_reads + 1, dtype=np.uint64)
+    np.cumsum(cnt, out=off[1:])
+    who = rng.integers(0, nsamples, int(off[-1]))
+    lut = np.array([list(oracle.sample_code(int(i), sos)) for i in range(nsamples)], dtype=np.uint8)
+    return off, lut[who], who
+
+
+@pytest.mark.parametrize("name,sos,nsamples", [("clean", 1, 100), ("small", 2, 1000), ("deep", 1, 222)])
+def test_locate_samples_and_carriers(name, sos, nsamples, datasets, engine):
+    case, P = datasets.case(name), datasets.port(name)
+    off, codes, who = _sample_table(case.num_strings, nsamples, sos, seed=4)
+    with _gpu(engine, case) as B:
+        B.set_sai(case.sai)
+        B.set_samples(off, codes, sos)
+        q = case.queries(3000, 31, seed=61)
+        res = B.locate(q, 31, max_hits=50, max_steps=128)
+        lo, up = P.find_interval_batch(q, 31, nthreads=4)
+        cnt = np.minimum(np.where(up >= lo, up - lo + 1, 0), 50).astype(np.uint64)
+        want_off = np.concatenate([[0], np.cumsum(cnt)]).astype(np.uint64)
+        assert np.array_equal(res["hit_offsets"], want_off) and int(want_off[-1]) > 0
+        want_rows = np.concatenate([np.arange(lo[i], lo[i] + cnt[i], dtype=np.uint64) for i in range(len(q))])
+        assert np.array_equal(res["rows"], want_rows)
+        lex, st, ri_post, _ = P.locate_batch(want_rows, nthreads=4, max_steps=128)
+        assert np.array_equal(res["lexrank"], lex) and np.array_equal(res["steps"], st)
+        done = st != 0xFFFFFFFF
+        assert np.array_equal(res["read_index"][done], case.sai[lex[done].astype(np.int64)])
+        if name != "small":   # empty tail region: the .sai read index is the postfix walk's read index
+            assert done.all() and np.array_equal(res["read_index"], ri_post)
+        # sample gather == decode of the reference's value bytes for the same reads (A10)
+        ri = res["read_index"]
+        soff, scodes = B.samples(ri)
+        j = 0
+        for t, r in enumerate(ri[:400]):
+            want = [] if r >= case.num_strings else oracle.decode_sample_value(codes[int(off[r]):int(off[r + 1])].tobytes(), sos, False)
+            got = scodes[int(soff[t]):int(soff[t + 1])]
+            assert [bytes(g) for g in got] == [w[0] for w in want]
+        valid = ri < case.num_strings
+        assert int(soff[-1]) == int((off[ri[valid].astype(np.int64) + 1] - off[ri[valid].astype(np.int64)]).sum())
+        # carrier sets: sorted distinct samples per k-mer
+        coff, ccodes = B.carriers(res["hit_offsets"], ri)
+        ho = res["hit_offsets"].astype(np.int64)
+        for i in range(0, len(q), 7):
+            reads = ri[ho[i]:ho[i + 1]]
+            reads = reads[reads < case.num_strings].astype(np.int64)
+            want = sorted({int(s) for r in reads for s in who[int(off[r]):int(off[r + 1])]})
+            got = [bytes(c) for c in ccodes[int(coff[i]):int(coff[i + 1])]]
+            assert got == [oracle.sample_code(s, sos) for s in want]
+
+
 def test_tail_emulation_switch(datasets, engine):
     import torch
     from readserver_b200 import datagen as dg
