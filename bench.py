@@ -53,6 +53,7 @@ def parse():
     ap.add_argument("--k", type=int, default=31)
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-random-roofline", action="store_true")
     ap.add_argument("--lanes", type=int, default=0, help="lanes per query (1,2,4,8); 0 = library default")
     ap.add_argument("--locate-queries", type=int, default=100_000, help="k-mers of the count+locate side measurement")
     return ap.parse_args()
@@ -314,6 +315,46 @@ def run_ours(args):
     if world == 1:
         assert np.array_equal(dlo.cpu().numpy().view(np.uint64), hlo) and np.array_equal(dup.cpu().numpy().view(np.uint64), hup)
 
+    # ---- side measurement: count + locate (findInterval -> rows -> extractPrefix walk -> .sai) ----
+    locate = None
+    if world == 1 and args.locate_queries > 0:
+        QL = min(Q, args.locate_queries)
+        max_hits, max_steps = 256, args.read_len + 28
+        cap = QL * 128
+        d_off = torch.empty(QL + 1, dtype=torch.int64, device=dev)
+        d_ri = torch.empty(cap, dtype=torch.int64, device=dev)
+        d_st = torch.empty(cap, dtype=torch.int32, device=dev)
+        for _ in range(2):
+            hits = B.locate_dev(dq, k, QL, max_hits, max_steps, d_off, cap, None, None, d_ri, d_st, stream)
+        torch.cuda.synchronize()
+        B.read_stats(reset=True)
+        lms = []
+        for _ in range(max(3, args.steps // 4)):
+            flush.fill_(1)
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            hits = B.locate_dev(dq, k, QL, max_hits, max_steps, d_off, cap, None, None, d_ri, d_st, stream)
+            e1.record()
+            torch.cuda.synchronize()
+            lms.append(e0.elapsed_time(e1))
+        isteps, wsteps = B.read_stats(reset=True)
+        lt = sum(lms) / 1e3
+        locate = {"metric": "31-mer count+locate queries/s (interval, rows <= 256 per k-mer, LF walk to '$', .sai read index)",
+                  "value": QL * len(lms) / lt, "unit": UNIT, "queries_per_step": QL, "hits_per_step": hits,
+                  "hit_rows_per_s": hits * len(lms) / lt, "ms_per_step": 1e3 * lt / len(lms),
+                  "walk_steps_per_step": wsteps / len(lms),
+                  "achieved_GBps": (2.0 * isteps + wsteps) * BYTES_PER_RANK / lt / 1e9,
+                  "kernels_per_step": 5, "note": "includes one stream sync per step to size the hit list"}
+        del d_off, d_ri, d_st
+
+    random_gbs = None
+    if world == 1 and not args.no_random_roofline:
+        try:
+            random_gbs = engine.measure_random_access(local_rank, 8 << 30, 1 << 27)
+        except Exception as ex:  # not fatal for the bench line
+            random_gbs = None
+            print(f"random-access roofline measurement failed: {ex}", file=sys.stderr)
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -343,12 +384,17 @@ def run_ours(args):
             "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
             "algorithmic_bytes": "executed getOcc calls x 128 B (SURVEY.md 8(d)); lower/upper of a step usually share a block",
             "getocc_per_launch": ranks_per_launch,
+            "random_access_peak": random_gbs,
+            "frac_of_random_access_peak": (achieved / random_gbs) if random_gbs else None,
+            "random_access_peak_source": "measured in this run: random 128-B line loads over 8 GiB (rs_measure_random_access)",
         },
         "e2e": {"value": world * Q * args.steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": Q * k,
                 "d2h_bytes_per_step": 2 * Q * 8, "api": "rs_find_interval_batch (host pointers, pinned)"},
         "gpu_launches": args.steps,
         "clocks": clk,
     }
+    if locate:
+        line["locate"] = locate
     if world == 1 and not args.no_cpu_baseline:
         cores = os.cpu_count() or 1
         r = cpu_find_interval(shard, hq, k, cores, target_seconds=args.cpu_seconds, steps=1)

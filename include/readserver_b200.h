@@ -79,6 +79,9 @@ int rs_index_read_stats(rs_index* ix, uint64_t* interval_steps, uint64_t* walk_s
  * (1, 2, 4 or 8; also settable as RS_B200_LANES in the environment).  Results do not depend on it. */
 int rs_config_set_lanes(int lanes);
 int rs_config_get_lanes(void);
+/* Measurement aid, no reference counterpart: achieved GB/s of random, 128-byte-aligned, 128-byte
+ * loads over a buffer_bytes buffer on `device` -- the random-access roofline of this path. */
+int rs_measure_random_access(int device, uint64_t buffer_bytes, uint64_t lines_to_read, double* gbytes_per_s);
 const char* rs_last_error(void);
 /* pinned host memory for the host-pointer calls (optional; any host memory is accepted) */
 int rs_host_alloc(void** p, size_t bytes);

@@ -60,6 +60,7 @@ def lib() -> C.CDLL:
         "rs_index_read_stats": (i32, [vp, C.POINTER(u64), C.POINTER(u64), i32]),
         "rs_config_set_lanes": (i32, [i32]),
         "rs_config_get_lanes": (i32, []),
+        "rs_measure_random_access": (i32, [i32, u64, u64, C.POINTER(C.c_double)]),
         "rs_last_error": (C.c_char_p, []),
         "rs_host_alloc": (i32, [C.POINTER(vp), sz]),
         "rs_host_free": (None, [vp]),
@@ -106,6 +107,13 @@ def set_lanes(lanes: int):
 
 def get_lanes() -> int:
     return int(lib().rs_config_get_lanes())
+
+
+def measure_random_access(device: int = 0, buffer_bytes: int = 16 << 30, lines: int = 1 << 28) -> float:
+    """GB/s of random 128-byte line loads over a buffer much larger than L2 (roofline denominator)."""
+    v = C.c_double()
+    _check(lib().rs_measure_random_access(device, buffer_bytes, lines, C.byref(v)))
+    return float(v.value)
 
 
 def _ptr(a) -> int:
