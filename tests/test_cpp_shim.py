@@ -1,0 +1,69 @@
+"""include/rs_gpu_bwt.hpp -- the C++ mirror of `class BWT` + query.h.  CPU: it compiles against the C ABI
+(and, when /root/reference is there, against the reference's own bwt.h/query.h).  GPU: the program runs
+and its answers equal the oracle's."""
+import os
+import subprocess
+
+import numpy as np
+import pytest
+
+import oracle
+from readserver_b200 import build as rs_build
+from tests import common
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+SRC = os.path.join(ROOT, "tests", "cpp", "shim_test.cpp")
+EXE = os.path.join(ROOT, "tests", "cpp", "shim_test")
+REF_INC = "/root/reference/include/bwt"
+
+
+def _compile(extra=()):
+    lib = rs_build.build()
+    cmd = ["g++", "-std=c++11", "-O1", "-Wall", "-I", os.path.join(ROOT, "include"), *extra, SRC, "-o", EXE,
+           "-L", os.path.dirname(lib), "-lrs_b200", "-Wl,-rpath," + os.path.dirname(lib)]
+    subprocess.run(cmd, check=True)
+    return EXE
+
+
+def test_shim_compiles_and_links():
+    assert os.path.exists(_compile())
+
+
+@pytest.mark.skipif(not os.path.isdir(REF_INC), reason="needs the reference headers")
+def test_shim_compiles_against_reference_headers(tmp_path):
+    """With the reference's bwt.h / query.h included first, GpuBWT derives from THEIR class BWT."""
+    src = tmp_path / "with_ref.cpp"
+    src.write_text('#include "bwt.h"\n#include "query.h"\n#include "rs_gpu_bwt.hpp"\n'
+                   'uint64_t f(const BWT* p) { return p->getBWLen(); }\n'
+                   'uint64_t g(rsb200::GpuBWT* b) { return f(b) + rsb200::findInterval(b, "ACGT").lower; }\n')
+    subprocess.run(["g++", "-std=c++11", "-c", "-I", REF_INC, "-I", os.path.join(ROOT, "include"), str(src), "-o",
+                    str(tmp_path / "with_ref.o")], check=True)
+
+
+@pytest.mark.gpu
+def test_shim_matches_oracle(tmp_path):
+    exe = _compile()
+    bwt = os.path.join(common.GOLDEN, "clean.bwt")
+    z = np.load(os.path.join(common.GOLDEN, "clean.npz"))
+    P = oracle.PortIndex(bwt)
+    qs = [bytes(k).decode() for k in z["kmers"][:40]] + [str(s) for s in z["var_queries"]] + ["ACGTNACGT"]
+    qf = tmp_path / "q.txt"
+    qf.write_text("\n".join(qs) + "\n")
+    out = subprocess.run([exe, bwt, str(qf)], check=True, capture_output=True, text=True).stdout.splitlines()
+    assert out[0] == f"bwlen {P.bwlen} pc " + " ".join(str(P.get_pc(c)) for c in "$ACGT")
+    for i, (w, line) in enumerate(zip(qs, out[1:1 + len(qs)])):
+        f = line.split()
+        lo, up = P.find_interval(w)
+        ok = all(c in "ACGT" for c in w)   # other bytes never reach findInterval in the reference
+        if ok:
+            assert (int(f[1]), int(f[2]), int(f[3]), int(f[4])) == (lo, up, lo, up), w
+        if i < 16 or not ok:
+            want = [P.extract_read(r) for r in range(lo, up + 1)] if ok and up >= lo else []
+            if i < 16:
+                assert int(f[5]) == len(want) and f[7:] == want
+                assert int(f[6]) == int(w in want)
+    tail = out[1 + len(qs)].split()
+    n = P.bwlen
+    assert tail[1] == P.get_f(0) + P.get_f(P.get_pc("C")) + P.get_f(n - 1)
+    assert tail[3] == P.get_char(12345) and int(tail[5]) == P.get_occ_at("G", 777)
+    assert out[2 + len(qs)] == "error 1"
