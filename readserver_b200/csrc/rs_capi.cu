@@ -36,6 +36,12 @@ static void set_tail(rs_index* ix, bool on) {
 static int upload(rs_index* ix, const RsHostIndex& h) {
   CU(cudaSetDevice(ix->device));
   CU(cudaStreamCreateWithFlags(&ix->stream, cudaStreamNonBlocking));
+  CU(cudaStreamCreateWithFlags(&ix->s_h2d, cudaStreamNonBlocking));
+  CU(cudaStreamCreateWithFlags(&ix->s_d2h, cudaStreamNonBlocking));
+  for (int i = 0; i < RS_MAX_CHUNKS; ++i) {
+    CU(cudaEventCreateWithFlags(&ix->ev_in[i], cudaEventDisableTiming));
+    CU(cudaEventCreateWithFlags(&ix->ev_done[i], cudaEventDisableTiming));
+  }
   const size_t bb = h.blocks.size() * sizeof(rs_block), db = h.dir.size() * sizeof(uint64_t);
   CU(cudaMalloc(&ix->d_blocks, bb));
   CU(cudaMalloc(&ix->d_dir, db));
@@ -120,6 +126,12 @@ void rs_index_close(rs_index* ix) {
   ix->s_out3.release();
   ix->s_out4.release();
   if (ix->stream) cudaStreamDestroy(ix->stream);
+  if (ix->s_h2d) cudaStreamDestroy(ix->s_h2d);
+  if (ix->s_d2h) cudaStreamDestroy(ix->s_d2h);
+  for (int i = 0; i < RS_MAX_CHUNKS; ++i) {
+    if (ix->ev_in[i]) cudaEventDestroy(ix->ev_in[i]);
+    if (ix->ev_done[i]) cudaEventDestroy(ix->ev_done[i]);
+  }
   delete ix;
 }
 
@@ -234,6 +246,8 @@ int rs_get_f_batch(const rs_index* ix, const uint64_t* index, size_t n, char* ou
   return char_like(ix, index, n, out, true);
 }
 
+#define RS_CHUNK_MIN 131072 /* queries per pipelined chunk, at least */
+
 static int find_host(const rs_index* ix, const char* text, const uint64_t* offsets, int k, size_t Q, uint64_t* lower,
                      uint64_t* upper, int mode, int strand) {
   if (!ix || (Q && (!text || !lower || (mode == 0 && !upper)))) return fail(RS_STATUS_ARG, "null argument");
@@ -247,12 +261,35 @@ static int find_host(const rs_index* ix, const char* text, const uint64_t* offse
   CU(ix->s_out.need(Q * 8));
   if (mode == 0) CU(ix->s_out2.need(Q * 8));
   cudaStream_t st = ix->stream;
-  CU(cudaMemcpyAsync(ix->s_in.p, text, tbytes, cudaMemcpyHostToDevice, st));
+  uint8_t* d_text = (uint8_t*)ix->s_in.p;
+  uint64_t *d_lo = (uint64_t*)ix->s_out.p, *d_up = (uint64_t*)ix->s_out2.p;
+  if (!offsets && Q >= 2 * RS_CHUNK_MIN) {
+    /* Large fixed-k batch: split into chunks and run copy-in, search and copy-out of successive chunks
+     * on three streams, so the PCIe transfers hide behind the kernels (and vice versa). */
+    size_t nch = Q / RS_CHUNK_MIN;
+    if (nch > RS_MAX_CHUNKS) nch = RS_MAX_CHUNKS;
+    const size_t per = (Q + nch - 1) / nch;
+    for (size_t c = 0; c < nch; ++c) {
+      const size_t q0 = c * per, qn = (q0 + per <= Q ? per : Q - q0);
+      CU(cudaMemcpyAsync(d_text + q0 * k, text + q0 * k, qn * (size_t)k, cudaMemcpyHostToDevice, ix->s_h2d));
+      CU(cudaEventRecord(ix->ev_in[c], ix->s_h2d));
+      CU(cudaStreamWaitEvent(st, ix->ev_in[c], 0));
+      CU(rs_launch_find_interval(ix->dev, d_text + q0 * k, nullptr, (uint32_t)k, qn, d_lo + q0, d_up + q0, mode, strand,
+                                 nullptr, st));
+      CU(cudaEventRecord(ix->ev_done[c], st));
+      CU(cudaStreamWaitEvent(ix->s_d2h, ix->ev_done[c], 0));
+      CU(cudaMemcpyAsync(lower + q0, d_lo + q0, qn * 8, cudaMemcpyDeviceToHost, ix->s_d2h));
+      if (mode == 0) CU(cudaMemcpyAsync(upper + q0, d_up + q0, qn * 8, cudaMemcpyDeviceToHost, ix->s_d2h));
+    }
+    CU(cudaStreamSynchronize(ix->s_d2h));
+    return RS_STATUS_OK;
+  }
+  CU(cudaMemcpyAsync(d_text, text, tbytes, cudaMemcpyHostToDevice, st));
   if (offsets) CU(cudaMemcpyAsync(ix->s_in2.p, offsets, (Q + 1) * 8, cudaMemcpyHostToDevice, st));
-  CU(rs_launch_find_interval(ix->dev, (const uint8_t*)ix->s_in.p, offsets ? (const uint64_t*)ix->s_in2.p : nullptr,
-                             (uint32_t)k, Q, (uint64_t*)ix->s_out.p, (uint64_t*)ix->s_out2.p, mode, strand, nullptr, st));
-  CU(cudaMemcpyAsync(lower, ix->s_out.p, Q * 8, cudaMemcpyDeviceToHost, st));
-  if (mode == 0) CU(cudaMemcpyAsync(upper, ix->s_out2.p, Q * 8, cudaMemcpyDeviceToHost, st));
+  CU(rs_launch_find_interval(ix->dev, d_text, offsets ? (const uint64_t*)ix->s_in2.p : nullptr, (uint32_t)k, Q, d_lo,
+                             d_up, mode, strand, nullptr, st));
+  CU(cudaMemcpyAsync(lower, d_lo, Q * 8, cudaMemcpyDeviceToHost, st));
+  if (mode == 0) CU(cudaMemcpyAsync(upper, d_up, Q * 8, cudaMemcpyDeviceToHost, st));
   CU(cudaStreamSynchronize(st));
   return RS_STATUS_OK;
 }
