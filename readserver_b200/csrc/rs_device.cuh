@@ -263,6 +263,27 @@ __device__ __forceinline__ void rs_grp_occ2(const rs_index_dev& ix, const rs_grp
   *r2 = none2 ? 0 : x2;
 }
 
+/* One block scan for up to two targets: rank of c at position pos and, when rel2 >= 0, at pos + rel2
+ * (which the caller knows to lie in the same block).  Building block of K1's one-scan-per-trip loop. */
+template <int LANES>
+__device__ __forceinline__ void rs_grp_scan2(const rs_index_dev& ix, const rs_grp<LANES>& G, uint32_t c, uint64_t pos,
+                                             uint64_t b, bool verify, int32_t rel2, uint64_t* x1, uint64_t* x2) {
+  rs_hit<LANES> H;
+  rs_blk_load(ix, b, G, &H.B);
+  rs_grp_settle(ix, G, pos, b, verify, &H);
+  const int32_t t1 = (int32_t)H.off - (int32_t)H.lane_base;
+  const int32_t t2 = rel2 < 0 ? -1 : t1 + rel2;
+  uint32_t a1, a2;
+  rs_words_rank<rs_grp<LANES>::NW, true>(H.B.w, c, t1, t2, &a1, &a2);
+  const uint64_t before = rs_blk_count_before(G, H.B, c, H.start);
+  if (LANES > 1) {
+    a1 = rs_grp_sum(G, a1);
+    a2 = rs_grp_sum(G, a2);
+  }
+  *x1 = before + a1;
+  *x2 = before + a2;
+}
+
 /* One LF step of extractPrefix (src/bwt/query.cpp:49-51): b = getChar(idx); idx' = PC(b) + getOcc(b, idx-1).
  * Returns the symbol code (0 = '$') and writes idx'.  Bit-exact with the reference including its tail. */
 template <int LANES>

@@ -80,6 +80,10 @@ __global__ void __launch_bounds__(RS_THREADS)
   bool active = false;
   const bool rc = (mode == 1 && strand == 1);
   unsigned long long nsteps = 0; /* updateInterval calls executed by this group (2 ranks each) */
+  /* a step whose second position lives in another block is finished on the next trip */
+  bool pending = false, none1 = false, none2 = false, m2 = false;
+  uint32_t c = 0;
+  uint64_t r1 = 0, r2 = 0, b2 = 0, pend_pos = 0;
 
   while (true) {
     if (!active && next_q < Q) {
@@ -126,22 +130,61 @@ __global__ void __launch_bounds__(RS_THREADS)
       continue;
     }
     if (active) {
-      /* updateInterval (query.cpp:11-15).  Reverse complement: the searched string is
-       * revcomp(w), whose character at search index j is the complement of w[len-1-j]. */
-      const uint32_t c = rc ? 5u - rs_code(w[len - 1 - j]) : rs_code(w[j]);
-      uint64_t r1, r2;
-      rs_grp_occ2(ix, G, c, lo - 1, hi, &r1, &r2);
-      ++nsteps;
-      const uint64_t pb = ix.pc[c];
-      lo = pb + r1;
-      hi = pb + r2 - 1;
-      --j;
-      if (lo > hi || j < 0) {
-        if (G.g == 0) {
-          if (mode == 1) lower[q] = hi >= lo ? hi - lo + 1 : 0;
-          else { lower[q] = lo; upper[q] = hi; }
+      /* One block scan per trip.  A step (updateInterval, query.cpp:11-15) whose two positions share a
+       * block takes one trip; otherwise the second position is scanned on the next trip, while the other
+       * lanes of the warp go on with their own work: every lane always runs the same code. */
+      uint64_t pos, blk;
+      bool verify;
+      int32_t rel2 = -1;
+      const bool was_pending = pending;
+      if (!pending) {
+        /* reverse complement: revcomp(w)[j] is the complement of w[len-1-j] */
+        c = rc ? 5u - rs_code(w[len - 1 - j]) : rs_code(w[j]);
+        const uint64_t i1 = lo - 1;
+        none1 = (i1 == ~0ull);
+        uint64_t p1 = none1 ? 0 : rs_ref_pos(ix, i1);
+        none2 = (hi == ~0ull); /* getOcc(b, 2^64-1) = 0 in the reference */
+        uint64_t p2 = none2 ? 0 : rs_ref_pos(ix, hi);
+        if (p1 >= ix.n) p1 = ix.n - 1;
+        if (p2 >= ix.n) p2 = ix.n - 1;
+        const uint64_t e1 = __ldg(ix.dir + (p1 >> RS_SLOT_SHIFT));
+        const uint64_t e2 = __ldg(ix.dir + (p2 >> RS_SLOT_SHIFT));
+        bool m1;
+        const uint64_t b1 = rs_dir_block(e1, (uint32_t)p1 & RS_SLOT_MASK, &m1);
+        b2 = rs_dir_block(e2, (uint32_t)p2 & RS_SLOT_MASK, &m2);
+        pend_pos = p2;
+        pending = (b1 != b2) || m1 || m2 || p2 < p1;
+        if (!pending) rel2 = (int32_t)(uint32_t)(p2 - p1);
+        pos = p1;
+        blk = b1;
+        verify = m1;
+        ++nsteps;
+      } else {
+        pos = pend_pos;
+        blk = b2;
+        verify = m2;
+      }
+      uint64_t x1, x2;
+      rs_grp_scan2(ix, G, c, pos, blk, verify, rel2, &x1, &x2);
+      if (was_pending) {
+        r2 = none2 ? 0 : x1;
+        pending = false;
+      } else {
+        r1 = none1 ? 0 : x1;
+        r2 = none2 ? 0 : x2;
+      }
+      if (!pending) {
+        const uint64_t pb = ix.pc[c];
+        lo = pb + r1;
+        hi = pb + r2 - 1;
+        --j;
+        if (lo > hi || j < 0) {
+          if (G.g == 0) {
+            if (mode == 1) lower[q] = hi >= lo ? hi - lo + 1 : 0;
+            else { lower[q] = lo; upper[q] = hi; }
+          }
+          active = false;
         }
-        active = false;
       }
     }
   }
