@@ -57,6 +57,8 @@ typedef struct rs_index_info {
   uint64_t ref_vlast;    /* index of the last m_vSum hint                                     */
   int32_t q2_safe;       /* 0: the reference would read m_vSum out of bounds   */
   int32_t device;        /* CUDA device ordinal                                               */
+  int32_t prefix_table_k; /* length of the k-mer suffix table (0 = none)                      */
+  int32_t reserved_;
 } rs_index_info;
 
 /* ---- lifecycle -------------------------------------------------------------------------------- */
@@ -70,6 +72,10 @@ void rs_index_close(rs_index* ix);
 int rs_index_get_info(const rs_index* ix, rs_index_info* info);
 /* 1 (default): bit-exact with the reference; 0: exact rank/access everywhere. */
 int rs_index_set_tail_emulation(rs_index* ix, int on);
+/* k-mer suffix table, no reference counterpart (results do not depend on it): the intervals of all
+ * 4^k strings of length k, so that findInterval starts k-1 steps in.  Built automatically at open
+ * (k <= 10, at most a quarter of the blocks' size; RS_B200_FTAB=k overrides); k = 0 drops it. */
+int rs_index_set_prefix_table(rs_index* ix, int k);
 /* Work counters for the *_dev calls (kept on the device, off by default): executed updateInterval
  * steps of findInterval (2 getOcc each) and executed LF steps of extractPrefix.  Used by bench.py
  * to turn a kernel time into achieved bytes/s; no reference counterpart. */

@@ -2,6 +2,8 @@
  * kernel launches.  No torch types, no CPU compute path. */
 #include "rs_internal.h"
 
+#include <stdlib.h>
+
 static thread_local std::string g_err;
 
 int rs_fail(int code, const char* fmt, ...) {
@@ -31,6 +33,39 @@ static void set_tail(rs_index* ix, bool on) {
   d.tail_from = on ? (win > d.clamp_c ? win : d.clamp_c) : ~0ull;
   d.tail_from_char = on ? (win > d.clamp_char ? win : d.clamp_char) : ~0ull;
   for (int c = 0; c < RS_NSYM; ++c) d.init_occ[c] = on ? ix->init_occ_ref[c] : d.tot[c];
+}
+
+/* (Re)build the k-mer suffix table with t characters (t < 2: drop it).  Must run after any change of
+ * the tail-emulation switch: the table holds reference-semantics or exact intervals accordingly. */
+static int build_ftab(rs_index* ix, uint32_t t) {
+  if (ix->d_ftab) {
+    CU(cudaStreamSynchronize(ix->stream));
+    cudaFree(ix->d_ftab);
+    ix->hbm_bytes -= (16ull << (2 * ix->dev.ftab_k));
+    ix->d_ftab = nullptr;
+  }
+  ix->dev.ftab = nullptr;
+  ix->dev.ftab_k = 0;
+  if (t < 2) return RS_STATUS_OK;
+  if (t > 12) return fail(RS_STATUS_ARG, "prefix table length must be <= 12");
+  const size_t bytes = 16ull << (2 * t);
+  CU(cudaMalloc((void**)&ix->d_ftab, bytes));
+  CU(rs_build_ftab(ix->dev, t, ix->d_ftab, ix->stream));
+  CU(cudaStreamSynchronize(ix->stream));
+  ix->dev.ftab = ix->d_ftab;
+  ix->dev.ftab_k = t;
+  ix->hbm_bytes += bytes;
+  return RS_STATUS_OK;
+}
+
+static uint32_t auto_ftab_k(const rs_index* ix) {
+  const char* e = getenv("RS_B200_FTAB");
+  if (e) return (uint32_t)atoi(e);
+  /* largest t <= 10 whose table is at most a quarter of the blocks */
+  const uint64_t budget = ix->dev.nblocks * (uint64_t)RS_BLOCK_BYTES / 4;
+  uint32_t t = 0;
+  while (t < 10 && (16ull << (2 * (t + 1))) <= budget) ++t;
+  return t;
 }
 
 static int upload(rs_index* ix, const RsHostIndex& h) {
@@ -74,7 +109,7 @@ static int upload(rs_index* ix, const RsHostIndex& h) {
   ix->num_runs = h.num_runs;
   ix->depth = h.depth;
   ix->q2_safe = h.q2_safe;
-  return RS_STATUS_OK;
+  return build_ftab(ix, auto_ftab_k(ix));
 }
 
 int rs_index_from_runs(const uint8_t* runs, uint64_t num_runs, uint64_t num_strings, uint64_t num_symbols, int device,
@@ -119,6 +154,7 @@ void rs_index_close(rs_index* ix) {
   if (ix->d_samp_off) cudaFree(ix->d_samp_off);
   if (ix->d_samp_codes) cudaFree(ix->d_samp_codes);
   if (ix->d_stats) cudaFree(ix->d_stats);
+  if (ix->d_ftab) cudaFree(ix->d_ftab);
   ix->s_in.release();
   ix->s_in2.release();
   ix->s_out.release();
@@ -152,6 +188,7 @@ int rs_index_get_info(const rs_index* ix, rs_index_info* info) {
   info->ref_vlast = ix->dev.vlast;
   info->q2_safe = ix->q2_safe ? 1 : 0;
   info->device = ix->device;
+  info->prefix_table_k = (int32_t)ix->dev.ftab_k;
   return RS_STATUS_OK;
 }
 
@@ -159,7 +196,15 @@ int rs_index_set_tail_emulation(rs_index* ix, int on) {
   if (!ix) return fail(RS_STATUS_ARG, "null index");
   std::lock_guard<std::mutex> lk(ix->mu);
   set_tail(ix, on != 0); /* initInterval's constant (query.cpp:18-21) follows the same switch */
-  return RS_STATUS_OK;
+  CU(cudaSetDevice(ix->device));
+  return build_ftab(ix, ix->dev.ftab_k); /* the table holds intervals of the semantics it was built with */
+}
+
+int rs_index_set_prefix_table(rs_index* ix, int k) {
+  if (!ix || k < 0) return fail(RS_STATUS_ARG, "bad argument");
+  std::lock_guard<std::mutex> lk(ix->mu);
+  CU(cudaSetDevice(ix->device));
+  return build_ftab(ix, (uint32_t)k);
 }
 
 int rs_index_enable_stats(rs_index* ix, int on) {

@@ -62,6 +62,7 @@ struct rs_index {
   uint8_t* d_samp_codes = nullptr;
   int size_of_sample = 0;
   uint32_t num_samples = 0; /* 1 + largest sample number that occurs in the table */
+  uint64_t* d_ftab = nullptr; /* k-mer suffix table (rs_layout.h), 4^ftab_k pairs */
   uint64_t* d_stats = nullptr; /* [0] updateInterval steps, [1] LF-walk steps; null unless profiling is on */
   cudaStream_t stream = nullptr;
   /* copy-in / copy-out streams and per-chunk events of the pipelined host-pointer calls */

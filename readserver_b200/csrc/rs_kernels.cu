@@ -64,7 +64,7 @@ __global__ void k_getf(const __grid_constant__ rs_index_dev ix, const uint64_t* 
  * or the interval went empty: query.cpp:35-37) picks up its next query on the following trip, so
  * lanes never idle behind a longer neighbour.
  *   mode 0: write lower/upper.   mode 1: write counts (count_reads, service.cpp:279-315), strand as given. */
-template <int LANES>
+template <int LANES, bool FTAB>
 __global__ void __launch_bounds__(RS_THREADS)
     k_find_interval(const __grid_constant__ rs_index_dev ix, const uint8_t* __restrict__ text,
                     const uint64_t* __restrict__ offs, uint32_t k, uint64_t Q, uint64_t* __restrict__ lower,
@@ -112,10 +112,27 @@ __global__ void __launch_bounds__(RS_THREADS)
         active = false;
       } else {
         /* initInterval (query.cpp:18-21) on the last character of the searched string */
-        const uint32_t c = rc ? 5u - rs_code(w[0]) : rs_code(w[len - 1]);
-        lo = ix.pc[c];
-        hi = lo + ix.init_occ[c] - 1;
+        const uint32_t c0 = rc ? 5u - rs_code(w[0]) : rs_code(w[len - 1]);
+        lo = ix.pc[c0];
+        hi = lo + ix.init_occ[c0] - 1;
         j = (int32_t)len - 2;
+        if (FTAB && len >= ix.ftab_k) {
+          /* the first ftab_k - 1 steps are a table lookup when the last ftab_k characters are all ACGT */
+          const uint32_t t = ix.ftab_k;
+          uint32_t idx = 0, ok = 1;
+          for (uint32_t a = 0; a < t; ++a) {
+            const uint32_t cc = rc ? 5u - rs_code(w[t - 1 - a]) : rs_code(w[len - t + a]);
+            ok &= (cc - 1u) < 4u;
+            idx = idx * 4u + ((cc - 1u) & 3u);
+          }
+          if (ok) {
+            const ulonglong2 e = __ldg(reinterpret_cast<const ulonglong2*>(ix.ftab) + idx);
+            lo = e.x;
+            hi = e.y;
+            j = (int32_t)len - (int32_t)t - 1;
+            if (lo > hi) j = -1; /* the search had already stopped inside the suffix (query.cpp:35-37) */
+          }
+        }
         if (j < 0) {
           if (G.g == 0) {
             if (mode == 1) lower[q] = hi >= lo ? hi - lo + 1 : 0;
@@ -400,12 +417,70 @@ cudaError_t rs_launch_getf(const rs_index_dev& ix, const uint64_t* idx, uint64_t
   return cudaGetLastError();
 }
 
+template <int LANES>
+static void launch_fi(const rs_index_dev& ix, const uint8_t* text, const uint64_t* offs, uint32_t k, uint64_t Q,
+                      uint64_t* lower, uint64_t* upper, int mode, int strand, unsigned long long* stats,
+                      cudaStream_t st) {
+  if (ix.ftab && ix.ftab_k > 1)
+    k_find_interval<LANES, true><<<rs_grid_for((const void*)k_find_interval<LANES, true>, LANES, Q), RS_THREADS, 0, st>>>(
+        ix, text, offs, k, Q, lower, upper, mode, strand, stats);
+  else
+    k_find_interval<LANES, false><<<rs_grid_for((const void*)k_find_interval<LANES, false>, LANES, Q), RS_THREADS, 0, st>>>(
+        ix, text, offs, k, Q, lower, upper, mode, strand, stats);
+}
+
 cudaError_t rs_launch_find_interval(const rs_index_dev& ix, const uint8_t* text, const uint64_t* offs, uint32_t k,
                                     uint64_t Q, uint64_t* lower, uint64_t* upper, int mode, int strand,
                                     unsigned long long* stats, cudaStream_t st) {
   if (!Q) return cudaSuccess;
-  RS_DISPATCH(k_find_interval, Q, st, ix, text, offs, k, Q, lower, upper, mode, strand, stats);
+  switch (rs_get_lanes()) {
+    case 1: launch_fi<1>(ix, text, offs, k, Q, lower, upper, mode, strand, stats, st); break;
+    case 2: launch_fi<2>(ix, text, offs, k, Q, lower, upper, mode, strand, stats, st); break;
+    case 4: launch_fi<4>(ix, text, offs, k, Q, lower, upper, mode, strand, stats, st); break;
+    default: launch_fi<8>(ix, text, offs, k, Q, lower, upper, mode, strand, stats, st); break;
+  }
   return cudaGetLastError();
+}
+
+/* all 4^t strings of length t over ACGT, string number i at out + i*t (first character most significant) */
+__global__ void k_all_kmers(uint32_t t, uint64_t n, uint8_t* __restrict__ out) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  uint64_t v = i;
+  for (int a = (int)t - 1; a >= 0; --a) {
+    out[i * t + a] = (uint8_t)rs_ascii(1u + (uint32_t)(v & 3u));
+    v >>= 2;
+  }
+}
+
+__global__ void k_interleave(const uint64_t* __restrict__ lo, const uint64_t* __restrict__ up, uint64_t n,
+                             ulonglong2* __restrict__ out) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = make_ulonglong2(lo[i], up[i]);
+}
+
+/* Fills table[4^t] with findInterval of every t-mer, computed by K1 itself WITHOUT a table (ix.ftab is ignored). */
+cudaError_t rs_build_ftab(const rs_index_dev& ix_in, uint32_t t, uint64_t* table, cudaStream_t st) {
+  rs_index_dev ix = ix_in;
+  ix.ftab = nullptr;
+  ix.ftab_k = 0;
+  const uint64_t n = 1ull << (2 * t);
+  uint8_t* kmers = nullptr;
+  uint64_t *lo = nullptr, *up = nullptr;
+  cudaError_t e;
+  if ((e = cudaMallocAsync((void**)&kmers, n * t, st)) != cudaSuccess) return e;
+  if ((e = cudaMallocAsync((void**)&lo, n * 8, st)) != cudaSuccess) return e;
+  if ((e = cudaMallocAsync((void**)&up, n * 8, st)) != cudaSuccess) return e;
+  k_all_kmers<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(t, n, kmers);
+  e = rs_launch_find_interval(ix, kmers, nullptr, t, n, lo, up, 0, 0, nullptr, st);
+  if (e == cudaSuccess) {
+    k_interleave<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(lo, up, n, reinterpret_cast<ulonglong2*>(table));
+    e = cudaGetLastError();
+  }
+  cudaFreeAsync(kmers, st);
+  cudaFreeAsync(lo, st);
+  cudaFreeAsync(up, st);
+  return e;
 }
 
 cudaError_t rs_launch_extract_prefix(const rs_index_dev& ix, const uint64_t* rows, uint64_t n, uint32_t max_steps,

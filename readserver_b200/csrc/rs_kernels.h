@@ -22,6 +22,7 @@ cudaError_t rs_launch_getf(const rs_index_dev& ix, const uint64_t* idx, uint64_t
 cudaError_t rs_launch_find_interval(const rs_index_dev& ix, const uint8_t* text, const uint64_t* offs, uint32_t k,
                                     uint64_t Q, uint64_t* lower, uint64_t* upper, int mode, int strand,
                                     unsigned long long* stats, cudaStream_t st);
+cudaError_t rs_build_ftab(const rs_index_dev& ix, uint32_t t, uint64_t* table, cudaStream_t st);
 cudaError_t rs_launch_extract_prefix(const rs_index_dev& ix, const uint64_t* rows, uint64_t n, uint32_t max_steps,
                                      uint64_t* lexrank, uint32_t* steps, const uint64_t* sai, uint64_t* read_index,
                                      uint8_t* bases, unsigned long long* stats, cudaStream_t st);

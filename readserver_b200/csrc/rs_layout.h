@@ -69,6 +69,11 @@ typedef struct rs_index_dev {
   uint64_t tail_from;        /* getOcc  */
   uint64_t tail_from_char;   /* getChar */
   uint32_t emulate_tail;     /* 1 = bit-exact with the reference (default), 0 = true rank       */
+  /* k-mer suffix table: the interval findInterval holds after consuming the last ftab_k characters of a
+   * query (including the value at which it stopped early), indexed by those characters as a base-4
+   * number, first character most significant.  {lower, upper} pairs; null / 0 = not built. */
+  const uint64_t* ftab;
+  uint32_t ftab_k;
   uint32_t sel_shift[RS_NSYM]; /* select directory of c: one entry per 2^sel_shift[c] occurrences */
 } rs_index_dev;
 

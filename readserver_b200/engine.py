@@ -34,7 +34,8 @@ class Info(C.Structure):
     _fields_ = [("bwlen", C.c_uint64), ("num_strings", C.c_uint64), ("num_runs", C.c_uint64),
                 ("num_blocks", C.c_uint64), ("hbm_bytes", C.c_uint64), ("pc", C.c_uint64 * 5),
                 ("total", C.c_uint64 * 5), ("ref_depth", C.c_uint64), ("ref_clamp_c", C.c_uint64),
-                ("ref_vlast", C.c_uint64), ("q2_safe", C.c_int32), ("device", C.c_int32)]
+                ("ref_vlast", C.c_uint64), ("q2_safe", C.c_int32), ("device", C.c_int32),
+                ("prefix_table_k", C.c_int32), ("reserved_", C.c_int32)]
 
 
 _LIB = None
@@ -56,6 +57,7 @@ def lib() -> C.CDLL:
         "rs_index_close": (None, [vp]),
         "rs_index_get_info": (i32, [vp, C.POINTER(Info)]),
         "rs_index_set_tail_emulation": (i32, [vp, i32]),
+        "rs_index_set_prefix_table": (i32, [vp, i32]),
         "rs_index_enable_stats": (i32, [vp, i32]),
         "rs_index_read_stats": (i32, [vp, C.POINTER(u64), C.POINTER(u64), i32]),
         "rs_config_set_lanes": (i32, [i32]),
@@ -168,6 +170,11 @@ class GpuBWT:
 
     def set_tail_emulation(self, on: bool):
         _check(lib().rs_index_set_tail_emulation(self._h, int(on)))
+
+    def set_prefix_table(self, k: int):
+        """(Re)build the k-mer suffix table with k characters; 0 drops it. Results do not depend on it."""
+        _check(lib().rs_index_set_prefix_table(self._h, k))
+        _check(lib().rs_index_get_info(self._h, C.byref(self.info)))
 
     def enable_stats(self, on: bool = True):
         _check(lib().rs_index_enable_stats(self._h, int(on)))

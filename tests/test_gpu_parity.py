@@ -177,6 +177,43 @@ def test_locate_samples_and_carriers(name, sos, nsamples, datasets, engine):
             assert got == [oracle.sample_code(s, sos) for s in want]
 
 
+@pytest.mark.parametrize("name", ["small", "clean", "deep"])
+def test_prefix_table_does_not_change_results(name, datasets, engine):
+    """The k-mer suffix table only skips steps: intervals (including early-exit values) and counts on both
+    strands must be the oracle's for every table length, for queries shorter, equal and longer than it."""
+    case, P = datasets.case(name), datasets.port(name)
+    comp = np.zeros(256, dtype=np.uint8)
+    for a, b in zip(b"ACGT", b"TGCA"):
+        comp[a] = b
+    with _gpu(engine, case) as B:
+        auto = B.info.prefix_table_k
+        for t in (0, 2, 5, 8, auto):
+            B.set_prefix_table(t)
+            assert B.info.prefix_table_k == t
+            for k in (1, 4, 5, 6, 8, 9, 31):
+                q = case.queries(4000, k, seed=300 + k)
+                q[5, k // 2] = ord("N")     # non-ACGT inside / at the end of the suffix: table must not be used
+                q[6, k - 1] = ord("$")
+                lo, up = B.find_interval(q, k)
+                lo2, up2 = P.find_interval_batch(q, k, nthreads=4)
+                ok = np.ones(len(q), dtype=bool)
+                ok[5] = False               # 'N' is outside the contract of findInterval (SURVEY.md Q4)
+                assert np.array_equal(lo[ok], lo2[ok]) and np.array_equal(up[ok], up2[ok]), (t, k)
+                rcq = np.ascontiguousarray(comp[q[:, ::-1]])
+                lo3, up3 = P.find_interval_batch(rcq, k, nthreads=4)
+                okc = ok.copy()
+                okc[6] = False
+                want = np.where(up3 >= lo3, up3 - lo3 + 1, 0)
+                got = B.count(q, k, strand=1)
+                assert np.array_equal(got[okc], want[okc]) and got[5] == 0 and got[6] == 0, (t, k)
+        B.set_tail_emulation(False)         # the table is rebuilt with the other semantics
+        q = case.queries(2000, 31, seed=17)
+        lo, up = B.find_interval(q, 31)
+        B.set_prefix_table(0)
+        lo2, up2 = B.find_interval(q, 31)
+        assert np.array_equal(lo, lo2) and np.array_equal(up, up2)
+
+
 def test_tail_emulation_switch(datasets, engine):
     import torch
     from readserver_b200 import datagen as dg
