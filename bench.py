@@ -247,6 +247,8 @@ def run_ours(args):
     B.enable_stats(True)
     Q, k = args.queries, args.k
     dq = shard["queries"]
+    torch.cuda.synchronize()
+    torch.cuda.cudart().cudaProfilerStart()  # `ncu --profile-from-start off` skips the synthetic-data build
     dlo = torch.empty(Q, dtype=torch.int64, device=dev)
     dup = torch.empty(Q, dtype=torch.int64, device=dev)
     dcnt = torch.empty(Q, dtype=torch.int64, device=dev)
