@@ -54,7 +54,6 @@ def parse():
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-random-roofline", action="store_true")
-    ap.add_argument("--lanes", type=int, default=0, help="lanes per query (1,2,4,8); 0 = library default")
     ap.add_argument("--locate-queries", type=int, default=100_000, help="k-mers of the count+locate side measurement")
     return ap.parse_args()
 
@@ -237,8 +236,6 @@ def run_ours(args):
     torch.cuda.set_device(local_rank)
     dev = f"cuda:{local_rank}"
     from readserver_b200 import engine
-    if args.lanes:
-        engine.set_lanes(args.lanes)
 
     shard = build_shard(args, dev, rank)
     B = engine.GpuBWT(runs=shard["runs"], num_strings=shard["num_strings"], num_symbols=shard["num_symbols"],
@@ -373,7 +370,7 @@ def run_ours(args):
         "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
         "config": {
             "workload": workload_name(args), "k": k, "queries_per_step": Q, "shards_per_gpu": 1,
-            "lanes_per_query": engine.get_lanes(),
+            "threads_per_query": 1, "block_layout": "128 B = 32 B header + 3 x (8 B record + 24 runs); 2 sectors per rank",
             "bwt_symbols": shard["num_symbols"], "bwt_runs": int(shard["runs"].size), "reads_unique": shard["num_strings"],
             "index_hbm_bytes": int(B.info.hbm_bytes), "index_fits_l2": bool(B.info.hbm_bytes < 126e6),
             "l2": "256 MiB buffer written between timed steps (untimed) -> index and queries start cold",

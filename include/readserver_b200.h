@@ -81,10 +81,6 @@ int rs_index_set_prefix_table(rs_index* ix, int k);
  * to turn a kernel time into achieved bytes/s; no reference counterpart. */
 int rs_index_enable_stats(rs_index* ix, int on);
 int rs_index_read_stats(rs_index* ix, uint64_t* interval_steps, uint64_t* walk_steps, int reset);
-/* Tuning knob, no reference counterpart: lanes of a warp that cooperate on one query / walker
- * (1, 2, 4 or 8; also settable as RS_B200_LANES in the environment).  Results do not depend on it. */
-int rs_config_set_lanes(int lanes);
-int rs_config_get_lanes(void);
 /* Measurement aid, no reference counterpart: achieved GB/s of random, 128-byte-aligned, 128-byte
  * loads over a buffer_bytes buffer on `device` -- the random-access roofline of this path. */
 int rs_measure_random_access(int device, uint64_t buffer_bytes, uint64_t lines_to_read, double* gbytes_per_s);

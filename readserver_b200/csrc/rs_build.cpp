@@ -69,6 +69,19 @@ int rs_build_host_index(const uint8_t* runs, uint64_t R, uint64_t num_strings, u
   uint64_t bi = 0;
   uint32_t fill = RS_PAYLOAD; /* forces a new block at run 0 */
   rs_block* cur = nullptr;
+  uint64_t in_blk[RS_NSYM] = {0, 0, 0, 0, 0}, in_tot = 0; /* counts inside the current block */
+  auto rec_now = [&]() -> uint64_t {
+    return in_blk[1] | (in_blk[2] << RS_REC_BITS) | (in_blk[3] << (2 * RS_REC_BITS)) | (in_blk[4] << (3 * RS_REC_BITS)) |
+           (in_tot << RS_REC_SYM_SHIFT);
+  };
+  /* sub-blocks a short last block leaves empty repeat the block's totals (rs_ops.h relies on it) */
+  auto close_block = [&]() {
+    if (!cur) return;
+    const uint32_t used = (fill + RS_SUB_RUNS - 1) / RS_SUB_RUNS;
+    for (uint32_t j = used; j < RS_SUBS; ++j) cur->sub[j].rec = rec_now();
+    if (used < 2) cur->bounds = (uint32_t)in_tot | ((uint32_t)in_tot << RS_REC_BITS);
+    else if (used < 3) cur->bounds |= (uint32_t)in_tot << RS_REC_BITS;
+  };
   for (uint64_t i = 0; i < R; ++i) {
     const uint32_t sym = runs[i] >> 5, len = runs[i] & 31u;
     if (sym > 4 || len == 0) return RS_ERR_RUNBYTE;
@@ -84,16 +97,34 @@ int rs_build_host_index(const uint8_t* runs, uint64_t R, uint64_t num_strings, u
       snaps.push_back(s);
     }
     if (fill == RS_PAYLOAD) {
+      close_block();
       cur = &out.blocks[bi++];
+      memset(cur, 0, sizeof(*cur));
       cur->start = tot;
-      for (int c = 0; c < 4; ++c) cur->cnt[c] = cnt[c + 1];
-      memset(cur->runs, 0, RS_PAYLOAD);
+      for (int c = 0; c < 4; ++c) {
+        if (cnt[c + 1] >> 40) return RS_ERR_TOO_LARGE;
+        cur->cnt_lo[c] = (uint32_t)cnt[c + 1];
+        cur->cnt_hi |= (uint32_t)(cnt[c + 1] >> 32) << (8 * c);
+      }
       fill = 0;
+      in_tot = 0;
+      for (int c = 0; c < RS_NSYM; ++c) in_blk[c] = 0;
     }
-    cur->runs[fill++] = runs[i];
+    if (fill % RS_SUB_RUNS == 0) {
+      const uint32_t j = fill / RS_SUB_RUNS;
+      cur->sub[j].rec = rec_now();
+      if (j == 1) cur->bounds = (uint32_t)in_tot;
+      if (j == 2) cur->bounds |= (uint32_t)in_tot << RS_REC_BITS;
+    }
+    if (fill >= RS_PAYLOAD) return RS_ERR_ARG; /* unreachable */
+    cur->sub[fill / RS_SUB_RUNS].runs[fill % RS_SUB_RUNS] = runs[i];
+    ++fill;
+    in_blk[sym] += len;
+    in_tot += len;
     cnt[sym] += len;
     tot += len;
   }
+  close_block();
   if (tot != num_symbols) return RS_ERR_ARG;
   out.n = tot;
   memcpy(out.tot, cnt, sizeof(cnt));
@@ -176,8 +207,11 @@ int rs_build_host_index(const uint8_t* runs, uint64_t R, uint64_t num_strings, u
       uint64_t after[RS_NSYM];
       if (b + 1 < nblocks) {
         const rs_block& N = out.blocks[b + 1];
-        after[0] = N.start - (N.cnt[0] + N.cnt[1] + N.cnt[2] + N.cnt[3]);
-        for (int c = 1; c < RS_NSYM; ++c) after[c] = N.cnt[c - 1];
+        after[0] = N.start;
+        for (int c = 1; c < RS_NSYM; ++c) {
+          after[c] = (uint64_t)N.cnt_lo[c - 1] | ((uint64_t)((N.cnt_hi >> (8 * (c - 1))) & 0xFFu) << 32);
+          after[0] -= after[c];
+        }
       } else {
         memcpy(after, cnt, sizeof(after));
       }
@@ -190,4 +224,30 @@ int rs_build_host_index(const uint8_t* runs, uint64_t R, uint64_t num_strings, u
     }
   }
   return RS_OK;
+}
+
+void rs_view_set_tail(const uint64_t init_occ_ref[RS_NSYM], bool on, rs_index_dev* d) {
+  d->emulate_tail = on ? 1u : 0u;
+  const uint64_t win = d->vlast ? (d->vlast << 16) - 1 : 0; /* (i + 1) >> 16 >= vlast  <=>  i >= win (i != 2^64-1) */
+  d->tail_from = on ? (win > d->clamp_c ? win : d->clamp_c) : ~0ull;
+  d->tail_from_char = on ? (win > d->clamp_char ? win : d->clamp_char) : ~0ull;
+  for (int c = 0; c < RS_NSYM; ++c) d->init_occ[c] = on ? init_occ_ref[c] : d->tot[c];
+}
+
+void rs_view_set_tail(const RsHostIndex& h, bool on, rs_index_dev* d) { rs_view_set_tail(h.init_occ, on, d); }
+
+void rs_fill_view(const RsHostIndex& h, rs_index_dev* d) {
+  memset(d, 0, sizeof(*d));
+  for (int c = 0; c < RS_NSYM; ++c) {
+    d->sel_shift[c] = h.sel_shift[c];
+    d->pc[c] = h.pc[c];
+    d->tot[c] = h.tot[c];
+  }
+  d->n = h.n;
+  d->nblocks = h.blocks.size();
+  d->num_strings = h.num_strings;
+  d->clamp_c = h.clamp_c;
+  d->clamp_char = h.clamp_char;
+  d->vlast = h.vlast;
+  rs_view_set_tail(h, true, d);
 }

@@ -44,4 +44,11 @@ int rs_read_bwt_file(const char* path, std::vector<uint8_t>& runs, uint64_t& num
 int rs_build_host_index(const uint8_t* runs, uint64_t nruns, uint64_t num_strings, uint64_t num_symbols,
                         RsHostIndex& out);
 
+/* Scalar fields of the kernel-side view from a host index (the caller sets the pointers), and the
+ * reference-tail switch: folds "last m_vSum window and at/after the clamp" into one threshold per
+ * lookup kind, and picks initInterval's constant (query.cpp:18-21). */
+void rs_fill_view(const RsHostIndex& h, rs_index_dev* d);
+void rs_view_set_tail(const RsHostIndex& h, bool on, rs_index_dev* d);
+void rs_view_set_tail(const uint64_t init_occ_ref[RS_NSYM], bool on, rs_index_dev* d);
+
 #endif

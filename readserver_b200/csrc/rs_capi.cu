@@ -18,22 +18,8 @@ int rs_fail(int code, const char* fmt, ...) {
 
 const char* rs_last_error(void) { return g_err.c_str(); }
 
-int rs_config_set_lanes(int lanes) {
-  if (lanes != 1 && lanes != 2 && lanes != 4 && lanes != 8) return fail(RS_STATUS_ARG, "lanes must be 1, 2, 4 or 8");
-  rs_set_lanes(lanes);
-  return RS_STATUS_OK;
-}
-int rs_config_get_lanes(void) { return rs_get_lanes(); }
 
-/* fold "last m_vSum window and at/after the clamp" into one threshold per lookup kind */
-static void set_tail(rs_index* ix, bool on) {
-  rs_index_dev& d = ix->dev;
-  d.emulate_tail = on ? 1u : 0u;
-  const uint64_t win = d.vlast ? (d.vlast << 16) - 1 : 0; /* (i + 1) >> 16 >= vlast  <=>  i >= win (i != 2^64-1) */
-  d.tail_from = on ? (win > d.clamp_c ? win : d.clamp_c) : ~0ull;
-  d.tail_from_char = on ? (win > d.clamp_char ? win : d.clamp_char) : ~0ull;
-  for (int c = 0; c < RS_NSYM; ++c) d.init_occ[c] = on ? ix->init_occ_ref[c] : d.tot[c];
-}
+static void set_tail(rs_index* ix, bool on) { rs_view_set_tail(ix->init_occ_ref, on, &ix->dev); }
 
 /* (Re)build the k-mer suffix table with t characters (t < 2: drop it).  Must run after any change of
  * the tail-emulation switch: the table holds reference-semantics or exact intervals accordingly. */
@@ -83,29 +69,17 @@ static int upload(rs_index* ix, const RsHostIndex& h) {
   CU(cudaMemcpy(ix->d_blocks, h.blocks.data(), bb, cudaMemcpyHostToDevice));
   CU(cudaMemcpy(ix->d_dir, h.dir.data(), db, cudaMemcpyHostToDevice));
   ix->hbm_bytes = bb + db;
-  memset(&ix->dev, 0, sizeof(ix->dev));
+  rs_fill_view(h, &ix->dev);
   for (int c = 0; c < RS_NSYM; ++c) {
     const size_t sb = h.sel[c].size() * sizeof(uint32_t);
     CU(cudaMalloc(&ix->d_sel[c], sb));
     CU(cudaMemcpy(ix->d_sel[c], h.sel[c].data(), sb, cudaMemcpyHostToDevice));
     ix->dev.sel[c] = (const uint32_t*)ix->d_sel[c];
-    ix->dev.sel_shift[c] = h.sel_shift[c];
     ix->hbm_bytes += sb;
-    ix->dev.pc[c] = h.pc[c];
-    ix->dev.tot[c] = h.tot[c];
-    ix->dev.init_occ[c] = h.init_occ[c];
     ix->init_occ_ref[c] = h.init_occ[c];
   }
   ix->dev.blocks = ix->d_blocks;
   ix->dev.dir = (const uint64_t*)ix->d_dir;
-  ix->dev.n = h.n;
-  ix->dev.nblocks = h.blocks.size();
-  ix->dev.num_strings = h.num_strings;
-  ix->dev.clamp_c = h.clamp_c;
-  ix->dev.clamp_char = h.clamp_char;
-  ix->dev.vlast = h.vlast;
-  ix->dev.emulate_tail = 1;
-  set_tail(ix, true);
   ix->num_runs = h.num_runs;
   ix->depth = h.depth;
   ix->q2_safe = h.q2_safe;

@@ -1,14 +1,16 @@
-/* sm_100a kernels of the FM-index hot path.  LANES lanes per query / walker (rs_device.cuh).
+/* sm_100a kernels of the FM-index hot path.  One thread per query / walker (rs_ops.h); the lanes of
+ * a warp always run the same code on different queries.
  *
  *   k_find_interval   findInterval            src/bwt/query.cpp:24-41   (K1)
  *   k_extract_prefix  extractPrefix           src/bwt/query.cpp:43-63   (K2)
- *   k_occ / k_char    RLEBWT::getOcc/getChar  src/bwt/rlebwt.cpp:202-301
+ *   k_extract_postfix extractPostfix          src/bwt/query.cpp:65-85
+ *   k_occ / k_char / k_occ_at / k_getf        src/bwt/rlebwt.cpp:202-314
  */
 #include "rs_kernels.h"
 
 #include <stdlib.h>
 
-#include "rs_device.cuh"
+#include "rs_ops.h"
 
 #define RS_FULL 0xFFFFFFFFu
 
@@ -22,30 +24,27 @@ __device__ __forceinline__ uint32_t rs_code(uint32_t ch) {
 }
 __device__ __forceinline__ uint32_t rs_ascii(uint32_t code) { return (0x5447434124ull >> (8 * code)) & 0xFFu; }
 
-template <int LANES>
 __global__ void __launch_bounds__(RS_THREADS) k_occ(const __grid_constant__ rs_index_dev ix, const uint8_t* __restrict__ syms,
                                                     const uint64_t* __restrict__ idx, uint64_t n,
                                                     uint64_t* __restrict__ out) {
-  const rs_grp<LANES> G;
-  constexpr int GPB = RS_THREADS / LANES;
-  const uint64_t ngroups = (uint64_t)gridDim.x * GPB;
-  /* a group leaves the loop as a whole, so the group-masked shuffles inside stay well formed */
-  for (uint64_t i = (uint64_t)blockIdx.x * GPB + threadIdx.x / LANES; i < n; i += ngroups) {
-    const uint64_t r = rs_grp_occ(ix, G, rs_code(syms[i]), idx[i]);
-    if (G.g == 0) out[i] = r;
-  }
+  const uint64_t stride = (uint64_t)gridDim.x * RS_THREADS;
+  for (uint64_t i = (uint64_t)blockIdx.x * RS_THREADS + threadIdx.x; i < n; i += stride)
+    out[i] = rs_occ(ix, rs_code(syms[i]), idx[i]);
 }
 
-template <int LANES>
 __global__ void __launch_bounds__(RS_THREADS) k_char(const __grid_constant__ rs_index_dev ix, const uint64_t* __restrict__ idx,
                                                      uint64_t n, uint8_t* __restrict__ out) {
-  const rs_grp<LANES> G;
-  constexpr int GPB = RS_THREADS / LANES;
-  const uint64_t ngroups = (uint64_t)gridDim.x * GPB;
-  for (uint64_t i = (uint64_t)blockIdx.x * GPB + threadIdx.x / LANES; i < n; i += ngroups) {
-    const uint32_t s = rs_grp_char(ix, G, idx[i]);
-    if (G.g == 0) out[i] = (uint8_t)rs_ascii(s);
-  }
+  const uint64_t stride = (uint64_t)gridDim.x * RS_THREADS;
+  for (uint64_t i = (uint64_t)blockIdx.x * RS_THREADS + threadIdx.x; i < n; i += stride)
+    out[i] = (uint8_t)rs_ascii(rs_char(ix, idx[i]));
+}
+
+__global__ void __launch_bounds__(RS_THREADS) k_occ_at(const __grid_constant__ rs_index_dev ix, const uint8_t* __restrict__ syms,
+                                                       const uint64_t* __restrict__ cnt, uint64_t n,
+                                                       uint64_t* __restrict__ out) {
+  const uint64_t stride = (uint64_t)gridDim.x * RS_THREADS;
+  for (uint64_t i = (uint64_t)blockIdx.x * RS_THREADS + threadIdx.x; i < n; i += stride)
+    out[i] = rs_occ_at(ix, rs_code(syms[i]), cnt[i]);
 }
 
 /* getF (rlebwt.cpp:307-314): last symbol whose C[] value is <= index. One thread per item. */
@@ -59,36 +58,34 @@ __global__ void k_getf(const __grid_constant__ rs_index_dev ix, const uint64_t* 
   out[i] = (uint8_t)rs_ascii(ci - 1);
 }
 
-/* K1.  Each group owns one query at a time and all groups of a warp advance one backward-search
- * step per loop trip, whatever query they are on: a group whose query ends (all characters consumed,
- * or the interval went empty: query.cpp:35-37) picks up its next query on the following trip, so
- * lanes never idle behind a longer neighbour.
+/* K1.  Each thread owns one query at a time and all lanes of a warp perform one sub-block scan per
+ * loop trip, whatever query they are on: a thread whose query ends (all characters consumed, or the
+ * interval went empty: query.cpp:35-37) picks up its next query on the following trip, so lanes never
+ * idle behind a longer neighbour.  A step (updateInterval, query.cpp:11-15) whose two positions share
+ * a sub-block takes one trip; otherwise the second position is scanned on the next trip.
  *   mode 0: write lower/upper.   mode 1: write counts (count_reads, service.cpp:279-315), strand as given. */
-template <int LANES, bool FTAB>
+template <bool FTAB>
 __global__ void __launch_bounds__(RS_THREADS)
     k_find_interval(const __grid_constant__ rs_index_dev ix, const uint8_t* __restrict__ text,
                     const uint64_t* __restrict__ offs, uint32_t k, uint64_t Q, uint64_t* __restrict__ lower,
                     uint64_t* __restrict__ upper, int mode, int strand, unsigned long long* __restrict__ stats) {
-  const rs_grp<LANES> G;
-  constexpr int GPB = RS_THREADS / LANES;
-  const uint64_t ngroups = (uint64_t)gridDim.x * GPB;
-  uint64_t next_q = (uint64_t)blockIdx.x * GPB + threadIdx.x / LANES;
+  const uint64_t stride = (uint64_t)gridDim.x * RS_THREADS;
+  uint64_t next_q = (uint64_t)blockIdx.x * RS_THREADS + threadIdx.x;
   uint64_t q = 0, lo = 0, hi = 0;
   const uint8_t* w = text; /* the query's characters */
   int32_t j = -1;          /* index of the next character in search order */
   uint32_t len = 0;
   bool active = false;
   const bool rc = (mode == 1 && strand == 1);
-  unsigned long long nsteps = 0; /* updateInterval calls executed by this group (2 ranks each) */
-  /* a step whose second position lives in another block is finished on the next trip */
-  bool pending = false, none1 = false, none2 = false, m2 = false;
+  unsigned long long nsteps = 0; /* updateInterval calls executed by this thread (2 ranks each) */
+  bool pending = false, none1 = false, none2 = false;
   uint32_t c = 0;
-  uint64_t r1 = 0, r2 = 0, b2 = 0, pend_pos = 0;
+  uint64_t r1 = 0, b2 = 0, pend_pos = 0;
 
   while (true) {
     if (!active && next_q < Q) {
       q = next_q;
-      next_q += ngroups;
+      next_q += stride;
       uint64_t base;
       if (offs) {
         base = offs[q];
@@ -100,15 +97,11 @@ __global__ void __launch_bounds__(RS_THREADS)
       w = text + base;
       active = true;
       bool bad = (len == 0);
-      if (mode == 1) { /* any byte outside ACGT -> count 0 (service.cpp:299-301) */
-        for (uint32_t t = G.g; t < len; t += LANES) bad |= (rs_code(w[t]) == 0);
-        if (LANES > 1) bad = (__ballot_sync(G.mask, bad) & G.mask) != 0;
-      }
+      if (mode == 1) /* any byte outside ACGT -> count 0 (service.cpp:299-301) */
+        for (uint32_t t = 0; t < len; ++t) bad |= (rs_code(w[t]) == 0);
       if (bad) {
-        if (G.g == 0) {
-          if (mode == 1) lower[q] = 0;
-          else { lower[q] = 1; upper[q] = 0; }
-        }
+        if (mode == 1) lower[q] = 0;
+        else { lower[q] = 1; upper[q] = 0; }
         active = false;
       } else {
         /* initInterval (query.cpp:18-21) on the last character of the searched string */
@@ -134,10 +127,8 @@ __global__ void __launch_bounds__(RS_THREADS)
           }
         }
         if (j < 0) {
-          if (G.g == 0) {
-            if (mode == 1) lower[q] = hi >= lo ? hi - lo + 1 : 0;
-            else { lower[q] = lo; upper[q] = hi; }
-          }
+          if (mode == 1) lower[q] = hi >= lo ? hi - lo + 1 : 0;
+          else { lower[q] = lo; upper[q] = hi; }
           active = false;
         }
       }
@@ -147,12 +138,8 @@ __global__ void __launch_bounds__(RS_THREADS)
       continue;
     }
     if (active) {
-      /* One block scan per trip.  A step (updateInterval, query.cpp:11-15) whose two positions share a
-       * block takes one trip; otherwise the second position is scanned on the next trip, while the other
-       * lanes of the warp go on with their own work: every lane always runs the same code. */
-      uint64_t pos, blk;
-      bool verify;
-      int32_t rel2 = -1;
+      uint64_t pos, pos2, blk;
+      bool try2 = false;
       const bool was_pending = pending;
       if (!pending) {
         /* reverse complement: revcomp(w)[j] is the complement of w[len-1-j] */
@@ -164,31 +151,29 @@ __global__ void __launch_bounds__(RS_THREADS)
         uint64_t p2 = none2 ? 0 : rs_ref_pos(ix, hi);
         if (p1 >= ix.n) p1 = ix.n - 1;
         if (p2 >= ix.n) p2 = ix.n - 1;
-        const uint64_t e1 = __ldg(ix.dir + (p1 >> RS_SLOT_SHIFT));
-        const uint64_t e2 = __ldg(ix.dir + (p2 >> RS_SLOT_SHIFT));
-        bool m1;
-        const uint64_t b1 = rs_dir_block(e1, (uint32_t)p1 & RS_SLOT_MASK, &m1);
-        b2 = rs_dir_block(e2, (uint32_t)p2 & RS_SLOT_MASK, &m2);
+        const uint64_t b1 = rs_find_block(ix, p1);
+        b2 = rs_find_block(ix, p2);
         pend_pos = p2;
-        pending = (b1 != b2) || m1 || m2 || p2 < p1;
-        if (!pending) rel2 = (int32_t)(uint32_t)(p2 - p1);
+        try2 = (b1 == b2) && p2 >= p1;
         pos = p1;
+        pos2 = p2;
         blk = b1;
-        verify = m1;
         ++nsteps;
       } else {
-        pos = pend_pos;
+        pos = pos2 = pend_pos;
         blk = b2;
-        verify = m2;
       }
       uint64_t x1, x2;
-      rs_grp_scan2(ix, G, c, pos, blk, verify, rel2, &x1, &x2);
+      bool did2;
+      rs_scan2(ix, c, blk, pos, pos2, try2, &x1, &x2, &did2);
+      uint64_t r2 = 0;
       if (was_pending) {
         r2 = none2 ? 0 : x1;
         pending = false;
       } else {
         r1 = none1 ? 0 : x1;
         r2 = none2 ? 0 : x2;
+        pending = !did2;
       }
       if (!pending) {
         const uint64_t pb = ix.pc[c];
@@ -196,39 +181,34 @@ __global__ void __launch_bounds__(RS_THREADS)
         hi = pb + r2 - 1;
         --j;
         if (lo > hi || j < 0) {
-          if (G.g == 0) {
-            if (mode == 1) lower[q] = hi >= lo ? hi - lo + 1 : 0;
-            else { lower[q] = lo; upper[q] = hi; }
-          }
+          if (mode == 1) lower[q] = hi >= lo ? hi - lo + 1 : 0;
+          else { lower[q] = lo; upper[q] = hi; }
           active = false;
         }
       }
     }
   }
-  if (stats && G.g == 0 && nsteps) atomicAdd(stats, nsteps);
+  if (stats && nsteps) atomicAdd(stats, nsteps);
 }
 
 /* K2.  extractPrefix (query.cpp:43-63): LF-walk from each row to its '$'.  Same step-interleaved
- * scheme as K1: a group whose walk ends takes its next row on the following trip, so the set of
+ * scheme as K1: a thread whose walk ends takes its next row on the following trip, so the set of
  * live walkers stays dense in every warp without a separate compaction pass. */
-template <int LANES>
 __global__ void __launch_bounds__(RS_THREADS)
     k_extract_prefix(const __grid_constant__ rs_index_dev ix, const uint64_t* __restrict__ rows, uint64_t n,
                      uint32_t max_steps, uint64_t* __restrict__ lexrank, uint32_t* __restrict__ steps,
                      const uint64_t* __restrict__ sai, uint64_t* __restrict__ read_index, uint8_t* __restrict__ bases,
                      unsigned long long* __restrict__ stats) {
-  const rs_grp<LANES> G;
-  constexpr int GPB = RS_THREADS / LANES;
-  const uint64_t ngroups = (uint64_t)gridDim.x * GPB;
+  const uint64_t stride = (uint64_t)gridDim.x * RS_THREADS;
   unsigned long long lf_steps = 0;
-  uint64_t next_i = (uint64_t)blockIdx.x * GPB + threadIdx.x / LANES;
+  uint64_t next_i = (uint64_t)blockIdx.x * RS_THREADS + threadIdx.x;
   uint64_t i = 0, idx = 0;
   uint32_t s = 0;
   bool active = false;
   while (true) {
     if (!active && next_i < n) {
       i = next_i;
-      next_i += ngroups;
+      next_i += stride;
       idx = rows[i];
       s = 0;
       active = true;
@@ -236,7 +216,7 @@ __global__ void __launch_bounds__(RS_THREADS)
     if (__all_sync(RS_FULL, !active)) break;
     if (active) {
       uint64_t nxt;
-      const uint32_t sym = rs_grp_lf_step(ix, G, idx, &nxt);
+      const uint32_t sym = rs_lf_step(ix, idx, &nxt);
       ++lf_steps;
       idx = nxt;
       bool done = false;
@@ -247,7 +227,7 @@ __global__ void __launch_bounds__(RS_THREADS)
         term = idx;
         nsteps = s;
       } else {
-        if (bases && s < max_steps && G.g == 0) bases[i * (uint64_t)max_steps + s] = (uint8_t)rs_ascii(sym);
+        if (bases && s < max_steps) bases[i * (uint64_t)max_steps + s] = (uint8_t)rs_ascii(sym);
         ++s;
         if (s > max_steps) { /* the reference would never return (walk cycling in its tail region) */
           done = true;
@@ -256,61 +236,42 @@ __global__ void __launch_bounds__(RS_THREADS)
         }
       }
       if (done) {
-        if (G.g == 0) {
-          if (lexrank) lexrank[i] = term;
-          if (steps) steps[i] = nsteps;
-          if (read_index) read_index[i] = (term != ~0ull && term < ix.num_strings) ? sai[term] : ~0ull;
-        }
+        if (lexrank) lexrank[i] = term;
+        if (steps) steps[i] = nsteps;
+        if (read_index) read_index[i] = (term != ~0ull && term < ix.num_strings) ? sai[term] : ~0ull;
         if (bases) { /* std::reverse (query.cpp:60): the walk produced the prefix back to front */
           uint8_t* p = bases + i * (uint64_t)max_steps;
           const uint32_t m = nsteps == 0xFFFFFFFFu ? 0u : nsteps;
-          __syncwarp(G.mask);
-          for (uint32_t a = G.g; a < m / 2; a += LANES) {
+          for (uint32_t a = 0; a < m / 2; ++a) {
             const uint8_t t = p[a];
             p[a] = p[m - 1 - a];
             p[m - 1 - a] = t;
           }
-          for (uint32_t a = m + G.g; a < max_steps; a += LANES) p[a] = 0;
+          for (uint32_t a = m; a < max_steps; ++a) p[a] = 0;
         }
         active = false;
       }
     }
   }
-  if (stats && G.g == 0 && lf_steps) atomicAdd(stats + 1, lf_steps);
-}
-
-template <int LANES>
-__global__ void __launch_bounds__(RS_THREADS) k_occ_at(const __grid_constant__ rs_index_dev ix, const uint8_t* __restrict__ syms,
-                                                       const uint64_t* __restrict__ cnt, uint64_t n,
-                                                       uint64_t* __restrict__ out) {
-  const rs_grp<LANES> G;
-  constexpr int GPB = RS_THREADS / LANES;
-  const uint64_t ngroups = (uint64_t)gridDim.x * GPB;
-  for (uint64_t i = (uint64_t)blockIdx.x * GPB + threadIdx.x / LANES; i < n; i += ngroups) {
-    const uint64_t r = rs_grp_occ_at(ix, G, rs_code(syms[i]), cnt[i]);
-    if (G.g == 0) out[i] = r;
-  }
+  if (stats && lf_steps) atomicAdd(stats + 1, lf_steps);
 }
 
 /* extractPostfix (query.cpp:65-85): forward walk by getF / getOccAt from each row to the '$' row of
  * its read.  read_index = the row at which getF returned '$' (the read's index in builder input
  * order); the select of that last step is still performed, as the reference does. */
-template <int LANES>
 __global__ void __launch_bounds__(RS_THREADS)
     k_extract_postfix(const __grid_constant__ rs_index_dev ix, const uint64_t* __restrict__ rows, uint64_t n,
                       uint32_t max_steps, uint64_t* __restrict__ read_index, uint32_t* __restrict__ steps,
                       uint8_t* __restrict__ bases) {
-  const rs_grp<LANES> G;
-  constexpr int GPB = RS_THREADS / LANES;
-  const uint64_t ngroups = (uint64_t)gridDim.x * GPB;
-  uint64_t next_i = (uint64_t)blockIdx.x * GPB + threadIdx.x / LANES;
+  const uint64_t stride = (uint64_t)gridDim.x * RS_THREADS;
+  uint64_t next_i = (uint64_t)blockIdx.x * RS_THREADS + threadIdx.x;
   uint64_t i = 0, idx = 0;
   uint32_t s = 0;
   bool active = false;
   while (true) {
     if (!active && next_i < n) {
       i = next_i;
-      next_i += ngroups;
+      next_i += stride;
       idx = rows[i];
       s = 0;
       active = true;
@@ -319,7 +280,7 @@ __global__ void __launch_bounds__(RS_THREADS)
     if (active) {
       uint64_t nxt;
       const uint64_t at = idx;
-      const uint32_t f = rs_grp_fl_step(ix, G, idx < ix.n ? idx : ix.n - 1, &nxt);
+      const uint32_t f = rs_fl_step(ix, idx < ix.n ? idx : ix.n - 1, &nxt);
       idx = nxt;
       bool done = false;
       uint64_t term = 0;
@@ -329,7 +290,7 @@ __global__ void __launch_bounds__(RS_THREADS)
         term = at;
         nsteps = s;
       } else {
-        if (bases && s < max_steps && G.g == 0) bases[i * (uint64_t)max_steps + s] = (uint8_t)rs_ascii(f);
+        if (bases && s < max_steps) bases[i * (uint64_t)max_steps + s] = (uint8_t)rs_ascii(f);
         ++s;
         if (s > max_steps || idx == ~0ull) {
           done = true;
@@ -338,15 +299,12 @@ __global__ void __launch_bounds__(RS_THREADS)
         }
       }
       if (done) {
-        if (G.g == 0) {
-          if (read_index) read_index[i] = term;
-          if (steps) steps[i] = nsteps;
-        }
+        if (read_index) read_index[i] = term;
+        if (steps) steps[i] = nsteps;
         if (bases) {
           uint8_t* p = bases + i * (uint64_t)max_steps;
           const uint32_t m = nsteps == 0xFFFFFFFFu ? 0u : nsteps;
-          __syncwarp(G.mask);
-          for (uint32_t a = m + G.g; a < max_steps; a += LANES) p[a] = 0;
+          for (uint32_t a = m; a < max_steps; ++a) p[a] = 0;
         }
         active = false;
       }
@@ -355,59 +313,33 @@ __global__ void __launch_bounds__(RS_THREADS)
 }
 
 /* ---- launchers ---- */
-static int g_lanes = 0;
-
-int rs_get_lanes() {
-  if (!g_lanes) {
-    const char* e = getenv("RS_B200_LANES");
-    const int v = e ? atoi(e) : 0;
-    g_lanes = (v == 1 || v == 2 || v == 4 || v == 8) ? v : RS_DEFAULT_LANES;
-  }
-  return g_lanes;
-}
-
-void rs_set_lanes(int lanes) {
-  if (lanes == 1 || lanes == 2 || lanes == 4 || lanes == 8) g_lanes = lanes;
-}
-
-static int rs_grid_for(const void* kernel, int lanes, uint64_t items) {
-  static int sms = 0;
-  if (!sms) {
-    int dev = 0;
-    cudaGetDevice(&dev);
-    cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-    if (sms <= 0) sms = 148;
-  }
+static int rs_grid_for(const void* kernel, uint64_t items) {
+  int dev = 0, sms = 0;
+  cudaGetDevice(&dev);
+  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+  if (sms <= 0) sms = 148;
   int per_sm = 0;
   cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, RS_THREADS, 0);
   if (per_sm < 1) per_sm = 1;
   uint64_t grid = (uint64_t)sms * per_sm; /* one resident wave, a multiple of the SM count */
-  const uint64_t gpb = RS_THREADS / lanes;
-  const uint64_t need = (items + gpb - 1) / gpb;
+  const uint64_t need = (items + RS_THREADS - 1) / RS_THREADS;
   if (need < grid) grid = need;
   return grid ? (int)grid : 1;
 }
 
-#define RS_DISPATCH(KERNEL, ITEMS, ST, ...)                                                                       \
-  do {                                                                                                            \
-    switch (rs_get_lanes()) {                                                                                     \
-      case 1: KERNEL<1><<<rs_grid_for((const void*)KERNEL<1>, 1, ITEMS), RS_THREADS, 0, ST>>>(__VA_ARGS__); break; \
-      case 2: KERNEL<2><<<rs_grid_for((const void*)KERNEL<2>, 2, ITEMS), RS_THREADS, 0, ST>>>(__VA_ARGS__); break; \
-      case 4: KERNEL<4><<<rs_grid_for((const void*)KERNEL<4>, 4, ITEMS), RS_THREADS, 0, ST>>>(__VA_ARGS__); break; \
-      default: KERNEL<8><<<rs_grid_for((const void*)KERNEL<8>, 8, ITEMS), RS_THREADS, 0, ST>>>(__VA_ARGS__); break; \
-    }                                                                                                             \
-  } while (0)
+#define RS_LAUNCH(KERNEL, ITEMS, ST, ...) \
+  KERNEL<<<rs_grid_for((const void*)KERNEL, ITEMS), RS_THREADS, 0, ST>>>(__VA_ARGS__)
 
 cudaError_t rs_launch_occ(const rs_index_dev& ix, const uint8_t* syms, const uint64_t* idx, uint64_t n, uint64_t* out,
                           cudaStream_t st) {
   if (!n) return cudaSuccess;
-  RS_DISPATCH(k_occ, n, st, ix, syms, idx, n, out);
+  RS_LAUNCH(k_occ, n, st, ix, syms, idx, n, out);
   return cudaGetLastError();
 }
 
 cudaError_t rs_launch_char(const rs_index_dev& ix, const uint64_t* idx, uint64_t n, uint8_t* out, cudaStream_t st) {
   if (!n) return cudaSuccess;
-  RS_DISPATCH(k_char, n, st, ix, idx, n, out);
+  RS_LAUNCH(k_char, n, st, ix, idx, n, out);
   return cudaGetLastError();
 }
 
@@ -417,28 +349,14 @@ cudaError_t rs_launch_getf(const rs_index_dev& ix, const uint64_t* idx, uint64_t
   return cudaGetLastError();
 }
 
-template <int LANES>
-static void launch_fi(const rs_index_dev& ix, const uint8_t* text, const uint64_t* offs, uint32_t k, uint64_t Q,
-                      uint64_t* lower, uint64_t* upper, int mode, int strand, unsigned long long* stats,
-                      cudaStream_t st) {
-  if (ix.ftab && ix.ftab_k > 1)
-    k_find_interval<LANES, true><<<rs_grid_for((const void*)k_find_interval<LANES, true>, LANES, Q), RS_THREADS, 0, st>>>(
-        ix, text, offs, k, Q, lower, upper, mode, strand, stats);
-  else
-    k_find_interval<LANES, false><<<rs_grid_for((const void*)k_find_interval<LANES, false>, LANES, Q), RS_THREADS, 0, st>>>(
-        ix, text, offs, k, Q, lower, upper, mode, strand, stats);
-}
-
 cudaError_t rs_launch_find_interval(const rs_index_dev& ix, const uint8_t* text, const uint64_t* offs, uint32_t k,
                                     uint64_t Q, uint64_t* lower, uint64_t* upper, int mode, int strand,
                                     unsigned long long* stats, cudaStream_t st) {
   if (!Q) return cudaSuccess;
-  switch (rs_get_lanes()) {
-    case 1: launch_fi<1>(ix, text, offs, k, Q, lower, upper, mode, strand, stats, st); break;
-    case 2: launch_fi<2>(ix, text, offs, k, Q, lower, upper, mode, strand, stats, st); break;
-    case 4: launch_fi<4>(ix, text, offs, k, Q, lower, upper, mode, strand, stats, st); break;
-    default: launch_fi<8>(ix, text, offs, k, Q, lower, upper, mode, strand, stats, st); break;
-  }
+  if (ix.ftab && ix.ftab_k > 1)
+    RS_LAUNCH(k_find_interval<true>, Q, st, ix, text, offs, k, Q, lower, upper, mode, strand, stats);
+  else
+    RS_LAUNCH(k_find_interval<false>, Q, st, ix, text, offs, k, Q, lower, upper, mode, strand, stats);
   return cudaGetLastError();
 }
 
@@ -487,20 +405,20 @@ cudaError_t rs_launch_extract_prefix(const rs_index_dev& ix, const uint64_t* row
                                      uint64_t* lexrank, uint32_t* steps, const uint64_t* sai, uint64_t* read_index,
                                      uint8_t* bases, unsigned long long* stats, cudaStream_t st) {
   if (!n) return cudaSuccess;
-  RS_DISPATCH(k_extract_prefix, n, st, ix, rows, n, max_steps, lexrank, steps, sai, read_index, bases, stats);
+  RS_LAUNCH(k_extract_prefix, n, st, ix, rows, n, max_steps, lexrank, steps, sai, read_index, bases, stats);
   return cudaGetLastError();
 }
 
 cudaError_t rs_launch_occ_at(const rs_index_dev& ix, const uint8_t* syms, const uint64_t* cnt, uint64_t n, uint64_t* out,
                              cudaStream_t st) {
   if (!n) return cudaSuccess;
-  RS_DISPATCH(k_occ_at, n, st, ix, syms, cnt, n, out);
+  RS_LAUNCH(k_occ_at, n, st, ix, syms, cnt, n, out);
   return cudaGetLastError();
 }
 
 cudaError_t rs_launch_extract_postfix(const rs_index_dev& ix, const uint64_t* rows, uint64_t n, uint32_t max_steps,
                                       uint64_t* read_index, uint32_t* steps, uint8_t* bases, cudaStream_t st) {
   if (!n) return cudaSuccess;
-  RS_DISPATCH(k_extract_postfix, n, st, ix, rows, n, max_steps, read_index, steps, bases);
+  RS_LAUNCH(k_extract_postfix, n, st, ix, rows, n, max_steps, read_index, steps, bases);
   return cudaGetLastError();
 }

@@ -8,10 +8,6 @@
 #include "rs_layout.h"
 
 #define RS_THREADS 256
-#define RS_DEFAULT_LANES 1 /* lanes per query; RS_B200_LANES=1|2|4|8 in the environment overrides */
-
-int rs_get_lanes();
-void rs_set_lanes(int lanes);
 
 cudaError_t rs_launch_occ(const rs_index_dev& ix, const uint8_t* syms, const uint64_t* idx, uint64_t n, uint64_t* out,
                           cudaStream_t st);

@@ -60,8 +60,6 @@ def lib() -> C.CDLL:
         "rs_index_set_prefix_table": (i32, [vp, i32]),
         "rs_index_enable_stats": (i32, [vp, i32]),
         "rs_index_read_stats": (i32, [vp, C.POINTER(u64), C.POINTER(u64), i32]),
-        "rs_config_set_lanes": (i32, [i32]),
-        "rs_config_get_lanes": (i32, []),
         "rs_measure_random_access": (i32, [i32, u64, u64, C.POINTER(C.c_double)]),
         "rs_last_error": (C.c_char_p, []),
         "rs_host_alloc": (i32, [C.POINTER(vp), sz]),
@@ -100,15 +98,6 @@ def lib() -> C.CDLL:
 def _check(rc: int):
     if rc != 0:
         raise RsError(rc, (lib().rs_last_error() or b"").decode("utf-8", "replace"))
-
-
-def set_lanes(lanes: int):
-    """Lanes of a warp cooperating on one query (1, 2, 4, 8): a tuning knob, results do not depend on it."""
-    _check(lib().rs_config_set_lanes(lanes))
-
-
-def get_lanes() -> int:
-    return int(lib().rs_config_get_lanes())
 
 
 def measure_random_access(device: int = 0, buffer_bytes: int = 16 << 30, lines: int = 1 << 28) -> float:

@@ -94,7 +94,7 @@ def write_case(case: Case, path: str) -> str:
 # ------------------------------------------------------------------------------------------------
 def build_emul() -> str:
     srcs = [os.path.join(EMUL_DIR, "rs_emul.cpp"), os.path.join(CSRC, "rs_build.cpp")]
-    deps = srcs + [os.path.join(CSRC, h) for h in ("rs_build.h", "rs_layout.h", "rs_swar.h")]
+    deps = srcs + [os.path.join(CSRC, h) for h in ("rs_build.h", "rs_layout.h", "rs_swar.h", "rs_ops.h")]
     if os.path.exists(EMUL_SO) and all(os.path.getmtime(d) <= os.path.getmtime(EMUL_SO) for d in deps):
         return EMUL_SO
     subprocess.run(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-Wall", "-Wno-unknown-pragmas", "-I", CSRC,
@@ -115,17 +115,19 @@ class Emul:
             L.emul_open_file.argtypes = [C.c_char_p, C.POINTER(C.c_int)]
             L.emul_close.argtypes = [C.c_void_p]
             L.emul_set_tail.argtypes = [C.c_void_p, C.c_int]
-            L.emul_set_lanes.argtypes = [C.c_void_p, C.c_int]
             L.emul_info.argtypes = [C.c_void_p, _u64p]
             L.emul_occ_batch.argtypes = [C.c_void_p, _u8p, _u64p, C.c_uint64, _u64p]
             L.emul_char_batch.argtypes = [C.c_void_p, _u64p, C.c_uint64, _u8p]
             L.emul_occ_at_batch.argtypes = [C.c_void_p, _u8p, _u64p, C.c_uint64, _u64p]
             L.emul_find_interval_batch.argtypes = [C.c_void_p, _u8p, C.c_int, C.c_uint64, _u64p, _u64p]
             L.emul_prefix_walk_batch.argtypes = [C.c_void_p, _u64p, C.c_uint64, C.c_uint32, _u64p, _u32p]
+            L.emul_postfix_walk_batch.argtypes = [C.c_void_p, _u64p, C.c_uint64, C.c_uint32, _u64p, _u32p]
+            L.emul_blocks.restype = C.c_void_p
+            L.emul_blocks.argtypes = [C.c_void_p]
             cls._lib = L
         return cls._lib
 
-    def __init__(self, case: Case | None = None, path: str | None = None, lanes: int = 8):
+    def __init__(self, case: Case | None = None, path: str | None = None):
         L = self.lib()
         st = C.c_int()
         if path is not None:
@@ -141,7 +143,6 @@ class Emul:
             self.tot = [int(x) for x in info[12:17]]
             self.init_occ = [int(x) for x in info[17:22]]
             self.clamp_char = int(info[22])
-            L.emul_set_lanes(self._h, lanes)
 
     def __del__(self):
         if getattr(self, "_h", None):
@@ -150,10 +151,6 @@ class Emul:
 
     def set_tail(self, on: bool):
         self.lib().emul_set_tail(self._h, int(on))
-
-    def set_lanes(self, lanes: int):
-        """lanes per query of the replayed device code: 1, 2, 4 or 8"""
-        self.lib().emul_set_lanes(self._h, lanes)
 
     def occ(self, syms, idx):
         idx = np.ascontiguousarray(idx, dtype=np.uint64)
@@ -182,6 +179,19 @@ class Emul:
         up = np.empty(q, dtype=np.uint64)
         self.lib().emul_find_interval_batch(self._h, kmers, k, q, lo, up)
         return lo, up
+
+    def blocks(self) -> np.ndarray:
+        """the raw 128-byte blocks as a [nblocks, 128] uint8 array (a copy)"""
+        p = self.lib().emul_blocks(self._h)
+        buf = (C.c_uint8 * (self.nblocks * 128)).from_address(p)
+        return np.frombuffer(buf, dtype=np.uint8).reshape(self.nblocks, 128).copy()
+
+    def postfix_walk(self, rows, max_steps=1024):
+        rows = np.ascontiguousarray(rows, dtype=np.uint64)
+        ri = np.empty(rows.size, dtype=np.uint64)
+        st = np.empty(rows.size, dtype=np.uint32)
+        self.lib().emul_postfix_walk_batch(self._h, rows, rows.size, max_steps, ri, st)
+        return ri, st
 
     def prefix_walk(self, rows, max_steps=1024):
         rows = np.ascontiguousarray(rows, dtype=np.uint64)

@@ -14,14 +14,12 @@ pytestmark = pytest.mark.gpu
 U64MAX = np.iinfo(np.uint64).max
 
 
-@pytest.fixture(scope="module", params=[8, 4, 2, 1], ids=lambda l: f"lanes{l}")
-def engine(request):
-    """The C-ABI engine, once per lane-group width (a tuning knob: results must not depend on it)."""
+@pytest.fixture(scope="module")
+def engine():
+    """The C-ABI engine (ctypes over librs_b200.so)."""
     import torch
     assert torch.cuda.is_available(), "GPU tests need a CUDA device"
     from readserver_b200 import engine as e
-    e.set_lanes(request.param)
-    assert e.get_lanes() == request.param
     return e
 
 
@@ -266,6 +264,9 @@ def test_degenerate_blocks_on_gpu(engine):
     shapes = [((rng.integers(0, 5, 5000).astype(np.uint8) << 5) | 1),
               ((rng.integers(1, 5, 3000).astype(np.uint8) << 5) | 31),
               np.array([(2 << 5) | 7], dtype=np.uint8),
+              ((rng.integers(0, 5, 24).astype(np.uint8) << 5) | rng.integers(1, 32, 24).astype(np.uint8)),
+              ((rng.integers(0, 5, 72).astype(np.uint8) << 5) | rng.integers(1, 32, 72).astype(np.uint8)),
+              ((rng.integers(0, 5, 97).astype(np.uint8) << 5) | rng.integers(1, 32, 97).astype(np.uint8)),
               np.concatenate([(rng.integers(0, 5, 4000).astype(np.uint8) << 5) | 1,
                               (rng.integers(0, 5, 70000).astype(np.uint8) << 5) | rng.integers(1, 4, 70000).astype(np.uint8)])]
     for runs in shapes:
@@ -280,6 +281,10 @@ def test_degenerate_blocks_on_gpu(engine):
                 s = np.full(idx.size, c, dtype=np.uint8)
                 assert np.array_equal(B.get_occ(s, idx), P.get_occ_batch(s, idx))
             assert np.array_equal(B.get_char(idx[:-1]), P.get_char_batch(idx[:-1]))
+            for ci, c in enumerate(b"$ACGT"):
+                cnt = np.arange(1, int(B.info.total[ci]) + 1, dtype=np.uint64)
+                s = np.full(cnt.size, c, dtype=np.uint8)
+                assert np.array_equal(B.get_occ_at(s, cnt), P.get_occ_at_batch(s, cnt))
 
 
 def test_error_behaviour(engine, tmp_path):

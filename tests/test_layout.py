@@ -1,6 +1,6 @@
 """Host logic of the product on the CPU: the .bwt reader + block/directory builder (rs_build.cpp) and
-the per-lane SWAR rank/access/select arithmetic (rs_swar.h), replayed lane by lane (tests/emul) and
-compared with the oracle.  No GPU needed."""
+the per-query rank/access/select code the kernels are compiled from (rs_ops.h, rs_swar.h), replayed on
+host memory (tests/emul) and compared with the oracle.  No GPU needed."""
 import hashlib
 import os
 
@@ -14,12 +14,9 @@ from tests.golden.make_golden import random_runs
 U64MAX = np.iinfo(np.uint64).max
 
 
-@pytest.mark.parametrize("lanes", [1, 2, 4, 8])
 @pytest.mark.parametrize("name", ["tiny", "small", "clean", "mid", "deep"])
-def test_rank_access_select_match_oracle(name, lanes, datasets):
-    if lanes in (2, 4) and name in ("mid", "deep"):
-        pytest.skip("covered by lanes 1 and 8 at this size")
-    case, P, E = datasets.case(name), datasets.port(name), common.Emul(datasets.case(name), lanes=lanes)
+def test_rank_access_select_match_oracle(name, datasets):
+    case, P, E = datasets.case(name), datasets.port(name), common.Emul(datasets.case(name))
     assert E.status == 0 and E.q2_safe == 1 and E.depth == P.depth and E.vlast == P.vsum_size - 1
     assert E.pc == [P.get_pc(c) for c in "$ACGT"]
     assert E.init_occ == [P.get_occ(c, E.n - 1) for c in "$ACGT"]
@@ -36,12 +33,9 @@ def test_rank_access_select_match_oracle(name, lanes, datasets):
         assert np.array_equal(E.occ_at(s, cnt), P.get_occ_at_batch(s, cnt)), chr(c)
 
 
-@pytest.mark.parametrize("lanes", [1, 2, 4, 8])
 @pytest.mark.parametrize("name", ["tiny", "small", "clean", "mid", "deep"])
-def test_find_interval_and_walk_match_oracle(name, lanes, datasets):
-    if lanes in (2, 4) and name in ("mid", "deep"):
-        pytest.skip("covered by lanes 1 and 8 at this size")
-    case, P, E = datasets.case(name), datasets.port(name), common.Emul(datasets.case(name), lanes=lanes)
+def test_find_interval_and_walk_match_oracle(name, datasets):
+    case, P, E = datasets.case(name), datasets.port(name), common.Emul(datasets.case(name))
     for k in (1, 2, 12, 31, 73):
         q = case.queries(1500, k, seed=40 + k)
         a, b = E.find_interval(q, k), P.find_interval_batch(q, k)
@@ -50,6 +44,43 @@ def test_find_interval_and_walk_match_oracle(name, lanes, datasets):
     lex, st = E.prefix_walk(rows, 300)
     lex2, st2, _, _ = P.locate_batch(rows, postfix=False, max_steps=300)
     assert np.array_equal(lex, lex2) and np.array_equal(st, st2)
+    ri, st = E.postfix_walk(rows, 300)
+    _, _, ri2, st2 = P.locate_batch(rows, prefix=False, max_steps=300)
+    assert np.array_equal(ri, ri2) and np.array_equal(st, st2)
+
+
+def test_block_structure(datasets):
+    """The 128-byte block as rs_layout.h documents it: header sector + three sub-block sectors whose
+    records and bounds agree with a plain decode of the run bytes."""
+    case = datasets.case("small")
+    E = common.Emul(case)
+    blocks = E.blocks()
+    runs = case.runs
+    assert E.nblocks == (runs.size + 71) // 72
+    sym, ln = (runs >> 5).astype(np.int64), (runs & 31).astype(np.int64)
+    csum = np.zeros((5, runs.size + 1), dtype=np.int64)
+    for c in range(5):
+        csum[c, 1:] = np.cumsum(np.where(sym == c, ln, 0))
+    tot = np.concatenate([[0], np.cumsum(ln)])
+    for b in (0, 1, E.nblocks // 2, E.nblocks - 1):
+        raw = blocks[b]
+        r0 = b * 72
+        assert int(raw[0:8].view(np.uint64)[0]) == tot[r0]
+        lo, hi = raw[8:24].view(np.uint32), raw[24:28]
+        for c in range(4):
+            assert int(lo[c]) + (int(hi[c]) << 32) == csum[c + 1, r0]
+        bounds = int(raw[28:32].view(np.uint32)[0])
+        for j in range(3):
+            sec = raw[32 + 32 * j: 64 + 32 * j]
+            rec = int(sec[0:8].view(np.uint64)[0])
+            rj = min(r0 + 24 * j, runs.size)
+            for c in range(4):
+                assert (rec >> (11 * c)) & 0x7FF == csum[c + 1, rj] - csum[c + 1, r0]
+            assert (rec >> 44) & 0xFFF == tot[rj] - tot[r0]
+            body = runs[rj: min(rj + 24, runs.size)]
+            assert np.array_equal(sec[8: 8 + body.size], body) and not sec[8 + body.size:].any()
+            if j:
+                assert (bounds >> (11 * (j - 1))) & 0x7FF == tot[rj] - tot[r0]
 
 
 def test_without_tail_emulation_rank_is_exact(datasets):
@@ -103,17 +134,20 @@ def test_ragged_and_degenerate_blocks():
         "all_len31": ((rng.integers(1, 5, 3000).astype(np.uint8) << 5) | 31),
         "single_run": np.array([(2 << 5) | 7], dtype=np.uint8),
         "dollars": np.full(200, (0 << 5) | 31, dtype=np.uint8),
-        "exact_88": ((rng.integers(0, 5, 88).astype(np.uint8) << 5) | rng.integers(1, 32, 88).astype(np.uint8)),
-        "exact_176": ((rng.integers(0, 5, 176).astype(np.uint8) << 5) | rng.integers(1, 32, 176).astype(np.uint8)),
+        "exact_72": ((rng.integers(0, 5, 72).astype(np.uint8) << 5) | rng.integers(1, 32, 72).astype(np.uint8)),
+        "exact_144": ((rng.integers(0, 5, 144).astype(np.uint8) << 5) | rng.integers(1, 32, 144).astype(np.uint8)),
+        "one_sub": ((rng.integers(0, 5, 24).astype(np.uint8) << 5) | rng.integers(1, 32, 24).astype(np.uint8)),
+        "sub_plus_1": ((rng.integers(0, 5, 97).astype(np.uint8) << 5) | rng.integers(1, 32, 97).astype(np.uint8)),
+        "two_subs": ((rng.integers(0, 5, 72 + 48).astype(np.uint8) << 5) | rng.integers(1, 32, 120).astype(np.uint8)),
         "mixed": np.concatenate([(rng.integers(0, 5, 4000).astype(np.uint8) << 5) | 1,
                                  (rng.integers(0, 5, 4000).astype(np.uint8) << 5) | 31,
                                  (rng.integers(0, 5, 70000).astype(np.uint8) << 5) | rng.integers(1, 4, 70000).astype(np.uint8)]),
     }
-    for (name, runs), lanes in [(kv, l) for kv in shapes.items() for l in (1, 2, 4, 8)]:
+    for name, runs in shapes.items():
         runs = np.ascontiguousarray(runs, dtype=np.uint8)
         n = int((runs & 31).astype(np.int64).sum())
         case = common.Case(name, runs, 1, n, np.zeros(1, np.uint64), None)
-        E = common.Emul(case, lanes=lanes)
+        E = common.Emul(case)
         assert E.status == 0, name
         P = oracle.PortIndex(runs=runs, num_strings=1, num_symbols=n)
         idx = np.concatenate([np.arange(n, dtype=np.uint64), np.array([U64MAX], dtype=np.uint64)])
