@@ -39,7 +39,8 @@ def is_stale() -> bool:
 def build(force: bool = False, verbose: bool = False) -> str:
     if not force and not is_stale():
         return LIB
-    cmd = [_nvcc(), *NVCC_FLAGS, "-I", CSRC, "-o", LIB] + [os.path.join(CSRC, f) for f in SOURCES]
+    extra = os.environ.get("RS_NVCC_EXTRA", "").split()  # e.g. -DRS_K1_BLOCKS=6 for tuning experiments
+    cmd = [_nvcc(), *NVCC_FLAGS, *extra, "-I", CSRC, "-o", LIB] + [os.path.join(CSRC, f) for f in SOURCES]
     if verbose:
         cmd.insert(1, "-Xptxas=-v")
         print(" ".join(cmd))

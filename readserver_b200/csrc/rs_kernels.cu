@@ -58,33 +58,110 @@ __global__ void k_getf(const __grid_constant__ rs_index_dev ix, const uint64_t* 
   out[i] = (uint8_t)rs_ascii(ci - 1);
 }
 
+/* Pre-pass of K1 for fixed-length queries of k <= 31 characters: the searched string (the query, or its
+ * reverse complement when rc) as a base-4 number, first character most significant, A,C,G,T = 0..3;
+ * bit 63 = the query holds a byte outside ACGT.  A block stages its 256 queries through shared memory
+ * so that the ASCII batch is read with coalesced loads.  The result is parked in lower[] (each K1
+ * thread reads lower[q] before it writes it). */
+#define RS_PACK_MAX_K 31
+__global__ void __launch_bounds__(RS_THREADS) k_pack_kmers(const uint8_t* __restrict__ text, uint32_t k, uint64_t Q,
+                                                          int rc, uint64_t* __restrict__ packed) {
+  __shared__ uint8_t sm[RS_THREADS * RS_PACK_MAX_K];
+  const uint64_t q0 = (uint64_t)blockIdx.x * RS_THREADS;
+  const uint32_t nq = (uint32_t)(Q - q0 < RS_THREADS ? Q - q0 : RS_THREADS);
+  const uint32_t nbytes = nq * k;
+  const uint8_t* src = text + q0 * k;
+  const uint32_t head = (uint32_t)((4 - ((uintptr_t)src & 3)) & 3); /* bytes before the first aligned word */
+  for (uint32_t i = threadIdx.x; i < head && i < nbytes; i += RS_THREADS) sm[i] = src[i];
+  if (nbytes > head) {
+    /* aligned words are stored to shared memory byte by byte: sm has no alignment relation to src */
+    const uint32_t nwords = (nbytes - head) / 4;
+    const uint32_t* w = reinterpret_cast<const uint32_t*>(src + head);
+    for (uint32_t i = threadIdx.x; i < nwords; i += RS_THREADS) {
+      const uint32_t v = __ldg(w + i);
+      uint8_t* d = sm + head + 4 * i;
+      d[0] = (uint8_t)v;
+      d[1] = (uint8_t)(v >> 8);
+      d[2] = (uint8_t)(v >> 16);
+      d[3] = (uint8_t)(v >> 24);
+    }
+    for (uint32_t i = head + 4 * nwords + threadIdx.x; i < nbytes; i += RS_THREADS) sm[i] = src[i];
+  }
+  __syncthreads();
+  if (threadIdx.x >= nq) return;
+  const uint8_t* s = sm + threadIdx.x * k;
+  uint64_t v = 0;
+  uint32_t bad = 0;
+  for (uint32_t i = 0; i < k; ++i) {
+    const uint32_t code = rs_code(rc ? s[k - 1 - i] : s[i]);
+    bad |= (code == 0);
+    const uint32_t two = (code - 1u) & 3u;
+    v = (v << 2) | (rc ? 3u - two : two);
+  }
+  packed[q0 + threadIdx.x] = v | ((uint64_t)(bad != 0) << 63);
+}
+
 /* K1.  Each thread owns one query at a time and all lanes of a warp perform one sub-block scan per
  * loop trip, whatever query they are on: a thread whose query ends (all characters consumed, or the
  * interval went empty: query.cpp:35-37) picks up its next query on the following trip, so lanes never
  * idle behind a longer neighbour.  A step (updateInterval, query.cpp:11-15) whose two positions share
  * a sub-block takes one trip; otherwise the second position is scanned on the next trip.
  *   mode 0: write lower/upper.   mode 1: write counts (count_reads, service.cpp:279-315), strand as given. */
-template <bool FTAB>
-__global__ void __launch_bounds__(RS_THREADS)
+#ifndef RS_K1_BLOCKS
+#define RS_K1_BLOCKS 5 /* resident CTAs per SM the register allocation must allow (4: 1532, 5: 1573, 6: 1477 M q/s) */
+#endif
+template <bool FTAB, bool PACKED>
+__global__ void __launch_bounds__(RS_THREADS, RS_K1_BLOCKS)
     k_find_interval(const __grid_constant__ rs_index_dev ix, const uint8_t* __restrict__ text,
                     const uint64_t* __restrict__ offs, uint32_t k, uint64_t Q, uint64_t* __restrict__ lower,
                     uint64_t* __restrict__ upper, int mode, int strand, unsigned long long* __restrict__ stats) {
   const uint64_t stride = (uint64_t)gridDim.x * RS_THREADS;
   uint64_t next_q = (uint64_t)blockIdx.x * RS_THREADS + threadIdx.x;
-  uint64_t q = 0, lo = 0, hi = 0;
+  uint64_t lo = 0, hi = 0;
   const uint8_t* w = text; /* the query's characters */
   int32_t j = -1;          /* index of the next character in search order */
   uint32_t len = 0;
   bool active = false;
   const bool rc = (mode == 1 && strand == 1);
-  unsigned long long nsteps = 0; /* updateInterval calls executed by this thread (2 ranks each) */
-  bool pending = false, none1 = false, none2 = false;
-  uint32_t c = 0;
-  uint64_t r1 = 0, b2 = 0, pend_pos = 0;
+  uint32_t nsteps = 0; /* updateInterval calls executed by this thread (2 ranks each) */
+  bool pending = false; /* the second position of the step in hand is still to be scanned */
+  uint32_t c = 0, b2 = 0;
+  uint64_t r1 = 0;
+  uint64_t pk = 0; /* PACKED: the searched string as k_pack_kmers left it in lower[q] */
 
   while (true) {
-    if (!active && next_q < Q) {
-      q = next_q;
+    if (PACKED && !active && next_q < Q) {
+      const uint64_t q = next_q;
+      next_q += stride;
+      pk = lower[q];
+      len = k;
+      active = true;
+      if (pk >> 63) { /* a byte outside ACGT */
+        if (mode == 1) lower[q] = 0; /* service.cpp:299-301 */
+        /* mode 0 searches such a byte as '$' (alphabet.h:11-32): left flagged for the tail loop below */
+        active = false;
+      } else {
+        const uint32_t c0 = (uint32_t)(pk & 3u) + 1u; /* initInterval (query.cpp:18-21) on the last character */
+        lo = ix.pc[c0];
+        hi = lo + ix.init_occ[c0] - 1;
+        j = (int32_t)len - 2;
+        if (FTAB && len >= ix.ftab_k) {
+          const uint32_t t = ix.ftab_k;
+          const ulonglong2 e = __ldg(reinterpret_cast<const ulonglong2*>(ix.ftab) + (pk & ((1ull << (2 * t)) - 1)));
+          lo = e.x;
+          hi = e.y;
+          j = (int32_t)len - (int32_t)t - 1;
+          if (lo > hi) j = -1; /* the search had already stopped inside the suffix (query.cpp:35-37) */
+        }
+        if (j < 0) {
+          if (mode == 1) lower[q] = hi >= lo ? hi - lo + 1 : 0;
+          else { lower[q] = lo; upper[q] = hi; }
+          active = false;
+        }
+      }
+    }
+    if (!PACKED && !active && next_q < Q) {
+      const uint64_t q = next_q;
       next_q += stride;
       uint64_t base;
       if (offs) {
@@ -138,34 +215,33 @@ __global__ void __launch_bounds__(RS_THREADS)
       continue;
     }
     if (active) {
-      uint64_t pos, pos2, blk;
+      /* positions of the step in hand (recomputed on the second trip of a split step: cheaper than
+       * keeping them in registers across trips) */
+      const bool none1 = (lo == 0), none2 = (hi == ~0ull); /* getOcc(b, 2^64-1) = 0 in the reference */
+      uint64_t p1 = none1 ? 0 : rs_ref_pos(ix, lo - 1);
+      uint64_t p2 = none2 ? 0 : rs_ref_pos(ix, hi);
+      if (p1 >= ix.n) p1 = ix.n - 1;
+      if (p2 >= ix.n) p2 = ix.n - 1;
+      uint64_t pos, blk;
       bool try2 = false;
       const bool was_pending = pending;
       if (!pending) {
+        if (PACKED) c = (uint32_t)((pk >> (2 * (len - 1 - (uint32_t)j))) & 3u) + 1u;
         /* reverse complement: revcomp(w)[j] is the complement of w[len-1-j] */
-        c = rc ? 5u - rs_code(w[len - 1 - j]) : rs_code(w[j]);
-        const uint64_t i1 = lo - 1;
-        none1 = (i1 == ~0ull);
-        uint64_t p1 = none1 ? 0 : rs_ref_pos(ix, i1);
-        none2 = (hi == ~0ull); /* getOcc(b, 2^64-1) = 0 in the reference */
-        uint64_t p2 = none2 ? 0 : rs_ref_pos(ix, hi);
-        if (p1 >= ix.n) p1 = ix.n - 1;
-        if (p2 >= ix.n) p2 = ix.n - 1;
+        else c = rc ? 5u - rs_code(w[len - 1 - j]) : rs_code(w[j]);
         const uint64_t b1 = rs_find_block(ix, p1);
-        b2 = rs_find_block(ix, p2);
-        pend_pos = p2;
+        b2 = (uint32_t)rs_find_block(ix, p2);
         try2 = (b1 == b2) && p2 >= p1;
         pos = p1;
-        pos2 = p2;
         blk = b1;
         ++nsteps;
       } else {
-        pos = pos2 = pend_pos;
+        pos = p2;
         blk = b2;
       }
       uint64_t x1, x2;
       bool did2;
-      rs_scan2(ix, c, blk, pos, pos2, try2, &x1, &x2, &did2);
+      rs_scan2(ix, c, blk, pos, p2, try2, &x1, &x2, &did2);
       uint64_t r2 = 0;
       if (was_pending) {
         r2 = none2 ? 0 : x1;
@@ -181,6 +257,7 @@ __global__ void __launch_bounds__(RS_THREADS)
         hi = pb + r2 - 1;
         --j;
         if (lo > hi || j < 0) {
+          const uint64_t q = next_q - stride;
           if (mode == 1) lower[q] = hi >= lo ? hi - lo + 1 : 0;
           else { lower[q] = lo; upper[q] = hi; }
           active = false;
@@ -188,7 +265,29 @@ __global__ void __launch_bounds__(RS_THREADS)
       }
     }
   }
-  if (stats && nsteps) atomicAdd(stats, nsteps);
+  if (PACKED && mode == 0) {
+    /* the rare queries holding a byte outside ACGT, one whole findInterval each (query.cpp:24-41); a valid
+     * lower bound never has bit 63 set */
+    for (uint64_t q = (uint64_t)blockIdx.x * RS_THREADS + threadIdx.x; q < Q; q += stride) {
+      if (!(lower[q] >> 63)) continue;
+      w = text + q * (uint64_t)k;
+      c = rs_code(w[k - 1]);
+      lo = ix.pc[c];
+      hi = lo + ix.init_occ[c] - 1;
+      for (j = (int32_t)k - 2; j >= 0; --j) {
+        c = rs_code(w[j]);
+        uint64_t a1, a2;
+        rs_occ2(ix, c, lo - 1, hi, &a1, &a2);
+        ++nsteps;
+        lo = ix.pc[c] + a1;
+        hi = ix.pc[c] + a2 - 1;
+        if (lo > hi) break;
+      }
+      lower[q] = lo;
+      upper[q] = hi;
+    }
+  }
+  if (stats && nsteps) atomicAdd(stats, (unsigned long long)nsteps);
 }
 
 /* K2.  extractPrefix (query.cpp:43-63): LF-walk from each row to its '$'.  Same step-interleaved
@@ -353,10 +452,16 @@ cudaError_t rs_launch_find_interval(const rs_index_dev& ix, const uint8_t* text,
                                     uint64_t Q, uint64_t* lower, uint64_t* upper, int mode, int strand,
                                     unsigned long long* stats, cudaStream_t st) {
   if (!Q) return cudaSuccess;
-  if (ix.ftab && ix.ftab_k > 1)
-    RS_LAUNCH(k_find_interval<true>, Q, st, ix, text, offs, k, Q, lower, upper, mode, strand, stats);
-  else
-    RS_LAUNCH(k_find_interval<false>, Q, st, ix, text, offs, k, Q, lower, upper, mode, strand, stats);
+  const bool ftab = ix.ftab && ix.ftab_k > 1;
+  if (!offs && k >= 1 && k <= RS_PACK_MAX_K) {
+    k_pack_kmers<<<(unsigned)((Q + RS_THREADS - 1) / RS_THREADS), RS_THREADS, 0, st>>>(text, k, Q, mode == 1 && strand == 1,
+                                                                                   lower);
+    if (ftab) RS_LAUNCH((k_find_interval<true, true>), Q, st, ix, text, offs, k, Q, lower, upper, mode, strand, stats);
+    else RS_LAUNCH((k_find_interval<false, true>), Q, st, ix, text, offs, k, Q, lower, upper, mode, strand, stats);
+  } else {
+    if (ftab) RS_LAUNCH((k_find_interval<true, false>), Q, st, ix, text, offs, k, Q, lower, upper, mode, strand, stats);
+    else RS_LAUNCH((k_find_interval<false, false>), Q, st, ix, text, offs, k, Q, lower, upper, mode, strand, stats);
+  }
   return cudaGetLastError();
 }
 
