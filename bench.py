@@ -10,8 +10,9 @@ N = 1     workload = BASELINE.json configs[1]: 50M x 100bp reads from a random 1
           de-duplicated, one RLBWT; 1M 31-mers (90% cut from the genome).
 N > 1     weak scaling: every rank holds its OWN shard of that size (a different read sample of the same
           genome -- the reference shards by read, and every query visits every shard: SURVEY.md 8(e)),
-          all ranks search the same Q k-mers and the per-shard counts are summed with one NCCL all-reduce
-          inside the timed region (the reference's ZMQ fan-in + sum, server.cpp:184-197, 404-410).
+          all ranks search the same Q k-mers and the search kernel itself adds each per-shard count into the
+          buffer of the rank owning the k-mer (by prefix) over NVLink peer memory, followed by one flag
+          barrier -- inside the timed region (the reference's ZMQ fan-in + sum, server.cpp:184-197, 404-410).
           The unit is therefore one 31-mer searched in one shard; value = N*Q*K / max-over-ranks time.
 
 Prints ONE JSON line on rank 0.  `--impl reference` times the reference's own CPU code (oracle/_ref, or
@@ -252,10 +253,19 @@ def run_ours(args):
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
     stream = torch.cuda.current_stream().cuda_stream
 
+    comm = None
+    fused_ptr = [0]
+    if world > 1:
+        from readserver_b200 import sharding
+        comm = sharding.connect_peers(engine.PeerComm(local_rank, rank, world, Q), dev)
+
     def step():
         if world > 1:
-            B.count_dev(dq, k, Q, 0, dcnt, stream)
-            dist.all_reduce(dcnt)  # per-shard counts -> population counts (C1)
+            # K1 adds every finished query's count into the owning rank's buffer over NVLink peer memory
+            # (search + reduce-scatter in one kernel), then one flag barrier across the GPUs (C1)
+            comm.begin(Q, stream)
+            comm.accumulate(B, dq, k, Q, 0, stream)
+            fused_ptr[0] = comm.finish(stream)
         else:
             B.find_interval_dev(dq, k, Q, dlo, dup, stream)
 
@@ -286,6 +296,22 @@ def run_ours(args):
         dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
     total_ms = float(total_ms.item())
     interval_steps, _ = B.read_stats(reset=True)
+
+    fused_ok = None
+    if world > 1:
+        # the fused reduce-scatter against NCCL: per-shard counts summed with an all-reduce, owned entries compared
+        from readserver_b200 import sharding
+        assert not comm.timed_out(), "peer barrier timed out"
+        fused = sharding.counts_view(fused_ptr[0], Q, dev).clone()
+        B.count_dev(dq, k, Q, 0, dcnt, stream)
+        torch.cuda.synchronize()
+        dist.all_reduce(dcnt)
+        own = torch.from_numpy(sharding.owner_of(dq.cpu().numpy().reshape(Q, k), world)).to(dev) == rank
+        ok = bool(torch.equal(fused[own], dcnt[own]) and int(fused[~own].abs().sum()) == 0)
+        okt = torch.tensor([int(ok)], device=dev)
+        dist.all_reduce(okt, op=dist.ReduceOp.MIN)
+        fused_ok = bool(okt.item())
+        assert fused_ok, "fused peer-memory reduction differs from the NCCL all-reduce of per-shard counts"
 
     # ---- e2e: the host-pointer C-ABI call, pinned host buffers, copies inside the timed region ----
     hq, _p1 = pinned_array(engine, Q * k, np.uint8, (Q, k))
@@ -375,7 +401,10 @@ def run_ours(args):
             "index_hbm_bytes": int(B.info.hbm_bytes), "index_fits_l2": bool(B.info.hbm_bytes < 126e6),
             "l2": "256 MiB buffer written between timed steps (untimed) -> index and queries start cold",
             "timing": "CUDA events around each step on the launching stream, summed; max over ranks",
-            "collective": "none" if world == 1 else "NCCL all-reduce of per-shard counts inside the timed step",
+            "collective": "none" if world == 1 else
+            "fused into K1: counts added into the owning rank's buffer over NVLink peer memory + one flag barrier "
+            "per step, inside the timed step; checked against an NCCL all-reduce of the per-shard counts",
+            "fused_reduce_equals_nccl": fused_ok,
             "data_build_seconds": round(shard["build_seconds"], 1),
         },
         "roofline": {
@@ -389,7 +418,7 @@ def run_ours(args):
         },
         "e2e": {"value": world * Q * args.steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": Q * k,
                 "d2h_bytes_per_step": 2 * Q * 8, "api": "rs_find_interval_batch (host pointers, pinned)"},
-        "gpu_launches": args.steps,
+        "gpu_launches": args.steps * (2 if world == 1 else 3),  # k_pack_kmers + k_find_interval (+ k_peer_barrier)
         "clocks": clk,
     }
     if locate:

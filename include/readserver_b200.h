@@ -180,6 +180,34 @@ int rs_samples_batch(const rs_index* ix, const uint64_t* read_index, size_t n, u
 int rs_carriers_batch(const rs_index* ix, const uint64_t* hit_offsets, const uint64_t* read_index, size_t Q,
                       uint64_t* out_offsets, uint64_t capacity, uint8_t* out_codes);
 
+/* ---- fan-in of per-shard counts across the GPUs of one box ----------------------------------------
+ * Replaces the front end's sum over shard replies (src/service/server.cpp:184-197, 404-410).  One
+ * process per GPU; every rank searches the whole batch in its shards and each finished query's count
+ * is added by the search kernel itself into the buffer of the rank that OWNS the k-mer (its first four
+ * bases as a base-4 number, A,C,G,T = 0..3, modulo the number of ranks) through NVLink peer memory.
+ *
+ *   rs_comm_create   allocates this rank's buffers (capacity max_queries per step)
+ *   rs_comm_export   64-byte CUDA IPC handle of that allocation, to be exchanged by the caller
+ *   rs_comm_connect  maps the peers: `handles` = world x 64 bytes in rank order (own slot ignored)
+ *   per step, identically on every rank and on one stream:
+ *     rs_comm_begin(Q) ; rs_count_accumulate_dev(...) once per local shard ; rs_comm_finish
+ *   rs_comm_finish   cross-GPU barrier on the stream; *d_counts = device array of Q u64 whose entries for
+ *                    the k-mers this rank owns hold the population counts (other entries are 0); valid
+ *                    until the next-but-one rs_comm_begin
+ *   rs_comm_error    1 if a barrier gave up waiting for a peer (5 s)
+ * Fixed-length queries of 1..31 characters; any byte outside ACGT counts 0 (service.cpp:299-301). */
+typedef struct rs_comm rs_comm;
+#define RS_COMM_HANDLE_BYTES 64
+int rs_comm_create(int device, int rank, int world, uint64_t max_queries, rs_comm** out);
+int rs_comm_export(rs_comm* c, uint8_t handle[RS_COMM_HANDLE_BYTES]);
+int rs_comm_connect(rs_comm* c, const uint8_t* handles);
+void rs_comm_destroy(rs_comm* c);
+int rs_comm_begin(rs_comm* c, uint64_t Q, void* stream);
+int rs_count_accumulate_dev(const rs_index* ix, rs_comm* c, const void* d_kmers, int k, size_t Q, int strand,
+                            void* stream);
+int rs_comm_finish(rs_comm* c, void* stream, void** d_counts);
+int rs_comm_error(rs_comm* c, int* timed_out);
+
 #ifdef __cplusplus
 }
 #endif

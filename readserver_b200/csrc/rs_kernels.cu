@@ -9,6 +9,7 @@
 #include "rs_kernels.h"
 
 #include <stdlib.h>
+#include <string.h>
 
 #include "rs_ops.h"
 
@@ -107,6 +108,35 @@ __global__ void __launch_bounds__(RS_THREADS) k_pack_kmers(const uint8_t* __rest
  * idle behind a longer neighbour.  A step (updateInterval, query.cpp:11-15) whose two positions share
  * a sub-block takes one trip; otherwise the second position is scanned on the next trip.
  *   mode 0: write lower/upper.   mode 1: write counts (count_reads, service.cpp:279-315), strand as given. */
+/* Where a finished query's answer goes.  mode 0: lower/upper; mode 1: count into lower[];
+ * mode 2 (packed queries only): the count is added into the accumulation buffer of the rank that
+ * owns the k-mer -- its first four bases as a base-4 number, modulo the number of ranks -- directly
+ * through NVLink peer memory: K1 and the reduce-scatter of the per-shard counts are one kernel
+ * (replaces the front end's fan-in sum, src/service/server.cpp:184-197, 404-410). */
+__device__ __forceinline__ uint32_t rs_owner_of(uint64_t pk, uint32_t k, bool rc, uint32_t world) {
+  uint32_t prefix;
+  if (!rc) {
+    prefix = k >= 4 ? (uint32_t)(pk >> (2 * (k - 4))) & 0xFFu : (uint32_t)pk & 0xFFu;
+  } else { /* pk holds the reverse complement: the query's first bases are its last ones, complemented */
+    const uint32_t t = ~(uint32_t)pk & 0xFFu;
+    prefix = k >= 4 ? ((t & 3u) << 6) | (((t >> 2) & 3u) << 4) | (((t >> 4) & 3u) << 2) | (t >> 6) : t;
+  }
+  return prefix % world;
+}
+
+__device__ __forceinline__ void rs_emit(int mode, uint64_t* __restrict__ lower, uint64_t* __restrict__ upper,
+                                        const rs_peers& peers, uint64_t q, uint64_t lo, uint64_t hi, uint64_t pk,
+                                        uint32_t k, bool rc) {
+  if (mode == 0) {
+    lower[q] = lo;
+    upper[q] = hi;
+  } else {
+    const uint64_t cnt = hi >= lo ? hi - lo + 1 : 0;
+    if (mode == 1) lower[q] = cnt;
+    else if (cnt) atomicAdd(reinterpret_cast<unsigned long long*>(peers.buf[rs_owner_of(pk, k, rc, peers.world)]) + q, cnt);
+  }
+}
+
 #ifndef RS_K1_BLOCKS
 #define RS_K1_BLOCKS 5 /* resident CTAs per SM the register allocation must allow (4: 1532, 5: 1573, 6: 1477 M q/s) */
 #endif
@@ -114,7 +144,8 @@ template <bool FTAB, bool PACKED>
 __global__ void __launch_bounds__(RS_THREADS, RS_K1_BLOCKS)
     k_find_interval(const __grid_constant__ rs_index_dev ix, const uint8_t* __restrict__ text,
                     const uint64_t* __restrict__ offs, uint32_t k, uint64_t Q, uint64_t* __restrict__ lower,
-                    uint64_t* __restrict__ upper, int mode, int strand, unsigned long long* __restrict__ stats) {
+                    uint64_t* __restrict__ upper, int mode, int strand, unsigned long long* __restrict__ stats,
+                    const __grid_constant__ rs_peers peers) {
   const uint64_t stride = (uint64_t)gridDim.x * RS_THREADS;
   uint64_t next_q = (uint64_t)blockIdx.x * RS_THREADS + threadIdx.x;
   uint64_t lo = 0, hi = 0;
@@ -122,7 +153,7 @@ __global__ void __launch_bounds__(RS_THREADS, RS_K1_BLOCKS)
   int32_t j = -1;          /* index of the next character in search order */
   uint32_t len = 0;
   bool active = false;
-  const bool rc = (mode == 1 && strand == 1);
+  const bool rc = (mode >= 1 && strand == 1);
   uint32_t nsteps = 0; /* updateInterval calls executed by this thread (2 ranks each) */
   bool pending = false; /* the second position of the step in hand is still to be scanned */
   uint32_t c = 0, b2 = 0;
@@ -137,7 +168,7 @@ __global__ void __launch_bounds__(RS_THREADS, RS_K1_BLOCKS)
       len = k;
       active = true;
       if (pk >> 63) { /* a byte outside ACGT */
-        if (mode == 1) lower[q] = 0; /* service.cpp:299-301 */
+        if (mode == 1) lower[q] = 0; /* service.cpp:299-301; mode 2: nothing to add */
         /* mode 0 searches such a byte as '$' (alphabet.h:11-32): left flagged for the tail loop below */
         active = false;
       } else {
@@ -154,8 +185,7 @@ __global__ void __launch_bounds__(RS_THREADS, RS_K1_BLOCKS)
           if (lo > hi) j = -1; /* the search had already stopped inside the suffix (query.cpp:35-37) */
         }
         if (j < 0) {
-          if (mode == 1) lower[q] = hi >= lo ? hi - lo + 1 : 0;
-          else { lower[q] = lo; upper[q] = hi; }
+          rs_emit(mode, lower, upper, peers, q, lo, hi, pk, k, rc);
           active = false;
         }
       }
@@ -257,9 +287,7 @@ __global__ void __launch_bounds__(RS_THREADS, RS_K1_BLOCKS)
         hi = pb + r2 - 1;
         --j;
         if (lo > hi || j < 0) {
-          const uint64_t q = next_q - stride;
-          if (mode == 1) lower[q] = hi >= lo ? hi - lo + 1 : 0;
-          else { lower[q] = lo; upper[q] = hi; }
+          rs_emit(mode, lower, upper, peers, next_q - stride, lo, hi, pk, k, rc);
           active = false;
         }
       }
@@ -450,17 +478,21 @@ cudaError_t rs_launch_getf(const rs_index_dev& ix, const uint64_t* idx, uint64_t
 
 cudaError_t rs_launch_find_interval(const rs_index_dev& ix, const uint8_t* text, const uint64_t* offs, uint32_t k,
                                     uint64_t Q, uint64_t* lower, uint64_t* upper, int mode, int strand,
-                                    unsigned long long* stats, cudaStream_t st) {
+                                    unsigned long long* stats, cudaStream_t st, const rs_peers* peers_in) {
   if (!Q) return cudaSuccess;
+  rs_peers peers;
+  memset(&peers, 0, sizeof(peers));
+  if (peers_in) peers = *peers_in;
+  if (mode == 2 && (!peers_in || offs || k > RS_PACK_MAX_K)) return cudaErrorInvalidValue;
   const bool ftab = ix.ftab && ix.ftab_k > 1;
   if (!offs && k >= 1 && k <= RS_PACK_MAX_K) {
     k_pack_kmers<<<(unsigned)((Q + RS_THREADS - 1) / RS_THREADS), RS_THREADS, 0, st>>>(text, k, Q, mode == 1 && strand == 1,
                                                                                    lower);
-    if (ftab) RS_LAUNCH((k_find_interval<true, true>), Q, st, ix, text, offs, k, Q, lower, upper, mode, strand, stats);
-    else RS_LAUNCH((k_find_interval<false, true>), Q, st, ix, text, offs, k, Q, lower, upper, mode, strand, stats);
+    if (ftab) RS_LAUNCH((k_find_interval<true, true>), Q, st, ix, text, offs, k, Q, lower, upper, mode, strand, stats, peers);
+    else RS_LAUNCH((k_find_interval<false, true>), Q, st, ix, text, offs, k, Q, lower, upper, mode, strand, stats, peers);
   } else {
-    if (ftab) RS_LAUNCH((k_find_interval<true, false>), Q, st, ix, text, offs, k, Q, lower, upper, mode, strand, stats);
-    else RS_LAUNCH((k_find_interval<false, false>), Q, st, ix, text, offs, k, Q, lower, upper, mode, strand, stats);
+    if (ftab) RS_LAUNCH((k_find_interval<true, false>), Q, st, ix, text, offs, k, Q, lower, upper, mode, strand, stats, peers);
+    else RS_LAUNCH((k_find_interval<false, false>), Q, st, ix, text, offs, k, Q, lower, upper, mode, strand, stats, peers);
   }
   return cudaGetLastError();
 }
@@ -495,7 +527,7 @@ cudaError_t rs_build_ftab(const rs_index_dev& ix_in, uint32_t t, uint64_t* table
   if ((e = cudaMallocAsync((void**)&lo, n * 8, st)) != cudaSuccess) return e;
   if ((e = cudaMallocAsync((void**)&up, n * 8, st)) != cudaSuccess) return e;
   k_all_kmers<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(t, n, kmers);
-  e = rs_launch_find_interval(ix, kmers, nullptr, t, n, lo, up, 0, 0, nullptr, st);
+  e = rs_launch_find_interval(ix, kmers, nullptr, t, n, lo, up, 0, 0, nullptr, st, nullptr);
   if (e == cudaSuccess) {
     k_interleave<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(lo, up, n, reinterpret_cast<ulonglong2*>(table));
     e = cudaGetLastError();

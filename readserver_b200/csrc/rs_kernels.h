@@ -13,11 +13,24 @@ cudaError_t rs_launch_occ(const rs_index_dev& ix, const uint8_t* syms, const uin
                           cudaStream_t st);
 cudaError_t rs_launch_char(const rs_index_dev& ix, const uint64_t* idx, uint64_t n, uint8_t* out, cudaStream_t st);
 cudaError_t rs_launch_getf(const rs_index_dev& ix, const uint64_t* idx, uint64_t n, uint8_t* out, cudaStream_t st);
+#define RS_MAX_RANKS 16
+/* accumulation buffers of the ranks of one box, mapped into this process (rs_peer.cu) */
+typedef struct rs_peers {
+  uint64_t* buf[RS_MAX_RANKS];
+  uint32_t world, rank;
+} rs_peers;
+
 /* mode 0: lower/upper; mode 1: counts into `lower` (strand 0 forward, 1 reverse complement);
+ * mode 2: counts added into the owning rank's buffer through peer memory (`lower` = Q words of scratch,
+ * fixed-length queries of k <= 31 only);
  * stats (nullable): += number of updateInterval steps executed (2 ranks each) */
 cudaError_t rs_launch_find_interval(const rs_index_dev& ix, const uint8_t* text, const uint64_t* offs, uint32_t k,
                                     uint64_t Q, uint64_t* lower, uint64_t* upper, int mode, int strand,
-                                    unsigned long long* stats, cudaStream_t st);
+                                    unsigned long long* stats, cudaStream_t st, const rs_peers* peers = nullptr);
+/* cross-GPU barrier over peer-mapped flag words: every rank writes `epoch` into its slot of every peer's
+ * flag array, then waits until all slots of its own array reached it (or ~timeout_ms passed: *err = 1) */
+cudaError_t rs_launch_peer_barrier(uint64_t* const* peer_flags, uint32_t world, uint32_t rank, uint64_t epoch,
+                                   uint32_t timeout_ms, uint32_t* err, cudaStream_t st);
 cudaError_t rs_build_ftab(const rs_index_dev& ix, uint32_t t, uint64_t* table, cudaStream_t st);
 cudaError_t rs_launch_extract_prefix(const rs_index_dev& ix, const uint64_t* rows, uint64_t n, uint32_t max_steps,
                                      uint64_t* lexrank, uint32_t* steps, const uint64_t* sai, uint64_t* read_index,

@@ -64,6 +64,14 @@ def lib() -> C.CDLL:
         "rs_last_error": (C.c_char_p, []),
         "rs_host_alloc": (i32, [C.POINTER(vp), sz]),
         "rs_host_free": (None, [vp]),
+        "rs_comm_create": (i32, [i32, i32, i32, u64, C.POINTER(vp)]),
+        "rs_comm_export": (i32, [vp, vp]),
+        "rs_comm_connect": (i32, [vp, vp]),
+        "rs_comm_destroy": (None, [vp]),
+        "rs_comm_begin": (i32, [vp, u64, vp]),
+        "rs_count_accumulate_dev": (i32, [vp, vp, vp, i32, sz, i32, vp]),
+        "rs_comm_finish": (i32, [vp, vp, C.POINTER(vp)]),
+        "rs_comm_error": (i32, [vp, C.POINTER(i32)]),
         "rs_get_pc": (u64, [vp, C.c_char]),
         "rs_get_bwlen": (u64, [vp]),
         "rs_get_occ_batch": (i32, [vp, vp, vp, sz, vp]),
@@ -382,3 +390,53 @@ class GpuBWT:
                            d_bases=None, stream: int = 0):
         _check(lib().rs_extract_prefix_batch_dev(self._h, _ptr(d_rows), n, max_steps, _ptr(d_lexrank), _ptr(d_steps),
                                                  _ptr(d_read_index), _ptr(d_bases), stream))
+
+
+class PeerComm:
+    """Fan-in of per-shard counts across the GPUs of one box through NVLink peer memory (rs_comm_* of the
+    C ABI; replaces the front end's sum over shard replies, src/service/server.cpp:184-197, 404-410).
+    The caller exchanges the 64-byte handles (e.g. with torch.distributed.all_gather)."""
+    HANDLE_BYTES = 64
+
+    def __init__(self, device: int, rank: int, world: int, max_queries: int):
+        self._h = C.c_void_p()
+        self.rank, self.world, self.max_queries = rank, world, max_queries
+        _check(lib().rs_comm_create(device, rank, world, max_queries, C.byref(self._h)))
+
+    def export(self) -> np.ndarray:
+        h = np.zeros(self.HANDLE_BYTES, dtype=np.uint8)
+        _check(lib().rs_comm_export(self._h, h.ctypes.data))
+        return h
+
+    def connect(self, handles: np.ndarray):
+        handles = np.ascontiguousarray(handles, dtype=np.uint8).reshape(-1)
+        assert handles.size == self.world * self.HANDLE_BYTES
+        _check(lib().rs_comm_connect(self._h, handles.ctypes.data))
+
+    def begin(self, q: int, stream: int = 0):
+        _check(lib().rs_comm_begin(self._h, q, stream))
+
+    def accumulate(self, bwt: "GpuBWT", d_kmers, k: int, q: int, strand: int = 0, stream: int = 0):
+        _check(lib().rs_count_accumulate_dev(bwt._h, self._h, _ptr(d_kmers), k, q, strand, stream))
+
+    def finish(self, stream: int = 0) -> int:
+        """Barrier on the stream; returns the device address of this step's Q u64 counts."""
+        p = C.c_void_p()
+        _check(lib().rs_comm_finish(self._h, stream, C.byref(p)))
+        return int(p.value)
+
+    def timed_out(self) -> bool:
+        v = C.c_int32()
+        _check(lib().rs_comm_error(self._h, C.byref(v)))
+        return bool(v.value)
+
+    def close(self):
+        if self._h:
+            lib().rs_comm_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()

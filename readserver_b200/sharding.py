@@ -149,3 +149,26 @@ class ShardedCounter:
             c = torch.as_tensor(np.asarray(c).astype(np.int64)) if not torch.is_tensor(c) else c
             total += c.to(self.device)
         return reduce_counts(total, self.group)
+
+
+def connect_peers(comm, device, group=None):
+    """Exchange the CUDA IPC handles of a `engine.PeerComm` over torch.distributed and map the peers."""
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    mine = torch.from_numpy(comm.export()).to(device)
+    if world > 1:
+        allh = [torch.empty_like(mine) for _ in range(world)]
+        dist.all_gather(allh, mine, group=group)
+        handles = torch.cat(allh).cpu().numpy()
+    else:
+        handles = mine.cpu().numpy()
+    comm.connect(handles)
+    if world > 1:
+        dist.barrier(group=group)  # nobody searches before every rank has mapped every peer
+    return comm
+
+
+def counts_view(ptr: int, q: int, device) -> torch.Tensor:
+    """int64 torch view of the Q counts at device address `ptr` (the buffer belongs to the communicator)."""
+    class _Arr:
+        __cuda_array_interface__ = {"shape": (q,), "typestr": "<i8", "data": (ptr, False), "version": 3}
+    return torch.as_tensor(_Arr(), device=device)
