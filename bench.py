@@ -36,7 +36,8 @@ if ROOT not in sys.path:
 
 METRIC = "31-mer count queries/s (findInterval, one shard per GPU)"
 UNIT = "queries/s"
-BYTES_PER_RANK = 128          # one 128-byte block per getOcc
+BYTES_PER_RANK = 64           # one getOcc reads two 32-byte sectors of its block: header + sub-block;
+                              # SURVEY.md 8(d) assumed a whole 128-byte line per getOcc (reported beside it)
 FALLBACK_HBM_GBS = 6650.0     # /opt/skills/guides/B200_PROFILING.md
 
 
@@ -137,7 +138,7 @@ class ClockSampler:
                         self.reasons.add(name)
             except Exception:
                 pass
-            self._stop.wait(0.02)
+            self._stop.wait(0.002)
 
     def start(self):
         if self.nv:
@@ -215,6 +216,16 @@ def hbm_peak():
         return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs, streaming copy)"
     except Exception:
         return FALLBACK_HBM_GBS, "fallback (B200_PROFILING.md)"
+
+
+def k1_traffic():
+    """dram__bytes_read + dram__bytes_write of one K1 launch on this workload, from the committed ncu --set full
+    capture (profiles/k1_traffic.json, written by profiles/ncu_traffic.py); None when there is none."""
+    try:
+        d = json.load(open(os.path.join(ROOT, "profiles", "k1_traffic.json")))
+        return float(d["dram_bytes_per_launch"]), d.get("source")
+    except Exception:
+        return None, None
 
 
 def pinned_array(engine, nbytes, dtype, shape):
@@ -387,6 +398,7 @@ def run_ours(args):
 
     value = world * Q * args.steps / (total_ms / 1e3)
     peak, peak_src = hbm_peak()
+    traffic, traffic_src = k1_traffic()
     kern_ms = sum(step_ms) / len(step_ms)  # at N = 1 the step IS the kernel launch
     ranks_per_launch = 2.0 * interval_steps / args.steps
     achieved = ranks_per_launch * BYTES_PER_RANK / (kern_ms / 1e3) / 1e9
@@ -409,9 +421,11 @@ def run_ours(args):
         },
         "roofline": {
             "bound": "hbm", "kernel": "k_find_interval", "achieved": achieved, "peak": peak, "unit": "GB/s",
-            "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
-            "algorithmic_bytes": "executed getOcc calls x 128 B (SURVEY.md 8(d)); lower/upper of a step usually share a block",
+            "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
+            "algorithmic_bytes": "executed getOcc calls x 64 B (header sector + sub-block sector of the 128-B block); "
+                                 "lower/upper of a step often share a sub-block",
             "getocc_per_launch": ranks_per_launch,
+            "achieved_at_128B_per_getocc": 2 * achieved, "frac_at_128B_per_getocc": 2 * achieved / peak,
             "random_access_peak": random_gbs,
             "frac_of_random_access_peak": (achieved / random_gbs) if random_gbs else None,
             "random_access_peak_source": "measured in this run: random 128-B line loads over 8 GiB (rs_measure_random_access)",
