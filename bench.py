@@ -36,7 +36,7 @@ if ROOT not in sys.path:
 
 METRIC = "31-mer count queries/s (findInterval, one shard per GPU)"
 UNIT = "queries/s"
-BYTES_PER_RANK = 64           # one getOcc reads two 32-byte sectors of its block: header + sub-block;
+BYTES_PER_RANK = 64           # one getOcc reads one 64-byte block = two 32-byte sectors;
                               # SURVEY.md 8(d) assumed a whole 128-byte line per getOcc (reported beside it)
 FALLBACK_HBM_GBS = 6650.0     # /opt/skills/guides/B200_PROFILING.md
 
@@ -408,7 +408,7 @@ def run_ours(args):
         "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
         "config": {
             "workload": workload_name(args), "k": k, "queries_per_step": Q, "shards_per_gpu": 1,
-            "threads_per_query": 1, "block_layout": "128 B = 32 B header + 3 x (8 B record + 24 runs); 2 sectors per rank",
+            "threads_per_query": 1, "block_layout": "64 B = 28 B header (start, 4 x 40-bit counters) + 36 run bytes; 2 sectors per rank",
             "bwt_symbols": shard["num_symbols"], "bwt_runs": int(shard["runs"].size), "reads_unique": shard["num_strings"],
             "index_hbm_bytes": int(B.info.hbm_bytes), "index_fits_l2": bool(B.info.hbm_bytes < 126e6),
             "l2": "256 MiB buffer written between timed steps (untimed) -> index and queries start cold",
@@ -422,8 +422,8 @@ def run_ours(args):
         "roofline": {
             "bound": "hbm", "kernel": "k_find_interval", "achieved": achieved, "peak": peak, "unit": "GB/s",
             "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
-            "algorithmic_bytes": "executed getOcc calls x 64 B (header sector + sub-block sector of the 128-B block); "
-                                 "lower/upper of a step often share a sub-block",
+            "algorithmic_bytes": "executed getOcc calls x 64 B (one 64-byte block: header + 36 run bytes); "
+                                 "lower/upper of a step often share a block",
             "getocc_per_launch": ranks_per_launch,
             "achieved_at_128B_per_getocc": 2 * achieved, "frac_at_128B_per_getocc": 2 * achieved / peak,
             "random_access_peak": random_gbs,

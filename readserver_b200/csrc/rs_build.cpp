@@ -69,19 +69,6 @@ int rs_build_host_index(const uint8_t* runs, uint64_t R, uint64_t num_strings, u
   uint64_t bi = 0;
   uint32_t fill = RS_PAYLOAD; /* forces a new block at run 0 */
   rs_block* cur = nullptr;
-  uint64_t in_blk[RS_NSYM] = {0, 0, 0, 0, 0}, in_tot = 0; /* counts inside the current block */
-  auto rec_now = [&]() -> uint64_t {
-    return in_blk[1] | (in_blk[2] << RS_REC_BITS) | (in_blk[3] << (2 * RS_REC_BITS)) | (in_blk[4] << (3 * RS_REC_BITS)) |
-           (in_tot << RS_REC_SYM_SHIFT);
-  };
-  /* sub-blocks a short last block leaves empty repeat the block's totals (rs_ops.h relies on it) */
-  auto close_block = [&]() {
-    if (!cur) return;
-    const uint32_t used = (fill + RS_SUB_RUNS - 1) / RS_SUB_RUNS;
-    for (uint32_t j = used; j < RS_SUBS; ++j) cur->sub[j].rec = rec_now();
-    if (used < 2) cur->bounds = (uint32_t)in_tot | ((uint32_t)in_tot << RS_REC_BITS);
-    else if (used < 3) cur->bounds |= (uint32_t)in_tot << RS_REC_BITS;
-  };
   for (uint64_t i = 0; i < R; ++i) {
     const uint32_t sym = runs[i] >> 5, len = runs[i] & 31u;
     if (sym > 4 || len == 0) return RS_ERR_RUNBYTE;
@@ -97,7 +84,6 @@ int rs_build_host_index(const uint8_t* runs, uint64_t R, uint64_t num_strings, u
       snaps.push_back(s);
     }
     if (fill == RS_PAYLOAD) {
-      close_block();
       cur = &out.blocks[bi++];
       memset(cur, 0, sizeof(*cur));
       cur->start = tot;
@@ -107,24 +93,11 @@ int rs_build_host_index(const uint8_t* runs, uint64_t R, uint64_t num_strings, u
         cur->cnt_hi |= (uint32_t)(cnt[c + 1] >> 32) << (8 * c);
       }
       fill = 0;
-      in_tot = 0;
-      for (int c = 0; c < RS_NSYM; ++c) in_blk[c] = 0;
     }
-    if (fill % RS_SUB_RUNS == 0) {
-      const uint32_t j = fill / RS_SUB_RUNS;
-      cur->sub[j].rec = rec_now();
-      if (j == 1) cur->bounds = (uint32_t)in_tot;
-      if (j == 2) cur->bounds |= (uint32_t)in_tot << RS_REC_BITS;
-    }
-    if (fill >= RS_PAYLOAD) return RS_ERR_ARG; /* unreachable */
-    cur->sub[fill / RS_SUB_RUNS].runs[fill % RS_SUB_RUNS] = runs[i];
-    ++fill;
-    in_blk[sym] += len;
-    in_tot += len;
+    cur->runs[fill++] = runs[i];
     cnt[sym] += len;
     tot += len;
   }
-  close_block();
   if (tot != num_symbols) return RS_ERR_ARG;
   out.n = tot;
   memcpy(out.tot, cnt, sizeof(cnt));
@@ -185,7 +158,7 @@ int rs_build_host_index(const uint8_t* runs, uint64_t R, uint64_t num_strings, u
       int nb = 0;
       uint64_t q = b + 1;
       for (; q < nblocks && out.blocks[q].start < p + RS_SLOT_SIZE; ++q) {
-        if (nb < 3) e |= (out.blocks[q].start - p) << (32 + 10 * nb);
+        if (nb < 3) e |= (out.blocks[q].start - p) << (32 + RS_SLOT_SHIFT * nb);
         ++nb;
       }
       if (nb > 3) e |= RS_DIR_MORE;

@@ -102,11 +102,11 @@ __global__ void __launch_bounds__(RS_THREADS) k_pack_kmers(const uint8_t* __rest
   packed[q0 + threadIdx.x] = v | ((uint64_t)(bad != 0) << 63);
 }
 
-/* K1.  Each thread owns one query at a time and all lanes of a warp perform one sub-block scan per
+/* K1.  Each thread owns one query at a time and all lanes of a warp perform one block scan per
  * loop trip, whatever query they are on: a thread whose query ends (all characters consumed, or the
  * interval went empty: query.cpp:35-37) picks up its next query on the following trip, so lanes never
  * idle behind a longer neighbour.  A step (updateInterval, query.cpp:11-15) whose two positions share
- * a sub-block takes one trip; otherwise the second position is scanned on the next trip.
+ * a block takes one trip; otherwise the second position is scanned on the next trip.
  *   mode 0: write lower/upper.   mode 1: write counts (count_reads, service.cpp:279-315), strand as given. */
 /* Where a finished query's answer goes.  mode 0: lower/upper; mode 1: count into lower[];
  * mode 2 (packed queries only): the count is added into the accumulation buffer of the rank that
@@ -253,7 +253,7 @@ __global__ void __launch_bounds__(RS_THREADS, RS_K1_BLOCKS)
       if (p1 >= ix.n) p1 = ix.n - 1;
       if (p2 >= ix.n) p2 = ix.n - 1;
       uint64_t pos, blk;
-      bool try2 = false;
+      bool two = false;
       const bool was_pending = pending;
       if (!pending) {
         if (PACKED) c = (uint32_t)((pk >> (2 * (len - 1 - (uint32_t)j))) & 3u) + 1u;
@@ -261,7 +261,7 @@ __global__ void __launch_bounds__(RS_THREADS, RS_K1_BLOCKS)
         else c = rc ? 5u - rs_code(w[len - 1 - j]) : rs_code(w[j]);
         const uint64_t b1 = rs_find_block(ix, p1);
         b2 = (uint32_t)rs_find_block(ix, p2);
-        try2 = (b1 == b2) && p2 >= p1;
+        two = (b1 == b2) && p2 >= p1;
         pos = p1;
         blk = b1;
         ++nsteps;
@@ -270,8 +270,7 @@ __global__ void __launch_bounds__(RS_THREADS, RS_K1_BLOCKS)
         blk = b2;
       }
       uint64_t x1, x2;
-      bool did2;
-      rs_scan2(ix, c, blk, pos, p2, try2, &x1, &x2, &did2);
+      rs_scan2(ix, c, blk, pos, p2, two, &x1, &x2);
       uint64_t r2 = 0;
       if (was_pending) {
         r2 = none2 ? 0 : x1;
@@ -279,7 +278,7 @@ __global__ void __launch_bounds__(RS_THREADS, RS_K1_BLOCKS)
       } else {
         r1 = none1 ? 0 : x1;
         r2 = none2 ? 0 : x2;
-        pending = !did2;
+        pending = !two;
       }
       if (!pending) {
         const uint64_t pb = ix.pc[c];

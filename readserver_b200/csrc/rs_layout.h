@@ -2,51 +2,41 @@
  *
  * Replaces the reference's RLVector + multi-level BP-tree (include/bwt/rlunit.h:8-89,
  * include/bwt/BPTree.h:20-206, BPNodes.h:34-241, built by src/bwt/rlebwt.cpp:34-148) with a flat
- * array of 128-byte blocks -- one L2 line, four 32-byte DRAM sectors -- and a position directory
- * that resolves "symbol position -> block" in one 8-byte read.  A rank touches TWO sectors of its
- * block: the header sector and the sector of the sub-block the position falls in.
+ * array of 64-byte blocks -- two 32-byte DRAM sectors, half an L2 line, read with four independent
+ * 128-bit loads -- and a position directory that resolves "symbol position -> block" in one 8-byte
+ * read.  A rank is two dependent memory accesses: directory entry, then block.
  *
- *   block (128 B, 128-B aligned)
- *     sector 0 (header)
- *       +0   u64 start          symbols before this block
- *       +8   u32 cnt_lo[4]      low 32 bits of the occurrences of A,C,G,T before this block
- *       +24  u32 cnt_hi         byte c-1 = bits 32..39 of that count ('$' = start - sum)
- *       +28  u32 bounds         bits 0..10 symbols held by sub-block 0, bits 11..21 by sub-blocks 0..1
- *     sectors 1..3 (sub-blocks 0..2), each
- *       +0   u64 rec            occurrences of A,C,G,T inside this block before the sub-block
- *                               (4 x 11 bits), bits 44..55 symbols inside this block before it
- *       +8   u8  runs[24]       SGA run bytes  sym<<5 | len  (rlunit.h:8-16), 0x00 = padding
+ *   block (64 B, 64-B aligned)
+ *     +0   u64 start          symbols before this block
+ *     +8   u32 cnt_lo[4]      low 32 bits of the occurrences of A,C,G,T before this block
+ *     +24  u32 cnt_hi         byte c-1 = bits 32..39 of that count ('$' = start - sum)
+ *     +28  u8  runs[36]       SGA run bytes  sym<<5 | len  (rlunit.h:8-16), 0x00 = padding
  *
  *   position directory: one u64 per 2^RS_SLOT_SHIFT symbols
  *     bits  0..31  index of the block holding the slot's first symbol
- *     bits 32..41  b1  offset inside the slot at which block +1 starts (0 = no such boundary)
- *     bits 42..51  b2  ... block +2
- *     bits 52..61  b3  ... block +3
+ *     bits 32..40  b1  offset inside the slot at which block +1 starts (0 = no such boundary)
+ *     bits 41..49  b2  ... block +2
+ *     bits 50..58  b3  ... block +3
  *     bit  62      more than three block boundaries fall inside the slot (then the start fields of
- *                  the following headers are compared until the block is found)
+ *                  the following blocks are compared until the block is found)
  *
  *   select directory (per symbol c): one u32 per 2^s occurrences of c, s = sel_shift[c] chosen so
  *     that a directory slot spans about two blocks (a sparse symbol such as '$' gets a small s)
  *     entry k = index of the block holding the ((k << s) + 1)-th occurrence of c,
  *     i.e. the block with cnt_before[c] <= k << s < cnt_before_next[c].
  *
- * Limits of one shard: 2^32 blocks (512 GB), 2^40 occurrences per symbol.
+ * Limits of one shard: 2^32 blocks (256 GB), 2^40 occurrences per symbol.
  */
 #ifndef RS_LAYOUT_H
 #define RS_LAYOUT_H
 
 #include <stdint.h>
 
-#define RS_BLOCK_BYTES 128
-#define RS_HDR_BYTES 32
-#define RS_SUBS 3
-#define RS_SUB_RUNS 24
-#define RS_SUB_WORDS (RS_SUB_RUNS / 4)
-#define RS_PAYLOAD (RS_SUBS * RS_SUB_RUNS) /* 72 runs per block */
-#define RS_REC_BITS 11
-#define RS_REC_MASK 0x7FFu
-#define RS_REC_SYM_SHIFT 44
-#define RS_SLOT_SHIFT 10
+#define RS_BLOCK_BYTES 64
+#define RS_HDR_BYTES 28
+#define RS_PAYLOAD 36 /* runs per block */
+#define RS_BLOCK_WORDS (RS_PAYLOAD / 4)
+#define RS_SLOT_SHIFT 9
 #define RS_SLOT_SIZE (1u << RS_SLOT_SHIFT)
 #define RS_SLOT_MASK (RS_SLOT_SIZE - 1u)
 #define RS_DIR_MORE (1ull << 62)
@@ -54,17 +44,11 @@
 #define RS_NSYM 5
 #define RS_NO_ROW 0xFFFFFFFFFFFFFFFFull
 
-typedef struct rs_subblock {
-  uint64_t rec;
-  uint8_t runs[RS_SUB_RUNS];
-} rs_subblock;
-
 typedef struct rs_block {
   uint64_t start;
   uint32_t cnt_lo[4];
   uint32_t cnt_hi;
-  uint32_t bounds;
-  rs_subblock sub[RS_SUBS];
+  uint8_t runs[RS_PAYLOAD];
 } rs_block;
 
 /* Everything a kernel needs, passed by value as a __grid_constant__ parameter. */

@@ -1,9 +1,8 @@
-/* Rank / access / select over the 128-byte blocks of rs_layout.h, one thread per query or walker.
+/* Rank / access / select over the 64-byte blocks of rs_layout.h, one thread per query or walker.
  *
- * Every operation resolves its block through the position (or select) directory, reads the 32-byte
- * header sector, picks the sub-block from the header's bounds and reads that one 32-byte sector:
- * four 128-bit loads and a 6-word SWAR scan (rs_swar.h) per rank.  The header load carries an
- * L2::128B prefetch hint, so that the sub-block sector is an L2 hit when the line came from DRAM.
+ * Every operation resolves its block through the position (or select) directory and reads the whole
+ * block with four independent 128-bit loads: header (start + counters) and 9 words of run bytes,
+ * scanned with 32-bit SWAR (rs_swar.h).  Two dependent memory accesses and two DRAM sectors per rank.
  *
  * The same source compiles for the sm_100a kernels and for the host: tests/emul replays it on host
  * memory (pointers of rs_index_dev into the host builder's arrays) against the oracle at every
@@ -34,19 +33,6 @@ RS_HD rs_u4 rs_ld128(const void* p) {
   rs_u4 v;
   memcpy(&v, p, 16);
   return v;
-#endif
-}
-
-/* the same with a hint to bring the whole 128-byte line into L2 on a miss */
-RS_HD rs_u4 rs_ld128_line(const void* p) {
-#if defined(__CUDA_ARCH__) && !defined(RS_NO_LINE_PREFETCH)
-  rs_u4 v;
-  asm volatile("ld.global.nc.L2::128B.v4.u32 {%0,%1,%2,%3}, [%4];"
-               : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w)
-               : "l"(__cvta_generic_to_global(p)));
-  return v;
-#else
-  return rs_ld128(p);
 #endif
 }
 
@@ -81,7 +67,8 @@ RS_HD uint64_t rs_find_block(const rs_index_dev& ix, uint64_t pos) {
   const uint64_t e = rs_ld64(ix.dir + (pos >> RS_SLOT_SHIFT));
   const uint32_t o = (uint32_t)pos & RS_SLOT_MASK;
   const uint32_t hi = (uint32_t)(e >> 32);
-  const uint32_t b1 = hi & RS_SLOT_MASK, b2 = (hi >> 10) & RS_SLOT_MASK, b3 = (hi >> 20) & RS_SLOT_MASK;
+  const uint32_t b1 = hi & RS_SLOT_MASK, b2 = (hi >> RS_SLOT_SHIFT) & RS_SLOT_MASK,
+                 b3 = (hi >> (2 * RS_SLOT_SHIFT)) & RS_SLOT_MASK;
   const uint32_t add = (uint32_t)(b1 != 0 && o >= b1) + (uint32_t)(b2 != 0 && o >= b2) + (uint32_t)(b3 != 0 && o >= b3);
   uint64_t b = (uint64_t)(uint32_t)e + add;
   if ((hi >> 30) != 0 && add == 3) {
@@ -91,36 +78,38 @@ RS_HD uint64_t rs_find_block(const rs_index_dev& ix, uint64_t pos) {
   return b;
 }
 
-/* header sector of a block */
-struct rs_hdr {
+/* a whole block: header fields and the 9 payload words */
+struct rs_blk {
   uint64_t start;
   uint32_t cl[4];
   uint32_t ch;
-  uint32_t bounds;
+  uint32_t w[RS_BLOCK_WORDS];
 };
 
-RS_HD rs_hdr rs_load_hdr(const rs_index_dev& ix, uint64_t b) {
+RS_HD rs_blk rs_load_block(const rs_index_dev& ix, uint64_t b) {
   const uint8_t* p = rs_block_ptr(ix, b);
-  const rs_u4 a = rs_ld128_line(p), c = rs_ld128(p + 16);
-  rs_hdr h;
-  h.start = ((uint64_t)a.y << 32) | a.x;
-  h.cl[0] = a.z;
-  h.cl[1] = a.w;
-  h.cl[2] = c.x;
-  h.cl[3] = c.y;
-  h.ch = c.z;
-  h.bounds = c.w;
-  return h;
-}
-
-/* sub-block (0..2) holding the off-th symbol of the block, off 1-based */
-RS_HD uint32_t rs_hdr_sub(const rs_hdr& h, uint32_t off) {
-  const uint32_t s1 = h.bounds & RS_REC_MASK, s2 = (h.bounds >> RS_REC_BITS) & RS_REC_MASK;
-  return (uint32_t)(off > s1) + (uint32_t)(off > s2);
+  const rs_u4 v0 = rs_ld128(p), v1 = rs_ld128(p + 16), v2 = rs_ld128(p + 32), v3 = rs_ld128(p + 48);
+  rs_blk k;
+  k.start = ((uint64_t)v0.y << 32) | v0.x;
+  k.cl[0] = v0.z;
+  k.cl[1] = v0.w;
+  k.cl[2] = v1.x;
+  k.cl[3] = v1.y;
+  k.ch = v1.z;
+  k.w[0] = v1.w;
+  k.w[1] = v2.x;
+  k.w[2] = v2.y;
+  k.w[3] = v2.z;
+  k.w[4] = v2.w;
+  k.w[5] = v3.x;
+  k.w[6] = v3.y;
+  k.w[7] = v3.z;
+  k.w[8] = v3.w;
+  return k;
 }
 
 /* occurrences of c (0..4) before the block */
-RS_HD uint64_t rs_hdr_count(const rs_hdr& h, uint32_t c) {
+RS_HD uint64_t rs_blk_count(const rs_blk& h, uint32_t c) {
   if (c != 0) {
     const uint32_t k = c - 1;
     const uint32_t lo = k == 0 ? h.cl[0] : k == 1 ? h.cl[1] : k == 2 ? h.cl[2] : h.cl[3];
@@ -131,45 +120,26 @@ RS_HD uint64_t rs_hdr_count(const rs_hdr& h, uint32_t c) {
   return h.start - (lo + (hi << 32));
 }
 
-/* one sub-block sector */
-struct rs_sub {
-  uint64_t rec;
-  uint32_t w[RS_SUB_WORDS];
-};
-
-RS_HD rs_sub rs_load_sub(const rs_index_dev& ix, uint64_t b, uint32_t j) {
-  const uint8_t* p = rs_block_ptr(ix, b) + RS_HDR_BYTES + j * 32u;
-  const rs_u4 a = rs_ld128(p), c = rs_ld128(p + 16);
-  rs_sub s;
-  s.rec = ((uint64_t)a.y << 32) | a.x;
-  s.w[0] = a.z;
-  s.w[1] = a.w;
-  s.w[2] = c.x;
-  s.w[3] = c.y;
-  s.w[4] = c.z;
-  s.w[5] = c.w;
-  return s;
-}
-
-RS_HD uint32_t rs_rec_sym(uint64_t rec) { return (uint32_t)(rec >> RS_REC_SYM_SHIFT) & 0xFFFu; }
-
-/* occurrences of c inside the block before the sub-block whose record is rec */
-RS_HD uint32_t rs_rec_count(uint64_t rec, uint32_t c) {
-  if (c != 0) return (uint32_t)(rec >> (RS_REC_BITS * (c - 1))) & RS_REC_MASK;
-  const uint32_t a = (uint32_t)rec & RS_REC_MASK, cc = (uint32_t)(rec >> 11) & RS_REC_MASK;
-  const uint32_t g = (uint32_t)(rec >> 22) & RS_REC_MASK, t = (uint32_t)(rec >> 33) & RS_REC_MASK;
-  return rs_rec_sym(rec) - (a + cc + g + t);
+/* One block scan for up to two targets: rank of c at p1 and, when two (p2 >= p1 lies in the same block),
+ * at p2 as well.  Building block of K1's one-scan-per-trip loop. */
+RS_HD void rs_scan2(const rs_index_dev& ix, uint32_t c, uint64_t b, uint64_t p1, uint64_t p2, bool two, uint64_t* x1,
+                    uint64_t* x2) {
+  const rs_blk k = rs_load_block(ix, b);
+  const uint32_t off = (uint32_t)(p1 - k.start) + 1u;
+  uint32_t a1, a2;
+  rs_words_rank<RS_BLOCK_WORDS, true>(k.w, c, (int32_t)off, two ? (int32_t)(off + (uint32_t)(p2 - p1)) : -1, &a1, &a2);
+  const uint64_t before = rs_blk_count(k, c);
+  *x1 = before + a1;
+  *x2 = before + a2;
 }
 
 /* True rank: occurrences of c in BWT[0..pos], pos < n. */
 RS_HD uint64_t rs_rank(const rs_index_dev& ix, uint32_t c, uint64_t pos) {
   const uint64_t b = rs_find_block(ix, pos);
-  const rs_hdr h = rs_load_hdr(ix, b);
-  const uint32_t off = (uint32_t)(pos - h.start) + 1u;
-  const rs_sub s = rs_load_sub(ix, b, rs_hdr_sub(h, off));
+  const rs_blk k = rs_load_block(ix, b);
   uint32_t a, unused;
-  rs_words_rank<RS_SUB_WORDS, false>(s.w, c, (int32_t)(off - rs_rec_sym(s.rec)), 0, &a, &unused);
-  return rs_hdr_count(h, c) + rs_rec_count(s.rec, c) + a;
+  rs_words_rank<RS_BLOCK_WORDS, false>(k.w, c, (int32_t)((uint32_t)(pos - k.start) + 1u), 0, &a, &unused);
+  return rs_blk_count(k, c) + a;
 }
 
 /* getOcc(c, i) with the reference's semantics (i = 2^64-1 -> 0; tail clamp), rlebwt.cpp:268-301. */
@@ -180,25 +150,6 @@ RS_HD uint64_t rs_occ(const rs_index_dev& ix, uint32_t c, uint64_t i) {
   return rs_rank(ix, c, pos);
 }
 
-/* One block scan for up to two targets: rank of c at p1 and, when try2 and p2 (>= p1) falls in the
- * same sub-block, at p2 as well (*did2).  Building block of K1's one-scan-per-trip loop. */
-RS_HD void rs_scan2(const rs_index_dev& ix, uint32_t c, uint64_t b, uint64_t p1, uint64_t p2, bool try2, uint64_t* x1,
-                    uint64_t* x2, bool* did2) {
-  const rs_hdr h = rs_load_hdr(ix, b);
-  const uint32_t off = (uint32_t)(p1 - h.start) + 1u;
-  const uint32_t j = rs_hdr_sub(h, off);
-  const uint32_t off2 = off + (uint32_t)(p2 - p1);
-  const bool two = try2 && rs_hdr_sub(h, off2) == j;
-  const rs_sub s = rs_load_sub(ix, b, j);
-  const uint32_t sb = rs_rec_sym(s.rec);
-  uint32_t a1, a2;
-  rs_words_rank<RS_SUB_WORDS, true>(s.w, c, (int32_t)(off - sb), two ? (int32_t)(off2 - sb) : -1, &a1, &a2);
-  const uint64_t before = rs_hdr_count(h, c) + rs_rec_count(s.rec, c);
-  *x1 = before + a1;
-  *x2 = before + a2;
-  *did2 = two;
-}
-
 /* updateInterval's two ranks (src/bwt/query.cpp:11-15): getOcc(c, i1) and getOcc(c, i2). */
 RS_HD void rs_occ2(const rs_index_dev& ix, uint32_t c, uint64_t i1, uint64_t i2, uint64_t* r1, uint64_t* r2) {
   const bool none1 = (i1 == ~0ull), none2 = (i2 == ~0ull);
@@ -207,13 +158,12 @@ RS_HD void rs_occ2(const rs_index_dev& ix, uint32_t c, uint64_t i1, uint64_t i2,
   if (p1 >= ix.n) p1 = ix.n - 1;
   if (p2 >= ix.n) p2 = ix.n - 1;
   const uint64_t b1 = rs_find_block(ix, p1), b2 = rs_find_block(ix, p2);
+  const bool two = (b1 == b2) && p2 >= p1;
   uint64_t x1, x2;
-  bool did2;
-  rs_scan2(ix, c, b1, p1, p2, b1 == b2 && p2 >= p1, &x1, &x2, &did2);
-  if (!did2) {
+  rs_scan2(ix, c, b1, p1, p2, two, &x1, &x2);
+  if (!two) {
     uint64_t unused;
-    bool u2;
-    rs_scan2(ix, c, b2, p2, p2, false, &x2, &unused, &u2);
+    rs_scan2(ix, c, b2, p2, p2, false, &x2, &unused);
   }
   *r1 = none1 ? 0 : x1;
   *r2 = none2 ? 0 : x2;
@@ -222,16 +172,14 @@ RS_HD void rs_occ2(const rs_index_dev& ix, uint32_t c, uint64_t i1, uint64_t i2,
 /* Symbol at pos (< n) and the rank of that symbol at pos, from one scan. */
 RS_HD uint32_t rs_symbol_rank(const rs_index_dev& ix, uint64_t pos, uint64_t* rank) {
   const uint64_t b = rs_find_block(ix, pos);
-  const rs_hdr h = rs_load_hdr(ix, b);
-  const uint32_t off = (uint32_t)(pos - h.start) + 1u;
-  const rs_sub s = rs_load_sub(ix, b, rs_hdr_sub(h, off));
-  const int32_t t = (int32_t)(off - rs_rec_sym(s.rec));
-  uint32_t sym = rs_words_symbol<RS_SUB_WORDS>(s.w, t);
+  const rs_blk k = rs_load_block(ix, b);
+  const int32_t t = (int32_t)((uint32_t)(pos - k.start) + 1u);
+  uint32_t sym = rs_words_symbol<RS_BLOCK_WORDS>(k.w, t);
   if (sym > 4u) sym = 0u; /* unreachable for a well-formed index; keeps pc[] in bounds */
   if (rank) {
     uint32_t a, unused;
-    rs_words_rank<RS_SUB_WORDS, false>(s.w, sym, t, 0, &a, &unused);
-    *rank = rs_hdr_count(h, sym) + rs_rec_count(s.rec, sym) + a;
+    rs_words_rank<RS_BLOCK_WORDS, false>(k.w, sym, t, 0, &a, &unused);
+    *rank = rs_blk_count(k, sym) + a;
   }
   return sym;
 }
@@ -260,7 +208,7 @@ RS_HD uint32_t rs_lf_step(const rs_index_dev& ix, uint64_t idx, uint64_t* next) 
   return sym;
 }
 
-/* occurrences of c before block b, from its header sector */
+/* occurrences of c before block b, from its header */
 RS_HD uint64_t rs_block_count_before(const rs_index_dev& ix, uint64_t b, uint32_t c) {
   const uint8_t* p = rs_block_ptr(ix, b);
   if (c != 0) {
@@ -268,7 +216,10 @@ RS_HD uint64_t rs_block_count_before(const rs_index_dev& ix, uint64_t b, uint32_
     const uint32_t ch = rs_ld32(reinterpret_cast<const uint32_t*>(p + 24));
     return ((uint64_t)((ch >> (8 * (c - 1))) & 0xFFu) << 32) | lo;
   }
-  return rs_hdr_count(rs_load_hdr(ix, b), 0);
+  const rs_u4 v0 = rs_ld128(p), v1 = rs_ld128(p + 16);
+  const uint64_t lo = (uint64_t)v0.z + v0.w + v1.x + v1.y;
+  const uint64_t hi = (v1.z & 0xFFu) + ((v1.z >> 8) & 0xFFu) + ((v1.z >> 16) & 0xFFu) + (v1.z >> 24);
+  return (((uint64_t)v0.y << 32) | v0.x) - (lo + (hi << 32));
 }
 
 /* getOccAt(c, r) (rlebwt.cpp:233-266): position of the r-th occurrence of c, 1 <= r <= tot[c].
@@ -279,16 +230,10 @@ RS_HD uint64_t rs_occ_at(const rs_index_dev& ix, uint32_t c, uint64_t r) {
   uint64_t b = rs_ld32(ix.sel[c] + ((r - 1) >> ix.sel_shift[c]));
   /* skip blocks that end before the r-th occurrence: their successor's header says so */
   while (b + 1 < ix.nblocks && rs_block_count_before(ix, b + 1, c) < r) ++b;
-  const rs_hdr h = rs_load_hdr(ix, b);
-  const uint32_t want = (uint32_t)(r - rs_hdr_count(h, c));
-  const uint8_t* p = rs_block_ptr(ix, b) + RS_HDR_BYTES;
-  const uint32_t c1 = rs_rec_count(rs_ld64(reinterpret_cast<const uint64_t*>(p + 32)), c);
-  const uint32_t c2 = rs_rec_count(rs_ld64(reinterpret_cast<const uint64_t*>(p + 64)), c);
-  /* empty trailing sub-blocks of the last block repeat the block's totals, so want <= c1 stops early */
-  const uint32_t j = (uint32_t)(want > c1) + (uint32_t)(want > c2);
-  const rs_sub s = rs_load_sub(ix, b, j);
-  const uint32_t q = rs_words_select<RS_SUB_WORDS>(s.w, c, (int32_t)(want - rs_rec_count(s.rec, c)));
-  return h.start + rs_rec_sym(s.rec) + q - 1;
+  const rs_blk k = rs_load_block(ix, b);
+  const uint32_t want = (uint32_t)(r - rs_blk_count(k, c));
+  const uint32_t q = rs_words_select<RS_BLOCK_WORDS>(k.w, c, (int32_t)want);
+  return k.start + q - 1;
 }
 
 /* getF(i) (rlebwt.cpp:307-314) as a symbol code */

@@ -181,10 +181,10 @@ class Emul:
         return lo, up
 
     def blocks(self) -> np.ndarray:
-        """the raw 128-byte blocks as a [nblocks, 128] uint8 array (a copy)"""
+        """the raw 64-byte blocks as a [nblocks, 64] uint8 array (a copy)"""
         p = self.lib().emul_blocks(self._h)
-        buf = (C.c_uint8 * (self.nblocks * 128)).from_address(p)
-        return np.frombuffer(buf, dtype=np.uint8).reshape(self.nblocks, 128).copy()
+        buf = (C.c_uint8 * (self.nblocks * 64)).from_address(p)
+        return np.frombuffer(buf, dtype=np.uint8).reshape(self.nblocks, 64).copy()
 
     def postfix_walk(self, rows, max_steps=1024):
         rows = np.ascontiguousarray(rows, dtype=np.uint64)

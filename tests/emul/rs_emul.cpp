@@ -66,7 +66,7 @@ void emul_info(void* p, uint64_t* out) {
   for (int c = 0; c < 5; ++c) { out[7 + c] = h.pc[c]; out[12 + c] = h.tot[c]; out[17 + c] = h.init_occ[c]; }
 }
 
-/* raw 128-byte blocks, for the layout tests */
+/* raw 64-byte blocks, for the layout tests */
 const void* emul_blocks(void* p) { return ((Emul*)p)->h.blocks.data(); }
 
 void emul_occ_batch(void* p, const uint8_t* b, const uint64_t* idx, uint64_t n, uint64_t* out) {

@@ -264,8 +264,8 @@ def test_degenerate_blocks_on_gpu(engine):
     shapes = [((rng.integers(0, 5, 5000).astype(np.uint8) << 5) | 1),
               ((rng.integers(1, 5, 3000).astype(np.uint8) << 5) | 31),
               np.array([(2 << 5) | 7], dtype=np.uint8),
-              ((rng.integers(0, 5, 24).astype(np.uint8) << 5) | rng.integers(1, 32, 24).astype(np.uint8)),
-              ((rng.integers(0, 5, 72).astype(np.uint8) << 5) | rng.integers(1, 32, 72).astype(np.uint8)),
+              ((rng.integers(0, 5, 36).astype(np.uint8) << 5) | rng.integers(1, 32, 36).astype(np.uint8)),
+              ((rng.integers(0, 5, 37).astype(np.uint8) << 5) | rng.integers(1, 32, 37).astype(np.uint8)),
               ((rng.integers(0, 5, 97).astype(np.uint8) << 5) | rng.integers(1, 32, 97).astype(np.uint8)),
               np.concatenate([(rng.integers(0, 5, 4000).astype(np.uint8) << 5) | 1,
                               (rng.integers(0, 5, 70000).astype(np.uint8) << 5) | rng.integers(1, 4, 70000).astype(np.uint8)])]

@@ -50,13 +50,13 @@ def test_find_interval_and_walk_match_oracle(name, datasets):
 
 
 def test_block_structure(datasets):
-    """The 128-byte block as rs_layout.h documents it: header sector + three sub-block sectors whose
-    records and bounds agree with a plain decode of the run bytes."""
+    """The 64-byte block as rs_layout.h documents it: start, 40-bit counters split into low words and
+    high bytes, 36 run bytes (zero-padded in the last block), against a plain decode of the run bytes."""
     case = datasets.case("small")
     E = common.Emul(case)
     blocks = E.blocks()
     runs = case.runs
-    assert E.nblocks == (runs.size + 71) // 72
+    assert E.nblocks == (runs.size + 35) // 36
     sym, ln = (runs >> 5).astype(np.int64), (runs & 31).astype(np.int64)
     csum = np.zeros((5, runs.size + 1), dtype=np.int64)
     for c in range(5):
@@ -64,23 +64,13 @@ def test_block_structure(datasets):
     tot = np.concatenate([[0], np.cumsum(ln)])
     for b in (0, 1, E.nblocks // 2, E.nblocks - 1):
         raw = blocks[b]
-        r0 = b * 72
+        r0 = b * 36
         assert int(raw[0:8].view(np.uint64)[0]) == tot[r0]
         lo, hi = raw[8:24].view(np.uint32), raw[24:28]
         for c in range(4):
             assert int(lo[c]) + (int(hi[c]) << 32) == csum[c + 1, r0]
-        bounds = int(raw[28:32].view(np.uint32)[0])
-        for j in range(3):
-            sec = raw[32 + 32 * j: 64 + 32 * j]
-            rec = int(sec[0:8].view(np.uint64)[0])
-            rj = min(r0 + 24 * j, runs.size)
-            for c in range(4):
-                assert (rec >> (11 * c)) & 0x7FF == csum[c + 1, rj] - csum[c + 1, r0]
-            assert (rec >> 44) & 0xFFF == tot[rj] - tot[r0]
-            body = runs[rj: min(rj + 24, runs.size)]
-            assert np.array_equal(sec[8: 8 + body.size], body) and not sec[8 + body.size:].any()
-            if j:
-                assert (bounds >> (11 * (j - 1))) & 0x7FF == tot[rj] - tot[r0]
+        body = runs[r0: min(r0 + 36, runs.size)]
+        assert np.array_equal(raw[28: 28 + body.size], body) and not raw[28 + body.size:].any()
 
 
 def test_without_tail_emulation_rank_is_exact(datasets):
@@ -134,11 +124,10 @@ def test_ragged_and_degenerate_blocks():
         "all_len31": ((rng.integers(1, 5, 3000).astype(np.uint8) << 5) | 31),
         "single_run": np.array([(2 << 5) | 7], dtype=np.uint8),
         "dollars": np.full(200, (0 << 5) | 31, dtype=np.uint8),
+        "exact_36": ((rng.integers(0, 5, 36).astype(np.uint8) << 5) | rng.integers(1, 32, 36).astype(np.uint8)),
         "exact_72": ((rng.integers(0, 5, 72).astype(np.uint8) << 5) | rng.integers(1, 32, 72).astype(np.uint8)),
-        "exact_144": ((rng.integers(0, 5, 144).astype(np.uint8) << 5) | rng.integers(1, 32, 144).astype(np.uint8)),
-        "one_sub": ((rng.integers(0, 5, 24).astype(np.uint8) << 5) | rng.integers(1, 32, 24).astype(np.uint8)),
-        "sub_plus_1": ((rng.integers(0, 5, 97).astype(np.uint8) << 5) | rng.integers(1, 32, 97).astype(np.uint8)),
-        "two_subs": ((rng.integers(0, 5, 72 + 48).astype(np.uint8) << 5) | rng.integers(1, 32, 120).astype(np.uint8)),
+        "block_plus_1": ((rng.integers(0, 5, 37).astype(np.uint8) << 5) | rng.integers(1, 32, 37).astype(np.uint8)),
+        "short_tail": ((rng.integers(0, 5, 97).astype(np.uint8) << 5) | rng.integers(1, 32, 97).astype(np.uint8)),
         "mixed": np.concatenate([(rng.integers(0, 5, 4000).astype(np.uint8) << 5) | 1,
                                  (rng.integers(0, 5, 4000).astype(np.uint8) << 5) | 31,
                                  (rng.integers(0, 5, 70000).astype(np.uint8) << 5) | rng.integers(1, 4, 70000).astype(np.uint8)]),
