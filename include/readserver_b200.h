@@ -84,6 +84,9 @@ int rs_index_read_stats(rs_index* ix, uint64_t* interval_steps, uint64_t* walk_s
 /* Measurement aid, no reference counterpart: achieved GB/s of random, 128-byte-aligned, 128-byte
  * loads over a buffer_bytes buffer on `device` -- the random-access roofline of this path. */
 int rs_measure_random_access(int device, uint64_t buffer_bytes, uint64_t lines_to_read, double* gbytes_per_s);
+/* the same for random aligned loads of granule_bytes (32, 64 or 128) each */
+int rs_measure_random_access_granule(int device, uint64_t buffer_bytes, uint64_t lines_to_read, int granule_bytes,
+                                     double* gbytes_per_s);
 const char* rs_last_error(void);
 /* pinned host memory for the host-pointer calls (optional; any host memory is accepted) */
 int rs_host_alloc(void** p, size_t bytes);

@@ -61,6 +61,7 @@ def lib() -> C.CDLL:
         "rs_index_enable_stats": (i32, [vp, i32]),
         "rs_index_read_stats": (i32, [vp, C.POINTER(u64), C.POINTER(u64), i32]),
         "rs_measure_random_access": (i32, [i32, u64, u64, C.POINTER(C.c_double)]),
+        "rs_measure_random_access_granule": (i32, [i32, u64, u64, i32, C.POINTER(C.c_double)]),
         "rs_last_error": (C.c_char_p, []),
         "rs_host_alloc": (i32, [C.POINTER(vp), sz]),
         "rs_host_free": (None, [vp]),
@@ -108,10 +109,10 @@ def _check(rc: int):
         raise RsError(rc, (lib().rs_last_error() or b"").decode("utf-8", "replace"))
 
 
-def measure_random_access(device: int = 0, buffer_bytes: int = 16 << 30, lines: int = 1 << 28) -> float:
-    """GB/s of random 128-byte line loads over a buffer much larger than L2 (roofline denominator)."""
+def measure_random_access(device: int = 0, buffer_bytes: int = 16 << 30, lines: int = 1 << 28, granule: int = 128) -> float:
+    """GB/s of random aligned loads of `granule` bytes over a buffer much larger than L2 (roofline denominator)."""
     v = C.c_double()
-    _check(lib().rs_measure_random_access(device, buffer_bytes, lines, C.byref(v)))
+    _check(lib().rs_measure_random_access_granule(device, buffer_bytes, lines, granule, C.byref(v)))
     return float(v.value)
 
 
