@@ -59,6 +59,7 @@ static int upload(rs_index* ix, const RsHostIndex& h) {
   CU(cudaStreamCreateWithFlags(&ix->stream, cudaStreamNonBlocking));
   CU(cudaStreamCreateWithFlags(&ix->s_h2d, cudaStreamNonBlocking));
   CU(cudaStreamCreateWithFlags(&ix->s_d2h, cudaStreamNonBlocking));
+  CU(cudaStreamCreateWithFlags(&ix->s_k2, cudaStreamNonBlocking));
   for (int i = 0; i < RS_MAX_CHUNKS; ++i) {
     CU(cudaEventCreateWithFlags(&ix->ev_in[i], cudaEventDisableTiming));
     CU(cudaEventCreateWithFlags(&ix->ev_done[i], cudaEventDisableTiming));
@@ -138,6 +139,7 @@ void rs_index_close(rs_index* ix) {
   if (ix->stream) cudaStreamDestroy(ix->stream);
   if (ix->s_h2d) cudaStreamDestroy(ix->s_h2d);
   if (ix->s_d2h) cudaStreamDestroy(ix->s_d2h);
+  if (ix->s_k2) cudaStreamDestroy(ix->s_k2);
   for (int i = 0; i < RS_MAX_CHUNKS; ++i) {
     if (ix->ev_in[i]) cudaEventDestroy(ix->ev_in[i]);
     if (ix->ev_done[i]) cudaEventDestroy(ix->ev_done[i]);
@@ -265,7 +267,16 @@ int rs_get_f_batch(const rs_index* ix, const uint64_t* index, size_t n, char* ou
   return char_like(ix, index, n, out, true);
 }
 
-#define RS_CHUNK_MIN 131072 /* queries per pipelined chunk, at least */
+/* queries per pipelined chunk, at least (RS_B200_CHUNK in the environment overrides) */
+static size_t chunk_min() {
+  static size_t v = 0;
+  if (!v) {
+    const char* e = getenv("RS_B200_CHUNK");
+    const long long x = e ? atoll(e) : 0;
+    v = x >= 1024 ? (size_t)x : 131072;
+  }
+  return v;
+}
 
 static int find_host(const rs_index* ix, const char* text, const uint64_t* offsets, int k, size_t Q, uint64_t* lower,
                      uint64_t* upper, int mode, int strand) {
@@ -282,20 +293,23 @@ static int find_host(const rs_index* ix, const char* text, const uint64_t* offse
   cudaStream_t st = ix->stream;
   uint8_t* d_text = (uint8_t*)ix->s_in.p;
   uint64_t *d_lo = (uint64_t*)ix->s_out.p, *d_up = (uint64_t*)ix->s_out2.p;
-  if (!offsets && Q >= 2 * RS_CHUNK_MIN) {
+  if (!offsets && Q >= 2 * chunk_min()) {
     /* Large fixed-k batch: split into chunks and run copy-in, search and copy-out of successive chunks
-     * on three streams, so the PCIe transfers hide behind the kernels (and vice versa). */
-    size_t nch = Q / RS_CHUNK_MIN;
+     * on separate streams, so the PCIe transfers hide behind the kernels (and vice versa).  Searches
+     * alternate between two streams: the tail of one chunk's kernel (few queries left, SMs draining)
+     * overlaps the head of the next. */
+    size_t nch = Q / chunk_min();
     if (nch > RS_MAX_CHUNKS) nch = RS_MAX_CHUNKS;
     const size_t per = (Q + nch - 1) / nch;
     for (size_t c = 0; c < nch; ++c) {
       const size_t q0 = c * per, qn = (q0 + per <= Q ? per : Q - q0);
       CU(cudaMemcpyAsync(d_text + q0 * k, text + q0 * k, qn * (size_t)k, cudaMemcpyHostToDevice, ix->s_h2d));
       CU(cudaEventRecord(ix->ev_in[c], ix->s_h2d));
-      CU(cudaStreamWaitEvent(st, ix->ev_in[c], 0));
+      cudaStream_t sk = (c & 1) ? ix->s_k2 : st;
+      CU(cudaStreamWaitEvent(sk, ix->ev_in[c], 0));
       CU(rs_launch_find_interval(ix->dev, d_text + q0 * k, nullptr, (uint32_t)k, qn, d_lo + q0, d_up + q0, mode, strand,
-                                 nullptr, st));
-      CU(cudaEventRecord(ix->ev_done[c], st));
+                                 nullptr, sk));
+      CU(cudaEventRecord(ix->ev_done[c], sk));
       CU(cudaStreamWaitEvent(ix->s_d2h, ix->ev_done[c], 0));
       CU(cudaMemcpyAsync(lower + q0, d_lo + q0, qn * 8, cudaMemcpyDeviceToHost, ix->s_d2h));
       if (mode == 0) CU(cudaMemcpyAsync(upper + q0, d_up + q0, qn * 8, cudaMemcpyDeviceToHost, ix->s_d2h));

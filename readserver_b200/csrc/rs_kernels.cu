@@ -11,6 +11,8 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <mutex>
+
 #include "rs_ops.h"
 
 #define RS_FULL 0xFFFFFFFFu
@@ -440,13 +442,28 @@ __global__ void __launch_bounds__(RS_THREADS)
 
 /* ---- launchers ---- */
 static int rs_grid_for(const void* kernel, uint64_t items) {
-  int dev = 0, sms = 0;
-  cudaGetDevice(&dev);
-  cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
-  if (sms <= 0) sms = 148;
+  /* SM count and per-kernel occupancy are looked up once (the GPUs of a box are identical) */
+  static int sms = 0;
+  static struct { const void* k; int per_sm; } cache[16];
+  static int ncache = 0;
+  static std::mutex mu;
   int per_sm = 0;
-  cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, RS_THREADS, 0);
-  if (per_sm < 1) per_sm = 1;
+  {
+    std::lock_guard<std::mutex> lk(mu);
+    if (!sms) {
+      int dev = 0;
+      cudaGetDevice(&dev);
+      cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
+      if (sms <= 0) sms = 148;
+    }
+    for (int i = 0; i < ncache; ++i)
+      if (cache[i].k == kernel) per_sm = cache[i].per_sm;
+    if (!per_sm) {
+      cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, RS_THREADS, 0);
+      if (per_sm < 1) per_sm = 1;
+      if (ncache < 16) cache[ncache++] = {kernel, per_sm};
+    }
+  }
   uint64_t grid = (uint64_t)sms * per_sm; /* one resident wave, a multiple of the SM count */
   const uint64_t need = (items + RS_THREADS - 1) / RS_THREADS;
   if (need < grid) grid = need;
@@ -485,7 +502,7 @@ cudaError_t rs_launch_find_interval(const rs_index_dev& ix, const uint8_t* text,
   if (mode == 2 && (!peers_in || offs || k > RS_PACK_MAX_K)) return cudaErrorInvalidValue;
   const bool ftab = ix.ftab && ix.ftab_k > 1;
   if (!offs && k >= 1 && k <= RS_PACK_MAX_K) {
-    k_pack_kmers<<<(unsigned)((Q + RS_THREADS - 1) / RS_THREADS), RS_THREADS, 0, st>>>(text, k, Q, mode == 1 && strand == 1,
+    k_pack_kmers<<<(unsigned)((Q + RS_THREADS - 1) / RS_THREADS), RS_THREADS, 0, st>>>(text, k, Q, mode >= 1 && strand == 1,
                                                                                    lower);
     if (ftab) RS_LAUNCH((k_find_interval<true, true>), Q, st, ix, text, offs, k, Q, lower, upper, mode, strand, stats, peers);
     else RS_LAUNCH((k_find_interval<false, true>), Q, st, ix, text, offs, k, Q, lower, upper, mode, strand, stats, peers);

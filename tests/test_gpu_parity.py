@@ -7,6 +7,7 @@ import numpy as np
 import pytest
 
 import oracle
+from readserver_b200 import datagen as dg
 from tests import common
 from tests.golden.make_golden import random_runs
 
@@ -303,3 +304,66 @@ def test_error_behaviour(engine, tmp_path):
         assert e.value.status == 8
         lo, up = B.find_interval(np.zeros((0, 31), dtype=np.uint8), 31)
         assert lo.size == 0
+
+
+def test_64_shards_fused_count_on_one_gpu(engine):
+    """configs[2] shape in small: one read set split into the 64 shards of demo/permutations-3.txt (reversed
+    last 3 bases, service.cpp:820), every shard searched for the whole batch, per-shard counts added by the
+    search kernel into the communicator's buffer (world size 1: all k-mers are owned here).  The totals
+    equal the sum of the oracle's per-shard counts, both strands; with exact rank they equal brute-force
+    occurrence counts over the whole read set."""
+    import torch
+    from readserver_b200 import sharding
+    case = common.make_case("shards", 24000, 6800, 3, 73, keep_reads=True)
+    keys = sharding.permutation_keys(3)
+    by_key = {k: [] for k in keys}
+    for r in case.reads:
+        by_key[sharding.shard_of_read(r)].append(r)
+    shards = []
+    for k in keys:
+        if not by_key[k]:
+            continue
+        rd, ln = dg.strings_to_reads(by_key[k])
+        rd, ln, _, _ = dg.dedupe_rlo(rd, ln)
+        b = dg.build_bwt(rd, ln)
+        runs = b.runs.numpy().copy()
+        shards.append((engine.GpuBWT(runs=runs, num_strings=b.num_strings, num_symbols=b.num_symbols),
+                       oracle.PortIndex(runs=runs, num_strings=b.num_strings, num_symbols=b.num_symbols)))
+    assert len(shards) > 32
+    q = case.queries(3000, 31, seed=5)
+    comp = np.zeros(256, dtype=np.uint8)
+    for a, b in zip(b"ACGT", b"TGCA"):
+        comp[a] = b
+    q[1500:] = comp[q[1500:, ::-1]]  # the second half only occurs on the reverse strand
+    q[7, 3] = ord("N")  # counts 0 on every shard (service.cpp:299-301)
+    Q = q.shape[0]
+    dq = torch.from_numpy(q).cuda()
+    comm = sharding.connect_peers(engine.PeerComm(0, 0, 1, Q), "cuda:0")
+    try:
+        for strand in (0, 1):
+            for exact in (False, True):
+                for B, _ in shards:
+                    B.set_tail_emulation(not exact)
+                comm.begin(Q)
+                for B, _ in shards:
+                    comm.accumulate(B, dq, 31, Q, strand)
+                got = sharding.counts_view(comm.finish(), Q, "cuda:0").cpu().numpy()
+                assert not comm.timed_out()
+                if exact:
+                    strs = [bytes(k).decode() for k in q]
+                    if strand:
+                        strs = [s[::-1].translate(str.maketrans("ACGT", "TGCA")) for s in strs]
+                    want = np.array([0 if "N" in s else common.brute_count(case.reads, s) for s in strs])
+                    assert want.sum() > 1000
+                else:
+                    qq = np.ascontiguousarray(comp[q[:, ::-1]]) if strand else q
+                    valid = np.isin(q, np.frombuffer(b"ACGT", dtype=np.uint8)).all(axis=1)
+                    want = np.zeros(Q, dtype=np.int64)
+                    for _, P in shards:
+                        lo, up = P.find_interval_batch(qq, 31, nthreads=4)
+                        want += np.where(valid & (up >= lo), up - lo + 1, 0).astype(np.int64)
+                assert np.array_equal(got, want), (strand, exact)
+    finally:
+        comm.close()
+        for B, _ in shards:
+            B.close()
