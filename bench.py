@@ -204,7 +204,7 @@ def run_reference(args):
         "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=_REAL_STDOUT, flush=True)
 
 
 # ------------------------------------------------------------------------------------------------
@@ -292,6 +292,11 @@ def run_ours(args):
     evs = []
     for _ in range(args.steps):
         flush.fill_(1)  # evict the index and the queries from L2 between timed steps (untimed)
+        if world > 1:
+            # the untimed flush ends at different moments on different GPUs: line the ranks up again so that
+            # a step's time is the step, not the skew of what ran before it
+            torch.cuda.synchronize()
+            dist.barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         step()
@@ -413,7 +418,8 @@ def run_ours(args):
             "bwt_symbols": shard["num_symbols"], "bwt_runs": int(shard["runs"].size), "reads_unique": shard["num_strings"],
             "index_hbm_bytes": int(B.info.hbm_bytes), "index_fits_l2": bool(B.info.hbm_bytes < 126e6),
             "l2": "256 MiB buffer written between timed steps (untimed) -> index and queries start cold",
-            "timing": "CUDA events around each step on the launching stream, summed; max over ranks",
+            "timing": "CUDA events around each step on the launching stream, summed; max over ranks"
+                      + ("; ranks re-aligned with a barrier after each untimed L2 flush" if world > 1 else ""),
             "collective": "none" if world == 1 else
             "fused into K1: counts added into the owning rank's buffer over NVLink peer memory + one flag barrier "
             "per step, inside the timed step; checked against an NCCL all-reduce of the per-shard counts",
@@ -448,13 +454,22 @@ def run_ours(args):
                                 "sample": f"first {r['n']} of {Q} queries, {cores} threads striding the array",
                                 "gpu_results_bit_exact_on_sample": ok}
         assert ok, "GPU results differ from the CPU reference"
-    print(json.dumps(line), flush=True)
+    print(json.dumps(line), file=_REAL_STDOUT, flush=True)
     if world > 1:
         dist.destroy_process_group()
 
 
+_REAL_STDOUT = sys.stdout
+
+
 def main():
     args = parse()
+    # libraries (NCCL's version banner, torchrun notices) must not share stdout with the ONE JSON line:
+    # everything but that line goes to stderr
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     if args.impl == "reference":
         run_reference(args)
     else:
