@@ -183,6 +183,15 @@ int rs_samples_batch(const rs_index* ix, const uint64_t* read_index, size_t n, u
 int rs_carriers_batch(const rs_index* ix, const uint64_t* hit_offsets, const uint64_t* read_index, size_t Q,
                       uint64_t* out_offsets, uint64_t capacity, uint8_t* out_codes);
 
+/* ---- k-mer tiling of long queries (/kmermatch) ---------------------------------------------------
+ * get_tiles + the findInterval of find_reads for a whole batch (src/service/service.cpp:232-246, 466-500):
+ * query q (text[offsets[q] .. offsets[q+1])) is cut into tiles of `kmer` bases starting at 0, skip+1,
+ * 2(skip+1), ...; tile_offsets (Q+1, out) is the CSR of tiles per query; lower/upper (capacity entries)
+ * receive one interval per tile.  Tiles holding a byte outside ACGT, which the reference skips, come back
+ * as (1, 0).  RS_STATUS_CAPACITY when there are more tiles than `capacity` (tile_offsets is still filled). */
+int rs_tile_intervals_batch(const rs_index* ix, const char* text, const uint64_t* offsets, size_t Q, uint32_t kmer,
+                            uint32_t skip, uint64_t* tile_offsets, uint64_t capacity, uint64_t* lower, uint64_t* upper);
+
 /* ---- fan-in of per-shard counts across the GPUs of one box ----------------------------------------
  * Replaces the front end's sum over shard replies (src/service/server.cpp:184-197, 404-410).  One
  * process per GPU; every rank searches the whole batch in its shards and each finished query's count

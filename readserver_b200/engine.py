@@ -65,6 +65,7 @@ def lib() -> C.CDLL:
         "rs_last_error": (C.c_char_p, []),
         "rs_host_alloc": (i32, [C.POINTER(vp), sz]),
         "rs_host_free": (None, [vp]),
+        "rs_tile_intervals_batch": (i32, [vp, vp, vp, sz, C.c_uint32, C.c_uint32, vp, u64, vp, vp]),
         "rs_comm_create": (i32, [i32, i32, i32, u64, C.POINTER(vp)]),
         "rs_comm_export": (i32, [vp, vp]),
         "rs_comm_connect": (i32, [vp, vp]),
@@ -374,6 +375,22 @@ class GpuBWT:
     # -- device-pointer forms (torch tensors on self.device; asynchronous on `stream`) -------------
     def find_interval_dev(self, d_kmers, k: int, q: int, d_lower, d_upper, stream: int = 0):
         _check(lib().rs_find_interval_batch_dev(self._h, _ptr(d_kmers), k, q, _ptr(d_lower), _ptr(d_upper), stream))
+
+    def tile_intervals(self, queries: list, kmer: int, skip: int = 0):
+        """get_tiles + findInterval per tile (service.cpp:232-246, 466-500) for a batch of query strings.
+        Returns (tile_offsets [Q+1], lower [T], upper [T]); tiles the reference skips (non-ACGT) are (1, 0)."""
+        bs = [q.encode() if isinstance(q, str) else bytes(q) for q in queries]
+        text = np.frombuffer(b"".join(bs) or b"\0", dtype=np.uint8)
+        offs = np.zeros(len(bs) + 1, dtype=np.uint64)
+        offs[1:] = np.cumsum([len(b) for b in bs])
+        step = skip + 1
+        cap = int(sum(0 if len(b) < kmer else (len(b) - kmer) // step + 1 for b in bs))
+        toff = np.zeros(len(bs) + 1, dtype=np.uint64)
+        lo = np.empty(max(cap, 1), dtype=np.uint64)
+        up = np.empty(max(cap, 1), dtype=np.uint64)
+        _check(lib().rs_tile_intervals_batch(self._h, text.ctypes.data, offs.ctypes.data, len(bs), kmer, skip,
+                                             toff.ctypes.data, cap, lo.ctypes.data, up.ctypes.data))
+        return toff, lo[:cap], up[:cap]
 
     def count_dev(self, d_kmers, k: int, q: int, strand: int, d_counts, stream: int = 0):
         _check(lib().rs_count_batch_dev(self._h, _ptr(d_kmers), k, q, strand, _ptr(d_counts), stream))

@@ -367,3 +367,29 @@ def test_64_shards_fused_count_on_one_gpu(engine):
         comm.close()
         for B, _ in shards:
             B.close()
+
+
+@pytest.mark.parametrize("kmer,skip", [(31, 0), (31, 7), (73, 26), (12, 100)])
+def test_kmer_tiles_match_get_tiles(kmer, skip, datasets, engine):
+    """/kmermatch's tiling (get_tiles, service.cpp:232-246) + findInterval per tile, for a ragged batch."""
+    case, P = datasets.case("clean"), datasets.port("clean")
+    lens = [100, 73, 31, 30, 250, 12, 0, 101]
+    qs = []
+    for i, L in enumerate(lens):
+        parts, seed = [], 300 + i
+        while sum(len(p) for p in parts) < L:
+            parts.append(bytes(case.queries(1, 100, seed=seed)[0]).decode())
+            seed += 1000
+        qs.append("".join(parts)[:L])
+    qs[4] = qs[4][:40] + "N" + qs[4][41:]   # tiles over the N are skipped by the reference
+    with _gpu(engine, case) as B:
+        toff, lo, up = B.tile_intervals(qs, kmer, skip)
+    t = 0
+    for qi, w in enumerate(qs):
+        tiles = [w[i:i + kmer] for i in range(0, len(w) - kmer + 1, skip + 1)] if len(w) >= kmer else []
+        assert int(toff[qi + 1] - toff[qi]) == len(tiles)
+        for tile in tiles:
+            want = (1, 0) if any(c not in "ACGT" for c in tile) else P.find_interval(tile)
+            assert (int(lo[t]), int(up[t])) == want, (qi, tile)
+            t += 1
+    assert t == int(toff[-1])
