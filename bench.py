@@ -44,7 +44,7 @@ FALLBACK_HBM_GBS = 6650.0     # /opt/skills/guides/B200_PROFILING.md
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--steps", type=int, default=200)
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     # workload overrides (debugging only; the defaults are BASELINE.json configs[1])

@@ -322,7 +322,10 @@ __global__ void __launch_bounds__(RS_THREADS, RS_K1_BLOCKS)
 /* K2.  extractPrefix (query.cpp:43-63): LF-walk from each row to its '$'.  Same step-interleaved
  * scheme as K1: a thread whose walk ends takes its next row on the following trip, so the set of
  * live walkers stays dense in every warp without a separate compaction pass. */
-__global__ void __launch_bounds__(RS_THREADS)
+#ifndef RS_K2_BLOCKS
+#define RS_K2_BLOCKS 5 /* 4: 1119, 5: 1164, 6: 1012 M hit rows/s */
+#endif
+__global__ void __launch_bounds__(RS_THREADS, RS_K2_BLOCKS)
     k_extract_prefix(const __grid_constant__ rs_index_dev ix, const uint64_t* __restrict__ rows, uint64_t n,
                      uint32_t max_steps, uint64_t* __restrict__ lexrank, uint32_t* __restrict__ steps,
                      const uint64_t* __restrict__ sai, uint64_t* __restrict__ read_index, uint8_t* __restrict__ bases,
