@@ -174,6 +174,11 @@ int rs_locate_batch_dev(const rs_index* ix, const void* d_kmers, int k, size_t Q
  * [offsets[r], offsets[r+1]) of size_of_sample bytes each; offsets has num_strings+1 entries. */
 int rs_index_set_samples(rs_index* ix, const uint64_t* offsets, const uint8_t* codes, uint64_t num_strings,
                          int size_of_sample);
+/* The same table straight from the ETL's merged read file (`read\n codes\n` pairs in RLO order, the input of
+ * src/util/load_data_into_rocksdb.cpp:41-49): the i-th read without 'N' is read index i (build_bwt.sh:919);
+ * with has_other_meta_data each code is followed by count and lane bytes (service.cpp:829-843), which the
+ * table drops.  Replaces the 64 RocksDB loads of build_bwt.sh step 9 on this path. */
+int rs_index_load_samples_file(rs_index* ix, const char* path, int size_of_sample, int has_other_meta_data);
 /* Sample codes of n reads, order and duplicates preserved (service.cpp:829-843):
  * out_offsets[n+1] in codes (always written); out_codes holds `capacity` codes, else RS_STATUS_CAPACITY. */
 int rs_samples_batch(const rs_index* ix, const uint64_t* read_index, size_t n, uint64_t* out_offsets,

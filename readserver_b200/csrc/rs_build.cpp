@@ -224,3 +224,40 @@ void rs_fill_view(const RsHostIndex& h, rs_index_dev* d) {
   d->vlast = h.vlast;
   rs_view_set_tail(h, true, d);
 }
+
+int rs_parse_etl_samples(const char* path, int sos, int meta, std::vector<uint64_t>& offsets, std::vector<uint8_t>& codes) {
+  offsets.assign(1, 0);
+  codes.clear();
+  if (sos < 1) return RS_ERR_ARG;
+  FILE* f = fopen(path, "rb");
+  if (!f) return RS_ERR_OPEN;
+  const size_t stride = (size_t)sos + (meta ? 2 : 0);
+  std::string read, ids;
+  auto getline = [&](std::string& out) -> bool {
+    out.clear();
+    int ch;
+    bool any = false;
+    while ((ch = fgetc(f)) != EOF) {
+      any = true;
+      if (ch == '\n') return true;
+      out.push_back((char)ch);
+    }
+    return any;
+  };
+  int rc = RS_OK;
+  while (getline(read)) {
+    if (!getline(ids)) {
+      rc = RS_ERR_ARG; /* a read without its value line */
+      break;
+    }
+    if (read.find('N') != std::string::npos) continue; /* build_bwt.sh:919 drops it before sga index */
+    if (ids.size() % stride != 0) {
+      rc = RS_ERR_ARG;
+      break;
+    }
+    for (size_t i = 0; i < ids.size(); i += stride) codes.insert(codes.end(), ids.begin() + i, ids.begin() + i + sos);
+    offsets.push_back(codes.size() / (size_t)sos);
+  }
+  fclose(f);
+  return rc;
+}

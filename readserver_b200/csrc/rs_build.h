@@ -44,6 +44,15 @@ int rs_read_bwt_file(const char* path, std::vector<uint8_t>& runs, uint64_t& num
 int rs_build_host_index(const uint8_t* runs, uint64_t nruns, uint64_t num_strings, uint64_t num_symbols,
                         RsHostIndex& out);
 
+/* Sample table from the ETL's merged read file (`read\n codes\n` pairs in RLO order: rlosort_seq_and_convert_
+ * sample_names.cpp:47-53, merge_rlosorted_reads.cpp:45-47; the file load_data_into_rocksdb.cpp:41-49 reads).
+ * Reads holding 'N' never reach the BWT (build_bwt.sh:919), so the i-th N-free read of the file is read
+ * index i.  Each value is a run of size_of_sample-byte codes, each followed by 2 bytes (count, lane) iff
+ * has_other_meta_data (service.cpp:829-843); the table keeps the codes.  offsets gets one entry per kept
+ * read + 1.  Returns RS_OK, RS_ERR_OPEN, or RS_ERR_ARG (odd line count / value length not a multiple). */
+int rs_parse_etl_samples(const char* path, int size_of_sample, int has_other_meta_data, std::vector<uint64_t>& offsets,
+                         std::vector<uint8_t>& codes);
+
 /* Scalar fields of the kernel-side view from a host index (the caller sets the pointers), and the
  * reference-tail switch: folds "last m_vSum window and at/after the clamp" into one threshold per
  * lookup kind, and picks initInterval's constant (query.cpp:18-21). */

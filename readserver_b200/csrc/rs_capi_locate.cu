@@ -101,6 +101,16 @@ int rs_locate_batch(const rs_index* ix, const char* kmers, int k, size_t Q, uint
 }
 
 /* ---- sample table ---- */
+int rs_index_load_samples_file(rs_index* ix, const char* path, int size_of_sample, int has_other_meta_data) {
+  if (!ix || !path) return fail(RS_STATUS_ARG, "null argument");
+  std::vector<uint64_t> offsets;
+  std::vector<uint8_t> codes;
+  const int rc = rs_parse_etl_samples(path, size_of_sample, has_other_meta_data, offsets, codes);
+  if (rc == RS_ERR_OPEN) return fail(RS_STATUS_OPEN, "cannot open %s", path);
+  if (rc != RS_OK) return fail(RS_STATUS_ARG, "%s is not a `read / codes` file for size_of_sample %d", path, size_of_sample);
+  return rs_index_set_samples(ix, offsets.data(), codes.data(), offsets.size() - 1, size_of_sample);
+}
+
 int rs_index_set_samples(rs_index* ix, const uint64_t* offsets, const uint8_t* codes, uint64_t num_strings,
                          int size_of_sample) {
   if (!ix || !offsets) return fail(RS_STATUS_ARG, "null argument");

@@ -65,6 +65,7 @@ def lib() -> C.CDLL:
         "rs_last_error": (C.c_char_p, []),
         "rs_host_alloc": (i32, [C.POINTER(vp), sz]),
         "rs_host_free": (None, [vp]),
+        "rs_index_load_samples_file": (i32, [vp, C.c_char_p, i32, i32]),
         "rs_tile_intervals_batch": (i32, [vp, vp, vp, sz, C.c_uint32, C.c_uint32, vp, u64, vp, vp]),
         "rs_comm_create": (i32, [i32, i32, i32, u64, C.POINTER(vp)]),
         "rs_comm_export": (i32, [vp, vp]),
@@ -340,6 +341,11 @@ class GpuBWT:
         codes = np.ascontiguousarray(codes, dtype=np.uint8).reshape(-1)
         _check(lib().rs_index_set_samples(self._h, offsets.ctypes.data, codes.ctypes.data if codes.size else None,
                                           offsets.size - 1, size_of_sample))
+        self._sos = size_of_sample
+
+    def load_samples_file(self, path: str, size_of_sample: int, has_other_meta_data: bool = False):
+        """Sample table from the ETL's merged `read / codes` file (load_data_into_rocksdb.cpp:41-49)."""
+        _check(lib().rs_index_load_samples_file(self._h, path.encode(), size_of_sample, int(has_other_meta_data)))
         self._sos = size_of_sample
 
     def samples(self, read_index):

@@ -122,6 +122,9 @@ class Emul:
             L.emul_find_interval_batch.argtypes = [C.c_void_p, _u8p, C.c_int, C.c_uint64, _u64p, _u64p]
             L.emul_prefix_walk_batch.argtypes = [C.c_void_p, _u64p, C.c_uint64, C.c_uint32, _u64p, _u32p]
             L.emul_postfix_walk_batch.argtypes = [C.c_void_p, _u64p, C.c_uint64, C.c_uint32, _u64p, _u32p]
+            L.emul_parse_etl.restype = C.c_int
+            L.emul_parse_etl.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64,
+                                         C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
             L.emul_blocks.restype = C.c_void_p
             L.emul_blocks.argtypes = [C.c_void_p]
             cls._lib = L
@@ -199,6 +202,38 @@ class Emul:
         st = np.empty(rows.size, dtype=np.uint32)
         self.lib().emul_prefix_walk_batch(self._h, rows, rows.size, max_steps, lex, st)
         return lex, st
+
+
+def write_etl_file(path: str, reads: list, off, codes, sos: int, meta: bool, n_reads_every: int = 0, seed: int = 9):
+    """merged.rlosorted.reads as the reference's ETL writes it: `read\\n value\\n` per read, value = codes in
+    merge order, each followed by count+33 and lane+33 bytes iff meta (service.cpp:829-843).  With n_reads_every,
+    a read holding 'N' (dropped before the BWT is built, build_bwt.sh:919) is inserted every that many lines."""
+    rng = np.random.default_rng(seed)
+    codes = np.ascontiguousarray(codes, dtype=np.uint8).reshape(-1, sos)
+    with open(path, "wb") as f:
+        for i, r in enumerate(reads):
+            if n_reads_every and i % n_reads_every == 0:
+                f.write(b"ACGTNNACGT" + r.encode()[:20] + b"\n" + bytes(oracle.sample_code(1, sos)) + (b"\x22\x22" if meta else b"") + b"\n")
+            val = b""
+            for c in codes[int(off[i]):int(off[i + 1])]:
+                val += bytes(c)
+                if meta:
+                    val += bytes([33 + int(rng.integers(0, 90)), 33 + int(rng.integers(0, 8))])
+            f.write(r.encode() + b"\n" + val + b"\n")
+
+
+def parse_etl(path: str, sos: int, meta: bool):
+    """rs_parse_etl_samples through the test library: (status, offsets, codes)."""
+    L = Emul.lib()
+    nr, nc = C.c_uint64(), C.c_uint64()
+    rc = L.emul_parse_etl(path.encode(), sos, int(meta), None, 0, None, 0, C.byref(nr), C.byref(nc))
+    if rc != 0:
+        return rc, None, None
+    off = np.zeros(nr.value + 1, dtype=np.uint64)
+    codes = np.zeros(max(nc.value, 1), dtype=np.uint8)
+    rc = L.emul_parse_etl(path.encode(), sos, int(meta), off.ctypes.data, off.size, codes.ctypes.data, codes.size,
+                          C.byref(nr), C.byref(nc))
+    return rc, off, codes[: nc.value]
 
 
 def positions(n: int, limit: int = 400_000, seed: int = 0) -> np.ndarray:

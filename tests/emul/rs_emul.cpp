@@ -66,6 +66,21 @@ void emul_info(void* p, uint64_t* out) {
   for (int c = 0; c < 5; ++c) { out[7 + c] = h.pc[c]; out[12 + c] = h.tot[c]; out[17 + c] = h.init_occ[c]; }
 }
 
+/* rs_parse_etl_samples: returns status; *nreads, *ncodes sizes; data copied out by a second call */
+int emul_parse_etl(const char* path, int sos, int meta, uint64_t* offsets, uint64_t cap_off, uint8_t* codes, uint64_t cap_codes,
+                   uint64_t* nreads, uint64_t* ncodes) {
+  std::vector<uint64_t> off;
+  std::vector<uint8_t> cd;
+  const int rc = rs_parse_etl_samples(path, sos, meta, off, cd);
+  *nreads = off.size() - 1;
+  *ncodes = cd.size();
+  if (rc == RS_OK && offsets && off.size() <= cap_off && cd.size() <= cap_codes) {
+    memcpy(offsets, off.data(), off.size() * 8);
+    if (!cd.empty()) memcpy(codes, cd.data(), cd.size());
+  }
+  return rc;
+}
+
 /* raw 64-byte blocks, for the layout tests */
 const void* emul_blocks(void* p) { return ((Emul*)p)->h.blocks.data(); }
 

@@ -176,6 +176,27 @@ def test_locate_samples_and_carriers(name, sos, nsamples, datasets, engine):
             assert got == [oracle.sample_code(s, sos) for s in want]
 
 
+@pytest.mark.parametrize("sos,meta", [(1, False), (2, True)])
+def test_sample_table_from_etl_file(sos, meta, datasets, engine, tmp_path):
+    """rs_index_load_samples_file (the ETL's merged read file instead of 64 RocksDB stores) gives the same
+    sample gathers and carrier sets as the table attached from arrays."""
+    case = datasets.case("clean")
+    off, codes, who = _sample_table(case.num_strings, 150, sos, seed=8)
+    path = str(tmp_path / "merged.rlosorted.reads")
+    common.write_etl_file(path, case.reads, off, codes, sos, meta, n_reads_every=211)
+    ri = np.random.default_rng(1).integers(0, case.num_strings, 5000).astype(np.uint64)
+    hit_off = np.arange(0, 5001, 10, dtype=np.uint64)
+    with _gpu(engine, case) as A, _gpu(engine, case) as B:
+        A.set_samples(off, codes, sos)
+        B.load_samples_file(path, sos, meta)
+        a, b = A.samples(ri), B.samples(ri)
+        assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1]) and int(a[0][-1]) > 5000
+        ca, cb = A.carriers(hit_off, ri), B.carriers(hit_off, ri)
+        assert np.array_equal(ca[0], cb[0]) and np.array_equal(ca[1], cb[1])
+        with pytest.raises(engine.RsError):
+            B.load_samples_file(str(tmp_path / "nope"), sos, meta)
+
+
 @pytest.mark.parametrize("name", ["small", "clean", "deep"])
 def test_prefix_table_does_not_change_results(name, datasets, engine):
     """The k-mer suffix table only skips steps: intervals (including early-exit values) and counts on both

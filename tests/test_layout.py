@@ -166,3 +166,30 @@ def test_builder_rejects_bad_input(tmp_path):
     p.write_bytes(b"\xca\xca" + b"\x00" * 10)
     assert common.Emul(path=str(p)).status == 3
     assert common.Emul(path=str(tmp_path / "missing.bwt")).status == 1
+
+
+@pytest.mark.parametrize("sos,meta", [(1, False), (2, True), (1, True)])
+def test_etl_sample_file_parser(sos, meta, datasets, tmp_path):
+    """rs_parse_etl_samples: the merged `read / codes` file -> read-index-addressed CSR; reads with 'N' are not
+    in the BWT and take no index; count/lane metadata bytes are dropped."""
+    case = datasets.case("clean")
+    rng = np.random.default_rng(3)
+    n = case.num_strings
+    cnt = rng.integers(1, 5, n)
+    off = np.zeros(n + 1, dtype=np.uint64)
+    np.cumsum(cnt, out=off[1:])
+    who = rng.integers(0, 200, int(off[-1]))
+    codes = np.array([list(oracle.sample_code(int(i), sos)) for i in who], dtype=np.uint8)
+    path = str(tmp_path / "merged.rlosorted.reads")
+    common.write_etl_file(path, case.reads, off, codes, sos, meta, n_reads_every=97)
+    rc, off2, codes2 = common.parse_etl(path, sos, meta)
+    assert rc == 0 and np.array_equal(off2, off) and np.array_equal(codes2, codes.reshape(-1))
+    # the value bytes of one read decode, with the oracle's restatement of service.cpp:829-843, to the same codes
+    lines = open(path, "rb").read().split(b"\n")
+    kept = [(lines[i], lines[i + 1]) for i in range(0, len(lines) - 1, 2) if b"N" not in lines[i]]
+    for r in (0, 1, n // 2, n - 1):
+        dec = oracle.decode_sample_value(kept[r][1], sos, meta)
+        assert [d[0] for d in dec] == [bytes(c) for c in codes[int(off[r]):int(off[r + 1])]]
+    assert common.parse_etl(str(tmp_path / "missing"), sos, meta)[0] == 1
+    open(path, "ab").write(b"ACGT\n")          # a read without its value line
+    assert common.parse_etl(path, sos, meta)[0] == 5
