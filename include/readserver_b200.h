@@ -188,6 +188,20 @@ int rs_samples_batch(const rs_index* ix, const uint64_t* read_index, size_t n, u
 int rs_carriers_batch(const rs_index* ix, const uint64_t* hit_offsets, const uint64_t* read_index, size_t Q,
                       uint64_t* out_offsets, uint64_t capacity, uint8_t* out_codes);
 
+/* ---- read strings (output=reads) ------------------------------------------------------------------
+ * The reference rebuilds each matching read by walking the BWT from the hit row (query(): extractPrefix +
+ * extractPostfix, src/bwt/query.cpp:87-100; find_reads, service.cpp:714-751).  With the read index from the
+ * locate stage the string can be read from a table: all reads in builder input order, 2 bits per base.
+ *   rs_index_set_reads        text = the reads concatenated (ACGT only), offsets[num_strings + 1]
+ *   rs_index_load_reads_file  the same from the ETL's merged `read / codes` file (reads with 'N' skipped)
+ *   rs_reads_batch            out = n x max_len bytes, zero padded; out_len[i] = the read's length
+ *                             (2^32-1 for a read index outside the table)                              */
+int rs_index_set_reads(rs_index* ix, const char* text, const uint64_t* offsets, uint64_t num_strings);
+int rs_index_load_reads_file(rs_index* ix, const char* path);
+int rs_reads_batch(const rs_index* ix, const uint64_t* read_index, size_t n, uint32_t max_len, char* out, uint32_t* out_len);
+int rs_reads_batch_dev(const rs_index* ix, const void* d_read_index, size_t n, uint32_t max_len, void* d_out,
+                       void* d_out_len, void* stream);
+
 /* ---- k-mer tiling of long queries (/kmermatch) ---------------------------------------------------
  * get_tiles + the findInterval of find_reads for a whole batch (src/service/service.cpp:232-246, 466-500):
  * query q (text[offsets[q] .. offsets[q+1])) is cut into tiles of `kmer` bases starting at 0, skip+1,

@@ -261,3 +261,34 @@ int rs_parse_etl_samples(const char* path, int sos, int meta, std::vector<uint64
   fclose(f);
   return rc;
 }
+
+int rs_parse_etl_reads(const char* path, std::string& text, std::vector<uint64_t>& offsets) {
+  text.clear();
+  offsets.assign(1, 0);
+  FILE* f = fopen(path, "rb");
+  if (!f) return RS_ERR_OPEN;
+  std::string line;
+  bool is_read = true, keep = false;
+  int ch, rc = RS_OK;
+  bool any = false;
+  auto end_line = [&]() {
+    if (is_read) {
+      keep = line.find('N') == std::string::npos;
+      if (keep) {
+        text += line;
+        offsets.push_back(text.size());
+      }
+    }
+    is_read = !is_read;
+    line.clear();
+    any = false;
+  };
+  while ((ch = fgetc(f)) != EOF) {
+    if (ch == '\n') end_line();
+    else { if (is_read) line.push_back((char)ch); any = true; }
+  }
+  if (any) end_line();
+  if (!is_read) rc = RS_ERR_ARG; /* a read without its value line */
+  fclose(f);
+  return rc;
+}

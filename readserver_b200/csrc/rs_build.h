@@ -53,6 +53,9 @@ int rs_build_host_index(const uint8_t* runs, uint64_t nruns, uint64_t num_string
 int rs_parse_etl_samples(const char* path, int size_of_sample, int has_other_meta_data, std::vector<uint64_t>& offsets,
                          std::vector<uint8_t>& codes);
 
+/* The reads of the same file that reach the BWT (odd lines without 'N'), concatenated, with their offsets. */
+int rs_parse_etl_reads(const char* path, std::string& text, std::vector<uint64_t>& offsets);
+
 /* Scalar fields of the kernel-side view from a host index (the caller sets the pointers), and the
  * reference-tail switch: folds "last m_vSum window and at/after the clamp" into one threshold per
  * lookup kind, and picks initInterval's constant (query.cpp:18-21). */

@@ -130,6 +130,8 @@ void rs_index_close(rs_index* ix) {
   if (ix->d_samp_codes) cudaFree(ix->d_samp_codes);
   if (ix->d_stats) cudaFree(ix->d_stats);
   if (ix->d_ftab) cudaFree(ix->d_ftab);
+  if (ix->d_reads) cudaFree(ix->d_reads);
+  if (ix->d_read_off) cudaFree(ix->d_read_off);
   ix->s_in.release();
   ix->s_in2.release();
   ix->s_out.release();

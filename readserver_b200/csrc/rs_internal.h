@@ -62,6 +62,9 @@ struct rs_index {
   uint8_t* d_samp_codes = nullptr;
   int size_of_sample = 0;
   uint32_t num_samples = 0; /* 1 + largest sample number that occurs in the table */
+  uint32_t* d_reads = nullptr;     /* packed read table (rs_reads.cu): 16 bases per word */
+  uint64_t* d_read_off = nullptr;  /* first base of each read, num_strings + 1 entries */
+  uint64_t reads_bytes = 0;
   uint64_t* d_ftab = nullptr; /* k-mer suffix table (rs_layout.h), 4^ftab_k pairs */
   uint64_t* d_stats = nullptr; /* [0] updateInterval steps, [1] LF-walk steps; null unless profiling is on */
   cudaStream_t stream = nullptr;

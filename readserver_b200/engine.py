@@ -66,6 +66,10 @@ def lib() -> C.CDLL:
         "rs_host_alloc": (i32, [C.POINTER(vp), sz]),
         "rs_host_free": (None, [vp]),
         "rs_index_load_samples_file": (i32, [vp, C.c_char_p, i32, i32]),
+        "rs_index_set_reads": (i32, [vp, vp, vp, u64]),
+        "rs_index_load_reads_file": (i32, [vp, C.c_char_p]),
+        "rs_reads_batch": (i32, [vp, vp, sz, C.c_uint32, vp, vp]),
+        "rs_reads_batch_dev": (i32, [vp, vp, sz, C.c_uint32, vp, vp, vp]),
         "rs_tile_intervals_batch": (i32, [vp, vp, vp, sz, C.c_uint32, C.c_uint32, vp, u64, vp, vp]),
         "rs_comm_create": (i32, [i32, i32, i32, u64, C.POINTER(vp)]),
         "rs_comm_export": (i32, [vp, vp]),
@@ -347,6 +351,25 @@ class GpuBWT:
         """Sample table from the ETL's merged `read / codes` file (load_data_into_rocksdb.cpp:41-49)."""
         _check(lib().rs_index_load_samples_file(self._h, path.encode(), size_of_sample, int(has_other_meta_data)))
         self._sos = size_of_sample
+
+    def set_reads(self, reads: list):
+        """Attach the packed read table: the reads in builder input order (ACGT only)."""
+        bs = [r.encode() if isinstance(r, str) else bytes(r) for r in reads]
+        text = np.frombuffer(b"".join(bs) or b"\0", dtype=np.uint8)
+        off = np.zeros(len(bs) + 1, dtype=np.uint64)
+        off[1:] = np.cumsum([len(b) for b in bs])
+        _check(lib().rs_index_set_reads(self._h, text.ctypes.data, off.ctypes.data, len(bs)))
+
+    def load_reads_file(self, path: str):
+        _check(lib().rs_index_load_reads_file(self._h, path.encode()))
+
+    def reads(self, read_index, max_len: int = 128) -> list:
+        """Read strings by read index (None for an index outside the table)."""
+        ri = np.ascontiguousarray(read_index, dtype=np.uint64)
+        out = np.zeros((ri.size, max_len), dtype=np.uint8)
+        ln = np.zeros(ri.size, dtype=np.uint32)
+        _check(lib().rs_reads_batch(self._h, ri.ctypes.data, ri.size, max_len, out.ctypes.data, ln.ctypes.data))
+        return [None if l == 0xFFFFFFFF else out[i, :min(int(l), max_len)].tobytes().decode() for i, l in enumerate(ln)]
 
     def samples(self, read_index):
         """(offsets [n+1], codes [total, size_of_sample]) for n reads, order and duplicates preserved."""

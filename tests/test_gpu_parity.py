@@ -197,6 +197,37 @@ def test_sample_table_from_etl_file(sos, meta, datasets, engine, tmp_path):
             B.load_samples_file(str(tmp_path / "nope"), sos, meta)
 
 
+def test_read_table_equals_walked_reads(datasets, engine, tmp_path):
+    """output=reads: the packed read table addressed by the locate stage's read index gives the strings the
+    reference rebuilds by walking (query(): extractPrefix + extractPostfix, query.cpp:87-100)."""
+    case, P = datasets.case("clean"), datasets.port("clean")
+    path = str(tmp_path / "merged.rlosorted.reads")
+    off = np.arange(case.num_strings + 1, dtype=np.uint64)
+    common.write_etl_file(path, case.reads, off, np.full((case.num_strings, 1), 40, np.uint8), 1, False, n_reads_every=53)
+    q = case.queries(400, 31, seed=12)
+    with _gpu(engine, case) as B:
+        B.set_sai(case.sai)
+        res = B.locate(q, 31, max_hits=20, max_steps=128)
+        rows, ri = res["rows"], res["read_index"]
+        assert rows.size > 2000
+        want = [P.extract_read(int(r)) for r in rows[:1500]]
+        for attach in (lambda: B.set_reads(case.reads), lambda: B.load_reads_file(path)):
+            attach()
+            got = B.reads(ri[:1500], max_len=128)
+            assert got == want
+        assert B.reads(np.array([case.num_strings, 0], dtype=np.uint64), 128) == [None, case.reads[0]]
+        assert B.reads(ri[:3], max_len=10) == [w[:10] for w in want[:3]]   # truncated to max_len
+        with pytest.raises(engine.RsError):
+            B.set_reads(["ACGTN"] + case.reads[1:])
+    # the z golden vectors hold reads rebuilt by the unmodified reference
+    z = np.load(os.path.join(common.GOLDEN, "clean.npz"))
+    with engine.GpuBWT(os.path.join(common.GOLDEN, "clean.bwt")) as G:
+        gold = common.make_case("clean", *common.Datasets.SPECS["clean"][:3], min_len=73, keep_reads=True)
+        G.set_reads(gold.reads)
+        ri = G.extract_postfix(z["read_rows"], max_steps=300)[0]
+        assert G.reads(ri, 128) == [str(s) for s in z["read_strings"]]
+
+
 @pytest.mark.parametrize("name", ["small", "clean", "deep"])
 def test_prefix_table_does_not_change_results(name, datasets, engine):
     """The k-mer suffix table only skips steps: intervals (including early-exit values) and counts on both
