@@ -78,18 +78,22 @@ def build_shard(args, device, rank):
         reads, lens = dg.sample_reads([h1, h2], args.reads, args.read_len, seed=21 + 100 * rank + 7919 * attempt)
         reads, lens, _, _ = dg.dedupe_rlo(reads, lens)
         built = dg.build_bwt(reads, lens)
-        del reads, lens
         if dg.q2_safe(built.runs, built.num_symbols):
             break
     queries = dg.make_queries(h1, args.queries, args.k, seed=3).contiguous()
     runs = built.runs.cpu().numpy()
     sai = built.sai.cpu().numpy().astype(np.uint64)
     ns, nsym = built.num_strings, built.num_symbols
-    del built, h2
+    # the reads in builder input order, for the packed read table of the locate side measurement (rank 0 only)
+    reads_text = reads_off = None
+    if rank == 0 and args.impl == "ours" and args.locate_queries > 0 and int(lens.min()) == int(lens.max()):
+        reads_text = dg.ASCII[reads.cpu().numpy()].reshape(-1)
+        reads_off = np.arange(ns + 1, dtype=np.uint64) * np.uint64(reads.shape[1])
+    del built, h2, reads, lens
     if device != "cpu":
         torch.cuda.empty_cache()
     return dict(runs=runs, num_strings=ns, num_symbols=nsym, sai=sai, queries=queries, genome=h1,
-                build_seconds=time.time() - t0)
+                reads_text=reads_text, reads_off=reads_off, build_seconds=time.time() - t0)
 
 
 def workload_name(args):
@@ -386,6 +390,35 @@ def run_ours(args):
                   "walk_steps_per_step": wsteps / len(lms),
                   "achieved_GBps": (2.0 * isteps + wsteps) * BYTES_PER_RANK / lt / 1e9,
                   "kernels_per_step": 5, "note": "includes one stream sync per step to size the hit list"}
+        if shard.get("reads_text") is not None and hits:
+            # output=reads from the packed read table, addressed by the read indices just located
+            B.set_reads_arrays(shard["reads_text"], shard["reads_off"])
+            ml = args.read_len + 4
+            d_str = torch.empty(hits * ml, dtype=torch.uint8, device=dev)
+            d_len = torch.empty(hits, dtype=torch.int32, device=dev)
+            B.reads_dev(d_ri, hits, ml, d_str, d_len, stream)
+            torch.cuda.synchronize()
+            rms = []
+            for _ in range(5):
+                flush.fill_(1)
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                B.reads_dev(d_ri, hits, ml, d_str, d_len, stream)
+                e1.record()
+                torch.cuda.synchronize()
+                rms.append(e0.elapsed_time(e1))
+            # spot check against the table's source
+            ri_h = d_ri[:64].cpu().numpy().astype(np.int64)
+            got = d_str[: 64 * ml].cpu().numpy().reshape(64, ml)
+            for t, r in enumerate(ri_h):
+                if 0 <= r < shard["num_strings"]:
+                    a, b = int(shard["reads_off"][r]), int(shard["reads_off"][r + 1])
+                    assert np.array_equal(got[t, : b - a], shard["reads_text"][a:b]), "read table mismatch"
+            locate["reads_from_table"] = {"reads_per_s": hits * len(rms) / (sum(rms) / 1e3), "ms": sum(rms) / len(rms),
+                                          "bytes_written": hits * ml,
+                                          "note": "rs_reads_batch_dev on the located read indices (replaces extractPrefix + "
+                                                  "extractPostfix per row, query.cpp:87-100)"}
+            del d_str, d_len
         del d_off, d_ri, d_st
 
     random_gbs = random_gbs_128 = None

@@ -42,13 +42,28 @@ __global__ void k_unpack_reads(const uint32_t* __restrict__ packed, const uint64
     len = (uint32_t)(off[r + 1] - base);
   }
   const uint32_t m = len < max_len ? len : max_len;
-  for (uint32_t j = lane; j < max_len; j += 32) {
-    uint8_t ch = 0;
-    if (j < m) {
-      const uint64_t p = base + j;
-      ch = (uint8_t)((0x54474341u >> (8 * ((packed[p >> 4] >> (2 * (p & 15))) & 3u))) & 0xFFu); /* "ACGT" */
+  if (((max_len | (uint32_t)(uintptr_t)out) & 3u) == 0) {
+    /* rows are word aligned: each lane decodes four bases and stores one 32-bit word */
+    for (uint32_t j = 4 * lane; j < max_len; j += 128) {
+      uint32_t word = 0;
+#pragma unroll
+      for (uint32_t t = 0; t < 4; ++t) {
+        if (j + t < m) {
+          const uint64_t p = base + j + t;
+          word |= ((0x54474341u >> (8 * ((packed[p >> 4] >> (2 * (p & 15))) & 3u))) & 0xFFu) << (8 * t);
+        }
+      }
+      *reinterpret_cast<uint32_t*>(dst + j) = word;
     }
-    dst[j] = ch;
+  } else {
+    for (uint32_t j = lane; j < max_len; j += 32) {
+      uint8_t ch = 0;
+      if (j < m) {
+        const uint64_t p = base + j;
+        ch = (uint8_t)((0x54474341u >> (8 * ((packed[p >> 4] >> (2 * (p & 15))) & 3u))) & 0xFFu); /* "ACGT" */
+      }
+      dst[j] = ch;
+    }
   }
   if (lane == 0) out_len[i] = r < num_strings ? len : 0xFFFFFFFFu;
 }

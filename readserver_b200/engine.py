@@ -360,6 +360,15 @@ class GpuBWT:
         off[1:] = np.cumsum([len(b) for b in bs])
         _check(lib().rs_index_set_reads(self._h, text.ctypes.data, off.ctypes.data, len(bs)))
 
+    def set_reads_arrays(self, text: np.ndarray, offsets: np.ndarray):
+        """Packed read table from the concatenated ASCII reads (uint8) and their offsets (uint64, n + 1)."""
+        text = np.ascontiguousarray(text, dtype=np.uint8)
+        offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
+        _check(lib().rs_index_set_reads(self._h, text.ctypes.data, offsets.ctypes.data, offsets.size - 1))
+
+    def reads_dev(self, d_read_index, n: int, max_len: int, d_out, d_out_len, stream: int = 0):
+        _check(lib().rs_reads_batch_dev(self._h, _ptr(d_read_index), n, max_len, _ptr(d_out), _ptr(d_out_len), stream))
+
     def load_reads_file(self, path: str):
         _check(lib().rs_index_load_reads_file(self._h, path.encode()))
 
