@@ -36,7 +36,9 @@
 #define RS_HDR_BYTES 28
 #define RS_PAYLOAD 36 /* runs per block */
 #define RS_BLOCK_WORDS (RS_PAYLOAD / 4)
-#define RS_SLOT_SHIFT 9
+#ifndef RS_SLOT_SHIFT
+#define RS_SLOT_SHIFT 9 /* 512-symbol directory slots */
+#endif
 #define RS_SLOT_SIZE (1u << RS_SLOT_SHIFT)
 #define RS_SLOT_MASK (RS_SLOT_SIZE - 1u)
 #define RS_DIR_MORE (1ull << 62)
