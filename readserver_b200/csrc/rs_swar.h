@@ -1,10 +1,8 @@
-/* Per-lane arithmetic of the in-block rank / access / select over SGA run bytes.
+/* In-block rank / access / select over SGA run bytes, 32-bit SWAR.
  *
- * A lane owns NW consecutive 32-bit words (4 run bytes each) of a 128-byte block: 22 payload words
- * when one thread handles a whole block, fewer when 2, 4 or 8 lanes share it.  Everything here is
- * branch-free 32-bit SWAR so the same source compiles for the sm_100a kernels and for the host,
- * where tests/ replays it lane by lane against the oracle.  The cross-lane glue (scan / reduce /
- * broadcast) lives with the caller: warp shuffles on the device.
+ * A thread holds the NW consecutive 32-bit payload words (4 run bytes each) of one 64-byte block
+ * (NW = 9, rs_layout.h).  Everything here is branch-free so the same source compiles for the sm_100a
+ * kernels and for the host, where tests/ replays it against the oracle.
  *
  * Byte-SIMD without the video intrinsics (on sm_100a __vminu4 / __vsubus4 / __vcmpeq4 expand to 5-8
  * ALU instructions each): every quantity a byte holds here is < 128 (a word spans at most 4 x 31 =
