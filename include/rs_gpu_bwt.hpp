@@ -77,6 +77,13 @@ class GpuBWT : public BWT {
     check(rs_index_set_samples(ix_, offsets.data(), codes.data(), offsets.size() - 1, size_of_sample));
   }
 
+  // the same table from the ETL's merged `read / codes` file (load_data_into_rocksdb.cpp:41-49)
+  void loadSamplesFile(const std::string& path, int size_of_sample, bool has_other_meta_data) {
+    check(rs_index_load_samples_file(ix_, path.c_str(), size_of_sample, has_other_meta_data ? 1 : 0));
+  }
+  // packed read table for output=reads, from the same file (reads holding 'N' are not in the BWT)
+  void loadReadsFile(const std::string& path) { check(rs_index_load_reads_file(ix_, path.c_str())); }
+
   // ---- class BWT: batches of one ----
   char getChar(const uint64_t& index) const override {
     char c;
@@ -208,6 +215,42 @@ inline std::vector<std::string> query(const GpuBWT* bwt, const std::string& w, u
   const std::vector<std::string> pre = extractPrefixBatch(bwt, rows, max_len);
   const std::vector<std::string> post = extractPostfixBatch(bwt, rows, max_len);
   for (size_t i = 0; i < rows.size(); ++i) out.push_back(pre[i] + post[i]);
+  return out;
+}
+
+// The reads behind read indices (as the locate stage returns them), from the packed read table: what
+// query() rebuilds per row with extractPrefix + extractPostfix.  An index outside the table gives "".
+inline std::vector<std::string> readsBatch(const GpuBWT* bwt, const std::vector<uint64_t>& read_index, uint32_t max_len = 256) {
+  std::vector<std::string> out(read_index.size());
+  if (read_index.empty()) return out;
+  std::vector<char> buf(read_index.size() * (size_t)max_len);
+  std::vector<uint32_t> len(read_index.size());
+  check(rs_reads_batch(bwt->handle(), read_index.data(), read_index.size(), max_len, buf.data(), len.data()));
+  for (size_t i = 0; i < out.size(); ++i)
+    if (len[i] != 0xFFFFFFFFu) out[i].assign(&buf[i * (size_t)max_len], len[i] < max_len ? len[i] : max_len);
+  return out;
+}
+
+// get_tiles + findInterval per tile (service.cpp:232-246, 466-500) for a batch of queries: tiles of `kmer`
+// bases every skip+1 bases; result[q] = the intervals of query q's tiles, (1, 0) for a tile the reference skips.
+inline std::vector<std::vector<BWTInterval> > tileIntervalsBatch(const GpuBWT* bwt, const std::vector<std::string>& ws,
+                                                                size_t kmer, size_t skip) {
+  std::string text;
+  std::vector<uint64_t> offs;
+  detail::flatten(ws, text, offs);
+  uint64_t cap = 0;
+  for (const std::string& w : ws) cap += w.size() < kmer ? 0 : (w.size() - kmer) / (skip + 1) + 1;
+  std::vector<uint64_t> toff(ws.size() + 1), lo(cap ? cap : 1), up(cap ? cap : 1);
+  check(rs_tile_intervals_batch(bwt->handle(), text.data(), offs.data(), ws.size(), (uint32_t)kmer, (uint32_t)skip,
+                                toff.data(), cap, lo.data(), up.data()));
+  std::vector<std::vector<BWTInterval> > out(ws.size());
+  for (size_t q = 0; q < ws.size(); ++q)
+    for (uint64_t t = toff[q]; t < toff[q + 1]; ++t) {
+      BWTInterval iv;
+      iv.lower = lo[t];
+      iv.upper = up[t];
+      out[q].push_back(iv);
+    }
   return out;
 }
 

@@ -45,6 +45,12 @@ int main(int argc, char** argv) {
     }
     std::cout << "f " << p->getF(0) << p->getF(p->getPC('C')) << p->getF(p->getBWLen() - 1) << " char " << p->getChar(12345)
               << " occat " << p->getOccAt('G', 777) << "\n";
+    const std::vector<std::vector<BWTInterval> > tiles = rsb200::tileIntervalsBatch(&bwt, qs, 31, 4);
+    for (size_t i = 0; i < qs.size(); ++i) {
+      std::cout << "tiles " << tiles[i].size();
+      for (const BWTInterval& iv : tiles[i]) std::cout << ' ' << iv.lower << ' ' << iv.upper;
+      std::cout << "\n";
+    }
     try {
       rsb200::GpuBWT bad("/nonexistent.bwt");
       std::cout << "error none\n";

@@ -66,4 +66,11 @@ def test_shim_matches_oracle(tmp_path):
     n = P.bwlen
     assert tail[1] == P.get_f(0) + P.get_f(P.get_pc("C")) + P.get_f(n - 1)
     assert tail[3] == P.get_char(12345) and int(tail[5]) == P.get_occ_at("G", 777)
-    assert out[2 + len(qs)] == "error 1"
+    # tileIntervalsBatch: get_tiles (service.cpp:232-246) with kmer 31, skip 4, one line per query
+    for i, w in enumerate(qs):
+        f = out[2 + len(qs) + i].split()
+        tiles = [w[j:j + 31] for j in range(0, len(w) - 31 + 1, 5)] if len(w) >= 31 else []
+        assert f[0] == "tiles" and int(f[1]) == len(tiles)
+        got = [(int(f[2 + 2 * t]), int(f[3 + 2 * t])) for t in range(len(tiles))]
+        assert got == [(1, 0) if any(c not in "ACGT" for c in t) else P.find_interval(t) for t in tiles], w
+    assert out[2 + 2 * len(qs)] == "error 1"
