@@ -59,7 +59,8 @@ static int upload(rs_index* ix, const RsHostIndex& h) {
   CU(cudaStreamCreateWithFlags(&ix->stream, cudaStreamNonBlocking));
   CU(cudaStreamCreateWithFlags(&ix->s_h2d, cudaStreamNonBlocking));
   CU(cudaStreamCreateWithFlags(&ix->s_d2h, cudaStreamNonBlocking));
-  CU(cudaStreamCreateWithFlags(&ix->s_k2, cudaStreamNonBlocking));
+  ix->s_k[0] = ix->stream;
+  for (int i = 1; i < RS_SEARCH_STREAMS; ++i) CU(cudaStreamCreateWithFlags(&ix->s_k[i], cudaStreamNonBlocking));
   for (int i = 0; i < RS_MAX_CHUNKS; ++i) {
     CU(cudaEventCreateWithFlags(&ix->ev_in[i], cudaEventDisableTiming));
     CU(cudaEventCreateWithFlags(&ix->ev_done[i], cudaEventDisableTiming));
@@ -141,7 +142,8 @@ void rs_index_close(rs_index* ix) {
   if (ix->stream) cudaStreamDestroy(ix->stream);
   if (ix->s_h2d) cudaStreamDestroy(ix->s_h2d);
   if (ix->s_d2h) cudaStreamDestroy(ix->s_d2h);
-  if (ix->s_k2) cudaStreamDestroy(ix->s_k2);
+  for (int i = 1; i < RS_SEARCH_STREAMS; ++i)
+    if (ix->s_k[i]) cudaStreamDestroy(ix->s_k[i]);
   for (int i = 0; i < RS_MAX_CHUNKS; ++i) {
     if (ix->ev_in[i]) cudaEventDestroy(ix->ev_in[i]);
     if (ix->ev_done[i]) cudaEventDestroy(ix->ev_done[i]);
@@ -269,13 +271,24 @@ int rs_get_f_batch(const rs_index* ix, const uint64_t* index, size_t n, char* ou
   return char_like(ix, index, n, out, true);
 }
 
+/* search streams the pipelined calls rotate over (RS_B200_KSTREAMS in the environment overrides) */
+static size_t search_streams() {
+  static size_t v = 0;
+  if (!v) {
+    const char* e = getenv("RS_B200_KSTREAMS");
+    const long long x = e ? atoll(e) : 0;
+    v = (x >= 1 && x <= RS_SEARCH_STREAMS) ? (size_t)x : RS_SEARCH_STREAMS;
+  }
+  return v;
+}
+
 /* queries per pipelined chunk, at least (RS_B200_CHUNK in the environment overrides) */
 static size_t chunk_min() {
   static size_t v = 0;
   if (!v) {
     const char* e = getenv("RS_B200_CHUNK");
     const long long x = e ? atoll(e) : 0;
-    v = x >= 1024 ? (size_t)x : 131072;
+    v = x >= 1024 ? (size_t)x : 65536;
   }
   return v;
 }
@@ -298,8 +311,9 @@ static int find_host(const rs_index* ix, const char* text, const uint64_t* offse
   if (!offsets && Q >= 2 * chunk_min()) {
     /* Large fixed-k batch: split into chunks and run copy-in, search and copy-out of successive chunks
      * on separate streams, so the PCIe transfers hide behind the kernels (and vice versa).  Searches
-     * alternate between two streams: the tail of one chunk's kernel (few queries left, SMs draining)
-     * overlaps the head of the next. */
+     * rotate over four streams: the tail of one chunk's kernel (few queries left, SMs draining) overlaps
+     * the next ones.  Measured e2e on configs[1]: 1 stream 963, 2: 1050, 4: 1080, 4 with 64k chunks 1092 M q/s;
+     * the copies themselves (31 + 16 MB per 1 M queries) bound it at about 1.2 G q/s. */
     size_t nch = Q / chunk_min();
     if (nch > RS_MAX_CHUNKS) nch = RS_MAX_CHUNKS;
     const size_t per = (Q + nch - 1) / nch;
@@ -307,7 +321,7 @@ static int find_host(const rs_index* ix, const char* text, const uint64_t* offse
       const size_t q0 = c * per, qn = (q0 + per <= Q ? per : Q - q0);
       CU(cudaMemcpyAsync(d_text + q0 * k, text + q0 * k, qn * (size_t)k, cudaMemcpyHostToDevice, ix->s_h2d));
       CU(cudaEventRecord(ix->ev_in[c], ix->s_h2d));
-      cudaStream_t sk = (c & 1) ? ix->s_k2 : st;
+      cudaStream_t sk = ix->s_k[c % search_streams()];
       CU(cudaStreamWaitEvent(sk, ix->ev_in[c], 0));
       CU(rs_launch_find_interval(ix->dev, d_text + q0 * k, nullptr, (uint32_t)k, qn, d_lo + q0, d_up + q0, mode, strand,
                                  nullptr, sk));

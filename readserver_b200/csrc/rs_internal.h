@@ -16,6 +16,7 @@
 #include "rs_kernels.h"
 
 #define RS_MAX_CHUNKS 32
+#define RS_SEARCH_STREAMS 4
 
 int rs_fail(int code, const char* fmt, ...); /* records the thread's last error message */
 #define fail rs_fail
@@ -69,7 +70,8 @@ struct rs_index {
   uint64_t* d_stats = nullptr; /* [0] updateInterval steps, [1] LF-walk steps; null unless profiling is on */
   cudaStream_t stream = nullptr;
   /* copy-in / copy-out streams and per-chunk events of the pipelined host-pointer calls */
-  cudaStream_t s_h2d = nullptr, s_d2h = nullptr, s_k2 = nullptr;
+  cudaStream_t s_h2d = nullptr, s_d2h = nullptr;
+  cudaStream_t s_k[RS_SEARCH_STREAMS] = {}; /* search streams of the pipelined calls (s_k[0] = stream) */
   cudaEvent_t ev_in[RS_MAX_CHUNKS] = {}, ev_done[RS_MAX_CHUNKS] = {};
   mutable std::mutex mu; /* serialises the host-pointer calls (they share the scratch buffers) */
   mutable Scratch s_in, s_in2, s_out, s_out2, s_out3, s_out4;
