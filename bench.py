@@ -56,6 +56,8 @@ def parse():
     ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-random-roofline", action="store_true")
+    ap.add_argument("--sharded", type=int, default=64, choices=[0, 4, 16, 64],
+                    help="shards of the side measurement that splits the read set as the reference does (0 = skip)")
     ap.add_argument("--locate-queries", type=int, default=100_000, help="k-mers of the count+locate side measurement")
     return ap.parse_args()
 
@@ -85,15 +87,18 @@ def build_shard(args, device, rank):
     sai = built.sai.cpu().numpy().astype(np.uint64)
     ns, nsym = built.num_strings, built.num_symbols
     # the reads in builder input order, for the packed read table of the locate side measurement (rank 0 only)
-    reads_text = reads_off = None
-    if rank == 0 and args.impl == "ours" and args.locate_queries > 0 and int(lens.min()) == int(lens.max()):
-        reads_text = dg.ASCII[reads.cpu().numpy()].reshape(-1)
-        reads_off = np.arange(ns + 1, dtype=np.uint64) * np.uint64(reads.shape[1])
+    reads_text = reads_off = reads_dev = None
+    if rank == 0 and args.impl == "ours" and int(lens.min()) == int(lens.max()):
+        if args.locate_queries > 0:
+            reads_text = dg.ASCII[reads.cpu().numpy()].reshape(-1)
+            reads_off = np.arange(ns + 1, dtype=np.uint64) * np.uint64(reads.shape[1])
+        if args.sharded > 0 and device != "cpu":
+            reads_dev = reads
     del built, h2, reads, lens
     if device != "cpu":
         torch.cuda.empty_cache()
     return dict(runs=runs, num_strings=ns, num_symbols=nsym, sai=sai, queries=queries, genome=h1,
-                reads_text=reads_text, reads_off=reads_off, build_seconds=time.time() - t0)
+                reads_text=reads_text, reads_off=reads_off, reads_dev=reads_dev, build_seconds=time.time() - t0)
 
 
 def workload_name(args):
@@ -230,6 +235,79 @@ def k1_traffic():
         return float(d["dram_bytes_per_launch"]), d.get("source")
     except Exception:
         return None, None
+
+
+def sharded_measure(args, shard, B_whole, dq, engine, local_rank, stream, flush):
+    """Side measurement (configs[2] shape): the read set split into 4^p shards by its reads' reversed last p bases
+    (p = 3: the 64 keys of demo/permutations-3.txt, service.cpp:820), one BWT per shard, all on this GPU; every
+    shard searches the whole batch and the search kernel sums the per-shard counts (the front end's fan-in,
+    server.cpp:184-197, 404-410).  Checked: with exact rank the sum equals the count in the unsplit index."""
+    import torch
+    from readserver_b200 import datagen as dg
+    from readserver_b200 import sharding
+    reads = shard["reads_dev"]
+    n, L = reads.shape
+    p = {4: 1, 16: 2, 64: 3}[args.sharded]
+    dev = reads.device
+    key = torch.zeros(n, dtype=torch.int64, device=dev)
+    for j in range(p):
+        key = key * 4 + (reads[:, L - 1 - j].long() - 1)
+    t0 = time.time()
+    shards, sizes = [], []
+    for s in range(args.sharded):
+        idx = torch.nonzero(key == s).flatten()
+        if idx.numel() == 0:
+            continue
+        b = dg.build_bwt(reads[idx], torch.full((idx.numel(),), L, dtype=torch.int32, device=dev))
+        shards.append(engine.GpuBWT(runs=b.runs.cpu().numpy(), num_strings=b.num_strings, num_symbols=b.num_symbols,
+                                    device=local_rank))
+        sizes.append(int(shards[-1].info.hbm_bytes))
+        del b, idx
+    build_s = time.time() - t0
+    Q, k = args.queries, args.k
+    comm = sharding.connect_peers(engine.PeerComm(local_rank, 0, 1, Q), str(dev))
+
+    def step():
+        comm.begin(Q, stream)
+        for S in shards:
+            comm.accumulate(S, dq, k, Q, 0, stream)
+        return comm.finish(stream)
+
+    # parity: exact rank everywhere, shard sum == unsplit index
+    for S in shards:
+        S.set_tail_emulation(False)
+    B_whole.set_tail_emulation(False)
+    got = sharding.counts_view(step(), Q, dev).clone()
+    want = torch.empty(Q, dtype=torch.int64, device=dev)
+    B_whole.count_dev(dq, k, Q, 0, want, stream)
+    torch.cuda.synchronize()
+    ok = bool(torch.equal(got, want))
+    for S in shards:
+        S.set_tail_emulation(True)
+    B_whole.set_tail_emulation(True)
+    for _ in range(2):
+        step()
+    torch.cuda.synchronize()
+    ms = []
+    for _ in range(5):
+        flush.fill_(1)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        step()
+        e1.record()
+        torch.cuda.synchronize()
+        ms.append(e0.elapsed_time(e1))
+    t = sum(ms) / 1e3
+    out = {"shards": len(shards), "split": f"reads' reversed last {p} bases (service.cpp:820)", "queries_per_step": Q,
+           "population_queries_per_s": Q * len(ms) / t, "shard_queries_per_s": len(shards) * Q * len(ms) / t,
+           "ms_per_step": 1e3 * t / len(ms), "kernels_per_step": len(shards) + 2,
+           "shard_index_bytes_min_max": [min(sizes), max(sizes)], "sum_equals_unsplit_index_exact_rank": ok,
+           "build_seconds": round(build_s, 1)}
+    comm.close()
+    for S in shards:
+        S.close()
+    assert ok, "sum of per-shard counts differs from the unsplit index"
+    return out
 
 
 def pinned_array(engine, nbytes, dtype, shape):
@@ -421,6 +499,12 @@ def run_ours(args):
             del d_str, d_len
         del d_off, d_ri, d_st
 
+    sharded = None
+    if world == 1 and args.sharded > 0 and shard.get("reads_dev") is not None:
+        sharded = sharded_measure(args, shard, B, dq, engine, local_rank, stream, flush)
+        shard["reads_dev"] = None
+        torch.cuda.empty_cache()
+
     random_gbs = random_gbs_128 = None
     if world == 1 and not args.no_random_roofline:
         try:
@@ -479,6 +563,8 @@ def run_ours(args):
     }
     if locate:
         line["locate"] = locate
+    if sharded:
+        line["sharded"] = sharded
     if world == 1 and not args.no_cpu_baseline:
         cores = os.cpu_count() or 1
         r = cpu_find_interval(shard, hq, k, cores, target_seconds=args.cpu_seconds, steps=1)

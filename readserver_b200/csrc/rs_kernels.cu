@@ -502,11 +502,14 @@ cudaError_t rs_launch_find_interval(const rs_index_dev& ix, const uint8_t* text,
   rs_peers peers;
   memset(&peers, 0, sizeof(peers));
   if (peers_in) peers = *peers_in;
+  const bool packed_already = (mode == 3); /* mode 3 = mode 2 over keys an earlier call left in lower[] */
+  if (packed_already) mode = 2;
   if (mode == 2 && (!peers_in || offs || k > RS_PACK_MAX_K)) return cudaErrorInvalidValue;
   const bool ftab = ix.ftab && ix.ftab_k > 1;
   if (!offs && k >= 1 && k <= RS_PACK_MAX_K) {
-    k_pack_kmers<<<(unsigned)((Q + RS_THREADS - 1) / RS_THREADS), RS_THREADS, 0, st>>>(text, k, Q, mode >= 1 && strand == 1,
-                                                                                   lower);
+    if (!packed_already)
+      k_pack_kmers<<<(unsigned)((Q + RS_THREADS - 1) / RS_THREADS), RS_THREADS, 0, st>>>(text, k, Q, mode >= 1 && strand == 1,
+                                                                                     lower);
     if (ftab) RS_LAUNCH((k_find_interval<true, true>), Q, st, ix, text, offs, k, Q, lower, upper, mode, strand, stats, peers);
     else RS_LAUNCH((k_find_interval<false, true>), Q, st, ix, text, offs, k, Q, lower, upper, mode, strand, stats, peers);
   } else {

@@ -22,7 +22,8 @@ typedef struct rs_peers {
 
 /* mode 0: lower/upper; mode 1: counts into `lower` (strand 0 forward, 1 reverse complement);
  * mode 2: counts added into the owning rank's buffer through peer memory (`lower` = Q words of scratch,
- * fixed-length queries of k <= 31 only);
+ * fixed-length queries of k <= 31 only); mode 3: mode 2 reusing the packed queries an earlier mode-2 call on the
+ * same batch left in `lower` (several shards searched for one batch: the pre-pass runs once);
  * stats (nullable): += number of updateInterval steps executed (2 ranks each) */
 cudaError_t rs_launch_find_interval(const rs_index_dev& ix, const uint8_t* text, const uint64_t* offs, uint32_t k,
                                     uint64_t Q, uint64_t* lower, uint64_t* upper, int mode, int strand,

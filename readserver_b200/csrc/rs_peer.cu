@@ -27,6 +27,10 @@ struct rs_comm {
   uint64_t epoch = 0;
   uint64_t step_q = 0;                    /* queries of the step in progress */
   bool connected = false, in_step = false;
+  /* the batch whose packed form sits in the scratch area (one pre-pass per step, however many shards) */
+  const void* packed_src = nullptr;
+  int packed_k = 0, packed_strand = -1;
+  void* packed_stream = nullptr;
 };
 
 static size_t comm_bytes(uint64_t maxq) { return RS_COMM_HDR + 3 * maxq * sizeof(uint64_t); }
@@ -133,6 +137,7 @@ int rs_comm_begin(rs_comm* c, uint64_t Q, void* stream) {
   ++c->epoch;
   c->step_q = Q;
   c->in_step = true;
+  c->packed_src = nullptr;
   /* clear the NEXT step's buffer: peers add into it only after they passed this step's barrier, which
    * needs this rank's flag, which is written after this memset in stream order */
   CU(cudaMemsetAsync(comm_counts(c->base, c->max_queries, c->epoch + 1), 0, c->max_queries * sizeof(uint64_t),
@@ -153,8 +158,13 @@ int rs_count_accumulate_dev(const rs_index* ix, rs_comm* c, const void* d_kmers,
   peers.rank = c->rank;
   for (uint32_t r = 0; r < c->world; ++r) peers.buf[r] = comm_counts(c->peer_base[r], c->max_queries, c->epoch);
   uint64_t* scratch = reinterpret_cast<uint64_t*>(c->base + RS_COMM_HDR) + 2 * c->max_queries;
-  CU(rs_launch_find_interval(ix->dev, (const uint8_t*)d_kmers, nullptr, (uint32_t)k, Q, scratch, nullptr, 2, strand,
+  const bool reuse = c->packed_src == d_kmers && c->packed_k == k && c->packed_strand == strand && c->packed_stream == stream;
+  CU(rs_launch_find_interval(ix->dev, (const uint8_t*)d_kmers, nullptr, (uint32_t)k, Q, scratch, nullptr, reuse ? 3 : 2, strand,
                              (unsigned long long*)ix->d_stats, (cudaStream_t)stream, &peers));
+  c->packed_src = d_kmers;
+  c->packed_k = k;
+  c->packed_strand = strand;
+  c->packed_stream = stream;
   return RS_STATUS_OK;
 }
 

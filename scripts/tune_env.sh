@@ -3,7 +3,7 @@
 O=gpurun_out; mkdir -p $O; i=0
 for ev in "$@"; do
   i=$((i+1))
-  env $ev timeout 300 python bench.py --steps 60 --no-cpu-baseline --no-random-roofline --locate-queries 0 > $O/env_$i.json 2> $O/env_$i.err
+  env $ev timeout 300 python bench.py --steps 60 --no-cpu-baseline --no-random-roofline --locate-queries 0 --sharded 0 > $O/env_$i.json 2> $O/env_$i.err
   python - <<PY
 import json
 try:

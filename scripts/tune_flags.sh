@@ -4,7 +4,7 @@ O=gpurun_out; mkdir -p $O; i=0
 for fl in "$@"; do
   i=$((i+1))
   RS_NVCC_EXTRA="$fl" python -m readserver_b200.build --force > /dev/null 2>&1 || { echo "build [$fl] failed"; continue; }
-  timeout 300 python bench.py --steps 40 --no-cpu-baseline --no-random-roofline --locate-queries 0 > $O/flags_$i.json 2> $O/flags_$i.err
+  timeout 300 python bench.py --steps 40 --no-cpu-baseline --no-random-roofline --locate-queries 0 --sharded 0 > $O/flags_$i.json 2> $O/flags_$i.err
   python - <<PY
 import json
 try:
