@@ -17,11 +17,11 @@ if [ "${SKIP_REF:-0}" != 1 ]; then
 fi
 # launch list of the same command (serialised, cold-cache times: shares must agree, not absolutes)
 timeout 400 ncu --profile-from-start off --metrics gpu__time_duration.sum --clock-control none --csv \
-  --log-file $O/launches_$TAG.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-random-roofline \
+  --log-file $O/launches_$TAG.csv python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-random-roofline --sharded 0 \
   > $O/ncu_launches_$TAG.log 2>&1; echo "ncu list rc=$?"
 # one full capture of the dominant kernel
 timeout 500 ncu --profile-from-start off --set full --clock-control none --import-source on -k regex:k_find_interval -s 3 -c 1 \
-  -o $O/k1_$TAG -f python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-random-roofline --locate-queries 0 \
+  -o $O/k1_$TAG -f python bench.py --steps 2 --warmup 3 --no-cpu-baseline --no-random-roofline --locate-queries 0 --sharded 0 \
   > $O/ncu_full_$TAG.log 2>&1; echo "ncu full rc=$?"
 ncu -i $O/k1_$TAG.ncu-rep --page raw --csv > $O/k1_$TAG.raw.csv 2>/dev/null
 python profiles/ncu_summary.py $O/k1_$TAG.raw.csv > $O/k1_$TAG.summary.txt 2>&1; head -40 $O/k1_$TAG.summary.txt
