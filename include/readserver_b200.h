@@ -48,7 +48,7 @@ typedef struct rs_index_info {
   uint64_t bwlen;        /* getBWLen(), rlebwt.cpp:303-305                                   */
   uint64_t num_strings;  /* reads in the shard                                                */
   uint64_t num_runs;     /* run bytes of the .bwt                                             */
-  uint64_t num_blocks;   /* 128-byte blocks in HBM                                            */
+  uint64_t num_blocks;   /* 64-byte blocks in HBM                                             */
   uint64_t hbm_bytes;    /* blocks + directories + attached tables                            */
   uint64_t pc[5];        /* getPC for $,A,C,G,T                                               */
   uint64_t total[5];     /* occurrences of each symbol                                        */
@@ -63,7 +63,7 @@ typedef struct rs_index_info {
 
 /* ---- lifecycle -------------------------------------------------------------------------------- */
 /* RLEBWT::RLEBWT(filename) (src/bwt/rlebwt.cpp:11-32) + BWTReaderRLE (src/bwt/rlebwt_reader.cpp:21-48):
- * read an SGA binary RLE .bwt, re-encode it into 128-byte blocks and upload it to `device`. */
+ * read an SGA binary RLE .bwt, re-encode it into 64-byte blocks and upload it to `device`. */
 int rs_index_open(const char* bwt_path, int device, rs_index** out);
 /* Same from run bytes already in memory (sym<<5 | len, include/bwt/rlunit.h:8-16). */
 int rs_index_from_runs(const uint8_t* runs, uint64_t num_runs, uint64_t num_strings, uint64_t num_symbols,

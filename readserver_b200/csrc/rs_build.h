@@ -1,4 +1,4 @@
-/* Host-side re-encoder: SGA run bytes (.bwt) -> 128-byte blocks + directories (rs_layout.h).
+/* Host-side re-encoder: SGA run bytes (.bwt) -> 64-byte blocks + directories (rs_layout.h).
  * Takes the place of RLEBWT::initialiseFMIndex (src/bwt/rlebwt.cpp:34-148) and of the .bwt reader
  * (src/bwt/rlebwt_reader.cpp:21-48).  One streaming pass over the run bytes.
  */

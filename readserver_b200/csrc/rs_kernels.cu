@@ -109,7 +109,9 @@ __global__ void __launch_bounds__(RS_THREADS) k_pack_kmers(const uint8_t* __rest
  * interval went empty: query.cpp:35-37) picks up its next query on the following trip, so lanes never
  * idle behind a longer neighbour.  A step (updateInterval, query.cpp:11-15) whose two positions share
  * a block takes one trip; otherwise the second position is scanned on the next trip.
- *   mode 0: write lower/upper.   mode 1: write counts (count_reads, service.cpp:279-315), strand as given. */
+ *   mode 0: write lower/upper.   mode 1: write counts (count_reads, service.cpp:279-315), strand as given.
+ *   mode 2: add counts into the owning rank's buffer (rs_emit below). */
+
 /* Where a finished query's answer goes.  mode 0: lower/upper; mode 1: count into lower[];
  * mode 2 (packed queries only): the count is added into the accumulation buffer of the rank that
  * owns the k-mer -- its first four bases as a base-4 number, modulo the number of ranks -- directly

@@ -1,5 +1,5 @@
 """Shared test data: seeded synthetic read sets -> SGA-format run-length BWTs (datagen), the oracle
-handles over them, and the lane-group host replay (tests/emul).  TEST INFRASTRUCTURE."""
+handles over them, and the host replay of the device code (tests/emul).  TEST INFRASTRUCTURE."""
 from __future__ import annotations
 
 import ctypes as C
@@ -90,7 +90,7 @@ def write_case(case: Case, path: str) -> str:
 
 
 # ------------------------------------------------------------------------------------------------
-# lane-group host replay (tests/emul/rs_emul.cpp over the real builder + SWAR header)
+# host replay of the device code (tests/emul/rs_emul.cpp over the real builder + rs_ops.h)
 # ------------------------------------------------------------------------------------------------
 def build_emul() -> str:
     srcs = [os.path.join(EMUL_DIR, "rs_emul.cpp"), os.path.join(CSRC, "rs_build.cpp")]
