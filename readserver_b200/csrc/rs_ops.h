@@ -169,18 +169,19 @@ RS_HD void rs_occ2(const rs_index_dev& ix, uint32_t c, uint64_t i1, uint64_t i2,
   *r2 = none2 ? 0 : x2;
 }
 
-/* Symbol at pos (< n) and the rank of that symbol at pos, from one scan. */
+/* Symbol at pos (< n) and the rank of that symbol at pos, from one block. */
 RS_HD uint32_t rs_symbol_rank(const rs_index_dev& ix, uint64_t pos, uint64_t* rank) {
   const uint64_t b = rs_find_block(ix, pos);
   const rs_blk k = rs_load_block(ix, b);
   const int32_t t = (int32_t)((uint32_t)(pos - k.start) + 1u);
-  uint32_t sym = rs_words_symbol<RS_BLOCK_WORDS>(k.w, t);
-  if (sym > 4u) sym = 0u; /* unreachable for a well-formed index; keeps pc[] in bounds */
-  if (rank) {
-    uint32_t a, unused;
-    rs_words_rank<RS_BLOCK_WORDS, false>(k.w, sym, t, 0, &a, &unused);
-    *rank = rs_blk_count(k, sym) + a;
+  if (!rank) {
+    const uint32_t s = rs_words_symbol<RS_BLOCK_WORDS>(k.w, t);
+    return s > 4u ? 0u : s;
   }
+  uint32_t a;
+  uint32_t sym = rs_words_symbol_rank<RS_BLOCK_WORDS>(k.w, t, &a);
+  if (sym > 4u) sym = 0u; /* unreachable for a well-formed index; keeps pc[] in bounds */
+  *rank = rs_blk_count(k, sym) + a;
   return sym;
 }
 

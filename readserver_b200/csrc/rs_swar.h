@@ -130,6 +130,36 @@ RS_HD uint32_t rs_words_symbol(const uint32_t (&w)[NW], int32_t t) {
   return (bw >> (8 * byte + 5)) & 7u;
 }
 
+/* Symbol of the t-th symbol of the words (1 <= t <= total; 0xFF when outside) and, in *rank, the occurrences
+ * of that symbol among the first t symbols: one pass over the run lengths finds the word, one pass counts the
+ * matches in the words before it (the LF step of extractPrefix needs both, rlebwt.cpp:202-227 + 268-301). */
+template <int NW>
+RS_HD uint32_t rs_words_symbol_rank(const uint32_t (&w)[NW], int32_t t, uint32_t* rank) {
+  int32_t run = 0, rb = 0;
+  uint32_t bw = w[0];
+  int32_t jw = 0; /* index of the word holding the t-th symbol */
+#pragma unroll
+  for (int j = 0; j < NW; ++j) {
+    const int32_t end = run + (int32_t)rs_dot(w[j] & RS_LEN_MASK, RS_ONES, 0);
+    const uint32_t nxt = (j + 1 < NW) ? w[j + 1] : 0u;
+    if (end < t) { bw = nxt; rb = end; jw = j + 1; }
+    run = end;
+  }
+  *rank = 0;
+  if (t < 1 || t > run) return 0xFFu;
+  const uint32_t p = bw & RS_LEN_MASK;
+  const uint32_t byte = rs_w_byte_of(p, (uint32_t)(t - rb));
+  const uint32_t sym = (bw >> (8 * byte + 5)) & 7u;
+  const uint32_t cpat = sym * 0x20202020u;
+  uint32_t acc = 0;
+#pragma unroll
+  for (int j = 0; j < NW; ++j)
+    if (j < jw) acc = rs_dot(w[j] & RS_LEN_MASK, rs_w_match8(w[j], cpat), acc);
+  acc = rs_dot(rs_w_take(p, (uint32_t)(t - rb)), rs_w_match8(bw, cpat), acc);
+  *rank = acc >> 3;
+  return sym;
+}
+
 /* Occurrences of c in all the words. */
 template <int NW>
 RS_HD uint32_t rs_words_count_all(const uint32_t (&w)[NW], uint32_t c) {
