@@ -165,7 +165,7 @@ class ClockSampler:
 # ------------------------------------------------------------------------------------------------
 # CPU legs (the ONLY place bench.py touches oracle/)
 # ------------------------------------------------------------------------------------------------
-def cpu_find_interval(shard, queries_np, k, nthreads, target_seconds, steps=1, warmup=0):
+def cpu_find_interval(shard, queries_np, k, nthreads, target_seconds, steps=1, warmup=0, extras=False):
     """Times findInterval of the reference's CPU implementation on a bounded sample of the queries."""
     import oracle
     import torch
@@ -187,8 +187,35 @@ def cpu_find_interval(shard, queries_np, k, nthreads, target_seconds, steps=1, w
     for _ in range(steps):
         lo, up = ix.find_interval_batch(sample, k, nthreads=nthreads)
         secs.append(ix.last_seconds)
-    return dict(kind=ix.kind, n=n, seconds=secs, value=n * len(secs) / sum(secs), load_seconds=load_s,
-                lower=lo, upper=up)
+    out = dict(kind=ix.kind, n=n, seconds=secs, value=n * len(secs) / sum(secs), load_seconds=load_s,
+               lower=lo, upper=up)
+    if extras and ix.kind == "reference":
+        # (a) the reference as its Makefiles ship it (no -O flag), a few seconds of it; (b) the CPU locate leg:
+        # extractPrefix per hit row, the walk K2 replaces
+        try:
+            with tempfile.TemporaryDirectory() as d:
+                path = os.path.join(d, "shard.bwt")
+                dg.write_bwt(path, torch.from_numpy(shard["runs"]), shard["num_strings"], shard["num_symbols"])
+                slow = oracle.RefIndex(path, so=oracle.REF_O0_SO)
+            m = min(n, 200_000)
+            slow.find_interval_batch(sample[:m], k, nthreads=nthreads)
+            out["as_shipped_O0_value"] = m / max(slow.last_seconds, 1e-9)
+            slow.close()
+        except Exception as ex:  # the -O0 build is optional
+            out["as_shipped_O0_value"] = None
+            print(f"as-shipped reference leg skipped: {ex}", file=sys.stderr)
+        hit = np.nonzero(up >= lo)[0][:20_000]
+        rows = np.concatenate([np.arange(lo[i], min(up[i], lo[i] + 15) + 1, dtype=np.uint64) for i in hit]) if hit.size else np.zeros(0, np.uint64)
+        if rows.size:
+            rows = rows[:300_000]
+            ix.locate_batch(rows, nthreads=nthreads, prefix=True, postfix=False, max_steps=shard_read_len(shard) + 28)
+            out["locate_rows_per_s"] = rows.size / max(ix.last_seconds, 1e-9)
+            out["locate_rows"] = int(rows.size)
+    return out
+
+
+def shard_read_len(shard):
+    return int(shard["num_symbols"] // max(1, shard["num_strings"]))
 
 
 def run_reference(args):
@@ -567,11 +594,15 @@ def run_ours(args):
         line["sharded"] = sharded
     if world == 1 and not args.no_cpu_baseline:
         cores = os.cpu_count() or 1
-        r = cpu_find_interval(shard, hq, k, cores, target_seconds=args.cpu_seconds, steps=1)
+        r = cpu_find_interval(shard, hq, k, cores, target_seconds=args.cpu_seconds, steps=1, extras=True)
         ok = bool(np.array_equal(r["lower"], hlo[: r["n"]]) and np.array_equal(r["upper"], hup[: r["n"]]))
         line["cpu_baseline"] = {"value": r["value"], "unit": UNIT, "cores": cores, "kind": r["kind"],
                                 "sample": f"first {r['n']} of {Q} queries, {cores} threads striding the array",
-                                "gpu_results_bit_exact_on_sample": ok}
+                                "gpu_results_bit_exact_on_sample": ok,
+                                "as_shipped_O0_value": r.get("as_shipped_O0_value"),
+                                "locate_rows_per_s": r.get("locate_rows_per_s"), "locate_rows": r.get("locate_rows"),
+                                "note": "value: reference sources at -O2; as_shipped_O0_value: built without -O as its "
+                                        "Makefiles do; locate_rows_per_s: extractPrefix per hit row on the same threads"}
         assert ok, "GPU results differ from the CPU reference"
     print(json.dumps(line), file=_REAL_STDOUT, flush=True)
     if world > 1:
