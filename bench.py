@@ -461,6 +461,24 @@ def run_ours(args):
         dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
     e2e_s = float(e2e_t.item())
 
+    # the same through count_reads' batch call (service.cpp:279-315): 8 bytes back per query instead of 16
+    e2e_count = None
+    if world == 1:
+        hcnt, _p4 = pinned_array(engine, Q * 8, np.uint64, (Q,))
+        for _ in range(2):
+            assert L.rs_count_batch(B._h, hq.ctypes.data, k, Q, 0, hcnt.ctypes.data) == 0
+        cs = 0.0
+        nrep = max(3, args.steps // 4)
+        for _ in range(nrep):
+            flush.fill_(1)
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            rc = L.rs_count_batch(B._h, hq.ctypes.data, k, Q, 0, hcnt.ctypes.data)
+            cs += time.perf_counter() - t0
+            assert rc == 0
+        e2e_count = Q * nrep / cs
+        assert np.array_equal(hcnt, np.where(hup >= hlo, hup - hlo + 1, 0).astype(np.uint64)), "count != interval width"
+
     # results of the device path and of the host path agree (and, below, with the CPU reference)
     if world == 1:
         assert np.array_equal(dlo.cpu().numpy().view(np.uint64), hlo) and np.array_equal(dup.cpu().numpy().view(np.uint64), hup)
@@ -584,7 +602,9 @@ def run_ours(args):
             "random_access_peak_128B_lines": random_gbs_128,
         },
         "e2e": {"value": world * Q * args.steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": Q * k,
-                "d2h_bytes_per_step": 2 * Q * 8, "api": "rs_find_interval_batch (host pointers, pinned)"},
+                "d2h_bytes_per_step": 2 * Q * 8, "api": "rs_find_interval_batch (host pointers, pinned)",
+                "count_api_value": e2e_count,
+                "count_api": "rs_count_batch, forward strand: 8 bytes back per query (not the headline: kept beside it)"},
         "gpu_launches": args.steps * (2 if world == 1 else 3),  # k_pack_kmers + k_find_interval (+ k_peer_barrier)
         "clocks": clk,
     }

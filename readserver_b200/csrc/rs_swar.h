@@ -49,7 +49,13 @@ RS_HD int rs_ffs(uint32_t a) {
 /* 8 in every byte whose run symbol equals c (cpat = c * 0x20202020), else 0 */
 RS_HD uint32_t rs_w_match8(uint32_t w, uint32_t cpat) {
   const uint32_t x = (w ^ cpat) & RS_SYM_MASK;            /* 0 in the symbol bits where equal      */
-  return ~((x >> 5) + 0x07070707u) & 0x08080808u;         /* bit 3 stays clear only for x == 0     */
+#if defined(__CUDA_ARCH__)
+  /* (x >> 5) + 7 per byte as ONE multiply-high-add on the FMA pipe (the ALU pipe is the busy one) */
+  const uint32_t y = __umulhi(x, 0x08000000u) + 0x07070707u;
+#else
+  const uint32_t y = (x >> 5) + 0x07070707u;
+#endif
+  return ~y & 0x08080808u;                                /* bit 3 stays clear only for x == 0     */
 }
 
 /* byte j = number of symbols of run j that lie among the first tt symbols of the word;
@@ -85,19 +91,19 @@ RS_HD uint32_t rs_words_total(const uint32_t (&w)[NW]) {
 template <int NW, bool TWO>
 RS_HD void rs_words_rank(const uint32_t (&w)[NW], uint32_t c, int32_t t1, int32_t t2, uint32_t* r1, uint32_t* r2) {
   const uint32_t cpat = c * 0x20202020u;
-  int32_t run = 0;
+  uint32_t run = 0, accp = 0;    /* symbols / 8 x matches in the words seen so far (running dp4a sums) */
   uint32_t acc1 = 0, acc2 = 0;   /* 8 x count over fully included words           */
   uint32_t bw1 = w[0], bw2 = w[0]; /* first word that is not fully included        */
   int32_t rb1 = 0, rb2 = 0;      /* symbols before that word                       */
 #pragma unroll
   for (int j = 0; j < NW; ++j) {
     const uint32_t p = w[j] & RS_LEN_MASK;
-    const uint32_t cw = rs_dot(p, rs_w_match8(w[j], cpat), 0);
-    const int32_t end = run + (int32_t)rs_dot(p, RS_ONES, 0);
+    accp = rs_dot(p, rs_w_match8(w[j], cpat), accp);
+    run = rs_dot(p, RS_ONES, run);
+    const int32_t end = (int32_t)run;
     const uint32_t nxt = (j + 1 < NW) ? w[j + 1] : 0u;
-    if (end <= t1) { acc1 += cw; bw1 = nxt; rb1 = end; }
-    if (TWO && end <= t2) { acc2 += cw; bw2 = nxt; rb2 = end; }
-    run = end;
+    if (end <= t1) { acc1 = accp; bw1 = nxt; rb1 = end; }
+    if (TWO && end <= t2) { acc2 = accp; bw2 = nxt; rb2 = end; }
   }
   {
     int32_t tt = t1 - rb1;

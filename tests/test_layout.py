@@ -193,3 +193,39 @@ def test_etl_sample_file_parser(sos, meta, datasets, tmp_path):
     assert common.parse_etl(str(tmp_path / "missing"), sos, meta)[0] == 1
     open(path, "ab").write(b"ACGT\n")          # a read without its value line
     assert common.parse_etl(path, sos, meta)[0] == 5
+
+
+def test_fuzz_random_run_arrays_against_oracle():
+    """Random small run arrays (every symbol, every run length, block-boundary sizes): the device code replayed on
+    the host equals the oracle at every position; where the reference itself would read out of bounds (Q2) the
+    exact mode is checked against a plain decode instead."""
+    from hypothesis import given, settings, strategies as st, HealthCheck
+
+    @settings(max_examples=60, deadline=None, suppress_health_check=list(HealthCheck), derandomize=True)
+    @given(st.integers(1, 400), st.integers(0, 2**31 - 1), st.sampled_from([1, 2, 3, 31, 0]))
+    def run(nruns, seed, maxlen):
+        rng = np.random.default_rng(seed)
+        ln = rng.integers(1, 32, nruns) if maxlen == 0 else rng.integers(1, maxlen + 1, nruns)
+        runs = np.ascontiguousarray((rng.integers(0, 5, nruns) << 5 | ln).astype(np.uint8))
+        n = int(ln.sum())
+        E = common.Emul(common.Case("fuzz", runs, 1, n, np.zeros(1, np.uint64), None))
+        assert E.status == 0
+        idx = np.arange(n, dtype=np.uint64)
+        plain = np.repeat(runs >> 5, runs & 31)
+        if E.q2_safe:
+            P = oracle.PortIndex(runs=runs, num_strings=1, num_symbols=n)
+            for c in b"$ACGT":
+                s = np.full(n, c, dtype=np.uint8)
+                assert np.array_equal(E.occ(s, idx), P.get_occ_batch(s, idx))
+            assert np.array_equal(E.char(idx), P.get_char_batch(idx))
+        E.set_tail(False)
+        for code, c in enumerate(b"$ACGT"):
+            truth = np.cumsum(plain == code).astype(np.uint64)
+            assert np.array_equal(E.occ(np.full(n, c, dtype=np.uint8), idx), truth)
+            tot = int(truth[-1])
+            if tot:
+                want = np.nonzero(plain == code)[0].astype(np.uint64)
+                assert np.array_equal(E.occ_at(np.full(tot, c, np.uint8), np.arange(1, tot + 1, dtype=np.uint64)), want)
+        assert np.array_equal(E.char(idx), np.frombuffer(b"$ACGT", dtype=np.uint8)[plain])
+
+    run()
