@@ -127,7 +127,8 @@ RS_HD void rs_scan2(const rs_index_dev& ix, uint32_t c, uint64_t b, uint64_t p1,
   const rs_blk k = rs_load_block(ix, b);
   const uint32_t off = (uint32_t)(p1 - k.start) + 1u;
   uint32_t a1, a2;
-  rs_words_rank<RS_BLOCK_WORDS, true>(k.w, c, (int32_t)off, two ? (int32_t)(off + (uint32_t)(p2 - p1)) : -1, &a1, &a2);
+  rs_words_rank<RS_BLOCK_WORDS, true>(k.w, c, (int32_t)off, two ? (int32_t)(off + (uint32_t)(p2 - p1)) : -1, &a1, &a2,
+                                      ix.emulate_tail | 1u /* = 1, opaque to the assembler: rs_swar.h */);
   const uint64_t before = rs_blk_count(k, c);
   *x1 = before + a1;
   *x2 = before + a2;

@@ -89,30 +89,49 @@ RS_HD uint32_t rs_words_total(const uint32_t (&w)[NW]) {
  * (nothing) or >= the total (everything).  One pass: whole words before the target are added with
  * one dp4a; the single word the target falls into is kept aside and resolved once after the loop. */
 template <int NW, bool TWO>
-RS_HD void rs_words_rank(const uint32_t (&w)[NW], uint32_t c, int32_t t1, int32_t t2, uint32_t* r1, uint32_t* r2) {
+RS_HD void rs_words_rank(const uint32_t (&w)[NW], uint32_t c, int32_t t1, int32_t t2, uint32_t* r1, uint32_t* r2,
+                         uint32_t one = 1u) {
   const uint32_t cpat = c * 0x20202020u;
-  uint32_t run = 0, accp = 0;    /* symbols / 8 x matches in the words seen so far (running dp4a sums) */
+  int32_t run = 0;
   uint32_t acc1 = 0, acc2 = 0;   /* 8 x count over fully included words           */
   uint32_t bw1 = w[0], bw2 = w[0]; /* first word that is not fully included        */
-  int32_t rb1 = 0, rb2 = 0;      /* symbols before that word                       */
+  uint32_t rb1 = 0, rb2 = 0;     /* symbols before that word                       */
 #pragma unroll
   for (int j = 0; j < NW; ++j) {
     const uint32_t p = w[j] & RS_LEN_MASK;
-    accp = rs_dot(p, rs_w_match8(w[j], cpat), accp);
-    run = rs_dot(p, RS_ONES, run);
-    const int32_t end = (int32_t)run;
+    const uint32_t cw = rs_dot(p, rs_w_match8(w[j], cpat), 0);
+    const uint32_t len = rs_dot(p, RS_ONES, 0);
+    const int32_t end = run + (int32_t)len;
     const uint32_t nxt = (j + 1 < NW) ? w[j + 1] : 0u;
-    if (end <= t1) { acc1 = accp; bw1 = nxt; rb1 = end; }
-    if (TWO && end <= t2) { acc2 = accp; bw2 = nxt; rb2 = end; }
+    const uint32_t diff = nxt - w[j]; /* bw telescopes: w[0] + sum of the included differences = w[first excluded] */
+#if defined(__CUDA_ARCH__)
+    /* The ALU pipe (SEL / ISETP / LOP3 / IADD3, 16 lanes per cycle) is K1's busiest unit (ncu: 70 % against
+     * 10 % for the FMA pipe), so the three conditional updates per target are predicated multiply-adds, which
+     * issue on the FMA pipe; `one` is a 1 the assembler cannot see through (it would turn them back into adds). */
+    asm("{\n\t.reg .pred q;\n\tsetp.le.s32 q, %3, %4;\n\t@q mad.lo.u32 %0, %5, %8, %0;\n\t@q mad.lo.u32 %1, %6, %8, %1;\n\t"
+        "@q mad.lo.u32 %2, %7, %8, %2;\n\t}"
+        : "+r"(acc1), "+r"(rb1), "+r"(bw1)
+        : "r"(end), "r"(t1), "r"(cw), "r"(len), "r"(diff), "r"(one));
+    if (TWO)
+      asm("{\n\t.reg .pred q;\n\tsetp.le.s32 q, %3, %4;\n\t@q mad.lo.u32 %0, %5, %8, %0;\n\t@q mad.lo.u32 %1, %6, %8, %1;\n\t"
+          "@q mad.lo.u32 %2, %7, %8, %2;\n\t}"
+          : "+r"(acc2), "+r"(rb2), "+r"(bw2)
+          : "r"(end), "r"(t2), "r"(cw), "r"(len), "r"(diff), "r"(one));
+#else
+    (void)one;
+    if (end <= t1) { acc1 += cw; rb1 += len; bw1 += diff; }
+    if (TWO && end <= t2) { acc2 += cw; rb2 += len; bw2 += diff; }
+#endif
+    run = end;
   }
   {
-    int32_t tt = t1 - rb1;
+    int32_t tt = t1 - (int32_t)rb1;
     tt = tt < 0 ? 0 : (tt > 127 ? 127 : tt);
     acc1 = rs_dot(rs_w_take(bw1 & RS_LEN_MASK, (uint32_t)tt), rs_w_match8(bw1, cpat), acc1);
     *r1 = acc1 >> 3;
   }
   if (TWO) {
-    int32_t tt = t2 - rb2;
+    int32_t tt = t2 - (int32_t)rb2;
     tt = tt < 0 ? 0 : (tt > 127 ? 127 : tt);
     acc2 = rs_dot(rs_w_take(bw2 & RS_LEN_MASK, (uint32_t)tt), rs_w_match8(bw2, cpat), acc2);
     *r2 = acc2 >> 3;
