@@ -605,7 +605,7 @@ def run_ours(args):
                 "d2h_bytes_per_step": 2 * Q * 8, "api": "rs_find_interval_batch (host pointers, pinned)",
                 "count_api_value": e2e_count,
                 "count_api": "rs_count_batch, forward strand: 8 bytes back per query (not the headline: kept beside it)"},
-        "gpu_launches": args.steps * (2 if world == 1 else 3),  # k_pack_kmers + k_find_interval (+ k_peer_barrier)
+        "gpu_launches": args.steps * 3,  # k_pack_kmers + k_find_interval + k_search_flagged (N > 1: k_peer_barrier)
         "clocks": clk,
     }
     if locate:

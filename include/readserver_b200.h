@@ -211,6 +211,32 @@ int rs_reads_batch_dev(const rs_index* ix, const void* d_read_index, size_t n, u
 int rs_tile_intervals_batch(const rs_index* ix, const char* text, const uint64_t* offsets, size_t Q, uint32_t kmer,
                             uint32_t skip, uint64_t* tile_offsets, uint64_t capacity, uint64_t* lower, uint64_t* upper);
 
+/* ---- /gt seed stage: find_gt_reads (src/service/service.cpp:507-711) for a batch of site queries ---- */
+/* text/offsets: Q windows, already oriented and cut around the site as GtTask::run does (service.cpp:1027-1037);
+ * pos[q]: the site, 1-based, in window q.  Every window is cut into tiles of `kmer` bases every skip+1 bases
+ * ((len - kmer) / (skip + 1) + 1 of them, :1049); per tile the reference's interval search with its extension loop
+ * (while the interval holds more than max_interval_size rows: the constant 10000 of service.cpp:91) and its reach
+ * test on the rows' prefix / postfix lengths (indel allowance 4).  The union over a window's tiles comes back as
+ * sorted unique read indices (builder input order, through the .sai):
+ *   out_offsets[Q+1]  CSR offsets, always written when the call gets that far
+ *   read_index        capacity entries; RS_STATUS_CAPACITY if the sets do not fit
+ *   flags[Q]          RS_GT_FLAG_*: tiles on which the reference itself throws (THROW) or never returns (HANG)
+ *                     contribute no reads and mark their query; WALK marks rows whose walk was cut at max_steps
+ *   max_rows          bound on the candidate rows (before the reach test) the call may expand on the device;
+ *                     *candidate_rows (may be NULL) receives the number needed
+ * Needs the .sai table; postfix lengths come from the packed read table when one is attached (and rank is exact),
+ * else from the select walk. */
+#define RS_GT_KEEP_ALL 0u
+#define RS_GT_NEED_POSTFIX 1u
+#define RS_GT_NEED_PREFIX 2u
+#define RS_GT_FLAG_THROW 1u
+#define RS_GT_FLAG_HANG 2u
+#define RS_GT_FLAG_WALK 4u
+int rs_gt_reads_batch(const rs_index* ix, const char* text, const uint64_t* offsets, const uint64_t* pos, size_t Q,
+                      uint32_t kmer, uint32_t skip, uint64_t max_interval_size, uint32_t max_steps, uint64_t max_rows,
+                      uint64_t* out_offsets, uint64_t capacity, uint64_t* read_index, uint32_t* flags,
+                      uint64_t* candidate_rows);
+
 /* ---- fan-in of per-shard counts across the GPUs of one box ----------------------------------------
  * Replaces the front end's sum over shard replies (src/service/server.cpp:184-197, 404-410).  One
  * process per GPU; every rank searches the whole batch in its shards and each finished query's count

@@ -1,23 +1,6 @@
 /* C ABI, second part: count+locate pipeline, sample table, carrier sets (include/readserver_b200.h). */
 #include "rs_internal.h"
 
-namespace {
-/* stream-ordered temporaries for the *_dev pipeline (freed in stream order on scope exit) */
-struct Tmp {
-  cudaStream_t st;
-  std::vector<void*> ptrs;
-  explicit Tmp(cudaStream_t s) : st(s) {}
-  cudaError_t get(void** p, size_t bytes) {
-    cudaError_t e = cudaMallocAsync(p, bytes ? bytes : 8, st);
-    if (e == cudaSuccess) ptrs.push_back(*p);
-    return e;
-  }
-  ~Tmp() {
-    for (void* p : ptrs) cudaFreeAsync(p, st);
-  }
-};
-}  // namespace
-
 /* intervals -> hit offsets (device); returns total hits */
 static int hits_from_intervals(const uint64_t* d_lower, const uint64_t* d_upper, size_t Q, uint64_t max_hits,
                                uint64_t* d_hit_offsets, uint64_t* total, Tmp& tmp) {

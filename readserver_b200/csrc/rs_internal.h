@@ -48,6 +48,21 @@ struct Scratch {
   }
 };
 
+/* stream-ordered temporaries of a multi-kernel call (freed in stream order on scope exit) */
+struct Tmp {
+  cudaStream_t st;
+  std::vector<void*> ptrs;
+  explicit Tmp(cudaStream_t s) : st(s) {}
+  cudaError_t get(void** p, size_t bytes) {
+    cudaError_t e = cudaMallocAsync(p, bytes ? bytes : 8, st);
+    if (e == cudaSuccess) ptrs.push_back(*p);
+    return e;
+  }
+  ~Tmp() {
+    for (void* p : ptrs) cudaFreeAsync(p, st);
+  }
+};
+
 struct rs_index {
   int device = 0;
   rs_index_dev dev;

@@ -17,14 +17,6 @@
 
 #define RS_FULL 0xFFFFFFFFu
 
-/* alphabet.h:11-32: A,C,G,T -> 1..4, every other byte -> 0 ('$'); branch-free:
- * (ch >> 1) & 3 separates A,C,T,G (0,1,2,3); the byte must also equal the letter it selects. */
-__device__ __forceinline__ uint32_t rs_code(uint32_t ch) {
-  const uint32_t sel = ((ch >> 1) & 3u) * 8u;
-  const uint32_t letter = (0x47544341u >> sel) & 0xFFu; /* 'A','C','T','G' */
-  const uint32_t code = (0x03040201u >> sel) & 0xFFu;   /*  1 , 2 , 4 , 3  */
-  return ch == letter ? code : 0u;
-}
 __device__ __forceinline__ uint32_t rs_ascii(uint32_t code) { return (0x5447434124ull >> (8 * code)) & 0xFFu; }
 
 __global__ void __launch_bounds__(RS_THREADS) k_occ(const __grid_constant__ rs_index_dev ix, const uint8_t* __restrict__ syms,
@@ -173,7 +165,7 @@ __global__ void __launch_bounds__(RS_THREADS, RS_K1_BLOCKS)
       active = true;
       if (pk >> 63) { /* a byte outside ACGT */
         if (mode == 1) lower[q] = 0; /* service.cpp:299-301; mode 2: nothing to add */
-        /* mode 0 searches such a byte as '$' (alphabet.h:11-32): left flagged for the tail loop below */
+        /* mode 0: left flagged for the tail loop below, which searches it as the reference would */
         active = false;
       } else {
         const uint32_t c0 = (uint32_t)(pk & 3u) + 1u; /* initInterval (query.cpp:18-21) on the last character */
@@ -213,6 +205,9 @@ __global__ void __launch_bounds__(RS_THREADS, RS_K1_BLOCKS)
       if (bad) {
         if (mode == 1) lower[q] = 0;
         else { lower[q] = 1; upper[q] = 0; }
+        active = false;
+      } else if (mode == 0 && rs_is_stray(w[len - 1])) {
+        lower[q] = 1ull << 63; /* searched whole by the tail loop below */
         active = false;
       } else {
         /* initInterval (query.cpp:18-21) on the last character of the searched string */
@@ -263,6 +258,11 @@ __global__ void __launch_bounds__(RS_THREADS, RS_K1_BLOCKS)
         if (PACKED) c = (uint32_t)((pk >> (2 * (len - 1 - (uint32_t)j))) & 3u) + 1u;
         /* reverse complement: revcomp(w)[j] is the complement of w[len-1-j] */
         else c = rc ? 5u - rs_code(w[len - 1 - j]) : rs_code(w[j]);
+        if (!PACKED && mode == 0 && c == 0 && w[j] != '$') { /* a stray byte: the tail loop searches this query */
+          lower[next_q - stride] = 1ull << 63;
+          active = false;
+          continue;
+        }
         const uint64_t b1 = rs_find_block(ix, p1);
         b2 = (uint32_t)rs_find_block(ix, p2);
         two = (b1 == b2) && p2 >= p1;
@@ -296,27 +296,25 @@ __global__ void __launch_bounds__(RS_THREADS, RS_K1_BLOCKS)
       }
     }
   }
-  if (PACKED && mode == 0) {
-    /* the rare queries holding a byte outside ACGT, one whole findInterval each (query.cpp:24-41); a valid
-     * lower bound never has bit 63 set */
-    for (uint64_t q = (uint64_t)blockIdx.x * RS_THREADS + threadIdx.x; q < Q; q += stride) {
-      if (!(lower[q] >> 63)) continue;
-      w = text + q * (uint64_t)k;
-      c = rs_code(w[k - 1]);
-      lo = ix.pc[c];
-      hi = lo + ix.init_occ[c] - 1;
-      for (j = (int32_t)k - 2; j >= 0; --j) {
-        c = rs_code(w[j]);
-        uint64_t a1, a2;
-        rs_occ2(ix, c, lo - 1, hi, &a1, &a2);
-        ++nsteps;
-        lo = ix.pc[c] + a1;
-        hi = ix.pc[c] + a2 - 1;
-        if (lo > hi) break;
-      }
-      lower[q] = lo;
-      upper[q] = hi;
-    }
+  if (stats && nsteps) atomicAdd(stats, (unsigned long long)nsteps);
+}
+
+/* K1b.  The rare queries K1 left flagged (bit 63 of lower[q]: a byte outside "$ACGT"), one whole findInterval
+ * each, as the reference answers them (rs_find_interval_one).  A kernel of its own so that this path costs K1's
+ * loop no registers; when nothing is flagged it reads lower[] once (8 bytes per query, still in L2) and ends. */
+__global__ void __launch_bounds__(RS_THREADS)
+    k_search_flagged(const __grid_constant__ rs_index_dev ix, const uint8_t* __restrict__ text,
+                     const uint64_t* __restrict__ offs, uint32_t k, uint64_t Q, uint64_t* __restrict__ lower,
+                     uint64_t* __restrict__ upper, unsigned long long* __restrict__ stats) {
+  const uint64_t stride = (uint64_t)gridDim.x * RS_THREADS;
+  uint32_t nsteps = 0;
+  for (uint64_t q = (uint64_t)blockIdx.x * RS_THREADS + threadIdx.x; q < Q; q += stride) {
+    if (!(lower[q] >> 63)) continue; /* a valid lower bound never has bit 63 set */
+    const uint64_t base = offs ? offs[q] : q * (uint64_t)k;
+    uint64_t lo, hi;
+    nsteps += rs_find_interval_one(ix, text + base, offs ? offs[q + 1] - base : (uint64_t)k, &lo, &hi);
+    lower[q] = lo;
+    upper[q] = hi;
   }
   if (stats && nsteps) atomicAdd(stats, (unsigned long long)nsteps);
 }
@@ -517,6 +515,11 @@ cudaError_t rs_launch_find_interval(const rs_index_dev& ix, const uint8_t* text,
   } else {
     if (ftab) RS_LAUNCH((k_find_interval<true, false>), Q, st, ix, text, offs, k, Q, lower, upper, mode, strand, stats, peers);
     else RS_LAUNCH((k_find_interval<false, false>), Q, st, ix, text, offs, k, Q, lower, upper, mode, strand, stats, peers);
+  }
+  if (mode == 0) {
+    uint64_t blocks = (Q + 4 * RS_THREADS - 1) / (4 * RS_THREADS);
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    k_search_flagged<<<(unsigned)blocks, RS_THREADS, 0, st>>>(ix, text, offs, k, Q, lower, upper, stats);
   }
   return cudaGetLastError();
 }

@@ -186,6 +186,74 @@ RS_HD void rs_occ2(const rs_index_dev& ix, uint32_t c, uint64_t i1, uint64_t i2,
   *r2 = none2 ? 0 : x2;
 }
 
+/* alphabet.h:11-32: A,C,G,T -> 1..4, every other byte -> 0 ('$'); branch-free:
+ * (ch >> 1) & 3 separates A,C,T,G (0,1,2,3); the byte must also equal the letter it selects. */
+RS_HD uint32_t rs_code(uint32_t ch) {
+  const uint32_t sel = ((ch >> 1) & 3u) * 8u;
+  const uint32_t letter = (0x47544341u >> sel) & 0xFFu; /* 'A','C','T','G' */
+  const uint32_t code = (0x03040201u >> sel) & 0xFFu;   /*  1 , 2 , 4 , 3  */
+  return ch == letter ? code : 0u;
+}
+
+/* A query byte that is none of "$ACGT".  The reference gives it the '$' counters of its tree (getRank,
+ * alphabet.h:11-32) but compares CHARACTERS in the final run scan (rlebwt.cpp:286,293), where it matches no run:
+ * getOcc(stray, i) = number of '$' before the 64-run bottom bucket that holds position i (after the tail clamp).
+ * Callers keep such bytes away from findInterval except the /gt extension loop, which grows a
+ * tile over whatever the window holds (service.cpp:527-530). */
+RS_HD bool rs_is_stray(uint32_t ch) { return rs_code(ch) == 0 && ch != '$'; }
+
+/* getOcc(b, i) of the reference for a stray byte b.  The bucket boundary is recovered from the blocks themselves:
+ * position -> block and run inside it -> run index R; the bucket starts at run R & ~63, which lies in block
+ * (R & ~63) / RS_PAYLOAD; '$' before that block from its header, plus the '$' runs in front of the boundary.
+ * Plain byte loads: this path is rare and must not cost the kernels that inline it any registers. */
+RS_HD uint64_t rs_block_count_before(const rs_index_dev& ix, uint64_t b, uint32_t c);
+RS_HD uint64_t rs_occ_stray(const rs_index_dev& ix, uint64_t i) {
+  if (i == ~0ull) return 0;
+  uint64_t pos = rs_ref_pos(ix, i);
+  if (pos >= ix.n) pos = ix.n - 1;
+  const uint64_t b = rs_find_block(ix, pos);
+  const uint8_t* runs = rs_block_ptr(ix, b) + RS_HDR_BYTES;
+  uint64_t off = pos - rs_ld64(reinterpret_cast<const uint64_t*>(rs_block_ptr(ix, b)));
+  uint32_t r = 0;
+  while (r + 1 < RS_PAYLOAD && off >= (runs[r] & 31u)) off -= runs[r++] & 31u;
+  const uint64_t first = (b * RS_PAYLOAD + r) & ~63ull; /* first run of the bucket */
+  const uint64_t b2 = first / RS_PAYLOAD;
+  const uint32_t o = (uint32_t)(first % RS_PAYLOAD);
+  uint64_t d = rs_block_count_before(ix, b2, 0);
+  runs = rs_block_ptr(ix, b2) + RS_HDR_BYTES;
+  for (uint32_t t = 0; t < o; ++t)
+    if ((runs[t] >> 5) == 0) d += runs[t] & 31u;
+  return d;
+}
+
+/* findInterval (src/bwt/query.cpp:24-41) for one string of len >= 1 bytes, any byte value, as the reference
+ * answers it; returns the executed steps.  The batched kernel K1 is the fast path: this is for the rare queries
+ * it hands over (a byte outside "$ACGT") and for callers that search a handful of strings of varying length per
+ * thread (the /gt extension loop). */
+RS_HD uint32_t rs_find_interval_one(const rs_index_dev& ix, const uint8_t* w, uint64_t len, uint64_t* lower, uint64_t* upper) {
+  uint32_t c = rs_code(w[len - 1]);
+  uint64_t lo = ix.pc[c];
+  uint64_t hi = lo + (rs_is_stray(w[len - 1]) ? rs_occ_stray(ix, ix.n - 1) : ix.init_occ[c]) - 1;
+  uint32_t steps = 0;
+  for (uint64_t j = len - 1; j-- > 0;) {
+    c = rs_code(w[j]);
+    uint64_t a1, a2;
+    if (rs_is_stray(w[j])) {
+      a1 = rs_occ_stray(ix, lo - 1);
+      a2 = rs_occ_stray(ix, hi);
+    } else {
+      rs_occ2(ix, c, lo - 1, hi, &a1, &a2);
+    }
+    ++steps;
+    lo = ix.pc[c] + a1;
+    hi = ix.pc[c] + a2 - 1;
+    if (lo > hi) break;
+  }
+  *lower = lo;
+  *upper = hi;
+  return steps;
+}
+
 /* Symbol at pos (< n) and the rank of that symbol at pos, from one block. */
 RS_HD uint32_t rs_symbol_rank(const rs_index_dev& ix, uint64_t pos, uint64_t* rank) {
   const uint64_t b = rs_find_block(ix, pos);

@@ -24,6 +24,9 @@ _u64p = np.ctypeslib.ndpointer(dtype=np.uint64, flags="C_CONTIGUOUS")
 STATUS = {0: "OK", 1: "OPEN", 2: "MAGIC", 3: "SHORT", 4: "RUNBYTE", 5: "ARG", 6: "CUDA", 7: "TOO_LARGE", 8: "NO_TABLE", 9: "CAPACITY"}
 
 
+GT_FLAG_THROW, GT_FLAG_HANG, GT_FLAG_WALK = 1, 2, 4   # rs_gt_reads_batch flags (include/readserver_b200.h)
+
+
 class RsError(RuntimeError):
     def __init__(self, status: int, msg: str):
         super().__init__(f"readserver_b200: status {status} ({STATUS.get(status, '?')}): {msg}")
@@ -71,6 +74,7 @@ def lib() -> C.CDLL:
         "rs_reads_batch": (i32, [vp, vp, sz, C.c_uint32, vp, vp]),
         "rs_reads_batch_dev": (i32, [vp, vp, sz, C.c_uint32, vp, vp, vp]),
         "rs_tile_intervals_batch": (i32, [vp, vp, vp, sz, C.c_uint32, C.c_uint32, vp, u64, vp, vp]),
+        "rs_gt_reads_batch": (i32, [vp, vp, vp, vp, sz, C.c_uint32, C.c_uint32, u64, C.c_uint32, u64, vp, u64, vp, vp, vp]),
         "rs_comm_create": (i32, [i32, i32, i32, u64, C.POINTER(vp)]),
         "rs_comm_export": (i32, [vp, vp]),
         "rs_comm_connect": (i32, [vp, vp]),
@@ -429,6 +433,33 @@ class GpuBWT:
         _check(lib().rs_tile_intervals_batch(self._h, text.ctypes.data, offs.ctypes.data, len(bs), kmer, skip,
                                              toff.ctypes.data, cap, lo.ctypes.data, up.ctypes.data))
         return toff, lo[:cap], up[:cap]
+
+    def gt_reads(self, windows: list, pos, kmer: int, skip: int = 0, max_interval_size: int = 10000,
+                 max_steps: int = 1024, max_rows: int = 1 << 26):
+        """Seed stage of /gt, find_gt_reads over every tile (service.cpp:507-711, 1044-1072), for a batch of
+        oriented windows with their 1-based site positions.  Returns (offsets [Q+1], read_index, flags [Q],
+        candidate_rows): each window's sorted unique read indices and its GT_FLAG_* bits."""
+        bs = [w.encode() if isinstance(w, str) else bytes(w) for w in windows]
+        text = np.frombuffer(b"".join(bs) or b"\0", dtype=np.uint8)
+        offs = np.zeros(len(bs) + 1, dtype=np.uint64)
+        offs[1:] = np.cumsum([len(b) for b in bs])
+        pos = np.ascontiguousarray(pos, dtype=np.uint64)
+        assert pos.size == len(bs)
+        out_off = np.zeros(len(bs) + 1, dtype=np.uint64)
+        flags = np.zeros(max(len(bs), 1), dtype=np.uint32)
+        cand = C.c_uint64()
+        cap = 1 << 16
+        while True:
+            ri = np.empty(cap, dtype=np.uint64)
+            rc = lib().rs_gt_reads_batch(self._h, text.ctypes.data, offs.ctypes.data, pos.ctypes.data, len(bs), kmer, skip,
+                                         max_interval_size, max_steps, max_rows, out_off.ctypes.data, cap, ri.ctypes.data,
+                                         flags.ctypes.data, C.byref(cand))
+            if rc == 9 and int(cand.value) <= max_rows and int(out_off[-1]) > cap:  # RS_STATUS_CAPACITY on the output
+                cap = int(out_off[-1])
+                continue
+            _check(rc)
+            break
+        return out_off, ri[:int(out_off[-1])], flags[:len(bs)], int(cand.value)
 
     def count_dev(self, d_kmers, k: int, q: int, strand: int, d_counts, stream: int = 0):
         _check(lib().rs_count_batch_dev(self._h, _ptr(d_kmers), k, q, strand, _ptr(d_counts), stream))

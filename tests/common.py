@@ -94,7 +94,7 @@ def write_case(case: Case, path: str) -> str:
 # ------------------------------------------------------------------------------------------------
 def build_emul() -> str:
     srcs = [os.path.join(EMUL_DIR, "rs_emul.cpp"), os.path.join(CSRC, "rs_build.cpp")]
-    deps = srcs + [os.path.join(CSRC, h) for h in ("rs_build.h", "rs_layout.h", "rs_swar.h", "rs_ops.h")]
+    deps = srcs + [os.path.join(CSRC, h) for h in ("rs_build.h", "rs_layout.h", "rs_swar.h", "rs_ops.h", "rs_gt_ops.h")]
     if os.path.exists(EMUL_SO) and all(os.path.getmtime(d) <= os.path.getmtime(EMUL_SO) for d in deps):
         return EMUL_SO
     subprocess.run(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-Wall", "-Wno-unknown-pragmas", "-I", CSRC,
@@ -125,6 +125,8 @@ class Emul:
             L.emul_parse_etl.restype = C.c_int
             L.emul_parse_etl.argtypes = [C.c_char_p, C.c_int, C.c_int, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64,
                                          C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]
+            L.emul_gt_seeds.argtypes = [C.c_void_p, _u8p, C.c_uint64, C.c_uint64, C.c_uint64, C.c_uint32, C.c_uint32,
+                                        C.c_uint64, _u64p]
             L.emul_blocks.restype = C.c_void_p
             L.emul_blocks.argtypes = [C.c_void_p]
             cls._lib = L
@@ -182,6 +184,15 @@ class Emul:
         up = np.empty(q, dtype=np.uint64)
         self.lib().emul_find_interval_batch(self._h, kmers, k, q, lo, up)
         return lo, up
+
+    def gt_seeds(self, w: str, pos: int, kmers: int, skip: int, max_iv: int):
+        """per tile of window w: (lo0, hi0, thr0, lo1, hi1, thr1, kind, flags), the seed logic of rs_gt_ops.h"""
+        wb = np.frombuffer(w.encode(), dtype=np.uint8).copy()
+        nt = (len(w) - kmers) // (skip + 1) + 1 if len(w) >= kmers and pos <= len(w) else 0
+        out = np.zeros((nt, 8), dtype=np.uint64)
+        if nt:
+            self.lib().emul_gt_seeds(self._h, wb, wb.size, pos, nt, kmers, skip + 1, max_iv, out.reshape(-1))
+        return out
 
     def blocks(self) -> np.ndarray:
         """the raw 64-byte blocks as a [nblocks, 64] uint8 array (a copy)"""

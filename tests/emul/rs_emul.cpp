@@ -13,6 +13,7 @@
 
 #include "rs_build.h"
 #include "rs_layout.h"
+#include "rs_gt_ops.h"
 #include "rs_ops.h"
 
 namespace {
@@ -104,22 +105,9 @@ void emul_occ_at_batch(void* p, const uint8_t* b, const uint64_t* cnt, uint64_t 
 
 void emul_find_interval_batch(void* p, const uint8_t* kmers, int k, uint64_t Q, uint64_t* lower, uint64_t* upper) {
   const Emul& e = *(Emul*)p;
-  for (uint64_t q = 0; q < Q; ++q) {
-    const uint8_t* w = kmers + q * (uint64_t)k;
-    uint32_t c = code_of(w[k - 1]);
-    uint64_t lo = e.v.pc[c];
-    uint64_t hi = lo + e.v.init_occ[c] - 1;
-    for (int j = k - 2; j >= 0; --j) {
-      c = code_of(w[j]);
-      uint64_t r1, r2;
-      rs_occ2(e.v, c, lo - 1, hi, &r1, &r2); /* the two scans K1 spreads over one or two trips */
-      lo = e.v.pc[c] + r1;
-      hi = e.v.pc[c] + r2 - 1;
-      if (lo > hi) break;
-    }
-    lower[q] = lo;
-    upper[q] = hi;
-  }
+  /* the per-string search K1b and the /gt seed kernel run (any byte value); K1's own loop spreads the same
+   * rs_occ2 scans over one or two trips */
+  for (uint64_t q = 0; q < Q; ++q) rs_find_interval_one(e.v, kmers + q * (uint64_t)k, (uint64_t)k, lower + q, upper + q);
 }
 
 void emul_prefix_walk_batch(void* p, const uint64_t* rows, uint64_t n, uint32_t max_steps, uint64_t* lexrank,
@@ -166,6 +154,23 @@ void emul_postfix_walk_batch(void* p, const uint64_t* rows, uint64_t n, uint32_t
     }
     read_index[i] = term;
     steps[i] = s;
+  }
+}
+
+/* the per-tile seed logic of the /gt seed stage (rs_gt_ops.h, the source k_gt_seeds runs): out[i] =
+ * {lo0, hi0, thr0, lo1, hi1, thr1, kind, flags} for tile i of window w */
+void emul_gt_seeds(void* p, const uint8_t* w, uint64_t L, uint64_t pos, uint64_t ntiles, uint32_t kmers, uint32_t step,
+                   uint64_t max_iv, uint64_t* out) {
+  const Emul& e = *(Emul*)p;
+  for (uint64_t i = 0; i < ntiles; ++i) {
+    gt_iv seed[2];
+    uint64_t thr[2];
+    uint32_t kind, flag;
+    rs_gt_tile_seeds(e.v, w, L, pos, i, kmers, step, max_iv, seed, thr, &kind, &flag);
+    uint64_t* o = out + 8 * i;
+    o[0] = seed[0].lo, o[1] = seed[0].hi, o[2] = thr[0];
+    o[3] = seed[1].lo, o[4] = seed[1].hi, o[5] = thr[1];
+    o[6] = kind, o[7] = flag;
   }
 }
 

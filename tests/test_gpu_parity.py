@@ -58,6 +58,22 @@ def test_find_interval_matches_oracle(name, datasets, engine):
         for s, a, b in zip(strs[:-1], lo, up):
             assert (int(a), int(b)) == P.find_interval(s), s
         assert (int(lo[-1]), int(up[-1])) == (1, 0)
+        # bytes outside "$ACGT" (callers keep them away, SURVEY.md Q4, but the /gt extension loop does not): the
+        # reference gives them '$' counts at 64-run bucket granularity; packed (k <= 31), plain and ragged paths
+        rng = np.random.default_rng(3)
+        for k in (1, 3, 31, 32, 73):
+            q = case.queries(3000, k, seed=140 + k).copy()
+            for i in range(0, q.shape[0], 3):
+                for _ in range(1 + i % 2):
+                    q[i, int(rng.integers(0, k))] = [ord("N"), ord("$"), ord("n"), 0, 255, ord("X")][(i // 3) % 6]
+            lo, up = B.find_interval(q, k)
+            lo2, up2 = P.find_interval_batch(q, k, nthreads=4)
+            assert np.array_equal(lo, lo2) and np.array_equal(up, up2), ("stray", k)
+        strs = [bytes(case.queries(1, L, seed=190 + L)[0]).decode() for L in (37, 41, 100, 1, 200, 12)]
+        strs = [s[:len(s) // 2] + ch + s[len(s) // 2 + 1:] for s, ch in zip(strs, "NN$NxN")]
+        lo, up = B.find_interval_var(strs)
+        for s, a, b in zip(strs, lo, up):
+            assert (int(a), int(b)) == P.find_interval(s), s
 
 
 @pytest.mark.parametrize("name", ["small", "clean", "deep"])
@@ -247,13 +263,12 @@ def test_prefix_table_does_not_change_results(name, datasets, engine):
                 q[6, k - 1] = ord("$")
                 lo, up = B.find_interval(q, k)
                 lo2, up2 = P.find_interval_batch(q, k, nthreads=4)
-                ok = np.ones(len(q), dtype=bool)
-                ok[5] = False               # 'N' is outside the contract of findInterval
+                ok = np.ones(len(q), dtype=bool)  # query 5: the stray byte is searched as the reference does (K1b)
                 assert np.array_equal(lo[ok], lo2[ok]) and np.array_equal(up[ok], up2[ok]), (t, k)
                 rcq = np.ascontiguousarray(comp[q[:, ::-1]])
                 lo3, up3 = P.find_interval_batch(rcq, k, nthreads=4)
                 okc = ok.copy()
-                okc[6] = False
+                okc[5] = okc[6] = False     # count_reads answers 0 for anything outside ACGT (service.cpp:299-301)
                 want = np.where(up3 >= lo3, up3 - lo3 + 1, 0)
                 got = B.count(q, k, strand=1)
                 assert np.array_equal(got[okc], want[okc]) and got[5] == 0 and got[6] == 0, (t, k)
