@@ -254,6 +254,38 @@ inline std::vector<std::vector<BWTInterval> > tileIntervalsBatch(const GpuBWT* b
   return out;
 }
 
+// find_gt_reads over every tile of GtTask::run's loop (service.cpp:507-711, 1044-1072) for a batch of site
+// queries: ws[q] is the oriented window cut around the site, pos[q] the site's 1-based position in it.
+// result[q] = the sorted, unique read indices (builder input order) of the reads the reference would hand to the
+// aligner; flags[q] (optional) receives RS_GT_FLAG_* for windows on which the reference itself throws or hangs.
+inline std::vector<std::vector<uint64_t> > findGtReadsBatch(const GpuBWT* bwt, const std::vector<std::string>& ws,
+                                                            const std::vector<uint64_t>& pos, size_t kmer, size_t skip,
+                                                            uint64_t max_interval_size = 10000,
+                                                            std::vector<uint32_t>* flags = 0, uint32_t max_steps = 1024,
+                                                            uint64_t max_rows = (uint64_t)1 << 26) {
+  std::string text;
+  std::vector<uint64_t> offs;
+  detail::flatten(ws, text, offs);
+  std::vector<uint64_t> ooff(ws.size() + 1, 0), ri((size_t)1 << 12);
+  std::vector<uint32_t> fl(ws.size() ? ws.size() : 1, 0);
+  uint64_t cand = 0;
+  for (;;) {
+    const int rc = rs_gt_reads_batch(bwt->handle(), text.data(), offs.data(), pos.data(), ws.size(), (uint32_t)kmer,
+                                     (uint32_t)skip, max_interval_size, max_steps, max_rows, ooff.data(), ri.size(),
+                                     ri.data(), fl.data(), &cand);
+    if (rc == RS_STATUS_CAPACITY && cand <= max_rows && ooff[ws.size()] > ri.size()) {
+      ri.resize(ooff[ws.size()]);
+      continue;
+    }
+    check(rc);
+    break;
+  }
+  std::vector<std::vector<uint64_t> > out(ws.size());
+  for (size_t q = 0; q < ws.size(); ++q) out[q].assign(ri.begin() + ooff[q], ri.begin() + ooff[q + 1]);
+  if (flags) flags->assign(fl.begin(), fl.begin() + ws.size());
+  return out;
+}
+
 // query_exactmatch (query.cpp:102-120): is w one of the reads?
 inline bool query_exactmatch(const GpuBWT* bwt, const std::string& w, uint32_t max_len = 1024) {
   for (const std::string& s : query(bwt, w, max_len))

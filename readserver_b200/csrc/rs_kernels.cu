@@ -24,7 +24,7 @@ __global__ void __launch_bounds__(RS_THREADS) k_occ(const __grid_constant__ rs_i
                                                     uint64_t* __restrict__ out) {
   const uint64_t stride = (uint64_t)gridDim.x * RS_THREADS;
   for (uint64_t i = (uint64_t)blockIdx.x * RS_THREADS + threadIdx.x; i < n; i += stride)
-    out[i] = rs_occ(ix, rs_code(syms[i]), idx[i]);
+    out[i] = rs_occ_byte(ix, syms[i], idx[i]);
 }
 
 __global__ void __launch_bounds__(RS_THREADS) k_char(const __grid_constant__ rs_index_dev ix, const uint64_t* __restrict__ idx,

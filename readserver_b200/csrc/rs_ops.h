@@ -226,6 +226,11 @@ RS_HD uint64_t rs_occ_stray(const rs_index_dev& ix, uint64_t i) {
   return d;
 }
 
+/* getOcc(b, i) for any byte b (rlebwt.cpp:268-301) */
+RS_HD uint64_t rs_occ_byte(const rs_index_dev& ix, uint32_t ch, uint64_t i) {
+  return rs_is_stray(ch) ? rs_occ_stray(ix, i) : rs_occ(ix, rs_code(ch), i);
+}
+
 /* findInterval (src/bwt/query.cpp:24-41) for one string of len >= 1 bytes, any byte value, as the reference
  * answers it; returns the executed steps.  The batched kernel K1 is the fast path: this is for the rare queries
  * it hands over (a byte outside "$ACGT") and for callers that search a handful of strings of varying length per

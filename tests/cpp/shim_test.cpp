@@ -1,7 +1,7 @@
 // TEST PROGRAM for include/rs_gpu_bwt.hpp: drives the C++ mirror of the reference interface the way
 // the reference's worker does -- through a `const BWT*` (scalar virtual calls) and through the batched
 // replacements -- and prints the results for tests/test_cpp_shim.py to compare with the oracle.
-//   usage: shim_test <file.bwt> <queries.txt>
+//   usage: shim_test <file.bwt> <queries.txt> [file.sai.u64]
 #include <fstream>
 #include <iostream>
 
@@ -50,6 +50,21 @@ int main(int argc, char** argv) {
       std::cout << "tiles " << tiles[i].size();
       for (const BWTInterval& iv : tiles[i]) std::cout << ' ' << iv.lower << ' ' << iv.upper;
       std::cout << "\n";
+    }
+    if (argc > 3) {  // /gt seed stage: every query is a window with the site in its middle
+      std::ifstream sf(argv[3], std::ios::binary);
+      std::vector<uint64_t> sai;
+      for (uint64_t v; sf.read(reinterpret_cast<char*>(&v), 8);) sai.push_back(v);
+      bwt.setSai(sai);
+      std::vector<uint64_t> pos;
+      for (size_t i = 0; i < qs.size(); ++i) pos.push_back(qs[i].size() / 2 + 1);
+      std::vector<uint32_t> flags;
+      const std::vector<std::vector<uint64_t> > gt = rsb200::findGtReadsBatch(&bwt, qs, pos, 31, 7, 12, &flags);
+      for (size_t i = 0; i < qs.size(); ++i) {
+        std::cout << "gt " << flags[i] << ' ' << gt[i].size();
+        for (size_t j = 0; j < gt[i].size(); ++j) std::cout << ' ' << gt[i][j];
+        std::cout << "\n";
+      }
     }
     try {
       rsb200::GpuBWT bad("/nonexistent.bwt");

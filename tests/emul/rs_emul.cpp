@@ -87,7 +87,7 @@ const void* emul_blocks(void* p) { return ((Emul*)p)->h.blocks.data(); }
 
 void emul_occ_batch(void* p, const uint8_t* b, const uint64_t* idx, uint64_t n, uint64_t* out) {
   const Emul& e = *(Emul*)p;
-  for (uint64_t i = 0; i < n; ++i) out[i] = rs_occ(e.v, code_of(b[i]), idx[i]);
+  for (uint64_t i = 0; i < n; ++i) out[i] = rs_occ_byte(e.v, b[i], idx[i]);
 }
 
 void emul_char_batch(void* p, const uint64_t* idx, uint64_t n, uint8_t* out) {

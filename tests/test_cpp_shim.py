@@ -49,14 +49,15 @@ def test_shim_matches_oracle(tmp_path):
     qs = [bytes(k).decode() for k in z["kmers"][:40]] + [str(s) for s in z["var_queries"]] + ["ACGTNACGT"]
     qf = tmp_path / "q.txt"
     qf.write_text("\n".join(qs) + "\n")
-    out = subprocess.run([exe, bwt, str(qf)], check=True, capture_output=True, text=True).stdout.splitlines()
+    sf = tmp_path / "clean.sai.u64"
+    z["sai"].astype("<u8").tofile(str(sf))
+    out = subprocess.run([exe, bwt, str(qf), str(sf)], check=True, capture_output=True, text=True).stdout.splitlines()
     assert out[0] == f"bwlen {P.bwlen} pc " + " ".join(str(P.get_pc(c)) for c in "$ACGT")
     for i, (w, line) in enumerate(zip(qs, out[1:1 + len(qs)])):
         f = line.split()
         lo, up = P.find_interval(w)
-        ok = all(c in "ACGT" for c in w)   # other bytes never reach findInterval in the reference
-        if ok:
-            assert (int(f[1]), int(f[2]), int(f[3]), int(f[4])) == (lo, up, lo, up), w
+        ok = all(c in "ACGT" for c in w)   # query() answers nothing for other bytes (query.cpp:90)
+        assert (int(f[1]), int(f[2]), int(f[3]), int(f[4])) == (lo, up, lo, up), w
         if i < 16 or not ok:
             want = [P.extract_read(r) for r in range(lo, up + 1)] if ok and up >= lo else []
             if i < 16:
@@ -73,4 +74,14 @@ def test_shim_matches_oracle(tmp_path):
         assert f[0] == "tiles" and int(f[1]) == len(tiles)
         got = [(int(f[2 + 2 * t]), int(f[3 + 2 * t])) for t in range(len(tiles))]
         assert got == [(1, 0) if any(c not in "ACGT" for c in t) else P.find_interval(t) for t in tiles], w
-    assert out[2 + 2 * len(qs)] == "error 1"
+    # findGtReadsBatch: find_gt_reads over every tile (service.cpp:507-711), kmer 31, skip 7, intervals capped at 12
+    from oracle import gt as ogt
+    some = 0
+    for i, w in enumerate(qs):
+        f = out[2 + 2 * len(qs) + i].split()
+        reads, undefined = ogt.gt_task_reads(P, w, len(w) // 2 + 1, 31, 7, 12)
+        assert f[0] == "gt" and int(f[1]) == sum({"throw": 1, "hang": 2}[u] for u in undefined), w
+        assert [int(x) for x in f[3:]] == reads and int(f[2]) == len(reads), w
+        some += len(reads)
+    assert some > 0
+    assert out[2 + 3 * len(qs)] == "error 1"

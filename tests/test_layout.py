@@ -21,7 +21,9 @@ def test_rank_access_select_match_oracle(name, datasets):
     assert E.pc == [P.get_pc(c) for c in "$ACGT"]
     assert E.init_occ == [P.get_occ(c, E.n - 1) for c in "$ACGT"]
     idx = np.concatenate([common.positions(E.n), np.array([U64MAX], dtype=np.uint64)])
-    for c in b"$ACGT":  # other bytes never reach getOcc in the reference (its callers reject them)
+    # "$ACGT" and bytes outside it: the reference's callers reject those except the /gt extension
+    # loop; its getOcc then answers with '$' counts at 64-run bucket granularity (rs_occ_stray)
+    for c in b"$ACGTN\x00z":
         s = np.full(idx.size, c, dtype=np.uint8)
         assert np.array_equal(E.occ(s, idx), P.get_occ_batch(s, idx)), chr(c)
     assert np.array_equal(E.char(idx[:-1]), P.get_char_batch(idx[:-1]))
