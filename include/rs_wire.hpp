@@ -165,7 +165,10 @@ inline std::string encode_reply_reads(int32_t rt, const std::string& q, bool rev
 }
 
 // output=all (service.cpp:799-860): a { repeated forward_matches | revcomp_matches { r, repeated s } }
-inline std::string encode_reply_all(int32_t rt, const std::string& q, bool revcomp, const std::vector<ResultAll>& hits) {
+// QueryTask sets Reply.t to the request's return type and fills `a` for everything but Reads (service.cpp:1263,
+// 1292): a request with rt = Samples is answered with t = 4 and field `a`; hence reply_t.
+inline std::string encode_reply_all(int32_t rt, const std::string& q, bool revcomp, const std::vector<ResultAll>& hits,
+                                    int32_t reply_t = ReplyAll) {
   std::string a_msg;  // ReplyAll
   for (const ResultAll& h : hits) {
     std::string one;  // ResultAll
@@ -174,7 +177,7 @@ inline std::string encode_reply_all(int32_t rt, const std::string& q, bool revco
     put_bytes(a_msg, revcomp ? 2 : 1, one);
   }
   std::string out;
-  reply_head(out, rt, ReplyAll, q);
+  reply_head(out, rt, reply_t, q);
   put_bytes(out, 6, a_msg);
   return out;
 }

@@ -64,7 +64,7 @@ RS_HD void rs_gt_tile_seeds(const rs_index_dev& ix, const uint8_t* w, uint64_t L
           ++end;
         }
         if (ok) seed[0] = v, thr[0] = p - end;
-        if (index != 0) { /* then one base to the left and on */
+        if (ok && index != 0) { /* then one base to the left and on (not reached when the first loop hangs) */
           start = start0 - 1;
           end = end0;
           count = 1;
@@ -91,7 +91,7 @@ RS_HD void rs_gt_tile_seeds(const rs_index_dev& ix, const uint8_t* w, uint64_t L
           ok = gt_search(ix, w, L, start, kmers + count, &v, &flag);
         }
         if (ok) seed[0] = v, thr[0] = start - p;
-        if (end0 < L) { /* then one base to the right and on */
+        if (ok && end0 < L) { /* then one base to the right and on */
           start = start0;
           end = end0 + 1;
           count = 1;
@@ -118,7 +118,7 @@ RS_HD void rs_gt_tile_seeds(const rs_index_dev& ix, const uint8_t* w, uint64_t L
         if (ok) seed[0] = v;
         start = start0 - 1;
         count = 1;
-        ok = gt_search(ix, w, L, start, kmers + count, &v, &flag);
+        ok = ok && gt_search(ix, w, L, start, kmers + count, &v, &flag);
         while (ok && gt_wide(v, max_iv)) {
           ++count;
           --start;

@@ -41,7 +41,11 @@ def test_tile_seeds_match_restated_reference(kmers, skip, max_iv, datasets):
     case, P = datasets.case("clean"), datasets.port("clean")
     E = common.Emul(case)
     seen = {"wide": 0, "throw": 0, "hang": 0, "two": 0, 0: 0, 1: 0, 2: 0}
-    for w, pos in windows_of(case, 24, seed=kmers * 1000 + max_iv):
+    wins = windows_of(case, 24, seed=kmers * 1000 + max_iv)
+    # one-tile windows: an extension runs into both ends (the reference hangs in its first loop and never gets
+    # to the second one, which would throw)
+    wins += [(wins[1][0][:kmers], kmers // 2 + 1), (wins[2][0][:kmers + 3], 2), (wins[6][0][-kmers - 2:], kmers + 2)]
+    for w, pos in wins:
         got = E.gt_seeds(w, pos, kmers, skip, max_iv)
         tiles = (len(w) - kmers) // (skip + 1) + 1 if len(w) >= kmers and pos <= len(w) else 0
         assert got.shape[0] == tiles
@@ -116,6 +120,7 @@ def test_gt_reads_batch_on_gpu(kmers, skip, max_iv, datasets):
     case, P = datasets.case("clean"), datasets.port("clean")
     wins = windows_of(case, 40, seed=kmers * 1000 + max_iv)
     wins += [("ACGT", 2), ("", 0), (wins[0][0], len(wins[0][0]) + 1)]          # shorter than a tile; empty; pos > size
+    wins += [(wins[1][0][:kmers], kmers // 2 + 1), (wins[2][0][:kmers + 3], 2), (wins[6][0][-kmers - 2:], kmers + 2)]
     want = [ogt.gt_task_reads(P, w, pos, kmers, skip, max_iv) for w, pos in wins]
     with engine.GpuBWT(runs=case.runs, num_strings=case.num_strings, num_symbols=case.num_symbols) as B:
         with pytest.raises(engine.RsError):

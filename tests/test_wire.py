@@ -125,3 +125,83 @@ def test_count_batcher_sends_the_reference_replies(tmp_path):
     assert out[-1] == f"sent {len(want)}"
     assert out[skipped + 1:-1] == want
     assert sum(1 for w in want if not w.endswith("0800")) > 200  # most counts are non-zero
+
+
+@pytest.mark.gpu
+def test_query_batcher_replies_equal_query_task(tmp_path):
+    """rsb200::QueryBatcher against QueryTask::run (service.cpp:1259-1362) restated with google.protobuf over the
+    oracle: ExactMatch with output = reads / all / samples for k-mer queries, both strands, rows in find_reads'
+    order (an interval of more than 4,096 rows included), sample names through the hash file."""
+    import oracle
+    M = proto_schema.build()
+    lib = rs_build.build()
+    exe = os.path.join(CPP, "query_service_test")
+    subprocess.run(["g++", "-std=c++11", "-O1", "-Wall", "-I", os.path.join(ROOT, "include"),
+                    os.path.join(CPP, "query_service_test.cpp"), "-o", exe, "-L", os.path.dirname(lib), "-lrs_b200",
+                    "-Wl,-rpath," + os.path.dirname(lib)], check=True)
+    bwt = os.path.join(common.GOLDEN, "clean.bwt")
+    z = np.load(os.path.join(common.GOLDEN, "clean.npz"))
+    P = oracle.PortIndex(bwt)
+    gold = common.make_case("clean", *common.Datasets.SPECS["clean"][:3], min_len=73, keep_reads=True)
+    sos, nsamples = 1, 40
+    rng = np.random.default_rng(4)
+    per_read = rng.integers(1, 4, gold.num_strings)
+    off = np.zeros(gold.num_strings + 1, dtype=np.uint64)
+    off[1:] = np.cumsum(per_read)
+    who = rng.integers(0, nsamples, int(off[-1]))
+    codes = np.frombuffer(b"".join(oracle.sample_code(int(s), sos) for s in who), dtype=np.uint8)
+    etl = str(tmp_path / "merged.rlosorted.reads")
+    common.write_etl_file(etl, gold.reads, off, codes, sos, False)
+    names = {oracle.sample_code(s, sos): f"SAMPLE{s:03d}" for s in range(nsamples)}
+    hashfile = tmp_path / "hash.txt"
+    hashfile.write_bytes(b"".join(n.encode() + b"\t" + c + b"\n" for c, n in names.items()))
+
+    qs = [bytes(k).decode() for k in z["kmers"][:60]] + ["ACGTNACGT", "ACG", "A" * 80, "GATTACA"]
+    comp = str.maketrans("ACGT", "TGCA")
+    reqs, want, skipped = [], [], 0
+    for i, q in enumerate(qs):
+        rt = (2, 3, 4)[i % 3]
+        t = 2
+        if i % 20 == 19:
+            t, rt = 1, 1                             # CountReads: not this batcher's
+        reqs.append(M["Request"](t=t, rt=rt, q=q).SerializeToString().hex())
+        if t != 2 or len(q) >= 73:
+            skipped += 1
+            continue
+        for rev in (False, True):
+            s = q[::-1].translate(comp) if rev else q
+            lo, up = P.find_interval(s)
+            rows = []
+            if up >= lo:
+                start = lo
+                while up - start > 4096:
+                    start += 2048
+                rows = list(range(start, up + 1)) + list(range(lo, start))
+            r = M["Reply"]()
+            r.rt, r.t, r.q = 2, rt, q
+            if rt == 2:
+                r.r.SetInParent()
+                for row in rows:
+                    (r.r.revcomp_matches if rev else r.r.forward_matches).add().r = P.extract_read(row)
+            else:
+                r.a.SetInParent()
+                for row in rows:
+                    one = (r.a.revcomp_matches if rev else r.a.forward_matches).add()
+                    one.r = P.extract_read(row)
+                    ri = P.extract_postfix(row)[1]
+                    for c in range(int(off[ri]), int(off[ri + 1])):
+                        info = one.s.add()
+                        info.g, info.c, info.l = names[oracle.sample_code(int(who[c]), sos)], 0, 0
+            want.append(r.SerializeToString().hex())
+    f = tmp_path / "req.hex"
+    f.write_text("\n".join(reqs) + "\n")
+    out = subprocess.run([exe, bwt, str(f), etl, str(hashfile), str(sos)], check=True, capture_output=True,
+                         text=True).stdout.splitlines()
+    assert out[:skipped] == ["skip"] * skipped
+    assert out[skipped] == f"pending {len(qs) - skipped}"
+    assert out[-1] == f"sent {len(want)}"
+    got = out[skipped + 1:-1]
+    assert len(got) == len(want)
+    for g, w in zip(got, want):
+        assert g == w
+    assert max(len(w) for w in want) > 4096 * 73 * 2   # the 3-mer's reply holds more than 4,096 reads
