@@ -542,6 +542,28 @@ def run_ours(args):
                                           "note": "rs_reads_batch_dev on the located read indices (replaces extractPrefix + "
                                                   "extractPostfix per row, query.cpp:87-100)"}
             del d_str, d_len
+        if hits:
+            # config-5 style tail: hit reads -> sample codes -> sorted distinct sample set per k-mer (K3), through the
+            # host-pointer call (copies inside); synthetic table: 100 samples, 1-3 codes per read
+            rng = np.random.default_rng(11)
+            ns = int(shard["num_strings"])
+            soff = np.zeros(ns + 1, dtype=np.uint64)
+            np.cumsum(rng.integers(1, 4, ns), out=soff[1:])
+            scodes = (rng.integers(0, 100, int(soff[-1])) + 34).astype(np.uint8)   # code of sample s: s + 1 + 33
+            B.set_samples(soff, scodes, 1)
+            h_off = d_off.cpu().numpy().view(np.uint64)
+            h_ri = d_ri[:hits].cpu().numpy().view(np.uint64)
+            B.carriers(h_off, h_ri)
+            cs = []
+            for _ in range(3):
+                t0 = time.perf_counter()
+                coff, ccodes = B.carriers(h_off, h_ri)
+                cs.append(time.perf_counter() - t0)
+            locate["sample_sets"] = {"kmers_per_s": QL / min(cs), "hit_reads_per_s": hits / min(cs), "ms": 1e3 * min(cs),
+                                     "samples_out": int(coff[-1]), "note": "rs_carriers_batch (host pointers, two passes: "
+                                     "sizes, then codes): RocksDB Get + decode + set union per k-mer in the reference "
+                                     "(service.cpp:816-845)"}
+            del soff, scodes
         del d_off, d_ri, d_st
 
     sharded = None
