@@ -47,10 +47,12 @@ static int build_ftab(rs_index* ix, uint32_t t) {
 static uint32_t auto_ftab_k(const rs_index* ix) {
   const char* e = getenv("RS_B200_FTAB");
   if (e) return (uint32_t)atoi(e);
-  /* largest t <= 10 whose table is at most a quarter of the blocks */
-  const uint64_t budget = ix->dev.nblocks * (uint64_t)RS_BLOCK_BYTES / 4;
+  /* largest t <= 12 whose table is no larger than the blocks.  One 16-byte read per query replaces t - 1 steps of
+   * two block reads each, so the table pays even when it is far larger than L2 (configs[1], M q/s: t = 8: 1540,
+   * 9: 1598, 10: 1674, 11: 1802, 12: 1842 with a table 2.4 times the blocks) */
+  const uint64_t budget = ix->dev.nblocks * (uint64_t)RS_BLOCK_BYTES;
   uint32_t t = 0;
-  while (t < 10 && (16ull << (2 * (t + 1))) <= budget) ++t;
+  while (t < 12 && (16ull << (2 * (t + 1))) <= budget) ++t;
   return t;
 }
 
@@ -283,14 +285,46 @@ static size_t search_streams() {
 }
 
 /* queries per pipelined chunk, at least (RS_B200_CHUNK in the environment overrides) */
-static size_t chunk_min() {
+/* Chunk schedule of the pipelined host-pointer calls.  Every copy costs a few microseconds of its own (1 M
+ * 31-mers in and their intervals out, alone on the link: 618 us as one copy each way, 778 us as 15, 875 us as
+ * 30), so chunks should be large; but nothing overlaps the first chunk's copy-in nor the last chunk's search and
+ * copy-out, so those should be small.  Hence: RS_CHUNK_SMALL, doubling up to the big size, the bulk in equal big
+ * chunks, then two small ones.  RS_B200_CHUNK = big size, RS_B200_CHUNK_SMALL = first / last size. */
+static size_t env_size(const char* name, size_t dflt) {
+  const char* e = getenv(name);
+  const long long x = e ? atoll(e) : 0;
+  return x >= 1024 ? (size_t)x : dflt;
+}
+static size_t chunk_big() {
   static size_t v = 0;
-  if (!v) {
-    const char* e = getenv("RS_B200_CHUNK");
-    const long long x = e ? atoll(e) : 0;
-    v = x >= 1024 ? (size_t)x : 65536;
-  }
+  if (!v) v = env_size("RS_B200_CHUNK", 200000);
   return v;
+}
+static size_t chunk_small() {
+  static size_t v = 0;
+  if (!v) v = env_size("RS_B200_CHUNK_SMALL", 49152);
+  return v;
+}
+static std::vector<size_t> chunk_schedule(size_t Q) {
+  const size_t big = chunk_big(), small = chunk_small() < big ? chunk_small() : big;
+  std::vector<size_t> sz;
+  const size_t tail = 3 * small; /* 2 * small, small */
+  size_t used = 0;
+  for (size_t up = small; up < big && used + up + tail + big <= Q; up *= 2) {
+    sz.push_back(up);
+    used += up;
+  }
+  size_t mid = Q - used - tail;
+  size_t nmid = (mid + big - 1) / big;
+  if (sz.size() + nmid + 2 > RS_MAX_CHUNKS) nmid = RS_MAX_CHUNKS - 2 - sz.size();
+  for (size_t i = 0; i < nmid; ++i) {
+    const size_t per = (mid + (nmid - i) - 1) / (nmid - i);
+    sz.push_back(per);
+    mid -= per;
+  }
+  sz.push_back(2 * small);
+  sz.push_back(small);
+  return sz;
 }
 
 static int find_host(const rs_index* ix, const char* text, const uint64_t* offsets, int k, size_t Q, uint64_t* lower,
@@ -308,17 +342,16 @@ static int find_host(const rs_index* ix, const char* text, const uint64_t* offse
   cudaStream_t st = ix->stream;
   uint8_t* d_text = (uint8_t*)ix->s_in.p;
   uint64_t *d_lo = (uint64_t*)ix->s_out.p, *d_up = (uint64_t*)ix->s_out2.p;
-  if (!offsets && Q >= 2 * chunk_min()) {
+  if (!offsets && Q >= chunk_big() + 4 * chunk_small()) {
     /* Large fixed-k batch: split into chunks and run copy-in, search and copy-out of successive chunks
      * on separate streams, so the PCIe transfers hide behind the kernels (and vice versa).  Searches
      * rotate over four streams: the tail of one chunk's kernel (few queries left, SMs draining) overlaps
-     * the next ones.  Measured e2e on configs[1]: 1 stream 963, 2: 1050, 4: 1080, 4 with 64k chunks 1092 M q/s;
-     * the copies themselves (31 + 16 MB per 1 M queries) bound it at about 1.2 G q/s. */
-    size_t nch = Q / chunk_min();
-    if (nch > RS_MAX_CHUNKS) nch = RS_MAX_CHUNKS;
-    const size_t per = (Q + nch - 1) / nch;
-    for (size_t c = 0; c < nch; ++c) {
-      const size_t q0 = c * per, qn = (q0 + per <= Q ? per : Q - q0);
+     * the next ones.  Measured e2e on configs[1]: 1 stream 963, 2: 1050, 4: 1080 M q/s with equal 64k chunks;
+     * the copies alone, cut the same way, allow about 1.2-1.3 G q/s (scripts/pcie_probe.py). */
+    const std::vector<size_t> sz = chunk_schedule(Q);
+    size_t q0 = 0;
+    for (size_t c = 0; c < sz.size(); ++c) {
+      const size_t qn = sz[c];
       CU(cudaMemcpyAsync(d_text + q0 * k, text + q0 * k, qn * (size_t)k, cudaMemcpyHostToDevice, ix->s_h2d));
       CU(cudaEventRecord(ix->ev_in[c], ix->s_h2d));
       cudaStream_t sk = ix->s_k[c % search_streams()];
@@ -329,6 +362,7 @@ static int find_host(const rs_index* ix, const char* text, const uint64_t* offse
       CU(cudaStreamWaitEvent(ix->s_d2h, ix->ev_done[c], 0));
       CU(cudaMemcpyAsync(lower + q0, d_lo + q0, qn * 8, cudaMemcpyDeviceToHost, ix->s_d2h));
       if (mode == 0) CU(cudaMemcpyAsync(upper + q0, d_up + q0, qn * 8, cudaMemcpyDeviceToHost, ix->s_d2h));
+      q0 += qn;
     }
     CU(cudaStreamSynchronize(ix->s_d2h));
     return RS_STATUS_OK;
