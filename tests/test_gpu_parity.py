@@ -76,6 +76,27 @@ def test_find_interval_matches_oracle(name, datasets, engine):
             assert (int(a), int(b)) == P.find_interval(s), s
 
 
+def test_large_host_batch_goes_through_the_chunk_pipeline(datasets, engine):
+    """Host-pointer calls with several hundred thousand queries are cut into chunks (copy-in, search, copy-out on
+    separate streams, ramped chunk sizes): results must not depend on the cut, for intervals and for counts."""
+    case, P = datasets.case("mid"), datasets.port("mid")
+    for Q in (291_072, 400_001, 1_000_003):
+        q = case.queries(Q, 31, seed=77)
+        q[Q // 3, 5] = ord("N")
+        with _gpu(engine, case) as B:
+            lo, up = B.find_interval(q, 31)
+            cnt = B.count(q, 31, strand=0)
+            lo_s, up_s = B.find_interval(q[:50_000], 31)          # below the pipeline threshold: one launch
+        assert np.array_equal(lo[:50_000], lo_s) and np.array_equal(up[:50_000], up_s)
+        n = 120_000
+        sel = np.concatenate([np.arange(n), np.arange(Q - n, Q)])
+        lo2, up2 = P.find_interval_batch(q[sel], 31, nthreads=8)
+        assert np.array_equal(lo[sel], lo2) and np.array_equal(up[sel], up2), Q
+        want = np.where(up >= lo, up - lo + 1, 0)
+        want[Q // 3] = 0
+        assert np.array_equal(cnt, want), Q
+
+
 @pytest.mark.parametrize("name", ["small", "clean", "deep"])
 def test_count_reads_both_strands(name, datasets, engine):
     case, P = datasets.case(name), datasets.port(name)
