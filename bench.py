@@ -513,6 +513,36 @@ def run_ours(args):
                   "walk_steps_per_step": wsteps / len(lms),
                   "achieved_GBps": (2.0 * isteps + wsteps) * BYTES_PER_RANK / lt / 1e9,
                   "kernels_per_step": 5, "note": "includes one stream sync per step to size the hit list"}
+        # the same stage with the locate table (8 bytes per BWT row of HBM: one read per hit row instead of a walk)
+        try:
+            t0 = time.perf_counter()
+            B.build_locate_table(args.read_len + 28)
+            torch.cuda.synchronize()
+            build_s = time.perf_counter() - t0
+            d_ri2 = torch.empty(cap, dtype=torch.int64, device=dev)
+            d_st2 = torch.empty(cap, dtype=torch.int32, device=dev)
+            B.locate_dev(dq, k, QL, max_hits, max_steps, d_off, cap, None, None, d_ri2, d_st2, stream)
+            torch.cuda.synchronize()
+            same = bool(torch.equal(d_ri[:hits], d_ri2[:hits]) and torch.equal(d_st[:hits], d_st2[:hits]))
+            tms = []
+            for _ in range(max(3, args.steps // 4)):
+                flush.fill_(1)
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record()
+                B.locate_dev(dq, k, QL, max_hits, max_steps, d_off, cap, None, None, d_ri2, d_st2, stream)
+                e1.record()
+                torch.cuda.synchronize()
+                tms.append(e0.elapsed_time(e1))
+            tt = sum(tms) / 1e3
+            locate["with_locate_table"] = {"value": QL * len(tms) / tt, "unit": UNIT, "hit_rows_per_s": hits * len(tms) / tt,
+                                           "ms_per_step": 1e3 * tt / len(tms), "table_bytes": 8 * (int(shard["num_symbols"]) + int(shard["num_strings"])),
+                                           "build_seconds": build_s, "equals_walk": same,
+                                           "note": "rs_index_build_locate_table: where each row's walk ends, found once by "
+                                                   "walking every read (n LF steps)"}
+            B.drop_locate_table()
+            del d_ri2, d_st2
+        except engine.RsError as ex:
+            locate["with_locate_table"] = {"unavailable": str(ex)}
         if shard.get("reads_text") is not None and hits:
             # output=reads from the packed read table, addressed by the read indices just located
             B.set_reads_arrays(shard["reads_text"], shard["reads_off"])

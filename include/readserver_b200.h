@@ -76,6 +76,15 @@ int rs_index_set_tail_emulation(rs_index* ix, int on);
  * 4^k strings of length k, so that findInterval starts k-1 steps in.  Built automatically at open
  * (k <= 10, at most a quarter of the blocks' size; RS_B200_FTAB=k overrides); k = 0 drops it. */
 int rs_index_set_prefix_table(rs_index* ix, int k);
+/* Locate table, no reference counterpart (results do not depend on it): for every BWT row, where
+ * extractPrefix's walk from it ends and after how many bases, found once by walking every read from its
+ * terminator (n LF steps in one kernel).  With it the locate stage (rs_extract_prefix_batch without bases,
+ * rs_locate_batch, rs_gt_reads_batch) reads 8 bytes per hit row instead of walking ~read-length/2 blocks.
+ * Costs 8 bytes per BWT symbol of HBM (8.7 GB for a 1.08 G-symbol shard): meant for shards that leave the room.
+ * max_read_len bounds the walks of the build (rows on longer walks -- the reference's tail region can cycle --
+ * stay uncovered and are walked at query time as before).  Rebuilt by rs_index_set_tail_emulation. */
+int rs_index_build_locate_table(rs_index* ix, uint32_t max_read_len);
+int rs_index_drop_locate_table(rs_index* ix);
 /* Work counters for the *_dev calls (kept on the device, off by default): executed updateInterval
  * steps of findInterval (2 getOcc each) and executed LF steps of extractPrefix.  Used by bench.py
  * to turn a kernel time into achieved bytes/s; no reference counterpart. */

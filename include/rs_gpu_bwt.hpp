@@ -81,6 +81,10 @@ class GpuBWT : public BWT {
   void loadSamplesFile(const std::string& path, int size_of_sample, bool has_other_meta_data) {
     check(rs_index_load_samples_file(ix_, path.c_str(), size_of_sample, has_other_meta_data ? 1 : 0));
   }
+  // optional locate table (8 bytes of HBM per BWT symbol): the locate stage reads one entry per hit row instead of
+  // walking; results do not depend on it
+  void buildLocateTable(uint32_t max_read_len = 4096) { check(rs_index_build_locate_table(ix_, max_read_len)); }
+  void dropLocateTable() { check(rs_index_drop_locate_table(ix_)); }
   // packed read table for output=reads, from the same file (reads holding 'N' are not in the BWT)
   void loadReadsFile(const std::string& path) { check(rs_index_load_reads_file(ix_, path.c_str())); }
 

@@ -44,6 +44,53 @@ static int build_ftab(rs_index* ix, uint32_t t) {
   return RS_STATUS_OK;
 }
 
+/* (Re)build or drop the locate table.  Like the suffix table it holds the answers of the semantics in force
+ * (reference tail behaviour or exact), so the tail switch rebuilds it. */
+static int drop_locate(rs_index* ix) {
+  if (ix->d_loc) {
+    CU(cudaStreamSynchronize(ix->stream));
+    cudaFree(ix->d_loc);
+    cudaFree(ix->d_loc_fin);
+    ix->hbm_bytes -= (ix->dev.n + ix->dev.num_strings) * 8;
+    ix->d_loc = ix->d_loc_fin = nullptr;
+  }
+  ix->dev.loc = ix->dev.loc_fin = nullptr;
+  return RS_STATUS_OK;
+}
+static int build_locate(rs_index* ix, uint32_t max_len) {
+  const int rc = drop_locate(ix);
+  if (rc != RS_STATUS_OK) return rc;
+  if (ix->dev.num_strings >> 40) return fail(RS_STATUS_TOO_LARGE, "locate table: more than 2^40 reads");
+  CU(cudaMalloc((void**)&ix->d_loc, ix->dev.n * 8));
+  if (cudaMalloc((void**)&ix->d_loc_fin, (ix->dev.num_strings ? ix->dev.num_strings : 1) * 8) != cudaSuccess) {
+    cudaFree(ix->d_loc);
+    ix->d_loc = nullptr;
+    return fail(RS_STATUS_CUDA, "locate table: out of device memory");
+  }
+  CU(rs_build_locate_table(ix->dev, max_len, ix->d_loc, ix->d_loc_fin, ix->stream));
+  CU(cudaStreamSynchronize(ix->stream));
+  ix->dev.loc = ix->d_loc;
+  ix->dev.loc_fin = ix->d_loc_fin;
+  ix->loc_max_len = max_len;
+  ix->hbm_bytes += (ix->dev.n + ix->dev.num_strings) * 8;
+  return RS_STATUS_OK;
+}
+
+int rs_index_build_locate_table(rs_index* ix, uint32_t max_read_len) {
+  if (!ix) return fail(RS_STATUS_ARG, "null index");
+  if (max_read_len < 1 || max_read_len >= (1u << 24) - 1) return fail(RS_STATUS_ARG, "max_read_len must be in [1, 2^24 - 2]");
+  std::lock_guard<std::mutex> lk(ix->mu);
+  CU(cudaSetDevice(ix->device));
+  return build_locate(ix, max_read_len);
+}
+
+int rs_index_drop_locate_table(rs_index* ix) {
+  if (!ix) return fail(RS_STATUS_ARG, "null index");
+  std::lock_guard<std::mutex> lk(ix->mu);
+  CU(cudaSetDevice(ix->device));
+  return drop_locate(ix);
+}
+
 static uint32_t auto_ftab_k(const rs_index* ix) {
   const char* e = getenv("RS_B200_FTAB");
   if (e) return (uint32_t)atoi(e);
@@ -133,6 +180,8 @@ void rs_index_close(rs_index* ix) {
   if (ix->d_samp_codes) cudaFree(ix->d_samp_codes);
   if (ix->d_stats) cudaFree(ix->d_stats);
   if (ix->d_ftab) cudaFree(ix->d_ftab);
+  if (ix->d_loc) cudaFree(ix->d_loc);
+  if (ix->d_loc_fin) cudaFree(ix->d_loc_fin);
   if (ix->d_reads) cudaFree(ix->d_reads);
   if (ix->d_read_off) cudaFree(ix->d_read_off);
   ix->s_in.release();
@@ -179,7 +228,9 @@ int rs_index_set_tail_emulation(rs_index* ix, int on) {
   std::lock_guard<std::mutex> lk(ix->mu);
   set_tail(ix, on != 0); /* initInterval's constant (query.cpp:18-21) follows the same switch */
   CU(cudaSetDevice(ix->device));
-  return build_ftab(ix, ix->dev.ftab_k); /* the table holds intervals of the semantics it was built with */
+  const int rc = build_ftab(ix, ix->dev.ftab_k); /* the table holds intervals of the semantics it was built with */
+  if (rc != RS_STATUS_OK || !ix->d_loc) return rc;
+  return build_locate(ix, ix->loc_max_len);
 }
 
 int rs_index_set_prefix_table(rs_index* ix, int k) {

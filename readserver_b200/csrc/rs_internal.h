@@ -81,6 +81,9 @@ struct rs_index {
   uint32_t* d_reads = nullptr;     /* packed read table (rs_reads.cu): 16 bases per word */
   uint64_t* d_read_off = nullptr;  /* first base of each read, num_strings + 1 entries */
   uint64_t reads_bytes = 0;
+  uint64_t* d_loc = nullptr;      /* locate table (rs_layout.h), n entries */
+  uint64_t* d_loc_fin = nullptr;  /* num_strings entries */
+  uint32_t loc_max_len = 0;
   uint64_t* d_ftab = nullptr; /* k-mer suffix table (rs_layout.h), 4^ftab_k pairs */
   uint64_t* d_stats = nullptr; /* [0] updateInterval steps, [1] LF-walk steps; null unless profiling is on */
   cudaStream_t stream = nullptr;

@@ -319,6 +319,93 @@ __global__ void __launch_bounds__(RS_THREADS)
   if (stats && nsteps) atomicAdd(stats, (unsigned long long)nsteps);
 }
 
+/* Builds the locate table (rs_layout.h): one walker per read, from the row of its terminator back to its first
+ * base, leaving at every row it passes its own start row and the distance walked.  n LF steps in total. */
+#define RS_LOC_STEP_MASK 0xFFFFFFull
+#define RS_K2_BLOCKS_BUILD 4
+__global__ void __launch_bounds__(RS_THREADS, RS_K2_BLOCKS_BUILD)
+    k_build_locate(const __grid_constant__ rs_index_dev ix, uint32_t max_len, uint64_t* __restrict__ loc,
+                   uint64_t* __restrict__ fin) {
+  const uint64_t stride = (uint64_t)gridDim.x * RS_THREADS;
+  uint64_t next_i = (uint64_t)blockIdx.x * RS_THREADS + threadIdx.x;
+  uint64_t i = 0, idx = 0;
+  uint32_t s = 0;
+  bool active = false;
+  while (true) {
+    if (!active && next_i < ix.num_strings) {
+      i = next_i;
+      next_i += stride;
+      idx = i;
+      s = 0;
+      active = true;
+    }
+    if (__all_sync(RS_FULL, !active)) break;
+    if (active) {
+      loc[idx] = (i << 24) | s;
+      uint64_t nxt;
+      const uint32_t sym = rs_lf_step(ix, idx, &nxt);
+      idx = nxt;
+      if (sym == 0) {
+        fin[i] = (idx << 24) | s;
+        active = false;
+      } else if (++s > max_len) { /* longer than any read: a walk caught in the reference's tail region */
+        fin[i] = ~0ull;
+        active = false;
+      }
+    }
+  }
+}
+
+/* K2 with the locate table: one 8-byte read (+ one of loc_fin, + .sai) per row instead of a walk; rows the table
+ * does not cover (walks that never end, under the reference's tail behaviour) are walked as K2 does. */
+__global__ void __launch_bounds__(RS_THREADS)
+    k_locate_lookup(const __grid_constant__ rs_index_dev ix, const uint64_t* __restrict__ rows, uint64_t n,
+                    uint32_t max_steps, uint64_t* __restrict__ lexrank, uint32_t* __restrict__ steps,
+                    const uint64_t* __restrict__ sai, uint64_t* __restrict__ read_index,
+                    unsigned long long* __restrict__ stats) {
+  const uint64_t stride = (uint64_t)gridDim.x * RS_THREADS;
+  unsigned long long lf_steps = 0;
+  for (uint64_t i = (uint64_t)blockIdx.x * RS_THREADS + threadIdx.x; i < n; i += stride) {
+    uint64_t idx = rows[i];
+    uint64_t term = ~0ull;
+    uint32_t nsteps = 0xFFFFFFFFu;
+    bool known = false;
+    if (idx < ix.n) {
+      const uint64_t e = __ldg(ix.loc + idx);
+      if (e != ~0ull) {
+        const uint64_t f = __ldg(ix.loc_fin + (e >> 24));
+        if (f != ~0ull) {
+          known = true;
+          const uint32_t left = (uint32_t)(f & RS_LOC_STEP_MASK) - (uint32_t)(e & RS_LOC_STEP_MASK);
+          if (left <= max_steps) {
+            term = f >> 24;
+            nsteps = left;
+          }
+        }
+      }
+    }
+    if (!known) { /* extractPrefix as K2 walks it */
+      uint32_t s = 0;
+      while (true) {
+        uint64_t nxt;
+        const uint32_t sym = rs_lf_step(ix, idx, &nxt);
+        ++lf_steps;
+        idx = nxt;
+        if (sym == 0) {
+          term = idx;
+          nsteps = s;
+          break;
+        }
+        if (++s > max_steps) break;
+      }
+    }
+    if (lexrank) lexrank[i] = term;
+    if (steps) steps[i] = nsteps;
+    if (read_index) read_index[i] = (term != ~0ull && term < ix.num_strings) ? sai[term] : ~0ull;
+  }
+  if (stats && lf_steps) atomicAdd(stats + 1, lf_steps);
+}
+
 /* K2.  extractPrefix (query.cpp:43-63): LF-walk from each row to its '$'.  Same step-interleaved
  * scheme as K1: a thread whose walk ends takes its next row on the following trip, so the set of
  * live walkers stays dense in every warp without a separate compaction pass. */
@@ -569,7 +656,25 @@ cudaError_t rs_launch_extract_prefix(const rs_index_dev& ix, const uint64_t* row
                                      uint64_t* lexrank, uint32_t* steps, const uint64_t* sai, uint64_t* read_index,
                                      uint8_t* bases, unsigned long long* stats, cudaStream_t st) {
   if (!n) return cudaSuccess;
+  if (ix.loc && !bases) {
+    uint64_t blocks = (n + RS_THREADS - 1) / RS_THREADS;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    k_locate_lookup<<<(unsigned)blocks, RS_THREADS, 0, st>>>(ix, rows, n, max_steps, lexrank, steps, sai, read_index, stats);
+    return cudaGetLastError();
+  }
   RS_LAUNCH(k_extract_prefix, n, st, ix, rows, n, max_steps, lexrank, steps, sai, read_index, bases, stats);
+  return cudaGetLastError();
+}
+
+cudaError_t rs_build_locate_table(const rs_index_dev& ix_in, uint32_t max_len, uint64_t* loc, uint64_t* fin, cudaStream_t st) {
+  rs_index_dev ix = ix_in;
+  ix.loc = nullptr;
+  ix.loc_fin = nullptr;
+  cudaError_t e;
+  if ((e = cudaMemsetAsync(loc, 0xFF, ix.n * 8, st)) != cudaSuccess) return e;
+  if ((e = cudaMemsetAsync(fin, 0xFF, (ix.num_strings ? ix.num_strings : 1) * 8, st)) != cudaSuccess) return e;
+  if (!ix.num_strings) return cudaSuccess;
+  RS_LAUNCH(k_build_locate, ix.num_strings, st, ix, max_len, loc, fin);
   return cudaGetLastError();
 }
 

@@ -37,6 +37,9 @@ cudaError_t rs_launch_extract_prefix(const rs_index_dev& ix, const uint64_t* row
                                      uint64_t* lexrank, uint32_t* steps, const uint64_t* sai, uint64_t* read_index,
                                      uint8_t* bases, unsigned long long* stats, cudaStream_t st);
 
+/* fills loc[n] and fin[num_strings] (rs_layout.h: locate table); walks are cut at max_len symbols */
+cudaError_t rs_build_locate_table(const rs_index_dev& ix, uint32_t max_len, uint64_t* loc, uint64_t* fin, cudaStream_t st);
+
 cudaError_t rs_launch_occ_at(const rs_index_dev& ix, const uint8_t* syms, const uint64_t* cnt, uint64_t n, uint64_t* out,
                              cudaStream_t st);
 cudaError_t rs_launch_extract_postfix(const rs_index_dev& ix, const uint64_t* rows, uint64_t n, uint32_t max_steps,

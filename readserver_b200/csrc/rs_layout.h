@@ -83,6 +83,14 @@ typedef struct rs_index_dev {
   const uint64_t* ftab;
   uint32_t ftab_k;
   uint32_t sel_shift[RS_NSYM]; /* select directory of c: one entry per 2^sel_shift[c] occurrences */
+  /* Locate table, optional (null = not built): where extractPrefix's walk from a row ends, without walking.
+   * Every row lies on the walk that starts at the row of some read's terminator (rows 0 .. num_strings-1):
+   *   loc[row]   = start_row << 24 | symbols walked from start_row before reaching this row   (2^64-1: none)
+   *   loc_fin[s] = terminal row of the walk from start row s << 24 | its length in symbols    (2^64-1: the walk
+   *                does not end, reference tail region)
+   * so a row's own walk ends at the same terminal after (length - walked) symbols. */
+  const uint64_t* loc;
+  const uint64_t* loc_fin;
 } rs_index_dev;
 
 #endif

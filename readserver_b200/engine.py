@@ -74,6 +74,8 @@ def lib() -> C.CDLL:
         "rs_reads_batch": (i32, [vp, vp, sz, C.c_uint32, vp, vp]),
         "rs_reads_batch_dev": (i32, [vp, vp, sz, C.c_uint32, vp, vp, vp]),
         "rs_tile_intervals_batch": (i32, [vp, vp, vp, sz, C.c_uint32, C.c_uint32, vp, u64, vp, vp]),
+        "rs_index_build_locate_table": (i32, [vp, C.c_uint32]),
+        "rs_index_drop_locate_table": (i32, [vp]),
         "rs_gt_reads_batch": (i32, [vp, vp, vp, vp, sz, C.c_uint32, C.c_uint32, u64, C.c_uint32, u64, vp, u64, vp, vp, vp]),
         "rs_comm_create": (i32, [i32, i32, i32, u64, C.POINTER(vp)]),
         "rs_comm_export": (i32, [vp, vp]),
@@ -433,6 +435,15 @@ class GpuBWT:
         _check(lib().rs_tile_intervals_batch(self._h, text.ctypes.data, offs.ctypes.data, len(bs), kmer, skip,
                                              toff.ctypes.data, cap, lo.ctypes.data, up.ctypes.data))
         return toff, lo[:cap], up[:cap]
+
+    def build_locate_table(self, max_read_len: int = 4096):
+        """8 bytes per BWT symbol of HBM: the locate stage then reads one entry per hit row instead of walking."""
+        _check(lib().rs_index_build_locate_table(self._h, max_read_len))
+        _check(lib().rs_index_get_info(self._h, C.byref(self.info)))
+
+    def drop_locate_table(self):
+        _check(lib().rs_index_drop_locate_table(self._h))
+        _check(lib().rs_index_get_info(self._h, C.byref(self.info)))
 
     def gt_reads(self, windows: list, pos, kmer: int, skip: int = 0, max_interval_size: int = 10000,
                  max_steps: int = 1024, max_rows: int = 1 << 26):

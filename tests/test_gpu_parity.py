@@ -76,6 +76,45 @@ def test_find_interval_matches_oracle(name, datasets, engine):
             assert (int(a), int(b)) == P.find_interval(s), s
 
 
+@pytest.mark.parametrize("name", ["tiny", "small", "clean", "mid", "deep"])
+def test_locate_table_gives_the_walks_answers(name, datasets, engine):
+    """The optional locate table (8 bytes per BWT row: where the row's extractPrefix walk ends and after how many
+    bases) must answer exactly what the walk answers -- under the reference's tail behaviour, where some walks never
+    end and some rows lie on no read's walk, and with exact rank -- for every row of the small indexes."""
+    case, P = datasets.case(name), datasets.port(name)
+    n = P.bwlen
+    rows = np.arange(n, dtype=np.uint64) if n < 700_000 else np.concatenate(
+        [common.positions(n, 300_000, seed=3), np.arange(n - 70_000, n, dtype=np.uint64)])
+    with _gpu(engine, case) as B:
+        B.set_sai(case.sai)
+        B.drop_locate_table()           # nothing to drop: refreshes B.info
+        hbm0 = B.info.hbm_bytes
+        for emulate in (True, False):
+            B.set_tail_emulation(emulate)
+            lex0, st0, ri0 = B.extract_prefix(rows, max_steps=130, want_read_index=True)
+            B.build_locate_table(max_read_len=120)
+            assert B.info.hbm_bytes == hbm0 + 8 * (n + case.num_strings)
+            lex1, st1, ri1 = B.extract_prefix(rows, max_steps=130, want_read_index=True)
+            assert np.array_equal(lex0, lex1) and np.array_equal(st0, st1) and np.array_equal(ri0, ri1), (name, emulate)
+            # a cut below the read length: same rows reported as cut off
+            lex2, st2 = B.extract_prefix(rows[:50_000], max_steps=40)
+            B.drop_locate_table()
+            lex3, st3 = B.extract_prefix(rows[:50_000], max_steps=40)
+            assert np.array_equal(lex2, lex3) and np.array_equal(st2, st3)
+            assert B.info.hbm_bytes == hbm0
+        # the switch rebuilds the table with the other semantics
+        B.set_tail_emulation(True)
+        B.build_locate_table(120)
+        B.set_tail_emulation(False)
+        lex4, st4 = B.extract_prefix(rows[-60_000:], max_steps=130)
+        B.drop_locate_table()
+        lex5, st5 = B.extract_prefix(rows[-60_000:], max_steps=130)
+        assert np.array_equal(lex4, lex5) and np.array_equal(st4, st5)
+    if name == "clean":     # against the oracle directly
+        lexo, pso, _, _ = P.locate_batch(rows[:20_000], postfix=False)
+        assert np.array_equal(lex5[:0], lex5[:0]) and np.array_equal(lex1[:20_000], lexo) and np.array_equal(st1[:20_000], pso)
+
+
 def test_large_host_batch_goes_through_the_chunk_pipeline(datasets, engine):
     """Host-pointer calls with several hundred thousand queries are cut into chunks (copy-in, search, copy-out on
     separate streams, ramped chunk sizes): results must not depend on the cut, for intervals and for counts."""
