@@ -51,37 +51,88 @@ static int drop_locate(rs_index* ix) {
     CU(cudaStreamSynchronize(ix->stream));
     cudaFree(ix->d_loc);
     cudaFree(ix->d_loc_fin);
-    ix->hbm_bytes -= (ix->dev.n + ix->dev.num_strings) * 8;
-    ix->d_loc = ix->d_loc_fin = nullptr;
+    if (ix->d_loc_mark) cudaFree(ix->d_loc_mark);
+    if (ix->d_loc_rank) cudaFree(ix->d_loc_rank);
+    ix->hbm_bytes -= ix->loc_bytes;
+    ix->d_loc = ix->d_loc_fin = ix->d_loc_mark = ix->d_loc_rank = nullptr;
+    ix->loc_bytes = 0;
   }
-  ix->dev.loc = ix->dev.loc_fin = nullptr;
+  ix->dev.loc = ix->dev.loc_fin = ix->dev.loc_mark = ix->dev.loc_rank = nullptr;
+  ix->dev.loc_every = 0;
   return RS_STATUS_OK;
 }
-static int build_locate(rs_index* ix, uint32_t max_len) {
+static int build_locate(rs_index* ix, uint32_t max_len, uint32_t every) {
   const int rc = drop_locate(ix);
   if (rc != RS_STATUS_OK) return rc;
   if (ix->dev.num_strings >> 40) return fail(RS_STATUS_TOO_LARGE, "locate table: more than 2^40 reads");
-  CU(cudaMalloc((void**)&ix->d_loc, ix->dev.n * 8));
-  if (cudaMalloc((void**)&ix->d_loc_fin, (ix->dev.num_strings ? ix->dev.num_strings : 1) * 8) != cudaSuccess) {
-    cudaFree(ix->d_loc);
-    ix->d_loc = nullptr;
-    return fail(RS_STATUS_CUDA, "locate table: out of device memory");
+  const uint64_t n = ix->dev.n, ns = ix->dev.num_strings;
+  cudaStream_t st = ix->stream;
+  uint64_t bytes = 0;
+  auto alloc = [&](uint64_t** p, uint64_t count) {
+    const cudaError_t e = cudaMalloc((void**)p, (count ? count : 1) * 8);
+    if (e == cudaSuccess) bytes += (count ? count : 1) * 8;
+    return e;
+  };
+  auto bail = [&](const char* what) {
+    if (ix->d_loc) cudaFree(ix->d_loc);
+    if (ix->d_loc_fin) cudaFree(ix->d_loc_fin);
+    if (ix->d_loc_mark) cudaFree(ix->d_loc_mark);
+    if (ix->d_loc_rank) cudaFree(ix->d_loc_rank);
+    ix->d_loc = ix->d_loc_fin = ix->d_loc_mark = ix->d_loc_rank = nullptr;
+    cudaGetLastError();
+    return fail(RS_STATUS_CUDA, "locate table: %s", what);
+  };
+  if (alloc(&ix->d_loc_fin, ns) != cudaSuccess) return bail("out of device memory");
+  if (every <= 1) {
+    if (alloc(&ix->d_loc, n) != cudaSuccess) return bail("out of device memory");
+    if (rs_build_locate_table(ix->dev, max_len, ix->d_loc, ix->d_loc_fin, st) != cudaSuccess) return bail("build failed");
+  } else {
+    const uint64_t nwords = (n + 63) / 64, ngroups = (nwords + 7) / 8;
+    if (alloc(&ix->d_loc_mark, nwords) != cudaSuccess || alloc(&ix->d_loc_rank, ngroups + 1) != cudaSuccess)
+      return bail("out of device memory");
+    uint64_t* d_counts = nullptr;
+    void* d_scan = nullptr;
+    size_t scan_bytes = 0;
+    if (rs_scan_bytes(ngroups, &scan_bytes) != cudaSuccess || cudaMalloc((void**)&d_counts, (ngroups + 1) * 8) != cudaSuccess ||
+        cudaMalloc(&d_scan, scan_bytes ? scan_bytes : 8) != cudaSuccess) {
+      if (d_counts) cudaFree(d_counts);
+      return bail("out of device memory");
+    }
+    uint64_t nsamples = 0;
+    cudaError_t e = rs_locate_mark(ix->dev, max_len, every, ix->d_loc_mark, ix->d_loc_fin, st);
+    if (e == cudaSuccess) e = rs_locate_mark_counts(ix->d_loc_mark, n, d_counts, st);
+    if (e == cudaSuccess) e = rs_exclusive_scan(d_counts, ix->d_loc_rank, ngroups, d_scan, scan_bytes, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(&nsamples, ix->d_loc_rank + ngroups, 8, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = cudaStreamSynchronize(st);
+    cudaFree(d_counts);
+    cudaFree(d_scan);
+    if (e != cudaSuccess) return bail(cudaGetErrorString(e));
+    if (alloc(&ix->d_loc, nsamples) != cudaSuccess) return bail("out of device memory");
+    if (rs_locate_fill(ix->dev, max_len, every, ix->d_loc_mark, ix->d_loc_rank, ix->d_loc, nsamples, st) != cudaSuccess)
+      return bail("build failed");
   }
-  CU(rs_build_locate_table(ix->dev, max_len, ix->d_loc, ix->d_loc_fin, ix->stream));
-  CU(cudaStreamSynchronize(ix->stream));
+  if (cudaStreamSynchronize(st) != cudaSuccess) return bail("build failed");
   ix->dev.loc = ix->d_loc;
   ix->dev.loc_fin = ix->d_loc_fin;
+  ix->dev.loc_mark = ix->d_loc_mark;
+  ix->dev.loc_rank = ix->d_loc_rank;
+  ix->dev.loc_every = every <= 1 ? 1 : every;
   ix->loc_max_len = max_len;
-  ix->hbm_bytes += (ix->dev.n + ix->dev.num_strings) * 8;
+  ix->loc_every = every;
+  ix->loc_bytes = bytes;
+  ix->hbm_bytes += bytes;
   return RS_STATUS_OK;
 }
 
-int rs_index_build_locate_table(rs_index* ix, uint32_t max_read_len) {
+int rs_index_build_locate_table(rs_index* ix, uint32_t max_read_len) { return rs_index_build_locate_samples(ix, max_read_len, 1); }
+
+int rs_index_build_locate_samples(rs_index* ix, uint32_t max_read_len, uint32_t every) {
   if (!ix) return fail(RS_STATUS_ARG, "null index");
   if (max_read_len < 1 || max_read_len >= (1u << 24) - 1) return fail(RS_STATUS_ARG, "max_read_len must be in [1, 2^24 - 2]");
+  if (every < 1) return fail(RS_STATUS_ARG, "every must be >= 1");
   std::lock_guard<std::mutex> lk(ix->mu);
   CU(cudaSetDevice(ix->device));
-  return build_locate(ix, max_read_len);
+  return build_locate(ix, max_read_len, every);
 }
 
 int rs_index_drop_locate_table(rs_index* ix) {
@@ -182,6 +233,8 @@ void rs_index_close(rs_index* ix) {
   if (ix->d_ftab) cudaFree(ix->d_ftab);
   if (ix->d_loc) cudaFree(ix->d_loc);
   if (ix->d_loc_fin) cudaFree(ix->d_loc_fin);
+  if (ix->d_loc_mark) cudaFree(ix->d_loc_mark);
+  if (ix->d_loc_rank) cudaFree(ix->d_loc_rank);
   if (ix->d_reads) cudaFree(ix->d_reads);
   if (ix->d_read_off) cudaFree(ix->d_read_off);
   ix->s_in.release();
@@ -230,7 +283,7 @@ int rs_index_set_tail_emulation(rs_index* ix, int on) {
   CU(cudaSetDevice(ix->device));
   const int rc = build_ftab(ix, ix->dev.ftab_k); /* the table holds intervals of the semantics it was built with */
   if (rc != RS_STATUS_OK || !ix->d_loc) return rc;
-  return build_locate(ix, ix->loc_max_len);
+  return build_locate(ix, ix->loc_max_len, ix->loc_every);
 }
 
 int rs_index_set_prefix_table(rs_index* ix, int k) {

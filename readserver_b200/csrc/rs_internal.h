@@ -83,7 +83,10 @@ struct rs_index {
   uint64_t reads_bytes = 0;
   uint64_t* d_loc = nullptr;      /* locate table (rs_layout.h), n entries */
   uint64_t* d_loc_fin = nullptr;  /* num_strings entries */
-  uint32_t loc_max_len = 0;
+  uint64_t* d_loc_mark = nullptr; /* sampled variant: one bit per row, and its rank directory */
+  uint64_t* d_loc_rank = nullptr;
+  uint32_t loc_max_len = 0, loc_every = 0;
+  uint64_t loc_bytes = 0;
   uint64_t* d_ftab = nullptr; /* k-mer suffix table (rs_layout.h), 4^ftab_k pairs */
   uint64_t* d_stats = nullptr; /* [0] updateInterval steps, [1] LF-walk steps; null unless profiling is on */
   cudaStream_t stream = nullptr;

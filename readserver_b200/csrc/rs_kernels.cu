@@ -406,6 +406,110 @@ __global__ void __launch_bounds__(RS_THREADS)
   if (stats && lf_steps) atomicAdd(stats + 1, lf_steps);
 }
 
+/* ---- sampled locate table ---- */
+/* pass 1: mark the rows every `every` symbols along each read's walk; fin as in the full table */
+__global__ void __launch_bounds__(RS_THREADS, RS_K2_BLOCKS_BUILD)
+    k_mark_locate(const __grid_constant__ rs_index_dev ix, uint32_t max_len, uint32_t every,
+                  unsigned long long* __restrict__ mark, uint64_t* __restrict__ fin) {
+  const uint64_t stride = (uint64_t)gridDim.x * RS_THREADS;
+  for (uint64_t i = (uint64_t)blockIdx.x * RS_THREADS + threadIdx.x; i < ix.num_strings; i += stride) {
+    uint64_t idx = i;
+    uint32_t s = 0;
+    while (true) {
+      if (s % every == 0) atomicOr(mark + (idx >> 6), 1ull << (idx & 63));
+      uint64_t nxt;
+      const uint32_t sym = rs_lf_step(ix, idx, &nxt);
+      idx = nxt;
+      if (sym == 0) {
+        fin[i] = (idx << 24) | s;
+        break;
+      }
+      if (++s > max_len) {
+        fin[i] = ~0ull;
+        break;
+      }
+    }
+  }
+}
+
+/* set bits of each 512-row group */
+__global__ void k_mark_counts(const uint64_t* __restrict__ mark, uint64_t ngroups, uint64_t nwords,
+                              uint64_t* __restrict__ counts) {
+  const uint64_t g = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (g >= ngroups) return;
+  uint64_t c = 0;
+  for (uint32_t w = 0; w < 8 && g * 8 + w < nwords; ++w) c += __popcll(mark[g * 8 + w]);
+  counts[g] = c;
+}
+
+__device__ __forceinline__ uint64_t rs_sample_slot(const uint64_t* __restrict__ mark, const uint64_t* __restrict__ rank,
+                                                   uint64_t row) {
+  uint64_t slot = rank[row >> 9];
+  for (uint64_t w = (row >> 9) << 3; w < (row >> 6); ++w) slot += __popcll(mark[w]);
+  return slot + __popcll(mark[row >> 6] & ((1ull << (row & 63)) - 1));
+}
+
+/* pass 2: the same walks again, filling the entries of the sampled rows */
+__global__ void __launch_bounds__(RS_THREADS, RS_K2_BLOCKS_BUILD)
+    k_fill_locate(const __grid_constant__ rs_index_dev ix, uint32_t max_len, uint32_t every,
+                  const uint64_t* __restrict__ mark, const uint64_t* __restrict__ rank, uint64_t* __restrict__ loc) {
+  const uint64_t stride = (uint64_t)gridDim.x * RS_THREADS;
+  for (uint64_t i = (uint64_t)blockIdx.x * RS_THREADS + threadIdx.x; i < ix.num_strings; i += stride) {
+    uint64_t idx = i;
+    uint32_t s = 0;
+    while (true) {
+      if (s % every == 0) loc[rs_sample_slot(mark, rank, idx)] = (i << 24) | s;
+      uint64_t nxt;
+      const uint32_t sym = rs_lf_step(ix, idx, &nxt);
+      idx = nxt;
+      if (sym == 0 || ++s > max_len) break;
+    }
+  }
+}
+
+/* K2 with the sampled table: follow the walk until a sampled row (or the '$') */
+__global__ void __launch_bounds__(RS_THREADS, RS_K2_BLOCKS_BUILD)
+    k_locate_sampled(const __grid_constant__ rs_index_dev ix, const uint64_t* __restrict__ rows, uint64_t n,
+                     uint32_t max_steps, uint64_t* __restrict__ lexrank, uint32_t* __restrict__ steps,
+                     const uint64_t* __restrict__ sai, uint64_t* __restrict__ read_index,
+                     unsigned long long* __restrict__ stats) {
+  const uint64_t stride = (uint64_t)gridDim.x * RS_THREADS;
+  unsigned long long lf_steps = 0;
+  for (uint64_t i = (uint64_t)blockIdx.x * RS_THREADS + threadIdx.x; i < n; i += stride) {
+    uint64_t idx = rows[i];
+    uint64_t term = ~0ull;
+    uint32_t nsteps = 0xFFFFFFFFu, s = 0;
+    while (true) {
+      if (idx < ix.n && ((__ldg(ix.loc_mark + (idx >> 6)) >> (idx & 63)) & 1ull)) {
+        const uint64_t e = __ldg(ix.loc + rs_sample_slot(ix.loc_mark, ix.loc_rank, idx));
+        const uint64_t f = e != ~0ull ? __ldg(ix.loc_fin + (e >> 24)) : ~0ull;
+        if (f != ~0ull) {
+          const uint64_t total = (uint64_t)s + ((f & RS_LOC_STEP_MASK) - (e & RS_LOC_STEP_MASK));
+          if (total <= max_steps) {
+            term = f >> 24;
+            nsteps = (uint32_t)total;
+          }
+          break;
+        }
+      }
+      uint64_t nxt;
+      const uint32_t sym = rs_lf_step(ix, idx, &nxt);
+      ++lf_steps;
+      idx = nxt;
+      if (sym == 0) {
+        term = idx;
+        nsteps = s;
+        break;
+      }
+      if (++s > max_steps) break;
+    }
+    if (lexrank) lexrank[i] = term;
+    if (steps) steps[i] = nsteps;
+    if (read_index) read_index[i] = (term != ~0ull && term < ix.num_strings) ? sai[term] : ~0ull;
+  }
+  if (stats && lf_steps) atomicAdd(stats + 1, lf_steps);
+}
+
 /* K2.  extractPrefix (query.cpp:43-63): LF-walk from each row to its '$'.  Same step-interleaved
  * scheme as K1: a thread whose walk ends takes its next row on the following trip, so the set of
  * live walkers stays dense in every warp without a separate compaction pass. */
@@ -656,6 +760,10 @@ cudaError_t rs_launch_extract_prefix(const rs_index_dev& ix, const uint64_t* row
                                      uint64_t* lexrank, uint32_t* steps, const uint64_t* sai, uint64_t* read_index,
                                      uint8_t* bases, unsigned long long* stats, cudaStream_t st) {
   if (!n) return cudaSuccess;
+  if (ix.loc && ix.loc_every > 1 && !bases) {
+    RS_LAUNCH(k_locate_sampled, n, st, ix, rows, n, max_steps, lexrank, steps, sai, read_index, stats);
+    return cudaGetLastError();
+  }
   if (ix.loc && !bases) {
     uint64_t blocks = (n + RS_THREADS - 1) / RS_THREADS;
     if (blocks > 148 * 8) blocks = 148 * 8;
@@ -666,10 +774,46 @@ cudaError_t rs_launch_extract_prefix(const rs_index_dev& ix, const uint64_t* row
   return cudaGetLastError();
 }
 
+/* sampled table, pass 1: mark[] (zeroed here) and fin[]; the caller sizes loc from the marks (rs_locate_marks_scan) */
+cudaError_t rs_locate_mark(const rs_index_dev& ix_in, uint32_t max_len, uint32_t every, uint64_t* mark, uint64_t* fin,
+                           cudaStream_t st) {
+  rs_index_dev ix = ix_in;
+  ix.loc = nullptr;
+  ix.loc_every = 0;
+  cudaError_t e;
+  const uint64_t nwords = (ix.n + 63) / 64;
+  if ((e = cudaMemsetAsync(mark, 0, nwords * 8, st)) != cudaSuccess) return e;
+  if ((e = cudaMemsetAsync(fin, 0xFF, (ix.num_strings ? ix.num_strings : 1) * 8, st)) != cudaSuccess) return e;
+  if (!ix.num_strings) return cudaSuccess;
+  RS_LAUNCH(k_mark_locate, ix.num_strings, st, ix, max_len, every, reinterpret_cast<unsigned long long*>(mark), fin);
+  return cudaGetLastError();
+}
+
+/* counts[g] = marked rows of group g (512 rows); the caller scans them into the rank directory */
+cudaError_t rs_locate_mark_counts(const uint64_t* mark, uint64_t n, uint64_t* counts, cudaStream_t st) {
+  const uint64_t nwords = (n + 63) / 64, ngroups = (nwords + 7) / 8;
+  k_mark_counts<<<(unsigned)((ngroups + 255) / 256), 256, 0, st>>>(mark, ngroups, nwords, counts);
+  return cudaGetLastError();
+}
+
+/* sampled table, pass 2 */
+cudaError_t rs_locate_fill(const rs_index_dev& ix_in, uint32_t max_len, uint32_t every, const uint64_t* mark,
+                           const uint64_t* rank, uint64_t* loc, uint64_t nsamples, cudaStream_t st) {
+  rs_index_dev ix = ix_in;
+  ix.loc = nullptr;
+  ix.loc_every = 0;
+  cudaError_t e;
+  if ((e = cudaMemsetAsync(loc, 0xFF, (nsamples ? nsamples : 1) * 8, st)) != cudaSuccess) return e;
+  if (!ix.num_strings) return cudaSuccess;
+  RS_LAUNCH(k_fill_locate, ix.num_strings, st, ix, max_len, every, mark, rank, loc);
+  return cudaGetLastError();
+}
+
 cudaError_t rs_build_locate_table(const rs_index_dev& ix_in, uint32_t max_len, uint64_t* loc, uint64_t* fin, cudaStream_t st) {
   rs_index_dev ix = ix_in;
   ix.loc = nullptr;
   ix.loc_fin = nullptr;
+  ix.loc_every = 0;
   cudaError_t e;
   if ((e = cudaMemsetAsync(loc, 0xFF, ix.n * 8, st)) != cudaSuccess) return e;
   if ((e = cudaMemsetAsync(fin, 0xFF, (ix.num_strings ? ix.num_strings : 1) * 8, st)) != cudaSuccess) return e;

@@ -75,6 +75,7 @@ def lib() -> C.CDLL:
         "rs_reads_batch_dev": (i32, [vp, vp, sz, C.c_uint32, vp, vp, vp]),
         "rs_tile_intervals_batch": (i32, [vp, vp, vp, sz, C.c_uint32, C.c_uint32, vp, u64, vp, vp]),
         "rs_index_build_locate_table": (i32, [vp, C.c_uint32]),
+        "rs_index_build_locate_samples": (i32, [vp, C.c_uint32, C.c_uint32]),
         "rs_index_drop_locate_table": (i32, [vp]),
         "rs_gt_reads_batch": (i32, [vp, vp, vp, vp, sz, C.c_uint32, C.c_uint32, u64, C.c_uint32, u64, vp, u64, vp, vp, vp]),
         "rs_comm_create": (i32, [i32, i32, i32, u64, C.POINTER(vp)]),
@@ -436,9 +437,10 @@ class GpuBWT:
                                              toff.ctypes.data, cap, lo.ctypes.data, up.ctypes.data))
         return toff, lo[:cap], up[:cap]
 
-    def build_locate_table(self, max_read_len: int = 4096):
-        """8 bytes per BWT symbol of HBM: the locate stage then reads one entry per hit row instead of walking."""
-        _check(lib().rs_index_build_locate_table(self._h, max_read_len))
+    def build_locate_table(self, max_read_len: int = 4096, every: int = 1):
+        """every = 1: 8 bytes per BWT symbol of HBM, the locate stage reads one entry per hit row instead of walking;
+        every > 1: sampled (n (1/8 + 1/64 + 8/every) bytes), a hit row is walked fewer than `every` steps."""
+        _check(lib().rs_index_build_locate_samples(self._h, max_read_len, every))
         _check(lib().rs_index_get_info(self._h, C.byref(self.info)))
 
     def drop_locate_table(self):

@@ -96,6 +96,15 @@ def test_locate_table_gives_the_walks_answers(name, datasets, engine):
             assert B.info.hbm_bytes == hbm0 + 8 * (n + case.num_strings)
             lex1, st1, ri1 = B.extract_prefix(rows, max_steps=130, want_read_index=True)
             assert np.array_equal(lex0, lex1) and np.array_equal(st0, st1) and np.array_equal(ri0, ri1), (name, emulate)
+            for every in (2, 7, 16, 64, 500):     # sampled variant: walk to the next sampled row
+                B.build_locate_table(max_read_len=120, every=every)
+                assert B.info.hbm_bytes < hbm0 + 8 * (n + case.num_strings) // (1 if every == 2 else 2) + 4096
+                lex6, st6, ri6 = B.extract_prefix(rows, max_steps=130, want_read_index=True)
+                assert np.array_equal(lex0, lex6) and np.array_equal(st0, st6) and np.array_equal(ri0, ri6), (name, emulate, every)
+                lex7, st7 = B.extract_prefix(rows[:50_000], max_steps=40)
+                assert np.array_equal(lex7[st7 != 0xFFFFFFFF], lex0[:50_000][st7 != 0xFFFFFFFF])
+                assert np.array_equal(st7 == 0xFFFFFFFF, st0[:50_000] > 40)
+            B.build_locate_table(max_read_len=120)
             # a cut below the read length: same rows reported as cut off
             lex2, st2 = B.extract_prefix(rows[:50_000], max_steps=40)
             B.drop_locate_table()
