@@ -83,7 +83,10 @@ class GpuBWT : public BWT {
   }
   // optional locate table (8 bytes of HBM per BWT symbol): the locate stage reads one entry per hit row instead of
   // walking; results do not depend on it
-  void buildLocateTable(uint32_t max_read_len = 4096) { check(rs_index_build_locate_table(ix_, max_read_len)); }
+  // every > 1: sampled variant, n (1/8 + 1/64 + 8/every) bytes, a hit row is walked fewer than `every` steps
+  void buildLocateTable(uint32_t max_read_len = 4096, uint32_t every = 1) {
+    check(rs_index_build_locate_samples(ix_, max_read_len, every));
+  }
   void dropLocateTable() { check(rs_index_drop_locate_table(ix_)); }
   // packed read table for output=reads, from the same file (reads holding 'N' are not in the BWT)
   void loadReadsFile(const std::string& path) { check(rs_index_load_reads_file(ix_, path.c_str())); }

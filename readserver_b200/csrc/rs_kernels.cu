@@ -480,7 +480,12 @@ __global__ void __launch_bounds__(RS_THREADS, RS_K2_BLOCKS_BUILD)
     uint64_t term = ~0ull;
     uint32_t nsteps = 0xFFFFFFFFu, s = 0;
     while (true) {
-      if (idx < ix.n && ((__ldg(ix.loc_mark + (idx >> 6)) >> (idx & 63)) & 1ull)) {
+      /* the marker word and the blocks of the LF step are fetched together: the step is wasted on a sampled row,
+       * but the two reads do not wait for each other on the others */
+      const uint64_t mw = idx < ix.n ? __ldg(ix.loc_mark + (idx >> 6)) : 0;
+      uint64_t nxt;
+      const uint32_t sym = rs_lf_step(ix, idx, &nxt);
+      if ((mw >> (idx & 63)) & 1ull) {
         const uint64_t e = __ldg(ix.loc + rs_sample_slot(ix.loc_mark, ix.loc_rank, idx));
         const uint64_t f = e != ~0ull ? __ldg(ix.loc_fin + (e >> 24)) : ~0ull;
         if (f != ~0ull) {
@@ -492,8 +497,6 @@ __global__ void __launch_bounds__(RS_THREADS, RS_K2_BLOCKS_BUILD)
           break;
         }
       }
-      uint64_t nxt;
-      const uint32_t sym = rs_lf_step(ix, idx, &nxt);
       ++lf_steps;
       idx = nxt;
       if (sym == 0) {
