@@ -68,6 +68,25 @@ int rs_index_open(const char* bwt_path, int device, rs_index** out);
 /* Same from run bytes already in memory (sym<<5 | len, include/bwt/rlunit.h:8-16). */
 int rs_index_from_runs(const uint8_t* runs, uint64_t num_runs, uint64_t num_strings, uint64_t num_symbols,
                        int device, rs_index** out);
+/* Same from run bytes already in device memory on `device` (no host staging at all).  The re-encoding itself --
+ * RLEBWT::initialiseFMIndex, rlebwt.cpp:34-148, one pass on one host thread in the reference -- runs on the GPU
+ * for all three (rs_encode.cu). */
+int rs_index_from_runs_dev(const void* d_runs, uint64_t num_runs, uint64_t num_strings, uint64_t num_symbols,
+                           int device, rs_index** out);
+/* The same index built by the host-side encoder (one streaming pass, rs_build.cpp): kept as the cross-check of
+ * the device encoder -- tests compare the arrays of the two byte for byte (rs_index_export). */
+int rs_index_from_runs_host(const uint8_t* runs, uint64_t num_runs, uint64_t num_strings, uint64_t num_symbols,
+                            int device, rs_index** out);
+/* Persisted HBM-layout index: what the reference's .bpi2 file is to its BP-tree (RLEBWT::serialiseFMIndex /
+ * deserialiseFMIndex, rlebwt.cpp:22-31, 150-200; written by src/util/index_rlebwt.cpp).  rs_index_save writes the
+ * blocks, both directories, the constants and -- when attached -- the .sai table; rs_index_open_encoded loads such
+ * a file without touching the .bwt (file -> pinned staging -> HBM, read and copy overlapped) and rebuilds only
+ * the k-mer suffix table. */
+int rs_index_save(const rs_index* ix, const char* path);
+int rs_index_open_encoded(const char* path, int device, rs_index** out);
+/* Copy of one device array of the index (0 blocks, 1 position directory, 2..6 select directory of $,A,C,G,T,
+ * 7 k-mer suffix table): *bytes = its size; copied when buf != NULL and capacity suffices. */
+int rs_index_export(const rs_index* ix, int what, void* buf, uint64_t capacity, uint64_t* bytes);
 void rs_index_close(rs_index* ix);
 int rs_index_get_info(const rs_index* ix, rs_index_info* info);
 /* 1 (default): bit-exact with the reference; 0: exact rank/access everywhere. */
@@ -145,6 +164,7 @@ int rs_count_batch_dev(const rs_index* ix, const void* d_kmers, int k, size_t Q,
 /* Attach the lexicographic-rank -> read-index table (SGA's .sai, written by `sga index` next to the
  * .bwt: submodules/sga/src/SuffixTools/SampledSuffixArray.cpp:171-189).  sai has num_strings entries. */
 int rs_index_set_sai(rs_index* ix, const uint64_t* sai, uint64_t num_strings);
+int rs_index_set_sai_dev(rs_index* ix, const void* d_sai, uint64_t num_strings); /* device-to-device copy */
 /* extractPrefix (src/bwt/query.cpp:43-63) for n BWT rows: LF-walk to the '$'.
  *   lexrank[i]  terminal row = lexicographic rank of the read (UINT64_MAX if the walk did not end
  *               within max_steps bases: inside the reference's tail region it can cycle forever)
@@ -188,15 +208,25 @@ int rs_locate_batch_dev(const rs_index* ix, const void* d_kmers, int k, size_t Q
  * [offsets[r], offsets[r+1]) of size_of_sample bytes each; offsets has num_strings+1 entries. */
 int rs_index_set_samples(rs_index* ix, const uint64_t* offsets, const uint8_t* codes, uint64_t num_strings,
                          int size_of_sample);
+int rs_index_set_samples_dev(rs_index* ix, const void* d_offsets, const void* d_codes, uint64_t num_strings,
+                             int size_of_sample); /* device-to-device copy */
+/* With the store's other metadata (has_other_meta_data = 1, demo/TEMPLATE.service.cfg:23): meta holds 2 bytes per
+ * code, the count and lane characters that follow it in the value (service.cpp:829-843); NULL = none. */
+int rs_index_set_samples_meta(rs_index* ix, const uint64_t* offsets, const uint8_t* codes, const uint8_t* meta,
+                              uint64_t num_strings, int size_of_sample);
 /* The same table straight from the ETL's merged read file (`read\n codes\n` pairs in RLO order, the input of
  * src/util/load_data_into_rocksdb.cpp:41-49): the i-th read without 'N' is read index i (build_bwt.sh:919);
- * with has_other_meta_data each code is followed by count and lane bytes (service.cpp:829-843), which the
- * table drops.  Replaces the 64 RocksDB loads of build_bwt.sh step 9 on this path. */
+ * with has_other_meta_data each code is followed by count and lane bytes (service.cpp:829-843), kept beside the
+ * codes (rs_samples_meta_batch).  Replaces the 64 RocksDB loads of build_bwt.sh step 9 on this path. */
 int rs_index_load_samples_file(rs_index* ix, const char* path, int size_of_sample, int has_other_meta_data);
 /* Sample codes of n reads, order and duplicates preserved (service.cpp:829-843):
  * out_offsets[n+1] in codes (always written); out_codes holds `capacity` codes, else RS_STATUS_CAPACITY. */
 int rs_samples_batch(const rs_index* ix, const uint64_t* read_index, size_t n, uint64_t* out_offsets,
                      uint64_t capacity, uint8_t* out_codes);
+/* The same plus, per code, its count and lane bytes as stored (char - 33 each is the number: service.cpp:833-841);
+ * out_meta = 2 x capacity bytes, needs a table attached with metadata. */
+int rs_samples_meta_batch(const rs_index* ix, const uint64_t* read_index, size_t n, uint64_t* out_offsets,
+                          uint64_t capacity, uint8_t* out_codes, uint8_t* out_meta);
 /* Carrier sets: for each of Q k-mers whose hits are read_index[hit_offsets[q] .. hit_offsets[q+1]),
  * the distinct sample codes over those reads in ascending order. */
 int rs_carriers_batch(const rs_index* ix, const uint64_t* hit_offsets, const uint64_t* read_index, size_t Q,
@@ -250,6 +280,55 @@ int rs_gt_reads_batch(const rs_index* ix, const char* text, const uint64_t* offs
                       uint32_t kmer, uint32_t skip, uint64_t max_interval_size, uint32_t max_steps, uint64_t max_rows,
                       uint64_t* out_offsets, uint64_t capacity, uint64_t* read_index, uint32_t* flags,
                       uint64_t* candidate_rows);
+
+/* ---- population queries over a set of shards on one GPU ------------------------------------------------
+ * The reference runs one worker per BWT shard; its front end broadcasts every query to all of them and, per query,
+ * sums their counts and concatenates their read lists (src/service/server.cpp:124, 184-197, 404-410, 957); a worker
+ * answers with findInterval, one walk per hit row and one sample-store lookup per read (service.cpp:279-315, 714-751,
+ * 816-845).  A shard set holds the shards resident on one GPU and answers a whole batch in one device pipeline.
+ *
+ *   rs_shardset_add     the index stays owned by the caller and must outlive the set; needs its .sai attached
+ *                       (and its sample table, if carrier sets are wanted); shard_id < 4096 names it in the hits
+ *   rs_shardset_seal    locate_every = 1: builds a read-index table per shard (4 bytes per BWT row: the rows of an
+ *                       interval are contiguous, so a query's read indices are read with coalesced loads instead of
+ *                       walking; per-read sample-set bitmaps as well when the tables hold <= 128 samples);
+ *                       locate_every > 1: the sampled locate table of rs_index_build_locate_samples per shard;
+ *                       locate_every = 0: plain walks (K2).  max_read_len bounds every walk.
+ *   rs_pop_query[_dev]  Q k-mers of one length k <= 31: ASCII (packed = 0, k bytes each) or packed (packed = 1:
+ *                       one uint64 per k-mer, 2 bits per base A,C,G,T = 0..3, first base most significant, bit 63
+ *                       set = the k-mer holds a byte outside ACGT and counts 0, service.cpp:299-301).  Forward strand.
+ *     counts[Q]           population count = sum over the set's shards of the interval widths (count_reads)
+ *     hit_offsets[Q+1]    may be NULL (count only).  CSR of each k-mer's hits; a k-mer's hits are contiguous: shard
+ *                         after shard in the order added, rows of the shard's interval in order, at most max_hits
+ *                         rows per shard
+ *     hits[capacity]      shard_id << 40 | read index (the read's position in the shard's builder input order, what
+ *                         the .sai gives for the terminal row of extractPrefix's walk); UINT64_MAX for a row whose
+ *                         walk does not end (reference tail region).  Hits beyond capacity are dropped:
+ *                         *total_hits > capacity tells (the host-pointer call then returns RS_STATUS_CAPACITY)
+ *     carriers[Q x W]     may be NULL.  Bit s of a k-mer's W 32-bit words = sample number s (0-based: code - 1,
+ *                         create_samples_hash.cpp:41-50) carries at least one of its hit reads; W = carrier_words
+ *                         of rs_shardset_get_info.  Needs the hit list.
+ * The _dev call is asynchronous on `stream` and never synchronises; calls on one set are serialised. */
+typedef struct rs_shardset rs_shardset;
+typedef struct rs_shardset_info {
+  uint32_t num_shards, sealed, locate_every, max_read_len, num_samples, carrier_words;
+  uint64_t index_bytes;   /* blocks, directories and attached tables of the shards            */
+  uint64_t table_bytes;   /* read-index tables and sample-set bitmaps built by the seal       */
+  uint64_t bwlen, num_strings, num_runs; /* summed over the shards                            */
+  uint64_t chunk_queries; /* queries per pipeline chunk                                        */
+} rs_shardset_info;
+int rs_shardset_create(int device, rs_shardset** out);
+int rs_shardset_add(rs_shardset* set, rs_index* ix, uint32_t shard_id);
+int rs_shardset_seal(rs_shardset* set, uint32_t max_read_len, uint32_t locate_every);
+void rs_shardset_destroy(rs_shardset* set);
+int rs_shardset_get_info(const rs_shardset* set, rs_shardset_info* info);
+int rs_shardset_enable_stats(rs_shardset* set, int on);
+int rs_shardset_read_stats(rs_shardset* set, uint64_t* interval_steps, uint64_t* walk_steps, int reset);
+int rs_pop_query_dev(rs_shardset* set, const void* d_kmers, int k, size_t Q, int packed, uint64_t max_hits,
+                     void* d_counts, void* d_hit_offsets, void* d_hits, uint64_t capacity, void* d_carriers,
+                     void* d_total_hits, void* stream);
+int rs_pop_query(rs_shardset* set, const void* kmers, int k, size_t Q, int packed, uint64_t max_hits, uint64_t* counts,
+                 uint64_t* hit_offsets, uint64_t* hits, uint64_t capacity, uint32_t* carriers, uint64_t* total_hits);
 
 /* ---- fan-in of per-shard counts across the GPUs of one box ----------------------------------------
  * Replaces the front end's sum over shard replies (src/service/server.cpp:184-197, 404-410).  One

@@ -14,8 +14,8 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "librs_b200.so")
-SOURCES = ["rs_capi.cu", "rs_capi_locate.cu", "rs_kernels.cu", "rs_pipeline.cu", "rs_roofline.cu", "rs_peer.cu", "rs_tiles.cu", "rs_gt.cu", "rs_reads.cu", "rs_build.cpp"]
-HEADERS = ["rs_internal.h", "rs_layout.h", "rs_swar.h", "rs_ops.h", "rs_kernels.h", "rs_build.h",
+SOURCES = ["rs_capi.cu", "rs_capi_locate.cu", "rs_kernels.cu", "rs_pipeline.cu", "rs_roofline.cu", "rs_peer.cu", "rs_tiles.cu", "rs_gt.cu", "rs_reads.cu", "rs_pop.cu", "rs_encode.cu", "rs_build.cpp"]
+HEADERS = ["rs_internal.h", "rs_layout.h", "rs_swar.h", "rs_ops.h", "rs_kernels.h", "rs_build.h", "rs_pop.h", "rs_gt_ops.h", "rs_encode.h",
            os.path.join("..", "..", "include", "readserver_b200.h")]
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-lineinfo", "-O3", "-std=c++17",
               "-Xcompiler", "-fPIC,-O2,-Wall", "--shared", "-cudart", "static"]

@@ -1,8 +1,12 @@
 /* Host-side re-encoder: see rs_build.h. */
 #include "rs_build.h"
 
+#include <fcntl.h>
 #include <stdio.h>
 #include <string.h>
+#include <sys/mman.h>
+#include <sys/stat.h>
+#include <unistd.h>
 
 int rs_read_bwt_file(const char* path, std::vector<uint8_t>& runs, uint64_t& num_strings, uint64_t& num_symbols) {
   /* SGA binary RLE BWT (rlebwt_reader.cpp:27-48; writer submodules/sga/src/SuffixTools/BWTWriterBinary.cpp:28-46):
@@ -23,6 +27,17 @@ int rs_read_bwt_file(const char* path, std::vector<uint8_t>& runs, uint64_t& num
   if (magic != 0xCACA) {
     fclose(f);
     return RS_ERR_MAGIC;
+  }
+  /* a corrupt header must not size the allocation: the run bytes are what is left of the file */
+  {
+    const long at = ftell(f);
+    fseek(f, 0, SEEK_END);
+    const long end = ftell(f);
+    fseek(f, at, SEEK_SET);
+    if (at < 0 || end < at || (uint64_t)(end - at) < nruns) {
+      fclose(f);
+      return RS_ERR_SHORT;
+    }
   }
   runs.resize(nruns);
   if (nruns && fread(runs.data(), 1, nruns, f) != nruns) {
@@ -225,70 +240,78 @@ void rs_fill_view(const RsHostIndex& h, rs_index_dev* d) {
   rs_view_set_tail(h, true, d);
 }
 
-int rs_parse_etl_samples(const char* path, int sos, int meta, std::vector<uint64_t>& offsets, std::vector<uint8_t>& codes) {
+namespace {
+/* read-only view of a whole file (mmap; an empty file maps to nothing) */
+struct MappedFile {
+  const char* p = nullptr;
+  size_t n = 0;
+  int fd = -1;
+  bool open(const char* path) {
+    fd = ::open(path, O_RDONLY);
+    if (fd < 0) return false;
+    struct stat st;
+    if (fstat(fd, &st) != 0) return false;
+    n = (size_t)st.st_size;
+    if (n) {
+      void* m = mmap(nullptr, n, PROT_READ, MAP_PRIVATE, fd, 0);
+      if (m == MAP_FAILED) return false;
+      p = (const char*)m;
+      madvise(m, n, MADV_SEQUENTIAL);
+    }
+    return true;
+  }
+  ~MappedFile() {
+    if (p) munmap((void*)p, n);
+    if (fd >= 0) ::close(fd);
+  }
+};
+
+/* next line of [cur, end): returns false at the end; a last line without '\n' counts when non-empty */
+inline bool next_line(const char*& cur, const char* end, const char*& b, const char*& e) {
+  if (cur >= end) return false;
+  b = cur;
+  const char* nl = (const char*)memchr(cur, '\n', (size_t)(end - cur));
+  e = nl ? nl : end;
+  cur = nl ? nl + 1 : end;
+  return true;
+}
+}  // namespace
+
+int rs_parse_etl_samples(const char* path, int sos, int meta, std::vector<uint64_t>& offsets, std::vector<uint8_t>& codes,
+                         std::vector<uint8_t>* meta_out) {
   offsets.assign(1, 0);
   codes.clear();
+  if (meta_out) meta_out->clear();
   if (sos < 1) return RS_ERR_ARG;
-  FILE* f = fopen(path, "rb");
-  if (!f) return RS_ERR_OPEN;
+  MappedFile f;
+  if (!f.open(path)) return RS_ERR_OPEN;
   const size_t stride = (size_t)sos + (meta ? 2 : 0);
-  std::string read, ids;
-  auto getline = [&](std::string& out) -> bool {
-    out.clear();
-    int ch;
-    bool any = false;
-    while ((ch = fgetc(f)) != EOF) {
-      any = true;
-      if (ch == '\n') return true;
-      out.push_back((char)ch);
+  const char *cur = f.p, *end = f.p + f.n, *rb, *re, *vb, *ve;
+  while (next_line(cur, end, rb, re)) {
+    if (!next_line(cur, end, vb, ve)) return RS_ERR_ARG; /* a read without its value line */
+    if (memchr(rb, 'N', (size_t)(re - rb))) continue;    /* build_bwt.sh:919 drops it before sga index */
+    const size_t len = (size_t)(ve - vb);
+    if (len % stride != 0) return RS_ERR_ARG;
+    for (size_t i = 0; i < len; i += stride) {
+      codes.insert(codes.end(), (const uint8_t*)vb + i, (const uint8_t*)vb + i + sos);
+      if (meta && meta_out) meta_out->insert(meta_out->end(), (const uint8_t*)vb + i + sos, (const uint8_t*)vb + i + sos + 2);
     }
-    return any;
-  };
-  int rc = RS_OK;
-  while (getline(read)) {
-    if (!getline(ids)) {
-      rc = RS_ERR_ARG; /* a read without its value line */
-      break;
-    }
-    if (read.find('N') != std::string::npos) continue; /* build_bwt.sh:919 drops it before sga index */
-    if (ids.size() % stride != 0) {
-      rc = RS_ERR_ARG;
-      break;
-    }
-    for (size_t i = 0; i < ids.size(); i += stride) codes.insert(codes.end(), ids.begin() + i, ids.begin() + i + sos);
     offsets.push_back(codes.size() / (size_t)sos);
   }
-  fclose(f);
-  return rc;
+  return RS_OK;
 }
 
 int rs_parse_etl_reads(const char* path, std::string& text, std::vector<uint64_t>& offsets) {
   text.clear();
   offsets.assign(1, 0);
-  FILE* f = fopen(path, "rb");
-  if (!f) return RS_ERR_OPEN;
-  std::string line;
-  bool is_read = true, keep = false;
-  int ch, rc = RS_OK;
-  bool any = false;
-  auto end_line = [&]() {
-    if (is_read) {
-      keep = line.find('N') == std::string::npos;
-      if (keep) {
-        text += line;
-        offsets.push_back(text.size());
-      }
-    }
-    is_read = !is_read;
-    line.clear();
-    any = false;
-  };
-  while ((ch = fgetc(f)) != EOF) {
-    if (ch == '\n') end_line();
-    else { if (is_read) line.push_back((char)ch); any = true; }
+  MappedFile f;
+  if (!f.open(path)) return RS_ERR_OPEN;
+  const char *cur = f.p, *end = f.p + f.n, *rb, *re, *vb, *ve;
+  while (next_line(cur, end, rb, re)) {
+    if (!next_line(cur, end, vb, ve)) return RS_ERR_ARG; /* a read without its value line */
+    if (memchr(rb, 'N', (size_t)(re - rb))) continue;
+    text.append(rb, (size_t)(re - rb));
+    offsets.push_back(text.size());
   }
-  if (any) end_line();
-  if (!is_read) rc = RS_ERR_ARG; /* a read without its value line */
-  fclose(f);
-  return rc;
+  return RS_OK;
 }

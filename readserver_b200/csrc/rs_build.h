@@ -48,10 +48,11 @@ int rs_build_host_index(const uint8_t* runs, uint64_t nruns, uint64_t num_string
  * sample_names.cpp:47-53, merge_rlosorted_reads.cpp:45-47; the file load_data_into_rocksdb.cpp:41-49 reads).
  * Reads holding 'N' never reach the BWT (build_bwt.sh:919), so the i-th N-free read of the file is read
  * index i.  Each value is a run of size_of_sample-byte codes, each followed by 2 bytes (count, lane) iff
- * has_other_meta_data (service.cpp:829-843); the table keeps the codes.  offsets gets one entry per kept
+ * has_other_meta_data (service.cpp:829-843); the codes go to `codes`, the 2 metadata bytes per code to
+ * `meta_out` when given.  offsets gets one entry per kept
  * read + 1.  Returns RS_OK, RS_ERR_OPEN, or RS_ERR_ARG (odd line count / value length not a multiple). */
 int rs_parse_etl_samples(const char* path, int size_of_sample, int has_other_meta_data, std::vector<uint64_t>& offsets,
-                         std::vector<uint8_t>& codes);
+                         std::vector<uint8_t>& codes, std::vector<uint8_t>* meta_out = nullptr);
 
 /* The reads of the same file that reach the BWT (odd lines without 'N'), concatenated, with their offsets. */
 int rs_parse_etl_reads(const char* path, std::string& text, std::vector<uint64_t>& offsets);

@@ -4,6 +4,10 @@
 
 #include <stdlib.h>
 
+#include <new>
+
+#include "rs_encode.h"
+
 static thread_local std::string g_err;
 
 int rs_fail(int code, const char* fmt, ...) {
@@ -154,7 +158,7 @@ static uint32_t auto_ftab_k(const rs_index* ix) {
   return t;
 }
 
-static int upload(rs_index* ix, const RsHostIndex& h) {
+static int init_streams(rs_index* ix) {
   CU(cudaSetDevice(ix->device));
   CU(cudaStreamCreateWithFlags(&ix->stream, cudaStreamNonBlocking));
   CU(cudaStreamCreateWithFlags(&ix->s_h2d, cudaStreamNonBlocking));
@@ -165,18 +169,27 @@ static int upload(rs_index* ix, const RsHostIndex& h) {
     CU(cudaEventCreateWithFlags(&ix->ev_in[i], cudaEventDisableTiming));
     CU(cudaEventCreateWithFlags(&ix->ev_done[i], cudaEventDisableTiming));
   }
+  return RS_STATUS_OK;
+}
+
+/* host-built arrays -> device (the encoder of rs_build.cpp: kept as the cross-check of rs_encode.cu) */
+static int upload(rs_index* ix, const RsHostIndex& h) {
+  const int rc = init_streams(ix);
+  if (rc != RS_STATUS_OK) return rc;
   const size_t bb = h.blocks.size() * sizeof(rs_block), db = h.dir.size() * sizeof(uint64_t);
   CU(cudaMalloc(&ix->d_blocks, bb));
   CU(cudaMalloc(&ix->d_dir, db));
   CU(cudaMemcpy(ix->d_blocks, h.blocks.data(), bb, cudaMemcpyHostToDevice));
   CU(cudaMemcpy(ix->d_dir, h.dir.data(), db, cudaMemcpyHostToDevice));
   ix->hbm_bytes = bb + db;
+  ix->ndir = h.dir.size();
   rs_fill_view(h, &ix->dev);
   for (int c = 0; c < RS_NSYM; ++c) {
     const size_t sb = h.sel[c].size() * sizeof(uint32_t);
     CU(cudaMalloc(&ix->d_sel[c], sb));
     CU(cudaMemcpy(ix->d_sel[c], h.sel[c].data(), sb, cudaMemcpyHostToDevice));
     ix->dev.sel[c] = (const uint32_t*)ix->d_sel[c];
+    ix->nsel[c] = h.sel[c].size();
     ix->hbm_bytes += sb;
     ix->init_occ_ref[c] = h.init_occ[c];
   }
@@ -188,15 +201,111 @@ static int upload(rs_index* ix, const RsHostIndex& h) {
   return build_ftab(ix, auto_ftab_k(ix));
 }
 
+/* arrays built on the device (rs_encode.cu) become the index's own */
+static void adopt(rs_index* ix, rs_encoded& e, uint64_t num_strings, uint64_t num_runs) {
+  memset(&ix->dev, 0, sizeof(ix->dev));
+  ix->d_blocks = e.d_blocks;
+  ix->d_dir = e.d_dir;
+  ix->ndir = e.ndir;
+  ix->hbm_bytes = e.nblocks * sizeof(rs_block) + e.ndir * 8;
+  ix->dev.blocks = e.d_blocks;
+  ix->dev.dir = (const uint64_t*)e.d_dir;
+  ix->dev.n = e.tail.n;
+  ix->dev.nblocks = e.nblocks;
+  ix->dev.num_strings = num_strings;
+  uint64_t pc = 0;
+  for (int c = 0; c < RS_NSYM; ++c) {
+    ix->d_sel[c] = e.d_sel[c];
+    ix->nsel[c] = e.nsel[c];
+    ix->dev.sel[c] = (const uint32_t*)e.d_sel[c];
+    ix->dev.sel_shift[c] = e.sel_shift[c];
+    ix->hbm_bytes += e.nsel[c] * 4;
+    ix->dev.pc[c] = pc;
+    pc += e.tail.tot[c];
+    ix->dev.tot[c] = e.tail.tot[c];
+    ix->init_occ_ref[c] = e.tail.init_occ[c];
+  }
+  ix->dev.clamp_c = e.tail.clamp_c;
+  ix->dev.clamp_char = e.tail.clamp_char;
+  ix->dev.vlast = e.tail.vlast;
+  ix->num_runs = num_runs;
+  ix->depth = e.depth;
+  ix->q2_safe = e.tail.q2_safe != 0;
+  rs_view_set_tail(ix->init_occ_ref, true, &ix->dev);
+  memset(&e, 0, sizeof(e)); /* ownership moved */
+}
+
+static int device_ok(int device) {
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev)
+    return fail(RS_STATUS_CUDA, "CUDA device %d not available (%d devices): this engine has no CPU path", device, ndev);
+  return RS_STATUS_OK;
+}
+
+int rs_index_from_runs_dev(const void* d_runs, uint64_t num_runs, uint64_t num_strings, uint64_t num_symbols, int device,
+                           rs_index** out) {
+  if (!out) return fail(RS_STATUS_ARG, "out is null");
+  *out = nullptr;
+  int rc = device_ok(device);
+  if (rc != RS_STATUS_OK) return rc;
+  if (!d_runs || !num_runs) return fail(RS_STATUS_ARG, "no run bytes");
+  rs_index* ix = new (std::nothrow) rs_index;
+  if (!ix) return fail(RS_STATUS_ARG, "out of host memory");
+  ix->device = device;
+  rc = init_streams(ix);
+  if (rc == RS_STATUS_OK) {
+    rs_encoded enc;
+    const int erc = rs_encode_device((const uint8_t*)d_runs, num_runs, num_symbols, ix->stream, &enc);
+    if (erc == RS_ERR_CUDA) rc = RS_STATUS_CUDA; /* message already recorded */
+    else if (erc != RS_OK) rc = fail(erc, "cannot build index from run bytes (status %d)", erc);
+    else {
+      adopt(ix, enc, num_strings, num_runs);
+      rc = build_ftab(ix, auto_ftab_k(ix));
+    }
+  }
+  if (rc != RS_STATUS_OK) {
+    rs_index_close(ix);
+    return rc;
+  }
+  *out = ix;
+  return RS_STATUS_OK;
+}
+
 int rs_index_from_runs(const uint8_t* runs, uint64_t num_runs, uint64_t num_strings, uint64_t num_symbols, int device,
                        rs_index** out) {
   if (!out) return fail(RS_STATUS_ARG, "out is null");
   *out = nullptr;
-  int ndev = 0;
-  if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev)
-    return fail(RS_STATUS_CUDA, "CUDA device %d not available (%d devices): this engine has no CPU path", device, ndev);
+  const int rc = device_ok(device);
+  if (rc != RS_STATUS_OK) return rc;
+  if (!runs || !num_runs) return fail(RS_STATUS_ARG, "no run bytes");
+  CU(cudaSetDevice(device));
+  uint8_t* d_runs = nullptr;
+  CU(cudaMalloc((void**)&d_runs, num_runs));
+  cudaError_t e = cudaMemcpy(d_runs, runs, num_runs, cudaMemcpyHostToDevice);
+  if (e != cudaSuccess) {
+    cudaFree(d_runs);
+    return fail(RS_STATUS_CUDA, "copy of the run bytes: %s", cudaGetErrorString(e));
+  }
+  const int st = rs_index_from_runs_dev(d_runs, num_runs, num_strings, num_symbols, device, out);
+  cudaFree(d_runs);
+  return st;
+}
+
+/* The same index through the HOST encoder (rs_build.cpp, one streaming pass on one thread): the cross-check of
+ * the device encoder; tests compare the arrays of the two byte for byte. */
+int rs_index_from_runs_host(const uint8_t* runs, uint64_t num_runs, uint64_t num_strings, uint64_t num_symbols, int device,
+                            rs_index** out) {
+  if (!out) return fail(RS_STATUS_ARG, "out is null");
+  *out = nullptr;
+  const int drc = device_ok(device);
+  if (drc != RS_STATUS_OK) return drc;
   RsHostIndex h;
-  const int rc = rs_build_host_index(runs, num_runs, num_strings, num_symbols, h);
+  int rc;
+  try {
+    rc = rs_build_host_index(runs, num_runs, num_strings, num_symbols, h);
+  } catch (const std::bad_alloc&) {
+    return fail(RS_STATUS_ARG, "out of host memory");
+  }
   if (rc != RS_OK) return fail(rc, "cannot build index from run bytes (status %d)", rc);
   rs_index* ix = new rs_index;
   ix->device = device;
@@ -211,11 +320,214 @@ int rs_index_from_runs(const uint8_t* runs, uint64_t num_runs, uint64_t num_stri
 
 int rs_index_open(const char* bwt_path, int device, rs_index** out) {
   if (!bwt_path || !out) return fail(RS_STATUS_ARG, "null argument");
+  *out = nullptr;
   std::vector<uint8_t> runs;
   uint64_t ns = 0, nsym = 0;
-  const int rc = rs_read_bwt_file(bwt_path, runs, ns, nsym);
+  int rc;
+  try {
+    rc = rs_read_bwt_file(bwt_path, runs, ns, nsym);
+  } catch (const std::exception&) { /* bad_alloc / length_error on a corrupt header */
+    rc = RS_ERR_SHORT;
+  }
   if (rc != RS_OK) return fail(rc, "%s: cannot read SGA .bwt (status %d)", bwt_path, rc);
   return rs_index_from_runs(runs.data(), runs.size(), ns, nsym, device, out);
+}
+
+/* ---- persisted HBM-layout index (the .bpi2 analogue: rlebwt.cpp:22-31, 150-176; src/util/index_rlebwt.cpp) ---- */
+namespace {
+struct IndexFileHeader {
+  char magic[8]; /* "RSB2IDX1" */
+  uint64_t n, num_strings, num_runs, nblocks, ndir;
+  uint64_t nsel[RS_NSYM], sel_shift[RS_NSYM], pc[RS_NSYM], tot[RS_NSYM], init_occ_ref[RS_NSYM];
+  uint64_t clamp_c, clamp_char, vlast, depth, q2_safe, has_sai;
+};
+const size_t kIoChunk = 64u << 20;
+
+int write_dev(FILE* f, const void* d, size_t bytes, uint8_t* stage) {
+  for (size_t o = 0; o < bytes; o += kIoChunk) {
+    const size_t m = bytes - o < kIoChunk ? bytes - o : kIoChunk;
+    if (cudaMemcpy(stage, (const uint8_t*)d + o, m, cudaMemcpyDeviceToHost) != cudaSuccess) return 1;
+    if (fwrite(stage, 1, m, f) != m) return 2;
+  }
+  return 0;
+}
+
+/* file -> device through two pinned buffers: the read of a chunk overlaps the copy of the previous one */
+int read_dev(FILE* f, void* d, size_t bytes, uint8_t* stage[2], cudaEvent_t ev[2], cudaStream_t st, int* turn) {
+  for (size_t o = 0; o < bytes; o += kIoChunk) {
+    const size_t m = bytes - o < kIoChunk ? bytes - o : kIoChunk;
+    const int t = (*turn)++ & 1;
+    if (cudaEventSynchronize(ev[t]) != cudaSuccess) return 1;
+    if (fread(stage[t], 1, m, f) != m) return 2;
+    if (cudaMemcpyAsync((uint8_t*)d + o, stage[t], m, cudaMemcpyHostToDevice, st) != cudaSuccess) return 1;
+    if (cudaEventRecord(ev[t], st) != cudaSuccess) return 1;
+  }
+  return 0;
+}
+}  // namespace
+
+int rs_index_save(const rs_index* ix, const char* path) {
+  if (!ix || !path) return fail(RS_STATUS_ARG, "null argument");
+  std::lock_guard<std::mutex> lk(ix->mu);
+  CU(cudaSetDevice(ix->device));
+  CU(cudaStreamSynchronize(ix->stream));
+  FILE* f = fopen(path, "wb");
+  if (!f) return fail(RS_STATUS_OPEN, "cannot create %s", path);
+  IndexFileHeader h;
+  memset(&h, 0, sizeof(h));
+  memcpy(h.magic, "RSB2IDX1", 8);
+  h.n = ix->dev.n;
+  h.num_strings = ix->dev.num_strings;
+  h.num_runs = ix->num_runs;
+  h.nblocks = ix->dev.nblocks;
+  h.ndir = ix->ndir;
+  for (int c = 0; c < RS_NSYM; ++c) {
+    h.nsel[c] = ix->nsel[c];
+    h.sel_shift[c] = ix->dev.sel_shift[c];
+    h.pc[c] = ix->dev.pc[c];
+    h.tot[c] = ix->dev.tot[c];
+    h.init_occ_ref[c] = ix->init_occ_ref[c];
+  }
+  h.clamp_c = ix->dev.clamp_c;
+  h.clamp_char = ix->dev.clamp_char;
+  h.vlast = ix->dev.vlast;
+  h.depth = ix->depth;
+  h.q2_safe = ix->q2_safe ? 1 : 0;
+  h.has_sai = ix->d_sai ? 1 : 0;
+  uint8_t* stage = nullptr;
+  if (cudaMallocHost((void**)&stage, kIoChunk) != cudaSuccess) {
+    fclose(f);
+    return fail(RS_STATUS_CUDA, "cannot allocate the staging buffer");
+  }
+  int bad = fwrite(&h, sizeof(h), 1, f) != 1 ? 2 : 0;
+  if (!bad) bad = write_dev(f, ix->d_blocks, h.nblocks * sizeof(rs_block), stage);
+  if (!bad) bad = write_dev(f, ix->d_dir, h.ndir * 8, stage);
+  for (int c = 0; c < RS_NSYM && !bad; ++c) bad = write_dev(f, ix->d_sel[c], h.nsel[c] * 4, stage);
+  if (!bad && ix->d_sai) bad = write_dev(f, ix->d_sai, h.num_strings * 8, stage);
+  cudaFreeHost(stage);
+  if (fclose(f) != 0 && !bad) bad = 2;
+  if (bad == 1) return fail(RS_STATUS_CUDA, "device read failed while saving %s", path);
+  if (bad) return fail(RS_STATUS_OPEN, "write to %s failed", path);
+  return RS_STATUS_OK;
+}
+
+int rs_index_open_encoded(const char* path, int device, rs_index** out) {
+  if (!path || !out) return fail(RS_STATUS_ARG, "null argument");
+  *out = nullptr;
+  int rc = device_ok(device);
+  if (rc != RS_STATUS_OK) return rc;
+  FILE* f = fopen(path, "rb");
+  if (!f) return fail(RS_STATUS_OPEN, "cannot open %s", path);
+  IndexFileHeader h;
+  if (fread(&h, sizeof(h), 1, f) != 1) {
+    fclose(f);
+    return fail(RS_STATUS_SHORT, "%s: truncated header", path);
+  }
+  if (memcmp(h.magic, "RSB2IDX1", 8) != 0) {
+    fclose(f);
+    return fail(RS_STATUS_MAGIC, "%s is not an encoded index of this library", path);
+  }
+  /* sizes must agree with the file before anything is allocated from them */
+  uint64_t need = sizeof(h) + h.nblocks * sizeof(rs_block) + h.ndir * 8 + (h.has_sai ? h.num_strings * 8 : 0);
+  for (int c = 0; c < RS_NSYM; ++c) need += h.nsel[c] * 4;
+  fseek(f, 0, SEEK_END);
+  const uint64_t have = (uint64_t)ftell(f);
+  fseek(f, (long)sizeof(h), SEEK_SET);
+  if (have < need || h.nblocks == 0 || h.nblocks > 0xFFFFFFFFull || h.ndir != (h.n >> RS_SLOT_SHIFT) + 2) {
+    fclose(f);
+    return fail(RS_STATUS_SHORT, "%s: truncated or inconsistent (%llu bytes, header asks for %llu)", path,
+                (unsigned long long)have, (unsigned long long)need);
+  }
+  rs_index* ix = new (std::nothrow) rs_index;
+  if (!ix) {
+    fclose(f);
+    return fail(RS_STATUS_ARG, "out of host memory");
+  }
+  ix->device = device;
+  rc = init_streams(ix);
+  uint8_t* stage[2] = {nullptr, nullptr};
+  cudaEvent_t ev[2] = {nullptr, nullptr};
+  int turn = 0, bad = 0;
+  if (rc == RS_STATUS_OK) {
+    cudaError_t e = cudaMallocHost((void**)&stage[0], kIoChunk);
+    if (e == cudaSuccess) e = cudaMallocHost((void**)&stage[1], kIoChunk);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ev[0], cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaEventCreateWithFlags(&ev[1], cudaEventDisableTiming);
+    if (e == cudaSuccess) e = cudaMalloc(&ix->d_blocks, h.nblocks * sizeof(rs_block));
+    if (e == cudaSuccess) e = cudaMalloc(&ix->d_dir, h.ndir * 8);
+    for (int c = 0; c < RS_NSYM && e == cudaSuccess; ++c) e = cudaMalloc(&ix->d_sel[c], (h.nsel[c] ? h.nsel[c] : 1) * 4);
+    if (e == cudaSuccess && h.has_sai) e = cudaMalloc((void**)&ix->d_sai, (h.num_strings ? h.num_strings : 1) * 8);
+    if (e != cudaSuccess) rc = fail(RS_STATUS_CUDA, "%s: %s", path, cudaGetErrorString(e));
+  }
+  if (rc == RS_STATUS_OK) {
+    cudaStream_t st = ix->s_h2d;
+    bad = read_dev(f, ix->d_blocks, h.nblocks * sizeof(rs_block), stage, ev, st, &turn);
+    if (!bad) bad = read_dev(f, ix->d_dir, h.ndir * 8, stage, ev, st, &turn);
+    for (int c = 0; c < RS_NSYM && !bad; ++c) bad = read_dev(f, ix->d_sel[c], h.nsel[c] * 4, stage, ev, st, &turn);
+    if (!bad && h.has_sai) bad = read_dev(f, ix->d_sai, h.num_strings * 8, stage, ev, st, &turn);
+    if (cudaStreamSynchronize(st) != cudaSuccess) bad = 1;
+    if (bad) rc = fail(bad == 1 ? RS_STATUS_CUDA : RS_STATUS_SHORT, "%s: read failed", path);
+  }
+  fclose(f);
+  for (int t = 0; t < 2; ++t) {
+    if (stage[t]) cudaFreeHost(stage[t]);
+    if (ev[t]) cudaEventDestroy(ev[t]);
+  }
+  if (rc == RS_STATUS_OK) {
+    memset(&ix->dev, 0, sizeof(ix->dev));
+    ix->dev.blocks = ix->d_blocks;
+    ix->dev.dir = (const uint64_t*)ix->d_dir;
+    ix->dev.n = h.n;
+    ix->dev.nblocks = h.nblocks;
+    ix->dev.num_strings = h.num_strings;
+    ix->ndir = h.ndir;
+    ix->hbm_bytes = h.nblocks * sizeof(rs_block) + h.ndir * 8 + (h.has_sai ? h.num_strings * 8 : 0);
+    for (int c = 0; c < RS_NSYM; ++c) {
+      ix->dev.sel[c] = (const uint32_t*)ix->d_sel[c];
+      ix->dev.sel_shift[c] = (uint32_t)h.sel_shift[c];
+      ix->nsel[c] = h.nsel[c];
+      ix->hbm_bytes += h.nsel[c] * 4;
+      ix->dev.pc[c] = h.pc[c];
+      ix->dev.tot[c] = h.tot[c];
+      ix->init_occ_ref[c] = h.init_occ_ref[c];
+    }
+    ix->dev.clamp_c = h.clamp_c;
+    ix->dev.clamp_char = h.clamp_char;
+    ix->dev.vlast = h.vlast;
+    ix->num_runs = h.num_runs;
+    ix->depth = h.depth;
+    ix->q2_safe = h.q2_safe != 0;
+    rs_view_set_tail(ix->init_occ_ref, true, &ix->dev);
+    rc = build_ftab(ix, auto_ftab_k(ix));
+  }
+  if (rc != RS_STATUS_OK) {
+    rs_index_close(ix);
+    return rc;
+  }
+  *out = ix;
+  return RS_STATUS_OK;
+}
+
+/* Copies one of the index's device arrays to the host (tests: device encoder == host encoder; saved == loaded).
+ * what: 0 blocks, 1 position directory, 2..6 select directory of $,A,C,G,T, 7 suffix table.  *bytes receives the
+ * array's size; the copy is made when buf is non-null and capacity suffices. */
+int rs_index_export(const rs_index* ix, int what, void* buf, uint64_t capacity, uint64_t* bytes) {
+  if (!ix || !bytes) return fail(RS_STATUS_ARG, "null argument");
+  const void* d = nullptr;
+  uint64_t n = 0;
+  if (what == 0) { d = ix->d_blocks; n = ix->dev.nblocks * sizeof(rs_block); }
+  else if (what == 1) { d = ix->d_dir; n = ix->ndir * 8; }
+  else if (what >= 2 && what <= 6) { d = ix->d_sel[what - 2]; n = ix->nsel[what - 2] * 4; }
+  else if (what == 7) { d = ix->d_ftab; n = ix->d_ftab ? (16ull << (2 * ix->dev.ftab_k)) : 0; }
+  else return fail(RS_STATUS_ARG, "unknown array %d", what);
+  *bytes = n;
+  if (!buf) return RS_STATUS_OK;
+  if (capacity < n) return fail(RS_STATUS_CAPACITY, "array needs %llu bytes", (unsigned long long)n);
+  std::lock_guard<std::mutex> lk(ix->mu);
+  CU(cudaSetDevice(ix->device));
+  CU(cudaStreamSynchronize(ix->stream));
+  if (n) CU(cudaMemcpy(buf, d, n, cudaMemcpyDeviceToHost));
+  return RS_STATUS_OK;
 }
 
 void rs_index_close(rs_index* ix) {
@@ -229,6 +541,7 @@ void rs_index_close(rs_index* ix) {
   if (ix->d_sai) cudaFree(ix->d_sai);
   if (ix->d_samp_off) cudaFree(ix->d_samp_off);
   if (ix->d_samp_codes) cudaFree(ix->d_samp_codes);
+  if (ix->d_samp_meta) cudaFree(ix->d_samp_meta);
   if (ix->d_stats) cudaFree(ix->d_stats);
   if (ix->d_ftab) cudaFree(ix->d_ftab);
   if (ix->d_loc) cudaFree(ix->d_loc);
@@ -539,6 +852,24 @@ int rs_index_set_sai(rs_index* ix, const uint64_t* sai, uint64_t num_strings) {
   }
   CU(cudaMalloc((void**)&ix->d_sai, num_strings ? num_strings * 8 : 8));
   CU(cudaMemcpy(ix->d_sai, sai, num_strings * 8, cudaMemcpyHostToDevice));
+  ix->hbm_bytes += num_strings * 8;
+  return RS_STATUS_OK;
+}
+
+int rs_index_set_sai_dev(rs_index* ix, const void* d_sai, uint64_t num_strings) {
+  if (!ix || !d_sai) return fail(RS_STATUS_ARG, "null argument");
+  if (num_strings != ix->dev.num_strings)
+    return fail(RS_STATUS_ARG, "sai has %llu entries, the index holds %llu strings", (unsigned long long)num_strings,
+                (unsigned long long)ix->dev.num_strings);
+  std::lock_guard<std::mutex> lk(ix->mu);
+  CU(cudaSetDevice(ix->device));
+  if (ix->d_sai) {
+    cudaFree(ix->d_sai);
+    ix->hbm_bytes -= num_strings * 8;
+    ix->d_sai = nullptr;
+  }
+  CU(cudaMalloc((void**)&ix->d_sai, num_strings ? num_strings * 8 : 8));
+  CU(cudaMemcpy(ix->d_sai, d_sai, num_strings * 8, cudaMemcpyDeviceToDevice));
   ix->hbm_bytes += num_strings * 8;
   return RS_STATUS_OK;
 }

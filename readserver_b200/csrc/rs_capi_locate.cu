@@ -87,59 +87,152 @@ int rs_locate_batch(const rs_index* ix, const char* kmers, int k, size_t Q, uint
 int rs_index_load_samples_file(rs_index* ix, const char* path, int size_of_sample, int has_other_meta_data) {
   if (!ix || !path) return fail(RS_STATUS_ARG, "null argument");
   std::vector<uint64_t> offsets;
-  std::vector<uint8_t> codes;
-  const int rc = rs_parse_etl_samples(path, size_of_sample, has_other_meta_data, offsets, codes);
+  std::vector<uint8_t> codes, meta;
+  int rc;
+  try {
+    rc = rs_parse_etl_samples(path, size_of_sample, has_other_meta_data, offsets, codes, has_other_meta_data ? &meta : nullptr);
+  } catch (const std::exception&) {
+    return fail(RS_STATUS_ARG, "out of host memory while reading %s", path);
+  }
   if (rc == RS_ERR_OPEN) return fail(RS_STATUS_OPEN, "cannot open %s", path);
   if (rc != RS_OK) return fail(RS_STATUS_ARG, "%s is not a `read / codes` file for size_of_sample %d", path, size_of_sample);
-  return rs_index_set_samples(ix, offsets.data(), codes.data(), offsets.size() - 1, size_of_sample);
+  return rs_index_set_samples_meta(ix, offsets.data(), codes.data(), has_other_meta_data ? meta.data() : nullptr,
+                                   offsets.size() - 1, size_of_sample);
 }
 
-int rs_index_set_samples(rs_index* ix, const uint64_t* offsets, const uint8_t* codes, uint64_t num_strings,
-                         int size_of_sample) {
+/* validation of a sample table on the device: offsets ascending, every code byte a base-223 digit (>= 33),
+ * no code decoding to 0; max[0] = largest sample number (create_samples_hash.cpp:41-50: 1-based) */
+__global__ void k_check_offsets(const uint64_t* __restrict__ off, uint64_t n, unsigned int* __restrict__ bad) {
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += stride)
+    if (off[r + 1] < off[r]) atomicOr(bad, 1u);
+}
+__global__ void k_check_codes(const uint8_t* __restrict__ codes, uint64_t ncodes, uint32_t sos, uint32_t stride_bytes,
+                              unsigned int* __restrict__ bad, unsigned long long* __restrict__ maxv) {
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  unsigned long long m = 0;
+  unsigned int b = 0;
+  for (uint64_t t = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; t < ncodes; t += stride) {
+    unsigned long long v = 0;
+    for (uint32_t i = 0; i < sos; ++i) {
+      const uint32_t ch = codes[t * stride_bytes + i];
+      if (ch < 33) b |= 2u;
+      v = v * 223ull + (unsigned long long)(ch - 33u);
+    }
+    if (v == 0) b |= 4u;
+    if (v > m) m = v;
+  }
+  if (b) atomicOr(bad, b);
+  if (m) atomicMax(maxv, m);
+}
+
+static int adopt_samples(rs_index* ix, uint64_t* d_off, uint8_t* d_codes, uint8_t* d_meta, uint64_t num_strings, int sos,
+                         uint64_t ncodes) {
+  /* takes ownership of the device arrays (frees them on failure) */
+  unsigned int* d_bad = nullptr;
+  unsigned long long* d_max = nullptr;
+  unsigned int bad = 0;
+  unsigned long long maxv = 0;
+  cudaError_t e = cudaMalloc((void**)&d_bad, 4);
+  if (e == cudaSuccess) e = cudaMalloc((void**)&d_max, 8);
+  if (e == cudaSuccess) e = cudaMemset(d_bad, 0, 4);
+  if (e == cudaSuccess) e = cudaMemset(d_max, 0, 8);
+  if (e == cudaSuccess) {
+    if (num_strings) k_check_offsets<<<148 * 4, 256>>>(d_off, num_strings, d_bad);
+    if (ncodes) k_check_codes<<<148 * 8, 256>>>(d_codes, ncodes, (uint32_t)sos, (uint32_t)sos, d_bad, d_max);
+    e = cudaGetLastError();
+  }
+  if (e == cudaSuccess) e = cudaMemcpy(&bad, d_bad, 4, cudaMemcpyDeviceToHost);
+  if (e == cudaSuccess) e = cudaMemcpy(&maxv, d_max, 8, cudaMemcpyDeviceToHost);
+  if (d_bad) cudaFree(d_bad);
+  if (d_max) cudaFree(d_max);
+  if (e != cudaSuccess || bad) {
+    cudaFree(d_off);
+    cudaFree(d_codes);
+    if (d_meta) cudaFree(d_meta);
+    if (e != cudaSuccess) return fail(RS_STATUS_CUDA, "sample table: %s", cudaGetErrorString(e));
+    if (bad & 1u) return fail(RS_STATUS_ARG, "sample offsets are not ascending");
+    if (bad & 2u) return fail(RS_STATUS_ARG, "a sample code holds a byte that is not a base-223 digit (< 33)");
+    return fail(RS_STATUS_ARG, "a sample code decodes to 0 (codes are 1-based)");
+  }
+  if (ix->d_samp_off) {
+    cudaFree(ix->d_samp_off);
+    cudaFree(ix->d_samp_codes);
+    if (ix->d_samp_meta) cudaFree(ix->d_samp_meta);
+    ix->hbm_bytes -= ix->samp_bytes;
+  }
+  ix->d_samp_off = d_off;
+  ix->d_samp_codes = d_codes;
+  ix->d_samp_meta = d_meta;
+  ix->size_of_sample = sos;
+  ix->num_samples = (uint32_t)maxv;
+  ix->samp_bytes = (num_strings + 1) * 8 + ncodes * (uint64_t)sos + (d_meta ? ncodes * 2 : 0);
+  ix->hbm_bytes += ix->samp_bytes;
+  return RS_STATUS_OK;
+}
+
+static int set_samples_any(rs_index* ix, const uint64_t* offsets, const uint8_t* codes, const uint8_t* meta,
+                           uint64_t num_strings, int size_of_sample, uint64_t ncodes, cudaMemcpyKind kind) {
+  std::lock_guard<std::mutex> lk(ix->mu);
+  CU(cudaSetDevice(ix->device));
+  uint64_t* d_off = nullptr;
+  uint8_t *d_codes = nullptr, *d_meta = nullptr;
+  const size_t ob = (num_strings + 1) * 8, cb = ncodes * (size_t)size_of_sample;
+  cudaError_t e = cudaMalloc((void**)&d_off, ob);
+  if (e == cudaSuccess) e = cudaMalloc((void**)&d_codes, cb ? cb : 8);
+  if (e == cudaSuccess && meta) e = cudaMalloc((void**)&d_meta, ncodes ? ncodes * 2 : 8);
+  if (e == cudaSuccess) e = cudaMemcpy(d_off, offsets, ob, kind);
+  if (e == cudaSuccess && cb) e = cudaMemcpy(d_codes, codes, cb, kind);
+  if (e == cudaSuccess && meta && ncodes) e = cudaMemcpy(d_meta, meta, ncodes * 2, kind);
+  if (e != cudaSuccess) {
+    if (d_off) cudaFree(d_off);
+    if (d_codes) cudaFree(d_codes);
+    if (d_meta) cudaFree(d_meta);
+    return fail(RS_STATUS_CUDA, "sample table: %s", cudaGetErrorString(e));
+  }
+  return adopt_samples(ix, d_off, d_codes, d_meta, num_strings, size_of_sample, ncodes);
+}
+
+static int samples_args(rs_index* ix, const void* offsets, uint64_t num_strings, int size_of_sample) {
   if (!ix || !offsets) return fail(RS_STATUS_ARG, "null argument");
   if (size_of_sample < 1 || size_of_sample > 4) return fail(RS_STATUS_ARG, "size_of_sample must be 1..4");
   if (num_strings != ix->dev.num_strings)
     return fail(RS_STATUS_ARG, "sample table has %llu reads, the index holds %llu", (unsigned long long)num_strings,
                 (unsigned long long)ix->dev.num_strings);
-  const uint64_t ncodes = offsets[num_strings];
-  if (ncodes && !codes) return fail(RS_STATUS_ARG, "null codes");
-  for (uint64_t r = 0; r < num_strings; ++r)
-    if (offsets[r + 1] < offsets[r]) return fail(RS_STATUS_ARG, "sample offsets are not ascending at read %llu", (unsigned long long)r);
-  /* largest sample number in the table (create_samples_hash.cpp:41-50: base-223 digits + 33, 1-based) */
-  uint64_t max_sample = 0;
-  for (uint64_t t = 0; t < ncodes; ++t) {
-    uint64_t v = 0;
-    for (int i = 0; i < size_of_sample; ++i) {
-      const uint8_t ch = codes[t * size_of_sample + i];
-      if (ch < 33) return fail(RS_STATUS_ARG, "byte %u in sample code %llu is not a base-223 digit", ch, (unsigned long long)t);
-      v = v * 223 + (uint64_t)(ch - 33);
-    }
-    if (v == 0) return fail(RS_STATUS_ARG, "sample code %llu decodes to 0 (codes are 1-based)", (unsigned long long)t);
-    if (v > max_sample) max_sample = v;
-  }
-  std::lock_guard<std::mutex> lk(ix->mu);
-  CU(cudaSetDevice(ix->device));
-  if (ix->d_samp_off) {
-    cudaFree(ix->d_samp_off);
-    cudaFree(ix->d_samp_codes);
-    ix->d_samp_off = nullptr;
-    ix->d_samp_codes = nullptr;
-  }
-  const size_t ob = (num_strings + 1) * 8, cb = ncodes * (size_t)size_of_sample;
-  CU(cudaMalloc((void**)&ix->d_samp_off, ob));
-  CU(cudaMalloc((void**)&ix->d_samp_codes, cb ? cb : 8));
-  CU(cudaMemcpy(ix->d_samp_off, offsets, ob, cudaMemcpyHostToDevice));
-  if (cb) CU(cudaMemcpy(ix->d_samp_codes, codes, cb, cudaMemcpyHostToDevice));
-  ix->size_of_sample = size_of_sample;
-  ix->num_samples = (uint32_t)max_sample;
-  ix->hbm_bytes += ob + cb;
   return RS_STATUS_OK;
 }
 
-int rs_samples_batch(const rs_index* ix, const uint64_t* read_index, size_t n, uint64_t* out_offsets,
-                     uint64_t capacity, uint8_t* out_codes) {
+int rs_index_set_samples_meta(rs_index* ix, const uint64_t* offsets, const uint8_t* codes, const uint8_t* meta,
+                              uint64_t num_strings, int size_of_sample) {
+  const int rc = samples_args(ix, offsets, num_strings, size_of_sample);
+  if (rc != RS_STATUS_OK) return rc;
+  const uint64_t ncodes = offsets[num_strings];
+  if (ncodes && !codes) return fail(RS_STATUS_ARG, "null codes");
+  return set_samples_any(ix, offsets, codes, meta, num_strings, size_of_sample, ncodes, cudaMemcpyHostToDevice);
+}
+
+int rs_index_set_samples(rs_index* ix, const uint64_t* offsets, const uint8_t* codes, uint64_t num_strings,
+                         int size_of_sample) {
+  return rs_index_set_samples_meta(ix, offsets, codes, nullptr, num_strings, size_of_sample);
+}
+
+int rs_index_set_samples_dev(rs_index* ix, const void* d_offsets, const void* d_codes, uint64_t num_strings,
+                             int size_of_sample) {
+  const int rc = samples_args(ix, d_offsets, num_strings, size_of_sample);
+  if (rc != RS_STATUS_OK) return rc;
+  CU(cudaSetDevice(ix->device));
+  uint64_t ncodes = 0;
+  CU(cudaMemcpy(&ncodes, (const uint64_t*)d_offsets + num_strings, 8, cudaMemcpyDeviceToHost));
+  if (ncodes && !d_codes) return fail(RS_STATUS_ARG, "null codes");
+  return set_samples_any(ix, (const uint64_t*)d_offsets, (const uint8_t*)d_codes, nullptr, num_strings, size_of_sample,
+                         ncodes, cudaMemcpyDeviceToDevice);
+}
+
+int rs_samples_meta_batch(const rs_index* ix, const uint64_t* read_index, size_t n, uint64_t* out_offsets,
+                          uint64_t capacity, uint8_t* out_codes, uint8_t* out_meta) {
   if (!ix || !out_offsets || (n && !read_index)) return fail(RS_STATUS_ARG, "null argument");
   if (!ix->d_samp_off) return fail(RS_STATUS_NO_TABLE, "no sample table attached");
+  if (out_meta && !ix->d_samp_meta) return fail(RS_STATUS_NO_TABLE, "the sample table holds no count / lane metadata");
   std::lock_guard<std::mutex> lk(ix->mu);
   CU(cudaSetDevice(ix->device));
   cudaStream_t st = ix->stream;
@@ -164,11 +257,20 @@ int rs_samples_batch(const rs_index* ix, const uint64_t* read_index, size_t n, u
                 (unsigned long long)capacity);
   if (!total) return RS_STATUS_OK;
   uint8_t* d_codes;
-  CU(tmp.get((void**)&d_codes, total * sos));
+  CU(tmp.get((void**)&d_codes, total * (sos > 2 ? sos : 2)));
   CU(rs_launch_sample_gather(ix->d_samp_off, ix->d_samp_codes, sos, ix->dev.num_strings, d_ri, n, d_off, d_codes, st));
   CU(cudaMemcpyAsync(out_codes, d_codes, total * sos, cudaMemcpyDeviceToHost, st));
+  if (out_meta) { /* the count and lane bytes travel beside the codes: same offsets, 2 bytes per code */
+    CU(rs_launch_sample_gather(ix->d_samp_off, ix->d_samp_meta, 2, ix->dev.num_strings, d_ri, n, d_off, d_codes, st));
+    CU(cudaMemcpyAsync(out_meta, d_codes, total * 2, cudaMemcpyDeviceToHost, st));
+  }
   CU(cudaStreamSynchronize(st));
   return RS_STATUS_OK;
+}
+
+int rs_samples_batch(const rs_index* ix, const uint64_t* read_index, size_t n, uint64_t* out_offsets,
+                     uint64_t capacity, uint8_t* out_codes) {
+  return rs_samples_meta_batch(ix, read_index, n, out_offsets, capacity, out_codes, nullptr);
 }
 
 int rs_carriers_batch(const rs_index* ix, const uint64_t* hit_offsets, const uint64_t* read_index, size_t Q,

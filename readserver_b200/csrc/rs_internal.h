@@ -72,10 +72,13 @@ struct rs_index {
   uint64_t init_occ_ref[RS_NSYM] = {0, 0, 0, 0, 0}; /* the reference's getOcc(c, n-1) */
   void* d_blocks = nullptr;
   void* d_dir = nullptr;
+  uint64_t ndir = 0, nsel[RS_NSYM] = {0, 0, 0, 0, 0}; /* entries of the position / select directories */
   void* d_sel[RS_NSYM] = {nullptr, nullptr, nullptr, nullptr, nullptr};
   uint64_t* d_sai = nullptr;
   uint64_t* d_samp_off = nullptr;
   uint8_t* d_samp_codes = nullptr;
+  uint8_t* d_samp_meta = nullptr; /* 2 bytes per code (count + 33, lane + 33) when the store has_other_meta_data */
+  uint64_t samp_bytes = 0;
   int size_of_sample = 0;
   uint32_t num_samples = 0; /* 1 + largest sample number that occurs in the table */
   uint32_t* d_reads = nullptr;     /* packed read table (rs_reads.cu): 16 bases per word */

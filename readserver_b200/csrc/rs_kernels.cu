@@ -115,7 +115,12 @@ __device__ __forceinline__ uint32_t rs_owner_of(uint64_t pk, uint32_t k, bool rc
     prefix = k >= 4 ? (uint32_t)(pk >> (2 * (k - 4))) & 0xFFu : (uint32_t)pk & 0xFFu;
   } else { /* pk holds the reverse complement: the query's first bases are its last ones, complemented */
     const uint32_t t = ~(uint32_t)pk & 0xFFu;
-    prefix = k >= 4 ? ((t & 3u) << 6) | (((t >> 2) & 3u) << 4) | (((t >> 4) & 3u) << 2) | (t >> 6) : t;
+    if (k >= 4) {
+      prefix = ((t & 3u) << 6) | (((t >> 2) & 3u) << 4) | (((t >> 4) & 3u) << 2) | (t >> 6);
+    } else { /* fewer than four bases: reverse the k complemented digits only */
+      prefix = 0;
+      for (uint32_t a = 0; a < k; ++a) prefix = (prefix << 2) | ((t >> (2 * a)) & 3u);
+    }
   }
   return prefix % world;
 }
@@ -126,6 +131,10 @@ __device__ __forceinline__ void rs_emit(int mode, uint64_t* __restrict__ lower, 
   if (mode == 0) {
     lower[q] = lo;
     upper[q] = hi;
+  } else if (mode == 4) { /* shard set (rs_pop.cu): first row and number of rows, 12 bytes per shard-query */
+    const uint64_t cnt = hi >= lo ? hi - lo + 1 : 0;
+    lower[q] = lo;
+    reinterpret_cast<uint32_t*>(upper)[q] = cnt > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)cnt;
   } else {
     const uint64_t cnt = hi >= lo ? hi - lo + 1 : 0;
     if (mode == 1) lower[q] = cnt;
@@ -139,7 +148,7 @@ __device__ __forceinline__ void rs_emit(int mode, uint64_t* __restrict__ lower, 
 template <bool FTAB, bool PACKED>
 __global__ void __launch_bounds__(RS_THREADS, RS_K1_BLOCKS)
     k_find_interval(const __grid_constant__ rs_index_dev ix, const uint8_t* __restrict__ text,
-                    const uint64_t* __restrict__ offs, uint32_t k, uint64_t Q, uint64_t* __restrict__ lower,
+                    const uint64_t* __restrict__ offs, uint32_t k, uint64_t Q, const uint64_t* pkeys, uint64_t* lower,
                     uint64_t* __restrict__ upper, int mode, int strand, unsigned long long* __restrict__ stats,
                     const __grid_constant__ rs_peers peers) {
   const uint64_t stride = (uint64_t)gridDim.x * RS_THREADS;
@@ -160,11 +169,12 @@ __global__ void __launch_bounds__(RS_THREADS, RS_K1_BLOCKS)
     if (PACKED && !active && next_q < Q) {
       const uint64_t q = next_q;
       next_q += stride;
-      pk = lower[q];
+      pk = pkeys[q]; /* PACKED: k_pack_kmers' output; parked in lower[] itself unless the caller keeps it apart */
       len = k;
       active = true;
       if (pk >> 63) { /* a byte outside ACGT */
         if (mode == 1) lower[q] = 0; /* service.cpp:299-301; mode 2: nothing to add */
+        if (mode == 4) { lower[q] = 1; reinterpret_cast<uint32_t*>(upper)[q] = 0; } /* count_reads: 0 rows */
         /* mode 0: left flagged for the tail loop below, which searches it as the reference would */
         active = false;
       } else {
@@ -341,7 +351,8 @@ __global__ void __launch_bounds__(RS_THREADS, RS_K2_BLOCKS_BUILD)
     }
     if (__all_sync(RS_FULL, !active)) break;
     if (active) {
-      loc[idx] = (i << 24) | s;
+      /* under the reference's tail behaviour an LF step can land on row n: nothing to record there */
+      if (idx < ix.n) loc[idx] = (i << 24) | s;
       uint64_t nxt;
       const uint32_t sym = rs_lf_step(ix, idx, &nxt);
       idx = nxt;
@@ -362,7 +373,8 @@ __global__ void __launch_bounds__(RS_THREADS)
     k_locate_lookup(const __grid_constant__ rs_index_dev ix, const uint64_t* __restrict__ rows, uint64_t n,
                     uint32_t max_steps, uint64_t* __restrict__ lexrank, uint32_t* __restrict__ steps,
                     const uint64_t* __restrict__ sai, uint64_t* __restrict__ read_index,
-                    unsigned long long* __restrict__ stats) {
+                    unsigned long long* __restrict__ stats, const uint64_t* __restrict__ n_dev) {
+  if (n_dev && *n_dev < n) n = *n_dev; /* item count left on the device by an earlier kernel (rs_pop.cu) */
   const uint64_t stride = (uint64_t)gridDim.x * RS_THREADS;
   unsigned long long lf_steps = 0;
   for (uint64_t i = (uint64_t)blockIdx.x * RS_THREADS + threadIdx.x; i < n; i += stride) {
@@ -416,7 +428,7 @@ __global__ void __launch_bounds__(RS_THREADS, RS_K2_BLOCKS_BUILD)
     uint64_t idx = i;
     uint32_t s = 0;
     while (true) {
-      if (s % every == 0) atomicOr(mark + (idx >> 6), 1ull << (idx & 63));
+      if (s % every == 0 && idx < ix.n) atomicOr(mark + (idx >> 6), 1ull << (idx & 63));
       uint64_t nxt;
       const uint32_t sym = rs_lf_step(ix, idx, &nxt);
       idx = nxt;
@@ -458,7 +470,7 @@ __global__ void __launch_bounds__(RS_THREADS, RS_K2_BLOCKS_BUILD)
     uint64_t idx = i;
     uint32_t s = 0;
     while (true) {
-      if (s % every == 0) loc[rs_sample_slot(mark, rank, idx)] = (i << 24) | s;
+      if (s % every == 0 && idx < ix.n) loc[rs_sample_slot(mark, rank, idx)] = (i << 24) | s;
       uint64_t nxt;
       const uint32_t sym = rs_lf_step(ix, idx, &nxt);
       idx = nxt;
@@ -472,7 +484,8 @@ __global__ void __launch_bounds__(RS_THREADS, RS_K2_BLOCKS_BUILD)
     k_locate_sampled(const __grid_constant__ rs_index_dev ix, const uint64_t* __restrict__ rows, uint64_t n,
                      uint32_t max_steps, uint64_t* __restrict__ lexrank, uint32_t* __restrict__ steps,
                      const uint64_t* __restrict__ sai, uint64_t* __restrict__ read_index,
-                     unsigned long long* __restrict__ stats) {
+                     unsigned long long* __restrict__ stats, const uint64_t* __restrict__ n_dev) {
+  if (n_dev && *n_dev < n) n = *n_dev; /* item count left on the device by an earlier kernel (rs_pop.cu) */
   const uint64_t stride = (uint64_t)gridDim.x * RS_THREADS;
   unsigned long long lf_steps = 0;
   for (uint64_t i = (uint64_t)blockIdx.x * RS_THREADS + threadIdx.x; i < n; i += stride) {
@@ -523,7 +536,8 @@ __global__ void __launch_bounds__(RS_THREADS, RS_K2_BLOCKS)
     k_extract_prefix(const __grid_constant__ rs_index_dev ix, const uint64_t* __restrict__ rows, uint64_t n,
                      uint32_t max_steps, uint64_t* __restrict__ lexrank, uint32_t* __restrict__ steps,
                      const uint64_t* __restrict__ sai, uint64_t* __restrict__ read_index, uint8_t* __restrict__ bases,
-                     unsigned long long* __restrict__ stats) {
+                     unsigned long long* __restrict__ stats, const uint64_t* __restrict__ n_dev) {
+  if (n_dev && *n_dev < n) n = *n_dev;
   const uint64_t stride = (uint64_t)gridDim.x * RS_THREADS;
   unsigned long long lf_steps = 0;
   uint64_t next_i = (uint64_t)blockIdx.x * RS_THREADS + threadIdx.x;
@@ -699,22 +713,48 @@ cudaError_t rs_launch_find_interval(const rs_index_dev& ix, const uint8_t* text,
   const bool packed_already = (mode == 3); /* mode 3 = mode 2 over keys an earlier call left in lower[] */
   if (packed_already) mode = 2;
   if (mode == 2 && (!peers_in || offs || k > RS_PACK_MAX_K)) return cudaErrorInvalidValue;
+  if (mode == 4) return cudaErrorInvalidValue; /* rs_launch_find_interval_packed */
   const bool ftab = ix.ftab && ix.ftab_k > 1;
   if (!offs && k >= 1 && k <= RS_PACK_MAX_K) {
     if (!packed_already)
       k_pack_kmers<<<(unsigned)((Q + RS_THREADS - 1) / RS_THREADS), RS_THREADS, 0, st>>>(text, k, Q, mode >= 1 && strand == 1,
                                                                                      lower);
-    if (ftab) RS_LAUNCH((k_find_interval<true, true>), Q, st, ix, text, offs, k, Q, lower, upper, mode, strand, stats, peers);
-    else RS_LAUNCH((k_find_interval<false, true>), Q, st, ix, text, offs, k, Q, lower, upper, mode, strand, stats, peers);
+    if (ftab) RS_LAUNCH((k_find_interval<true, true>), Q, st, ix, text, offs, k, Q, lower, lower, upper, mode, strand, stats, peers);
+    else RS_LAUNCH((k_find_interval<false, true>), Q, st, ix, text, offs, k, Q, lower, lower, upper, mode, strand, stats, peers);
   } else {
-    if (ftab) RS_LAUNCH((k_find_interval<true, false>), Q, st, ix, text, offs, k, Q, lower, upper, mode, strand, stats, peers);
-    else RS_LAUNCH((k_find_interval<false, false>), Q, st, ix, text, offs, k, Q, lower, upper, mode, strand, stats, peers);
+    if (ftab) RS_LAUNCH((k_find_interval<true, false>), Q, st, ix, text, offs, k, Q, lower, lower, upper, mode, strand, stats, peers);
+    else RS_LAUNCH((k_find_interval<false, false>), Q, st, ix, text, offs, k, Q, lower, lower, upper, mode, strand, stats, peers);
   }
   if (mode == 0) {
     uint64_t blocks = (Q + 4 * RS_THREADS - 1) / (4 * RS_THREADS);
     if (blocks > 148 * 8) blocks = 148 * 8;
     k_search_flagged<<<(unsigned)blocks, RS_THREADS, 0, st>>>(ix, text, offs, k, Q, lower, upper, stats);
   }
+  return cudaGetLastError();
+}
+
+cudaError_t rs_launch_pack_kmers(const uint8_t* text, uint32_t k, uint64_t Q, int rc, uint64_t* packed, cudaStream_t st) {
+  if (!Q) return cudaSuccess;
+  if (k < 1 || k > RS_PACK_MAX_K) return cudaErrorInvalidValue;
+  k_pack_kmers<<<(unsigned)((Q + RS_THREADS - 1) / RS_THREADS), RS_THREADS, 0, st>>>(text, k, Q, rc, packed);
+  return cudaGetLastError();
+}
+
+/* K1 over packed keys kept apart from the outputs (one batch searched in many shards: rs_pop.cu).
+ * mode 4: first[q] = lower bound, rows[q] = rows of the interval (0 for a key flagged as holding a byte outside
+ * ACGT: count_reads, service.cpp:299-301).  mode 2: counts added into the owners' buffers (peers). */
+cudaError_t rs_launch_find_interval_packed(const rs_index_dev& ix, const uint64_t* pkeys, uint32_t k, uint64_t Q,
+                                           uint64_t* first, uint32_t* rows, int mode, unsigned long long* stats,
+                                           cudaStream_t st, const rs_peers* peers_in) {
+  if (!Q) return cudaSuccess;
+  if (k < 1 || k > RS_PACK_MAX_K || (mode != 4 && mode != 2) || (mode == 2 && !peers_in)) return cudaErrorInvalidValue;
+  rs_peers peers;
+  memset(&peers, 0, sizeof(peers));
+  if (peers_in) peers = *peers_in;
+  const bool ftab = ix.ftab && ix.ftab_k > 1;
+  uint64_t* up = reinterpret_cast<uint64_t*>(rows);
+  if (ftab) RS_LAUNCH((k_find_interval<true, true>), Q, st, ix, nullptr, nullptr, k, Q, pkeys, first, up, mode, 0, stats, peers);
+  else RS_LAUNCH((k_find_interval<false, true>), Q, st, ix, nullptr, nullptr, k, Q, pkeys, first, up, mode, 0, stats, peers);
   return cudaGetLastError();
 }
 
@@ -744,9 +784,14 @@ cudaError_t rs_build_ftab(const rs_index_dev& ix_in, uint32_t t, uint64_t* table
   uint8_t* kmers = nullptr;
   uint64_t *lo = nullptr, *up = nullptr;
   cudaError_t e;
-  if ((e = cudaMallocAsync((void**)&kmers, n * t, st)) != cudaSuccess) return e;
-  if ((e = cudaMallocAsync((void**)&lo, n * 8, st)) != cudaSuccess) return e;
-  if ((e = cudaMallocAsync((void**)&up, n * 8, st)) != cudaSuccess) return e;
+  e = cudaMallocAsync((void**)&kmers, n * t, st);
+  if (e == cudaSuccess) e = cudaMallocAsync((void**)&lo, n * 8, st);
+  if (e == cudaSuccess) e = cudaMallocAsync((void**)&up, n * 8, st);
+  if (e != cudaSuccess) {
+    if (kmers) cudaFreeAsync(kmers, st);
+    if (lo) cudaFreeAsync(lo, st);
+    return e;
+  }
   k_all_kmers<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(t, n, kmers);
   e = rs_launch_find_interval(ix, kmers, nullptr, t, n, lo, up, 0, 0, nullptr, st, nullptr);
   if (e == cudaSuccess) {
@@ -759,21 +804,39 @@ cudaError_t rs_build_ftab(const rs_index_dev& ix_in, uint32_t t, uint64_t* table
   return e;
 }
 
+/* n_dev (nullable): device word holding the number of rows (<= n, which then only bounds the grid) */
+cudaError_t rs_launch_extract_prefix_n(const rs_index_dev& ix, const uint64_t* rows, const uint64_t* n_dev, uint64_t n,
+                                       uint32_t max_steps, const uint64_t* sai, uint64_t* read_index,
+                                       unsigned long long* stats, cudaStream_t st) {
+  if (!n) return cudaSuccess;
+  if (ix.loc && ix.loc_every > 1) {
+    RS_LAUNCH(k_locate_sampled, n, st, ix, rows, n, max_steps, nullptr, nullptr, sai, read_index, stats, n_dev);
+  } else if (ix.loc) {
+    uint64_t blocks = (n + RS_THREADS - 1) / RS_THREADS;
+    if (blocks > 148 * 8) blocks = 148 * 8;
+    k_locate_lookup<<<(unsigned)blocks, RS_THREADS, 0, st>>>(ix, rows, n, max_steps, nullptr, nullptr, sai, read_index, stats, n_dev);
+  } else {
+    RS_LAUNCH(k_extract_prefix, n, st, ix, rows, n, max_steps, nullptr, nullptr, sai, read_index, nullptr, stats, n_dev);
+  }
+  return cudaGetLastError();
+}
+
 cudaError_t rs_launch_extract_prefix(const rs_index_dev& ix, const uint64_t* rows, uint64_t n, uint32_t max_steps,
                                      uint64_t* lexrank, uint32_t* steps, const uint64_t* sai, uint64_t* read_index,
                                      uint8_t* bases, unsigned long long* stats, cudaStream_t st) {
   if (!n) return cudaSuccess;
+  const uint64_t* none = nullptr;
   if (ix.loc && ix.loc_every > 1 && !bases) {
-    RS_LAUNCH(k_locate_sampled, n, st, ix, rows, n, max_steps, lexrank, steps, sai, read_index, stats);
+    RS_LAUNCH(k_locate_sampled, n, st, ix, rows, n, max_steps, lexrank, steps, sai, read_index, stats, none);
     return cudaGetLastError();
   }
   if (ix.loc && !bases) {
     uint64_t blocks = (n + RS_THREADS - 1) / RS_THREADS;
     if (blocks > 148 * 8) blocks = 148 * 8;
-    k_locate_lookup<<<(unsigned)blocks, RS_THREADS, 0, st>>>(ix, rows, n, max_steps, lexrank, steps, sai, read_index, stats);
+    k_locate_lookup<<<(unsigned)blocks, RS_THREADS, 0, st>>>(ix, rows, n, max_steps, lexrank, steps, sai, read_index, stats, none);
     return cudaGetLastError();
   }
-  RS_LAUNCH(k_extract_prefix, n, st, ix, rows, n, max_steps, lexrank, steps, sai, read_index, bases, stats);
+  RS_LAUNCH(k_extract_prefix, n, st, ix, rows, n, max_steps, lexrank, steps, sai, read_index, bases, stats, none);
   return cudaGetLastError();
 }
 

@@ -28,6 +28,11 @@ typedef struct rs_peers {
 cudaError_t rs_launch_find_interval(const rs_index_dev& ix, const uint8_t* text, const uint64_t* offs, uint32_t k,
                                     uint64_t Q, uint64_t* lower, uint64_t* upper, int mode, int strand,
                                     unsigned long long* stats, cudaStream_t st, const rs_peers* peers = nullptr);
+cudaError_t rs_launch_pack_kmers(const uint8_t* text, uint32_t k, uint64_t Q, int rc, uint64_t* packed, cudaStream_t st);
+/* K1 over packed keys kept apart from its outputs (mode 4: first row + row count per key; mode 2 as above) */
+cudaError_t rs_launch_find_interval_packed(const rs_index_dev& ix, const uint64_t* pkeys, uint32_t k, uint64_t Q,
+                                           uint64_t* first, uint32_t* rows, int mode, unsigned long long* stats,
+                                           cudaStream_t st, const rs_peers* peers = nullptr);
 /* cross-GPU barrier over peer-mapped flag words: every rank writes `epoch` into its slot of every peer's
  * flag array, then waits until all slots of its own array reached it (or ~timeout_ms passed: *err = 1) */
 cudaError_t rs_launch_peer_barrier(uint64_t* const* peer_flags, uint32_t world, uint32_t rank, uint64_t epoch,
@@ -36,6 +41,9 @@ cudaError_t rs_build_ftab(const rs_index_dev& ix, uint32_t t, uint64_t* table, c
 cudaError_t rs_launch_extract_prefix(const rs_index_dev& ix, const uint64_t* rows, uint64_t n, uint32_t max_steps,
                                      uint64_t* lexrank, uint32_t* steps, const uint64_t* sai, uint64_t* read_index,
                                      uint8_t* bases, unsigned long long* stats, cudaStream_t st);
+cudaError_t rs_launch_extract_prefix_n(const rs_index_dev& ix, const uint64_t* rows, const uint64_t* n_dev, uint64_t n,
+                                       uint32_t max_steps, const uint64_t* sai, uint64_t* read_index,
+                                       unsigned long long* stats, cudaStream_t st);
 
 /* fills loc[n] and fin[num_strings] (rs_layout.h: locate table); walks are cut at max_len symbols */
 cudaError_t rs_build_locate_table(const rs_index_dev& ix, uint32_t max_len, uint64_t* loc, uint64_t* fin, cudaStream_t st);

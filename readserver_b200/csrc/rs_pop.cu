@@ -1,0 +1,696 @@
+/* Population queries over a SET of BWT shards resident on one GPU: count + locate + sample sets in one
+ * device-side pipeline (include/readserver_b200.h, rs_shardset_* / rs_pop_*).
+ *
+ * The reference runs one worker process per shard; the front end broadcasts every query to every worker
+ * (src/service/server.cpp:124,957) and, per query, sums the workers' counts and concatenates their read lists
+ * (server.cpp:184-197, 404-410); each worker answers with findInterval (src/bwt/query.cpp:24-41), one walk per
+ * hit row (extractPrefix / extractPostfix, query.cpp:43-85; find_reads, service.cpp:714-751) and one RocksDB Get +
+ * value decode per read (service.cpp:816-845).  Here the shards of a box live in the HBM of its GPUs and one call
+ * answers a whole batch:
+ *
+ *   k_pack_kmers          the batch becomes one u64 per k-mer, once
+ *   per chunk of queries (the chunk's per-shard intervals stay in L2-sized scratch):
+ *     K1 per shard        first row + row count of every query in that shard (mode 4; the shard's blocks, directory
+ *                         and suffix table -- tens of MB -- stay L2-resident while the chunk streams through)
+ *     k_pop_totals        population count = sum over shards; hits per query (rows capped at max_hits per shard)
+ *     CUB scan            hit offsets (query-major: a query's hits are contiguous, shard after shard, row order)
+ *     k_pop_gather        read index of every hit row and the union of the reads' sample sets:
+ *                           read-index table (4 B per BWT row): an interval's rows are contiguous, so the read
+ *                           indices of a query's hits are read with coalesced loads -- no walk at all;
+ *                           per-read sample-set bitmaps (<= 128 samples): one 16-byte load per hit, OR-reduced
+ *                           across the warp
+ *     or, without the table (shards too large for 4 B per row):
+ *     k_pop_expand + K2   per shard: rows -> LF walk (plain or to the next sampled row) -> scatter to the query's slot
+ *
+ * Hits are reported as  shard_id << 40 | read index  (read index = position in the shard's builder input order,
+ * what the .sai gives for the walk's terminal row).
+ */
+#include "rs_internal.h"
+
+#include <algorithm>
+
+#include "rs_ops.h"
+#include "rs_pop.h"
+
+#define RS_FULL 0xFFFFFFFFu
+
+/* ------------------------------------------------------------------------------------------------
+ * read-index table: rid[row] = read index of the read whose suffix sits at `row` (0xFFFFFFFF: the
+ * walk from that row does not end within max_len steps -- only possible inside the reference's tail
+ * region -- or the row is not on any read's walk)
+ * ---------------------------------------------------------------------------------------------- */
+#define RS_RID_NONE 0xFFFFFFFFu
+
+/* pass 1: one walker per read from the row of its terminator (row i belongs to read i in builder input order);
+ * every row it passes is stamped with i; term[i] = where the walk ended (lexicographic rank of the read) */
+__global__ void __launch_bounds__(RS_THREADS, 4)
+    k_rid_walk(const __grid_constant__ rs_index_dev ix, uint32_t max_len, uint32_t* __restrict__ rid,
+               uint64_t* __restrict__ term) {
+  const uint64_t stride = (uint64_t)gridDim.x * RS_THREADS;
+  uint64_t next_i = (uint64_t)blockIdx.x * RS_THREADS + threadIdx.x;
+  uint64_t i = 0, idx = 0;
+  uint32_t s = 0;
+  bool active = false;
+  while (true) {
+    if (!active && next_i < ix.num_strings) {
+      i = next_i;
+      next_i += stride;
+      idx = i;
+      s = 0;
+      active = true;
+    }
+    if (__all_sync(RS_FULL, !active)) break;
+    if (active) {
+      if (idx < ix.n) rid[idx] = (uint32_t)i;
+      uint64_t nxt;
+      const uint32_t sym = rs_lf_step(ix, idx, &nxt);
+      idx = nxt;
+      if (sym == 0) {
+        term[i] = idx;
+        active = false;
+      } else if (++s > max_len) {
+        term[i] = ~0ull;
+        active = false;
+      }
+    }
+  }
+}
+
+/* pass 2: stamp -> read index through the walk's terminal row and the .sai */
+__global__ void k_rid_resolve(uint32_t* __restrict__ rid, uint64_t n, const uint64_t* __restrict__ term,
+                              const uint64_t* __restrict__ sai, uint64_t num_strings) {
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; r < n; r += stride) {
+    const uint32_t v = rid[r];
+    if (v == RS_RID_NONE) continue;
+    const uint64_t t = term[v];
+    uint32_t out = RS_RID_NONE;
+    if (t < num_strings) {
+      const uint64_t ri = sai[t];
+      if (ri < RS_RID_NONE) out = (uint32_t)ri;
+    }
+    rid[r] = out;
+  }
+}
+
+/* per-read sample-set bitmaps (<= 128 samples): bit s of read r's 16 bytes = sample s carries the read */
+__global__ void k_read_sets(const uint64_t* __restrict__ samp_off, const uint8_t* __restrict__ samp_codes, uint32_t sos,
+                            uint64_t num_strings, uint4* __restrict__ sets) {
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; r < num_strings; r += stride) {
+    uint32_t w[4] = {0, 0, 0, 0};
+    for (uint64_t t = samp_off[r]; t < samp_off[r + 1]; ++t) {
+      uint32_t v = 0;
+      for (uint32_t i = 0; i < sos; ++i) v = v * 223u + (uint32_t)(samp_codes[t * sos + i] - 33u);
+      const uint32_t s = v - 1u; /* codes are 1-based (create_samples_hash.cpp:41-50) */
+      if (s < 128u) w[s >> 5] |= 1u << (s & 31);
+    }
+    sets[r] = make_uint4(w[0], w[1], w[2], w[3]);
+  }
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * pipeline kernels
+ * ---------------------------------------------------------------------------------------------- */
+/* per query of the chunk: population count and number of hits to report */
+__global__ void k_pop_totals(const uint32_t* __restrict__ cnt, uint32_t S, uint64_t C, uint64_t nq, uint64_t max_hits,
+                             uint64_t* __restrict__ counts, uint64_t* __restrict__ nhits, uint32_t* __restrict__ seg) {
+  const uint64_t q = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= nq) return;
+  uint64_t tot = 0, h = 0;
+  for (uint32_t s = 0; s < S; ++s) {
+    const uint64_t c = cnt[(uint64_t)s * C + q];
+    if (seg) seg[(uint64_t)s * C + q] = (uint32_t)h; /* where shard s's hits start inside the query's slot */
+    tot += c;
+    h += c < max_hits ? c : max_hits;
+  }
+  counts[q] = tot;
+  nhits[q] = h;
+}
+
+/* hit_offsets[q] = base + local offset; the running base advances by the chunk's hits */
+__global__ void k_pop_add_base(const uint64_t* __restrict__ local, uint64_t nq, const uint64_t* __restrict__ base,
+                               uint64_t* __restrict__ hit_offsets) {
+  const uint64_t q = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (q <= nq) hit_offsets[q] = *base + local[q]; /* entry nq = the next chunk's first (rewritten by it, same value) */
+}
+__global__ void k_pop_advance(const uint64_t* __restrict__ local, uint64_t nq, uint64_t* __restrict__ base,
+                              uint64_t* __restrict__ hit_offsets_end, uint64_t* __restrict__ total) {
+  *base += local[nq];
+  if (hit_offsets_end) *hit_offsets_end = *base;
+  if (total) *total = *base;
+}
+
+/* extractPrefix from one row of shard `v` (rows the read-index table does not cover): as K2 walks it */
+__device__ __noinline__ uint64_t rs_pop_walk_one(const rs_index_dev* __restrict__ views, uint32_t s,
+                                                 const uint64_t* const* __restrict__ sais, uint64_t row,
+                                                 uint32_t max_steps) {
+  const rs_index_dev ix = views[s];
+  uint64_t idx = row;
+  for (uint32_t st = 0; st <= max_steps; ++st) {
+    uint64_t nxt;
+    const uint32_t sym = rs_lf_step(ix, idx, &nxt);
+    idx = nxt;
+    if (sym == 0) return idx < ix.num_strings ? sais[s][idx] : ~0ull;
+  }
+  return ~0ull;
+}
+
+/* One warp per query: its hits shard after shard, rows in order, straight from the read-index tables; the union of
+ * the hit reads' sample sets when `carriers` is given (W = 4 words of 32 samples). */
+__global__ void __launch_bounds__(256)
+    k_pop_gather(const __grid_constant__ rs_pop_tables T, const uint64_t* __restrict__ lo, const uint32_t* __restrict__ cnt,
+                 uint64_t C, uint64_t nq, uint64_t max_hits, const uint64_t* __restrict__ hit_offsets, uint64_t capacity,
+                 uint64_t* __restrict__ hits, uint32_t* __restrict__ carriers) {
+  const uint32_t lane = threadIdx.x & 31;
+  const uint64_t warps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
+  for (uint64_t q = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; q < nq; q += warps) {
+    uint64_t off = hit_offsets[q];
+    uint32_t b0 = 0, b1 = 0, b2 = 0, b3 = 0;
+    for (uint32_t s = 0; s < T.nshards; ++s) {
+      uint64_t c = cnt[(uint64_t)s * C + q];
+      if (c == 0) continue;
+      if (c > max_hits) c = max_hits;
+      const uint64_t first = lo[(uint64_t)s * C + q];
+      const uint32_t* __restrict__ rid = T.rid[s];
+      const uint4* __restrict__ sets = T.sets[s];
+      const uint64_t tag = T.tag[s];
+      for (uint64_t j = lane; j < c; j += 32) {
+        uint64_t r = rid[first + j];
+        if (r == RS_RID_NONE) r = rs_pop_walk_one(T.views, s, T.sai, first + j, T.max_steps);
+        if (off + j < capacity) hits[off + j] = r == ~0ull ? ~0ull : (tag | r);
+        if (carriers && sets && r != ~0ull) {
+          const uint4 v = __ldg(sets + r);
+          b0 |= v.x;
+          b1 |= v.y;
+          b2 |= v.z;
+          b3 |= v.w;
+        }
+      }
+      off += c;
+    }
+    if (carriers) {
+      b0 = __reduce_or_sync(RS_FULL, b0);
+      b1 = __reduce_or_sync(RS_FULL, b1);
+      b2 = __reduce_or_sync(RS_FULL, b2);
+      b3 = __reduce_or_sync(RS_FULL, b3);
+      if (lane == 0) reinterpret_cast<uint4*>(carriers)[q] = make_uint4(b0, b1, b2, b3);
+    }
+  }
+}
+
+/* ---- without the read-index table: per shard, rows -> walk -> scatter ---- */
+__global__ void k_pop_shard_counts(const uint32_t* __restrict__ cnt_s, uint64_t nq, uint64_t max_hits,
+                                   uint64_t* __restrict__ out) {
+  const uint64_t q = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= nq) return;
+  const uint64_t c = cnt_s[q];
+  out[q] = c < max_hits ? c : max_hits;
+}
+
+/* rows[loff[q] + j] = first[q] + j,  dst[..] = hit_offsets[q] + seg[q] + j; one warp per query */
+__global__ void k_pop_expand(const uint64_t* __restrict__ first, const uint64_t* __restrict__ loff, uint64_t nq,
+                             const uint64_t* __restrict__ hit_offsets, const uint32_t* __restrict__ seg,
+                             uint64_t* __restrict__ rows, uint64_t* __restrict__ dst) {
+  const uint32_t lane = threadIdx.x & 31;
+  const uint64_t warps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
+  for (uint64_t q = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; q < nq; q += warps) {
+    const uint64_t b = loff[q], e = loff[q + 1];
+    if (b == e) continue;
+    const uint64_t f = first[q], d0 = hit_offsets[q] + seg[q];
+    for (uint64_t j = b + lane; j < e; j += 32) {
+      rows[j] = f + (j - b);
+      dst[j] = d0 + (j - b);
+    }
+  }
+}
+
+/* hits[dst[i]] = tag | read_index[i]; n read from the device (the shard's hit count of this chunk) */
+__global__ void k_pop_scatter(const uint64_t* __restrict__ read_index, const uint64_t* __restrict__ dst,
+                              const uint64_t* __restrict__ n_dev, uint64_t tag, uint64_t capacity,
+                              uint64_t* __restrict__ hits) {
+  const uint64_t n = *n_dev;
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    const uint64_t r = read_index[i], d = dst[i];
+    if (d < capacity) hits[d] = r == ~0ull ? ~0ull : (tag | r);
+  }
+}
+
+/* union of the hit reads' sample sets from the hit list (any number of samples: a bitmap per warp in shared memory;
+ * sample codes decoded as create_samples_hash.cpp:31-51 wrote them) */
+__global__ void __launch_bounds__(256)
+    k_pop_carriers(const __grid_constant__ rs_pop_tables T, const uint64_t* __restrict__ hit_offsets, uint64_t nq,
+                   const uint64_t* __restrict__ hits, uint64_t capacity, uint32_t words, uint32_t* __restrict__ carriers) {
+  extern __shared__ uint32_t smem[];
+  const uint32_t lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
+  uint32_t* bm = smem + wib * words;
+  const uint64_t warps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
+  for (uint64_t q = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; q < nq; q += warps) {
+    for (uint32_t w = lane; w < words; w += 32) bm[w] = 0;
+    __syncwarp();
+    const uint64_t b = hit_offsets[q], e = hit_offsets[q + 1] < capacity ? hit_offsets[q + 1] : capacity;
+    for (uint64_t j = b + lane; j < e; j += 32) {
+      const uint64_t h = hits[j];
+      if (h == ~0ull) continue;
+      const uint32_t s = T.slot_of_shard[h >> 40];
+      const uint64_t r = h & ((1ull << 40) - 1);
+      const uint64_t* __restrict__ so = T.samp_off[s];
+      const uint8_t* __restrict__ sc = T.samp_codes[s];
+      if (!so) continue;
+      for (uint64_t t = so[r]; t < so[r + 1]; ++t) {
+        uint32_t v = 0;
+        for (uint32_t i = 0; i < T.sos; ++i) v = v * 223u + (uint32_t)(sc[t * T.sos + i] - 33u);
+        const uint32_t smp = v - 1u;
+        if (smp < words * 32u) atomicOr(&bm[smp >> 5], 1u << (smp & 31));
+      }
+    }
+    __syncwarp();
+    for (uint32_t w = lane; w < words; w += 32) carriers[q * words + w] = bm[w];
+    __syncwarp();
+  }
+}
+
+/* ------------------------------------------------------------------------------------------------
+ * host side
+ * ---------------------------------------------------------------------------------------------- */
+struct rs_shardset {
+  int device = 0;
+  bool sealed = false;
+  std::vector<rs_index*> shards;
+  std::vector<uint32_t> shard_ids;
+  std::vector<uint32_t*> d_rid;   /* owned: read-index tables */
+  std::vector<uint4*> d_sets;     /* owned: per-read sample-set bitmaps */
+  uint32_t max_read_len = 0, locate_every = 0;
+  uint32_t num_samples = 0, words = 0; /* carrier-set width */
+  int sos = 0;
+  bool have_samples = false, have_sets = false;
+  uint64_t table_bytes = 0;
+  rs_pop_tables tab;              /* device pointer tables (point into d_tabmem) */
+  void* d_tabmem = nullptr;
+  /* per-call scratch, grown on demand; calls on one set are serialised */
+  std::mutex mu;
+  cudaStream_t stream = nullptr;
+  Scratch s_packed, s_lo, s_cnt, s_seg, s_nh, s_loc, s_scan, s_base, s_rows, s_dst, s_ri, s_in, s_lcnt;
+  uint64_t* d_stats = nullptr; /* executed updateInterval steps / LF steps of the set's calls (bench.py) */
+  uint64_t chunk = 1u << 20;
+};
+
+int rs_shardset_create(int device, rs_shardset** out) {
+  if (!out) return fail(RS_STATUS_ARG, "out is null");
+  *out = nullptr;
+  int ndev = 0;
+  if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev)
+    return fail(RS_STATUS_CUDA, "CUDA device %d not available (%d devices): this engine has no CPU path", device, ndev);
+  CU(cudaSetDevice(device));
+  rs_shardset* s = new rs_shardset;
+  s->device = device;
+  memset(&s->tab, 0, sizeof(s->tab));
+  const char* e = getenv("RS_B200_POP_CHUNK");
+  if (e && atoll(e) >= 1024) s->chunk = (uint64_t)atoll(e);
+  cudaError_t ce = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking);
+  if (ce != cudaSuccess) {
+    delete s;
+    return fail(RS_STATUS_CUDA, "cudaStreamCreate: %s", cudaGetErrorString(ce));
+  }
+  *out = s;
+  return RS_STATUS_OK;
+}
+
+int rs_shardset_add(rs_shardset* set, rs_index* ix, uint32_t shard_id) {
+  if (!set || !ix) return fail(RS_STATUS_ARG, "null argument");
+  if (set->sealed) return fail(RS_STATUS_ARG, "shard set is sealed");
+  if (ix->device != set->device) return fail(RS_STATUS_ARG, "shard lives on another device");
+  if (shard_id >= RS_POP_MAX_SHARD_ID) return fail(RS_STATUS_ARG, "shard id must be below %u", RS_POP_MAX_SHARD_ID);
+  if (set->shards.size() >= RS_POP_MAX_SHARDS) return fail(RS_STATUS_TOO_LARGE, "at most %d shards per set", RS_POP_MAX_SHARDS);
+  if (!ix->d_sai) return fail(RS_STATUS_NO_TABLE, "shard %u has no .sai table attached", shard_id);
+  if (ix->dev.num_strings >> 32) return fail(RS_STATUS_TOO_LARGE, "shard %u holds more than 2^32 reads", shard_id);
+  for (uint32_t id : set->shard_ids)
+    if (id == shard_id) return fail(RS_STATUS_ARG, "shard id %u added twice", shard_id);
+  set->shards.push_back(ix);
+  set->shard_ids.push_back(shard_id);
+  return RS_STATUS_OK;
+}
+
+static void free_tables(rs_shardset* set) {
+  for (auto p : set->d_rid)
+    if (p) cudaFree(p);
+  for (auto p : set->d_sets)
+    if (p) cudaFree(p);
+  set->d_rid.clear();
+  set->d_sets.clear();
+  if (set->d_tabmem) cudaFree(set->d_tabmem);
+  set->d_tabmem = nullptr;
+  set->table_bytes = 0;
+}
+
+void rs_shardset_destroy(rs_shardset* set) {
+  if (!set) return;
+  cudaSetDevice(set->device);
+  if (set->stream) cudaStreamSynchronize(set->stream);
+  free_tables(set);
+  Scratch* all[] = {&set->s_packed, &set->s_lo, &set->s_cnt, &set->s_seg, &set->s_nh, &set->s_loc, &set->s_scan,
+                    &set->s_base, &set->s_rows, &set->s_dst, &set->s_ri, &set->s_in, &set->s_lcnt};
+  for (Scratch* s : all) s->release();
+  if (set->d_stats) cudaFree(set->d_stats);
+  if (set->stream) cudaStreamDestroy(set->stream);
+  delete set;
+}
+
+static int grid_for(uint64_t items, int per_block, int cap_blocks) {
+  uint64_t b = (items + per_block - 1) / per_block;
+  if (b > (uint64_t)cap_blocks) b = cap_blocks;
+  return b ? (int)b : 1;
+}
+
+int rs_shardset_seal(rs_shardset* set, uint32_t max_read_len, uint32_t locate_every) {
+  if (!set) return fail(RS_STATUS_ARG, "null argument");
+  if (set->shards.empty()) return fail(RS_STATUS_ARG, "shard set is empty");
+  if (max_read_len < 1 || max_read_len >= (1u << 24) - 1) return fail(RS_STATUS_ARG, "max_read_len must be in [1, 2^24 - 2]");
+  std::lock_guard<std::mutex> lk(set->mu);
+  CU(cudaSetDevice(set->device));
+  CU(cudaStreamSynchronize(set->stream));
+  free_tables(set);
+  set->sealed = false;
+  const size_t S = set->shards.size();
+  cudaStream_t st = set->stream;
+  /* sample tables: all shards or none, one code width */
+  set->have_samples = true;
+  set->sos = 0;
+  set->num_samples = 0;
+  for (rs_index* ix : set->shards) {
+    if (!ix->d_samp_off) set->have_samples = false;
+  }
+  if (set->have_samples) {
+    set->sos = set->shards[0]->size_of_sample;
+    for (rs_index* ix : set->shards) {
+      if (ix->size_of_sample != set->sos) return fail(RS_STATUS_ARG, "shards disagree on size_of_sample");
+      set->num_samples = std::max(set->num_samples, ix->num_samples);
+    }
+  }
+  set->words = set->have_samples ? std::max<uint32_t>(4u, ((set->num_samples + 31) / 32 + 3) / 4 * 4) : 0;
+  set->have_sets = set->have_samples && set->num_samples <= 128 && locate_every == 1;
+  if (set->words > 1536) return fail(RS_STATUS_TOO_LARGE, "carrier sets support at most 49152 samples (tables hold %u)", set->num_samples);
+  set->max_read_len = max_read_len;
+  set->locate_every = locate_every;
+
+  set->d_rid.assign(S, nullptr);
+  set->d_sets.assign(S, nullptr);
+  if (locate_every == 1) {
+    /* read-index tables, one shard at a time (the walkers of a shard keep its blocks in L2) */
+    for (size_t i = 0; i < S; ++i) {
+      rs_index* ix = set->shards[i];
+      rs_index_dev v = ix->dev;
+      v.loc = v.loc_fin = v.loc_mark = v.loc_rank = nullptr;
+      v.loc_every = 0;
+      const uint64_t n = v.n, ns = v.num_strings;
+      uint64_t* d_term = nullptr;
+      CU(cudaMalloc((void**)&set->d_rid[i], (n ? n : 1) * 4));
+      CU(cudaMallocAsync((void**)&d_term, (ns ? ns : 1) * 8, st));
+      CU(cudaMemsetAsync(set->d_rid[i], 0xFF, (n ? n : 1) * 4, st));
+      if (ns) {
+        int per_sm = 0, sms = 148;
+        cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_rid_walk, RS_THREADS, 0);
+        cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, set->device);
+        k_rid_walk<<<grid_for(ns, RS_THREADS, sms * std::max(per_sm, 1)), RS_THREADS, 0, st>>>(v, max_read_len, set->d_rid[i], d_term);
+        k_rid_resolve<<<grid_for(n, 256, 148 * 16), 256, 0, st>>>(set->d_rid[i], n, d_term, ix->d_sai, ns);
+      }
+      CU(cudaGetLastError());
+      CU(cudaFreeAsync(d_term, st));
+      set->table_bytes += n * 4;
+      if (set->have_sets) {
+        CU(cudaMalloc((void**)&set->d_sets[i], (ns ? ns : 1) * sizeof(uint4)));
+        if (ns) k_read_sets<<<grid_for(ns, 256, 148 * 16), 256, 0, st>>>(ix->d_samp_off, ix->d_samp_codes, (uint32_t)set->sos, ns, set->d_sets[i]);
+        CU(cudaGetLastError());
+        set->table_bytes += ns * sizeof(uint4);
+      }
+    }
+  } else if (locate_every > 1) {
+    for (rs_index* ix : set->shards) {
+      if (ix->dev.loc_every != locate_every) {
+        const int rc = rs_index_build_locate_samples(ix, max_read_len, locate_every);
+        if (rc != RS_STATUS_OK) return rc;
+      }
+    }
+  }
+
+  /* device pointer tables */
+  rs_pop_tables& T = set->tab;
+  memset(&T, 0, sizeof(T));
+  T.nshards = (uint32_t)S;
+  T.max_steps = max_read_len;
+  T.sos = (uint32_t)set->sos;
+  const size_t bytes = S * (sizeof(void*) * 5 + sizeof(uint64_t)) + RS_POP_MAX_SHARD_ID * sizeof(uint32_t) + S * sizeof(rs_index_dev) + 64;
+  CU(cudaMalloc(&set->d_tabmem, bytes));
+  std::vector<uint8_t> host(bytes, 0);
+  size_t o = 0;
+  auto put = [&](const void* src, size_t nbytes, size_t align) {
+    o = (o + align - 1) / align * align;
+    memcpy(host.data() + o, src, nbytes);
+    const size_t at = o;
+    o += nbytes;
+    return (uint8_t*)set->d_tabmem + at;
+  };
+  std::vector<const void*> p_rid(S), p_sets(S), p_sai(S), p_so(S), p_sc(S);
+  std::vector<uint64_t> tag(S);
+  std::vector<uint32_t> slot(RS_POP_MAX_SHARD_ID, 0);
+  std::vector<rs_index_dev> views(S);
+  for (size_t i = 0; i < S; ++i) {
+    rs_index* ix = set->shards[i];
+    p_rid[i] = set->d_rid[i];
+    p_sets[i] = set->d_sets[i];
+    p_sai[i] = ix->d_sai;
+    p_so[i] = set->have_samples ? ix->d_samp_off : nullptr;
+    p_sc[i] = set->have_samples ? ix->d_samp_codes : nullptr;
+    tag[i] = (uint64_t)set->shard_ids[i] << 40;
+    slot[set->shard_ids[i]] = (uint32_t)i;
+    views[i] = ix->dev;
+    views[i].loc = views[i].loc_fin = views[i].loc_mark = views[i].loc_rank = nullptr;
+    views[i].loc_every = 0;
+  }
+  T.rid = (const uint32_t* const*)put(p_rid.data(), S * sizeof(void*), 16);
+  T.sets = (const uint4* const*)put(p_sets.data(), S * sizeof(void*), 16);
+  T.sai = (const uint64_t* const*)put(p_sai.data(), S * sizeof(void*), 16);
+  T.samp_off = (const uint64_t* const*)put(p_so.data(), S * sizeof(void*), 16);
+  T.samp_codes = (const uint8_t* const*)put(p_sc.data(), S * sizeof(void*), 16);
+  T.tag = (const uint64_t*)put(tag.data(), S * sizeof(uint64_t), 16);
+  T.slot_of_shard = (const uint32_t*)put(slot.data(), slot.size() * sizeof(uint32_t), 16);
+  T.views = (const rs_index_dev*)put(views.data(), S * sizeof(rs_index_dev), 16);
+  CU(cudaMemcpyAsync(set->d_tabmem, host.data(), bytes, cudaMemcpyHostToDevice, st));
+  CU(cudaStreamSynchronize(st));
+  set->sealed = true;
+  return RS_STATUS_OK;
+}
+
+int rs_shardset_get_info(const rs_shardset* set, rs_shardset_info* info) {
+  if (!set || !info) return fail(RS_STATUS_ARG, "null argument");
+  memset(info, 0, sizeof(*info));
+  info->num_shards = (uint32_t)set->shards.size();
+  info->sealed = set->sealed ? 1 : 0;
+  info->locate_every = set->locate_every;
+  info->max_read_len = set->max_read_len;
+  info->num_samples = set->num_samples;
+  info->carrier_words = set->words;
+  info->table_bytes = set->table_bytes;
+  for (rs_index* ix : set->shards) {
+    info->index_bytes += ix->hbm_bytes;
+    info->bwlen += ix->dev.n;
+    info->num_strings += ix->dev.num_strings;
+    info->num_runs += ix->num_runs;
+  }
+  info->chunk_queries = set->chunk;
+  return RS_STATUS_OK;
+}
+
+int rs_shardset_enable_stats(rs_shardset* set, int on) {
+  if (!set) return fail(RS_STATUS_ARG, "null argument");
+  std::lock_guard<std::mutex> lk(set->mu);
+  CU(cudaSetDevice(set->device));
+  if (on && !set->d_stats) {
+    CU(cudaMalloc((void**)&set->d_stats, 16));
+    CU(cudaMemset(set->d_stats, 0, 16));
+  } else if (!on && set->d_stats) {
+    CU(cudaDeviceSynchronize());
+    cudaFree(set->d_stats);
+    set->d_stats = nullptr;
+  }
+  return RS_STATUS_OK;
+}
+
+int rs_shardset_read_stats(rs_shardset* set, uint64_t* interval_steps, uint64_t* walk_steps, int reset) {
+  if (!set) return fail(RS_STATUS_ARG, "null argument");
+  if (!set->d_stats) return fail(RS_STATUS_NO_TABLE, "statistics are not enabled");
+  CU(cudaSetDevice(set->device));
+  CU(cudaDeviceSynchronize());
+  uint64_t v[2] = {0, 0};
+  CU(cudaMemcpy(v, set->d_stats, 16, cudaMemcpyDeviceToHost));
+  if (interval_steps) *interval_steps = v[0];
+  if (walk_steps) *walk_steps = v[1];
+  if (reset) CU(cudaMemset(set->d_stats, 0, 16));
+  return RS_STATUS_OK;
+}
+
+/* the pipeline proper; everything on `st`, no host synchronisation */
+static int pop_run(rs_shardset* set, const void* d_kmers, int k, size_t Q, int packed, uint64_t max_hits, uint64_t* d_counts,
+                   uint64_t* d_hit_offsets, uint64_t* d_hits, uint64_t capacity, uint32_t* d_carriers, uint64_t* d_total,
+                   cudaStream_t st) {
+  const uint32_t S = (uint32_t)set->shards.size();
+  const uint64_t C = std::min<uint64_t>(set->chunk, Q);
+  const bool want_hits = d_hit_offsets != nullptr;
+  const bool table = set->locate_every == 1;
+  const uint64_t* keys = (const uint64_t*)d_kmers;
+  if (!packed) {
+    CU(set->s_packed.need(Q * 8));
+    CU(rs_launch_pack_kmers((const uint8_t*)d_kmers, (uint32_t)k, Q, 0, (uint64_t*)set->s_packed.p, st));
+    keys = (const uint64_t*)set->s_packed.p;
+  }
+  CU(set->s_lo.need((size_t)S * C * 8));
+  CU(set->s_cnt.need((size_t)S * C * 4));
+  CU(set->s_nh.need((C + 1) * 8));
+  CU(set->s_loc.need((C + 1) * 8));
+  CU(set->s_base.need(8));
+  size_t scan_bytes = 0;
+  CU(rs_scan_bytes(C, &scan_bytes));
+  CU(set->s_scan.need(scan_bytes ? scan_bytes : 8));
+  if (want_hits && !table) CU(set->s_seg.need((size_t)S * C * 4));
+  uint64_t* lo = (uint64_t*)set->s_lo.p;
+  uint32_t* cnt = (uint32_t*)set->s_cnt.p;
+  uint64_t* nh = (uint64_t*)set->s_nh.p;
+  uint64_t* loc = (uint64_t*)set->s_loc.p;
+  uint64_t* base = (uint64_t*)set->s_base.p;
+  uint32_t* seg = (want_hits && !table) ? (uint32_t*)set->s_seg.p : nullptr;
+  CU(cudaMemsetAsync(base, 0, 8, st));
+  for (uint64_t q0 = 0; q0 < Q; q0 += C) {
+    const uint64_t nq = std::min<uint64_t>(C, Q - q0);
+    for (uint32_t s = 0; s < S; ++s)
+      CU(rs_launch_find_interval_packed(set->shards[s]->dev, keys + q0, (uint32_t)k, nq, lo + (uint64_t)s * C,
+                                        cnt + (uint64_t)s * C, 4, (unsigned long long*)set->d_stats, st));
+    k_pop_totals<<<(unsigned)((nq + 255) / 256), 256, 0, st>>>(cnt, S, C, nq, max_hits, d_counts + q0, nh, seg);
+    CU(cudaGetLastError());
+    if (!want_hits) continue;
+    CU(rs_exclusive_scan(nh, loc, nq, set->s_scan.p, scan_bytes, st));
+    k_pop_add_base<<<(unsigned)((nq + 256) / 256), 256, 0, st>>>(loc, nq, base, d_hit_offsets + q0);
+    k_pop_advance<<<1, 1, 0, st>>>(loc, nq, base, q0 + nq == Q ? d_hit_offsets + Q : nullptr, q0 + nq == Q ? d_total : nullptr);
+    CU(cudaGetLastError());
+    if (table) {
+      k_pop_gather<<<grid_for(nq * 32, 256, 148 * 8), 256, 0, st>>>(set->tab, lo, cnt, C, nq, max_hits, d_hit_offsets + q0,
+                                                                 capacity, d_hits,
+                                                                 (d_carriers && set->have_sets) ? d_carriers + q0 * set->words : nullptr);
+      CU(cudaGetLastError());
+      if (d_carriers && !set->have_sets && set->have_samples) {
+        k_pop_carriers<<<grid_for(nq * 32, 256, 148 * 8), 256, 8 * set->words * 4, st>>>(set->tab, d_hit_offsets + q0, nq, d_hits, capacity,
+                                                                                      set->words, d_carriers + q0 * set->words);
+        CU(cudaGetLastError());
+      }
+    } else {
+      /* shards too large for the read-index table: per shard, rows -> walk (K2 / sampled) -> scatter */
+      CU(set->s_lcnt.need((C + 1) * 8));
+      uint64_t* lcnt = (uint64_t*)set->s_lcnt.p;
+      uint64_t* loff = nh; /* nh is free again after the scan above */
+      /* a chunk's hits in one shard are bounded by the caller's capacity as well */
+      const uint64_t bound = std::min<uint64_t>(capacity, nq * std::min<uint64_t>(max_hits, 0xFFFFFFFFull));
+      CU(set->s_rows.need((bound ? bound : 1) * 8));
+      CU(set->s_dst.need((bound ? bound : 1) * 8));
+      CU(set->s_ri.need((bound ? bound : 1) * 8));
+      for (uint32_t s = 0; s < S; ++s) {
+        rs_index* ix = set->shards[s];
+        k_pop_shard_counts<<<(unsigned)((nq + 255) / 256), 256, 0, st>>>(cnt + (uint64_t)s * C, nq, max_hits, lcnt);
+        CU(rs_exclusive_scan(lcnt, loff, nq, set->s_scan.p, scan_bytes, st));
+        k_pop_expand<<<grid_for(nq * 32, 256, 148 * 8), 256, 0, st>>>(lo + (uint64_t)s * C, loff, nq, d_hit_offsets + q0,
+                                                                   seg + (uint64_t)s * C, (uint64_t*)set->s_rows.p,
+                                                                   (uint64_t*)set->s_dst.p);
+        CU(cudaGetLastError());
+        CU(rs_launch_extract_prefix_n(ix->dev, (const uint64_t*)set->s_rows.p, loff + nq, bound, set->max_read_len, ix->d_sai,
+                                      (uint64_t*)set->s_ri.p, (unsigned long long*)set->d_stats, st));
+        k_pop_scatter<<<148 * 8, 256, 0, st>>>((const uint64_t*)set->s_ri.p, (const uint64_t*)set->s_dst.p, loff + nq,
+                                              (uint64_t)set->shard_ids[s] << 40, capacity, d_hits);
+        CU(cudaGetLastError());
+      }
+      if (d_carriers && set->have_samples) {
+        k_pop_carriers<<<grid_for(nq * 32, 256, 148 * 8), 256, 8 * set->words * 4, st>>>(set->tab, d_hit_offsets + q0, nq, d_hits, capacity,
+                                                                                      set->words, d_carriers + q0 * set->words);
+        CU(cudaGetLastError());
+      }
+    }
+  }
+  if (!want_hits && d_total) CU(cudaMemsetAsync(d_total, 0, 8, st));
+  return RS_STATUS_OK;
+}
+
+static int pop_check(rs_shardset* set, const void* kmers, int k, size_t Q, const void* counts, const void* hit_offsets,
+                     const void* hits, uint64_t capacity, const void* carriers) {
+  if (!set || (Q && (!kmers || !counts))) return fail(RS_STATUS_ARG, "null argument");
+  if (!set->sealed) return fail(RS_STATUS_ARG, "shard set is not sealed");
+  if (k < 1 || k > 31) return fail(RS_STATUS_ARG, "population queries are fixed-length k-mers of 1..31 characters");
+  if (hit_offsets && capacity && !hits) return fail(RS_STATUS_ARG, "capacity given but hits is null");
+  if (carriers && !hit_offsets) return fail(RS_STATUS_ARG, "carrier sets need the hit list (hit_offsets / hits)");
+  if (carriers && !set->have_samples) return fail(RS_STATUS_NO_TABLE, "carrier sets requested but a shard has no sample table");
+  return RS_STATUS_OK;
+}
+
+int rs_pop_query_dev(rs_shardset* set, const void* d_kmers, int k, size_t Q, int packed, uint64_t max_hits, void* d_counts,
+                     void* d_hit_offsets, void* d_hits, uint64_t capacity, void* d_carriers, void* d_total_hits,
+                     void* stream) {
+  const int rc = pop_check(set, d_kmers, k, Q, d_counts, d_hit_offsets, d_hits, capacity, d_carriers);
+  if (rc != RS_STATUS_OK) return rc;
+  std::lock_guard<std::mutex> lk(set->mu);
+  CU(cudaSetDevice(set->device));
+  if (!Q) {
+    if (d_hit_offsets) CU(cudaMemsetAsync(d_hit_offsets, 0, 8, (cudaStream_t)stream));
+    if (d_total_hits) CU(cudaMemsetAsync(d_total_hits, 0, 8, (cudaStream_t)stream));
+    return RS_STATUS_OK;
+  }
+  return pop_run(set, d_kmers, k, Q, packed, max_hits, (uint64_t*)d_counts, (uint64_t*)d_hit_offsets, (uint64_t*)d_hits,
+                 capacity, (uint32_t*)d_carriers, (uint64_t*)d_total_hits, (cudaStream_t)stream);
+}
+
+/* host buffers (pinned or not): copy in, run, copy out; RS_STATUS_CAPACITY when hits were dropped */
+int rs_pop_query(rs_shardset* set, const void* kmers, int k, size_t Q, int packed, uint64_t max_hits, uint64_t* counts,
+                 uint64_t* hit_offsets, uint64_t* hits, uint64_t capacity, uint32_t* carriers, uint64_t* total_hits) {
+  const int rc = pop_check(set, kmers, k, Q, counts, hit_offsets, hits, capacity, carriers);
+  if (rc != RS_STATUS_OK) return rc;
+  if (total_hits) *total_hits = 0;
+  if (!Q) {
+    if (hit_offsets) hit_offsets[0] = 0;
+    return RS_STATUS_OK;
+  }
+  std::lock_guard<std::mutex> lk(set->mu);
+  CU(cudaSetDevice(set->device));
+  cudaStream_t st = set->stream;
+  Tmp tmp(st);
+  const size_t in_bytes = packed ? Q * 8 : Q * (size_t)k;
+  CU(set->s_in.need(in_bytes));
+  uint64_t *d_counts, *d_off = nullptr, *d_hits = nullptr, *d_total;
+  uint32_t* d_carr = nullptr;
+  CU(tmp.get((void**)&d_counts, Q * 8));
+  CU(tmp.get((void**)&d_total, 8));
+  if (hit_offsets) {
+    CU(tmp.get((void**)&d_off, (Q + 1) * 8));
+    if (capacity) CU(tmp.get((void**)&d_hits, capacity * 8));
+    if (carriers) CU(tmp.get((void**)&d_carr, Q * (size_t)set->words * 4));
+  }
+  CU(cudaMemcpyAsync(set->s_in.p, kmers, in_bytes, cudaMemcpyHostToDevice, st));
+  const int prc = pop_run(set, set->s_in.p, k, Q, packed, max_hits, d_counts, d_off, d_hits, capacity, d_carr, d_total, st);
+  if (prc != RS_STATUS_OK) {
+    cudaStreamSynchronize(st);
+    return prc;
+  }
+  uint64_t total = 0;
+  CU(cudaMemcpyAsync(counts, d_counts, Q * 8, cudaMemcpyDeviceToHost, st));
+  CU(cudaMemcpyAsync(&total, d_total, 8, cudaMemcpyDeviceToHost, st));
+  if (hit_offsets) {
+    CU(cudaMemcpyAsync(hit_offsets, d_off, (Q + 1) * 8, cudaMemcpyDeviceToHost, st));
+    if (carriers) CU(cudaMemcpyAsync(carriers, d_carr, Q * (size_t)set->words * 4, cudaMemcpyDeviceToHost, st));
+  }
+  CU(cudaStreamSynchronize(st));
+  if (total_hits) *total_hits = total;
+  if (hit_offsets && hits) {
+    const uint64_t ncopy = total < capacity ? total : capacity;
+    if (ncopy) CU(cudaMemcpyAsync(hits, d_hits, ncopy * 8, cudaMemcpyDeviceToHost, st));
+    CU(cudaStreamSynchronize(st));
+  }
+  if (hit_offsets && total > capacity)
+    return fail(RS_STATUS_CAPACITY, "%llu hits do not fit the %llu provided", (unsigned long long)total,
+                (unsigned long long)capacity);
+  return RS_STATUS_OK;
+}

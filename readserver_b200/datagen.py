@@ -313,3 +313,192 @@ def config2(device="cpu", genome_len: int = 10_000_000, n_reads: int = 50_000_00
     built = build_bwt(reads, lens, keep_plain=keep_plain)
     queries = make_queries(h1, n_queries, k, seed=3)
     return Workload(f"config2:{n_reads}x{read_len}bp/{genome_len}bp", [h1, h2], reads, lens, built, queries)
+
+
+# ----------------------------------------------------------------------------------------------
+# population of diploid samples, reads partitioned into shards (BASELINE.json configs[2])
+# ----------------------------------------------------------------------------------------------
+PATTERN_BITS = 16   # sites a read window may span (population site density 1/300: a 100-bp window holds ~0.3)
+
+
+@dataclass
+class Population:
+    """A reference genome, a shared list of variant sites and, per haplotype, which sites carry the alternative
+    allele.  Sample i owns haplotypes 2i and 2i+1."""
+    genome: torch.Tensor      # uint8 [G], codes 1..4
+    site_pos: torch.Tensor    # int64 [M], ascending
+    site_alt: torch.Tensor    # uint8 [M], alternative base (differs from the genome's)
+    hap_alt: torch.Tensor     # bool [2 * n_samples, M]
+    site_cum: torch.Tensor    # int32 [G + 1]: sites at positions < p
+    n_samples: int
+
+    @property
+    def n_haplotypes(self) -> int:
+        return 2 * self.n_samples
+
+
+def make_population(genome_len: int, n_samples: int, seed: int = 4, site_rate: float = 1.0 / 300, snp_rate: float = 1e-3,
+                    device="cpu") -> Population:
+    """Random genome; a population site list (each position with probability site_rate); every haplotype carries the
+    alternative allele at a site with probability snp_rate / site_rate, i.e. ~snp_rate substitutions per base."""
+    g = _gen(seed, device)
+    genome = torch.randint(1, 5, (genome_len,), generator=g, device=device, dtype=torch.uint8)
+    is_site = torch.rand(genome_len, generator=g, device=device) < site_rate
+    site_pos = torch.nonzero(is_site).flatten()
+    m = site_pos.numel()
+    shift = torch.randint(1, 4, (m,), generator=g, device=device, dtype=torch.uint8)
+    site_alt = (genome[site_pos] - 1 + shift) % 4 + 1
+    hap_alt = torch.rand((2 * n_samples, m), generator=g, device=device) < (snp_rate / site_rate)
+    site_cum = torch.zeros(genome_len + 1, dtype=torch.int32, device=device)
+    site_cum[1:] = torch.cumsum(is_site.to(torch.int32), 0)
+    return Population(genome, site_pos, site_alt, hap_alt, site_cum, n_samples)
+
+
+def _read_keys(pop: Population, start: torch.Tensor, hap: torch.Tensor, read_len: int):
+    """Per read (start, haplotype): its shard (reversed last 3 bases as a base-4 number: the 64 keys of
+    demo/permutations-3.txt in that file's order, service.cpp:820) and the pattern of alternative alleles over the
+    sites inside its window -- (start, pattern) identifies the read's string."""
+    m = pop.site_pos.numel()
+    a = pop.site_cum[start].long()
+    b = pop.site_cum[start + read_len].long()
+    nsites = b - a
+    if nsites.numel() and int(nsites.max()) > PATTERN_BITS:
+        raise RuntimeError("a read window spans more variant sites than PATTERN_BITS")
+    flat = pop.hap_alt.reshape(-1)
+    pattern = torch.zeros_like(start)
+    for j in range(int(nsites.max()) if nsites.numel() else 0):
+        idx = (a + j).clamp(max=max(m - 1, 0))
+        bit = flat[hap.long() * m + idx] & (a + j < b)
+        pattern |= bit.long() << j
+    # last three bases under the haplotype
+    shard = torch.zeros_like(start)
+    for j in range(3):
+        p = start + read_len - 1 - j
+        sidx = pop.site_cum[p].long()
+        at_site = pop.site_cum[p + 1].long() > sidx
+        sidx_c = sidx.clamp(max=max(m - 1, 0))
+        alt = at_site & flat[hap.long() * m + sidx_c] if m else at_site
+        base = torch.where(alt, pop.site_alt[sidx_c] if m else pop.genome[p], pop.genome[p]).long()
+        shard = shard * 4 + (base - 1)
+    return shard, pattern
+
+
+def population_read_keys(pop: Population, coverage: float, read_len: int, seed: int, shards: list[int] | None = None,
+                         n_shard_keys: int = 64):
+    """All reads of the population as sorted 63-bit keys  shard << 57 | start << 26 | pattern << 10 | haplotype
+    (forward strand, error free, uniform start, coverage x per diploid sample split evenly over its two haplotypes).
+    Only the reads of `shards` are kept (None = all); the per-shard raw read counts of ALL shards are returned too
+    (the weights for placing shards on GPUs).  haplotype < 1024, start < 2^31."""
+    dev = pop.genome.device
+    G = pop.genome.numel()
+    per_sample = int(coverage * G / read_len)
+    assert pop.n_haplotypes <= 1024 and G < (1 << 31) and n_shard_keys <= 64
+    keep = None
+    if shards is not None:
+        keep = torch.zeros(n_shard_keys, dtype=torch.bool, device=dev)
+        keep[torch.tensor(sorted(shards), device=dev, dtype=torch.long)] = True
+    hist = torch.zeros(n_shard_keys, dtype=torch.int64, device=dev)
+    parts = []
+    for s in range(pop.n_samples):
+        g = _gen(seed * 1_000_003 + s, dev)
+        start = torch.randint(0, G - read_len + 1, (per_sample,), generator=g, device=dev)
+        hap = torch.randint(0, 2, (per_sample,), generator=g, device=dev) + 2 * s
+        shard, pattern = _read_keys(pop, start, hap, read_len)
+        hist += torch.bincount(shard, minlength=n_shard_keys)
+        key = (shard << 57) | (start << 26) | (pattern << 10) | hap
+        if keep is not None:
+            key = key[keep[shard]]
+        parts.append(key)
+        del start, hap, shard, pattern
+    keys = torch.cat(parts) if parts else torch.zeros(0, dtype=torch.int64, device=dev)
+    del parts
+    keys = torch.sort(keys).values
+    return keys, hist
+
+
+@dataclass
+class ShardData:
+    shard: int                 # 0..63: index into permutation_keys(3)
+    reads: torch.Tensor        # uint8 [U, L] unique reads in RLO order (= builder input order = read index)
+    built: BuiltBWT
+    samp_off: torch.Tensor     # int64 [U + 1]
+    samp_codes: torch.Tensor   # uint8 [total]: code of sample i = 34 + i (create_samples_hash.cpp: 1-based + 33), in
+                               #   sample order, one per occurrence of the read (rlosort...cpp:47-53, merge...cpp:45-47)
+    raw_reads: int
+    dropped_reads: int = 0     # unique reads removed to keep the reference's m_vSum lookup in bounds (Q2)
+
+
+def build_population_shard(pop: Population, keys: torch.Tensor, shard: int, read_len: int, keep_plain: bool = False) -> ShardData:
+    """One shard's slice of the sorted keys -> unique reads (RLO order), their BWT + .sai, and the sample table."""
+    dev = pop.genome.device
+    bounds = torch.tensor([shard << 57, ((shard + 1) << 57) - 1], device=dev, dtype=torch.int64)
+    lo = int(torch.searchsorted(keys, bounds[:1])[0])
+    hi = int(torch.searchsorted(keys, bounds[1:], right=True)[0])
+    k = keys[lo:hi]
+    n_raw = k.numel()
+    cand_key = k >> 10                                   # (shard, start, pattern): one candidate read string each
+    first = torch.ones(n_raw, dtype=torch.bool, device=dev)
+    if n_raw > 1:
+        first[1:] = cand_key[1:] != cand_key[:-1]
+    cand_of = torch.cumsum(first.long(), 0) - 1          # raw read -> candidate
+    ck = cand_key[first]
+    start = (ck >> 16) & 0x7FFFFFFF
+    pattern = ck & 0xFFFF
+    U0 = ck.numel()
+    cols = torch.arange(read_len, device=dev)
+    reads = pop.genome[start[:, None] + cols[None, :]]
+    a = pop.site_cum[start].long()
+    m = pop.site_pos.numel()
+    for j in range(PATTERN_BITS):
+        sel = torch.nonzero((pattern >> j) & 1).flatten()
+        if sel.numel() == 0:
+            continue
+        sidx = (a[sel] + j).clamp(max=max(m - 1, 0))
+        reads[sel, pop.site_pos[sidx] - start[sel]] = pop.site_alt[sidx]
+    lens = torch.full((U0,), read_len, dtype=torch.int32, device=dev)
+    ureads, ulens, _, inverse = dedupe_rlo(reads, lens)  # exact: two windows with the same string merge here
+    del reads
+    built = build_bwt(ureads, ulens, keep_plain=keep_plain)
+    dropped = 0
+    while not q2_safe(built.runs, built.num_symbols) and ureads.shape[0] > 1:
+        # the reference would read m_vSum out of bounds on this BWT (SURVEY.md Q2, ~31/65536 of all BWTs): drop the
+        # shard's last read (RLO order) until it would not -- deterministic, and the generator's only other choice
+        # would be to re-seed the whole population
+        dropped += 1
+        ureads, ulens = ureads[:-1], ulens[:-1]
+        built = build_bwt(ureads, ulens, keep_plain=keep_plain)
+    U = ureads.shape[0]
+    if dropped:
+        keep_raw = inverse[cand_of] < U
+        k, cand_of = k[keep_raw], cand_of[keep_raw]
+    # sample table: per unique read, the codes of the samples it was seen in, sample order, duplicates kept
+    rid = inverse[cand_of]
+    sample = (k & 1023) >> 1
+    order = torch.sort(rid * 1024 + sample).values
+    samp_codes = (order % 1024 + 34).to(torch.uint8)
+    samp_off = torch.zeros(U + 1, dtype=torch.int64, device=dev)
+    samp_off[1:] = torch.cumsum(torch.bincount(order // 1024, minlength=U), 0)
+    return ShardData(shard, ureads, built, samp_off, samp_codes, n_raw, dropped)
+
+
+def population_queries(pop: Population, n_queries: int, k: int, seed: int, frac_present: float = 0.9) -> torch.Tensor:
+    """[Q, k] ASCII: frac_present cut from the reference genome (haplotypes differ from it at ~1/kb), the rest random."""
+    return make_queries(pop.genome, n_queries, k, seed, frac_present)
+
+
+def site_probe_kmers(pop: Population, n_sites: int, k: int, seed: int):
+    """configs[4]: for n_sites sites of the population list, the reference-allele and the alternative-allele k-mer
+    centred on the site.  Returns (ref [n, k] ASCII, alt [n, k] ASCII, site numbers [n])."""
+    dev = pop.genome.device
+    g = _gen(seed, dev)
+    G = pop.genome.numel()
+    half = k // 2
+    ok = torch.nonzero((pop.site_pos >= half) & (pop.site_pos + (k - half) <= G)).flatten()
+    pick = ok[torch.randint(0, ok.numel(), (n_sites,), generator=g, device=dev)]
+    pos = pop.site_pos[pick]
+    cols = torch.arange(k, device=dev)
+    ref = pop.genome[(pos - half)[:, None] + cols[None, :]]
+    alt = ref.clone()
+    alt[:, half] = pop.site_alt[pick]
+    lut = torch.from_numpy(ASCII.copy()).to(dev)
+    return lut[ref.long()], lut[alt.long()], pick

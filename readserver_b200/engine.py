@@ -41,6 +41,13 @@ class Info(C.Structure):
                 ("prefix_table_k", C.c_int32), ("reserved_", C.c_int32)]
 
 
+class ShardSetInfo(C.Structure):
+    _fields_ = [("num_shards", C.c_uint32), ("sealed", C.c_uint32), ("locate_every", C.c_uint32),
+                ("max_read_len", C.c_uint32), ("num_samples", C.c_uint32), ("carrier_words", C.c_uint32),
+                ("index_bytes", C.c_uint64), ("table_bytes", C.c_uint64), ("bwlen", C.c_uint64),
+                ("num_strings", C.c_uint64), ("num_runs", C.c_uint64), ("chunk_queries", C.c_uint64)]
+
+
 _LIB = None
 
 
@@ -57,6 +64,24 @@ def lib() -> C.CDLL:
     sig = {
         "rs_index_open": (i32, [C.c_char_p, i32, C.POINTER(vp)]),
         "rs_index_from_runs": (i32, [vp, u64, u64, u64, i32, C.POINTER(vp)]),
+        "rs_index_from_runs_dev": (i32, [vp, u64, u64, u64, i32, C.POINTER(vp)]),
+        "rs_index_from_runs_host": (i32, [vp, u64, u64, u64, i32, C.POINTER(vp)]),
+        "rs_index_save": (i32, [vp, C.c_char_p]),
+        "rs_index_open_encoded": (i32, [C.c_char_p, i32, C.POINTER(vp)]),
+        "rs_index_export": (i32, [vp, i32, vp, u64, C.POINTER(u64)]),
+        "rs_index_set_sai_dev": (i32, [vp, vp, u64]),
+        "rs_index_set_samples_dev": (i32, [vp, vp, vp, u64, i32]),
+        "rs_index_set_samples_meta": (i32, [vp, vp, vp, vp, u64, i32]),
+        "rs_samples_meta_batch": (i32, [vp, vp, sz, vp, u64, vp, vp]),
+        "rs_shardset_create": (i32, [i32, C.POINTER(vp)]),
+        "rs_shardset_add": (i32, [vp, vp, C.c_uint32]),
+        "rs_shardset_seal": (i32, [vp, C.c_uint32, C.c_uint32]),
+        "rs_shardset_destroy": (None, [vp]),
+        "rs_shardset_get_info": (i32, [vp, C.POINTER(ShardSetInfo)]),
+        "rs_shardset_enable_stats": (i32, [vp, i32]),
+        "rs_shardset_read_stats": (i32, [vp, C.POINTER(u64), C.POINTER(u64), i32]),
+        "rs_pop_query_dev": (i32, [vp, vp, i32, sz, i32, u64, vp, vp, vp, u64, vp, vp, vp]),
+        "rs_pop_query": (i32, [vp, vp, i32, sz, i32, u64, vp, vp, vp, u64, vp, C.POINTER(u64)]),
         "rs_index_close": (None, [vp]),
         "rs_index_get_info": (i32, [vp, C.POINTER(Info)]),
         "rs_index_set_tail_emulation": (i32, [vp, i32]),
@@ -150,14 +175,23 @@ class GpuBWT:
     """One BWT shard resident in the HBM of one B200 (``RLEBWT``, rlebwt.cpp:11-32)."""
 
     def __init__(self, bwt_path: str | None = None, *, runs=None, num_strings: int = 0, num_symbols: int = 0,
-                 device: int = 0):
+                 device: int = 0, encoded_path: str | None = None, host_encoder: bool = False):
+        """bwt_path: an SGA .bwt file; runs: its run bytes (numpy: host memory; torch CUDA tensor: device memory,
+        encoded in place on the GPU); encoded_path: a file written by save(); host_encoder: build the blocks with
+        the host-side encoder instead of the device one (cross-check)."""
         L = lib()
         h = C.c_void_p()
-        if bwt_path is not None:
+        if encoded_path is not None:
+            _check(L.rs_index_open_encoded(os.fsencode(encoded_path), device, C.byref(h)))
+        elif bwt_path is not None:
             _check(L.rs_index_open(os.fsencode(bwt_path), device, C.byref(h)))
+        elif not isinstance(runs, np.ndarray) and hasattr(runs, "data_ptr"):
+            assert runs.is_cuda and runs.is_contiguous() and runs.element_size() == 1
+            _check(L.rs_index_from_runs_dev(runs.data_ptr(), runs.numel(), num_strings, num_symbols, device, C.byref(h)))
         else:
             runs = np.ascontiguousarray(runs, dtype=np.uint8)
-            _check(L.rs_index_from_runs(runs.ctypes.data, runs.size, num_strings, num_symbols, device, C.byref(h)))
+            f = L.rs_index_from_runs_host if host_encoder else L.rs_index_from_runs
+            _check(f(runs.ctypes.data, runs.size, num_strings, num_symbols, device, C.byref(h)))
         self._h = h
         self.device = device
         info = Info()
@@ -197,8 +231,24 @@ class GpuBWT:
         return int(a.value), int(b.value)
 
     def set_sai(self, sai):
+        if not isinstance(sai, np.ndarray) and hasattr(sai, "data_ptr"):  # torch CUDA tensor (int64 / uint64)
+            assert sai.is_cuda and sai.is_contiguous() and sai.element_size() == 8
+            _check(lib().rs_index_set_sai_dev(self._h, sai.data_ptr(), sai.numel()))
+            return
         sai = np.ascontiguousarray(sai, dtype=np.uint64)
         _check(lib().rs_index_set_sai(self._h, sai.ctypes.data, sai.size))
+
+    def save(self, path: str):
+        """Persist the HBM-layout index (the .bpi2 analogue): reopen with GpuBWT(encoded_path=...)."""
+        _check(lib().rs_index_save(self._h, os.fsencode(path)))
+
+    def export(self, what: int) -> np.ndarray:
+        """Raw bytes of one device array: 0 blocks, 1 position directory, 2..6 select directories, 7 suffix table."""
+        n = C.c_uint64()
+        _check(lib().rs_index_export(self._h, what, None, 0, C.byref(n)))
+        buf = np.zeros(max(int(n.value), 1), dtype=np.uint8)
+        _check(lib().rs_index_export(self._h, what, buf.ctypes.data, buf.size, C.byref(n)))
+        return buf[: int(n.value)]
 
     # -- class BWT -------------------------------------------------------------------------------
     def get_bwlen(self) -> int:
@@ -347,12 +397,39 @@ class GpuBWT:
             out["read_index"] = ri
         return out
 
-    def set_samples(self, offsets, codes, size_of_sample: int):
+    def set_samples(self, offsets, codes, size_of_sample: int, meta=None):
+        """Sample table: read r owns codes [offsets[r], offsets[r+1]); meta (optional) = 2 bytes per code, the count
+        and lane characters of a store with has_other_meta_data.  torch CUDA tensors are copied device to device."""
+        self._sos = size_of_sample
+        if not isinstance(offsets, np.ndarray) and hasattr(offsets, "data_ptr"):
+            assert meta is None and offsets.is_cuda and offsets.is_contiguous() and codes.is_contiguous()
+            _check(lib().rs_index_set_samples_dev(self._h, offsets.data_ptr(), codes.data_ptr(), offsets.numel() - 1,
+                                                  size_of_sample))
+            return
         offsets = np.ascontiguousarray(offsets, dtype=np.uint64)
         codes = np.ascontiguousarray(codes, dtype=np.uint8).reshape(-1)
-        _check(lib().rs_index_set_samples(self._h, offsets.ctypes.data, codes.ctypes.data if codes.size else None,
-                                          offsets.size - 1, size_of_sample))
-        self._sos = size_of_sample
+        if meta is not None:
+            meta = np.ascontiguousarray(meta, dtype=np.uint8).reshape(-1)
+            assert meta.size == 2 * (codes.size // size_of_sample)
+        _check(lib().rs_index_set_samples_meta(self._h, offsets.ctypes.data, codes.ctypes.data if codes.size else None,
+                                               meta.ctypes.data if meta is not None and meta.size else None,
+                                               offsets.size - 1, size_of_sample))
+
+    def samples_meta(self, read_index):
+        """(offsets [n+1], codes [total, sos], meta [total, 2]) for n reads of a table with count / lane metadata."""
+        ri = np.ascontiguousarray(read_index, dtype=np.uint64)
+        off = np.empty(ri.size + 1, dtype=np.uint64)
+        L = lib()
+        rc = L.rs_samples_meta_batch(self._h, ri.ctypes.data, ri.size, off.ctypes.data, 0, None, None)
+        if rc not in (0, 9):
+            _check(rc)
+        tot = int(off[ri.size])
+        codes = np.empty((tot, self._sos), dtype=np.uint8)
+        meta = np.empty((tot, 2), dtype=np.uint8)
+        if tot:
+            _check(L.rs_samples_meta_batch(self._h, ri.ctypes.data, ri.size, off.ctypes.data, tot, codes.ctypes.data,
+                                           meta.ctypes.data))
+        return off, codes, meta
 
     def load_samples_file(self, path: str, size_of_sample: int, has_other_meta_data: bool = False):
         """Sample table from the ETL's merged `read / codes` file (load_data_into_rocksdb.cpp:41-49)."""
@@ -490,6 +567,113 @@ class GpuBWT:
                            d_bases=None, stream: int = 0):
         _check(lib().rs_extract_prefix_batch_dev(self._h, _ptr(d_rows), n, max_steps, _ptr(d_lexrank), _ptr(d_steps),
                                                  _ptr(d_read_index), _ptr(d_bases), stream))
+
+
+class ShardSet:
+    """The BWT shards resident on one GPU, queried together (rs_shardset_* / rs_pop_query of the C ABI): what the
+    reference's front end does over its per-shard workers -- broadcast, sum of counts, concatenation of read lists
+    (src/service/server.cpp:124, 184-197, 404-410) -- as one device pipeline."""
+
+    def __init__(self, device: int = 0):
+        self._h = C.c_void_p()
+        self.device = device
+        self._keep = []
+        _check(lib().rs_shardset_create(device, C.byref(self._h)))
+
+    def add(self, bwt: "GpuBWT", shard_id: int):
+        _check(lib().rs_shardset_add(self._h, bwt._h, shard_id))
+        self._keep.append(bwt)  # the set borrows the index
+
+    def seal(self, max_read_len: int, locate_every: int = 1):
+        """locate_every = 1: read-index tables (4 bytes per BWT row); > 1: sampled locate tables; 0: plain walks."""
+        _check(lib().rs_shardset_seal(self._h, max_read_len, locate_every))
+        return self.info
+
+    @property
+    def info(self) -> ShardSetInfo:
+        i = ShardSetInfo()
+        _check(lib().rs_shardset_get_info(self._h, C.byref(i)))
+        return i
+
+    def enable_stats(self, on: bool = True):
+        _check(lib().rs_shardset_enable_stats(self._h, int(on)))
+
+    def read_stats(self, reset: bool = True) -> tuple[int, int]:
+        a, b = C.c_uint64(), C.c_uint64()
+        _check(lib().rs_shardset_read_stats(self._h, C.byref(a), C.byref(b), int(reset)))
+        return int(a.value), int(b.value)
+
+    def query_dev(self, d_kmers, k: int, q: int, packed: bool, max_hits: int, d_counts, d_hit_offsets=None, d_hits=None,
+                  capacity: int = 0, d_carriers=None, d_total=None, stream: int = 0):
+        """Asynchronous on `stream`, device buffers (torch tensors); see rs_pop_query_dev."""
+        _check(lib().rs_pop_query_dev(self._h, _ptr(d_kmers), k, q, int(packed), max_hits, _ptr(d_counts), _ptr(d_hit_offsets),
+                                      _ptr(d_hits), capacity, _ptr(d_carriers), _ptr(d_total), stream))
+
+    def query(self, kmers, k: int | None = None, max_hits: int = 1 << 20, locate: bool = True, carriers: bool = False,
+              packed: bool = False):
+        """Host arrays in, host arrays out: dict(counts, hit_offsets, hits, carriers)."""
+        if packed:
+            kmers = np.ascontiguousarray(kmers, dtype=np.uint64)
+            q = kmers.size
+        else:
+            kmers = _ascii(kmers)
+            if k is None:
+                k = kmers.shape[-1]
+            kmers = kmers.reshape(-1)
+            q = kmers.size // k
+        counts = np.zeros(q, dtype=np.uint64)
+        out = {"counts": counts}
+        L = lib()
+        tot = C.c_uint64()
+        if not locate:
+            _check(L.rs_pop_query(self._h, kmers.ctypes.data, k, q, int(packed), max_hits, counts.ctypes.data, None, None, 0,
+                                  None, C.byref(tot)))
+            return out
+        off = np.zeros(q + 1, dtype=np.uint64)
+        rc = L.rs_pop_query(self._h, kmers.ctypes.data, k, q, int(packed), max_hits, counts.ctypes.data, off.ctypes.data, None,
+                            0, None, C.byref(tot))
+        if rc not in (0, 9):
+            _check(rc)
+        cap = int(tot.value)
+        hits = np.zeros(max(cap, 1), dtype=np.uint64)
+        W = int(self.info.carrier_words)
+        carr = np.zeros((q, W), dtype=np.uint32) if carriers else None
+        _check(L.rs_pop_query(self._h, kmers.ctypes.data, k, q, int(packed), max_hits, counts.ctypes.data, off.ctypes.data,
+                              hits.ctypes.data, cap, _ptr(carr), C.byref(tot)))
+        out.update(hit_offsets=off, hits=hits[:cap])
+        if carriers:
+            out["carriers"] = carr
+        return out
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().rs_shardset_destroy(self._h)
+            self._h = None
+        self._keep = []
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+
+def pack_kmers(kmers: np.ndarray) -> np.ndarray:
+    """[Q, k] ASCII -> uint64 keys of the packed-query entry points: 2 bits per base (A,C,G,T = 0..3), first base
+    most significant; bit 63 set when the k-mer holds any other byte (it then counts 0, service.cpp:299-301)."""
+    kmers = np.ascontiguousarray(kmers, dtype=np.uint8)
+    lut = np.full(256, 255, dtype=np.uint8)
+    for i, c in enumerate(b"ACGT"):
+        lut[c] = i
+    codes = lut[kmers]
+    bad = (codes == 255).any(axis=1)
+    v = np.zeros(kmers.shape[0], dtype=np.uint64)
+    for j in range(kmers.shape[1]):
+        v = (v << np.uint64(2)) | (codes[:, j] & 3).astype(np.uint64)
+    v[bad] |= np.uint64(1) << np.uint64(63)
+    return v
 
 
 class PeerComm:

@@ -1,0 +1,293 @@
+"""GPU parity of this round's additions, through the C ABI against the CPU oracle:
+the device-side re-encoder (K4), the persisted index, and the shard-set pipeline (count + locate + sample sets over
+the reference's 64 read-suffix shards; front end fan-in server.cpp:184-197, 404-410)."""
+import os
+
+import numpy as np
+import pytest
+
+import oracle
+from readserver_b200 import datagen as dg
+from tests import common
+from tests.golden.make_golden import random_runs
+
+pytestmark = pytest.mark.gpu
+U64MAX = np.iinfo(np.uint64).max
+
+
+@pytest.fixture(scope="module")
+def engine():
+    import torch
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    from readserver_b200 import engine as e
+    return e
+
+
+# ------------------------------------------------------------------------------------------------
+# K4 on the device == K4 on the host, array by array
+# ------------------------------------------------------------------------------------------------
+def _arrays_equal(a, b):
+    for what in range(0, 8):
+        assert np.array_equal(a.export(what), b.export(what)), what
+    ia, ib = a.info, b.info
+    for f in ("bwlen", "num_strings", "num_runs", "num_blocks", "ref_depth", "ref_clamp_c", "ref_vlast", "q2_safe"):
+        assert getattr(ia, f) == getattr(ib, f), f
+    assert list(ia.pc) == list(ib.pc) and list(ia.total) == list(ib.total)
+
+
+@pytest.mark.parametrize("name", ["tiny", "small", "clean", "mid", "deep"])
+def test_device_encoder_equals_host_encoder(name, datasets, engine):
+    import torch
+    case = datasets.case(name)
+    kw = dict(num_strings=case.num_strings, num_symbols=case.num_symbols)
+    with engine.GpuBWT(runs=case.runs, **kw) as D, engine.GpuBWT(runs=case.runs, host_encoder=True, **kw) as H, \
+            engine.GpuBWT(runs=torch.from_numpy(case.runs).cuda(), **kw) as DD:
+        _arrays_equal(D, H)
+        _arrays_equal(DD, H)
+        # getChar's own clamp is not in rs_index_info: compare its effect at the end of the BWT
+        idx = np.arange(max(0, case.num_symbols - 70000), case.num_symbols, dtype=np.uint64)
+        assert np.array_equal(D.get_char(idx), H.get_char(idx))
+        q = case.queries(2000, 31, seed=77)
+        assert all(np.array_equal(x, y) for x, y in zip(D.find_interval(q, 31), H.find_interval(q, 31)))
+
+
+@pytest.mark.parametrize("shape", ["ones", "single", "multiple36", "rand_depth3", "rand_small"])
+def test_device_encoder_on_degenerate_run_shapes(shape, engine):
+    rng = np.random.default_rng(12)
+    if shape == "ones":          # every run has length 1: more than three block boundaries per 512-symbol slot
+        runs = ((rng.integers(0, 5, 20000) << 5) | 1).astype(np.uint8)
+    elif shape == "single":
+        runs = np.array([(2 << 5) | 17], dtype=np.uint8)
+    elif shape == "multiple36":
+        runs = ((rng.integers(1, 5, 36 * 50) << 5) | rng.integers(1, 32, 36 * 50)).astype(np.uint8)
+    elif shape == "rand_depth3":
+        runs, _ = random_runs(5, 1_200_000)
+    else:
+        runs, _ = random_runs(6, 70_000)
+    n = int((runs & 31).sum())
+    ns = int((runs[(runs >> 5) == 0] & 31).sum())
+    with engine.GpuBWT(runs=runs, num_strings=ns, num_symbols=n) as D, \
+            engine.GpuBWT(runs=runs, num_strings=ns, num_symbols=n, host_encoder=True) as H:
+        _arrays_equal(D, H)
+        P = oracle.PortIndex(runs=runs, num_strings=ns, num_symbols=n)
+        idx = common.positions(n, limit=100_000)
+        for c in b"$ACGT":
+            s = np.full(idx.size, c, dtype=np.uint8)
+            assert np.array_equal(D.get_occ(s, idx), P.get_occ_batch(s, idx))
+        assert np.array_equal(D.get_char(idx), P.get_char_batch(idx))
+
+
+def test_device_encoder_rejects_what_the_host_encoder_rejects(engine):
+    bad = np.array([(5 << 5) | 3, (1 << 5) | 2], dtype=np.uint8)
+    with pytest.raises(engine.RsError) as e:
+        engine.GpuBWT(runs=bad, num_strings=0, num_symbols=5)
+    assert e.value.status == 4
+    zero = np.array([(1 << 5) | 0], dtype=np.uint8)
+    with pytest.raises(engine.RsError) as e:
+        engine.GpuBWT(runs=zero, num_strings=0, num_symbols=0)
+    assert e.value.status == 4
+    ok = np.array([(1 << 5) | 3], dtype=np.uint8)
+    with pytest.raises(engine.RsError) as e:
+        engine.GpuBWT(runs=ok, num_strings=0, num_symbols=4)   # symbol count disagrees with the runs
+    assert e.value.status == 5
+
+
+@pytest.mark.parametrize("name", ["small", "deep"])
+def test_saved_index_reopens_identically(name, datasets, engine, tmp_path):
+    case, P = datasets.case(name), datasets.port(name)
+    path = str(tmp_path / "shard.rsb2")
+    with engine.GpuBWT(runs=case.runs, num_strings=case.num_strings, num_symbols=case.num_symbols) as B:
+        B.set_sai(case.sai)
+        B.save(path)
+        with engine.GpuBWT(encoded_path=path) as R:
+            _arrays_equal(B, R)
+            q = case.queries(5000, 31, seed=3)
+            lo, up = R.find_interval(q, 31)
+            lo2, up2 = P.find_interval_batch(q, 31, nthreads=4)
+            assert np.array_equal(lo, lo2) and np.array_equal(up, up2)
+            hit = np.nonzero(up >= lo)[0][:300]
+            rows = np.concatenate([np.arange(lo[i], up[i] + 1, dtype=np.uint64) for i in hit])
+            a = R.extract_prefix(rows, max_steps=128, want_read_index=True)
+            b = B.extract_prefix(rows, max_steps=128, want_read_index=True)
+            assert all(np.array_equal(x, y) for x, y in zip(a, b))
+    with open(path, "r+b") as f:          # truncated and foreign files are refused with a status, not a crash
+        f.truncate(os.path.getsize(path) // 2)
+    with pytest.raises(engine.RsError) as e:
+        engine.GpuBWT(encoded_path=path)
+    assert e.value.status == 3
+    with open(path, "wb") as f:
+        f.write(b"not an index" * 100)
+    with pytest.raises(engine.RsError) as e:
+        engine.GpuBWT(encoded_path=path)
+    assert e.value.status == 2
+
+
+# ------------------------------------------------------------------------------------------------
+# shard set: count + locate + sample sets over the 64 read-suffix shards
+# ------------------------------------------------------------------------------------------------
+class PopCase:
+    """A small population (configs[2] shape), its 64 shards on the GPU and their CPU oracles."""
+
+    def __init__(self, engine, genome_len=40_000, n_samples=9, coverage=20, read_len=100, device_runs=True):
+        import torch
+        self.pop = dg.make_population(genome_len, n_samples, seed=4, device="cuda")
+        keys, self.hist = dg.population_read_keys(self.pop, coverage, read_len, seed=41)
+        self.read_len = read_len
+        self.gpu, self.port, self.sai, self.samp = [], [], [], []
+        for s in range(64):
+            sh = dg.build_population_shard(self.pop, keys, s, read_len)
+            b = sh.built
+            runs_h = b.runs.cpu().numpy()
+            B = engine.GpuBWT(runs=b.runs.contiguous() if device_runs else runs_h, num_strings=b.num_strings,
+                              num_symbols=b.num_symbols)
+            B.set_sai(b.sai.contiguous() if device_runs else b.sai.cpu().numpy().astype(np.uint64))
+            if device_runs:
+                B.set_samples(sh.samp_off.contiguous(), sh.samp_codes.contiguous(), 1)
+            else:
+                B.set_samples(sh.samp_off.cpu().numpy().astype(np.uint64), sh.samp_codes.cpu().numpy(), 1)
+            self.gpu.append(B)
+            self.port.append(oracle.PortIndex(runs=runs_h, num_strings=b.num_strings, num_symbols=b.num_symbols))
+            self.sai.append(b.sai.cpu().numpy().astype(np.uint64))
+            self.samp.append((sh.samp_off.cpu().numpy(), sh.samp_codes.cpu().numpy()))
+        self.queries = dg.population_queries(self.pop, 3000, 31, seed=5).cpu().numpy()
+
+    def expected(self, q, max_hits, shard_order=None):
+        """counts, hit_offsets, hits, carriers (4 words) from the per-shard oracles, in the set's hit order."""
+        order = list(range(64)) if shard_order is None else shard_order
+        Q = q.shape[0]
+        per = []
+        counts = np.zeros(Q, dtype=np.uint64)
+        for s in order:
+            lo, up = self.port[s].find_interval_batch(q, q.shape[1], nthreads=4)
+            c = np.where(up >= lo, up - lo + 1, 0).astype(np.uint64)
+            counts += c
+            per.append((s, lo, np.minimum(c, max_hits)))
+        hits = [[] for _ in range(Q)]
+        for s, lo, c in per:
+            nz = np.nonzero(c)[0]
+            if nz.size == 0:
+                continue
+            rows = np.concatenate([np.arange(lo[i], lo[i] + c[i], dtype=np.uint64) for i in nz])
+            lex, _, _, _ = self.port[s].locate_batch(rows, prefix=True, postfix=False, max_steps=self.read_len + 28)
+            ns = self.sai[s].size
+            ri = np.where(lex < ns, self.sai[s][np.minimum(lex, ns - 1)], U64MAX)
+            at = 0
+            for i in nz:
+                for r in ri[at: at + int(c[i])]:
+                    hits[i].append(U64MAX if r == U64MAX else (np.uint64(s) << np.uint64(40)) | r)
+                at += int(c[i])
+        off = np.zeros(Q + 1, dtype=np.uint64)
+        off[1:] = np.cumsum([len(h) for h in hits])
+        flat = np.array([x for h in hits for x in h], dtype=np.uint64)
+        carr = np.zeros((Q, 4), dtype=np.uint32)
+        for i, h in enumerate(hits):
+            for x in h:
+                if x == U64MAX:
+                    continue
+                s, r = int(x) >> 40, int(x) & ((1 << 40) - 1)
+                so, sc = self.samp[s]
+                for code in sc[so[r]: so[r + 1]]:
+                    smp = int(code) - 34
+                    carr[i, smp >> 5] |= np.uint32(1 << (smp & 31))
+        return counts, off, flat, carr
+
+    def close(self):
+        for b in self.gpu:
+            b.close()
+
+
+@pytest.fixture(scope="module")
+def popcase(engine):
+    c = PopCase(engine)
+    yield c
+    c.close()
+
+
+@pytest.mark.parametrize("locate_every", [1, 8, 0])
+def test_shard_set_count_locate_carriers_match_per_shard_oracles(locate_every, popcase, engine):
+    q = popcase.queries
+    with engine.ShardSet() as S:
+        for s, b in enumerate(popcase.gpu):
+            S.add(b, s)
+        info = S.seal(popcase.read_len + 28, locate_every)
+        assert info.num_shards == 64 and info.num_samples == 9 and info.carrier_words == 4
+        for max_hits in (1 << 20, 3):
+            want = popcase.expected(q, max_hits)
+            got = S.query(q, 31, max_hits=max_hits, carriers=True)
+            assert np.array_equal(got["counts"], want[0])
+            assert np.array_equal(got["hit_offsets"], want[1])
+            assert np.array_equal(got["hits"], want[2])
+            assert np.array_equal(got["carriers"], want[3])
+        assert int(want[0].sum()) > 10 * q.shape[0]      # the batch really hits
+        # packed queries give the same answers; count-only call
+        got2 = S.query(engine.pack_kmers(q), 31, packed=True, max_hits=3, carriers=True)
+        assert all(np.array_equal(got[k], got2[k]) for k in got)
+        assert np.array_equal(S.query(q, 31, locate=False)["counts"], want[0])
+
+
+def test_shard_set_order_ids_chunks_and_bad_bytes(popcase, engine, monkeypatch):
+    """Shards added in another order with other ids; a chunk size that splits the batch unevenly; k-mers holding a
+    byte outside ACGT count 0 (service.cpp:299-301); k < 31."""
+    monkeypatch.setenv("RS_B200_POP_CHUNK", "1100")
+    order = [63 - s for s in range(0, 64, 3)]
+    q = popcase.queries[:2500, :24].copy()
+    q[::50, 7] = ord("N")
+    with engine.ShardSet() as S:
+        for s in order:
+            S.add(popcase.gpu[s], s)
+        S.seal(popcase.read_len + 28, 1)
+        assert S.info.chunk_queries == 1100
+        want = popcase.expected(q, 1 << 20, shard_order=order)
+        assert int(want[0][::50].sum()) == 0
+        got = S.query(q, 24, carriers=True)
+        assert np.array_equal(got["counts"], want[0]) and np.array_equal(got["hit_offsets"], want[1])
+        assert np.array_equal(got["hits"], want[2]) and np.array_equal(got["carriers"], want[3])
+        # capacity too small: offsets and total still reported, status CAPACITY
+        import ctypes as C
+        L = engine.lib()
+        counts = np.zeros(q.shape[0], dtype=np.uint64)
+        off = np.zeros(q.shape[0] + 1, dtype=np.uint64)
+        hits = np.zeros(10, dtype=np.uint64)
+        tot = C.c_uint64()
+        flat = np.ascontiguousarray(q).reshape(-1)
+        rc = L.rs_pop_query(S._h, flat.ctypes.data, 24, q.shape[0], 0, 1 << 20, counts.ctypes.data, off.ctypes.data,
+                            hits.ctypes.data, 10, None, C.byref(tot))
+        assert rc == 9 and tot.value == want[1][-1] and np.array_equal(off, want[1]) and np.array_equal(hits, want[2][:10])
+
+
+def test_shard_set_under_the_reference_tail_behaviour(datasets, engine):
+    """A single shard whose tail region is NOT empty ('small': walks into it are cut or wander): the read-index table
+    leaves those rows uncovered and the pipeline walks them, ending where K2 and the oracle end."""
+    case, P = datasets.case("small"), datasets.port("small")
+    q = case.queries(4000, 20, seed=9)
+    with engine.GpuBWT(runs=case.runs, num_strings=case.num_strings, num_symbols=case.num_symbols) as B:
+        B.set_sai(case.sai)
+        for every in (1, 4, 0):
+            with engine.ShardSet() as S:
+                S.add(B, 17)
+                S.seal(128, every)
+                got = S.query(q, 20, max_hits=64)
+                lo, up = P.find_interval_batch(q, 20, nthreads=4)
+                c = np.where(up >= lo, up - lo + 1, 0).astype(np.uint64)
+                assert np.array_equal(got["counts"], c)
+                ch = np.minimum(c, 64)
+                rows = np.concatenate([np.arange(lo[i], lo[i] + ch[i], dtype=np.uint64) for i in np.nonzero(ch)[0]])
+                lex, _, _, _ = P.locate_batch(rows, prefix=True, postfix=False, max_steps=128)
+                ns = case.sai.size
+                ri = np.where(lex < ns, case.sai[np.minimum(lex, ns - 1)], U64MAX)
+                want = np.where(ri == U64MAX, U64MAX, (np.uint64(17) << np.uint64(40)) | ri)
+                assert np.array_equal(got["hits"], want), every
+
+
+def test_shard_set_argument_errors(popcase, engine):
+    with engine.ShardSet() as S:
+        with pytest.raises(engine.RsError):
+            S.seal(100, 1)                       # empty
+        S.add(popcase.gpu[0], 0)
+        with pytest.raises(engine.RsError):
+            S.add(popcase.gpu[1], 0)             # id twice
+        with pytest.raises(engine.RsError):
+            S.query(popcase.queries[:4], 31)     # not sealed
+        S.seal(128, 1)
+        with pytest.raises(engine.RsError):
+            S.query(np.zeros((2, 40), dtype=np.uint8) + 65, 40)   # k > 31

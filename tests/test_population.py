@@ -1,0 +1,80 @@
+"""The population generator (BASELINE.json configs[2] shape): reads of many diploid samples,
+partitioned into the reference's 64 shards by reversed last 3 bases (service.cpp:820, load_data_into_rocksdb.cpp:45),
+per shard the unique reads in RLO order with their sample codes in merge order (rlosort_seq_and_convert_sample_names.cpp:
+47-53, merge_rlosorted_reads.cpp:45-47).  Checked here against a naive regeneration of every read string."""
+from collections import defaultdict
+
+import numpy as np
+import torch
+
+from readserver_b200 import datagen as dg
+from readserver_b200 import sharding
+
+
+def naive_reads(pop, coverage, read_len, seed):
+    G = pop.genome.numel()
+    haps = []
+    for h in range(pop.n_haplotypes):
+        x = pop.genome.clone()
+        x[pop.site_pos[pop.hap_alt[h]]] = pop.site_alt[pop.hap_alt[h]]
+        haps.append(dg.ASCII[x.numpy()].tobytes().decode())
+    per = int(coverage * G / read_len)
+    out = []
+    for s in range(pop.n_samples):
+        g = dg._gen(seed * 1_000_003 + s, "cpu")
+        start = torch.randint(0, G - read_len + 1, (per,), generator=g)
+        hap = torch.randint(0, 2, (per,), generator=g) + 2 * s
+        for st, h in zip(start.tolist(), hap.tolist()):
+            out.append((haps[h][st:st + read_len], s))
+    return out
+
+
+def test_population_shards_equal_naive_regeneration():
+    pop = dg.make_population(60_000, 5, seed=4, site_rate=1 / 50, snp_rate=1 / 200)   # dense sites: many patterns
+    L = 60
+    keys, hist = dg.population_read_keys(pop, 25, L, seed=41)
+    allreads = naive_reads(pop, 25, L, 41)
+    assert int(hist.sum()) == len(allreads) == keys.numel()
+    names = sharding.permutation_keys(3)
+    seen = 0
+    for shard in (0, 7, 31, 32, 63):
+        sh = dg.build_population_shard(pop, keys, shard, L)
+        strs = dg.reads_to_strings(sh.reads, torch.full((sh.reads.shape[0],), L, dtype=torch.int32))
+        d = defaultdict(list)
+        for r, s in allreads:
+            if sharding.shard_of_read(r) == names[shard]:
+                d[r].append(s)
+        want = sorted(d.keys(), key=lambda r: r[::-1])
+        if sh.dropped_reads:
+            want = want[: len(want) - sh.dropped_reads]
+        assert want == strs
+        off, codes = sh.samp_off.numpy(), sh.samp_codes.numpy()
+        for i, r in enumerate(strs):
+            assert [int(c) - 34 for c in codes[off[i]:off[i + 1]]] == sorted(d[r])
+        assert sh.raw_reads == int(hist[shard])
+        assert dg.q2_safe(sh.built.runs, sh.built.num_symbols)
+        seen += len(strs)
+    assert seen > 0
+
+
+def test_only_the_requested_shards_are_kept_and_the_histogram_is_global():
+    pop = dg.make_population(30_000, 3, seed=9)
+    all_keys, hist = dg.population_read_keys(pop, 10, 50, seed=5)
+    mine, hist2 = dg.population_read_keys(pop, 10, 50, seed=5, shards=[3, 40])
+    assert torch.equal(hist, hist2)
+    sel = ((all_keys >> 57) == 3) | ((all_keys >> 57) == 40)
+    assert torch.equal(all_keys[sel], mine)
+    a = dg.build_population_shard(pop, all_keys, 40, 50)
+    b = dg.build_population_shard(pop, mine, 40, 50)
+    assert torch.equal(a.built.runs, b.built.runs) and torch.equal(a.samp_codes, b.samp_codes)
+
+
+def test_site_probes_differ_at_the_centre_only():
+    pop = dg.make_population(20_000, 2, seed=3)
+    ref, alt, pick = dg.site_probe_kmers(pop, 50, 31, seed=8)
+    diff = (ref != alt).numpy()
+    assert diff[:, 15].all() and diff.sum() == 50
+    g = dg.ASCII[pop.genome.numpy()]
+    for i in range(50):
+        p = int(pop.site_pos[pick[i]])
+        assert np.array_equal(ref[i].numpy(), g[p - 15:p + 16])
