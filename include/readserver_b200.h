@@ -324,6 +324,11 @@ void rs_shardset_destroy(rs_shardset* set);
 int rs_shardset_get_info(const rs_shardset* set, rs_shardset_info* info);
 int rs_shardset_enable_stats(rs_shardset* set, int on);
 int rs_shardset_read_stats(rs_shardset* set, uint64_t* interval_steps, uint64_t* walk_steps, int reset);
+/* Measurement aid: CUDA events around the pipeline's stages on the call's own stream.  ms[4] / launches[4] =
+ * time and kernel launches of 0 k_pack_kmers, 1 K1 (search), 2 offsets, 3 locate + sample sets, summed over the
+ * calls since the last read (which synchronises the device). */
+int rs_shardset_enable_timing(rs_shardset* set, int on);
+int rs_shardset_read_timing(rs_shardset* set, double ms[4], uint64_t launches[4]);
 int rs_pop_query_dev(rs_shardset* set, const void* d_kmers, int k, size_t Q, int packed, uint64_t max_hits,
                      void* d_counts, void* d_hit_offsets, void* d_hits, uint64_t capacity, void* d_carriers,
                      void* d_total_hits, void* stream);

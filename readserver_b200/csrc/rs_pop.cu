@@ -210,7 +210,7 @@ __global__ void k_pop_shard_counts(const uint32_t* __restrict__ cnt_s, uint64_t 
 
 /* rows[loff[q] + j] = first[q] + j,  dst[..] = hit_offsets[q] + seg[q] + j; one warp per query */
 __global__ void k_pop_expand(const uint64_t* __restrict__ first, const uint64_t* __restrict__ loff, uint64_t nq,
-                             const uint64_t* __restrict__ hit_offsets, const uint32_t* __restrict__ seg,
+                             const uint64_t* __restrict__ hit_offsets, const uint32_t* __restrict__ seg, uint64_t bound,
                              uint64_t* __restrict__ rows, uint64_t* __restrict__ dst) {
   const uint32_t lane = threadIdx.x & 31;
   const uint64_t warps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
@@ -218,7 +218,7 @@ __global__ void k_pop_expand(const uint64_t* __restrict__ first, const uint64_t*
     const uint64_t b = loff[q], e = loff[q + 1];
     if (b == e) continue;
     const uint64_t f = first[q], d0 = hit_offsets[q] + seg[q];
-    for (uint64_t j = b + lane; j < e; j += 32) {
+    for (uint64_t j = b + lane; j < e && j < bound; j += 32) { /* rows past `bound` could not be reported anyway */
       rows[j] = f + (j - b);
       dst[j] = d0 + (j - b);
     }
@@ -294,6 +294,43 @@ struct rs_shardset {
   Scratch s_packed, s_lo, s_cnt, s_seg, s_nh, s_loc, s_scan, s_base, s_rows, s_dst, s_ri, s_in, s_lcnt;
   uint64_t* d_stats = nullptr; /* executed updateInterval steps / LF steps of the set's calls (bench.py) */
   uint64_t chunk = 1u << 20;
+  /* stage timing (bench.py: which kernel a step's time goes to): events recorded on the call's stream around the
+   * stages of every chunk, read back -- and summed per stage -- by rs_shardset_read_timing */
+  bool timing = false;
+  std::vector<cudaEvent_t> ev_pool;
+  size_t ev_used = 0;
+  struct Span { int stage; size_t a, b; };
+  std::vector<Span> spans;
+  uint64_t launches[RS_POP_STAGES] = {0, 0, 0, 0};
+  size_t mark(cudaStream_t st) {
+    if (ev_used == ev_pool.size()) {
+      cudaEvent_t e;
+      if (cudaEventCreate(&e) != cudaSuccess) return (size_t)-1;
+      ev_pool.push_back(e);
+    }
+    cudaEventRecord(ev_pool[ev_used], st);
+    return ev_used++;
+  }
+};
+
+/* RAII: one timed span of a stage on the stream (no-op unless timing is on) */
+struct StageTimer {
+  rs_shardset* set;
+  cudaStream_t st;
+  int stage;
+  size_t a;
+  StageTimer(rs_shardset* s, cudaStream_t stream, int stg, uint64_t nlaunch) : set(s), st(stream), stage(stg), a((size_t)-1) {
+    if (set->timing && set->spans.size() < 100000) {
+      a = set->mark(st);
+      set->launches[stage] += nlaunch;
+    }
+  }
+  ~StageTimer() {
+    if (a != (size_t)-1) {
+      const size_t b = set->mark(st);
+      if (b != (size_t)-1) set->spans.push_back({stage, a, b});
+    }
+  }
 };
 
 int rs_shardset_create(int device, rs_shardset** out) {
@@ -353,6 +390,7 @@ void rs_shardset_destroy(rs_shardset* set) {
                     &set->s_base, &set->s_rows, &set->s_dst, &set->s_ri, &set->s_in, &set->s_lcnt};
   for (Scratch* s : all) s->release();
   if (set->d_stats) cudaFree(set->d_stats);
+  for (cudaEvent_t e : set->ev_pool) cudaEventDestroy(e);
   if (set->stream) cudaStreamDestroy(set->stream);
   delete set;
 }
@@ -530,6 +568,35 @@ int rs_shardset_read_stats(rs_shardset* set, uint64_t* interval_steps, uint64_t*
   return RS_STATUS_OK;
 }
 
+int rs_shardset_enable_timing(rs_shardset* set, int on) {
+  if (!set) return fail(RS_STATUS_ARG, "null argument");
+  std::lock_guard<std::mutex> lk(set->mu);
+  set->timing = on != 0;
+  set->spans.clear();
+  set->ev_used = 0;
+  for (int i = 0; i < RS_POP_STAGES; ++i) set->launches[i] = 0;
+  return RS_STATUS_OK;
+}
+
+int rs_shardset_read_timing(rs_shardset* set, double ms[RS_POP_STAGES], uint64_t launches[RS_POP_STAGES]) {
+  if (!set || !ms) return fail(RS_STATUS_ARG, "null argument");
+  std::lock_guard<std::mutex> lk(set->mu);
+  CU(cudaSetDevice(set->device));
+  CU(cudaDeviceSynchronize());
+  for (int i = 0; i < RS_POP_STAGES; ++i) ms[i] = 0.0;
+  for (const auto& sp : set->spans) {
+    float t = 0.f;
+    CU(cudaEventElapsedTime(&t, set->ev_pool[sp.a], set->ev_pool[sp.b]));
+    ms[sp.stage] += t;
+  }
+  if (launches)
+    for (int i = 0; i < RS_POP_STAGES; ++i) launches[i] = set->launches[i];
+  set->spans.clear();
+  set->ev_used = 0;
+  for (int i = 0; i < RS_POP_STAGES; ++i) set->launches[i] = 0;
+  return RS_STATUS_OK;
+}
+
 /* the pipeline proper; everything on `st`, no host synchronisation */
 static int pop_run(rs_shardset* set, const void* d_kmers, int k, size_t Q, int packed, uint64_t max_hits, uint64_t* d_counts,
                    uint64_t* d_hit_offsets, uint64_t* d_hits, uint64_t capacity, uint32_t* d_carriers, uint64_t* d_total,
@@ -541,6 +608,7 @@ static int pop_run(rs_shardset* set, const void* d_kmers, int k, size_t Q, int p
   const uint64_t* keys = (const uint64_t*)d_kmers;
   if (!packed) {
     CU(set->s_packed.need(Q * 8));
+    StageTimer tm(set, st, RS_POP_STAGE_PACK, 1);
     CU(rs_launch_pack_kmers((const uint8_t*)d_kmers, (uint32_t)k, Q, 0, (uint64_t*)set->s_packed.p, st));
     keys = (const uint64_t*)set->s_packed.p;
   }
@@ -562,16 +630,27 @@ static int pop_run(rs_shardset* set, const void* d_kmers, int k, size_t Q, int p
   CU(cudaMemsetAsync(base, 0, 8, st));
   for (uint64_t q0 = 0; q0 < Q; q0 += C) {
     const uint64_t nq = std::min<uint64_t>(C, Q - q0);
-    for (uint32_t s = 0; s < S; ++s)
-      CU(rs_launch_find_interval_packed(set->shards[s]->dev, keys + q0, (uint32_t)k, nq, lo + (uint64_t)s * C,
-                                        cnt + (uint64_t)s * C, 4, (unsigned long long*)set->d_stats, st));
-    k_pop_totals<<<(unsigned)((nq + 255) / 256), 256, 0, st>>>(cnt, S, C, nq, max_hits, d_counts + q0, nh, seg);
-    CU(cudaGetLastError());
-    if (!want_hits) continue;
-    CU(rs_exclusive_scan(nh, loc, nq, set->s_scan.p, scan_bytes, st));
-    k_pop_add_base<<<(unsigned)((nq + 256) / 256), 256, 0, st>>>(loc, nq, base, d_hit_offsets + q0);
-    k_pop_advance<<<1, 1, 0, st>>>(loc, nq, base, q0 + nq == Q ? d_hit_offsets + Q : nullptr, q0 + nq == Q ? d_total : nullptr);
-    CU(cudaGetLastError());
+    {
+      StageTimer tm(set, st, RS_POP_STAGE_SEARCH, S);
+      for (uint32_t s = 0; s < S; ++s)
+        CU(rs_launch_find_interval_packed(set->shards[s]->dev, keys + q0, (uint32_t)k, nq, lo + (uint64_t)s * C,
+                                          cnt + (uint64_t)s * C, 4, (unsigned long long*)set->d_stats, st));
+    }
+    {
+      StageTimer tm(set, st, RS_POP_STAGE_OFFSETS, want_hits ? 4 : 1);
+      k_pop_totals<<<(unsigned)((nq + 255) / 256), 256, 0, st>>>(cnt, S, C, nq, max_hits, d_counts + q0, nh, seg);
+      CU(cudaGetLastError());
+      if (!want_hits) continue;
+      CU(rs_exclusive_scan(nh, loc, nq, set->s_scan.p, scan_bytes, st));
+      k_pop_add_base<<<(unsigned)((nq + 256) / 256), 256, 0, st>>>(loc, nq, base, d_hit_offsets + q0);
+      k_pop_advance<<<1, 1, 0, st>>>(loc, nq, base, q0 + nq == Q ? d_hit_offsets + Q : nullptr, q0 + nq == Q ? d_total : nullptr);
+      CU(cudaGetLastError());
+    }
+    if (!capacity) { /* sizing call: offsets and total only (carrier sets need reported hits) */
+      if (d_carriers) CU(cudaMemsetAsync(d_carriers + q0 * set->words, 0, nq * (size_t)set->words * 4, st));
+      continue;
+    }
+    StageTimer tm_locate(set, st, RS_POP_STAGE_LOCATE, table ? 1 : 5 * S + 1);
     if (table) {
       k_pop_gather<<<grid_for(nq * 32, 256, 148 * 8), 256, 0, st>>>(set->tab, lo, cnt, C, nq, max_hits, d_hit_offsets + q0,
                                                                  capacity, d_hits,
@@ -597,7 +676,7 @@ static int pop_run(rs_shardset* set, const void* d_kmers, int k, size_t Q, int p
         k_pop_shard_counts<<<(unsigned)((nq + 255) / 256), 256, 0, st>>>(cnt + (uint64_t)s * C, nq, max_hits, lcnt);
         CU(rs_exclusive_scan(lcnt, loff, nq, set->s_scan.p, scan_bytes, st));
         k_pop_expand<<<grid_for(nq * 32, 256, 148 * 8), 256, 0, st>>>(lo + (uint64_t)s * C, loff, nq, d_hit_offsets + q0,
-                                                                   seg + (uint64_t)s * C, (uint64_t*)set->s_rows.p,
+                                                                   seg + (uint64_t)s * C, bound, (uint64_t*)set->s_rows.p,
                                                                    (uint64_t*)set->s_dst.p);
         CU(cudaGetLastError());
         CU(rs_launch_extract_prefix_n(ix->dev, (const uint64_t*)set->s_rows.p, loff + nq, bound, set->max_read_len, ix->d_sai,

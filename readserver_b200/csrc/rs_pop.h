@@ -9,6 +9,11 @@
 
 #define RS_POP_MAX_SHARDS 1024
 #define RS_POP_MAX_SHARD_ID 4096u
+#define RS_POP_STAGES 4
+#define RS_POP_STAGE_PACK 0    /* k_pack_kmers                                  */
+#define RS_POP_STAGE_SEARCH 1  /* K1, one launch per shard and chunk            */
+#define RS_POP_STAGE_OFFSETS 2 /* totals, scan, offsets                         */
+#define RS_POP_STAGE_LOCATE 3  /* gather from the tables / expand + walk + scatter, carrier sets */
 
 typedef struct rs_pop_tables {
   uint32_t nshards;

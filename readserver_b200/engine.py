@@ -80,6 +80,8 @@ def lib() -> C.CDLL:
         "rs_shardset_get_info": (i32, [vp, C.POINTER(ShardSetInfo)]),
         "rs_shardset_enable_stats": (i32, [vp, i32]),
         "rs_shardset_read_stats": (i32, [vp, C.POINTER(u64), C.POINTER(u64), i32]),
+        "rs_shardset_enable_timing": (i32, [vp, i32]),
+        "rs_shardset_read_timing": (i32, [vp, C.POINTER(C.c_double), C.POINTER(u64)]),
         "rs_pop_query_dev": (i32, [vp, vp, i32, sz, i32, u64, vp, vp, vp, u64, vp, vp, vp]),
         "rs_pop_query": (i32, [vp, vp, i32, sz, i32, u64, vp, vp, vp, u64, vp, C.POINTER(u64)]),
         "rs_index_close": (None, [vp]),
@@ -602,6 +604,17 @@ class ShardSet:
         a, b = C.c_uint64(), C.c_uint64()
         _check(lib().rs_shardset_read_stats(self._h, C.byref(a), C.byref(b), int(reset)))
         return int(a.value), int(b.value)
+
+    def enable_timing(self, on: bool = True):
+        _check(lib().rs_shardset_enable_timing(self._h, int(on)))
+
+    def read_timing(self):
+        """({stage: ms}, {stage: kernel launches}) since the last read; stages pack, search (K1), offsets, locate."""
+        ms = (C.c_double * 4)()
+        n = (C.c_uint64 * 4)()
+        _check(lib().rs_shardset_read_timing(self._h, ms, n))
+        names = ("pack", "search", "offsets", "locate")
+        return {k: float(v) for k, v in zip(names, ms)}, {k: int(v) for k, v in zip(names, n)}
 
     def query_dev(self, d_kmers, k: int, q: int, packed: bool, max_hits: int, d_counts, d_hit_offsets=None, d_hits=None,
                   capacity: int = 0, d_carriers=None, d_total=None, stream: int = 0):
