@@ -335,6 +335,31 @@ int rs_pop_query_dev(rs_shardset* set, const void* d_kmers, int k, size_t Q, int
 int rs_pop_query(rs_shardset* set, const void* kmers, int k, size_t Q, int packed, uint64_t max_hits, uint64_t* counts,
                  uint64_t* hit_offsets, uint64_t* hits, uint64_t capacity, uint32_t* carriers, uint64_t* total_hits);
 
+/* ---- population queries across the GPUs of one box ---------------------------------------------------------
+ * One process per GPU, each with a shard set over the shards it holds.  Every rank runs the whole batch on its set;
+ * the answers are fanned in -- by the pipeline's own kernels, through NVLink peer memory (CUDA IPC), no collective
+ * library -- to the rank that OWNS the k-mer (its first four bases as a base-4 number modulo the ranks):
+ *   counts     each rank adds its shards' count into the owner's (the front end's sum, server.cpp:184-197, 404-410)
+ *   hit lists  each rank reports its number of hits per k-mer, the owner lays the list out (rank 0's hits first,
+ *              then rank 1's, ...) and tells every rank its slot; the locate kernel then writes the read indices
+ *              straight into the owner's list (the front end's concatenation of read lists)
+ *   carriers   each rank ORs the sample set of its hit reads into the owner's bitmap
+ * rs_popcomm_create allocates this rank's result buffers (max_queries per call, hit_capacity hits);
+ * export / connect exchange the 64-byte IPC handles as for rs_comm.  rs_pop_query_comm_dev is asynchronous on
+ * `stream`; all ranks must call it with the same batch and arguments.  The results stay in the communicator's
+ * buffers until its next call: rs_popcomm_results gives their device addresses (layouts as rs_pop_query_dev;
+ * entries of k-mers owned by other ranks are 0 / empty).  Carrier sets across GPUs need <= 128 samples. */
+typedef struct rs_popcomm rs_popcomm;
+int rs_popcomm_create(int device, int rank, int world, uint64_t max_queries, uint64_t hit_capacity, rs_popcomm** out);
+int rs_popcomm_export(rs_popcomm* c, uint8_t handle[64]);
+int rs_popcomm_connect(rs_popcomm* c, const uint8_t* handles);
+void rs_popcomm_destroy(rs_popcomm* c);
+int rs_pop_query_comm_dev(rs_shardset* set, rs_popcomm* comm, const void* d_kmers, int k, size_t Q, int packed,
+                          uint64_t max_hits, int want_hits, int want_carriers, void* stream);
+int rs_popcomm_results(rs_popcomm* c, void** d_counts, void** d_hit_offsets, void** d_hits, void** d_carriers,
+                       void** d_total_hits, uint64_t* hit_capacity);
+int rs_popcomm_error(rs_popcomm* c, int* timed_out);
+
 /* ---- fan-in of per-shard counts across the GPUs of one box ----------------------------------------
  * Replaces the front end's sum over shard replies (src/service/server.cpp:184-197, 404-410).  One
  * process per GPU; every rank searches the whole batch in its shards and each finished query's count

@@ -156,16 +156,70 @@ __device__ __noinline__ uint64_t rs_pop_walk_one(const rs_index_dev* __restrict_
   return ~0ull;
 }
 
+/* rank owning the reduced result of a packed k-mer: its first four bases as a base-4 number modulo the ranks
+ * (sharding.owner_of; same rule as K1's fused count reduction, rs_kernels.cu) */
+__device__ __forceinline__ uint32_t rs_owner_of(uint64_t pk, uint32_t k, bool, uint32_t world) {
+  const uint32_t prefix = k >= 4 ? (uint32_t)(pk >> (2 * (k - 4))) & 0xFFu : (uint32_t)pk & 0xFFu;
+  return prefix % world;
+}
+
+/* multi-GPU: per query of the chunk, this rank's count is added into the owner's population count and its number of
+ * hits stored into the owner's per-rank table -- both straight into the owner's memory over NVLink */
+__global__ void k_pop_totals_comm(const __grid_constant__ rs_pop_peers P, const uint64_t* __restrict__ keys, uint32_t k,
+                                  const uint32_t* __restrict__ cnt, uint32_t S, uint64_t C, uint64_t q0, uint64_t nq,
+                                  uint64_t max_hits, int want_hits) {
+  const uint64_t q = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= nq) return;
+  uint64_t tot = 0, h = 0;
+  for (uint32_t s = 0; s < S; ++s) {
+    const uint64_t c = cnt[(uint64_t)s * C + q];
+    tot += c;
+    h += c < max_hits ? c : max_hits;
+  }
+  const uint32_t owner = rs_owner_of(keys[q], k, false, P.world);
+  if (tot) atomicAdd(reinterpret_cast<unsigned long long*>(P.counts[owner]) + q0 + q, (unsigned long long)tot);
+  if (want_hits) P.rankh[owner][(uint64_t)P.rank * P.maxq + q0 + q] = h > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)h;
+}
+
+/* owner: hits of each query it owns, summed over the source ranks (0 for the queries of other owners) */
+__global__ void k_pop_owner_hits(const __grid_constant__ rs_pop_peers P, const uint64_t* __restrict__ keys, uint32_t k,
+                                 uint64_t q0, uint64_t nq, uint64_t* __restrict__ nhits) {
+  const uint64_t q = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= nq) return;
+  uint64_t h = 0;
+  if (rs_owner_of(keys[q], k, false, P.world) == P.rank)
+    for (uint32_t r = 0; r < P.world; ++r) h += P.rankh[P.rank][(uint64_t)r * P.maxq + q0 + q];
+  nhits[q] = h;
+}
+
+/* owner: tells every source rank where its hits of each owned query go (rank 0's first, then rank 1's, ...) */
+__global__ void k_pop_owner_slots(const __grid_constant__ rs_pop_peers P, const uint64_t* __restrict__ keys, uint32_t k,
+                                  uint64_t q0, uint64_t nq, const uint64_t* __restrict__ hit_offsets) {
+  const uint64_t q = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= nq) return;
+  if (rs_owner_of(keys[q], k, false, P.world) != P.rank) return;
+  uint64_t run = hit_offsets[q0 + q];
+  for (uint32_t r = 0; r < P.world; ++r) {
+    P.slot[r][q0 + q] = run;
+    run += P.rankh[P.rank][(uint64_t)r * P.maxq + q0 + q];
+  }
+}
+
 /* One warp per query: its hits shard after shard, rows in order, straight from the read-index tables; the union of
- * the hit reads' sample sets when `carriers` is given (W = 4 words of 32 samples). */
+ * the hit reads' sample sets when carrier sets are wanted (W = 4 words of 32 samples).  The hits go to the rank that
+ * owns the query (P.world > 1: over NVLink peer memory, at the slot the owner assigned to this rank -- locate and the
+ * fan-in of the hit lists, server.cpp:184-197, are one kernel), the sample set is OR-ed into the owner's bitmap. */
 __global__ void __launch_bounds__(256)
-    k_pop_gather(const __grid_constant__ rs_pop_tables T, const uint64_t* __restrict__ lo, const uint32_t* __restrict__ cnt,
-                 uint64_t C, uint64_t nq, uint64_t max_hits, const uint64_t* __restrict__ hit_offsets, uint64_t capacity,
-                 uint64_t* __restrict__ hits, uint32_t* __restrict__ carriers) {
+    k_pop_gather(const __grid_constant__ rs_pop_tables T, const __grid_constant__ rs_pop_peers P,
+                 const uint64_t* __restrict__ keys, uint32_t k, const uint64_t* __restrict__ lo,
+                 const uint32_t* __restrict__ cnt, uint64_t C, uint64_t q0, uint64_t nq, uint64_t max_hits,
+                 const uint64_t* __restrict__ slot, uint64_t capacity, int want_carriers) {
   const uint32_t lane = threadIdx.x & 31;
   const uint64_t warps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
   for (uint64_t q = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; q < nq; q += warps) {
-    uint64_t off = hit_offsets[q];
+    const uint32_t owner = P.world > 1 ? rs_owner_of(keys[q], k, false, P.world) : 0u;
+    uint64_t* __restrict__ hits = P.hits[owner];
+    uint64_t off = slot[q0 + q];
     uint32_t b0 = 0, b1 = 0, b2 = 0, b3 = 0;
     for (uint32_t s = 0; s < T.nshards; ++s) {
       uint64_t c = cnt[(uint64_t)s * C + q];
@@ -179,7 +233,7 @@ __global__ void __launch_bounds__(256)
         uint64_t r = rid[first + j];
         if (r == RS_RID_NONE) r = rs_pop_walk_one(T.views, s, T.sai, first + j, T.max_steps);
         if (off + j < capacity) hits[off + j] = r == ~0ull ? ~0ull : (tag | r);
-        if (carriers && sets && r != ~0ull) {
+        if (want_carriers && sets && r != ~0ull) {
           const uint4 v = __ldg(sets + r);
           b0 |= v.x;
           b1 |= v.y;
@@ -189,12 +243,18 @@ __global__ void __launch_bounds__(256)
       }
       off += c;
     }
-    if (carriers) {
+    if (want_carriers) {
       b0 = __reduce_or_sync(RS_FULL, b0);
       b1 = __reduce_or_sync(RS_FULL, b1);
       b2 = __reduce_or_sync(RS_FULL, b2);
       b3 = __reduce_or_sync(RS_FULL, b3);
-      if (lane == 0) reinterpret_cast<uint4*>(carriers)[q] = make_uint4(b0, b1, b2, b3);
+      uint32_t* dst = P.carr[owner] + (q0 + q) * 4;
+      if (P.world == 1) {
+        if (lane == 0) *reinterpret_cast<uint4*>(dst) = make_uint4(b0, b1, b2, b3);
+      } else if (lane < 4) { /* several ranks contribute to one bitmap (cleared by its owner before the step) */
+        const uint32_t v = lane == 0 ? b0 : lane == 1 ? b1 : lane == 2 ? b2 : b3;
+        if (v) atomicOr(dst + lane, v);
+      }
     }
   }
 }
@@ -208,32 +268,36 @@ __global__ void k_pop_shard_counts(const uint32_t* __restrict__ cnt_s, uint64_t 
   out[q] = c < max_hits ? c : max_hits;
 }
 
-/* rows[loff[q] + j] = first[q] + j,  dst[..] = hit_offsets[q] + seg[q] + j; one warp per query */
-__global__ void k_pop_expand(const uint64_t* __restrict__ first, const uint64_t* __restrict__ loff, uint64_t nq,
-                             const uint64_t* __restrict__ hit_offsets, const uint32_t* __restrict__ seg, uint64_t bound,
-                             uint64_t* __restrict__ rows, uint64_t* __restrict__ dst) {
+/* rows[loff[q] + j] = first[q] + j,  dst[..] = ADDRESS of the hit's slot in the owner's list (0: beyond its capacity);
+ * one warp per query */
+__global__ void k_pop_expand(const __grid_constant__ rs_pop_peers P, const uint64_t* __restrict__ keys, uint32_t k,
+                             const uint64_t* __restrict__ first, const uint64_t* __restrict__ loff, uint64_t q0, uint64_t nq,
+                             const uint64_t* __restrict__ slot, const uint32_t* __restrict__ seg, uint64_t bound,
+                             uint64_t capacity, uint64_t* __restrict__ rows, uint64_t* __restrict__ dst) {
   const uint32_t lane = threadIdx.x & 31;
   const uint64_t warps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
   for (uint64_t q = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; q < nq; q += warps) {
     const uint64_t b = loff[q], e = loff[q + 1];
     if (b == e) continue;
-    const uint64_t f = first[q], d0 = hit_offsets[q] + seg[q];
+    const uint32_t owner = P.world > 1 ? rs_owner_of(keys[q], k, false, P.world) : 0u;
+    const uint64_t f = first[q], d0 = slot[q0 + q] + seg[q];
     for (uint64_t j = b + lane; j < e && j < bound; j += 32) { /* rows past `bound` could not be reported anyway */
       rows[j] = f + (j - b);
-      dst[j] = d0 + (j - b);
+      const uint64_t d = d0 + (j - b);
+      dst[j] = d < capacity ? (uint64_t)(uintptr_t)(P.hits[owner] + d) : 0ull;
     }
   }
 }
 
-/* hits[dst[i]] = tag | read_index[i]; n read from the device (the shard's hit count of this chunk) */
+/* *dst[i] = tag | read_index[i]; n read from the device (the shard's hit count of this chunk) */
 __global__ void k_pop_scatter(const uint64_t* __restrict__ read_index, const uint64_t* __restrict__ dst,
-                              const uint64_t* __restrict__ n_dev, uint64_t tag, uint64_t capacity,
-                              uint64_t* __restrict__ hits) {
-  const uint64_t n = *n_dev;
+                              const uint64_t* __restrict__ n_dev, uint64_t bound, uint64_t tag) {
+  const uint64_t n = *n_dev < bound ? *n_dev : bound;
   const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
   for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
-    const uint64_t r = read_index[i], d = dst[i];
-    if (d < capacity) hits[d] = r == ~0ull ? ~0ull : (tag | r);
+    const uint64_t r = read_index[i];
+    uint64_t* d = reinterpret_cast<uint64_t*>((uintptr_t)dst[i]);
+    if (d) *d = r == ~0ull ? ~0ull : (tag | r);
   }
 }
 
@@ -242,6 +306,7 @@ __global__ void k_pop_scatter(const uint64_t* __restrict__ read_index, const uin
 __global__ void __launch_bounds__(256)
     k_pop_carriers(const __grid_constant__ rs_pop_tables T, const uint64_t* __restrict__ hit_offsets, uint64_t nq,
                    const uint64_t* __restrict__ hits, uint64_t capacity, uint32_t words, uint32_t* __restrict__ carriers) {
+  /* single-GPU sets only: the sample tables of a hit's shard must be resident on the rank that holds the hit list */
   extern __shared__ uint32_t smem[];
   const uint32_t lane = threadIdx.x & 31, wib = threadIdx.x >> 5;
   uint32_t* bm = smem + wib * words;
@@ -597,14 +662,156 @@ int rs_shardset_read_timing(rs_shardset* set, double ms[RS_POP_STAGES], uint64_t
   return RS_STATUS_OK;
 }
 
+/* ---- several GPUs: one process per GPU, results fanned in to the query's owner through peer memory ---- */
+#define RS_POPCOMM_HDR 256
+struct rs_popcomm {
+  int device = 0;
+  uint32_t rank = 0, world = 1;
+  uint64_t maxq = 0, cap = 0;
+  uint8_t* base = nullptr;
+  uint8_t* peer_base[RS_MAX_RANKS] = {};
+  uint64_t** d_peer_flags = nullptr;
+  uint64_t epoch = 0;
+  bool connected = false, ipc = false;
+  size_t o_counts = 0, o_rankh = 0, o_slot = 0, o_off = 0, o_carr = 0, o_total = 0, o_hits = 0, bytes = 0;
+  rs_pop_peers peers;
+};
+
+int rs_popcomm_create(int device, int rank, int world, uint64_t max_queries, uint64_t hit_capacity, rs_popcomm** out) {
+  if (!out || rank < 0 || world < 1 || rank >= world || world > RS_MAX_RANKS || max_queries == 0)
+    return fail(RS_STATUS_ARG, "bad argument");
+  *out = nullptr;
+  CU(cudaSetDevice(device));
+  rs_popcomm* c = new rs_popcomm;
+  c->device = device;
+  c->rank = (uint32_t)rank;
+  c->world = (uint32_t)world;
+  c->maxq = max_queries;
+  c->cap = hit_capacity;
+  size_t o = RS_POPCOMM_HDR;
+  auto take = [&](size_t nbytes) {
+    const size_t at = o;
+    o = (o + nbytes + 255) / 256 * 256;
+    return at;
+  };
+  c->o_counts = take(max_queries * 8);
+  c->o_rankh = take((size_t)world * max_queries * 4);
+  c->o_slot = take(max_queries * 8);
+  c->o_off = take((max_queries + 1) * 8);
+  c->o_carr = take(max_queries * 16);
+  c->o_total = take(8);
+  c->o_hits = take((hit_capacity ? hit_capacity : 1) * 8);
+  c->bytes = o;
+  cudaError_t e = cudaMalloc((void**)&c->base, c->bytes);
+  if (e == cudaSuccess) e = cudaMemset(c->base, 0, c->o_hits); /* everything but the hit list */
+  if (e == cudaSuccess) e = cudaMalloc((void**)&c->d_peer_flags, RS_MAX_RANKS * sizeof(uint64_t*));
+  if (e == cudaSuccess) e = cudaDeviceSynchronize();
+  if (e != cudaSuccess) {
+    if (c->base) cudaFree(c->base);
+    delete c;
+    return fail(RS_STATUS_CUDA, "rs_popcomm_create: %s", cudaGetErrorString(e));
+  }
+  c->peer_base[rank] = c->base;
+  *out = c;
+  return RS_STATUS_OK;
+}
+
+int rs_popcomm_export(rs_popcomm* c, uint8_t handle[RS_COMM_HANDLE_BYTES]) {
+  if (!c || !handle) return fail(RS_STATUS_ARG, "null argument");
+  CU(cudaSetDevice(c->device));
+  cudaIpcMemHandle_t h;
+  CU(cudaIpcGetMemHandle(&h, c->base));
+  memcpy(handle, &h, sizeof(h));
+  return RS_STATUS_OK;
+}
+
+static int comm_finish_connect(rs_popcomm* c);
+
+int rs_popcomm_connect(rs_popcomm* c, const uint8_t* handles) {
+  if (!c || (!handles && c->world > 1)) return fail(RS_STATUS_ARG, "null argument");
+  if (c->connected) return fail(RS_STATUS_ARG, "already connected");
+  CU(cudaSetDevice(c->device));
+  for (uint32_t r = 0; r < c->world; ++r) {
+    if (r == c->rank) continue;
+    cudaIpcMemHandle_t h;
+    memcpy(&h, handles + (size_t)r * RS_COMM_HANDLE_BYTES, sizeof(h));
+    void* p = nullptr;
+    CU(cudaIpcOpenMemHandle(&p, h, cudaIpcMemLazyEnablePeerAccess));
+    c->peer_base[r] = (uint8_t*)p;
+  }
+  c->ipc = true;
+  return comm_finish_connect(c);
+}
+
+static int comm_finish_connect(rs_popcomm* c) {
+  CU(cudaSetDevice(c->device));
+  uint64_t* flags[RS_MAX_RANKS] = {};
+  memset(&c->peers, 0, sizeof(c->peers));
+  c->peers.world = c->world;
+  c->peers.rank = c->rank;
+  c->peers.maxq = c->maxq;
+  for (uint32_t r = 0; r < c->world; ++r) {
+    uint8_t* b = c->peer_base[r];
+    flags[r] = reinterpret_cast<uint64_t*>(b);
+    c->peers.counts[r] = reinterpret_cast<uint64_t*>(b + c->o_counts);
+    c->peers.rankh[r] = reinterpret_cast<uint32_t*>(b + c->o_rankh);
+    c->peers.slot[r] = reinterpret_cast<uint64_t*>(b + c->o_slot);
+    c->peers.hits[r] = reinterpret_cast<uint64_t*>(b + c->o_hits);
+    c->peers.carr[r] = reinterpret_cast<uint32_t*>(b + c->o_carr);
+  }
+  CU(cudaMemcpy(c->d_peer_flags, flags, sizeof(flags), cudaMemcpyHostToDevice));
+  c->connected = true;
+  return RS_STATUS_OK;
+}
+
+void rs_popcomm_destroy(rs_popcomm* c) {
+  if (!c) return;
+  cudaSetDevice(c->device);
+  cudaDeviceSynchronize();
+  for (uint32_t r = 0; r < c->world; ++r)
+    if (c->ipc && r != c->rank && c->peer_base[r]) cudaIpcCloseMemHandle(c->peer_base[r]);
+  if (c->d_peer_flags) cudaFree(c->d_peer_flags);
+  if (c->base) cudaFree(c->base);
+  delete c;
+}
+
+int rs_popcomm_results(rs_popcomm* c, void** d_counts, void** d_hit_offsets, void** d_hits, void** d_carriers,
+                       void** d_total_hits, uint64_t* hit_capacity) {
+  if (!c) return fail(RS_STATUS_ARG, "null argument");
+  if (d_counts) *d_counts = c->base + c->o_counts;
+  if (d_hit_offsets) *d_hit_offsets = c->base + c->o_off;
+  if (d_hits) *d_hits = c->base + c->o_hits;
+  if (d_carriers) *d_carriers = c->base + c->o_carr;
+  if (d_total_hits) *d_total_hits = c->base + c->o_total;
+  if (hit_capacity) *hit_capacity = c->cap;
+  return RS_STATUS_OK;
+}
+
+int rs_popcomm_error(rs_popcomm* c, int* timed_out) {
+  if (!c || !timed_out) return fail(RS_STATUS_ARG, "null argument");
+  CU(cudaSetDevice(c->device));
+  uint32_t v = 0;
+  CU(cudaMemcpy(&v, c->base + RS_MAX_RANKS * sizeof(uint64_t), sizeof(v), cudaMemcpyDeviceToHost));
+  *timed_out = (int)v;
+  return RS_STATUS_OK;
+}
+
+static int comm_barrier(rs_popcomm* c, cudaStream_t st) {
+  ++c->epoch;
+  uint32_t* err = reinterpret_cast<uint32_t*>(c->base + RS_MAX_RANKS * sizeof(uint64_t));
+  CU(rs_launch_peer_barrier(c->d_peer_flags, c->world, c->rank, c->epoch, 5000, err, st));
+  return RS_STATUS_OK;
+}
+
 /* the pipeline proper; everything on `st`, no host synchronisation */
-static int pop_run(rs_shardset* set, const void* d_kmers, int k, size_t Q, int packed, uint64_t max_hits, uint64_t* d_counts,
-                   uint64_t* d_hit_offsets, uint64_t* d_hits, uint64_t capacity, uint32_t* d_carriers, uint64_t* d_total,
-                   cudaStream_t st) {
+static int pop_run(rs_shardset* set, rs_popcomm* comm, const void* d_kmers, int k, size_t Q, int packed, uint64_t max_hits,
+                   uint64_t* d_counts, uint64_t* d_hit_offsets, uint64_t* d_hits, uint64_t capacity, uint32_t* d_carriers,
+                   uint64_t* d_total, cudaStream_t st) {
   const uint32_t S = (uint32_t)set->shards.size();
   const uint64_t C = std::min<uint64_t>(set->chunk, Q);
   const bool want_hits = d_hit_offsets != nullptr;
   const bool table = set->locate_every == 1;
+  const bool multi = comm != nullptr && comm->world > 1;
   const uint64_t* keys = (const uint64_t*)d_kmers;
   if (!packed) {
     CU(set->s_packed.need(Q * 8));
@@ -627,9 +834,31 @@ static int pop_run(rs_shardset* set, const void* d_kmers, int k, size_t Q, int p
   uint64_t* loc = (uint64_t*)set->s_loc.p;
   uint64_t* base = (uint64_t*)set->s_base.p;
   uint32_t* seg = (want_hits && !table) ? (uint32_t*)set->s_seg.p : nullptr;
+  /* where results go: own buffers (one GPU) or every rank's, through peer memory */
+  rs_pop_peers P;
+  if (multi) {
+    P = comm->peers;
+  } else {
+    memset(&P, 0, sizeof(P));
+    P.world = 1;
+    P.maxq = Q;
+    P.counts[0] = d_counts;
+    P.hits[0] = d_hits;
+    P.carr[0] = d_carriers;
+    P.slot[0] = d_hit_offsets; /* a query's hits start at its CSR offset */
+  }
+  const int want_carr = d_carriers != nullptr;
   CU(cudaMemsetAsync(base, 0, 8, st));
+  if (multi) {
+    /* own accumulation buffers cleared, then a barrier: no peer adds into them earlier */
+    CU(cudaMemsetAsync(d_counts, 0, Q * 8, st));
+    if (want_carr) CU(cudaMemsetAsync(d_carriers, 0, Q * 16, st));
+    const int rc = comm_barrier(comm, st);
+    if (rc != RS_STATUS_OK) return rc;
+  }
   for (uint64_t q0 = 0; q0 < Q; q0 += C) {
     const uint64_t nq = std::min<uint64_t>(C, Q - q0);
+    const unsigned gq = (unsigned)((nq + 255) / 256);
     {
       StageTimer tm(set, st, RS_POP_STAGE_SEARCH, S);
       for (uint32_t s = 0; s < S; ++s)
@@ -638,25 +867,41 @@ static int pop_run(rs_shardset* set, const void* d_kmers, int k, size_t Q, int p
     }
     {
       StageTimer tm(set, st, RS_POP_STAGE_OFFSETS, want_hits ? 4 : 1);
-      k_pop_totals<<<(unsigned)((nq + 255) / 256), 256, 0, st>>>(cnt, S, C, nq, max_hits, d_counts + q0, nh, seg);
+      if (!multi) {
+        k_pop_totals<<<gq, 256, 0, st>>>(cnt, S, C, nq, max_hits, d_counts + q0, nh, seg);
+      } else {
+        if (seg) k_pop_totals<<<gq, 256, 0, st>>>(cnt, S, C, nq, max_hits, loc /* unused sums */, nh, seg);
+        k_pop_totals_comm<<<gq, 256, 0, st>>>(P, keys + q0, (uint32_t)k, cnt, S, C, q0, nq, max_hits, want_hits ? 1 : 0);
+      }
       CU(cudaGetLastError());
       if (!want_hits) continue;
+      if (multi) {
+        int rc = comm_barrier(comm, st); /* every rank's hit numbers of this chunk have arrived */
+        if (rc != RS_STATUS_OK) return rc;
+        k_pop_owner_hits<<<gq, 256, 0, st>>>(P, keys + q0, (uint32_t)k, q0, nq, nh);
+      }
       CU(rs_exclusive_scan(nh, loc, nq, set->s_scan.p, scan_bytes, st));
       k_pop_add_base<<<(unsigned)((nq + 256) / 256), 256, 0, st>>>(loc, nq, base, d_hit_offsets + q0);
       k_pop_advance<<<1, 1, 0, st>>>(loc, nq, base, q0 + nq == Q ? d_hit_offsets + Q : nullptr, q0 + nq == Q ? d_total : nullptr);
       CU(cudaGetLastError());
+      if (multi) {
+        k_pop_owner_slots<<<gq, 256, 0, st>>>(P, keys + q0, (uint32_t)k, q0, nq, d_hit_offsets);
+        CU(cudaGetLastError());
+        const int rc = comm_barrier(comm, st); /* every owner's slots have arrived */
+        if (rc != RS_STATUS_OK) return rc;
+      }
     }
     if (!capacity) { /* sizing call: offsets and total only (carrier sets need reported hits) */
-      if (d_carriers) CU(cudaMemsetAsync(d_carriers + q0 * set->words, 0, nq * (size_t)set->words * 4, st));
+      if (d_carriers && !multi) CU(cudaMemsetAsync(d_carriers + q0 * set->words, 0, nq * (size_t)set->words * 4, st));
       continue;
     }
+    const uint64_t* slot = P.slot[multi ? comm->rank : 0];
     StageTimer tm_locate(set, st, RS_POP_STAGE_LOCATE, table ? 1 : 5 * S + 1);
     if (table) {
-      k_pop_gather<<<grid_for(nq * 32, 256, 148 * 8), 256, 0, st>>>(set->tab, lo, cnt, C, nq, max_hits, d_hit_offsets + q0,
-                                                                 capacity, d_hits,
-                                                                 (d_carriers && set->have_sets) ? d_carriers + q0 * set->words : nullptr);
+      k_pop_gather<<<grid_for(nq * 32, 256, 148 * 8), 256, 0, st>>>(set->tab, P, keys + q0, (uint32_t)k, lo, cnt, C, q0, nq, max_hits,
+                                                                 slot, capacity, (want_carr && set->have_sets) ? 1 : 0);
       CU(cudaGetLastError());
-      if (d_carriers && !set->have_sets && set->have_samples) {
+      if (want_carr && !set->have_sets) {
         k_pop_carriers<<<grid_for(nq * 32, 256, 148 * 8), 256, 8 * set->words * 4, st>>>(set->tab, d_hit_offsets + q0, nq, d_hits, capacity,
                                                                                       set->words, d_carriers + q0 * set->words);
         CU(cudaGetLastError());
@@ -673,19 +918,19 @@ static int pop_run(rs_shardset* set, const void* d_kmers, int k, size_t Q, int p
       CU(set->s_ri.need((bound ? bound : 1) * 8));
       for (uint32_t s = 0; s < S; ++s) {
         rs_index* ix = set->shards[s];
-        k_pop_shard_counts<<<(unsigned)((nq + 255) / 256), 256, 0, st>>>(cnt + (uint64_t)s * C, nq, max_hits, lcnt);
+        k_pop_shard_counts<<<gq, 256, 0, st>>>(cnt + (uint64_t)s * C, nq, max_hits, lcnt);
         CU(rs_exclusive_scan(lcnt, loff, nq, set->s_scan.p, scan_bytes, st));
-        k_pop_expand<<<grid_for(nq * 32, 256, 148 * 8), 256, 0, st>>>(lo + (uint64_t)s * C, loff, nq, d_hit_offsets + q0,
-                                                                   seg + (uint64_t)s * C, bound, (uint64_t*)set->s_rows.p,
-                                                                   (uint64_t*)set->s_dst.p);
+        k_pop_expand<<<grid_for(nq * 32, 256, 148 * 8), 256, 0, st>>>(P, keys + q0, (uint32_t)k, lo + (uint64_t)s * C, loff, q0, nq, slot,
+                                                                   seg + (uint64_t)s * C, bound, capacity,
+                                                                   (uint64_t*)set->s_rows.p, (uint64_t*)set->s_dst.p);
         CU(cudaGetLastError());
         CU(rs_launch_extract_prefix_n(ix->dev, (const uint64_t*)set->s_rows.p, loff + nq, bound, set->max_read_len, ix->d_sai,
                                       (uint64_t*)set->s_ri.p, (unsigned long long*)set->d_stats, st));
-        k_pop_scatter<<<148 * 8, 256, 0, st>>>((const uint64_t*)set->s_ri.p, (const uint64_t*)set->s_dst.p, loff + nq,
-                                              (uint64_t)set->shard_ids[s] << 40, capacity, d_hits);
+        k_pop_scatter<<<148 * 8, 256, 0, st>>>((const uint64_t*)set->s_ri.p, (const uint64_t*)set->s_dst.p, loff + nq, bound,
+                                              (uint64_t)set->shard_ids[s] << 40);
         CU(cudaGetLastError());
       }
-      if (d_carriers && set->have_samples) {
+      if (want_carr) {
         k_pop_carriers<<<grid_for(nq * 32, 256, 148 * 8), 256, 8 * set->words * 4, st>>>(set->tab, d_hit_offsets + q0, nq, d_hits, capacity,
                                                                                       set->words, d_carriers + q0 * set->words);
         CU(cudaGetLastError());
@@ -693,7 +938,34 @@ static int pop_run(rs_shardset* set, const void* d_kmers, int k, size_t Q, int p
     }
   }
   if (!want_hits && d_total) CU(cudaMemsetAsync(d_total, 0, 8, st));
+  if (multi) {
+    const int rc = comm_barrier(comm, st); /* every rank's adds, hits and bitmaps have landed */
+    if (rc != RS_STATUS_OK) return rc;
+  }
   return RS_STATUS_OK;
+}
+
+/* Several GPUs: every rank calls this with the same batch on its own shard set; the answers of the k-mers a rank owns
+ * (first four bases modulo the ranks) end up in that rank's communicator buffers (rs_popcomm_results). */
+int rs_pop_query_comm_dev(rs_shardset* set, rs_popcomm* comm, const void* d_kmers, int k, size_t Q, int packed,
+                          uint64_t max_hits, int want_hits, int want_carriers, void* stream) {
+  if (!set || !comm || (Q && !d_kmers)) return fail(RS_STATUS_ARG, "null argument");
+  if (!set->sealed) return fail(RS_STATUS_ARG, "shard set is not sealed");
+  if (!comm->connected) return fail(RS_STATUS_ARG, "communicator not connected");
+  if (set->device != comm->device) return fail(RS_STATUS_ARG, "shard set and communicator live on different devices");
+  if (k < 1 || k > 31) return fail(RS_STATUS_ARG, "population queries are fixed-length k-mers of 1..31 characters");
+  if (Q > comm->maxq) return fail(RS_STATUS_ARG, "batch larger than the communicator's capacity");
+  if (want_carriers && !want_hits) return fail(RS_STATUS_ARG, "carrier sets need the hit list");
+  if (want_carriers && comm->world > 1 && !set->have_sets)
+    return fail(RS_STATUS_NO_TABLE, "carrier sets across GPUs need the per-read sample-set tables (<= 128 samples, locate_every = 1)");
+  if (want_carriers && !set->have_samples) return fail(RS_STATUS_NO_TABLE, "carrier sets requested but a shard has no sample table");
+  if (want_carriers && set->words != 4) return fail(RS_STATUS_TOO_LARGE, "the communicator holds 128-sample carrier sets");
+  std::lock_guard<std::mutex> lk(set->mu);
+  CU(cudaSetDevice(set->device));
+  uint8_t* b = comm->base;
+  return pop_run(set, comm, d_kmers, k, Q, packed, max_hits, (uint64_t*)(b + comm->o_counts),
+                 want_hits ? (uint64_t*)(b + comm->o_off) : nullptr, (uint64_t*)(b + comm->o_hits), want_hits ? comm->cap : 0,
+                 want_carriers ? (uint32_t*)(b + comm->o_carr) : nullptr, (uint64_t*)(b + comm->o_total), (cudaStream_t)stream);
 }
 
 static int pop_check(rs_shardset* set, const void* kmers, int k, size_t Q, const void* counts, const void* hit_offsets,
@@ -719,7 +991,7 @@ int rs_pop_query_dev(rs_shardset* set, const void* d_kmers, int k, size_t Q, int
     if (d_total_hits) CU(cudaMemsetAsync(d_total_hits, 0, 8, (cudaStream_t)stream));
     return RS_STATUS_OK;
   }
-  return pop_run(set, d_kmers, k, Q, packed, max_hits, (uint64_t*)d_counts, (uint64_t*)d_hit_offsets, (uint64_t*)d_hits,
+  return pop_run(set, nullptr, d_kmers, k, Q, packed, max_hits, (uint64_t*)d_counts, (uint64_t*)d_hit_offsets, (uint64_t*)d_hits,
                  capacity, (uint32_t*)d_carriers, (uint64_t*)d_total_hits, (cudaStream_t)stream);
 }
 
@@ -749,7 +1021,7 @@ int rs_pop_query(rs_shardset* set, const void* kmers, int k, size_t Q, int packe
     if (carriers) CU(tmp.get((void**)&d_carr, Q * (size_t)set->words * 4));
   }
   CU(cudaMemcpyAsync(set->s_in.p, kmers, in_bytes, cudaMemcpyHostToDevice, st));
-  const int prc = pop_run(set, set->s_in.p, k, Q, packed, max_hits, d_counts, d_off, d_hits, capacity, d_carr, d_total, st);
+  const int prc = pop_run(set, nullptr, set->s_in.p, k, Q, packed, max_hits, d_counts, d_off, d_hits, capacity, d_carr, d_total, st);
   if (prc != RS_STATUS_OK) {
     cudaStreamSynchronize(st);
     return prc;

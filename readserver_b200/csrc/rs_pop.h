@@ -29,4 +29,20 @@ typedef struct rs_pop_tables {
   const rs_index_dev* views;           /* [nshards] kernel views (for the rare rows the tables do not cover) */
 } rs_pop_tables;
 
+
+/* Where the results of a step go.  One GPU: this process's own buffers.  Several GPUs (one process each, rs_popcomm):
+ * every rank's buffers as mapped into this process through CUDA IPC (NVLink peer memory), indexed by rank. */
+#ifndef RS_MAX_RANKS
+#define RS_MAX_RANKS 16
+#endif
+typedef struct rs_pop_peers {
+  uint32_t world, rank;
+  uint64_t maxq;                    /* row stride of rankh                                                     */
+  uint64_t* counts[RS_MAX_RANKS];   /* [maxq] population counts: the owner's entries are the sums               */
+  uint32_t* rankh[RS_MAX_RANKS];    /* [world][maxq] hits per query and source rank, written by the sources     */
+  uint64_t* slot[RS_MAX_RANKS];     /* [maxq] where THAT rank's hits of a query start in the owner's hit list   */
+  uint64_t* hits[RS_MAX_RANKS];     /* hit lists                                                                */
+  uint32_t* carr[RS_MAX_RANKS];     /* [maxq x 4] carrier bitmaps                                               */
+} rs_pop_peers;
+
 #endif

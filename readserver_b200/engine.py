@@ -82,6 +82,13 @@ def lib() -> C.CDLL:
         "rs_shardset_read_stats": (i32, [vp, C.POINTER(u64), C.POINTER(u64), i32]),
         "rs_shardset_enable_timing": (i32, [vp, i32]),
         "rs_shardset_read_timing": (i32, [vp, C.POINTER(C.c_double), C.POINTER(u64)]),
+        "rs_popcomm_create": (i32, [i32, i32, i32, u64, u64, C.POINTER(vp)]),
+        "rs_popcomm_export": (i32, [vp, vp]),
+        "rs_popcomm_connect": (i32, [vp, vp]),
+        "rs_popcomm_destroy": (None, [vp]),
+        "rs_pop_query_comm_dev": (i32, [vp, vp, vp, i32, sz, i32, u64, i32, i32, vp]),
+        "rs_popcomm_results": (i32, [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(u64)]),
+        "rs_popcomm_error": (i32, [vp, C.POINTER(i32)]),
         "rs_pop_query_dev": (i32, [vp, vp, i32, sz, i32, u64, vp, vp, vp, u64, vp, vp, vp]),
         "rs_pop_query": (i32, [vp, vp, i32, sz, i32, u64, vp, vp, vp, u64, vp, C.POINTER(u64)]),
         "rs_index_close": (None, [vp]),
@@ -663,6 +670,69 @@ class ShardSet:
             lib().rs_shardset_destroy(self._h)
             self._h = None
         self._keep = []
+
+    __del__ = close
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+
+class PopComm:
+    """Result buffers of one rank for population queries across the GPUs of a box (rs_popcomm_* of the C ABI): counts,
+    hit lists and carrier sets are fanned in to the k-mer's owner through NVLink peer memory by the pipeline's own
+    kernels (the front end's sum / concatenation over shard replies, src/service/server.cpp:184-197, 404-410)."""
+    HANDLE_BYTES = 64
+
+    def __init__(self, device: int, rank: int, world: int, max_queries: int, hit_capacity: int):
+        self._h = C.c_void_p()
+        self.device, self.rank, self.world = device, rank, world
+        self.max_queries, self.hit_capacity = max_queries, hit_capacity
+        _check(lib().rs_popcomm_create(device, rank, world, max_queries, hit_capacity, C.byref(self._h)))
+
+    def export(self) -> np.ndarray:
+        h = np.zeros(self.HANDLE_BYTES, dtype=np.uint8)
+        _check(lib().rs_popcomm_export(self._h, h.ctypes.data))
+        return h
+
+    def connect(self, handles: np.ndarray):
+        handles = np.ascontiguousarray(handles, dtype=np.uint8).reshape(-1)
+        assert handles.size == self.world * self.HANDLE_BYTES
+        _check(lib().rs_popcomm_connect(self._h, handles.ctypes.data))
+
+    def query_dev(self, shardset: "ShardSet", d_kmers, k: int, q: int, packed: bool, max_hits: int, want_hits: bool = True,
+                  want_carriers: bool = False, stream: int = 0):
+        _check(lib().rs_pop_query_comm_dev(shardset._h, self._h, _ptr(d_kmers), k, q, int(packed), max_hits, int(want_hits),
+                                           int(want_carriers), stream))
+
+    def results(self, q: int, device=None):
+        """torch views (no copy) of this rank's result buffers for a batch of q k-mers:
+        dict(counts [q], hit_offsets [q+1], hits [capacity], carriers [q, 4] int32, total [1])."""
+        import torch
+        p = [C.c_void_p() for _ in range(5)]
+        cap = C.c_uint64()
+        _check(lib().rs_popcomm_results(self._h, *[C.byref(x) for x in p], C.byref(cap)))
+        dev = device if device is not None else f"cuda:{self.device}"
+
+        def view(ptr, shape, typestr):
+            class _A:
+                __cuda_array_interface__ = {"shape": shape, "typestr": typestr, "data": (int(ptr.value), False), "version": 3}
+            return torch.as_tensor(_A(), device=dev)
+        return dict(counts=view(p[0], (q,), "<i8"), hit_offsets=view(p[1], (q + 1,), "<i8"),
+                    hits=view(p[2], (max(int(cap.value), 1),), "<i8"), carriers=view(p[3], (q, 4), "<i4"),
+                    total=view(p[4], (1,), "<i8"))
+
+    def timed_out(self) -> bool:
+        v = C.c_int32()
+        _check(lib().rs_popcomm_error(self._h, C.byref(v)))
+        return bool(v.value)
+
+    def close(self):
+        if getattr(self, "_h", None):
+            lib().rs_popcomm_destroy(self._h)
+            self._h = None
 
     __del__ = close
 

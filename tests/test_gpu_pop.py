@@ -128,9 +128,9 @@ def test_saved_index_reopens_identically(name, datasets, engine, tmp_path):
 class PopCase:
     """A small population (configs[2] shape), its 64 shards on the GPU and their CPU oracles."""
 
-    def __init__(self, engine, genome_len=400_000, n_samples=9, coverage=20, read_len=100, device_runs=True):
+    def __init__(self, engine, genome_len=400_000, n_samples=9, coverage=20, read_len=100, device_runs=True, device=0):
         import torch
-        self.pop = dg.make_population(genome_len, n_samples, seed=4, device="cuda")
+        self.pop = dg.make_population(genome_len, n_samples, seed=4, device=f"cuda:{device}")
         keys, self.hist = dg.population_read_keys(self.pop, coverage, read_len, seed=41)
         self.read_len = read_len
         self.gpu, self.port, self.sai, self.samp, self.reads = [], [], [], [], []
@@ -139,7 +139,7 @@ class PopCase:
             b = sh.built
             runs_h = b.runs.cpu().numpy()
             B = engine.GpuBWT(runs=b.runs.contiguous() if device_runs else runs_h, num_strings=b.num_strings,
-                              num_symbols=b.num_symbols)
+                              num_symbols=b.num_symbols, device=device)
             B.set_sai(b.sai.contiguous() if device_runs else b.sai.cpu().numpy().astype(np.uint64))
             if device_runs:
                 B.set_samples(sh.samp_off.contiguous(), sh.samp_codes.contiguous(), 1)
@@ -331,3 +331,35 @@ def test_shard_set_argument_errors(popcase, engine):
         S.seal(128, 1)
         with pytest.raises(engine.RsError):
             S.query(np.zeros((2, 40), dtype=np.uint8) + 65, 40)   # k > 31
+
+
+@pytest.mark.parametrize("locate_every,world", [(1, 3), (0, 2)])
+def test_multi_rank_fan_in_through_peer_memory(locate_every, world):
+    """The whole multi-GPU protocol with `world` PROCESSES (tests/pop_worker.py): CUDA IPC mapping of every rank's result
+    buffers, counts added into the owner's buffer, hit numbers, slots assigned by the owner, read indices written into
+    the owner's list, sample sets OR-ed into the owner's bitmap, flag barriers in between.  The ranks use GPU
+    rank % device_count, so on a one-GPU box they share the device (time-sliced); every owner must hold exactly what one
+    shard set over all 64 shards answers for its k-mers, the hits in rank order."""
+    import socket
+    import subprocess
+    import sys
+    with socket.socket() as sk:
+        sk.bind(("127.0.0.1", 0))
+        port = sk.getsockname()[1]
+    procs = []
+    for r in range(world):
+        env = dict(os.environ, RANK=str(r), WORLD_SIZE=str(world), MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port),
+                   RS_B200_POP_CHUNK="1024")
+        procs.append(subprocess.Popen([sys.executable, os.path.join(common.ROOT, "tests", "pop_worker.py"), str(locate_every)],
+                                      env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True))
+    outs = []
+    for p in procs:
+        try:
+            out, _ = p.communicate(timeout=600)
+        except subprocess.TimeoutExpired:
+            for x in procs:
+                x.kill()
+            raise
+        outs.append(out)
+    for r, (p, out) in enumerate(zip(procs, outs)):
+        assert p.returncode == 0 and "POP_WORKER_OK" in out, f"rank {r}:\n{out[-3000:]}"
