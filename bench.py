@@ -1,22 +1,26 @@
 #!/usr/bin/env python
-"""bench.py -- 31-mer FM-index query throughput on B200 (BASELINE.json metric).
+"""bench.py -- 31-mer count+locate throughput on B200 (BASELINE.json metric, configs[2]).
 
     python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
 
-A step = one pass of the hot path (findInterval, src/bwt/query.cpp:24-41) over one batch of Q
-synthetic 31-mers against one BWT shard per GPU.
+Workload = BASELINE.json configs[2]: 100 diploid samples over a random 64 Mbp genome (population site list 1/300,
+~1 SNP/kb per haplotype), 30x of 100-bp reads per sample, de-duplicated, partitioned into the reference's 64 shards by
+reversed last 3 bases (service.cpp:820, demo/permutations-3.txt), per shard a BWT + .sai + sample table
+(size_of_sample = 1); 10 M 31-mers (90 % cut from the genome).
 
-N = 1     workload = BASELINE.json configs[1]: 50M x 100bp reads from a random 10 Mbp diploid genome,
-          de-duplicated, one RLBWT; 1M 31-mers (90% cut from the genome).
-N > 1     weak scaling: every rank holds its OWN shard of that size (a different read sample of the same
-          genome -- the reference shards by read, and every query visits every shard: SURVEY.md 8(e)),
-          all ranks search the same Q k-mers and the search kernel itself adds each per-shard count into the
-          buffer of the rank owning the k-mer (by prefix) over NVLink peer memory, followed by one flag
-          barrier -- inside the timed region (the reference's ZMQ fan-in + sum, server.cpp:184-197, 404-410).
-          The unit is therefore one 31-mer searched in one shard; value = N*Q*K / max-over-ranks time.
+A step = ONE pass of the hot path over the whole batch: per k-mer and per shard findInterval (query.cpp:24-41), every row
+of every interval located (extractPrefix's walk -> .sai -> read index, query.cpp:43-63), the hit reads' sample codes
+united into the k-mer's sample set (service.cpp:816-845), per-shard answers summed / concatenated per k-mer as the
+reference's front end does (server.cpp:184-197, 404-410).  Outputs per k-mer: population count, hit list
+(shard, read index), carrier bitmap.
 
-Prints ONE JSON line on rank 0.  `--impl reference` times the reference's own CPU code (oracle/_ref, or
-the oracle port when that library is absent) on the host cores for the same workload.
+N = 1   all 64 shards on one GPU (rs_shardset / rs_pop_query_dev).
+N > 1   strong scaling: the 64 shards are placed on the N GPUs by raw read count (LPT), every rank runs the whole batch
+        on its shards, and the pipeline's own kernels write counts, hit lists and carrier sets into the buffers of the
+        rank owning each k-mer (first four bases mod N) over NVLink peer memory (rs_popcomm).  value = Q / time.
+
+Prints ONE JSON line on rank 0.  `--impl reference` times the reference's own CPU code (oracle/_ref: findInterval +
+extractPrefix + extractPostfix per hit row, all host threads) on a bounded sample of the same batch.
 """
 from __future__ import annotations
 
@@ -34,76 +38,97 @@ ROOT = os.path.dirname(os.path.abspath(__file__))
 if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
-METRIC = "31-mer count queries/s (findInterval, one shard per GPU)"
+METRIC = "31-mer count+locate queries/s (findInterval + locate + sample set per k-mer over 64 read-suffix shards)"
 UNIT = "queries/s"
-BYTES_PER_RANK = 64           # one getOcc reads one 64-byte block = two 32-byte sectors;
-                              # SURVEY.md 8(d) assumed a whole 128-byte line per getOcc (reported beside it)
+BYTES_PER_RANK = 64           # one getOcc reads one 64-byte block = two 32-byte sectors
 FALLBACK_HBM_GBS = 6650.0     # /opt/skills/guides/B200_PROFILING.md
+NSHARDS = 64
+MAX_HITS = 1 << 20            # rows reported per k-mer and shard (the reference's front end refuses > 100,000 reads)
 
 
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=200)
-    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    # workload overrides (debugging only; the defaults are BASELINE.json configs[1])
-    ap.add_argument("--genome", type=int, default=10_000_000)
-    ap.add_argument("--reads", type=int, default=50_000_000)
+    # workload (defaults = BASELINE.json configs[2]); --scale shrinks genome and batch together for debugging
+    ap.add_argument("--genome", type=int, default=64_000_000)
+    ap.add_argument("--samples", type=int, default=100)
+    ap.add_argument("--coverage", type=float, default=30.0)
     ap.add_argument("--read-len", type=int, default=100)
-    ap.add_argument("--queries", type=int, default=1_000_000)
+    ap.add_argument("--queries", type=int, default=10_000_000)
     ap.add_argument("--k", type=int, default=31)
-    ap.add_argument("--cpu-seconds", type=float, default=12.0, help="target CPU time of the cpu_baseline sample")
+    ap.add_argument("--scale", type=float, default=1.0)
+    ap.add_argument("--locate-every", type=int, default=1,
+                    help="1: read-index tables (4 B per BWT row); S > 1: sampled locate tables; 0: plain walks")
+    ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU time of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
-    ap.add_argument("--no-random-roofline", action="store_true")
-    ap.add_argument("--sharded", type=int, default=64, choices=[0, 4, 16, 64],
-                    help="shards of the side measurement that splits the read set as the reference does (0 = skip)")
-    ap.add_argument("--locate-queries", type=int, default=100_000, help="k-mers of the count+locate side measurement")
-    return ap.parse_args()
+    ap.add_argument("--no-side", action="store_true", help="skip the side measurements (configs[1] count line, roofline probe)")
+    a = ap.parse_args()
+    if a.scale != 1.0:
+        a.genome = max(200_000, int(a.genome * a.scale))
+        a.queries = max(10_000, int(a.queries * a.scale))
+    return a
 
 
 def dist_env():
     return int(os.environ.get("RANK", 0)), int(os.environ.get("LOCAL_RANK", 0)), int(os.environ.get("WORLD_SIZE", 1))
 
 
+def workload_name(args):
+    return (f"configs[2]: {args.samples} diploid samples x {args.coverage:g}x of {args.read_len}-bp reads over a random "
+            f"{args.genome / 1e6:g} Mbp genome (sites 1/300, ~1 SNP/kb per haplotype), de-duplicated, {NSHARDS} shards by "
+            f"reversed last 3 bases, per-shard RLBWT + .sai + sample table; {args.queries} random {args.k}-mers (90% present), "
+            f"count + locate + sample set")
+
+
 # ------------------------------------------------------------------------------------------------
 # workload
 # ------------------------------------------------------------------------------------------------
-def build_shard(args, device, rank):
-    """configs[1] for shard `rank`: (runs u8 [R] numpy, num_strings, num_symbols, sai numpy, queries [Q,k] tensor)."""
+def build_population(args, device, shards_wanted=None, keep_host=False, make_index=True, local_rank=0):
+    """Generates the population and builds the wanted shards (None = all).  Returns dict with per-shard entries:
+    gpu (engine.GpuBWT with .sai and sample table attached) and/or host arrays for the CPU legs."""
     import torch
     from readserver_b200 import datagen as dg
     t0 = time.time()
-    h1 = dg.random_genome(args.genome, seed=2, device=device)
-    h2 = dg.mutate_snps(h1, 1e-3, seed=20)
-    for attempt in range(4):  # re-seed until the reference would not read m_vSum out of bounds (SURVEY.md Q2)
-        reads, lens = dg.sample_reads([h1, h2], args.reads, args.read_len, seed=21 + 100 * rank + 7919 * attempt)
-        reads, lens, _, _ = dg.dedupe_rlo(reads, lens)
-        built = dg.build_bwt(reads, lens)
-        if dg.q2_safe(built.runs, built.num_symbols):
-            break
-    queries = dg.make_queries(h1, args.queries, args.k, seed=3).contiguous()
-    runs = built.runs.cpu().numpy()
-    sai = built.sai.cpu().numpy().astype(np.uint64)
-    ns, nsym = built.num_strings, built.num_symbols
-    # the reads in builder input order, for the packed read table of the locate side measurement (rank 0 only)
-    reads_text = reads_off = reads_dev = None
-    if rank == 0 and args.impl == "ours" and int(lens.min()) == int(lens.max()):
-        if args.locate_queries > 0:
-            reads_text = dg.ASCII[reads.cpu().numpy()].reshape(-1)
-            reads_off = np.arange(ns + 1, dtype=np.uint64) * np.uint64(reads.shape[1])
-        if args.sharded > 0 and device != "cpu":
-            reads_dev = reads
-    del built, h2, reads, lens
+    pop = dg.make_population(args.genome, args.samples, seed=4, device=device)
+    keys, hist = dg.population_read_keys(pop, args.coverage, args.read_len, seed=41)
+    hist = [int(x) for x in hist.cpu().numpy()]
+    t_keys = time.time() - t0
+    wanted = list(range(NSHARDS)) if shards_wanted is None else shards_wanted(hist)
+    if make_index:
+        from readserver_b200 import engine
+    out = {"hist": hist, "shards": {}, "wanted": wanted}
+    tot = dict(reads=0, symbols=0, runs=0, codes=0, dropped=0)
+    for s in wanted:
+        sh = dg.build_population_shard(pop, keys, s, args.read_len)
+        b = sh.built
+        ent = {"num_strings": b.num_strings, "num_symbols": b.num_symbols, "num_runs": int(b.runs.numel())}
+        if make_index:
+            B = engine.GpuBWT(runs=b.runs.contiguous(), num_strings=b.num_strings, num_symbols=b.num_symbols, device=local_rank)
+            B.set_sai(b.sai.contiguous())
+            B.set_samples(sh.samp_off.contiguous(), sh.samp_codes.contiguous(), 1)
+            ent["gpu"] = B
+        if keep_host:
+            ent["runs"] = b.runs.cpu().numpy()
+            ent["sai"] = b.sai.cpu().numpy().astype(np.uint64)
+            ent["samp_off"] = sh.samp_off.cpu().numpy()
+            ent["samp_codes"] = sh.samp_codes.cpu().numpy()
+        tot["reads"] += b.num_strings
+        tot["symbols"] += b.num_symbols
+        tot["runs"] += int(b.runs.numel())
+        tot["codes"] += int(sh.samp_codes.numel())
+        tot["dropped"] += sh.dropped_reads
+        out["shards"][s] = ent
+        del sh, b
+    del keys
+    queries = dg.population_queries(pop, args.queries, args.k, seed=5).contiguous()
+    out.update(queries=queries, totals=tot, build_seconds=time.time() - t0, key_seconds=t_keys)
+    del pop
     if device != "cpu":
         torch.cuda.empty_cache()
-    return dict(runs=runs, num_strings=ns, num_symbols=nsym, sai=sai, queries=queries, genome=h1,
-                reads_text=reads_text, reads_off=reads_off, reads_dev=reads_dev, build_seconds=time.time() - t0)
-
-
-def workload_name(args):
-    return (f"configs[1]: {args.reads // 1_000_000}M x {args.read_len}bp reads, random {args.genome / 1e6:g} Mbp diploid "
-            f"genome (SNPs 1/kb), de-duplicated, single RLBWT per GPU; {args.queries} random {args.k}-mers (90% present)")
+    return out
 
 
 # ------------------------------------------------------------------------------------------------
@@ -121,7 +146,6 @@ class ClockSampler:
             import pynvml
             pynvml.nvmlInit()
             self.nv = pynvml
-            # CUDA_VISIBLE_DEVICES may remap; use the UUID of the torch device
             import torch
             uuid = str(torch.cuda.get_device_properties(index).uuid)
             h = None
@@ -147,7 +171,7 @@ class ClockSampler:
                         self.reasons.add(name)
             except Exception:
                 pass
-            self._stop.wait(0.002)
+            self._stop.wait(0.005)
 
     def start(self):
         if self.nv:
@@ -165,57 +189,92 @@ class ClockSampler:
 # ------------------------------------------------------------------------------------------------
 # CPU legs (the ONLY place bench.py touches oracle/)
 # ------------------------------------------------------------------------------------------------
-def cpu_find_interval(shard, queries_np, k, nthreads, target_seconds, steps=1, warmup=0, extras=False):
-    """Times findInterval of the reference's CPU implementation on a bounded sample of the queries."""
-    import oracle
-    import torch
-    from readserver_b200 import datagen as dg
-    with tempfile.TemporaryDirectory() as d:
-        path = os.path.join(d, "shard.bwt")
-        dg.write_bwt(path, torch.from_numpy(shard["runs"]), shard["num_strings"], shard["num_symbols"])
+class CpuShards:
+    """The shards loaded into the reference's own CPU implementation (oracle/_ref when built, else the oracle port)."""
+
+    def __init__(self, data, read_len):
+        import oracle
+        import torch
+        from readserver_b200 import datagen as dg
+        self.ix, self.sai, self.samp = {}, {}, {}
+        self.max_steps = read_len + 28
         t0 = time.time()
-        ix = oracle.open_best(path)
-        load_s = time.time() - t0
-    probe = min(len(queries_np), 20_000)
-    ix.find_interval_batch(queries_np[:probe], k, nthreads=nthreads)
-    rate = probe / max(ix.last_seconds, 1e-9)
-    n = int(min(len(queries_np), max(probe, rate * target_seconds / max(1, steps + warmup))))
-    sample = np.ascontiguousarray(queries_np[:n])
-    for _ in range(warmup):
-        ix.find_interval_batch(sample, k, nthreads=nthreads)
-    secs = []
-    for _ in range(steps):
-        lo, up = ix.find_interval_batch(sample, k, nthreads=nthreads)
-        secs.append(ix.last_seconds)
-    out = dict(kind=ix.kind, n=n, seconds=secs, value=n * len(secs) / sum(secs), load_seconds=load_s,
-               lower=lo, upper=up)
-    if extras and ix.kind == "reference":
-        # (a) the reference as its Makefiles ship it (no -O flag), a few seconds of it; (b) the CPU locate leg:
-        # extractPrefix per hit row, the walk K2 replaces
-        try:
-            with tempfile.TemporaryDirectory() as d:
-                path = os.path.join(d, "shard.bwt")
-                dg.write_bwt(path, torch.from_numpy(shard["runs"]), shard["num_strings"], shard["num_symbols"])
-                slow = oracle.RefIndex(path, so=oracle.REF_O0_SO)
-            m = min(n, 200_000)
-            slow.find_interval_batch(sample[:m], k, nthreads=nthreads)
-            out["as_shipped_O0_value"] = m / max(slow.last_seconds, 1e-9)
-            slow.close()
-        except Exception as ex:  # the -O0 build is optional
-            out["as_shipped_O0_value"] = None
-            print(f"as-shipped reference leg skipped: {ex}", file=sys.stderr)
-        hit = np.nonzero(up >= lo)[0][:20_000]
-        rows = np.concatenate([np.arange(lo[i], min(up[i], lo[i] + 15) + 1, dtype=np.uint64) for i in hit]) if hit.size else np.zeros(0, np.uint64)
-        if rows.size:
-            rows = rows[:300_000]
-            ix.locate_batch(rows, nthreads=nthreads, prefix=True, postfix=False, max_steps=shard_read_len(shard) + 28)
-            out["locate_rows_per_s"] = rows.size / max(ix.last_seconds, 1e-9)
-            out["locate_rows"] = int(rows.size)
-    return out
+        with tempfile.TemporaryDirectory() as d:
+            for s, ent in data["shards"].items():
+                path = os.path.join(d, f"shard{s}.bwt")
+                dg.write_bwt(path, torch.from_numpy(ent["runs"]), ent["num_strings"], ent["num_symbols"])
+                self.ix[s] = oracle.open_best(path)
+                os.unlink(path)
+                self.sai[s] = ent["sai"]
+                self.samp[s] = (ent["samp_off"], ent["samp_codes"])
+        self.kind = next(iter(self.ix.values())).kind
+        self.load_seconds = time.time() - t0
 
+    def run(self, q, k, nthreads, keep=False):
+        """count + locate of the k-mers q [n, k] in every shard, as the workers do it: findInterval, then extractPrefix +
+        extractPostfix per hit row (find_reads, service.cpp:714-751).  Returns (seconds inside the reference's code,
+        per-shard results when keep)."""
+        secs, per = 0.0, {}
+        for s, ix in self.ix.items():
+            lo, up = ix.find_interval_batch(q, k, nthreads=nthreads)
+            secs += ix.last_seconds
+            c = np.where(up >= lo, np.minimum(up - lo + 1, MAX_HITS), 0).astype(np.int64)
+            tot = int(c.sum())
+            if tot:
+                starts = np.repeat(lo, c)
+                within = np.arange(tot, dtype=np.int64) - np.repeat(np.cumsum(c) - c, c)
+                rows = (starts + within.astype(np.uint64)).astype(np.uint64)
+                lex, _, ri, _ = ix.locate_batch(rows, nthreads=nthreads, prefix=True, postfix=True, max_steps=self.max_steps)
+                secs += ix.last_seconds
+            else:
+                lex = ri = np.zeros(0, dtype=np.uint64)
+            if keep:
+                per[s] = (lo, up, c, lex, ri)
+        return secs, per
 
-def shard_read_len(shard):
-    return int(shard["num_symbols"] // max(1, shard["num_strings"]))
+    def expected(self, per, order, n):
+        """counts, hit_offsets, hits (shard << 40 | read index, the set's order), carriers [n, 4] from per-shard results."""
+        U64MAX = np.uint64(0xFFFFFFFFFFFFFFFF)
+        counts = np.zeros(n, dtype=np.uint64)
+        tot_h = np.zeros(n, dtype=np.int64)
+        for s in order:
+            lo, up, c, _, _ = per[s]
+            counts += np.where(up >= lo, up - lo + 1, 0).astype(np.uint64)
+            tot_h += c
+        off = np.zeros(n + 1, dtype=np.int64)
+        np.cumsum(tot_h, out=off[1:])
+        hits = np.zeros(int(off[n]), dtype=np.uint64)
+        carr = np.zeros((n, 4), dtype=np.uint32)
+        run = off[:-1].copy()
+        postfix_agrees = True
+        for s in order:
+            lo, up, c, lex, ri_post = per[s]
+            tot = int(c.sum())
+            if tot:
+                sai = self.sai[s]
+                ns = sai.size
+                ri = np.where(lex < ns, sai[np.minimum(lex, ns - 1).astype(np.int64)], U64MAX)
+                postfix_agrees &= bool(np.array_equal(ri, ri_post))
+                qid = np.repeat(np.arange(n), c)
+                within = np.arange(tot, dtype=np.int64) - np.repeat(np.cumsum(c) - c, c)
+                hits[run[qid] + within] = np.where(ri == U64MAX, U64MAX, (np.uint64(s) << np.uint64(40)) | ri)
+                # sample sets: union of (code - 34) over the codes of every hit read
+                so, sc = self.samp[s]
+                ok = ri != U64MAX
+                r_ok, q_ok = ri[ok].astype(np.int64), qid[ok]
+                ncodes = (so[r_ok + 1] - so[r_ok]).astype(np.int64)
+                tc = int(ncodes.sum())
+                if tc:
+                    src = np.repeat(so[r_ok].astype(np.int64), ncodes) + (np.arange(tc, dtype=np.int64) - np.repeat(np.cumsum(ncodes) - ncodes, ncodes))
+                    smp = sc[src].astype(np.int64) - 34
+                    qq = np.repeat(q_ok, ncodes)
+                    np.bitwise_or.at(carr, (qq, smp >> 5), (np.uint32(1) << (smp & 31).astype(np.uint32)))
+            run += c
+        return counts, off.astype(np.uint64), hits, carr, postfix_agrees
+
+    def close(self):
+        for ix in self.ix.values():
+            ix.close()
 
 
 def run_reference(args):
@@ -224,22 +283,34 @@ def run_reference(args):
         return
     import torch
     device = "cuda:0" if torch.cuda.is_available() else "cpu"
-    shard = build_shard(args, device, 0)
-    q = shard["queries"].cpu().numpy()
+    data = build_population(args, device, keep_host=True, make_index=False)
+    q = data["queries"].cpu().numpy()
     cores = os.cpu_count() or 1
-    r = cpu_find_interval(shard, q, args.k, cores, target_seconds=60.0, steps=args.steps, warmup=args.warmup)
-    ms = 1e3 * sum(r["seconds"]) / len(r["seconds"])
-    sample = f"first {r['n']} of {len(q)} queries per step, {cores} threads striding the array"
+    cpu = CpuShards(data, args.read_len)
+    probe = min(len(q), 2000)
+    t, _ = cpu.run(q[:probe], args.k, cores)
+    rate = probe / max(t, 1e-9)
+    n = int(min(len(q), max(probe, rate * 90.0 / max(1, args.steps + args.warmup))))
+    sample = np.ascontiguousarray(q[:n])
+    for _ in range(args.warmup):
+        cpu.run(sample, args.k, cores)
+    secs = [cpu.run(sample, args.k, cores)[0] for _ in range(args.steps)]
+    value = n * len(secs) / sum(secs)
     line = {
-        "impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "u64", "data": "synthetic",
-        "config": {"workload": workload_name(args), "bwt_symbols": shard["num_symbols"], "bwt_runs": int(shard["runs"].size),
-                   "queries_per_step": r["n"]},
-        "cpu_baseline": {"value": r["value"], "unit": UNIT, "cores": cores, "kind": r["kind"], "sample": sample},
-        "e2e": {"value": r["value"], "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 * sum(secs) / len(secs), "higher_is_better": True,
+        "scaling": "strong", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+        "config": {"workload": workload_name(args), "queries_per_step": n, "shards": NSHARDS,
+                   "bwt_symbols": data["totals"]["symbols"], "bwt_runs": data["totals"]["runs"],
+                   "reads_unique": data["totals"]["reads"],
+                   "note": "findInterval in all 64 shards + extractPrefix + extractPostfix per hit row (find_reads, "
+                           "service.cpp:714-751); the RocksDB lookups of the sample store are not timed (no RocksDB here)"},
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": cpu.kind,
+                         "sample": f"first {n} of {len(q)} k-mers per step, all {NSHARDS} shards, {cores} threads"},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
+    cpu.close()
     print(json.dumps(line), file=_REAL_STDOUT, flush=True)
 
 
@@ -254,96 +325,89 @@ def hbm_peak():
         return FALLBACK_HBM_GBS, "fallback (B200_PROFILING.md)"
 
 
-def k1_traffic():
-    """dram__bytes_read + dram__bytes_write of one K1 launch on this workload, from the committed ncu --set full
-    capture (profiles/k1_traffic.json, written by profiles/ncu_traffic.py); None when there is none."""
+def committed_traffic(name):
+    """dram bytes per launch of the dominant kernel from the committed ncu --set full capture (profiles/<name>), or None."""
     try:
-        d = json.load(open(os.path.join(ROOT, "profiles", "k1_traffic.json")))
+        d = json.load(open(os.path.join(ROOT, "profiles", name)))
         return float(d["dram_bytes_per_launch"]), d.get("source")
     except Exception:
         return None, None
 
 
-def sharded_measure(args, shard, B_whole, dq, engine, local_rank, stream, flush):
-    """Side measurement (configs[2] shape): the read set split into 4^p shards by its reads' reversed last p bases
-    (p = 3: the 64 keys of demo/permutations-3.txt, service.cpp:820), one BWT per shard, all on this GPU; every
-    shard searches the whole batch and the search kernel sums the per-shard counts (the front end's fan-in,
-    server.cpp:184-197, 404-410).  Checked: with exact rank the sum equals the count in the unsplit index."""
-    import torch
-    from readserver_b200 import datagen as dg
-    from readserver_b200 import sharding
-    reads = shard["reads_dev"]
-    n, L = reads.shape
-    p = {4: 1, 16: 2, 64: 3}[args.sharded]
-    dev = reads.device
-    key = torch.zeros(n, dtype=torch.int64, device=dev)
-    for j in range(p):
-        key = key * 4 + (reads[:, L - 1 - j].long() - 1)
-    t0 = time.time()
-    shards, sizes = [], []
-    for s in range(args.sharded):
-        idx = torch.nonzero(key == s).flatten()
-        if idx.numel() == 0:
-            continue
-        b = dg.build_bwt(reads[idx], torch.full((idx.numel(),), L, dtype=torch.int32, device=dev))
-        shards.append(engine.GpuBWT(runs=b.runs.cpu().numpy(), num_strings=b.num_strings, num_symbols=b.num_symbols,
-                                    device=local_rank))
-        sizes.append(int(shards[-1].info.hbm_bytes))
-        del b, idx
-    build_s = time.time() - t0
-    Q, k = args.queries, args.k
-    comm = sharding.connect_peers(engine.PeerComm(local_rank, 0, 1, Q), str(dev))
-
-    def step():
-        comm.begin(Q, stream)
-        for S in shards:
-            comm.accumulate(S, dq, k, Q, 0, stream)
-        return comm.finish(stream)
-
-    # parity: exact rank everywhere, shard sum == unsplit index
-    for S in shards:
-        S.set_tail_emulation(False)
-    B_whole.set_tail_emulation(False)
-    got = sharding.counts_view(step(), Q, dev).clone()
-    want = torch.empty(Q, dtype=torch.int64, device=dev)
-    B_whole.count_dev(dq, k, Q, 0, want, stream)
-    torch.cuda.synchronize()
-    ok = bool(torch.equal(got, want))
-    for S in shards:
-        S.set_tail_emulation(True)
-    B_whole.set_tail_emulation(True)
-    for _ in range(2):
-        step()
-    torch.cuda.synchronize()
-    ms = []
-    for _ in range(5):
-        flush.fill_(1)
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        step()
-        e1.record()
-        torch.cuda.synchronize()
-        ms.append(e0.elapsed_time(e1))
-    t = sum(ms) / 1e3
-    out = {"shards": len(shards), "split": f"reads' reversed last {p} bases (service.cpp:820)", "queries_per_step": Q,
-           "population_queries_per_s": Q * len(ms) / t, "shard_queries_per_s": len(shards) * Q * len(ms) / t,
-           "ms_per_step": 1e3 * t / len(ms), "kernels_per_step": len(shards) + 2,
-           "shard_index_bytes_min_max": [min(sizes), max(sizes)], "sum_equals_unsplit_index_exact_rank": ok,
-           "build_seconds": round(build_s, 1)}
-    comm.close()
-    for S in shards:
-        S.close()
-    assert ok, "sum of per-shard counts differs from the unsplit index"
-    return out
-
-
 def pinned_array(engine, nbytes, dtype, shape):
     import ctypes as C
     p = C.c_void_p()
-    rc = engine.lib().rs_host_alloc(C.byref(p), nbytes)
+    rc = engine.lib().rs_host_alloc(C.byref(p), max(nbytes, 8))
     assert rc == 0
-    buf = (C.c_uint8 * nbytes).from_address(p.value)
-    return np.frombuffer(buf, dtype=dtype).reshape(shape), p
+    buf = (C.c_uint8 * max(nbytes, 8)).from_address(p.value)
+    return np.frombuffer(buf, dtype=dtype)[: int(np.prod(shape))].reshape(shape), p
+
+
+def side_configs1(args, engine, dev, local_rank, flush):
+    """configs[1] count line (round 1's headline), kept as a side entry: one 1.08 G-symbol RLBWT, 1 M 31-mers, K1 alone."""
+    import torch
+    from readserver_b200 import datagen as dg
+    t0 = time.time()
+    h1 = dg.random_genome(10_000_000, seed=2, device=dev)
+    h2 = dg.mutate_snps(h1, 1e-3, seed=20)
+    reads, lens = dg.sample_reads([h1, h2], 50_000_000, 100, seed=21)
+    reads, lens, _, _ = dg.dedupe_rlo(reads, lens)
+    built = dg.build_bwt(reads, lens)
+    del reads, lens, h2
+    Q, k = 1_000_000, 31
+    dq = dg.make_queries(h1, Q, k, seed=3).contiguous()
+    B = engine.GpuBWT(runs=built.runs.contiguous(), num_strings=built.num_strings, num_symbols=built.num_symbols, device=local_rank)
+    B.enable_stats(True)
+    nsym, nruns = built.num_symbols, int(built.runs.numel())
+    del built
+    torch.cuda.empty_cache()
+    build_s = time.time() - t0
+    dlo = torch.empty(Q, dtype=torch.int64, device=dev)
+    dup = torch.empty(Q, dtype=torch.int64, device=dev)
+    stream = torch.cuda.current_stream().cuda_stream
+    for _ in range(3):
+        B.find_interval_dev(dq, k, Q, dlo, dup, stream)
+    torch.cuda.synchronize()
+    B.read_stats(reset=True)
+    ms = []
+    for _ in range(20):
+        flush.fill_(1)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        B.find_interval_dev(dq, k, Q, dlo, dup, stream)
+        e1.record()
+        torch.cuda.synchronize()
+        ms.append(e0.elapsed_time(e1))
+    steps, _ = B.read_stats(reset=True)
+    t = sum(ms) / 1e3
+    # e2e through the host-pointer call, pinned buffers
+    hq, _p1 = pinned_array(engine, Q * k, np.uint8, (Q, k))
+    hlo, _p2 = pinned_array(engine, Q * 8, np.uint64, (Q,))
+    hup, _p3 = pinned_array(engine, Q * 8, np.uint64, (Q,))
+    hq[:] = dq.cpu().numpy()
+    L = engine.lib()
+    for _ in range(3):
+        assert L.rs_find_interval_batch(B._h, hq.ctypes.data, k, Q, hlo.ctypes.data, hup.ctypes.data) == 0
+    es = 0.0
+    for _ in range(10):
+        flush.fill_(1)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        assert L.rs_find_interval_batch(B._h, hq.ctypes.data, k, Q, hlo.ctypes.data, hup.ctypes.data) == 0
+        es += time.perf_counter() - t0
+    same = bool(np.array_equal(dlo.cpu().numpy().view(np.uint64), hlo) and np.array_equal(dup.cpu().numpy().view(np.uint64), hup))
+    out = {"workload": "configs[1]: 50M x 100bp reads, random 10 Mbp diploid genome, de-duplicated, one RLBWT; 1M 31-mers",
+           "metric": "31-mer count queries/s (findInterval)", "value": Q * len(ms) / t, "ms_per_step": 1e3 * t / len(ms),
+           "e2e_value": Q * 10 / es, "e2e_api": "rs_find_interval_batch (host pointers, pinned, 31 B in + 16 B out per query)",
+           "achieved_GBps_at_64B_per_getocc": 2.0 * steps / len(ms) * BYTES_PER_RANK / (t / len(ms)) / 1e9,
+           "index_hbm_bytes": int(B.info.hbm_bytes), "bwt_symbols": nsym, "bwt_runs": nruns, "host_equals_device": same,
+           "build_seconds": round(build_s, 1)}
+    B.close()
+    for p in (_p1, _p2, _p3):
+        engine.lib().rs_host_free(p)
+    del dq, dlo, dup
+    torch.cuda.empty_cache()
+    return out
 
 
 def run_ours(args):
@@ -356,56 +420,70 @@ def run_ours(args):
         dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local_rank}"))
     torch.cuda.set_device(local_rank)
     dev = f"cuda:{local_rank}"
-    from readserver_b200 import engine
+    from readserver_b200 import engine, sharding
 
-    shard = build_shard(args, dev, rank)
-    B = engine.GpuBWT(runs=shard["runs"], num_strings=shard["num_strings"], num_symbols=shard["num_symbols"],
-                      device=local_rank)
-    B.set_sai(shard["sai"])
-    B.enable_stats(True)
+    want_cpu = (world == 1 and not args.no_cpu_baseline)
+    place = (lambda hist: sharding.assign_shards(hist, world)[rank]) if world > 1 else None
+    data = build_population(args, dev, shards_wanted=place, keep_host=want_cpu, make_index=True, local_rank=local_rank)
+    my_shards = data["wanted"]
+    t0 = time.time()
+    S = engine.ShardSet(local_rank)
+    for s in my_shards:
+        S.add(data["shards"][s]["gpu"], s)
+    info = S.seal(args.read_len + 28, args.locate_every)
+    seal_s = time.time() - t0
+    S.enable_stats(True)
     Q, k = args.queries, args.k
-    dq = shard["queries"]
+    dq = data["queries"]
+    W = int(info.carrier_words)
     torch.cuda.synchronize()
     torch.cuda.cudart().cudaProfilerStart()  # `ncu --profile-from-start off` skips the synthetic-data build
-    dlo = torch.empty(Q, dtype=torch.int64, device=dev)
-    dup = torch.empty(Q, dtype=torch.int64, device=dev)
-    dcnt = torch.empty(Q, dtype=torch.int64, device=dev)
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
     stream = torch.cuda.current_stream().cuda_stream
-
+    d_counts = torch.empty(Q, dtype=torch.int64, device=dev)
+    d_off = torch.empty(Q + 1, dtype=torch.int64, device=dev)
+    d_total = torch.zeros(1, dtype=torch.int64, device=dev)
+    # sizing pass: hits of the batch in this rank's shards
+    S.query_dev(dq, k, Q, False, MAX_HITS, d_counts, d_off, None, 0, None, d_total, stream)
+    torch.cuda.synchronize()
+    local_hits = int(d_total.item())
     comm = None
-    fused_ptr = [0]
     if world > 1:
-        from readserver_b200 import sharding
-        comm = sharding.connect_peers(engine.PeerComm(local_rank, rank, world, Q), dev)
+        th = torch.tensor([local_hits], dtype=torch.int64, device=dev)
+        dist.all_reduce(th)
+        total_hits = int(th.item())
+        cap = int(total_hits / world * 1.3) + (1 << 20)   # ownership by 4-base prefix is even for random k-mers
+        comm = sharding.connect_peers(engine.PopComm(local_rank, rank, world, Q, cap), dev)
+        del d_counts, d_off
+    else:
+        total_hits = local_hits
+        cap = max(total_hits, 1)
+        d_hits = torch.empty(cap, dtype=torch.int64, device=dev)
+        d_carr = torch.empty((Q, W), dtype=torch.int32, device=dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
 
     def step():
         if world > 1:
-            # K1 adds every finished query's count into the owning rank's buffer over NVLink peer memory
-            # (search + reduce-scatter in one kernel), then one flag barrier across the GPUs (C1)
-            comm.begin(Q, stream)
-            comm.accumulate(B, dq, k, Q, 0, stream)
-            fused_ptr[0] = comm.finish(stream)
+            comm.query_dev(S, dq, k, Q, False, MAX_HITS, True, True, stream)
         else:
-            B.find_interval_dev(dq, k, Q, dlo, dup, stream)
+            S.query_dev(dq, k, Q, False, MAX_HITS, d_counts, d_off, d_hits, cap, d_carr, d_total, stream)
 
     for _ in range(max(3, args.warmup)):
         step()
     torch.cuda.synchronize()
-    B.read_stats(reset=True)
     if world > 1:
         dist.barrier()
+        assert not comm.timed_out(), "peer barrier timed out"
+    S.read_stats(reset=True)
+    S.enable_timing(True)
     clocks = ClockSampler(local_rank)
     clocks.start()
     torch.cuda.synchronize()
     evs = []
     for _ in range(args.steps):
-        flush.fill_(1)  # evict the index and the queries from L2 between timed steps (untimed)
+        flush.fill_(1)  # evict queries, scratch and whatever index lines L2 still holds (untimed)
         if world > 1:
-            # the untimed flush ends at different moments on different GPUs: line the ranks up again so that
-            # a step's time is the step, not the skew of what ran before it
             torch.cuda.synchronize()
-            dist.barrier()
+            dist.barrier()  # ranks start the step together: a step's time is the step, not the skew of the flush
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
         step()
@@ -416,289 +494,225 @@ def run_ours(args):
         dist.barrier()
     clk = clocks.stop()
     step_ms = [a.elapsed_time(b) for a, b in evs]
+    stage_ms, stage_launches = S.read_timing()
+    S.enable_timing(False)
+    interval_steps, walk_steps = S.read_stats(reset=True)
     total_ms = torch.tensor([sum(step_ms)], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
     total_ms = float(total_ms.item())
-    interval_steps, _ = B.read_stats(reset=True)
 
-    fused_ok = None
+    # ---- N > 1: the fanned-in answers against the ranks' own answers gathered with NCCL / gloo-style collectives ----
+    fan_in_ok = None
     if world > 1:
-        # the fused reduce-scatter against NCCL: per-shard counts summed with an all-reduce, owned entries compared
-        from readserver_b200 import sharding
         assert not comm.timed_out(), "peer barrier timed out"
-        fused = sharding.counts_view(fused_ptr[0], Q, dev).clone()
-        B.count_dev(dq, k, Q, 0, dcnt, stream)
+        res = comm.results(Q, dev)
+        owner = torch.from_numpy(sharding.owner_of(dq.cpu().numpy(), world)).to(dev)
+        mine = owner == rank
+        lc = torch.empty(Q, dtype=torch.int64, device=dev)
+        lo_ = torch.empty(Q + 1, dtype=torch.int64, device=dev)
+        lt = torch.zeros(1, dtype=torch.int64, device=dev)
+        lh = torch.empty(max(local_hits, 1), dtype=torch.int64, device=dev)
+        lcar = torch.empty((Q, W), dtype=torch.int32, device=dev)
+        S.query_dev(dq, k, Q, False, MAX_HITS, lc, lo_, lh, max(local_hits, 1), lcar, lt, stream)
         torch.cuda.synchronize()
-        dist.all_reduce(dcnt)
-        own = torch.from_numpy(sharding.owner_of(dq.cpu().numpy().reshape(Q, k), world)).to(dev) == rank
-        ok = bool(torch.equal(fused[own], dcnt[own]) and int(fused[~own].abs().sum()) == 0)
+        gc = lc.clone()
+        dist.all_reduce(gc)
+        ok = bool(torch.equal(res["counts"][mine], gc[mine]) and int(res["counts"][~mine].abs().sum()) == 0)
+        # hit lists: per owned k-mer the number of hits = sum of the ranks' numbers; on a sample the lists themselves
+        nh = (lo_[1:] - lo_[:-1]).clone()
+        dist.all_reduce(nh)
+        got_n = res["hit_offsets"][1:] - res["hit_offsets"][:-1]
+        ok &= bool(torch.equal(got_n[mine], nh[mine]) and int(got_n[~mine].sum()) == 0)
+        ok &= int(res["total"].item()) <= cap
+        nsamp = min(Q, 20000)
+        h_end = int(lo_[nsamp].item())
+        pieces = [None] * world
+        dist.all_gather_object(pieces, (lo_[: nsamp + 1].cpu().numpy(), lh[:h_end].cpu().numpy(), lcar[:nsamp].cpu().numpy()))
+        ro = res["hit_offsets"][: nsamp + 1].cpu().numpy()
+        rh = res["hits"][: int(ro[-1])].cpu().numpy() if int(ro[-1]) else np.zeros(0, np.int64)
+        rc = res["carriers"][:nsamp].cpu().numpy()
+        own_np = owner[:nsamp].cpu().numpy()
+        for i in np.nonzero(own_np == rank)[0][:4000]:
+            want = np.concatenate([p[1][int(p[0][i]): int(p[0][i + 1])] for p in pieces])
+            ok &= bool(np.array_equal(rh[int(ro[i]): int(ro[i + 1])], want))
+            wc = np.bitwise_or.reduce(np.stack([p[2][i] for p in pieces]), axis=0)
+            ok &= bool(np.array_equal(rc[i], wc))
         okt = torch.tensor([int(ok)], device=dev)
         dist.all_reduce(okt, op=dist.ReduceOp.MIN)
-        fused_ok = bool(okt.item())
-        assert fused_ok, "fused peer-memory reduction differs from the NCCL all-reduce of per-shard counts"
+        fan_in_ok = bool(okt.item())
+        assert fan_in_ok, "results fanned in through peer memory differ from the ranks' own answers"
+        del lc, lo_, lh, lcar, gc, nh
 
-    # ---- e2e: the host-pointer C-ABI call, pinned host buffers, copies inside the timed region ----
-    hq, _p1 = pinned_array(engine, Q * k, np.uint8, (Q, k))
-    hlo, _p2 = pinned_array(engine, Q * 8, np.uint64, (Q,))
-    hup, _p3 = pinned_array(engine, Q * 8, np.uint64, (Q,))
-    hq[:] = dq.cpu().numpy()
+    # ---- e2e: host-pointer call, pinned host buffers, every copy inside the timed region ----
     L = engine.lib()
-    for _ in range(3):
-        assert L.rs_find_interval_batch(B._h, hq.ctypes.data, k, Q, hlo.ctypes.data, hup.ctypes.data) == 0
+    import ctypes as C
+    hq, _p0 = pinned_array(engine, Q * k, np.uint8, (Q, k))
+    hq[:] = dq.cpu().numpy()
+    e2e_steps = max(3, args.steps // 2)
+    if world == 1:
+        hcounts, _p1 = pinned_array(engine, Q * 8, np.uint64, (Q,))
+        hoff, _p2 = pinned_array(engine, (Q + 1) * 8, np.uint64, (Q + 1,))
+        hhits, _p3 = pinned_array(engine, cap * 8, np.uint64, (cap,))
+        hcarr, _p4 = pinned_array(engine, Q * W * 4, np.uint32, (Q, W))
+        tot = C.c_uint64()
+
+        def e2e_call():
+            rc = L.rs_pop_query(S._h, hq.ctypes.data, k, Q, 0, MAX_HITS, hcounts.ctypes.data, hoff.ctypes.data,
+                                hhits.ctypes.data, cap, hcarr.ctypes.data, C.byref(tot))
+            assert rc == 0, rc
+        d2h = Q * 8 + (Q + 1) * 8 + total_hits * 8 + Q * W * 4 + 8
+    else:
+        # every rank: batch in, the pipeline with its fan-in, the answers of the k-mers it owns out
+        res = comm.results(Q, dev)
+        hcounts, _p1 = pinned_array(engine, Q * 8, np.int64, (Q,))
+        hoff, _p2 = pinned_array(engine, (Q + 1) * 8, np.int64, (Q + 1,))
+        hhits, _p3 = pinned_array(engine, cap * 8, np.int64, (cap,))
+        hcarr, _p4 = pinned_array(engine, Q * 16, np.int32, (Q, 4))
+        t_counts, t_off, t_hits, t_carr = (torch.from_numpy(x) for x in (hcounts, hoff, hhits, hcarr))
+        t_hq = torch.from_numpy(hq)
+        dq2 = torch.empty_like(dq)
+
+        def e2e_call():
+            dq2.copy_(t_hq, non_blocking=True)
+            comm.query_dev(S, dq2, k, Q, False, MAX_HITS, True, True, stream)
+            t_counts.copy_(res["counts"], non_blocking=True)
+            t_off.copy_(res["hit_offsets"], non_blocking=True)
+            t_carr.copy_(res["carriers"], non_blocking=True)
+            torch.cuda.synchronize()
+            n = int(hoff[Q])
+            t_hits[:n].copy_(res["hits"][:n], non_blocking=True)
+            torch.cuda.synchronize()
+        d2h = None
+    for _ in range(2):
+        e2e_call()
     if world > 1:
         dist.barrier()
     e2e_s = 0.0
-    for _ in range(args.steps):
+    for _ in range(e2e_steps):
         flush.fill_(1)
         torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
         t0 = time.perf_counter()
-        rc = L.rs_find_interval_batch(B._h, hq.ctypes.data, k, Q, hlo.ctypes.data, hup.ctypes.data)
+        e2e_call()
         e2e_s += time.perf_counter() - t0
-        assert rc == 0
     e2e_t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+    own_hits = torch.tensor([int(hoff[Q])], dtype=torch.int64, device=dev)
     if world > 1:
         dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(own_hits)
+        d2h = world * (Q * 8 + (Q + 1) * 8 + Q * 16) + int(own_hits.item()) * 8
     e2e_s = float(e2e_t.item())
-
-    # the same through count_reads' batch call (service.cpp:279-315): 8 bytes back per query instead of 16
-    e2e_count = None
     if world == 1:
-        hcnt, _p4 = pinned_array(engine, Q * 8, np.uint64, (Q,))
-        for _ in range(2):
-            assert L.rs_count_batch(B._h, hq.ctypes.data, k, Q, 0, hcnt.ctypes.data) == 0
-        cs = 0.0
-        nrep = max(3, args.steps // 4)
-        for _ in range(nrep):
-            flush.fill_(1)
-            torch.cuda.synchronize()
-            t0 = time.perf_counter()
-            rc = L.rs_count_batch(B._h, hq.ctypes.data, k, Q, 0, hcnt.ctypes.data)
-            cs += time.perf_counter() - t0
-            assert rc == 0
-        e2e_count = Q * nrep / cs
-        assert np.array_equal(hcnt, np.where(hup >= hlo, hup - hlo + 1, 0).astype(np.uint64)), "count != interval width"
+        # the host path and the device path give the same answers
+        assert np.array_equal(hcounts, d_counts.cpu().numpy().view(np.uint64)) and np.array_equal(hoff, d_off.cpu().numpy().view(np.uint64))
+        assert int(tot.value) == total_hits
+        assert np.array_equal(hcarr, d_carr.cpu().numpy().view(np.uint32))
 
-    # results of the device path and of the host path agree (and, below, with the CPU reference)
-    if world == 1:
-        assert np.array_equal(dlo.cpu().numpy().view(np.uint64), hlo) and np.array_equal(dup.cpu().numpy().view(np.uint64), hup)
-
-    # ---- side measurement: count + locate (findInterval -> rows -> extractPrefix walk -> .sai) ----
-    locate = None
-    if world == 1 and args.locate_queries > 0:
-        QL = min(Q, args.locate_queries)
-        max_hits, max_steps = 256, args.read_len + 28
-        cap = QL * 128
-        d_off = torch.empty(QL + 1, dtype=torch.int64, device=dev)
-        d_ri = torch.empty(cap, dtype=torch.int64, device=dev)
-        d_st = torch.empty(cap, dtype=torch.int32, device=dev)
-        for _ in range(2):
-            hits = B.locate_dev(dq, k, QL, max_hits, max_steps, d_off, cap, None, None, d_ri, d_st, stream)
-        torch.cuda.synchronize()
-        B.read_stats(reset=True)
-        lms = []
-        for _ in range(max(3, args.steps // 4)):
-            flush.fill_(1)
-            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-            e0.record()
-            hits = B.locate_dev(dq, k, QL, max_hits, max_steps, d_off, cap, None, None, d_ri, d_st, stream)
-            e1.record()
-            torch.cuda.synchronize()
-            lms.append(e0.elapsed_time(e1))
-        isteps, wsteps = B.read_stats(reset=True)
-        lt = sum(lms) / 1e3
-        locate = {"metric": "31-mer count+locate queries/s (interval, rows <= 256 per k-mer, LF walk to '$', .sai read index)",
-                  "value": QL * len(lms) / lt, "unit": UNIT, "queries_per_step": QL, "hits_per_step": hits,
-                  "hit_rows_per_s": hits * len(lms) / lt, "ms_per_step": 1e3 * lt / len(lms),
-                  "walk_steps_per_step": wsteps / len(lms),
-                  "achieved_GBps": (2.0 * isteps + wsteps) * BYTES_PER_RANK / lt / 1e9,
-                  "kernels_per_step": 5, "note": "includes one stream sync per step to size the hit list"}
-        # the same stage with the locate table (8 bytes per BWT row of HBM: one read per hit row instead of a walk)
+    side = None
+    if world == 1 and not args.no_side:
+        side = {}
         try:
-            t0 = time.perf_counter()
-            B.build_locate_table(args.read_len + 28)
-            torch.cuda.synchronize()
-            build_s = time.perf_counter() - t0
-            d_ri2 = torch.empty(cap, dtype=torch.int64, device=dev)
-            d_st2 = torch.empty(cap, dtype=torch.int32, device=dev)
-            B.locate_dev(dq, k, QL, max_hits, max_steps, d_off, cap, None, None, d_ri2, d_st2, stream)
-            torch.cuda.synchronize()
-            same = bool(torch.equal(d_ri[:hits], d_ri2[:hits]) and torch.equal(d_st[:hits], d_st2[:hits]))
-            tms = []
-            for _ in range(max(3, args.steps // 4)):
-                flush.fill_(1)
-                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                e0.record()
-                B.locate_dev(dq, k, QL, max_hits, max_steps, d_off, cap, None, None, d_ri2, d_st2, stream)
-                e1.record()
-                torch.cuda.synchronize()
-                tms.append(e0.elapsed_time(e1))
-            tt = sum(tms) / 1e3
-            locate["with_locate_table"] = {"value": QL * len(tms) / tt, "unit": UNIT, "hit_rows_per_s": hits * len(tms) / tt,
-                                           "ms_per_step": 1e3 * tt / len(tms), "table_bytes": 8 * (int(shard["num_symbols"]) + int(shard["num_strings"])),
-                                           "build_seconds": build_s, "equals_walk": same,
-                                           "note": "rs_index_build_locate_table: where each row's walk ends, found once by "
-                                                   "walking every read (n LF steps)"}
-            # sampled variant: 1/16 of the rows hold an entry, a hit row is walked < 16 steps
-            t0 = time.perf_counter()
-            B.build_locate_table(args.read_len + 28, every=16)
-            torch.cuda.synchronize()
-            build16 = time.perf_counter() - t0
-            tbytes16 = int(B.info.hbm_bytes)
-            B.locate_dev(dq, k, QL, max_hits, max_steps, d_off, cap, None, None, d_ri2, d_st2, stream)
-            torch.cuda.synchronize()
-            same16 = bool(torch.equal(d_ri[:hits], d_ri2[:hits]) and torch.equal(d_st[:hits], d_st2[:hits]))
-            sms = []
-            for _ in range(max(3, args.steps // 4)):
-                flush.fill_(1)
-                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                e0.record()
-                B.locate_dev(dq, k, QL, max_hits, max_steps, d_off, cap, None, None, d_ri2, d_st2, stream)
-                e1.record()
-                torch.cuda.synchronize()
-                sms.append(e0.elapsed_time(e1))
-            B.drop_locate_table()
-            tbytes16 -= int(B.info.hbm_bytes)
-            st_ = sum(sms) / 1e3
-            locate["with_sampled_locate_table"] = {"every": 16, "value": QL * len(sms) / st_, "unit": UNIT,
-                                                   "hit_rows_per_s": hits * len(sms) / st_, "ms_per_step": 1e3 * st_ / len(sms),
-                                                   "table_bytes": tbytes16, "build_seconds": build16, "equals_walk": same16}
-            del d_ri2, d_st2
-        except engine.RsError as ex:
-            locate["with_locate_table"] = {"unavailable": str(ex)}
-        if shard.get("reads_text") is not None and hits:
-            # output=reads from the packed read table, addressed by the read indices just located
-            B.set_reads_arrays(shard["reads_text"], shard["reads_off"])
-            ml = args.read_len + 4
-            d_str = torch.empty(hits * ml, dtype=torch.uint8, device=dev)
-            d_len = torch.empty(hits, dtype=torch.int32, device=dev)
-            B.reads_dev(d_ri, hits, ml, d_str, d_len, stream)
-            torch.cuda.synchronize()
-            rms = []
-            for _ in range(5):
-                flush.fill_(1)
-                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-                e0.record()
-                B.reads_dev(d_ri, hits, ml, d_str, d_len, stream)
-                e1.record()
-                torch.cuda.synchronize()
-                rms.append(e0.elapsed_time(e1))
-            # spot check against the table's source
-            ri_h = d_ri[:64].cpu().numpy().astype(np.int64)
-            got = d_str[: 64 * ml].cpu().numpy().reshape(64, ml)
-            for t, r in enumerate(ri_h):
-                if 0 <= r < shard["num_strings"]:
-                    a, b = int(shard["reads_off"][r]), int(shard["reads_off"][r + 1])
-                    assert np.array_equal(got[t, : b - a], shard["reads_text"][a:b]), "read table mismatch"
-            locate["reads_from_table"] = {"reads_per_s": hits * len(rms) / (sum(rms) / 1e3), "ms": sum(rms) / len(rms),
-                                          "bytes_written": hits * ml,
-                                          "note": "rs_reads_batch_dev on the located read indices (replaces extractPrefix + "
-                                                  "extractPostfix per row, query.cpp:87-100)"}
-            del d_str, d_len
-        if hits:
-            # config-5 style tail: hit reads -> sample codes -> sorted distinct sample set per k-mer (K3), through the
-            # host-pointer call (copies inside); synthetic table: 100 samples, 1-3 codes per read
-            rng = np.random.default_rng(11)
-            ns = int(shard["num_strings"])
-            soff = np.zeros(ns + 1, dtype=np.uint64)
-            np.cumsum(rng.integers(1, 4, ns), out=soff[1:])
-            scodes = (rng.integers(0, 100, int(soff[-1])) + 34).astype(np.uint8)   # code of sample s: s + 1 + 33
-            B.set_samples(soff, scodes, 1)
-            h_off = d_off.cpu().numpy().view(np.uint64)
-            h_ri = d_ri[:hits].cpu().numpy().view(np.uint64)
-            B.carriers(h_off, h_ri)
-            cs = []
-            for _ in range(3):
-                t0 = time.perf_counter()
-                coff, ccodes = B.carriers(h_off, h_ri)
-                cs.append(time.perf_counter() - t0)
-            locate["sample_sets"] = {"kmers_per_s": QL / min(cs), "hit_reads_per_s": hits / min(cs), "ms": 1e3 * min(cs),
-                                     "samples_out": int(coff[-1]), "note": "rs_carriers_batch (host pointers, two passes: "
-                                     "sizes, then codes): RocksDB Get + decode + set union per k-mer in the reference "
-                                     "(service.cpp:816-845)"}
-            del soff, scodes
-        del d_off, d_ri, d_st
-
-    sharded = None
-    if world == 1 and args.sharded > 0 and shard.get("reads_dev") is not None:
-        sharded = sharded_measure(args, shard, B, dq, engine, local_rank, stream, flush)
-        shard["reads_dev"] = None
-        torch.cuda.empty_cache()
-
-    random_gbs = random_gbs_128 = None
-    if world == 1 and not args.no_random_roofline:
-        try:
-            random_gbs = engine.measure_random_access(local_rank, 8 << 30, 1 << 27, 64)
-            random_gbs_128 = engine.measure_random_access(local_rank, 8 << 30, 1 << 27, 128)
-        except Exception as ex:  # not fatal for the bench line
-            random_gbs = None
+            gran = {}
+            for g in (64, 128):
+                gran[f"{g}B"] = engine.measure_random_access(local_rank, 16 << 30, 1 << 28, g)
+            side["random_access_GBps"] = gran
+        except Exception as ex:
             print(f"random-access roofline measurement failed: {ex}", file=sys.stderr)
-
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
 
-    value = world * Q * args.steps / (total_ms / 1e3)
+    value = Q * args.steps / (total_ms / 1e3)
     peak, peak_src = hbm_peak()
-    traffic, traffic_src = k1_traffic()
-    kern_ms = sum(step_ms) / len(step_ms)  # at N = 1 the step IS the kernel launch
-    ranks_per_launch = 2.0 * interval_steps / args.steps
-    achieved = ranks_per_launch * BYTES_PER_RANK / (kern_ms / 1e3) / 1e9
+    k1_s = stage_ms["search"] / 1e3
+    k1_launches = max(1, stage_launches["search"])
+    getocc = 2.0 * interval_steps
+    achieved = getocc * BYTES_PER_RANK / max(k1_s, 1e-12) / 1e9
+    traffic, traffic_src = committed_traffic("r2_k1_traffic.json")
+    chunks = (Q + int(info.chunk_queries) - 1) // int(info.chunk_queries)
+    ours_per_step = 1 + chunks * (len(my_shards) + 4 + (1 if args.locate_every == 1 else 4 * len(my_shards) + 1)) \
+        + (chunks * 2 + 2 + chunks * 3 if world > 1 else 0)
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": max(3, args.warmup), "ms_per_step": total_ms / args.steps, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+        "scaling": "strong", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
         "config": {
-            "workload": workload_name(args), "k": k, "queries_per_step": Q, "shards_per_gpu": 1,
-            "threads_per_query": 1, "block_layout": "64 B = 28 B header (start, 4 x 40-bit counters) + 36 run bytes; 2 sectors per rank",
-            "bwt_symbols": shard["num_symbols"], "bwt_runs": int(shard["runs"].size), "reads_unique": shard["num_strings"],
-            "index_hbm_bytes": int(B.info.hbm_bytes), "index_fits_l2": bool(B.info.hbm_bytes < 126e6),
-            "l2": "256 MiB buffer written between timed steps (untimed) -> index and queries start cold",
+            "workload": workload_name(args), "k": k, "queries_per_step": Q, "shards": NSHARDS,
+            "shards_on_rank0": len(my_shards), "hits_per_step": total_hits, "hits_per_query": total_hits / Q,
+            "locate": {1: "read-index table, 4 B per BWT row (coalesced reads of an interval's rows)", 0: "LF walk to '$' (K2)"}.get(
+                args.locate_every, f"sampled locate table, every {args.locate_every} rows"),
+            "bwt_symbols": data["totals"]["symbols"], "bwt_runs": data["totals"]["runs"], "reads_unique": data["totals"]["reads"],
+            "sample_codes": data["totals"]["codes"], "reads_dropped_for_q2": data["totals"]["dropped"],
+            "index_hbm_bytes_rank0": int(info.index_bytes), "table_hbm_bytes_rank0": int(info.table_bytes),
+            "chunk_queries": int(info.chunk_queries), "carrier_words": W,
+            "l2": "working set (index + tables) far larger than the 126 MB L2; 256 MiB written between timed steps (untimed)",
             "timing": "CUDA events around each step on the launching stream, summed; max over ranks"
-                      + ("; ranks re-aligned with a barrier after each untimed L2 flush" if world > 1 else ""),
+                      + ("; ranks aligned with a barrier before each step" if world > 1 else ""),
             "collective": "none" if world == 1 else
-            "fused into K1: counts added into the owning rank's buffer over NVLink peer memory + one flag barrier "
-            "per step, inside the timed step; checked against an NCCL all-reduce of the per-shard counts",
-            "fused_reduce_equals_nccl": fused_ok,
-            "data_build_seconds": round(shard["build_seconds"], 1),
+            "fused into the pipeline's kernels over NVLink peer memory (CUDA IPC): counts atomically added into the owner's "
+            "buffer, hit numbers -> owner assigns slots -> read indices written into the owner's hit list by the locate "
+            "kernel, sample sets OR-ed into the owner's bitmap; flag barriers between the phases; inside the timed step",
+            "fan_in_equals_ranks_own_answers": fan_in_ok,
+            "data_build_seconds": round(data["build_seconds"], 1), "seal_seconds": round(seal_s, 1),
         },
         "roofline": {
-            "bound": "hbm", "kernel": "k_find_interval", "achieved": achieved, "peak": peak, "unit": "GB/s",
-            "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
-            "algorithmic_bytes": "executed getOcc calls x 64 B (one 64-byte block: header + 36 run bytes); "
-                                 "lower/upper of a step often share a block",
-            "getocc_per_launch": ranks_per_launch,
-            "achieved_at_128B_per_getocc": 2 * achieved, "frac_at_128B_per_getocc": 2 * achieved / peak,
-            "random_access_peak": random_gbs,
-            "frac_of_random_access_peak": (achieved / random_gbs) if random_gbs else None,
-            "random_access_peak_source": "measured in this run: random aligned 64-B loads (one block each) over 8 GiB "
-                                         "(rs_measure_random_access_granule)",
-            "random_access_peak_128B_lines": random_gbs_128,
+            "bound": "hbm", "kernel": "k_find_interval (K1), one launch per shard and chunk", "achieved": achieved, "peak": peak,
+            "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
+            "algorithmic_bytes": "executed getOcc calls x 64 B (one block: header + 36 run bytes)",
+            "getocc_per_launch": getocc / k1_launches, "launches_timed": k1_launches,
+            "avg_launch_ms": stage_ms["search"] / k1_launches,
+            "k1_share_of_step": stage_ms["search"] / max(sum(step_ms), 1e-9),
+            "stage_ms_per_step": {s: v / args.steps for s, v in stage_ms.items()},
+            "note": "a shard's blocks + directory + suffix table are tens of MB: L2-resident while a chunk of queries streams "
+                    "through it, so the achieved figure is served by L2, not HBM (DESIGN.md 6)",
         },
-        "e2e": {"value": world * Q * args.steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": Q * k,
-                "d2h_bytes_per_step": 2 * Q * 8, "api": "rs_find_interval_batch (host pointers, pinned)",
-                "count_api_value": e2e_count,
-                "count_api": "rs_count_batch, forward strand: 8 bytes back per query (not the headline: kept beside it)"},
-        "gpu_launches": args.steps * 3,  # k_pack_kmers + k_find_interval + k_search_flagged (N > 1: k_peer_barrier)
+        "e2e": {"value": Q * e2e_steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": (world if world > 1 else 1) * Q * k,
+                "d2h_bytes_per_step": d2h, "steps": e2e_steps,
+                "api": "rs_pop_query (host pointers, pinned): k-mers in, counts + hit offsets + hits + carrier sets out" if world == 1
+                else "per rank: batch H2D, rs_pop_query_comm_dev, the owned answers D2H"},
+        "gpu_launches": args.steps * ours_per_step,
         "clocks": clk,
     }
-    if locate:
-        line["locate"] = locate
-    if sharded:
-        line["sharded"] = sharded
-    if world == 1 and not args.no_cpu_baseline:
+    if side is not None:
+        try:
+            side["configs1_count"] = side_configs1(args, engine, dev, local_rank, flush)
+        except Exception as ex:
+            print(f"configs[1] side measurement failed: {ex}", file=sys.stderr)
+        line["side"] = side
+        ra = side.get("random_access_GBps", {}).get("64B")
+        if ra:
+            line["roofline"]["random_access_peak_64B"] = ra
+            line["roofline"]["frac_of_random_access_peak"] = achieved / ra
+    if want_cpu:
         cores = os.cpu_count() or 1
-        r = cpu_find_interval(shard, hq, k, cores, target_seconds=args.cpu_seconds, steps=1, extras=True)
-        ok = bool(np.array_equal(r["lower"], hlo[: r["n"]]) and np.array_equal(r["upper"], hup[: r["n"]]))
-        line["cpu_baseline"] = {"value": r["value"], "unit": UNIT, "cores": cores, "kind": r["kind"],
-                                "sample": f"first {r['n']} of {Q} queries, {cores} threads striding the array",
-                                "gpu_results_bit_exact_on_sample": ok,
-                                "as_shipped_O0_value": r.get("as_shipped_O0_value"),
-                                "locate_rows_per_s": r.get("locate_rows_per_s"), "locate_rows": r.get("locate_rows"),
-                                "note": "value: reference sources at -O2; as_shipped_O0_value: built without -O as its "
-                                        "Makefiles do; locate_rows_per_s: extractPrefix per hit row on the same threads"}
-        assert ok, "GPU results differ from the CPU reference"
+        order = my_shards
+        for ent in data["shards"].values():   # the GPU copies are no longer needed; the CPU leg wants the host RAM quiet
+            pass
+        cpu = CpuShards(data, args.read_len)
+        probe = min(Q, 2000)
+        t, _ = cpu.run(hq[:probe], k, cores)
+        n = int(min(Q, max(probe, probe / max(t, 1e-9) * args.cpu_seconds)))
+        secs, per = cpu.run(np.ascontiguousarray(hq[:n]), k, cores, keep=True)
+        w_counts, w_off, w_hits, w_carr, post_ok = cpu.expected(per, order, n)
+        he = int(hoff[n])
+        ok_counts = bool(np.array_equal(hcounts[:n], w_counts))
+        ok_hits = bool(np.array_equal(hoff[: n + 1], w_off) and np.array_equal(hhits[:he], w_hits))
+        ok_carr = bool(np.array_equal(hcarr[:n], w_carr))
+        line["cpu_baseline"] = {
+            "value": n / secs, "unit": UNIT, "cores": cores, "kind": cpu.kind,
+            "sample": f"first {n} of {Q} k-mers, all {NSHARDS} shards, {cores} threads striding each batch",
+            "what": "findInterval per shard + extractPrefix + extractPostfix per hit row (find_reads, service.cpp:714-751); the "
+                    "sample-store lookups (RocksDB) are not in the timed part",
+            "load_seconds": round(cpu.load_seconds, 1),
+            "gpu_results_bit_exact_on_sample": ok_counts and ok_hits and ok_carr,
+            "checked": {"population_counts": ok_counts, "hit_lists_read_index": ok_hits, "sample_sets": ok_carr,
+                        "postfix_walk_gives_the_same_read_index": post_ok, "hits_checked": he},
+        }
+        cpu.close()
+        assert ok_counts and ok_hits and ok_carr, "GPU results differ from the CPU reference"
     print(json.dumps(line), file=_REAL_STDOUT, flush=True)
     if world > 1:
         dist.destroy_process_group()
@@ -709,8 +723,7 @@ _REAL_STDOUT = sys.stdout
 
 def main():
     args = parse()
-    # libraries (NCCL's version banner, torchrun notices) must not share stdout with the ONE JSON line:
-    # everything but that line goes to stderr
+    # libraries (NCCL's version banner, torchrun notices) must not share stdout with the ONE JSON line
     global _REAL_STDOUT
     sys.stdout.flush()
     _REAL_STDOUT = os.fdopen(os.dup(1), "w")

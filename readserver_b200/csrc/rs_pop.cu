@@ -209,6 +209,7 @@ __global__ void k_pop_owner_slots(const __grid_constant__ rs_pop_peers P, const 
  * the hit reads' sample sets when carrier sets are wanted (W = 4 words of 32 samples).  The hits go to the rank that
  * owns the query (P.world > 1: over NVLink peer memory, at the slot the owner assigned to this rank -- locate and the
  * fan-in of the hit lists, server.cpp:184-197, are one kernel), the sample set is OR-ed into the owner's bitmap. */
+#define RS_GATHER_LANE_ROWS 8u /* intervals up to this many rows are read by one lane; longer ones by the whole warp */
 __global__ void __launch_bounds__(256)
     k_pop_gather(const __grid_constant__ rs_pop_tables T, const __grid_constant__ rs_pop_peers P,
                  const uint64_t* __restrict__ keys, uint32_t k, const uint64_t* __restrict__ lo,
@@ -221,27 +222,64 @@ __global__ void __launch_bounds__(256)
     uint64_t* __restrict__ hits = P.hits[owner];
     uint64_t off = slot[q0 + q];
     uint32_t b0 = 0, b1 = 0, b2 = 0, b3 = 0;
-    for (uint32_t s = 0; s < T.nshards; ++s) {
-      uint64_t c = cnt[(uint64_t)s * C + q];
-      if (c == 0) continue;
+    /* A k-mer of a read set at 30x hits a handful of rows in most of the shards: the lanes take one shard each
+     * (32 independent chains of loads in flight per warp), a warp scan lays their rows out in shard order. */
+    for (uint32_t s0 = 0; s0 < T.nshards; s0 += 32) {
+      const uint32_t s = s0 + lane;
+      uint64_t c = s < T.nshards ? cnt[(uint64_t)s * C + q] : 0;
       if (c > max_hits) c = max_hits;
-      const uint64_t first = lo[(uint64_t)s * C + q];
-      const uint32_t* __restrict__ rid = T.rid[s];
-      const uint4* __restrict__ sets = T.sets[s];
-      const uint64_t tag = T.tag[s];
-      for (uint64_t j = lane; j < c; j += 32) {
-        uint64_t r = rid[first + j];
-        if (r == RS_RID_NONE) r = rs_pop_walk_one(T.views, s, T.sai, first + j, T.max_steps);
-        if (off + j < capacity) hits[off + j] = r == ~0ull ? ~0ull : (tag | r);
-        if (want_carriers && sets && r != ~0ull) {
-          const uint4 v = __ldg(sets + r);
-          b0 |= v.x;
-          b1 |= v.y;
-          b2 |= v.z;
-          b3 |= v.w;
+      uint64_t incl = c;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) {
+        const uint64_t t = __shfl_up_sync(RS_FULL, incl, d);
+        if ((int)lane >= d) incl += t;
+      }
+      const uint64_t total = __shfl_sync(RS_FULL, incl, 31);
+      if (total == 0) continue;
+      const uint64_t mine = off + incl - c; /* where this lane's shard starts in the query's list */
+      const uint64_t first = c ? lo[(uint64_t)s * C + q] : 0;
+      if (c && c <= RS_GATHER_LANE_ROWS) {
+        const uint32_t* __restrict__ rid = T.rid[s];
+        const uint4* __restrict__ sets = T.sets[s];
+        const uint64_t tag = T.tag[s];
+        for (uint32_t j = 0; j < (uint32_t)c; ++j) {
+          uint64_t r = rid[first + j];
+          if (r == RS_RID_NONE) r = rs_pop_walk_one(T.views, s, T.sai, first + j, T.max_steps);
+          if (mine + j < capacity) hits[mine + j] = r == ~0ull ? ~0ull : (tag | r);
+          if (want_carriers && sets && r != ~0ull) {
+            const uint4 v = __ldg(sets + r);
+            b0 |= v.x;
+            b1 |= v.y;
+            b2 |= v.z;
+            b3 |= v.w;
+          }
         }
       }
-      off += c;
+      /* long intervals (a repeat, a short k): the whole warp reads the rows of one shard, coalesced */
+      uint32_t big = __ballot_sync(RS_FULL, c > RS_GATHER_LANE_ROWS);
+      while (big) {
+        const int src = __ffs((int)big) - 1;
+        big &= big - 1;
+        const uint64_t bc = __shfl_sync(RS_FULL, c, src), bfirst = __shfl_sync(RS_FULL, first, src),
+                       bmine = __shfl_sync(RS_FULL, mine, src);
+        const uint32_t bs = s0 + (uint32_t)src;
+        const uint32_t* __restrict__ rid = T.rid[bs];
+        const uint4* __restrict__ sets = T.sets[bs];
+        const uint64_t tag = T.tag[bs];
+        for (uint64_t j = lane; j < bc; j += 32) {
+          uint64_t r = rid[bfirst + j];
+          if (r == RS_RID_NONE) r = rs_pop_walk_one(T.views, bs, T.sai, bfirst + j, T.max_steps);
+          if (bmine + j < capacity) hits[bmine + j] = r == ~0ull ? ~0ull : (tag | r);
+          if (want_carriers && sets && r != ~0ull) {
+            const uint4 v = __ldg(sets + r);
+            b0 |= v.x;
+            b1 |= v.y;
+            b2 |= v.z;
+            b3 |= v.w;
+          }
+        }
+      }
+      off += total;
     }
     if (want_carriers) {
       b0 = __reduce_or_sync(RS_FULL, b0);

@@ -6,7 +6,7 @@ import subprocess
 import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-TINY = ["--genome", "20000", "--reads", "6000", "--queries", "2000", "--steps", "2", "--warmup", "1"]
+TINY = ["--genome", "200000", "--samples", "4", "--coverage", "12", "--queries", "3000", "--steps", "2", "--warmup", "1"]
 
 
 def test_reference_arm_prints_one_json_line():
@@ -21,7 +21,8 @@ def test_reference_arm_prints_one_json_line():
     assert d["cpu_baseline"]["kind"] in ("reference", "port") and d["cpu_baseline"]["cores"] >= 1
     assert d["cpu_baseline"]["value"] == d["value"] and d["e2e"]["value"] == d["value"]
     assert d["e2e"]["h2d_bytes_per_step"] == 0 and d["e2e"]["d2h_bytes_per_step"] == 0
-    assert "workload" in d["config"] and d["metric"].startswith("31-mer")
+    assert "workload" in d["config"] and d["metric"].startswith("31-mer") and "count+locate" in d["metric"]
+    assert d["config"]["workload"].startswith("configs[2]") and d["config"]["shards"] == 64
 
 
 def test_our_arm_needs_a_device():
