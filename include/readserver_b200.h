@@ -58,7 +58,7 @@ typedef struct rs_index_info {
   int32_t q2_safe;       /* 0: the reference would read m_vSum out of bounds   */
   int32_t device;        /* CUDA device ordinal                                               */
   int32_t prefix_table_k; /* length of the k-mer suffix table (0 = none)                      */
-  int32_t reserved_;
+  int32_t dense_blocks;   /* 1: dense rank blocks are built (rs_index_set_dense)              */
 } rs_index_info;
 
 /* ---- lifecycle -------------------------------------------------------------------------------- */
@@ -85,7 +85,7 @@ int rs_index_from_runs_host(const uint8_t* runs, uint64_t num_runs, uint64_t num
 int rs_index_save(const rs_index* ix, const char* path);
 int rs_index_open_encoded(const char* path, int device, rs_index** out);
 /* Copy of one device array of the index (0 blocks, 1 position directory, 2..6 select directory of $,A,C,G,T,
- * 7 k-mer suffix table): *bytes = its size; copied when buf != NULL and capacity suffices. */
+ * 7 k-mer suffix table, 8 dense rank blocks): *bytes = its size; copied when buf != NULL and capacity suffices. */
 int rs_index_export(const rs_index* ix, int what, void* buf, uint64_t capacity, uint64_t* bytes);
 void rs_index_close(rs_index* ix);
 int rs_index_get_info(const rs_index* ix, rs_index_info* info);
@@ -95,6 +95,15 @@ int rs_index_set_tail_emulation(rs_index* ix, int on);
  * 4^k strings of length k, so that findInterval starts k-1 steps in.  Built automatically at open
  * (k <= 10, at most a quarter of the blocks' size; RS_B200_FTAB=k overrides); k = 0 drops it. */
 int rs_index_set_prefix_table(rs_index* ix, int k);
+/* Dense rank blocks, no reference counterpart (results do not depend on them): the BWT once more as 128 symbols per
+ * 64-byte block in three bit planes with the four base counts in front -- addressed by position alone, so a rank
+ * (getOcc) or access (getChar) is ONE memory access and a few logic + popcount instructions instead of a directory
+ * word, a run block and a scan over 36 run bytes.  0.5 bytes per BWT symbol beside the run blocks, which keep
+ * serving select (getOccAt) and the reference's rule for bytes outside "$ACGT".  Built automatically at open when
+ * they cost at most twice the run blocks -- runs of ~7 symbols or shorter, as in the shards of a read-partitioned
+ * population -- and every base occurs fewer than 2^32 times (RS_B200_DENSE = 0 / 1 in the environment: never /
+ * whenever possible); on = 0 drops them. */
+int rs_index_set_dense(rs_index* ix, int on);
 /* Locate table, no reference counterpart (results do not depend on it): for every BWT row, where
  * extractPrefix's walk from it ends and after how many bases, found once by walking every read from its
  * terminator (n LF steps in one kernel).  With it the locate stage (rs_extract_prefix_batch without bases,

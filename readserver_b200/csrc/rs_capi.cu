@@ -48,6 +48,62 @@ static int build_ftab(rs_index* ix, uint32_t t) {
   return RS_STATUS_OK;
 }
 
+/* Dense rank blocks (rs_layout.h): 0.5 bytes per symbol beside the run blocks; rank and access then need one memory
+ * access and a few instructions.  RS_B200_DENSE = 0 never, 1 always; default: when they cost at most twice the run
+ * blocks (runs of ~7 symbols or shorter) and every base occurs fewer than 2^32 times. */
+static int drop_dense(rs_index* ix) {
+  if (ix->d_dense) {
+    CU(cudaStreamSynchronize(ix->stream));
+    cudaFree(ix->d_dense);
+    ix->hbm_bytes -= ix->dense_bytes;
+    ix->d_dense = nullptr;
+    ix->dense_bytes = 0;
+  }
+  ix->dev.dense = nullptr;
+  return RS_STATUS_OK;
+}
+static int build_dense(rs_index* ix) {
+  int rc = drop_dense(ix);
+  if (rc != RS_STATUS_OK) return rc;
+  for (int c = 1; c < RS_NSYM; ++c)
+    if (ix->dev.tot[c] >> 32) return fail(RS_STATUS_TOO_LARGE, "dense rank blocks need fewer than 2^32 occurrences of each base");
+  const uint64_t nd = (ix->dev.n + RS_DENSE_SYMS - 1) >> RS_DENSE_SHIFT;
+  unsigned int* d_bad = nullptr;
+  unsigned int bad = 0;
+  CU(cudaMalloc(&ix->d_dense, (nd ? nd : 1) * 64));
+  cudaError_t e = cudaMalloc((void**)&d_bad, 4);
+  if (e == cudaSuccess) e = cudaMemsetAsync(d_bad, 0, 4, ix->stream);
+  if (e == cudaSuccess) e = rs_build_dense(ix->dev, nd, ix->d_dense, d_bad, ix->stream);
+  if (e == cudaSuccess) e = cudaMemcpyAsync(&bad, d_bad, 4, cudaMemcpyDeviceToHost, ix->stream);
+  if (e == cudaSuccess) e = cudaStreamSynchronize(ix->stream);
+  if (d_bad) cudaFree(d_bad);
+  if (e != cudaSuccess || bad) {
+    cudaFree(ix->d_dense);
+    ix->d_dense = nullptr;
+    if (e != cudaSuccess) return fail(RS_STATUS_CUDA, "dense rank blocks: %s", cudaGetErrorString(e));
+    return fail(RS_STATUS_TOO_LARGE, "dense rank blocks: a count does not fit 32 bits");
+  }
+  ix->dense_bytes = nd * 64;
+  ix->hbm_bytes += ix->dense_bytes;
+  ix->dev.dense = ix->d_dense;
+  return RS_STATUS_OK;
+}
+static bool auto_dense(const rs_index* ix) {
+  const char* e = getenv("RS_B200_DENSE");
+  if (e && e[0] == '0') return false;
+  for (int c = 1; c < RS_NSYM; ++c)
+    if (ix->dev.tot[c] >> 32) return false;
+  if (e && e[0] == '1') return true;
+  return ix->dev.n / 2 <= 2 * ix->dev.nblocks * (uint64_t)RS_BLOCK_BYTES;
+}
+
+int rs_index_set_dense(rs_index* ix, int on) {
+  if (!ix) return fail(RS_STATUS_ARG, "null index");
+  std::lock_guard<std::mutex> lk(ix->mu);
+  CU(cudaSetDevice(ix->device));
+  return on ? build_dense(ix) : drop_dense(ix);
+}
+
 /* (Re)build or drop the locate table.  Like the suffix table it holds the answers of the semantics in force
  * (reference tail behaviour or exact), so the tail switch rebuilds it. */
 static int drop_locate(rs_index* ix) {
@@ -198,6 +254,10 @@ static int upload(rs_index* ix, const RsHostIndex& h) {
   ix->num_runs = h.num_runs;
   ix->depth = h.depth;
   ix->q2_safe = h.q2_safe;
+  if (auto_dense(ix)) {
+    const int rc = build_dense(ix);
+    if (rc != RS_STATUS_OK) return rc;
+  }
   return build_ftab(ix, auto_ftab_k(ix));
 }
 
@@ -260,7 +320,8 @@ int rs_index_from_runs_dev(const void* d_runs, uint64_t num_runs, uint64_t num_s
     else if (erc != RS_OK) rc = fail(erc, "cannot build index from run bytes (status %d)", erc);
     else {
       adopt(ix, enc, num_strings, num_runs);
-      rc = build_ftab(ix, auto_ftab_k(ix));
+      rc = auto_dense(ix) ? build_dense(ix) : RS_STATUS_OK;
+      if (rc == RS_STATUS_OK) rc = build_ftab(ix, auto_ftab_k(ix));
     }
   }
   if (rc != RS_STATUS_OK) {
@@ -498,7 +559,8 @@ int rs_index_open_encoded(const char* path, int device, rs_index** out) {
     ix->depth = h.depth;
     ix->q2_safe = h.q2_safe != 0;
     rs_view_set_tail(ix->init_occ_ref, true, &ix->dev);
-    rc = build_ftab(ix, auto_ftab_k(ix));
+    rc = auto_dense(ix) ? build_dense(ix) : RS_STATUS_OK;
+    if (rc == RS_STATUS_OK) rc = build_ftab(ix, auto_ftab_k(ix));
   }
   if (rc != RS_STATUS_OK) {
     rs_index_close(ix);
@@ -519,6 +581,7 @@ int rs_index_export(const rs_index* ix, int what, void* buf, uint64_t capacity, 
   else if (what == 1) { d = ix->d_dir; n = ix->ndir * 8; }
   else if (what >= 2 && what <= 6) { d = ix->d_sel[what - 2]; n = ix->nsel[what - 2] * 4; }
   else if (what == 7) { d = ix->d_ftab; n = ix->d_ftab ? (16ull << (2 * ix->dev.ftab_k)) : 0; }
+  else if (what == 8) { d = ix->d_dense; n = ix->dense_bytes; }
   else return fail(RS_STATUS_ARG, "unknown array %d", what);
   *bytes = n;
   if (!buf) return RS_STATUS_OK;
@@ -544,6 +607,7 @@ void rs_index_close(rs_index* ix) {
   if (ix->d_samp_meta) cudaFree(ix->d_samp_meta);
   if (ix->d_stats) cudaFree(ix->d_stats);
   if (ix->d_ftab) cudaFree(ix->d_ftab);
+  if (ix->d_dense) cudaFree(ix->d_dense);
   if (ix->d_loc) cudaFree(ix->d_loc);
   if (ix->d_loc_fin) cudaFree(ix->d_loc_fin);
   if (ix->d_loc_mark) cudaFree(ix->d_loc_mark);
@@ -586,6 +650,7 @@ int rs_index_get_info(const rs_index* ix, rs_index_info* info) {
   info->q2_safe = ix->q2_safe ? 1 : 0;
   info->device = ix->device;
   info->prefix_table_k = (int32_t)ix->dev.ftab_k;
+  info->dense_blocks = ix->d_dense ? 1 : 0;
   return RS_STATUS_OK;
 }
 

@@ -90,6 +90,8 @@ struct rs_index {
   uint64_t* d_loc_rank = nullptr;
   uint32_t loc_max_len = 0, loc_every = 0;
   uint64_t loc_bytes = 0;
+  void* d_dense = nullptr;    /* dense rank blocks (rs_layout.h), optional */
+  uint64_t dense_bytes = 0;
   uint64_t* d_ftab = nullptr; /* k-mer suffix table (rs_layout.h), 4^ftab_k pairs */
   uint64_t* d_stats = nullptr; /* [0] updateInterval steps, [1] LF-walk steps; null unless profiling is on */
   cudaStream_t stream = nullptr;

@@ -309,6 +309,102 @@ __global__ void __launch_bounds__(RS_THREADS, RS_K1_BLOCKS)
   if (stats && nsteps) atomicAdd(stats, (unsigned long long)nsteps);
 }
 
+/* K1 over the dense rank blocks (rs_layout.h), packed queries.  A step (updateInterval, query.cpp:11-15) is one trip:
+ * the blocks of lower-1 and upper are addressed by position alone, so both loads issue at once (no directory word, no
+ * second trip for a step that spans two blocks) and each rank is a few logic + popcount instructions.  Lanes whose
+ * query has ended wait until RS_REFILL_MIN of the warp's lanes are idle: the set-up path (key, suffix table, emit) then
+ * runs for several lanes at once instead of for one lane on almost every trip. */
+#ifndef RS_K1D_BLOCKS
+#define RS_K1D_BLOCKS 4
+#endif
+#ifndef RS_REFILL_MIN
+#define RS_REFILL_MIN 6
+#endif
+template <bool FTAB>
+__global__ void __launch_bounds__(RS_THREADS, RS_K1D_BLOCKS)
+    k_find_interval_dense(const __grid_constant__ rs_index_dev ix, uint32_t k, uint64_t Q, const uint64_t* pkeys,
+                          uint64_t* lower, uint64_t* __restrict__ upper, int mode, int strand,
+                          unsigned long long* __restrict__ stats, const __grid_constant__ rs_peers peers) {
+  const uint64_t stride = (uint64_t)gridDim.x * RS_THREADS;
+  uint64_t next_q = (uint64_t)blockIdx.x * RS_THREADS + threadIdx.x;
+  uint64_t lo = 0, hi = 0, pk = 0;
+  int32_t j = -1;
+  bool active = false;
+  const bool rc = (mode >= 1 && mode != 4 && strand == 1);
+  uint32_t nsteps = 0;
+  while (true) {
+    const uint32_t idle = __ballot_sync(RS_FULL, !active);
+    if (idle == RS_FULL || __popc(idle) >= RS_REFILL_MIN) {
+      if (!active && next_q < Q) {
+        const uint64_t q = next_q;
+        next_q += stride;
+        pk = pkeys[q];
+        active = true;
+        if (pk >> 63) { /* a byte outside ACGT */
+          if (mode == 1) lower[q] = 0; /* service.cpp:299-301; mode 2: nothing to add */
+          if (mode == 4) { lower[q] = 1; reinterpret_cast<uint32_t*>(upper)[q] = 0; }
+          active = false; /* mode 0: left flagged for k_search_flagged */
+        } else {
+          const uint32_t c0 = (uint32_t)(pk & 3u) + 1u; /* initInterval (query.cpp:18-21) on the last character */
+          lo = ix.pc[c0];
+          hi = lo + ix.init_occ[c0] - 1;
+          j = (int32_t)k - 2;
+          if (FTAB && k >= ix.ftab_k) {
+            const uint32_t t = ix.ftab_k;
+            const ulonglong2 e = __ldg(reinterpret_cast<const ulonglong2*>(ix.ftab) + (pk & ((1ull << (2 * t)) - 1)));
+            lo = e.x;
+            hi = e.y;
+            j = (int32_t)k - (int32_t)t - 1;
+            if (lo > hi) j = -1; /* the search had already stopped inside the suffix (query.cpp:35-37) */
+          }
+          if (j < 0) {
+            rs_emit(mode, lower, upper, peers, q, lo, hi, pk, k, rc);
+            active = false;
+          }
+        }
+      }
+      if (__all_sync(RS_FULL, !active)) {
+        if (__all_sync(RS_FULL, next_q >= Q)) break;
+        continue;
+      }
+    }
+    if (active) {
+      const uint32_t c = (uint32_t)((pk >> (2 * (k - 1 - (uint32_t)j))) & 3u) + 1u;
+      const bool none1 = (lo == 0), none2 = (hi == ~0ull); /* getOcc(b, 2^64-1) = 0 in the reference */
+      uint64_t p1 = none1 ? 0 : rs_ref_pos(ix, lo - 1);
+      uint64_t p2 = none2 ? 0 : rs_ref_pos(ix, hi);
+      if (p1 >= ix.n) p1 = ix.n - 1;
+      if (p2 >= ix.n) p2 = ix.n - 1;
+      const uint64_t b1 = p1 >> RS_DENSE_SHIFT, b2 = p2 >> RS_DENSE_SHIFT;
+      const bool split = b1 != b2;
+      const rs_dblk k1 = rs_load_dense(ix, b1);
+      rs_dblk k2 = k1;
+      if (split) k2 = rs_load_dense(ix, b2); /* issued before anything waits on k1: two blocks in flight */
+      const uint32_t t1 = ((uint32_t)p1 & (RS_DENSE_SYMS - 1u)) + 1u, t2 = ((uint32_t)p2 & (RS_DENSE_SYMS - 1u)) + 1u;
+      uint32_t a1, a2;
+      rs_dense_count2(k1, c, t1, split ? 0u : t2, &a1, &a2);
+      uint64_t before2 = rs_dense_before(k1, b1, c);
+      const uint64_t r1 = none1 ? 0 : before2 + a1;
+      if (split) { /* rare once the interval is narrow: lower-1 and upper then sit in one block */
+        uint32_t unused;
+        rs_dense_count2(k2, c, t2, 0u, &a2, &unused);
+        before2 = rs_dense_before(k2, b2, c);
+      }
+      const uint64_t r2 = none2 ? 0 : before2 + a2;
+      ++nsteps;
+      const uint64_t pb = ix.pc[c];
+      lo = pb + r1;
+      hi = pb + r2 - 1;
+      --j;
+      if (lo > hi || j < 0) {
+        rs_emit(mode, lower, upper, peers, next_q - stride, lo, hi, pk, k, rc);
+        active = false;
+      }
+    }
+  }
+  if (stats && nsteps) atomicAdd(stats, (unsigned long long)nsteps);
+}
+
 /* K1b.  The rare queries K1 left flagged (bit 63 of lower[q]: a byte outside "$ACGT"), one whole findInterval
  * each, as the reference answers them (rs_find_interval_one).  A kernel of its own so that this path costs K1's
  * loop no registers; when nothing is flagged it reads lower[] once (8 bytes per query, still in L2) and ends. */
@@ -719,7 +815,10 @@ cudaError_t rs_launch_find_interval(const rs_index_dev& ix, const uint8_t* text,
     if (!packed_already)
       k_pack_kmers<<<(unsigned)((Q + RS_THREADS - 1) / RS_THREADS), RS_THREADS, 0, st>>>(text, k, Q, mode >= 1 && strand == 1,
                                                                                      lower);
-    if (ftab) RS_LAUNCH((k_find_interval<true, true>), Q, st, ix, text, offs, k, Q, lower, lower, upper, mode, strand, stats, peers);
+    if (ix.dense) {
+      if (ftab) RS_LAUNCH((k_find_interval_dense<true>), Q, st, ix, k, Q, lower, lower, upper, mode, strand, stats, peers);
+      else RS_LAUNCH((k_find_interval_dense<false>), Q, st, ix, k, Q, lower, lower, upper, mode, strand, stats, peers);
+    } else if (ftab) RS_LAUNCH((k_find_interval<true, true>), Q, st, ix, text, offs, k, Q, lower, lower, upper, mode, strand, stats, peers);
     else RS_LAUNCH((k_find_interval<false, true>), Q, st, ix, text, offs, k, Q, lower, lower, upper, mode, strand, stats, peers);
   } else {
     if (ftab) RS_LAUNCH((k_find_interval<true, false>), Q, st, ix, text, offs, k, Q, lower, lower, upper, mode, strand, stats, peers);
@@ -753,7 +852,10 @@ cudaError_t rs_launch_find_interval_packed(const rs_index_dev& ix, const uint64_
   if (peers_in) peers = *peers_in;
   const bool ftab = ix.ftab && ix.ftab_k > 1;
   uint64_t* up = reinterpret_cast<uint64_t*>(rows);
-  if (ftab) RS_LAUNCH((k_find_interval<true, true>), Q, st, ix, nullptr, nullptr, k, Q, pkeys, first, up, mode, 0, stats, peers);
+  if (ix.dense) {
+    if (ftab) RS_LAUNCH((k_find_interval_dense<true>), Q, st, ix, k, Q, pkeys, first, up, mode, 0, stats, peers);
+    else RS_LAUNCH((k_find_interval_dense<false>), Q, st, ix, k, Q, pkeys, first, up, mode, 0, stats, peers);
+  } else if (ftab) RS_LAUNCH((k_find_interval<true, true>), Q, st, ix, nullptr, nullptr, k, Q, pkeys, first, up, mode, 0, stats, peers);
   else RS_LAUNCH((k_find_interval<false, true>), Q, st, ix, nullptr, nullptr, k, Q, pkeys, first, up, mode, 0, stats, peers);
   return cudaGetLastError();
 }
@@ -899,5 +1001,58 @@ cudaError_t rs_launch_extract_postfix(const rs_index_dev& ix, const uint64_t* ro
                                       uint64_t* read_index, uint32_t* steps, uint8_t* bases, cudaStream_t st) {
   if (!n) return cudaSuccess;
   RS_LAUNCH(k_extract_postfix, n, st, ix, rows, n, max_steps, read_index, steps, bases);
+  return cudaGetLastError();
+}
+
+/* Dense rank blocks from the run blocks: one thread per dense block.  Header = exact ranks at the block's first
+ * position (through the run blocks); planes = the 128 symbols, decoded run by run. */
+__global__ void __launch_bounds__(RS_THREADS)
+    k_dense_build(const __grid_constant__ rs_index_dev ix, uint64_t ndense, uint4* __restrict__ out, unsigned int* __restrict__ bad) {
+  const uint64_t stride = (uint64_t)gridDim.x * RS_THREADS;
+  for (uint64_t b = (uint64_t)blockIdx.x * RS_THREADS + threadIdx.x; b < ndense; b += stride) {
+    const uint64_t P0 = b << RS_DENSE_SHIFT;
+    uint32_t cnt[4] = {0, 0, 0, 0}, p0[4] = {0, 0, 0, 0}, p1[4] = {0, 0, 0, 0}, p2[4] = {0, 0, 0, 0};
+    if (P0) {
+      for (uint32_t c = 1; c <= 4; ++c) {
+        const uint64_t r = rs_rank(ix, c, P0 - 1);
+        if (r >> 32) atomicOr(bad, 1u);
+        cnt[c - 1] = (uint32_t)r;
+      }
+    }
+    uint64_t pos = P0;
+    const uint64_t end = P0 + RS_DENSE_SYMS < ix.n ? P0 + RS_DENSE_SYMS : ix.n;
+    uint64_t rb = rs_find_block(ix, pos);
+    while (pos < end) {
+      const uint8_t* p = rs_block_ptr(ix, rb);
+      uint64_t at = rs_ld64(reinterpret_cast<const uint64_t*>(p)); /* first symbol of the run in hand */
+      for (uint32_t t = 0; t < RS_PAYLOAD && pos < end; ++t) {
+        const uint32_t v = p[RS_HDR_BYTES + t], len = v & 31u, sym = v >> 5;
+        if (!len) break; /* padding of the last block */
+        const uint64_t stop = at + len;
+        while (pos < stop && pos < end) { /* pos >= at: the block was found by position */
+          const uint32_t i = (uint32_t)(pos - P0), w = i >> 5, bit = 1u << (i & 31u);
+          if (sym == 0) p2[w] |= bit;
+          else {
+            if ((sym - 1u) & 1u) p0[w] |= bit;
+            if ((sym - 1u) & 2u) p1[w] |= bit;
+          }
+          ++pos;
+        }
+        at = stop;
+      }
+      ++rb;
+    }
+    out[4 * b + 0] = make_uint4(cnt[0], cnt[1], cnt[2], cnt[3]);
+    out[4 * b + 1] = make_uint4(p0[0], p0[1], p0[2], p0[3]);
+    out[4 * b + 2] = make_uint4(p1[0], p1[1], p1[2], p1[3]);
+    out[4 * b + 3] = make_uint4(p2[0], p2[1], p2[2], p2[3]);
+  }
+}
+
+cudaError_t rs_build_dense(const rs_index_dev& ix_in, uint64_t ndense, void* out, unsigned int* bad, cudaStream_t st) {
+  rs_index_dev ix = ix_in;
+  ix.dense = nullptr; /* built FROM the run blocks */
+  if (!ndense) return cudaSuccess;
+  RS_LAUNCH(k_dense_build, ndense, st, ix, ndense, reinterpret_cast<uint4*>(out), bad);
   return cudaGetLastError();
 }

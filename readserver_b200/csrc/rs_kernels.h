@@ -58,6 +58,9 @@ cudaError_t rs_launch_occ_at(const rs_index_dev& ix, const uint8_t* syms, const 
 cudaError_t rs_launch_extract_postfix(const rs_index_dev& ix, const uint64_t* rows, uint64_t n, uint32_t max_steps,
                                       uint64_t* read_index, uint32_t* steps, uint8_t* bases, cudaStream_t st);
 
+/* dense rank blocks (rs_layout.h) from the run blocks; *bad |= 1 when a count does not fit 32 bits */
+cudaError_t rs_build_dense(const rs_index_dev& ix, uint64_t ndense, void* out, unsigned int* bad, cudaStream_t st);
+
 /* rs_pipeline.cu */
 cudaError_t rs_scan_bytes(uint64_t n, size_t* bytes);
 cudaError_t rs_exclusive_scan(const uint64_t* counts, uint64_t* offsets, uint64_t n, void* tmp, size_t tmp_bytes,

@@ -98,6 +98,20 @@ typedef struct rs_index_dev {
   const uint64_t* loc_mark;
   const uint64_t* loc_rank;
   uint32_t loc_every; /* 0: no table, 1: full table, > 1: sampled */
+  /* Dense rank blocks, optional (null = not built): the same BWT once more, 128 symbols per 64-byte block as three
+   * bit planes, addressed by position alone (block = pos >> 7: no directory, one memory access per rank) and ranked
+   * with a handful of logic + popcount instructions instead of a scan over run bytes.  0.5 bytes per symbol: built
+   * beside the run blocks when runs are short (a shard of a read-partitioned population: ~3 symbols per run, where
+   * the run blocks cost 0.52 bytes per symbol themselves) or when the caller asks for it; rank and access use it,
+   * select and the reference's stray-byte rule keep using the run blocks.
+   *   +0   u32 cnt[4]   occurrences of A,C,G,T before the block (shards with < 2^32 of each)
+   *   +16  u32 p0[4]    bit i of word w: low  bit of (code - 1) of symbol 32 w + i   (0 for '$')
+   *   +32  u32 p1[4]                     high bit
+   *   +48  u32 p2[4]                     1 = the symbol is '$' */
+  const void* dense;
 } rs_index_dev;
+
+#define RS_DENSE_SHIFT 7
+#define RS_DENSE_SYMS 128u
 
 #endif

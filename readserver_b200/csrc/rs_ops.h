@@ -150,8 +150,85 @@ RS_HD void rs_scan2(const rs_index_dev& ix, uint32_t c, uint64_t b, uint64_t p1,
   *x2 = before + a2;
 }
 
+/* ---- dense rank blocks (rs_layout.h) ---- */
+struct rs_dblk {
+  uint32_t cnt[4], p0[4], p1[4], p2[4];
+};
+
+RS_HD rs_dblk rs_load_dense(const rs_index_dev& ix, uint64_t b) {
+  const uint8_t* p = reinterpret_cast<const uint8_t*>(ix.dense) + b * 64;
+  const rs_u4 v0 = rs_ld128(p), v1 = rs_ld128(p + 16), v2 = rs_ld128(p + 32), v3 = rs_ld128(p + 48);
+  rs_dblk k;
+  k.cnt[0] = v0.x; k.cnt[1] = v0.y; k.cnt[2] = v0.z; k.cnt[3] = v0.w;
+  k.p0[0] = v1.x; k.p0[1] = v1.y; k.p0[2] = v1.z; k.p0[3] = v1.w;
+  k.p1[0] = v2.x; k.p1[1] = v2.y; k.p1[2] = v2.z; k.p1[3] = v2.w;
+  k.p2[0] = v3.x; k.p2[1] = v3.y; k.p2[2] = v3.z; k.p2[3] = v3.w;
+  return k;
+}
+
+/* bits of plane word w that belong to the first t symbols of the block (0 <= t <= 128) */
+RS_HD uint32_t rs_dense_mask(uint32_t t, uint32_t w) {
+  const int32_t k = (int32_t)t - (int32_t)(32u * w);
+  return k <= 0 ? 0u : (k >= 32 ? 0xFFFFFFFFu : ((1u << k) - 1u));
+}
+
+RS_HD uint32_t rs_popc(uint32_t x) {
+#if defined(__CUDA_ARCH__)
+  return (uint32_t)__popc(x);
+#else
+  return (uint32_t)__builtin_popcount(x);
+#endif
+}
+
+/* occurrences of c (1..4) among the first t1 / t2 symbols of the block; c = 0 counts the '$' */
+RS_HD void rs_dense_count2(const rs_dblk& k, uint32_t c, uint32_t t1, uint32_t t2, uint32_t* r1, uint32_t* r2) {
+  const uint32_t cc = c - 1u;
+  const uint32_t m0 = (cc & 1u) ? 0u : 0xFFFFFFFFu, m1 = (cc & 2u) ? 0u : 0xFFFFFFFFu;
+  uint32_t a1 = 0, a2 = 0;
+#pragma unroll
+  for (uint32_t w = 0; w < 4; ++w) {
+    const uint32_t hit = c ? ((k.p0[w] ^ m0) & (k.p1[w] ^ m1) & ~k.p2[w]) : k.p2[w];
+    a1 += rs_popc(hit & rs_dense_mask(t1, w));
+    a2 += rs_popc(hit & rs_dense_mask(t2, w));
+  }
+  *r1 = a1;
+  *r2 = a2;
+}
+
+/* occurrences of c (0..4) before dense block b, from its header ('$' = symbols - the four bases) */
+RS_HD uint64_t rs_dense_before(const rs_dblk& k, uint64_t b, uint32_t c) {
+  if (c) return c == 1 ? k.cnt[0] : c == 2 ? k.cnt[1] : c == 3 ? k.cnt[2] : k.cnt[3];
+  return (b << RS_DENSE_SHIFT) - ((uint64_t)k.cnt[0] + k.cnt[1] + k.cnt[2] + k.cnt[3]);
+}
+
+RS_HD uint64_t rs_dense_rank(const rs_index_dev& ix, uint32_t c, uint64_t pos) {
+  const uint64_t b = pos >> RS_DENSE_SHIFT;
+  const rs_dblk k = rs_load_dense(ix, b);
+  uint32_t a, unused;
+  rs_dense_count2(k, c, ((uint32_t)pos & (RS_DENSE_SYMS - 1u)) + 1u, 0u, &a, &unused);
+  return rs_dense_before(k, b, c) + a;
+}
+
+/* symbol at pos and (when rank != null) its rank at pos, from one dense block */
+RS_HD uint32_t rs_dense_symbol_rank(const rs_index_dev& ix, uint64_t pos, uint64_t* rank) {
+  const uint64_t b = pos >> RS_DENSE_SHIFT;
+  const rs_dblk k = rs_load_dense(ix, b);
+  const uint32_t i = (uint32_t)pos & (RS_DENSE_SYMS - 1u), w = i >> 5, bit = i & 31u;
+  const uint32_t q0 = w == 0 ? k.p0[0] : w == 1 ? k.p0[1] : w == 2 ? k.p0[2] : k.p0[3];
+  const uint32_t q1 = w == 0 ? k.p1[0] : w == 1 ? k.p1[1] : w == 2 ? k.p1[2] : k.p1[3];
+  const uint32_t q2 = w == 0 ? k.p2[0] : w == 1 ? k.p2[1] : w == 2 ? k.p2[2] : k.p2[3];
+  const uint32_t sym = ((q2 >> bit) & 1u) ? 0u : 1u + ((q0 >> bit) & 1u) + 2u * ((q1 >> bit) & 1u);
+  if (rank) {
+    uint32_t a, unused;
+    rs_dense_count2(k, sym, i + 1u, 0u, &a, &unused);
+    *rank = rs_dense_before(k, b, sym) + a;
+  }
+  return sym;
+}
+
 /* True rank: occurrences of c in BWT[0..pos], pos < n. */
 RS_HD uint64_t rs_rank(const rs_index_dev& ix, uint32_t c, uint64_t pos) {
+  if (ix.dense) return rs_dense_rank(ix, c, pos);
   const uint64_t b = rs_find_block(ix, pos);
   const rs_blk k = rs_load_block(ix, b);
   uint32_t a, unused;
@@ -174,6 +251,11 @@ RS_HD void rs_occ2(const rs_index_dev& ix, uint32_t c, uint64_t i1, uint64_t i2,
   uint64_t p2 = none2 ? 0 : rs_ref_pos(ix, i2);
   if (p1 >= ix.n) p1 = ix.n - 1;
   if (p2 >= ix.n) p2 = ix.n - 1;
+  if (ix.dense) {
+    *r1 = none1 ? 0 : rs_dense_rank(ix, c, p1);
+    *r2 = none2 ? 0 : rs_dense_rank(ix, c, p2);
+    return;
+  }
   const uint64_t b1 = rs_find_block(ix, p1), b2 = rs_find_block(ix, p2);
   const bool two = (b1 == b2) && p2 >= p1;
   uint64_t x1, x2;
@@ -261,6 +343,7 @@ RS_HD uint32_t rs_find_interval_one(const rs_index_dev& ix, const uint8_t* w, ui
 
 /* Symbol at pos (< n) and the rank of that symbol at pos, from one block. */
 RS_HD uint32_t rs_symbol_rank(const rs_index_dev& ix, uint64_t pos, uint64_t* rank) {
+  if (ix.dense) return rs_dense_symbol_rank(ix, pos, rank);
   const uint64_t b = rs_find_block(ix, pos);
   const rs_blk k = rs_load_block(ix, b);
   const int32_t t = (int32_t)((uint32_t)(pos - k.start) + 1u);

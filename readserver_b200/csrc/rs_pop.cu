@@ -145,7 +145,7 @@ __global__ void k_pop_advance(const uint64_t* __restrict__ local, uint64_t nq, u
 __device__ __noinline__ uint64_t rs_pop_walk_one(const rs_index_dev* __restrict__ views, uint32_t s,
                                                  const uint64_t* const* __restrict__ sais, uint64_t row,
                                                  uint32_t max_steps) {
-  const rs_index_dev ix = views[s];
+  const rs_index_dev& ix = views[s]; /* fields read from global memory as needed: this path is rare */
   uint64_t idx = row;
   for (uint32_t st = 0; st <= max_steps; ++st) {
     uint64_t nxt;
@@ -210,7 +210,10 @@ __global__ void k_pop_owner_slots(const __grid_constant__ rs_pop_peers P, const 
  * owns the query (P.world > 1: over NVLink peer memory, at the slot the owner assigned to this rank -- locate and the
  * fan-in of the hit lists, server.cpp:184-197, are one kernel), the sample set is OR-ed into the owner's bitmap. */
 #define RS_GATHER_LANE_ROWS 8u /* intervals up to this many rows are read by one lane; longer ones by the whole warp */
-__global__ void __launch_bounds__(256)
+#ifndef RS_GATHER_BLOCKS
+#define RS_GATHER_BLOCKS 4 /* resident CTAs per SM: the kernel waits on memory, occupancy is its parallelism */
+#endif
+__global__ void __launch_bounds__(256, RS_GATHER_BLOCKS)
     k_pop_gather(const __grid_constant__ rs_pop_tables T, const __grid_constant__ rs_pop_peers P,
                  const uint64_t* __restrict__ keys, uint32_t k, const uint64_t* __restrict__ lo,
                  const uint32_t* __restrict__ cnt, uint64_t C, uint64_t q0, uint64_t nq, uint64_t max_hits,
@@ -936,7 +939,7 @@ static int pop_run(rs_shardset* set, rs_popcomm* comm, const void* d_kmers, int 
     const uint64_t* slot = P.slot[multi ? comm->rank : 0];
     StageTimer tm_locate(set, st, RS_POP_STAGE_LOCATE, table ? 1 : 5 * S + 1);
     if (table) {
-      k_pop_gather<<<grid_for(nq * 32, 256, 148 * 8), 256, 0, st>>>(set->tab, P, keys + q0, (uint32_t)k, lo, cnt, C, q0, nq, max_hits,
+      k_pop_gather<<<grid_for(nq * 32, 256, 148 * 2 * RS_GATHER_BLOCKS), 256, 0, st>>>(set->tab, P, keys + q0, (uint32_t)k, lo, cnt, C, q0, nq, max_hits,
                                                                  slot, capacity, (want_carr && set->have_sets) ? 1 : 0);
       CU(cudaGetLastError());
       if (want_carr && !set->have_sets) {

@@ -38,7 +38,7 @@ class Info(C.Structure):
                 ("num_blocks", C.c_uint64), ("hbm_bytes", C.c_uint64), ("pc", C.c_uint64 * 5),
                 ("total", C.c_uint64 * 5), ("ref_depth", C.c_uint64), ("ref_clamp_c", C.c_uint64),
                 ("ref_vlast", C.c_uint64), ("q2_safe", C.c_int32), ("device", C.c_int32),
-                ("prefix_table_k", C.c_int32), ("reserved_", C.c_int32)]
+                ("prefix_table_k", C.c_int32), ("dense_blocks", C.c_int32)]
 
 
 class ShardSetInfo(C.Structure):
@@ -95,6 +95,7 @@ def lib() -> C.CDLL:
         "rs_index_get_info": (i32, [vp, C.POINTER(Info)]),
         "rs_index_set_tail_emulation": (i32, [vp, i32]),
         "rs_index_set_prefix_table": (i32, [vp, i32]),
+        "rs_index_set_dense": (i32, [vp, i32]),
         "rs_index_enable_stats": (i32, [vp, i32]),
         "rs_index_read_stats": (i32, [vp, C.POINTER(u64), C.POINTER(u64), i32]),
         "rs_measure_random_access": (i32, [i32, u64, u64, C.POINTER(C.c_double)]),
@@ -228,6 +229,11 @@ class GpuBWT:
     def set_prefix_table(self, k: int):
         """(Re)build the k-mer suffix table with k characters; 0 drops it. Results do not depend on it."""
         _check(lib().rs_index_set_prefix_table(self._h, k))
+        _check(lib().rs_index_get_info(self._h, C.byref(self.info)))
+
+    def set_dense(self, on: bool):
+        """Build / drop the dense rank blocks (0.5 bytes per symbol; one memory access per rank). Results do not change."""
+        _check(lib().rs_index_set_dense(self._h, int(on)))
         _check(lib().rs_index_get_info(self._h, C.byref(self.info)))
 
     def enable_stats(self, on: bool = True):

@@ -363,3 +363,103 @@ def test_multi_rank_fan_in_through_peer_memory(locate_every, world):
         outs.append(out)
     for r, (p, out) in enumerate(zip(procs, outs)):
         assert p.returncode == 0 and "POP_WORKER_OK" in out, f"rank {r}:\n{out[-3000:]}"
+
+
+# ------------------------------------------------------------------------------------------------
+# dense rank blocks: same answers, array checked against the plain BWT
+# ------------------------------------------------------------------------------------------------
+def _expected_dense(runs: np.ndarray) -> np.ndarray:
+    sym = np.repeat(runs >> 5, runs & 31).astype(np.int64)
+    n = sym.size
+    nd = (n + 127) // 128
+    pad = np.full(nd * 128, -1, dtype=np.int64)
+    pad[:n] = sym
+    blk = pad.reshape(nd, 4, 32)
+    bit = (np.uint64(1) << np.arange(32, dtype=np.uint64))[None, None, :]
+    def plane(mask):
+        return (mask.astype(np.uint64) * bit).sum(axis=2).astype(np.uint32)
+    p0 = plane((blk >= 1) & (((blk - 1) & 1) == 1))
+    p1 = plane((blk >= 1) & (((blk - 1) & 2) == 2))
+    p2 = plane(blk == 0)
+    cnt = np.zeros((nd, 4), dtype=np.uint32)
+    for c in range(1, 5):
+        per = (pad.reshape(nd, 128) == c).sum(axis=1)
+        cnt[:, c - 1] = np.concatenate([[0], np.cumsum(per)[:-1]]).astype(np.uint32)
+    return np.concatenate([cnt, p0, p1, p2], axis=1).reshape(-1).view(np.uint8)
+
+
+@pytest.mark.parametrize("name", ["tiny", "small", "clean", "mid", "deep"])
+def test_dense_rank_blocks_change_no_answer(name, datasets, engine):
+    case, P = datasets.case(name), datasets.port(name)
+    kw = dict(num_strings=case.num_strings, num_symbols=case.num_symbols)
+    with engine.GpuBWT(runs=case.runs, **kw) as B, engine.GpuBWT(runs=case.runs, **kw) as D:
+        B.set_dense(False)
+        D.set_dense(True)
+        assert D.info.dense_blocks == 1 and B.info.dense_blocks == 0
+        assert np.array_equal(D.export(8), _expected_dense(case.runs))
+        B.set_sai(case.sai)
+        D.set_sai(case.sai)
+        for tail in (True, False):
+            B.set_tail_emulation(tail)
+            D.set_tail_emulation(tail)
+            assert D.info.dense_blocks == 1
+            assert np.array_equal(B.export(7), D.export(7))          # the suffix tables agree
+            idx = np.concatenate([common.positions(P.bwlen), np.array([U64MAX], dtype=np.uint64)])
+            for c in b"$ACGTN\xff":
+                s = np.full(idx.size, c, dtype=np.uint8)
+                got = D.get_occ(s, idx)
+                assert np.array_equal(got, B.get_occ(s, idx)), (chr(c), tail)
+                if tail:
+                    assert np.array_equal(got, P.get_occ_batch(s, idx)), chr(c)
+            assert np.array_equal(D.get_char(idx[:-1]), B.get_char(idx[:-1]))
+            for k in (1, 2, 12, 31, 73):
+                q = case.queries(20000 if k == 31 else 3000, k, seed=40 + k)
+                if k <= 31:
+                    q[::97, k // 2] = ord("N")                       # flagged queries take the stray-byte path
+                a, b = D.find_interval(q, k), B.find_interval(q, k)
+                assert np.array_equal(a[0], b[0]) and np.array_equal(a[1], b[1]), (k, tail)
+                if tail:
+                    lo2, up2 = P.find_interval_batch(q, k, nthreads=4)
+                    assert np.array_equal(a[0], lo2) and np.array_equal(a[1], up2), k
+                for strand in (0, 1):
+                    assert np.array_equal(D.count(q, k, strand), B.count(q, k, strand))
+            q = case.queries(3000, 31, seed=77)
+            lo, up = D.find_interval(q, 31)
+            hit = np.nonzero(up >= lo)[0][:400]
+            if hit.size:
+                rows = np.concatenate([np.arange(lo[i], min(up[i], lo[i] + 20) + 1, dtype=np.uint64) for i in hit])
+                a = D.extract_prefix(rows, max_steps=128, want_read_index=True, want_bases=True)
+                b = B.extract_prefix(rows, max_steps=128, want_read_index=True, want_bases=True)
+                assert all(np.array_equal(x, y) for x, y in zip(a, b)), tail
+                for every in (1, 8):
+                    D.build_locate_table(128, every=every)
+                    c = D.extract_prefix(rows, max_steps=128, want_read_index=True)
+                    assert all(np.array_equal(x, y) for x, y in zip(c, b[:3])), (tail, every)
+                    D.drop_locate_table()
+
+
+def test_dense_blocks_on_degenerate_shapes_and_auto_policy(engine, monkeypatch):
+    rng = np.random.default_rng(5)
+    shapes = {
+        "ones": ((rng.integers(0, 5, 20000) << 5) | 1).astype(np.uint8),            # runs of 1: auto builds dense blocks
+        "single": np.array([(2 << 5) | 17], dtype=np.uint8),
+        "exact128": ((rng.integers(1, 5, 64) << 5) | 2).astype(np.uint8),            # n = 128: one full dense block
+        "long": ((rng.integers(1, 5, 5000) << 5) | 31).astype(np.uint8),             # long runs: auto keeps run blocks only
+    }
+    for name, runs in shapes.items():
+        n = int((runs & 31).sum())
+        ns = int((runs[(runs >> 5) == 0] & 31).sum())
+        with engine.GpuBWT(runs=runs, num_strings=ns, num_symbols=n) as A:
+            assert A.info.dense_blocks == (0 if name == "long" else 1), name
+            A.set_dense(True)
+            assert np.array_equal(A.export(8), _expected_dense(runs)), name
+            P = oracle.PortIndex(runs=runs, num_strings=ns, num_symbols=n)
+            idx = np.arange(n, dtype=np.uint64)
+            for c in b"$ACGT":
+                s = np.full(idx.size, c, dtype=np.uint8)
+                assert np.array_equal(A.get_occ(s, idx), P.get_occ_batch(s, idx)), (name, chr(c))
+            assert np.array_equal(A.get_char(idx), P.get_char_batch(idx)), name
+    monkeypatch.setenv("RS_B200_DENSE", "0")
+    runs = shapes["ones"]
+    with engine.GpuBWT(runs=runs, num_strings=int(((runs >> 5) == 0).sum()), num_symbols=runs.size) as A:
+        assert A.info.dense_blocks == 0
