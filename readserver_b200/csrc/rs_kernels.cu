@@ -12,6 +12,7 @@
 #include <string.h>
 
 #include <mutex>
+#include <type_traits>
 
 #include "rs_ops.h"
 
@@ -315,67 +316,87 @@ __global__ void __launch_bounds__(RS_THREADS, RS_K1_BLOCKS)
  * query has ended wait until RS_REFILL_MIN of the warp's lanes are idle: the set-up path (key, suffix table, emit) then
  * runs for several lanes at once instead of for one lane on almost every trip. */
 #ifndef RS_K1D_BLOCKS
-#define RS_K1D_BLOCKS 4
+#define RS_K1D_BLOCKS 5 /* resident CTAs per SM (4: 137, 5: 129, 6: 165 ms per configs[2] step, spills at 6) */
 #endif
 #ifndef RS_REFILL_MIN
 #define RS_REFILL_MIN 6
 #endif
-template <bool FTAB>
+/* SMALL: the shard holds fewer than 2^31 symbols, so rows and counts live in 32-bit registers (half the ALU work of
+ * the position arithmetic; 2^32-1 stands for the reference's 2^64-1 = "upper bound before row 0"). */
+template <bool FTAB, bool SMALL>
 __global__ void __launch_bounds__(RS_THREADS, RS_K1D_BLOCKS)
     k_find_interval_dense(const __grid_constant__ rs_index_dev ix, uint32_t k, uint64_t Q, const uint64_t* pkeys,
                           uint64_t* lower, uint64_t* __restrict__ upper, int mode, int strand,
-                          unsigned long long* __restrict__ stats, const __grid_constant__ rs_peers peers) {
-  const uint64_t stride = (uint64_t)gridDim.x * RS_THREADS;
-  uint64_t next_q = (uint64_t)blockIdx.x * RS_THREADS + threadIdx.x;
-  uint64_t lo = 0, hi = 0, pk = 0;
+                          unsigned long long* __restrict__ stats, const __grid_constant__ rs_peers peers,
+                          unsigned long long* __restrict__ ticket) {
+  typedef typename std::conditional<SMALL, uint32_t, uint64_t>::type P;
+  const P NONE = (P)~(P)0;
+  const uint32_t lane = threadIdx.x & 31u;
+  uint64_t q = 0, pk = 0;
+  P lo = 0, hi = 0;
   int32_t j = -1;
-  bool active = false;
+  bool active = false, exhausted = false;
   const bool rc = (mode >= 1 && mode != 4 && strand == 1);
   uint32_t nsteps = 0;
+  /* the reference's tail rule (rs_ref_pos) and the clamp to the last row, in the position type */
+  const P tail_from = ix.tail_from > (uint64_t)NONE ? NONE : (P)ix.tail_from;
+  const P tail_pos = (P)(ix.clamp_c - 1), last = (P)(ix.n - 1);
   while (true) {
     const uint32_t idle = __ballot_sync(RS_FULL, !active);
     if (idle == RS_FULL || __popc(idle) >= RS_REFILL_MIN) {
-      if (!active && next_q < Q) {
-        const uint64_t q = next_q;
-        next_q += stride;
-        pk = pkeys[q];
-        active = true;
-        if (pk >> 63) { /* a byte outside ACGT */
-          if (mode == 1) lower[q] = 0; /* service.cpp:299-301; mode 2: nothing to add */
-          if (mode == 4) { lower[q] = 1; reinterpret_cast<uint32_t*>(upper)[q] = 0; }
-          active = false; /* mode 0: left flagged for k_search_flagged */
-        } else {
-          const uint32_t c0 = (uint32_t)(pk & 3u) + 1u; /* initInterval (query.cpp:18-21) on the last character */
-          lo = ix.pc[c0];
-          hi = lo + ix.init_occ[c0] - 1;
-          j = (int32_t)k - 2;
-          if (FTAB && k >= ix.ftab_k) {
-            const uint32_t t = ix.ftab_k;
-            const ulonglong2 e = __ldg(reinterpret_cast<const ulonglong2*>(ix.ftab) + (pk & ((1ull << (2 * t)) - 1)));
-            lo = e.x;
-            hi = e.y;
-            j = (int32_t)k - (int32_t)t - 1;
-            if (lo > hi) j = -1; /* the search had already stopped inside the suffix (query.cpp:35-37) */
-          }
-          if (j < 0) {
-            rs_emit(mode, lower, upper, peers, q, lo, hi, pk, k, rc);
-            active = false;
+      /* Queries are handed out from one counter, a warp taking as many as it has idle lanes: lanes of a warp (and
+       * warps of the grid) stay busy until the batch runs dry, however unevenly the searches end.  With a fixed
+       * share of the batch per thread a warp ran until its slowest lane was done: a third of the lane-trips idle. */
+      if (!exhausted) {
+        const int leader = __ffs((int)idle) - 1;
+        unsigned long long base = 0;
+        if ((int)lane == leader) base = atomicAdd(ticket, (unsigned long long)__popc(idle));
+        base = __shfl_sync(RS_FULL, base, leader);
+        if (base >= Q) exhausted = true;
+        if (!active && !exhausted) {
+          q = base + (uint64_t)__popc(idle & ((1u << lane) - 1u));
+          if (q < Q) {
+            pk = pkeys[q];
+            active = true;
+            if (pk >> 63) { /* a byte outside ACGT */
+              if (mode == 1) lower[q] = 0; /* service.cpp:299-301; mode 2: nothing to add */
+              if (mode == 4) { lower[q] = 1; reinterpret_cast<uint32_t*>(upper)[q] = 0; }
+              active = false; /* mode 0: left flagged for k_search_flagged */
+            } else {
+              const uint32_t c0 = (uint32_t)(pk & 3u) + 1u; /* initInterval (query.cpp:18-21) on the last character */
+              lo = (P)ix.pc[c0];
+              hi = (P)(ix.pc[c0] + ix.init_occ[c0] - 1);
+              j = (int32_t)k - 2;
+              if (FTAB && k >= ix.ftab_k) {
+                const uint32_t t = ix.ftab_k;
+                const ulonglong2 e = __ldg(reinterpret_cast<const ulonglong2*>(ix.ftab) + (pk & ((1ull << (2 * t)) - 1)));
+                lo = (P)e.x;
+                hi = (P)e.y; /* 2^64-1 becomes NONE */
+                j = (int32_t)k - (int32_t)t - 1;
+                if (e.x > e.y) j = -1; /* the search had already stopped inside the suffix (query.cpp:35-37) */
+              }
+              if (j < 0) {
+                rs_emit(mode, lower, upper, peers, q, (uint64_t)lo, hi == NONE ? ~0ull : (uint64_t)hi, pk, k, rc);
+                active = false;
+              }
+            }
           }
         }
       }
       if (__all_sync(RS_FULL, !active)) {
-        if (__all_sync(RS_FULL, next_q >= Q)) break;
+        if (exhausted) break;
         continue;
       }
     }
     if (active) {
       const uint32_t c = (uint32_t)((pk >> (2 * (k - 1 - (uint32_t)j))) & 3u) + 1u;
-      const bool none1 = (lo == 0), none2 = (hi == ~0ull); /* getOcc(b, 2^64-1) = 0 in the reference */
-      uint64_t p1 = none1 ? 0 : rs_ref_pos(ix, lo - 1);
-      uint64_t p2 = none2 ? 0 : rs_ref_pos(ix, hi);
-      if (p1 >= ix.n) p1 = ix.n - 1;
-      if (p2 >= ix.n) p2 = ix.n - 1;
-      const uint64_t b1 = p1 >> RS_DENSE_SHIFT, b2 = p2 >> RS_DENSE_SHIFT;
+      const bool none1 = (lo == 0), none2 = (hi == NONE); /* getOcc(b, 2^64-1) = 0 in the reference */
+      P p1 = lo - 1, p2 = hi;
+      p1 = p1 >= tail_from ? tail_pos : p1;
+      p2 = p2 >= tail_from ? tail_pos : p2;
+      p1 = none1 ? 0 : (p1 > last ? last : p1);
+      p2 = none2 ? 0 : (p2 > last ? last : p2);
+      const P b1 = p1 >> RS_DENSE_SHIFT, b2 = p2 >> RS_DENSE_SHIFT;
       const bool split = b1 != b2;
       const rs_dblk k1 = rs_load_dense(ix, b1);
       rs_dblk k2 = k1;
@@ -383,26 +404,53 @@ __global__ void __launch_bounds__(RS_THREADS, RS_K1D_BLOCKS)
       const uint32_t t1 = ((uint32_t)p1 & (RS_DENSE_SYMS - 1u)) + 1u, t2 = ((uint32_t)p2 & (RS_DENSE_SYMS - 1u)) + 1u;
       uint32_t a1, a2;
       rs_dense_count2(k1, c, t1, split ? 0u : t2, &a1, &a2);
-      uint64_t before2 = rs_dense_before(k1, b1, c);
-      const uint64_t r1 = none1 ? 0 : before2 + a1;
+      uint32_t before2 = c == 1 ? k1.cnt[0] : c == 2 ? k1.cnt[1] : c == 3 ? k1.cnt[2] : k1.cnt[3];
+      const P r1 = none1 ? 0 : (P)before2 + a1;
       if (split) { /* rare once the interval is narrow: lower-1 and upper then sit in one block */
         uint32_t unused;
         rs_dense_count2(k2, c, t2, 0u, &a2, &unused);
-        before2 = rs_dense_before(k2, b2, c);
+        before2 = c == 1 ? k2.cnt[0] : c == 2 ? k2.cnt[1] : c == 3 ? k2.cnt[2] : k2.cnt[3];
       }
-      const uint64_t r2 = none2 ? 0 : before2 + a2;
+      const P r2 = none2 ? 0 : (P)before2 + a2;
       ++nsteps;
-      const uint64_t pb = ix.pc[c];
+      const P pb = (P)ix.pc[c];
       lo = pb + r1;
       hi = pb + r2 - 1;
       --j;
+      /* query.cpp:35-37 compares unsigned: an upper bound of 2^64-1 ("before row 0", NONE here) is above every lower
+       * bound, so the reference searches on -- and so does this */
       if (lo > hi || j < 0) {
-        rs_emit(mode, lower, upper, peers, next_q - stride, lo, hi, pk, k, rc);
+        rs_emit(mode, lower, upper, peers, q, (uint64_t)lo, hi == NONE ? ~0ull : (uint64_t)hi, pk, k, rc);
         active = false;
       }
     }
   }
   if (stats && nsteps) atomicAdd(stats, (unsigned long long)nsteps);
+}
+
+/* One counter per launch, from a pool that is cleared in bulk: rs_ticket_take() hands out the next `n` consecutive
+ * slots; a slot is reused only after RS_TICKET_POOL further launches, by which time its kernel has long ended (the
+ * driver queues at most a few thousand launches). */
+#define RS_TICKET_POOL 65536u
+static unsigned long long* g_tickets[64] = {};
+static uint64_t g_ticket_next[64] = {};
+static std::mutex g_ticket_mu;
+
+cudaError_t rs_ticket_take(uint32_t n, unsigned long long** first, cudaStream_t st) {
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= 64 || n == 0 || n > RS_TICKET_POOL / 4) return cudaErrorInvalidValue;
+  std::lock_guard<std::mutex> lk(g_ticket_mu);
+  if (!g_tickets[dev]) {
+    e = cudaMalloc((void**)&g_tickets[dev], RS_TICKET_POOL * sizeof(unsigned long long));
+    if (e != cudaSuccess) return e;
+  }
+  uint64_t at = g_ticket_next[dev] % RS_TICKET_POOL;
+  if (at + n > RS_TICKET_POOL) at = 0; /* keep a request contiguous */
+  g_ticket_next[dev] = at + n;
+  *first = g_tickets[dev] + at;
+  return cudaMemsetAsync(*first, 0, (size_t)n * sizeof(unsigned long long), st);
 }
 
 /* K1b.  The rare queries K1 left flagged (bit 63 of lower[q]: a byte outside "$ACGT"), one whole findInterval
@@ -816,8 +864,14 @@ cudaError_t rs_launch_find_interval(const rs_index_dev& ix, const uint8_t* text,
       k_pack_kmers<<<(unsigned)((Q + RS_THREADS - 1) / RS_THREADS), RS_THREADS, 0, st>>>(text, k, Q, mode >= 1 && strand == 1,
                                                                                      lower);
     if (ix.dense) {
-      if (ftab) RS_LAUNCH((k_find_interval_dense<true>), Q, st, ix, k, Q, lower, lower, upper, mode, strand, stats, peers);
-      else RS_LAUNCH((k_find_interval_dense<false>), Q, st, ix, k, Q, lower, lower, upper, mode, strand, stats, peers);
+      unsigned long long* ticket = nullptr;
+      const cudaError_t te = rs_ticket_take(1, &ticket, st);
+      if (te != cudaSuccess) return te;
+      const bool small = ix.n < (1ull << 31);
+      if (ftab && small) RS_LAUNCH((k_find_interval_dense<true, true>), Q, st, ix, k, Q, lower, lower, upper, mode, strand, stats, peers, ticket);
+      else if (ftab) RS_LAUNCH((k_find_interval_dense<true, false>), Q, st, ix, k, Q, lower, lower, upper, mode, strand, stats, peers, ticket);
+      else if (small) RS_LAUNCH((k_find_interval_dense<false, true>), Q, st, ix, k, Q, lower, lower, upper, mode, strand, stats, peers, ticket);
+      else RS_LAUNCH((k_find_interval_dense<false, false>), Q, st, ix, k, Q, lower, lower, upper, mode, strand, stats, peers, ticket);
     } else if (ftab) RS_LAUNCH((k_find_interval<true, true>), Q, st, ix, text, offs, k, Q, lower, lower, upper, mode, strand, stats, peers);
     else RS_LAUNCH((k_find_interval<false, true>), Q, st, ix, text, offs, k, Q, lower, lower, upper, mode, strand, stats, peers);
   } else {
@@ -844,7 +898,7 @@ cudaError_t rs_launch_pack_kmers(const uint8_t* text, uint32_t k, uint64_t Q, in
  * ACGT: count_reads, service.cpp:299-301).  mode 2: counts added into the owners' buffers (peers). */
 cudaError_t rs_launch_find_interval_packed(const rs_index_dev& ix, const uint64_t* pkeys, uint32_t k, uint64_t Q,
                                            uint64_t* first, uint32_t* rows, int mode, unsigned long long* stats,
-                                           cudaStream_t st, const rs_peers* peers_in) {
+                                           cudaStream_t st, const rs_peers* peers_in, unsigned long long* ticket) {
   if (!Q) return cudaSuccess;
   if (k < 1 || k > RS_PACK_MAX_K || (mode != 4 && mode != 2) || (mode == 2 && !peers_in)) return cudaErrorInvalidValue;
   rs_peers peers;
@@ -853,8 +907,15 @@ cudaError_t rs_launch_find_interval_packed(const rs_index_dev& ix, const uint64_
   const bool ftab = ix.ftab && ix.ftab_k > 1;
   uint64_t* up = reinterpret_cast<uint64_t*>(rows);
   if (ix.dense) {
-    if (ftab) RS_LAUNCH((k_find_interval_dense<true>), Q, st, ix, k, Q, pkeys, first, up, mode, 0, stats, peers);
-    else RS_LAUNCH((k_find_interval_dense<false>), Q, st, ix, k, Q, pkeys, first, up, mode, 0, stats, peers);
+    if (!ticket) { /* the caller did not reserve (and clear) one with its other launches */
+      const cudaError_t te = rs_ticket_take(1, &ticket, st);
+      if (te != cudaSuccess) return te;
+    }
+    const bool small = ix.n < (1ull << 31);
+    if (ftab && small) RS_LAUNCH((k_find_interval_dense<true, true>), Q, st, ix, k, Q, pkeys, first, up, mode, 0, stats, peers, ticket);
+    else if (ftab) RS_LAUNCH((k_find_interval_dense<true, false>), Q, st, ix, k, Q, pkeys, first, up, mode, 0, stats, peers, ticket);
+    else if (small) RS_LAUNCH((k_find_interval_dense<false, true>), Q, st, ix, k, Q, pkeys, first, up, mode, 0, stats, peers, ticket);
+    else RS_LAUNCH((k_find_interval_dense<false, false>), Q, st, ix, k, Q, pkeys, first, up, mode, 0, stats, peers, ticket);
   } else if (ftab) RS_LAUNCH((k_find_interval<true, true>), Q, st, ix, nullptr, nullptr, k, Q, pkeys, first, up, mode, 0, stats, peers);
   else RS_LAUNCH((k_find_interval<false, true>), Q, st, ix, nullptr, nullptr, k, Q, pkeys, first, up, mode, 0, stats, peers);
   return cudaGetLastError();

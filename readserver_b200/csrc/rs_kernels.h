@@ -32,7 +32,10 @@ cudaError_t rs_launch_pack_kmers(const uint8_t* text, uint32_t k, uint64_t Q, in
 /* K1 over packed keys kept apart from its outputs (mode 4: first row + row count per key; mode 2 as above) */
 cudaError_t rs_launch_find_interval_packed(const rs_index_dev& ix, const uint64_t* pkeys, uint32_t k, uint64_t Q,
                                            uint64_t* first, uint32_t* rows, int mode, unsigned long long* stats,
-                                           cudaStream_t st, const rs_peers* peers = nullptr);
+                                           cudaStream_t st, const rs_peers* peers = nullptr,
+                                           unsigned long long* ticket = nullptr);
+/* work counters of the kernels that hand their items out dynamically: `n` consecutive cleared slots, one per launch */
+cudaError_t rs_ticket_take(uint32_t n, unsigned long long** first, cudaStream_t st);
 /* cross-GPU barrier over peer-mapped flag words: every rank writes `epoch` into its slot of every peer's
  * flag array, then waits until all slots of its own array reached it (or ~timeout_ms passed: *err = 1) */
 cudaError_t rs_launch_peer_barrier(uint64_t* const* peer_flags, uint32_t world, uint32_t rank, uint64_t epoch,

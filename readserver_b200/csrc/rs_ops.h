@@ -157,8 +157,20 @@ struct rs_dblk {
 
 RS_HD rs_dblk rs_load_dense(const rs_index_dev& ix, uint64_t b) {
   const uint8_t* p = reinterpret_cast<const uint8_t*>(ix.dense) + b * 64;
-  const rs_u4 v0 = rs_ld128(p), v1 = rs_ld128(p + 16), v2 = rs_ld128(p + 32), v3 = rs_ld128(p + 48);
   rs_dblk k;
+#if defined(__CUDA_ARCH__)
+  /* two 256-bit loads (LDG.E.256 on sm_100a) instead of four 128-bit ones: every load instruction of a warp whose
+   * lanes sit on different blocks costs one L1 tag look-up per lane, and K1 over dense blocks is bound by exactly
+   * that (ncu: l1tex throughput 91 % with four loads per block) */
+  asm("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+      : "=r"(k.cnt[0]), "=r"(k.cnt[1]), "=r"(k.cnt[2]), "=r"(k.cnt[3]), "=r"(k.p0[0]), "=r"(k.p0[1]), "=r"(k.p0[2]), "=r"(k.p0[3])
+      : "l"(__cvta_generic_to_global(p)));
+  asm("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+      : "=r"(k.p1[0]), "=r"(k.p1[1]), "=r"(k.p1[2]), "=r"(k.p1[3]), "=r"(k.p2[0]), "=r"(k.p2[1]), "=r"(k.p2[2]), "=r"(k.p2[3])
+      : "l"(__cvta_generic_to_global(p + 32)));
+  return k;
+#endif
+  const rs_u4 v0 = rs_ld128(p), v1 = rs_ld128(p + 16), v2 = rs_ld128(p + 32), v3 = rs_ld128(p + 48);
   k.cnt[0] = v0.x; k.cnt[1] = v0.y; k.cnt[2] = v0.z; k.cnt[3] = v0.w;
   k.p0[0] = v1.x; k.p0[1] = v1.y; k.p0[2] = v1.z; k.p0[3] = v1.w;
   k.p1[0] = v2.x; k.p1[1] = v2.y; k.p1[2] = v2.z; k.p1[3] = v2.w;
@@ -168,8 +180,16 @@ RS_HD rs_dblk rs_load_dense(const rs_index_dev& ix, uint64_t b) {
 
 /* bits of plane word w that belong to the first t symbols of the block (0 <= t <= 128) */
 RS_HD uint32_t rs_dense_mask(uint32_t t, uint32_t w) {
+#if defined(__CUDA_ARCH__)
+  /* all ones shifted right by max(32 (w + 1) - t, 0); the hardware shift gives 0 for amounts >= 32 */
+  const int32_t s = (int32_t)(32u * (w + 1u)) - (int32_t)t;
+  uint32_t m;
+  asm("shr.b32 %0, %1, %2;" : "=r"(m) : "r"(0xFFFFFFFFu), "r"((uint32_t)(s < 0 ? 0 : s)));
+  return m;
+#else
   const int32_t k = (int32_t)t - (int32_t)(32u * w);
   return k <= 0 ? 0u : (k >= 32 ? 0xFFFFFFFFu : ((1u << k) - 1u));
+#endif
 }
 
 RS_HD uint32_t rs_popc(uint32_t x) {

@@ -400,6 +400,7 @@ struct rs_shardset {
   Scratch s_packed, s_lo, s_cnt, s_seg, s_nh, s_loc, s_scan, s_base, s_rows, s_dst, s_ri, s_in, s_lcnt;
   uint64_t* d_stats = nullptr; /* executed updateInterval steps / LF steps of the set's calls (bench.py) */
   uint64_t chunk = 1u << 20;
+  bool chunk_forced = false; /* RS_B200_POP_CHUNK given */
   /* stage timing (bench.py: which kernel a step's time goes to): events recorded on the call's stream around the
    * stages of every chunk, read back -- and summed per stage -- by rs_shardset_read_timing */
   bool timing = false;
@@ -450,7 +451,10 @@ int rs_shardset_create(int device, rs_shardset** out) {
   s->device = device;
   memset(&s->tab, 0, sizeof(s->tab));
   const char* e = getenv("RS_B200_POP_CHUNK");
-  if (e && atoll(e) >= 1024) s->chunk = (uint64_t)atoll(e);
+  if (e && atoll(e) >= 1024) {
+    s->chunk = (uint64_t)atoll(e);
+    s->chunk_forced = true;
+  }
   cudaError_t ce = cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking);
   if (ce != cudaSuccess) {
     delete s;
@@ -642,7 +646,7 @@ int rs_shardset_get_info(const rs_shardset* set, rs_shardset_info* info) {
     info->num_strings += ix->dev.num_strings;
     info->num_runs += ix->num_runs;
   }
-  info->chunk_queries = set->chunk;
+  info->chunk_queries = set->chunk_forced ? set->chunk : std::max<uint64_t>(1u << 16, (RS_POP_SCRATCH_BYTES / 12) / std::max<size_t>(1, set->shards.size()));
   return RS_STATUS_OK;
 }
 
@@ -849,7 +853,14 @@ static int pop_run(rs_shardset* set, rs_popcomm* comm, const void* d_kmers, int 
                    uint64_t* d_counts, uint64_t* d_hit_offsets, uint64_t* d_hits, uint64_t capacity, uint32_t* d_carriers,
                    uint64_t* d_total, cudaStream_t st) {
   const uint32_t S = (uint32_t)set->shards.size();
-  const uint64_t C = std::min<uint64_t>(set->chunk, Q);
+  /* chunk: as many queries as the per-shard interval scratch (12 bytes per shard and query) may take; long launches
+   * keep every lane busy (the batch is handed out dynamically) and a shard's index hot in L2 */
+  uint64_t C = std::min<uint64_t>(set->chunk, Q);
+  if (!set->chunk_forced) {
+    const uint64_t fit = std::max<uint64_t>(1u << 16, (RS_POP_SCRATCH_BYTES / 12) / S);
+    const uint64_t nchunks = (Q + fit - 1) / fit;
+    C = (Q + nchunks - 1) / nchunks; /* equal chunks */
+  }
   const bool want_hits = d_hit_offsets != nullptr;
   const bool table = set->locate_every == 1;
   const bool multi = comm != nullptr && comm->world > 1;
@@ -901,10 +912,12 @@ static int pop_run(rs_shardset* set, rs_popcomm* comm, const void* d_kmers, int 
     const uint64_t nq = std::min<uint64_t>(C, Q - q0);
     const unsigned gq = (unsigned)((nq + 255) / 256);
     {
+      unsigned long long* tickets = nullptr; /* one work counter per launch, cleared together */
+      CU(rs_ticket_take(S, &tickets, st));
       StageTimer tm(set, st, RS_POP_STAGE_SEARCH, S);
       for (uint32_t s = 0; s < S; ++s)
         CU(rs_launch_find_interval_packed(set->shards[s]->dev, keys + q0, (uint32_t)k, nq, lo + (uint64_t)s * C,
-                                          cnt + (uint64_t)s * C, 4, (unsigned long long*)set->d_stats, st));
+                                          cnt + (uint64_t)s * C, 4, (unsigned long long*)set->d_stats, st, nullptr, tickets + s));
     }
     {
       StageTimer tm(set, st, RS_POP_STAGE_OFFSETS, want_hits ? 4 : 1);
