@@ -246,7 +246,7 @@ class CpuShards:
         hits = np.zeros(int(off[n]), dtype=np.uint64)
         carr = np.zeros((n, 4), dtype=np.uint32)
         run = off[:-1].copy()
-        postfix_agrees = True
+        postfix_agrees = {"hits_differing": 0, "shards_differing": []}
         for s in order:
             lo, up, c, lex, ri_post = per[s]
             tot = int(c.sum())
@@ -254,7 +254,10 @@ class CpuShards:
                 sai = self.sai[s]
                 ns = sai.size
                 ri = np.where(lex < ns, sai[np.minimum(lex, ns - 1).astype(np.int64)], U64MAX)
-                postfix_agrees &= bool(np.array_equal(ri, ri_post))
+                ndiff = int((ri != ri_post).sum())
+                if ndiff:
+                    postfix_agrees["hits_differing"] += ndiff
+                    postfix_agrees["shards_differing"].append(int(s))
                 qid = np.repeat(np.arange(n), c)
                 within = np.arange(tot, dtype=np.int64) - np.repeat(np.cumsum(c) - c, c)
                 hits[run[qid] + within] = np.where(ri == U64MAX, U64MAX, (np.uint64(s) << np.uint64(40)) | ri)
@@ -496,7 +499,7 @@ def run_ours(args):
     step_ms = [a.elapsed_time(b) for a, b in evs]
     stage_ms, stage_launches = S.read_timing()
     S.enable_timing(False)
-    interval_steps, walk_steps = S.read_stats(reset=True)
+    interval_steps, walk_steps, block_loads = S.read_stats(reset=True)
     total_ms = torch.tensor([sum(step_ms)], dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
@@ -630,7 +633,7 @@ def run_ours(args):
     k1_s = stage_ms["search"] / 1e3
     k1_launches = max(1, stage_launches["search"])
     getocc = 2.0 * interval_steps
-    achieved = getocc * BYTES_PER_RANK / max(k1_s, 1e-12) / 1e9
+    achieved = block_loads * BYTES_PER_RANK / max(k1_s, 1e-12) / 1e9
     traffic, traffic_src = committed_traffic("r2_k1_traffic.json")
     chunks = (Q + int(info.chunk_queries) - 1) // int(info.chunk_queries)
     ours_per_step = 1 + chunks * (len(my_shards) + 4 + (1 if args.locate_every == 1 else 4 * len(my_shards) + 1)) \
@@ -661,13 +664,16 @@ def run_ours(args):
         "roofline": {
             "bound": "hbm", "kernel": "k_find_interval (K1), one launch per shard and chunk", "achieved": achieved, "peak": peak,
             "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
-            "algorithmic_bytes": "executed getOcc calls x 64 B (one block: header + 36 run bytes)",
-            "getocc_per_launch": getocc / k1_launches, "launches_timed": k1_launches,
+            "algorithmic_bytes": "64-byte blocks K1 had to read x 64 B: one per updateInterval step whose two positions share "
+                                 "a block, two otherwise (counted on the device)",
+            "blocks_per_launch": block_loads / k1_launches, "getocc_per_launch": getocc / k1_launches,
+            "launches_timed": k1_launches,
             "avg_launch_ms": stage_ms["search"] / k1_launches,
             "k1_share_of_step": stage_ms["search"] / max(sum(step_ms), 1e-9),
             "stage_ms_per_step": {s: v / args.steps for s, v in stage_ms.items()},
-            "note": "a shard's blocks + directory + suffix table are tens of MB: L2-resident while a chunk of queries streams "
-                    "through it, so the achieved figure is served by L2, not HBM (DESIGN.md 6)",
+            "note": "one launch = the whole batch against ONE shard, whose rank blocks (70 MB) and suffix table stay largely "
+                    "L2-resident for the launch: the achieved figure is served by L2 + HBM together, `traffic` (ncu) says how "
+                    "much of it HBM carried (DESIGN.md 6)",
         },
         "e2e": {"value": Q * e2e_steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": (world if world > 1 else 1) * Q * k,
                 "d2h_bytes_per_step": d2h, "steps": e2e_steps,
@@ -677,6 +683,16 @@ def run_ours(args):
         "clocks": clk,
     }
     if side is not None:
+        # the population's shards leave HBM first: building configs[1] (a 1.08 G-symbol suffix sort) needs the room
+        S.close()
+        for ent in data["shards"].values():
+            if "gpu" in ent:
+                ent.pop("gpu").close()
+        try:
+            del d_hits, d_carr
+        except NameError:
+            pass
+        torch.cuda.empty_cache()
         try:
             side["configs1_count"] = side_configs1(args, engine, dev, local_rank, flush)
         except Exception as ex:
@@ -709,7 +725,11 @@ def run_ours(args):
             "load_seconds": round(cpu.load_seconds, 1),
             "gpu_results_bit_exact_on_sample": ok_counts and ok_hits and ok_carr,
             "checked": {"population_counts": ok_counts, "hit_lists_read_index": ok_hits, "sample_sets": ok_carr,
-                        "postfix_walk_gives_the_same_read_index": post_ok, "hits_checked": he},
+                        "hits_checked": he,
+                        "postfix_walk_vs_prefix_walk_read_index": post_ok},
+            "note": "read index = .sai[terminal row of extractPrefix's walk]; the reference's tail behaviour (SURVEY.md Q1) can "
+                    "send that walk elsewhere than extractPostfix's (select is unaffected) in shards whose tail region is "
+                    "not empty: both sides reproduce it, postfix_walk_vs_prefix_walk_read_index counts such hits",
         }
         cpu.close()
         assert ok_counts and ok_hits and ok_carr, "GPU results differ from the CPU reference"

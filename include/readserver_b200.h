@@ -332,7 +332,10 @@ int rs_shardset_seal(rs_shardset* set, uint32_t max_read_len, uint32_t locate_ev
 void rs_shardset_destroy(rs_shardset* set);
 int rs_shardset_get_info(const rs_shardset* set, rs_shardset_info* info);
 int rs_shardset_enable_stats(rs_shardset* set, int on);
-int rs_shardset_read_stats(rs_shardset* set, uint64_t* interval_steps, uint64_t* walk_steps, int reset);
+/* work counters of the set's calls: executed updateInterval steps (2 getOcc each), LF steps of the walks, and the
+ * 64-byte blocks K1 read (a step whose two positions share a block reads one) */
+int rs_shardset_read_stats(rs_shardset* set, uint64_t* interval_steps, uint64_t* walk_steps, uint64_t* block_loads,
+                           int reset);
 /* Measurement aid: CUDA events around the pipeline's stages on the call's own stream.  ms[4] / launches[4] =
  * time and kernel launches of 0 k_pack_kmers, 1 K1 (search), 2 offsets, 3 locate + sample sets, summed over the
  * calls since the last read (which synchronises the device). */
@@ -382,7 +385,8 @@ int rs_popcomm_error(rs_popcomm* c, int* timed_out);
  *     rs_comm_begin(Q) ; rs_count_accumulate_dev(...) once per local shard ; rs_comm_finish
  *   rs_comm_finish   cross-GPU barrier on the stream; *d_counts = device array of Q u64 whose entries for
  *                    the k-mers this rank owns hold the population counts (other entries are 0); valid
- *                    until the next-but-one rs_comm_begin
+ *                    until the next-but-one rs_comm_begin (three buffers rotate), for readers ordered after the
+ *                    barrier on `stream` (a reader on another stream must wait for an event recorded there)
  *   rs_comm_error    1 if a barrier gave up waiting for a peer (5 s)
  * Fixed-length queries of 1..31 characters; any byte outside ACGT counts 0 (service.cpp:299-301). */
 typedef struct rs_comm rs_comm;

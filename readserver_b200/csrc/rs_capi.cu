@@ -205,10 +205,10 @@ int rs_index_drop_locate_table(rs_index* ix) {
 static uint32_t auto_ftab_k(const rs_index* ix) {
   const char* e = getenv("RS_B200_FTAB");
   if (e) return (uint32_t)atoi(e);
-  /* largest t <= 12 whose table is no larger than the blocks.  One 16-byte read per query replaces t - 1 steps of
-   * two block reads each, so the table pays even when it is far larger than L2 (configs[1], M q/s: t = 8: 1540,
-   * 9: 1598, 10: 1674, 11: 1802, 12: 1842 with a table 2.4 times the blocks) */
-  const uint64_t budget = ix->dev.nblocks * (uint64_t)RS_BLOCK_BYTES;
+  /* largest t <= 12 whose table is at most four times the run blocks.  One 16-byte read per query replaces t - 1
+   * steps of two block reads each, so the table pays even when it is far larger than L2 (configs[1], M q/s: t = 8: 1540,
+   * 9: 1598, 10: 1674, 11: 1802, 12: 1842; configs[2], K1 ms per step over 64 shards: t = 9: 155, 10: 141, 11: 112, 12: 107) */
+  const uint64_t budget = 4 * ix->dev.nblocks * (uint64_t)RS_BLOCK_BYTES;
   uint32_t t = 0;
   while (t < 12 && (16ull << (2 * (t + 1))) <= budget) ++t;
   return t;
@@ -676,8 +676,8 @@ int rs_index_enable_stats(rs_index* ix, int on) {
   std::lock_guard<std::mutex> lk(ix->mu);
   CU(cudaSetDevice(ix->device));
   if (on && !ix->d_stats) {
-    CU(cudaMalloc((void**)&ix->d_stats, 2 * sizeof(uint64_t)));
-    CU(cudaMemset(ix->d_stats, 0, 2 * sizeof(uint64_t)));
+    CU(cudaMalloc((void**)&ix->d_stats, 4 * sizeof(uint64_t)));
+    CU(cudaMemset(ix->d_stats, 0, 4 * sizeof(uint64_t)));
   } else if (!on && ix->d_stats) {
     CU(cudaDeviceSynchronize());
     cudaFree(ix->d_stats);
@@ -691,7 +691,7 @@ int rs_index_read_stats(rs_index* ix, uint64_t* interval_steps, uint64_t* walk_s
   if (!ix->d_stats) return fail(RS_STATUS_NO_TABLE, "statistics are not enabled");
   CU(cudaSetDevice(ix->device));
   CU(cudaDeviceSynchronize());
-  uint64_t v[2] = {0, 0};
+  uint64_t v[4] = {0, 0, 0, 0};
   CU(cudaMemcpy(v, ix->d_stats, sizeof(v), cudaMemcpyDeviceToHost));
   if (interval_steps) *interval_steps = v[0];
   if (walk_steps) *walk_steps = v[1];
@@ -792,7 +792,8 @@ static std::vector<size_t> chunk_schedule(size_t Q) {
   std::vector<size_t> sz;
   const size_t tail = 3 * small; /* 2 * small, small */
   size_t used = 0;
-  for (size_t up = small; up < big && used + up + tail + big <= Q; up *= 2) {
+  /* the ramp leaves room for at least one bulk chunk and the two tail chunks among the RS_MAX_CHUNKS events */
+  for (size_t up = small; up < big && used + up + tail + big <= Q && sz.size() + 3 < RS_MAX_CHUNKS; up *= 2) {
     sz.push_back(up);
     used += up;
   }
@@ -832,19 +833,35 @@ static int find_host(const rs_index* ix, const char* text, const uint64_t* offse
      * the copies alone, cut the same way, allow about 1.2-1.3 G q/s (scripts/pcie_probe.py). */
     const std::vector<size_t> sz = chunk_schedule(Q);
     size_t q0 = 0;
-    for (size_t c = 0; c < sz.size(); ++c) {
+    cudaError_t e = cudaSuccess;
+    const char* what = "";
+#define PIPE(call)                     \
+  if (e == cudaSuccess) {              \
+    e = (call);                        \
+    if (e != cudaSuccess) what = #call; \
+  }
+    for (size_t c = 0; c < sz.size() && e == cudaSuccess; ++c) {
       const size_t qn = sz[c];
-      CU(cudaMemcpyAsync(d_text + q0 * k, text + q0 * k, qn * (size_t)k, cudaMemcpyHostToDevice, ix->s_h2d));
-      CU(cudaEventRecord(ix->ev_in[c], ix->s_h2d));
       cudaStream_t sk = ix->s_k[c % search_streams()];
-      CU(cudaStreamWaitEvent(sk, ix->ev_in[c], 0));
-      CU(rs_launch_find_interval(ix->dev, d_text + q0 * k, nullptr, (uint32_t)k, qn, d_lo + q0, d_up + q0, mode, strand,
-                                 nullptr, sk));
-      CU(cudaEventRecord(ix->ev_done[c], sk));
-      CU(cudaStreamWaitEvent(ix->s_d2h, ix->ev_done[c], 0));
-      CU(cudaMemcpyAsync(lower + q0, d_lo + q0, qn * 8, cudaMemcpyDeviceToHost, ix->s_d2h));
-      if (mode == 0) CU(cudaMemcpyAsync(upper + q0, d_up + q0, qn * 8, cudaMemcpyDeviceToHost, ix->s_d2h));
+      PIPE(cudaMemcpyAsync(d_text + q0 * k, text + q0 * k, qn * (size_t)k, cudaMemcpyHostToDevice, ix->s_h2d));
+      PIPE(cudaEventRecord(ix->ev_in[c], ix->s_h2d));
+      PIPE(cudaStreamWaitEvent(sk, ix->ev_in[c], 0));
+      PIPE(rs_launch_find_interval(ix->dev, d_text + q0 * k, nullptr, (uint32_t)k, qn, d_lo + q0, d_up + q0, mode, strand,
+                                   nullptr, sk));
+      PIPE(cudaEventRecord(ix->ev_done[c], sk));
+      PIPE(cudaStreamWaitEvent(ix->s_d2h, ix->ev_done[c], 0));
+      PIPE(cudaMemcpyAsync(lower + q0, d_lo + q0, qn * 8, cudaMemcpyDeviceToHost, ix->s_d2h));
+      if (mode == 0) PIPE(cudaMemcpyAsync(upper + q0, d_up + q0, qn * 8, cudaMemcpyDeviceToHost, ix->s_d2h));
       q0 += qn;
+    }
+#undef PIPE
+    if (e != cudaSuccess) {
+      /* copies and kernels already queued still use the scratch buffers and the caller's arrays: drain all three
+       * stream groups before handing control back */
+      cudaStreamSynchronize(ix->s_h2d);
+      for (int i = 0; i < RS_SEARCH_STREAMS; ++i) cudaStreamSynchronize(ix->s_k[i]);
+      cudaStreamSynchronize(ix->s_d2h);
+      return fail(RS_STATUS_CUDA, "%s: %s", what, cudaGetErrorString(e));
     }
     CU(cudaStreamSynchronize(ix->s_d2h));
     return RS_STATUS_OK;

@@ -161,6 +161,7 @@ __global__ void __launch_bounds__(RS_THREADS, RS_K1_BLOCKS)
   bool active = false;
   const bool rc = (mode >= 1 && strand == 1);
   uint32_t nsteps = 0; /* updateInterval calls executed by this thread (2 ranks each) */
+  uint32_t nscans = 0; /* 64-byte run blocks read (one per trip) */
   bool pending = false; /* the second position of the step in hand is still to be scanned */
   uint32_t c = 0, b2 = 0;
   uint64_t r1 = 0;
@@ -286,6 +287,7 @@ __global__ void __launch_bounds__(RS_THREADS, RS_K1_BLOCKS)
       }
       uint64_t x1, x2;
       rs_scan2(ix, c, blk, pos, p2, two, &x1, &x2);
+      ++nscans;
       uint64_t r2 = 0;
       if (was_pending) {
         r2 = none2 ? 0 : x1;
@@ -307,7 +309,10 @@ __global__ void __launch_bounds__(RS_THREADS, RS_K1_BLOCKS)
       }
     }
   }
-  if (stats && nsteps) atomicAdd(stats, (unsigned long long)nsteps);
+  if (stats && nsteps) {
+    atomicAdd(stats, (unsigned long long)nsteps);
+    atomicAdd(stats + 2, (unsigned long long)nscans);
+  }
 }
 
 /* K1 over the dense rank blocks (rs_layout.h), packed queries.  A step (updateInterval, query.cpp:11-15) is one trip:
@@ -337,7 +342,7 @@ __global__ void __launch_bounds__(RS_THREADS, RS_K1D_BLOCKS)
   int32_t j = -1;
   bool active = false, exhausted = false;
   const bool rc = (mode >= 1 && mode != 4 && strand == 1);
-  uint32_t nsteps = 0;
+  uint32_t nsteps = 0, nsplit = 0;
   /* the reference's tail rule (rs_ref_pos) and the clamp to the last row, in the position type */
   const P tail_from = ix.tail_from > (uint64_t)NONE ? NONE : (P)ix.tail_from;
   const P tail_pos = (P)(ix.clamp_c - 1), last = (P)(ix.n - 1);
@@ -410,6 +415,7 @@ __global__ void __launch_bounds__(RS_THREADS, RS_K1D_BLOCKS)
         uint32_t unused;
         rs_dense_count2(k2, c, t2, 0u, &a2, &unused);
         before2 = c == 1 ? k2.cnt[0] : c == 2 ? k2.cnt[1] : c == 3 ? k2.cnt[2] : k2.cnt[3];
+        ++nsplit;
       }
       const P r2 = none2 ? 0 : (P)before2 + a2;
       ++nsteps;
@@ -425,7 +431,10 @@ __global__ void __launch_bounds__(RS_THREADS, RS_K1D_BLOCKS)
       }
     }
   }
-  if (stats && nsteps) atomicAdd(stats, (unsigned long long)nsteps);
+  if (stats && nsteps) {
+    atomicAdd(stats, (unsigned long long)nsteps);
+    atomicAdd(stats + 2, (unsigned long long)(nsteps + nsplit)); /* 64-byte blocks read */
+  }
 }
 
 /* One counter per launch, from a pool that is cleared in bulk: rs_ticket_take() hands out the next `n` consecutive

@@ -8,10 +8,11 @@
  * all slots of its own.
  *
  * One device allocation per rank, exported through a CUDA IPC handle:
- *   [ flags: RS_MAX_RANKS x u64 | error word | pad to 256 B ][ counts A: max_queries x u64 ]
- *   [ counts B: max_queries x u64 ][ scratch: max_queries x u64 (packed queries of the running K1) ]
- * Steps alternate between A and B: a rank clears the buffer of the NEXT step before it searches, which
- * no peer can touch before it has passed this step's barrier.
+ *   [ flags: RS_MAX_RANKS x u64 | error word | pad to 256 B ][ counts 0 | counts 1 | counts 2: max_queries x u64 each ]
+ *   [ scratch: max_queries x u64 (packed queries of the running K1) ]
+ * Step e accumulates into buffer e mod 3.  A rank clears the buffer of the NEXT step before it searches, which no
+ * peer can touch before it has passed this step's barrier; with three buffers the counts rs_comm_finish(e) returned
+ * are still intact after rs_comm_begin(e + 1) (which clears buffer e + 2) and die with rs_comm_begin(e + 2).
  */
 #include "rs_internal.h"
 
@@ -33,9 +34,9 @@ struct rs_comm {
   void* packed_stream = nullptr;
 };
 
-static size_t comm_bytes(uint64_t maxq) { return RS_COMM_HDR + 3 * maxq * sizeof(uint64_t); }
+static size_t comm_bytes(uint64_t maxq) { return RS_COMM_HDR + 4 * maxq * sizeof(uint64_t); }
 static uint64_t* comm_counts(uint8_t* base, uint64_t maxq, uint64_t epoch) {
-  return reinterpret_cast<uint64_t*>(base + RS_COMM_HDR) + (epoch & 1) * maxq;
+  return reinterpret_cast<uint64_t*>(base + RS_COMM_HDR) + (epoch % 3) * maxq;
 }
 
 __global__ void k_peer_barrier(uint64_t* const* __restrict__ peer_flags, uint32_t world, uint32_t rank, uint64_t epoch,
@@ -157,7 +158,7 @@ int rs_count_accumulate_dev(const rs_index* ix, rs_comm* c, const void* d_kmers,
   peers.world = c->world;
   peers.rank = c->rank;
   for (uint32_t r = 0; r < c->world; ++r) peers.buf[r] = comm_counts(c->peer_base[r], c->max_queries, c->epoch);
-  uint64_t* scratch = reinterpret_cast<uint64_t*>(c->base + RS_COMM_HDR) + 2 * c->max_queries;
+  uint64_t* scratch = reinterpret_cast<uint64_t*>(c->base + RS_COMM_HDR) + 3 * c->max_queries;
   const bool reuse = c->packed_src == d_kmers && c->packed_k == k && c->packed_strand == strand && c->packed_stream == stream;
   CU(rs_launch_find_interval(ix->dev, (const uint8_t*)d_kmers, nullptr, (uint32_t)k, Q, scratch, nullptr, reuse ? 3 : 2, strand,
                              (unsigned long long*)ix->d_stats, (cudaStream_t)stream, &peers));

@@ -225,7 +225,10 @@ __global__ void __launch_bounds__(256, RS_GATHER_BLOCKS)
     uint64_t* __restrict__ hits = P.hits[owner];
     uint64_t off = slot[q0 + q];
     uint32_t b0 = 0, b1 = 0, b2 = 0, b3 = 0;
-    /* A k-mer of a read set at 30x hits a handful of rows in most of the shards: the lanes take one shard each
+    /* The table reads below are 4 and 16 bytes at random addresses, and HBM delivers whole 128-byte lines for them
+     * (ncu on configs[2]: 247 GB of DRAM reads per 10 M-query step for 790 M hits = 1.9 G line fetches at 26 G lines/s,
+     * the rate of the random-access probe); ld.global.cg instead of the L1 path made it slower (82 vs 73 ms).
+     * A k-mer of a read set at 30x hits a handful of rows in most of the shards: the lanes take one shard each
      * (32 independent chains of loads in flight per warp), a warp scan lays their rows out in shard order. */
     for (uint32_t s0 = 0; s0 < T.nshards; s0 += 32) {
       const uint32_t s = s0 + lane;
@@ -655,8 +658,8 @@ int rs_shardset_enable_stats(rs_shardset* set, int on) {
   std::lock_guard<std::mutex> lk(set->mu);
   CU(cudaSetDevice(set->device));
   if (on && !set->d_stats) {
-    CU(cudaMalloc((void**)&set->d_stats, 16));
-    CU(cudaMemset(set->d_stats, 0, 16));
+    CU(cudaMalloc((void**)&set->d_stats, 32));
+    CU(cudaMemset(set->d_stats, 0, 32));
   } else if (!on && set->d_stats) {
     CU(cudaDeviceSynchronize());
     cudaFree(set->d_stats);
@@ -665,16 +668,17 @@ int rs_shardset_enable_stats(rs_shardset* set, int on) {
   return RS_STATUS_OK;
 }
 
-int rs_shardset_read_stats(rs_shardset* set, uint64_t* interval_steps, uint64_t* walk_steps, int reset) {
+int rs_shardset_read_stats(rs_shardset* set, uint64_t* interval_steps, uint64_t* walk_steps, uint64_t* block_loads, int reset) {
   if (!set) return fail(RS_STATUS_ARG, "null argument");
   if (!set->d_stats) return fail(RS_STATUS_NO_TABLE, "statistics are not enabled");
   CU(cudaSetDevice(set->device));
   CU(cudaDeviceSynchronize());
-  uint64_t v[2] = {0, 0};
-  CU(cudaMemcpy(v, set->d_stats, 16, cudaMemcpyDeviceToHost));
+  uint64_t v[4] = {0, 0, 0, 0};
+  CU(cudaMemcpy(v, set->d_stats, 32, cudaMemcpyDeviceToHost));
   if (interval_steps) *interval_steps = v[0];
   if (walk_steps) *walk_steps = v[1];
-  if (reset) CU(cudaMemset(set->d_stats, 0, 16));
+  if (block_loads) *block_loads = v[2];
+  if (reset) CU(cudaMemset(set->d_stats, 0, 32));
   return RS_STATUS_OK;
 }
 

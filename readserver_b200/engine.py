@@ -79,7 +79,7 @@ def lib() -> C.CDLL:
         "rs_shardset_destroy": (None, [vp]),
         "rs_shardset_get_info": (i32, [vp, C.POINTER(ShardSetInfo)]),
         "rs_shardset_enable_stats": (i32, [vp, i32]),
-        "rs_shardset_read_stats": (i32, [vp, C.POINTER(u64), C.POINTER(u64), i32]),
+        "rs_shardset_read_stats": (i32, [vp, C.POINTER(u64), C.POINTER(u64), C.POINTER(u64), i32]),
         "rs_shardset_enable_timing": (i32, [vp, i32]),
         "rs_shardset_read_timing": (i32, [vp, C.POINTER(C.c_double), C.POINTER(u64)]),
         "rs_popcomm_create": (i32, [i32, i32, i32, u64, u64, C.POINTER(vp)]),
@@ -613,10 +613,11 @@ class ShardSet:
     def enable_stats(self, on: bool = True):
         _check(lib().rs_shardset_enable_stats(self._h, int(on)))
 
-    def read_stats(self, reset: bool = True) -> tuple[int, int]:
-        a, b = C.c_uint64(), C.c_uint64()
-        _check(lib().rs_shardset_read_stats(self._h, C.byref(a), C.byref(b), int(reset)))
-        return int(a.value), int(b.value)
+    def read_stats(self, reset: bool = True) -> tuple[int, int, int]:
+        """(updateInterval steps, LF-walk steps, 64-byte blocks read by K1) since the last reset."""
+        a, b, c = C.c_uint64(), C.c_uint64(), C.c_uint64()
+        _check(lib().rs_shardset_read_stats(self._h, C.byref(a), C.byref(b), C.byref(c), int(reset)))
+        return int(a.value), int(b.value), int(c.value)
 
     def enable_timing(self, on: bool = True):
         _check(lib().rs_shardset_enable_timing(self._h, int(on)))

@@ -463,3 +463,63 @@ def test_dense_blocks_on_degenerate_shapes_and_auto_policy(engine, monkeypatch):
     runs = shapes["ones"]
     with engine.GpuBWT(runs=runs, num_strings=int(((runs >> 5) == 0).sum()), num_symbols=runs.size) as A:
         assert A.info.dense_blocks == 0
+
+
+# ------------------------------------------------------------------------------------------------
+# round-1 advisor findings
+# ------------------------------------------------------------------------------------------------
+def test_fused_count_buffers_survive_the_next_begin(datasets, engine):
+    """rs_comm_finish(e)'s counts stay valid until the next-but-one rs_comm_begin (three rotating buffers)."""
+    import torch
+    from readserver_b200 import sharding
+    case = datasets.case("clean")
+    Q = 5000
+    q1, q2 = case.queries(Q, 31, seed=1), case.queries(Q, 31, seed=2)
+    with engine.GpuBWT(runs=case.runs, num_strings=case.num_strings, num_symbols=case.num_symbols) as B:
+        want1, want2 = B.count(q1, 31), B.count(q2, 31)
+        comm = sharding.connect_peers(engine.PeerComm(0, 0, 1, Q), "cuda:0")
+        d1, d2 = torch.from_numpy(q1).cuda(), torch.from_numpy(q2).cuda()
+        comm.begin(Q)
+        comm.accumulate(B, d1, 31, Q)
+        p1 = comm.finish()
+        comm.begin(Q)                                    # step e + 1 clears the buffer of step e + 2, not step e's
+        torch.cuda.synchronize()
+        assert np.array_equal(sharding.counts_view(p1, Q, "cuda:0").cpu().numpy().view(np.uint64), want1)
+        comm.accumulate(B, d2, 31, Q)
+        p2 = comm.finish()
+        torch.cuda.synchronize()
+        assert p2 != p1
+        assert np.array_equal(sharding.counts_view(p2, Q, "cuda:0").cpu().numpy().view(np.uint64), want2)
+        assert np.array_equal(sharding.counts_view(p1, Q, "cuda:0").cpu().numpy().view(np.uint64), want1)
+        comm.close()
+
+
+def test_locate_tables_when_the_tail_region_holds_no_T(engine):
+    """Under the reference's tail behaviour an LF step can land on row n (rank clamped, every T already counted): the
+    table builders must skip it instead of writing past their arrays.  Tail region here: the last runs are A/C/G only."""
+    runs, _ = random_runs(9, 60_000)
+    runs = runs.copy()
+    tail = runs[-6000:]
+    sym = tail >> 5
+    tail[sym == 4] = (np.uint8(1) << 5) | (tail[sym == 4] & 31)       # T -> A in the last 6000 runs
+    n = int((runs & 31).sum())
+    ns = int((runs[(runs >> 5) == 0] & 31).sum())
+    P = oracle.PortIndex(runs=runs, num_strings=ns, num_symbols=n)
+    with engine.GpuBWT(runs=runs, num_strings=ns, num_symbols=n) as B:
+        assert B.info.ref_clamp_c < n                                  # the tail region is not empty
+        rng = np.random.default_rng(1)
+        rows = np.concatenate([rng.integers(0, n, 20000).astype(np.uint64), np.arange(n - 3000, n, dtype=np.uint64)])
+        base = B.extract_prefix(rows, max_steps=200)
+        lex, st, _, _ = P.locate_batch(rows, prefix=True, postfix=False, max_steps=200)
+        assert np.array_equal(base[0], lex) and np.array_equal(base[1], st)
+        for dense in (True, False):
+            B.set_dense(dense)
+            for every in (1, 4, 16):
+                B.build_locate_table(200, every=every)
+                got = B.extract_prefix(rows, max_steps=200)
+                assert np.array_equal(got[0], base[0]) and np.array_equal(got[1], base[1]), (dense, every)
+                B.drop_locate_table()
+        B.set_sai(np.arange(ns, dtype=np.uint64))
+        with engine.ShardSet() as S:                                   # the read-index table takes the same walks
+            S.add(B, 0)
+            S.seal(200, 1)
