@@ -364,3 +364,124 @@ def decode_sample_value(value: bytes, size_of_sample: int, has_other_meta_data: 
                                                 codes.ctypes.data, counts.ctypes.data, lanes.ctypes.data, cap)
     return [(codes[i * size_of_sample:(i + 1) * size_of_sample].tobytes(), int(counts[i]), int(lanes[i]))
             for i in range(n)]
+
+
+# ------------------------------------------------------------------------------------------------
+# functions of the reference's query worker, its sample-code tool and its config library (oracle/_ref, Makefile `ref`)
+# ------------------------------------------------------------------------------------------------
+REF_SERVICE_SO = os.path.join(REF_DIR, "libref_service.so")
+REF_CREATE_SAMPLES_HASH = os.path.join(REF_DIR, "create_samples_hash")
+REF_CONFIG_SO = os.path.join(REF_DIR, "libref_config.so")
+
+
+def have_ref_service() -> bool:
+    return os.path.exists(REF_SERVICE_SO)
+
+
+class RefService:
+    """is_suffix_of / get_tiles / rev_comp / find_gt_reads exactly as src/service/service.cpp holds them: cut out of that
+    file at build time (oracle/Makefile) and compiled behind ref_service_shim.cpp, over the reference's own RLEBWT."""
+    _lib = None
+    THROW = (1 << 64) - 1
+
+    @classmethod
+    def lib(cls):
+        if cls._lib is None:
+            L = C.CDLL(REF_SERVICE_SO)
+            sz = C.c_size_t
+            L.refsvc_open.restype = C.c_void_p
+            L.refsvc_open.argtypes = [C.c_char_p]
+            L.refsvc_close.argtypes = [C.c_void_p]
+            L.refsvc_set_limits.argtypes = [sz, sz, sz]
+            L.refsvc_get_tiles.restype = sz
+            L.refsvc_get_tiles.argtypes = [C.c_char_p, sz, sz, C.c_char_p, sz]
+            L.refsvc_is_suffix_of.argtypes = [C.c_char_p, C.c_char_p]
+            L.refsvc_rev_comp.restype = sz
+            L.refsvc_rev_comp.argtypes = [C.c_char_p, C.c_char_p, sz]
+            L.refsvc_find_gt_reads.restype = sz
+            L.refsvc_find_gt_reads.argtypes = [C.c_void_p, C.c_char_p, sz, sz, sz, sz, C.c_char_p, sz]
+            L.refsvc_gt_task_reads.restype = sz
+            L.refsvc_gt_task_reads.argtypes = [C.c_void_p, C.c_char_p, sz, sz, sz, C.c_char_p, sz]
+            cls._lib = L
+        return cls._lib
+
+    def __init__(self, bwt_path: str | None = None):
+        self._L = self.lib()
+        self._h = self._L.refsvc_open(bwt_path.encode()) if bwt_path else None
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._L.refsvc_close(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def set_limits(self, max_interval_size: int = 10000, max_read_length: int = 100, min_read_length: int = 73):
+        self._L.refsvc_set_limits(max_interval_size, max_read_length, min_read_length)
+
+    def _strings(self, n, buf):
+        if n == self.THROW:
+            return None
+        assert n != self.THROW - 1, "buffer too small"
+        s = buf.value.decode("latin1")
+        out = s.split("\n")[:-1] if s else []
+        assert len(out) == n
+        return out
+
+    def get_tiles(self, w: str, kmer: int, skip: int = 0, cap: int = 1 << 22):
+        buf = C.create_string_buffer(cap)
+        return self._strings(self._L.refsvc_get_tiles(w.encode("latin1"), kmer, skip, buf, cap), buf)
+
+    def is_suffix_of(self, s: str, w: str) -> bool:
+        return bool(self._L.refsvc_is_suffix_of(s.encode(), w.encode()))
+
+    def rev_comp(self, w: str) -> str:
+        buf = C.create_string_buffer(len(w) + 8)
+        self._L.refsvc_rev_comp(w.encode("latin1"), buf, len(w) + 8)
+        return buf.value.decode("latin1")
+
+    def find_gt_reads(self, w: str, index: int, kmers: int, skip: int, pos: int, cap: int = 1 << 24):
+        """Sorted read strings of tile `index`; None when the reference throws (substr out of range)."""
+        buf = C.create_string_buffer(cap)
+        return self._strings(self._L.refsvc_find_gt_reads(self._h, w.encode("latin1"), index, kmers, skip, pos, buf, cap), buf)
+
+    def gt_task_reads(self, w: str, kmers: int, skip: int, pos: int, cap: int = 1 << 24):
+        buf = C.create_string_buffer(cap)
+        return self._strings(self._L.refsvc_gt_task_reads(self._h, w.encode("latin1"), kmers, skip, pos, buf, cap), buf)
+
+
+def ref_create_samples_hash(names: list[str]) -> dict:
+    """name -> code bytes, by running the reference's own tool (src/util/create_samples_hash.cpp) on a name list."""
+    import tempfile
+    with tempfile.TemporaryDirectory() as d:
+        src, dst = os.path.join(d, "names"), os.path.join(d, "hash")
+        with open(src, "w") as f:
+            f.write("\n".join(names) + "\n")
+        subprocess.run([REF_CREATE_SAMPLES_HASH, src, dst], check=True)
+        out = {}
+        with open(dst, "rb") as f:
+            for line in f.read().split(b"\n"):
+                if line:
+                    name, code = line.split(b"\t", 1)
+                    out[name.decode()] = code
+        return out
+
+
+def ref_config(path: str, string_keys: list[str], array_keys: list[str]) -> dict:
+    """The settings of a worker .cfg as the reference's libconfig 1.5 reads them (service.cpp:1407-1437)."""
+    L = C.CDLL(REF_CONFIG_SO)
+    L.refcfg_lookup_string.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.c_size_t]
+    L.refcfg_lookup_array.argtypes = [C.c_char_p, C.c_char_p, C.c_char_p, C.c_size_t]
+    buf = C.create_string_buffer(1 << 16)
+    out = {}
+    for k in string_keys:
+        rc = L.refcfg_lookup_string(path.encode(), k.encode(), buf, len(buf))
+        if rc < 0:
+            raise ValueError("libconfig: parse error")
+        out[k] = buf.value.decode() if rc == 1 else None
+    for k in array_keys:
+        n = L.refcfg_lookup_array(path.encode(), k.encode(), buf, len(buf))
+        if n == -1:
+            raise ValueError("libconfig: parse error")
+        out[k] = buf.value.decode().split("\n")[:-1] if n >= 0 else None
+    return out
