@@ -85,3 +85,40 @@ def test_shim_matches_oracle(tmp_path):
         some += len(reads)
     assert some > 0
     assert out[2 + 3 * len(qs)] == "error 1"
+
+
+@pytest.mark.gpu
+def test_references_own_query_cpp_runs_over_gpubwt(tmp_path):
+    """INTEGRATION.md section 2, proven: the reference's unmodified src/bwt/query.cpp -- findInterval, extractPrefix,
+    extractPostfix, query, query_exactmatch -- compiled from /root/reference in the build container and linked against
+    rsb200::GpuBWT (oracle/_ref/ref_query_over_gpubwt, built by oracle/Makefile), gives on the GPU what it gives over
+    the reference's own RLEBWT (the oracle)."""
+    import numpy as np
+    import oracle
+    from tests import common
+    exe = os.path.join(ROOT, "oracle", "_ref", "ref_query_over_gpubwt")
+    if not os.path.exists(exe):
+        pytest.skip("oracle/_ref/ref_query_over_gpubwt is built in the build container (needs /root/reference)")
+    bwt = os.path.join(common.GOLDEN, "clean.bwt")
+    z = np.load(os.path.join(common.GOLDEN, "clean.npz"))
+    P = oracle.open_best(bwt) if oracle.have_ref() else oracle.PortIndex(bwt)
+    Pp = oracle.PortIndex(bwt)
+    gold = common.make_case("clean", *common.Datasets.SPECS["clean"][:3], min_len=73, keep_reads=True)
+    full = [r for r in gold.reads if len(r) == 100]
+    qs = [bytes(k).decode() for k in z["kmers"][:25]] + [full[1], full[2][:80], "ACGTNACGT", "GATTACA", full[3][20:60]]
+    rows = [int(r) for r in z["read_rows"][:20]]
+    (tmp_path / "q.txt").write_text("\n".join(qs) + "\n")
+    (tmp_path / "r.txt").write_text("\n".join(str(r) for r in rows) + "\n")
+    out = subprocess.run([exe, bwt, str(tmp_path / "q.txt"), str(tmp_path / "r.txt")], check=True, capture_output=True,
+                         text=True).stdout.splitlines()
+    assert len(out) == 3 * len(qs) + len(rows)
+    for i, q in enumerate(qs):
+        lo, up = P.find_interval(q)
+        assert out[3 * i] == f"I {lo} {up}", q
+        acgt = all(c in "ACGT" for c in q)
+        reads = [Pp.extract_read(r) for r in range(lo, up + 1)] if acgt and up >= lo else []
+        assert out[3 * i + 1] == f"X {int(acgt and q in reads)}", q
+        assert out[3 * i + 2].split() == ["Q", str(len(reads))] + reads, q
+    for j, r in enumerate(rows):
+        assert out[3 * len(qs) + j] == f"R {Pp.extract_prefix(r)[0]}|{Pp.extract_postfix(r)[0]}"
+    assert any(l.startswith("X 1") for l in out)
