@@ -65,10 +65,19 @@ def parse():
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU time of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-side", action="store_true", help="skip the side measurements (configs[1] count line, roofline probe)")
+    ap.add_argument("--workload", default="configs2", choices=["configs2", "configs4"],
+                    help="configs2 (default, the metric's): 10 M 31-mers, forward strand.  configs4: variant-allele probes over "
+                         "the same population -- --sites sites of its list, the reference- and the alternative-allele 31-mer "
+                         "centred on each, both strands -> read indices -> carrier sets")
+    ap.add_argument("--sites", type=int, default=1_000_000)
     a = ap.parse_args()
     if a.scale != 1.0:
         a.genome = max(200_000, int(a.genome * a.scale))
         a.queries = max(10_000, int(a.queries * a.scale))
+        a.sites = max(5_000, int(a.sites * a.scale))
+    if a.workload == "configs4":
+        a.queries = 2 * a.sites
+    a.strands = (0, 1) if a.workload == "configs4" else (0,)
     return a
 
 
@@ -77,6 +86,11 @@ def dist_env():
 
 
 def workload_name(args):
+    if args.workload == "configs4":
+        return (f"configs[4]: {args.sites} sites of the population's list, reference- and alternative-allele {args.k}-mer centred "
+                f"on each ({args.queries} k-mers), both strands -> matching read indices -> per-k-mer carrier sets; population = "
+                f"configs[2]'s ({args.samples} diploid samples x {args.coverage:g}x of {args.read_len}-bp reads, random "
+                f"{args.genome / 1e6:g} Mbp genome, {NSHARDS} shards by reversed last 3 bases)")
     return (f"configs[2]: {args.samples} diploid samples x {args.coverage:g}x of {args.read_len}-bp reads over a random "
             f"{args.genome / 1e6:g} Mbp genome (sites 1/300, ~1 SNP/kb per haplotype), de-duplicated, {NSHARDS} shards by "
             f"reversed last 3 bases, per-shard RLBWT + .sai + sample table; {args.queries} random {args.k}-mers (90% present), "
@@ -123,7 +137,11 @@ def build_population(args, device, shards_wanted=None, keep_host=False, make_ind
         out["shards"][s] = ent
         del sh, b
     del keys
-    queries = dg.population_queries(pop, args.queries, args.k, seed=5).contiguous()
+    if args.workload == "configs4":
+        ref, alt, _ = dg.site_probe_kmers(pop, args.sites, args.k, seed=6)
+        queries = torch.stack([ref, alt], dim=1).reshape(-1, args.k).contiguous()   # ref, alt, ref, alt, ...
+    else:
+        queries = dg.population_queries(pop, args.queries, args.k, seed=5).contiguous()
     out.update(queries=queries, totals=tot, build_seconds=time.time() - t0, key_seconds=t_keys)
     del pop
     if device != "cpu":
@@ -413,7 +431,15 @@ def side_configs1(args, engine, dev, local_rank, flush):
     return out
 
 
+def revcomp_rows(q: np.ndarray) -> np.ndarray:
+    comp = np.zeros(256, dtype=np.uint8)
+    for x, y in zip(b"ACGT", b"TGCA"):
+        comp[x] = y
+    return np.ascontiguousarray(comp[q[:, ::-1]])
+
+
 def run_ours(args):
+    import ctypes as C
     import torch
     import torch.distributed as dist
     rank, local_rank, world = dist_env()
@@ -436,46 +462,52 @@ def run_ours(args):
     info = S.seal(args.read_len + 28, args.locate_every)
     seal_s = time.time() - t0
     S.enable_stats(True)
-    Q, k = args.queries, args.k
+    Q, k, strands = args.queries, args.k, args.strands
     dq = data["queries"]
     W = int(info.carrier_words)
     torch.cuda.synchronize()
     torch.cuda.cudart().cudaProfilerStart()  # `ncu --profile-from-start off` skips the synthetic-data build
     stream = torch.cuda.current_stream().cuda_stream
-    d_counts = torch.empty(Q, dtype=torch.int64, device=dev)
-    d_off = torch.empty(Q + 1, dtype=torch.int64, device=dev)
+    # sizing pass per strand: hits of the batch in this rank's shards
+    tmp_c = torch.empty(Q, dtype=torch.int64, device=dev)
+    tmp_o = torch.empty(Q + 1, dtype=torch.int64, device=dev)
     d_total = torch.zeros(1, dtype=torch.int64, device=dev)
-    # sizing pass: hits of the batch in this rank's shards
-    S.query_dev(dq, k, Q, False, MAX_HITS, d_counts, d_off, None, 0, None, d_total, stream)
-    torch.cuda.synchronize()
-    local_hits = int(d_total.item())
-    comm = None
-    if world > 1:
-        th = torch.tensor([local_hits], dtype=torch.int64, device=dev)
-        dist.all_reduce(th)
-        total_hits = int(th.item())
-        cap = int(total_hits / world * 1.3) + (1 << 20)   # ownership by 4-base prefix is even for random k-mers
-        comm = sharding.connect_peers(engine.PopComm(local_rank, rank, world, Q, cap), dev)
-        del d_counts, d_off
-    else:
-        total_hits = local_hits
-        cap = max(total_hits, 1)
-        d_hits = torch.empty(cap, dtype=torch.int64, device=dev)
-        d_carr = torch.empty((Q, W), dtype=torch.int32, device=dev)
+    local_hits = {}
+    for sd in strands:
+        S.query_dev(dq, k, Q, False, MAX_HITS, tmp_c, tmp_o, None, 0, None, d_total, stream, strand=sd)
+        torch.cuda.synchronize()
+        local_hits[sd] = int(d_total.item())
+    del tmp_c, tmp_o
+    out, comms, caps, total_hits = {}, {}, {}, {}
+    for sd in strands:
+        if world > 1:
+            th = torch.tensor([local_hits[sd]], dtype=torch.int64, device=dev)
+            dist.all_reduce(th)
+            total_hits[sd] = int(th.item())
+            caps[sd] = int(total_hits[sd] / world * 1.3) + (1 << 20)   # ownership by 4-base prefix is even for random k-mers
+            comms[sd] = sharding.connect_peers(engine.PopComm(local_rank, rank, world, Q, caps[sd]), dev)
+        else:
+            total_hits[sd] = local_hits[sd]
+            caps[sd] = max(total_hits[sd], 1)
+            out[sd] = dict(counts=torch.empty(Q, dtype=torch.int64, device=dev), off=torch.empty(Q + 1, dtype=torch.int64, device=dev),
+                           hits=torch.empty(caps[sd], dtype=torch.int64, device=dev),
+                           carr=torch.empty((Q, W), dtype=torch.int32, device=dev))
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)  # > 126 MB L2
 
     def step():
-        if world > 1:
-            comm.query_dev(S, dq, k, Q, False, MAX_HITS, True, True, stream)
-        else:
-            S.query_dev(dq, k, Q, False, MAX_HITS, d_counts, d_off, d_hits, cap, d_carr, d_total, stream)
+        for sd in strands:
+            if world > 1:
+                comms[sd].query_dev(S, dq, k, Q, False, MAX_HITS, True, True, stream, strand=sd)
+            else:
+                o = out[sd]
+                S.query_dev(dq, k, Q, False, MAX_HITS, o["counts"], o["off"], o["hits"], caps[sd], o["carr"], d_total, stream, strand=sd)
 
     for _ in range(max(3, args.warmup)):
         step()
     torch.cuda.synchronize()
     if world > 1:
         dist.barrier()
-        assert not comm.timed_out(), "peer barrier timed out"
+        assert not any(c.timed_out() for c in comms.values()), "peer barrier timed out"
     S.read_stats(reset=True)
     S.enable_timing(True)
     clocks = ClockSampler(local_rank)
@@ -505,86 +537,93 @@ def run_ours(args):
         dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
     total_ms = float(total_ms.item())
 
-    # ---- N > 1: the fanned-in answers against the ranks' own answers gathered with NCCL / gloo-style collectives ----
+    # ---- N > 1: the fanned-in answers against the ranks' own answers, gathered with torch.distributed ----
     fan_in_ok = None
     if world > 1:
-        assert not comm.timed_out(), "peer barrier timed out"
-        res = comm.results(Q, dev)
-        owner = torch.from_numpy(sharding.owner_of(dq.cpu().numpy(), world)).to(dev)
-        mine = owner == rank
-        lc = torch.empty(Q, dtype=torch.int64, device=dev)
-        lo_ = torch.empty(Q + 1, dtype=torch.int64, device=dev)
-        lt = torch.zeros(1, dtype=torch.int64, device=dev)
-        lh = torch.empty(max(local_hits, 1), dtype=torch.int64, device=dev)
-        lcar = torch.empty((Q, W), dtype=torch.int32, device=dev)
-        S.query_dev(dq, k, Q, False, MAX_HITS, lc, lo_, lh, max(local_hits, 1), lcar, lt, stream)
-        torch.cuda.synchronize()
-        gc = lc.clone()
-        dist.all_reduce(gc)
-        ok = bool(torch.equal(res["counts"][mine], gc[mine]) and int(res["counts"][~mine].abs().sum()) == 0)
-        # hit lists: per owned k-mer the number of hits = sum of the ranks' numbers; on a sample the lists themselves
-        nh = (lo_[1:] - lo_[:-1]).clone()
-        dist.all_reduce(nh)
-        got_n = res["hit_offsets"][1:] - res["hit_offsets"][:-1]
-        ok &= bool(torch.equal(got_n[mine], nh[mine]) and int(got_n[~mine].sum()) == 0)
-        ok &= int(res["total"].item()) <= cap
-        nsamp = min(Q, 20000)
-        h_end = int(lo_[nsamp].item())
-        pieces = [None] * world
-        dist.all_gather_object(pieces, (lo_[: nsamp + 1].cpu().numpy(), lh[:h_end].cpu().numpy(), lcar[:nsamp].cpu().numpy()))
-        ro = res["hit_offsets"][: nsamp + 1].cpu().numpy()
-        rh = res["hits"][: int(ro[-1])].cpu().numpy() if int(ro[-1]) else np.zeros(0, np.int64)
-        rc = res["carriers"][:nsamp].cpu().numpy()
-        own_np = owner[:nsamp].cpu().numpy()
-        for i in np.nonzero(own_np == rank)[0][:4000]:
-            want = np.concatenate([p[1][int(p[0][i]): int(p[0][i + 1])] for p in pieces])
-            ok &= bool(np.array_equal(rh[int(ro[i]): int(ro[i + 1])], want))
-            wc = np.bitwise_or.reduce(np.stack([p[2][i] for p in pieces]), axis=0)
-            ok &= bool(np.array_equal(rc[i], wc))
+        ok = True
+        dq_np = dq.cpu().numpy()
+        for sd in strands:
+            comm = comms[sd]
+            assert not comm.timed_out(), "peer barrier timed out"
+            res = comm.results(Q, dev)
+            searched = revcomp_rows(dq_np) if sd else dq_np          # ownership goes by the searched string
+            owner = torch.from_numpy(sharding.owner_of(searched, world)).to(dev)
+            mine = owner == rank
+            lc = torch.empty(Q, dtype=torch.int64, device=dev)
+            lo_ = torch.empty(Q + 1, dtype=torch.int64, device=dev)
+            lh = torch.empty(max(local_hits[sd], 1), dtype=torch.int64, device=dev)
+            lcar = torch.empty((Q, W), dtype=torch.int32, device=dev)
+            S.query_dev(dq, k, Q, False, MAX_HITS, lc, lo_, lh, max(local_hits[sd], 1), lcar, d_total, stream, strand=sd)
+            torch.cuda.synchronize()
+            gc = lc.clone()
+            dist.all_reduce(gc)
+            ok &= bool(torch.equal(res["counts"][mine], gc[mine]) and int(res["counts"][~mine].abs().sum()) == 0)
+            # hit lists: per owned k-mer the number of hits = sum of the ranks' numbers; on a sample the lists themselves
+            nh = (lo_[1:] - lo_[:-1]).clone()
+            dist.all_reduce(nh)
+            got_n = res["hit_offsets"][1:] - res["hit_offsets"][:-1]
+            ok &= bool(torch.equal(got_n[mine], nh[mine]) and int(got_n[~mine].sum()) == 0)
+            ok &= int(res["total"].item()) <= caps[sd]
+            nsamp = min(Q, 20000)
+            h_end = int(lo_[nsamp].item())
+            pieces = [None] * world
+            dist.all_gather_object(pieces, (lo_[: nsamp + 1].cpu().numpy(), lh[:h_end].cpu().numpy(), lcar[:nsamp].cpu().numpy()))
+            ro = res["hit_offsets"][: nsamp + 1].cpu().numpy()
+            rh = res["hits"][: int(ro[-1])].cpu().numpy() if int(ro[-1]) else np.zeros(0, np.int64)
+            rc = res["carriers"][:nsamp].cpu().numpy()
+            own_np = owner[:nsamp].cpu().numpy()
+            for i in np.nonzero(own_np == rank)[0][:4000]:
+                want = np.concatenate([p[1][int(p[0][i]): int(p[0][i + 1])] for p in pieces])
+                ok &= bool(np.array_equal(rh[int(ro[i]): int(ro[i + 1])], want))
+                wc = np.bitwise_or.reduce(np.stack([p[2][i] for p in pieces]), axis=0)
+                ok &= bool(np.array_equal(rc[i], wc))
+            del lc, lo_, lh, lcar, gc, nh
         okt = torch.tensor([int(ok)], device=dev)
         dist.all_reduce(okt, op=dist.ReduceOp.MIN)
         fan_in_ok = bool(okt.item())
         assert fan_in_ok, "results fanned in through peer memory differ from the ranks' own answers"
-        del lc, lo_, lh, lcar, gc, nh
 
-    # ---- e2e: host-pointer call, pinned host buffers, every copy inside the timed region ----
+    # ---- e2e: host buffers (pinned), every copy inside the timed region ----
     L = engine.lib()
-    import ctypes as C
     hq, _p0 = pinned_array(engine, Q * k, np.uint8, (Q, k))
     hq[:] = dq.cpu().numpy()
     e2e_steps = max(3, args.steps // 2)
+    host, keep_alive = {}, [_p0]
+    for sd in strands:
+        cap = caps[sd]
+        dt = np.uint64 if world == 1 else np.int64
+        a1, p1 = pinned_array(engine, Q * 8, dt, (Q,))
+        a2, p2 = pinned_array(engine, (Q + 1) * 8, dt, (Q + 1,))
+        a3, p3 = pinned_array(engine, cap * 8, dt, (cap,))
+        a4, p4 = pinned_array(engine, Q * W * 4, np.uint32 if world == 1 else np.int32, (Q, W))
+        host[sd] = dict(counts=a1, off=a2, hits=a3, carr=a4)
+        keep_alive += [p1, p2, p3, p4]
+    tot = C.c_uint64()
     if world == 1:
-        hcounts, _p1 = pinned_array(engine, Q * 8, np.uint64, (Q,))
-        hoff, _p2 = pinned_array(engine, (Q + 1) * 8, np.uint64, (Q + 1,))
-        hhits, _p3 = pinned_array(engine, cap * 8, np.uint64, (cap,))
-        hcarr, _p4 = pinned_array(engine, Q * W * 4, np.uint32, (Q, W))
-        tot = C.c_uint64()
-
         def e2e_call():
-            rc = L.rs_pop_query(S._h, hq.ctypes.data, k, Q, 0, MAX_HITS, hcounts.ctypes.data, hoff.ctypes.data,
-                                hhits.ctypes.data, cap, hcarr.ctypes.data, C.byref(tot))
-            assert rc == 0, rc
-        d2h = Q * 8 + (Q + 1) * 8 + total_hits * 8 + Q * W * 4 + 8
+            for sd in strands:
+                h = host[sd]
+                rc = L.rs_pop_query(S._h, hq.ctypes.data, k, Q, 0, sd, MAX_HITS, h["counts"].ctypes.data, h["off"].ctypes.data,
+                                    h["hits"].ctypes.data, caps[sd], h["carr"].ctypes.data, C.byref(tot))
+                assert rc == 0, rc
+        d2h = sum(Q * 8 + (Q + 1) * 8 + total_hits[sd] * 8 + Q * W * 4 + 8 for sd in strands)
     else:
         # every rank: batch in, the pipeline with its fan-in, the answers of the k-mers it owns out
-        res = comm.results(Q, dev)
-        hcounts, _p1 = pinned_array(engine, Q * 8, np.int64, (Q,))
-        hoff, _p2 = pinned_array(engine, (Q + 1) * 8, np.int64, (Q + 1,))
-        hhits, _p3 = pinned_array(engine, cap * 8, np.int64, (cap,))
-        hcarr, _p4 = pinned_array(engine, Q * 16, np.int32, (Q, 4))
-        t_counts, t_off, t_hits, t_carr = (torch.from_numpy(x) for x in (hcounts, hoff, hhits, hcarr))
         t_hq = torch.from_numpy(hq)
         dq2 = torch.empty_like(dq)
+        views = {sd: {n: torch.from_numpy(a) for n, a in host[sd].items()} for sd in strands}
 
         def e2e_call():
             dq2.copy_(t_hq, non_blocking=True)
-            comm.query_dev(S, dq2, k, Q, False, MAX_HITS, True, True, stream)
-            t_counts.copy_(res["counts"], non_blocking=True)
-            t_off.copy_(res["hit_offsets"], non_blocking=True)
-            t_carr.copy_(res["carriers"], non_blocking=True)
-            torch.cuda.synchronize()
-            n = int(hoff[Q])
-            t_hits[:n].copy_(res["hits"][:n], non_blocking=True)
+            for sd in strands:
+                res, v = comms[sd].results(Q, dev), views[sd]
+                comms[sd].query_dev(S, dq2, k, Q, False, MAX_HITS, True, True, stream, strand=sd)
+                v["counts"].copy_(res["counts"], non_blocking=True)
+                v["off"].copy_(res["hit_offsets"], non_blocking=True)
+                v["carr"].copy_(res["carriers"], non_blocking=True)
+                torch.cuda.synchronize()
+                n = int(host[sd]["off"][Q])
+                v["hits"][:n].copy_(res["hits"][:n], non_blocking=True)
             torch.cuda.synchronize()
         d2h = None
     for _ in range(2):
@@ -601,17 +640,21 @@ def run_ours(args):
         e2e_call()
         e2e_s += time.perf_counter() - t0
     e2e_t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
-    own_hits = torch.tensor([int(hoff[Q])], dtype=torch.int64, device=dev)
     if world > 1:
+        own_hits = torch.tensor([sum(int(host[sd]["off"][Q]) for sd in strands)], dtype=torch.int64, device=dev)
         dist.all_reduce(e2e_t, op=dist.ReduceOp.MAX)
         dist.all_reduce(own_hits)
-        d2h = world * (Q * 8 + (Q + 1) * 8 + Q * 16) + int(own_hits.item()) * 8
+        d2h = world * len(strands) * (Q * 8 + (Q + 1) * 8 + Q * 16) + int(own_hits.item()) * 8
     e2e_s = float(e2e_t.item())
     if world == 1:
         # the host path and the device path give the same answers
-        assert np.array_equal(hcounts, d_counts.cpu().numpy().view(np.uint64)) and np.array_equal(hoff, d_off.cpu().numpy().view(np.uint64))
-        assert int(tot.value) == total_hits
-        assert np.array_equal(hcarr, d_carr.cpu().numpy().view(np.uint32))
+        for sd in strands:
+            h, o = host[sd], out[sd]
+            assert np.array_equal(h["counts"], o["counts"].cpu().numpy().view(np.uint64))
+            assert np.array_equal(h["off"], o["off"].cpu().numpy().view(np.uint64))
+            assert np.array_equal(h["carr"], o["carr"].cpu().numpy().view(np.uint32))
+            n = int(h["off"][Q])
+            assert n == total_hits[sd] and np.array_equal(h["hits"][:n], o["hits"][:n].cpu().numpy().view(np.uint64))
 
     side = None
     if world == 1 and not args.no_side:
@@ -634,17 +677,20 @@ def run_ours(args):
     k1_launches = max(1, stage_launches["search"])
     getocc = 2.0 * interval_steps
     achieved = block_loads * BYTES_PER_RANK / max(k1_s, 1e-12) / 1e9
-    traffic, traffic_src = committed_traffic("r2_k1_traffic.json")
+    traffic, traffic_src = committed_traffic("r2_k1_traffic.json") if args.workload == "configs2" and world == 1 else (None, None)
     chunks = (Q + int(info.chunk_queries) - 1) // int(info.chunk_queries)
-    ours_per_step = 1 + chunks * (len(my_shards) + 4 + (1 if args.locate_every == 1 else 4 * len(my_shards) + 1)) \
-        + (chunks * 2 + 2 + chunks * 3 if world > 1 else 0)
+    ours_per_step = len(strands) * (1 + chunks * (len(my_shards) + 4 + (1 if args.locate_every == 1 else 4 * len(my_shards) + 1))
+                                    + (chunks * 2 + 2 + chunks * 3 if world > 1 else 0))
+    hits_all = sum(total_hits.values())
     line = {
-        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "metric": METRIC if args.workload == "configs2" else
+        "variant-probe 31-mers/s (ref / alt k-mer -> read indices -> carrier set, both strands, over 64 read-suffix shards)",
+        "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": max(3, args.warmup), "ms_per_step": total_ms / args.steps, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "u64", "data": "synthetic",
         "config": {
-            "workload": workload_name(args), "k": k, "queries_per_step": Q, "shards": NSHARDS,
-            "shards_on_rank0": len(my_shards), "hits_per_step": total_hits, "hits_per_query": total_hits / Q,
+            "workload": workload_name(args), "k": k, "queries_per_step": Q, "strands": len(strands), "shards": NSHARDS,
+            "shards_on_rank0": len(my_shards), "hits_per_step": hits_all, "hits_per_query": hits_all / Q,
             "locate": {1: "read-index table, 4 B per BWT row (coalesced reads of an interval's rows)", 0: "LF walk to '$' (K2)"}.get(
                 args.locate_every, f"sampled locate table, every {args.locate_every} rows"),
             "bwt_symbols": data["totals"]["symbols"], "bwt_runs": data["totals"]["runs"], "reads_unique": data["totals"]["reads"],
@@ -662,7 +708,7 @@ def run_ours(args):
             "data_build_seconds": round(data["build_seconds"], 1), "seal_seconds": round(seal_s, 1),
         },
         "roofline": {
-            "bound": "hbm", "kernel": "k_find_interval (K1), one launch per shard and chunk", "achieved": achieved, "peak": peak,
+            "bound": "hbm", "kernel": "k_find_interval_dense (K1), one launch per shard and chunk", "achieved": achieved, "peak": peak,
             "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src, "peak_source": peak_src,
             "algorithmic_bytes": "64-byte blocks K1 had to read x 64 B: one per updateInterval step whose two positions share "
                                  "a block, two otherwise (counted on the device)",
@@ -677,21 +723,52 @@ def run_ours(args):
         },
         "e2e": {"value": Q * e2e_steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": (world if world > 1 else 1) * Q * k,
                 "d2h_bytes_per_step": d2h, "steps": e2e_steps,
-                "api": "rs_pop_query (host pointers, pinned): k-mers in, counts + hit offsets + hits + carrier sets out" if world == 1
+                "api": "rs_pop_query (host pointers, pinned): k-mers in, counts + hit offsets + hits + carrier sets out; the "
+                       "copy-out of one sub-batch overlaps the kernels of the next" if world == 1
                 else "per rank: batch H2D, rs_pop_query_comm_dev, the owned answers D2H"},
         "gpu_launches": args.steps * ours_per_step,
         "clocks": clk,
     }
+    if want_cpu:
+        cores = os.cpu_count() or 1
+        cpu = CpuShards(data, args.read_len)
+        probe = min(Q, 1000)
+        t, _ = cpu.run(hq[:probe], k, cores)
+        n = int(min(Q, max(probe, probe / max(t, 1e-9) * args.cpu_seconds / len(strands))))
+        secs, checked, all_ok = 0.0, {}, True
+        for sd in strands:
+            sample = np.ascontiguousarray(hq[:n])
+            s1, per = cpu.run(revcomp_rows(sample) if sd else sample, k, cores, keep=True)
+            secs += s1
+            w_counts, w_off, w_hits, w_carr, post = cpu.expected(per, my_shards, n)
+            h = host[sd]
+            he = int(h["off"][n])
+            c = {"population_counts": bool(np.array_equal(h["counts"][:n], w_counts)),
+                 "hit_lists_read_index": bool(np.array_equal(h["off"][: n + 1], w_off) and np.array_equal(h["hits"][:he], w_hits)),
+                 "sample_sets": bool(np.array_equal(h["carr"][:n], w_carr)), "hits_checked": he,
+                 "postfix_walk_vs_prefix_walk_read_index": post}
+            all_ok &= c["population_counts"] and c["hit_lists_read_index"] and c["sample_sets"]
+            checked["forward" if sd == 0 else "reverse_complement"] = c
+        line["cpu_baseline"] = {
+            "value": n / secs, "unit": UNIT, "cores": cores, "kind": cpu.kind,
+            "sample": f"first {n} of {Q} k-mers, all {NSHARDS} shards, {len(strands)} strand(s), {cores} threads striding each batch",
+            "what": "findInterval per shard + extractPrefix + extractPostfix per hit row (find_reads, service.cpp:714-751); the "
+                    "sample-store lookups (RocksDB) are not in the timed part",
+            "load_seconds": round(cpu.load_seconds, 1),
+            "gpu_results_bit_exact_on_sample": all_ok, "checked": checked,
+            "note": "read index = .sai[terminal row of extractPrefix's walk]; the reference's tail behaviour (SURVEY.md Q1) can "
+                    "send that walk elsewhere than extractPostfix's (select is unaffected) in shards whose tail region is "
+                    "not empty: both sides reproduce it, postfix_walk_vs_prefix_walk_read_index counts such hits",
+        }
+        cpu.close()
+        assert all_ok, "GPU results differ from the CPU reference"
     if side is not None:
         # the population's shards leave HBM first: building configs[1] (a 1.08 G-symbol suffix sort) needs the room
         S.close()
         for ent in data["shards"].values():
             if "gpu" in ent:
                 ent.pop("gpu").close()
-        try:
-            del d_hits, d_carr
-        except NameError:
-            pass
+        out.clear()
         torch.cuda.empty_cache()
         try:
             side["configs1_count"] = side_configs1(args, engine, dev, local_rank, flush)
@@ -702,37 +779,6 @@ def run_ours(args):
         if ra:
             line["roofline"]["random_access_peak_64B"] = ra
             line["roofline"]["frac_of_random_access_peak"] = achieved / ra
-    if want_cpu:
-        cores = os.cpu_count() or 1
-        order = my_shards
-        for ent in data["shards"].values():   # the GPU copies are no longer needed; the CPU leg wants the host RAM quiet
-            pass
-        cpu = CpuShards(data, args.read_len)
-        probe = min(Q, 2000)
-        t, _ = cpu.run(hq[:probe], k, cores)
-        n = int(min(Q, max(probe, probe / max(t, 1e-9) * args.cpu_seconds)))
-        secs, per = cpu.run(np.ascontiguousarray(hq[:n]), k, cores, keep=True)
-        w_counts, w_off, w_hits, w_carr, post_ok = cpu.expected(per, order, n)
-        he = int(hoff[n])
-        ok_counts = bool(np.array_equal(hcounts[:n], w_counts))
-        ok_hits = bool(np.array_equal(hoff[: n + 1], w_off) and np.array_equal(hhits[:he], w_hits))
-        ok_carr = bool(np.array_equal(hcarr[:n], w_carr))
-        line["cpu_baseline"] = {
-            "value": n / secs, "unit": UNIT, "cores": cores, "kind": cpu.kind,
-            "sample": f"first {n} of {Q} k-mers, all {NSHARDS} shards, {cores} threads striding each batch",
-            "what": "findInterval per shard + extractPrefix + extractPostfix per hit row (find_reads, service.cpp:714-751); the "
-                    "sample-store lookups (RocksDB) are not in the timed part",
-            "load_seconds": round(cpu.load_seconds, 1),
-            "gpu_results_bit_exact_on_sample": ok_counts and ok_hits and ok_carr,
-            "checked": {"population_counts": ok_counts, "hit_lists_read_index": ok_hits, "sample_sets": ok_carr,
-                        "hits_checked": he,
-                        "postfix_walk_vs_prefix_walk_read_index": post_ok},
-            "note": "read index = .sai[terminal row of extractPrefix's walk]; the reference's tail behaviour (SURVEY.md Q1) can "
-                    "send that walk elsewhere than extractPostfix's (select is unaffected) in shards whose tail region is "
-                    "not empty: both sides reproduce it, postfix_walk_vs_prefix_walk_read_index counts such hits",
-        }
-        cpu.close()
-        assert ok_counts and ok_hits and ok_carr, "GPU results differ from the CPU reference"
     print(json.dumps(line), file=_REAL_STDOUT, flush=True)
     if world > 1:
         dist.destroy_process_group()

@@ -305,7 +305,8 @@ int rs_gt_reads_batch(const rs_index* ix, const char* text, const uint64_t* offs
  *                       locate_every = 0: plain walks (K2).  max_read_len bounds every walk.
  *   rs_pop_query[_dev]  Q k-mers of one length k <= 31: ASCII (packed = 0, k bytes each) or packed (packed = 1:
  *                       one uint64 per k-mer, 2 bits per base A,C,G,T = 0..3, first base most significant, bit 63
- *                       set = the k-mer holds a byte outside ACGT and counts 0, service.cpp:299-301).  Forward strand.
+ *                       set = the k-mer holds a byte outside ACGT and counts 0, service.cpp:299-301).  strand = 0 searches
+ *                       the k-mers as given, 1 their reverse complements (the worker's two tasks per request).
  *     counts[Q]           population count = sum over the set's shards of the interval widths (count_reads)
  *     hit_offsets[Q+1]    may be NULL (count only).  CSR of each k-mer's hits; a k-mer's hits are contiguous: shard
  *                         after shard in the order added, rows of the shard's interval in order, at most max_hits
@@ -341,11 +342,12 @@ int rs_shardset_read_stats(rs_shardset* set, uint64_t* interval_steps, uint64_t*
  * calls since the last read (which synchronises the device). */
 int rs_shardset_enable_timing(rs_shardset* set, int on);
 int rs_shardset_read_timing(rs_shardset* set, double ms[4], uint64_t launches[4]);
-int rs_pop_query_dev(rs_shardset* set, const void* d_kmers, int k, size_t Q, int packed, uint64_t max_hits,
+int rs_pop_query_dev(rs_shardset* set, const void* d_kmers, int k, size_t Q, int packed, int strand, uint64_t max_hits,
                      void* d_counts, void* d_hit_offsets, void* d_hits, uint64_t capacity, void* d_carriers,
                      void* d_total_hits, void* stream);
-int rs_pop_query(rs_shardset* set, const void* kmers, int k, size_t Q, int packed, uint64_t max_hits, uint64_t* counts,
-                 uint64_t* hit_offsets, uint64_t* hits, uint64_t capacity, uint32_t* carriers, uint64_t* total_hits);
+int rs_pop_query(rs_shardset* set, const void* kmers, int k, size_t Q, int packed, int strand, uint64_t max_hits,
+                 uint64_t* counts, uint64_t* hit_offsets, uint64_t* hits, uint64_t capacity, uint32_t* carriers,
+                 uint64_t* total_hits);
 
 /* ---- population queries across the GPUs of one box ---------------------------------------------------------
  * One process per GPU, each with a shard set over the shards it holds.  Every rank runs the whole batch on its set;
@@ -366,7 +368,7 @@ int rs_popcomm_create(int device, int rank, int world, uint64_t max_queries, uin
 int rs_popcomm_export(rs_popcomm* c, uint8_t handle[64]);
 int rs_popcomm_connect(rs_popcomm* c, const uint8_t* handles);
 void rs_popcomm_destroy(rs_popcomm* c);
-int rs_pop_query_comm_dev(rs_shardset* set, rs_popcomm* comm, const void* d_kmers, int k, size_t Q, int packed,
+int rs_pop_query_comm_dev(rs_shardset* set, rs_popcomm* comm, const void* d_kmers, int k, size_t Q, int packed, int strand,
                           uint64_t max_hits, int want_hits, int want_carriers, void* stream);
 int rs_popcomm_results(rs_popcomm* c, void** d_counts, void** d_hit_offsets, void** d_hits, void** d_carriers,
                        void** d_total_hits, uint64_t* hit_capacity);

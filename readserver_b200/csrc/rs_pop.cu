@@ -112,6 +112,20 @@ __global__ void k_read_sets(const uint64_t* __restrict__ samp_off, const uint8_t
 /* ------------------------------------------------------------------------------------------------
  * pipeline kernels
  * ---------------------------------------------------------------------------------------------- */
+/* packed k-mers -> their reverse complements (the RevComp task of every request, service.cpp:289-291); flagged keys
+ * (bit 63: a byte outside ACGT) stay flagged */
+__global__ void k_pop_revcomp(const uint64_t* __restrict__ in, uint32_t k, uint64_t Q, uint64_t* __restrict__ out) {
+  const uint64_t q = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= Q) return;
+  const uint64_t v = in[q];
+  uint64_t r = 0, x = ~v;
+  for (uint32_t i = 0; i < k; ++i) {
+    r = (r << 2) | (x & 3u);
+    x >>= 2;
+  }
+  out[q] = r | (v & (1ull << 63));
+}
+
 /* per query of the chunk: population count and number of hits to report */
 __global__ void k_pop_totals(const uint32_t* __restrict__ cnt, uint32_t S, uint64_t C, uint64_t nq, uint64_t max_hits,
                              uint64_t* __restrict__ counts, uint64_t* __restrict__ nhits, uint32_t* __restrict__ seg) {
@@ -401,6 +415,11 @@ struct rs_shardset {
   std::mutex mu;
   cudaStream_t stream = nullptr;
   Scratch s_packed, s_lo, s_cnt, s_seg, s_nh, s_loc, s_scan, s_base, s_rows, s_dst, s_ri, s_in, s_lcnt;
+  /* host-pointer calls: device-side result buffers, the copy-out stream, per-sub-batch events and hit-list marks */
+  Scratch s_hc, s_ho, s_hh, s_hw, s_hm;
+  cudaStream_t copy_stream = nullptr;
+  cudaEvent_t ev_sub[RS_POP_MAX_SUB] = {};
+  uint64_t* h_marks = nullptr;
   uint64_t* d_stats = nullptr; /* executed updateInterval steps / LF steps of the set's calls (bench.py) */
   uint64_t chunk = 1u << 20;
   bool chunk_forced = false; /* RS_B200_POP_CHUNK given */
@@ -500,8 +519,13 @@ void rs_shardset_destroy(rs_shardset* set) {
   if (set->stream) cudaStreamSynchronize(set->stream);
   free_tables(set);
   Scratch* all[] = {&set->s_packed, &set->s_lo, &set->s_cnt, &set->s_seg, &set->s_nh, &set->s_loc, &set->s_scan,
-                    &set->s_base, &set->s_rows, &set->s_dst, &set->s_ri, &set->s_in, &set->s_lcnt};
+                    &set->s_base, &set->s_rows, &set->s_dst, &set->s_ri, &set->s_in, &set->s_lcnt,
+                    &set->s_hc, &set->s_ho, &set->s_hh, &set->s_hw, &set->s_hm};
   for (Scratch* s : all) s->release();
+  if (set->copy_stream) cudaStreamDestroy(set->copy_stream);
+  if (set->h_marks) cudaFreeHost(set->h_marks);
+  for (int i = 0; i < RS_POP_MAX_SUB; ++i)
+    if (set->ev_sub[i]) cudaEventDestroy(set->ev_sub[i]);
   if (set->d_stats) cudaFree(set->d_stats);
   for (cudaEvent_t e : set->ev_pool) cudaEventDestroy(e);
   if (set->stream) cudaStreamDestroy(set->stream);
@@ -853,9 +877,9 @@ static int comm_barrier(rs_popcomm* c, cudaStream_t st) {
 }
 
 /* the pipeline proper; everything on `st`, no host synchronisation */
-static int pop_run(rs_shardset* set, rs_popcomm* comm, const void* d_kmers, int k, size_t Q, int packed, uint64_t max_hits,
+static int pop_run(rs_shardset* set, rs_popcomm* comm, const void* d_kmers, int k, size_t Q, int packed, int strand, uint64_t max_hits,
                    uint64_t* d_counts, uint64_t* d_hit_offsets, uint64_t* d_hits, uint64_t capacity, uint32_t* d_carriers,
-                   uint64_t* d_total, cudaStream_t st) {
+                   uint64_t* d_total, cudaStream_t st, bool keep_base = false) {
   const uint32_t S = (uint32_t)set->shards.size();
   /* chunk: as many queries as the per-shard interval scratch (12 bytes per shard and query) may take; long launches
    * keep every lane busy (the batch is handed out dynamically) and a shard's index hot in L2 */
@@ -872,7 +896,13 @@ static int pop_run(rs_shardset* set, rs_popcomm* comm, const void* d_kmers, int 
   if (!packed) {
     CU(set->s_packed.need(Q * 8));
     StageTimer tm(set, st, RS_POP_STAGE_PACK, 1);
-    CU(rs_launch_pack_kmers((const uint8_t*)d_kmers, (uint32_t)k, Q, 0, (uint64_t*)set->s_packed.p, st));
+    CU(rs_launch_pack_kmers((const uint8_t*)d_kmers, (uint32_t)k, Q, strand, (uint64_t*)set->s_packed.p, st));
+    keys = (const uint64_t*)set->s_packed.p;
+  } else if (strand) {
+    CU(set->s_packed.need(Q * 8));
+    StageTimer tm(set, st, RS_POP_STAGE_PACK, 1);
+    k_pop_revcomp<<<(unsigned)((Q + 255) / 256), 256, 0, st>>>(keys, (uint32_t)k, Q, (uint64_t*)set->s_packed.p);
+    CU(cudaGetLastError());
     keys = (const uint64_t*)set->s_packed.p;
   }
   CU(set->s_lo.need((size_t)S * C * 8));
@@ -904,7 +934,7 @@ static int pop_run(rs_shardset* set, rs_popcomm* comm, const void* d_kmers, int 
     P.slot[0] = d_hit_offsets; /* a query's hits start at its CSR offset */
   }
   const int want_carr = d_carriers != nullptr;
-  CU(cudaMemsetAsync(base, 0, 8, st));
+  if (!keep_base) CU(cudaMemsetAsync(base, 0, 8, st)); /* keep_base: this call continues the hit list of the previous one */
   if (multi) {
     /* own accumulation buffers cleared, then a barrier: no peer adds into them earlier */
     CU(cudaMemsetAsync(d_counts, 0, Q * 8, st));
@@ -1005,7 +1035,7 @@ static int pop_run(rs_shardset* set, rs_popcomm* comm, const void* d_kmers, int 
 
 /* Several GPUs: every rank calls this with the same batch on its own shard set; the answers of the k-mers a rank owns
  * (first four bases modulo the ranks) end up in that rank's communicator buffers (rs_popcomm_results). */
-int rs_pop_query_comm_dev(rs_shardset* set, rs_popcomm* comm, const void* d_kmers, int k, size_t Q, int packed,
+int rs_pop_query_comm_dev(rs_shardset* set, rs_popcomm* comm, const void* d_kmers, int k, size_t Q, int packed, int strand,
                           uint64_t max_hits, int want_hits, int want_carriers, void* stream) {
   if (!set || !comm || (Q && !d_kmers)) return fail(RS_STATUS_ARG, "null argument");
   if (!set->sealed) return fail(RS_STATUS_ARG, "shard set is not sealed");
@@ -1021,14 +1051,16 @@ int rs_pop_query_comm_dev(rs_shardset* set, rs_popcomm* comm, const void* d_kmer
   std::lock_guard<std::mutex> lk(set->mu);
   CU(cudaSetDevice(set->device));
   uint8_t* b = comm->base;
-  return pop_run(set, comm, d_kmers, k, Q, packed, max_hits, (uint64_t*)(b + comm->o_counts),
+  if (strand != 0 && strand != 1) return fail(RS_STATUS_ARG, "strand must be 0 (forward) or 1 (reverse complement)");
+  return pop_run(set, comm, d_kmers, k, Q, packed, strand, max_hits, (uint64_t*)(b + comm->o_counts),
                  want_hits ? (uint64_t*)(b + comm->o_off) : nullptr, (uint64_t*)(b + comm->o_hits), want_hits ? comm->cap : 0,
                  want_carriers ? (uint32_t*)(b + comm->o_carr) : nullptr, (uint64_t*)(b + comm->o_total), (cudaStream_t)stream);
 }
 
-static int pop_check(rs_shardset* set, const void* kmers, int k, size_t Q, const void* counts, const void* hit_offsets,
-                     const void* hits, uint64_t capacity, const void* carriers) {
+static int pop_check(rs_shardset* set, const void* kmers, int k, size_t Q, int strand, const void* counts,
+                     const void* hit_offsets, const void* hits, uint64_t capacity, const void* carriers) {
   if (!set || (Q && (!kmers || !counts))) return fail(RS_STATUS_ARG, "null argument");
+  if (strand != 0 && strand != 1) return fail(RS_STATUS_ARG, "strand must be 0 (forward) or 1 (reverse complement)");
   if (!set->sealed) return fail(RS_STATUS_ARG, "shard set is not sealed");
   if (k < 1 || k > 31) return fail(RS_STATUS_ARG, "population queries are fixed-length k-mers of 1..31 characters");
   if (hit_offsets && capacity && !hits) return fail(RS_STATUS_ARG, "capacity given but hits is null");
@@ -1037,10 +1069,10 @@ static int pop_check(rs_shardset* set, const void* kmers, int k, size_t Q, const
   return RS_STATUS_OK;
 }
 
-int rs_pop_query_dev(rs_shardset* set, const void* d_kmers, int k, size_t Q, int packed, uint64_t max_hits, void* d_counts,
-                     void* d_hit_offsets, void* d_hits, uint64_t capacity, void* d_carriers, void* d_total_hits,
-                     void* stream) {
-  const int rc = pop_check(set, d_kmers, k, Q, d_counts, d_hit_offsets, d_hits, capacity, d_carriers);
+int rs_pop_query_dev(rs_shardset* set, const void* d_kmers, int k, size_t Q, int packed, int strand, uint64_t max_hits,
+                     void* d_counts, void* d_hit_offsets, void* d_hits, uint64_t capacity, void* d_carriers,
+                     void* d_total_hits, void* stream) {
+  const int rc = pop_check(set, d_kmers, k, Q, strand, d_counts, d_hit_offsets, d_hits, capacity, d_carriers);
   if (rc != RS_STATUS_OK) return rc;
   std::lock_guard<std::mutex> lk(set->mu);
   CU(cudaSetDevice(set->device));
@@ -1049,14 +1081,17 @@ int rs_pop_query_dev(rs_shardset* set, const void* d_kmers, int k, size_t Q, int
     if (d_total_hits) CU(cudaMemsetAsync(d_total_hits, 0, 8, (cudaStream_t)stream));
     return RS_STATUS_OK;
   }
-  return pop_run(set, nullptr, d_kmers, k, Q, packed, max_hits, (uint64_t*)d_counts, (uint64_t*)d_hit_offsets, (uint64_t*)d_hits,
+  return pop_run(set, nullptr, d_kmers, k, Q, packed, strand, max_hits, (uint64_t*)d_counts, (uint64_t*)d_hit_offsets, (uint64_t*)d_hits,
                  capacity, (uint32_t*)d_carriers, (uint64_t*)d_total_hits, (cudaStream_t)stream);
 }
 
-/* host buffers (pinned or not): copy in, run, copy out; RS_STATUS_CAPACITY when hits were dropped */
-int rs_pop_query(rs_shardset* set, const void* kmers, int k, size_t Q, int packed, uint64_t max_hits, uint64_t* counts,
-                 uint64_t* hit_offsets, uint64_t* hits, uint64_t capacity, uint32_t* carriers, uint64_t* total_hits) {
-  const int rc = pop_check(set, kmers, k, Q, counts, hit_offsets, hits, capacity, carriers);
+/* host buffers (pinned or not): the batch goes through the pipeline in a few sub-batches so that the copy-out of one
+ * (its slice of counts, offsets, carrier sets and -- the bulk -- its hits) overlaps the kernels of the next;
+ * RS_STATUS_CAPACITY when hits were dropped */
+int rs_pop_query(rs_shardset* set, const void* kmers, int k, size_t Q, int packed, int strand, uint64_t max_hits,
+                 uint64_t* counts, uint64_t* hit_offsets, uint64_t* hits, uint64_t capacity, uint32_t* carriers,
+                 uint64_t* total_hits) {
+  const int rc = pop_check(set, kmers, k, Q, strand, counts, hit_offsets, hits, capacity, carriers);
   if (rc != RS_STATUS_OK) return rc;
   if (total_hits) *total_hits = 0;
   if (!Q) {
@@ -1066,38 +1101,63 @@ int rs_pop_query(rs_shardset* set, const void* kmers, int k, size_t Q, int packe
   std::lock_guard<std::mutex> lk(set->mu);
   CU(cudaSetDevice(set->device));
   cudaStream_t st = set->stream;
-  Tmp tmp(st);
-  const size_t in_bytes = packed ? Q * 8 : Q * (size_t)k;
-  CU(set->s_in.need(in_bytes));
-  uint64_t *d_counts, *d_off = nullptr, *d_hits = nullptr, *d_total;
-  uint32_t* d_carr = nullptr;
-  CU(tmp.get((void**)&d_counts, Q * 8));
-  CU(tmp.get((void**)&d_total, 8));
-  if (hit_offsets) {
-    CU(tmp.get((void**)&d_off, (Q + 1) * 8));
-    if (capacity) CU(tmp.get((void**)&d_hits, capacity * 8));
-    if (carriers) CU(tmp.get((void**)&d_carr, Q * (size_t)set->words * 4));
+  if (!set->copy_stream) {
+    CU(cudaStreamCreateWithFlags(&set->copy_stream, cudaStreamNonBlocking));
+    CU(cudaMallocHost((void**)&set->h_marks, RS_POP_MAX_SUB * sizeof(uint64_t)));
+    for (int i = 0; i < RS_POP_MAX_SUB; ++i) CU(cudaEventCreateWithFlags(&set->ev_sub[i], cudaEventDisableTiming));
   }
-  CU(cudaMemcpyAsync(set->s_in.p, kmers, in_bytes, cudaMemcpyHostToDevice, st));
-  const int prc = pop_run(set, nullptr, set->s_in.p, k, Q, packed, max_hits, d_counts, d_off, d_hits, capacity, d_carr, d_total, st);
-  if (prc != RS_STATUS_OK) {
-    cudaStreamSynchronize(st);
-    return prc;
+  cudaStream_t cs = set->copy_stream;
+  const size_t unit = packed ? 8 : (size_t)k;
+  const size_t W = set->words;
+  CU(set->s_in.need(Q * unit));
+  CU(set->s_hc.need(Q * 8));
+  CU(set->s_ho.need((Q + 1) * 8));
+  CU(set->s_hm.need(RS_POP_MAX_SUB * 8));
+  if (hit_offsets && capacity) CU(set->s_hh.need(capacity * 8));
+  if (carriers) CU(set->s_hw.need(Q * W * 4));
+  uint64_t *d_counts = (uint64_t*)set->s_hc.p, *d_off = hit_offsets ? (uint64_t*)set->s_ho.p : nullptr;
+  uint64_t *d_hits = (hit_offsets && capacity) ? (uint64_t*)set->s_hh.p : nullptr, *d_marks = (uint64_t*)set->s_hm.p;
+  uint32_t* d_carr = carriers ? (uint32_t*)set->s_hw.p : nullptr;
+  /* sub-batches: about 2.5 M queries each, at most RS_POP_MAX_SUB */
+  size_t nsub = (Q + 2500000 - 1) / 2500000;
+  if (nsub > RS_POP_MAX_SUB) nsub = RS_POP_MAX_SUB;
+  if (!hit_offsets) nsub = 1;
+  const size_t per = (Q + nsub - 1) / nsub;
+  CU(cudaMemcpyAsync(set->s_in.p, kmers, Q * unit, cudaMemcpyHostToDevice, st));
+  uint64_t copied = 0; /* hits already queued for copy-out */
+  int status = RS_STATUS_OK;
+  auto drain = [&](size_t b) -> int { /* sub-batch b is computed: queue its copy-out */
+    const size_t q0 = b * per, nq = std::min(per, Q - q0);
+    CU(cudaEventSynchronize(set->ev_sub[b]));
+    const uint64_t end = set->h_marks[b];
+    CU(cudaMemcpyAsync(counts + q0, d_counts + q0, nq * 8, cudaMemcpyDeviceToHost, cs));
+    if (hit_offsets) {
+      CU(cudaMemcpyAsync(hit_offsets + q0, d_off + q0, (nq + (q0 + nq == Q ? 1 : 0)) * 8, cudaMemcpyDeviceToHost, cs));
+      if (carriers) CU(cudaMemcpyAsync(carriers + q0 * W, d_carr + q0 * W, nq * W * 4, cudaMemcpyDeviceToHost, cs));
+      const uint64_t upto = end < capacity ? end : capacity;
+      if (hits && upto > copied) CU(cudaMemcpyAsync(hits + copied, d_hits + copied, (upto - copied) * 8, cudaMemcpyDeviceToHost, cs));
+      if (upto > copied) copied = upto;
+    }
+    return RS_STATUS_OK;
+  };
+  for (size_t b = 0; b < nsub && status == RS_STATUS_OK; ++b) {
+    const size_t q0 = b * per, nq = std::min(per, Q - q0);
+    status = pop_run(set, nullptr, (const uint8_t*)set->s_in.p + q0 * unit, k, nq, packed, strand, max_hits, d_counts + q0,
+                     d_off ? d_off + q0 : nullptr, d_hits, capacity, d_carr ? d_carr + q0 * W : nullptr, d_marks + b, st, b > 0);
+    if (status != RS_STATUS_OK) break;
+    /* the hit list's length so far, to the host; the copy stream may start on this sub-batch once it is there */
+    CU(cudaMemcpyAsync(&set->h_marks[b], d_marks + b, 8, cudaMemcpyDeviceToHost, st));
+    CU(cudaEventRecord(set->ev_sub[b], st));
+    CU(cudaStreamWaitEvent(cs, set->ev_sub[b], 0));
+    if (b > 0) status = drain(b - 1); /* while sub-batch b runs */
   }
-  uint64_t total = 0;
-  CU(cudaMemcpyAsync(counts, d_counts, Q * 8, cudaMemcpyDeviceToHost, st));
-  CU(cudaMemcpyAsync(&total, d_total, 8, cudaMemcpyDeviceToHost, st));
-  if (hit_offsets) {
-    CU(cudaMemcpyAsync(hit_offsets, d_off, (Q + 1) * 8, cudaMemcpyDeviceToHost, st));
-    if (carriers) CU(cudaMemcpyAsync(carriers, d_carr, Q * (size_t)set->words * 4, cudaMemcpyDeviceToHost, st));
-  }
-  CU(cudaStreamSynchronize(st));
+  if (status == RS_STATUS_OK) status = drain(nsub - 1);
+  cudaStreamSynchronize(st);
+  const cudaError_t ce = cudaStreamSynchronize(cs);
+  if (status != RS_STATUS_OK) return status;
+  if (ce != cudaSuccess) return fail(RS_STATUS_CUDA, "copy-out: %s", cudaGetErrorString(ce));
+  const uint64_t total = hit_offsets ? set->h_marks[nsub - 1] : 0;
   if (total_hits) *total_hits = total;
-  if (hit_offsets && hits) {
-    const uint64_t ncopy = total < capacity ? total : capacity;
-    if (ncopy) CU(cudaMemcpyAsync(hits, d_hits, ncopy * 8, cudaMemcpyDeviceToHost, st));
-    CU(cudaStreamSynchronize(st));
-  }
   if (hit_offsets && total > capacity)
     return fail(RS_STATUS_CAPACITY, "%llu hits do not fit the %llu provided", (unsigned long long)total,
                 (unsigned long long)capacity);

@@ -10,6 +10,7 @@
 #define RS_POP_MAX_SHARDS 1024
 #define RS_POP_MAX_SHARD_ID 4096u
 #define RS_POP_SCRATCH_BYTES (12ull << 30) /* per-shard interval scratch of one chunk, at most */
+#define RS_POP_MAX_SUB 16 /* sub-batches of a host-pointer call (copy-out overlapped with the next one's kernels) */
 #define RS_POP_STAGES 4
 #define RS_POP_STAGE_PACK 0    /* k_pack_kmers                                  */
 #define RS_POP_STAGE_SEARCH 1  /* K1, one launch per shard and chunk            */

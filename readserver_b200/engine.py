@@ -86,11 +86,11 @@ def lib() -> C.CDLL:
         "rs_popcomm_export": (i32, [vp, vp]),
         "rs_popcomm_connect": (i32, [vp, vp]),
         "rs_popcomm_destroy": (None, [vp]),
-        "rs_pop_query_comm_dev": (i32, [vp, vp, vp, i32, sz, i32, u64, i32, i32, vp]),
+        "rs_pop_query_comm_dev": (i32, [vp, vp, vp, i32, sz, i32, i32, u64, i32, i32, vp]),
         "rs_popcomm_results": (i32, [vp, C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(vp), C.POINTER(u64)]),
         "rs_popcomm_error": (i32, [vp, C.POINTER(i32)]),
-        "rs_pop_query_dev": (i32, [vp, vp, i32, sz, i32, u64, vp, vp, vp, u64, vp, vp, vp]),
-        "rs_pop_query": (i32, [vp, vp, i32, sz, i32, u64, vp, vp, vp, u64, vp, C.POINTER(u64)]),
+        "rs_pop_query_dev": (i32, [vp, vp, i32, sz, i32, i32, u64, vp, vp, vp, u64, vp, vp, vp]),
+        "rs_pop_query": (i32, [vp, vp, i32, sz, i32, i32, u64, vp, vp, vp, u64, vp, C.POINTER(u64)]),
         "rs_index_close": (None, [vp]),
         "rs_index_get_info": (i32, [vp, C.POINTER(Info)]),
         "rs_index_set_tail_emulation": (i32, [vp, i32]),
@@ -631,13 +631,13 @@ class ShardSet:
         return {k: float(v) for k, v in zip(names, ms)}, {k: int(v) for k, v in zip(names, n)}
 
     def query_dev(self, d_kmers, k: int, q: int, packed: bool, max_hits: int, d_counts, d_hit_offsets=None, d_hits=None,
-                  capacity: int = 0, d_carriers=None, d_total=None, stream: int = 0):
+                  capacity: int = 0, d_carriers=None, d_total=None, stream: int = 0, strand: int = 0):
         """Asynchronous on `stream`, device buffers (torch tensors); see rs_pop_query_dev."""
-        _check(lib().rs_pop_query_dev(self._h, _ptr(d_kmers), k, q, int(packed), max_hits, _ptr(d_counts), _ptr(d_hit_offsets),
+        _check(lib().rs_pop_query_dev(self._h, _ptr(d_kmers), k, q, int(packed), strand, max_hits, _ptr(d_counts), _ptr(d_hit_offsets),
                                       _ptr(d_hits), capacity, _ptr(d_carriers), _ptr(d_total), stream))
 
     def query(self, kmers, k: int | None = None, max_hits: int = 1 << 20, locate: bool = True, carriers: bool = False,
-              packed: bool = False):
+              packed: bool = False, strand: int = 0):
         """Host arrays in, host arrays out: dict(counts, hit_offsets, hits, carriers)."""
         if packed:
             kmers = np.ascontiguousarray(kmers, dtype=np.uint64)
@@ -653,11 +653,11 @@ class ShardSet:
         L = lib()
         tot = C.c_uint64()
         if not locate:
-            _check(L.rs_pop_query(self._h, kmers.ctypes.data, k, q, int(packed), max_hits, counts.ctypes.data, None, None, 0,
+            _check(L.rs_pop_query(self._h, kmers.ctypes.data, k, q, int(packed), strand, max_hits, counts.ctypes.data, None, None, 0,
                                   None, C.byref(tot)))
             return out
         off = np.zeros(q + 1, dtype=np.uint64)
-        rc = L.rs_pop_query(self._h, kmers.ctypes.data, k, q, int(packed), max_hits, counts.ctypes.data, off.ctypes.data, None,
+        rc = L.rs_pop_query(self._h, kmers.ctypes.data, k, q, int(packed), strand, max_hits, counts.ctypes.data, off.ctypes.data, None,
                             0, None, C.byref(tot))
         if rc not in (0, 9):
             _check(rc)
@@ -665,7 +665,7 @@ class ShardSet:
         hits = np.zeros(max(cap, 1), dtype=np.uint64)
         W = int(self.info.carrier_words)
         carr = np.zeros((q, W), dtype=np.uint32) if carriers else None
-        _check(L.rs_pop_query(self._h, kmers.ctypes.data, k, q, int(packed), max_hits, counts.ctypes.data, off.ctypes.data,
+        _check(L.rs_pop_query(self._h, kmers.ctypes.data, k, q, int(packed), strand, max_hits, counts.ctypes.data, off.ctypes.data,
                               hits.ctypes.data, cap, _ptr(carr), C.byref(tot)))
         out.update(hit_offsets=off, hits=hits[:cap])
         if carriers:
@@ -710,8 +710,8 @@ class PopComm:
         _check(lib().rs_popcomm_connect(self._h, handles.ctypes.data))
 
     def query_dev(self, shardset: "ShardSet", d_kmers, k: int, q: int, packed: bool, max_hits: int, want_hits: bool = True,
-                  want_carriers: bool = False, stream: int = 0):
-        _check(lib().rs_pop_query_comm_dev(shardset._h, self._h, _ptr(d_kmers), k, q, int(packed), max_hits, int(want_hits),
+                  want_carriers: bool = False, stream: int = 0, strand: int = 0):
+        _check(lib().rs_pop_query_comm_dev(shardset._h, self._h, _ptr(d_kmers), k, q, int(packed), strand, max_hits, int(want_hits),
                                            int(want_carriers), stream))
 
     def results(self, q: int, device=None):

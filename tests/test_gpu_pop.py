@@ -226,6 +226,16 @@ def test_shard_set_count_locate_carriers_match_per_shard_oracles(locate_every, p
         got2 = S.query(engine.pack_kmers(q), 31, packed=True, max_hits=3, carriers=True)
         assert all(np.array_equal(got[k], got2[k]) for k in got)
         assert np.array_equal(S.query(q, 31, locate=False)["counts"], want[0])
+        # the reverse-complement task of every request (service.cpp:289-291): ASCII and packed keys
+        comp = np.zeros(256, dtype=np.uint8)
+        for a, b in zip(b"ACGT", b"TGCA"):
+            comp[a] = b
+        qr = np.ascontiguousarray(comp[q[:, ::-1]])
+        fwd_of_rc = S.query(qr, 31, max_hits=3, carriers=True)
+        rc1 = S.query(q, 31, max_hits=3, carriers=True, strand=1)
+        rc2 = S.query(engine.pack_kmers(q), 31, max_hits=3, carriers=True, strand=1, packed=True)
+        for k_ in fwd_of_rc:
+            assert np.array_equal(fwd_of_rc[k_], rc1[k_]) and np.array_equal(fwd_of_rc[k_], rc2[k_]), k_
 
 
 def test_shard_set_with_exact_rank_equals_brute_force_over_the_reads(popcase, engine):
@@ -290,7 +300,7 @@ def test_shard_set_order_ids_chunks_and_bad_bytes(popcase, engine, monkeypatch):
         hits = np.zeros(10, dtype=np.uint64)
         tot = C.c_uint64()
         flat = np.ascontiguousarray(q).reshape(-1)
-        rc = L.rs_pop_query(S._h, flat.ctypes.data, 24, q.shape[0], 0, 1 << 20, counts.ctypes.data, off.ctypes.data,
+        rc = L.rs_pop_query(S._h, flat.ctypes.data, 24, q.shape[0], 0, 0, 1 << 20, counts.ctypes.data, off.ctypes.data,
                             hits.ctypes.data, 10, None, C.byref(tot))
         assert rc == 9 and tot.value == want[1][-1] and np.array_equal(off, want[1]) and np.array_equal(hits, want[2][:10])
 
