@@ -65,7 +65,7 @@ def parse():
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU time of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-side", action="store_true", help="skip the side measurements (configs[1] count line, roofline probe)")
-    ap.add_argument("--workload", default="configs2", choices=["configs2", "configs4"],
+    ap.add_argument("--workload", default="configs2", choices=["configs2", "configs4", "configs1"],
                     help="configs2 (default, the metric's): 10 M 31-mers, forward strand.  configs4: variant-allele probes over "
                          "the same population -- --sites sites of its list, the reference- and the alternative-allele 31-mer "
                          "centred on each, both strands -> read indices -> carrier sets")
@@ -794,7 +794,12 @@ def main():
     sys.stdout.flush()
     _REAL_STDOUT = os.fdopen(os.dup(1), "w")
     os.dup2(2, 1)
-    if args.impl == "reference":
+    if args.workload == "configs1":   # experiments only: round 1's count line alone (not the driver's contract)
+        import torch
+        from readserver_b200 import engine
+        flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda:0")
+        print(json.dumps(side_configs1(args, engine, "cuda:0", 0, flush)), file=_REAL_STDOUT, flush=True)
+    elif args.impl == "reference":
         run_reference(args)
     else:
         run_ours(args)

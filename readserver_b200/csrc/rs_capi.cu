@@ -205,10 +205,13 @@ int rs_index_drop_locate_table(rs_index* ix) {
 static uint32_t auto_ftab_k(const rs_index* ix) {
   const char* e = getenv("RS_B200_FTAB");
   if (e) return (uint32_t)atoi(e);
-  /* largest t <= 12 whose table is at most four times the run blocks.  One 16-byte read per query replaces t - 1
-   * steps of two block reads each, so the table pays even when it is far larger than L2 (configs[1], M q/s: t = 8: 1540,
-   * 9: 1598, 10: 1674, 11: 1802, 12: 1842; configs[2], K1 ms per step over 64 shards: t = 9: 155, 10: 141, 11: 112, 12: 107) */
-  const uint64_t budget = 4 * ix->dev.nblocks * (uint64_t)RS_BLOCK_BYTES;
+  /* largest t <= 12 whose table is no larger than the run blocks -- four times the run blocks when the index has
+   * dense rank blocks (short runs: the run blocks are then a poor measure of the index).  One 16-byte read per query
+   * replaces t - 1 steps of two block reads each, so the table pays even when it is larger than L2.  configs[1]
+   * (run blocks 111 MB, M q/s): t = 8: 1540, 9: 1598, 10: 1674, 11: 1802, 12: 1842 in round 1, 11: 1428 / 12: 1258 on
+   * this round's box; configs[2] (64 shards of 73 MB run blocks + 70 MB dense blocks, K1 ms per 10 M-query step):
+   * t = 9: 155, 10: 141, 11: 112, 12: 107 */
+  const uint64_t budget = (ix->d_dense ? 4 : 1) * ix->dev.nblocks * (uint64_t)RS_BLOCK_BYTES;
   uint32_t t = 0;
   while (t < 12 && (16ull << (2 * (t + 1))) <= budget) ++t;
   return t;

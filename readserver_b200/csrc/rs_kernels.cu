@@ -143,13 +143,16 @@ __device__ __forceinline__ void rs_emit(int mode, uint64_t* __restrict__ lower, 
   }
 }
 
+#ifndef RS_K1_RESTRICT
+#define RS_K1_RESTRICT
+#endif
 #ifndef RS_K1_BLOCKS
 #define RS_K1_BLOCKS 5 /* resident CTAs per SM the register allocation must allow (4: 1532, 5: 1573, 6: 1477 M q/s) */
 #endif
 template <bool FTAB, bool PACKED>
 __global__ void __launch_bounds__(RS_THREADS, RS_K1_BLOCKS)
     k_find_interval(const __grid_constant__ rs_index_dev ix, const uint8_t* __restrict__ text,
-                    const uint64_t* __restrict__ offs, uint32_t k, uint64_t Q, const uint64_t* pkeys, uint64_t* lower,
+                    const uint64_t* __restrict__ offs, uint32_t k, uint64_t Q, const uint64_t* pkeys, uint64_t* RS_K1_RESTRICT lower,
                     uint64_t* __restrict__ upper, int mode, int strand, unsigned long long* __restrict__ stats,
                     const __grid_constant__ rs_peers peers) {
   const uint64_t stride = (uint64_t)gridDim.x * RS_THREADS;
@@ -287,7 +290,9 @@ __global__ void __launch_bounds__(RS_THREADS, RS_K1_BLOCKS)
       }
       uint64_t x1, x2;
       rs_scan2(ix, c, blk, pos, p2, two, &x1, &x2);
+#ifndef RS_K1_NO_SCAN_COUNT
       ++nscans;
+#endif
       uint64_t r2 = 0;
       if (was_pending) {
         r2 = none2 ? 0 : x1;
