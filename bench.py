@@ -461,6 +461,7 @@ def run_ours(args):
         S.add(data["shards"][s]["gpu"], s)
     info = S.seal(args.read_len + 28, args.locate_every)
     seal_s = time.time() - t0
+    base_index_bytes = int(info.index_bytes)
     S.enable_stats(True)
     Q, k, strands = args.queries, args.k, args.strands
     dq = data["queries"]
@@ -763,7 +764,44 @@ def run_ours(args):
         cpu.close()
         assert all_ok, "GPU results differ from the CPU reference"
     if side is not None:
-        # the population's shards leave HBM first: building configs[1] (a 1.08 G-symbol suffix sort) needs the room
+        # the locate stage three ways on the first 4 M k-mers: read-index tables (the headline's), the sampled locate
+        # table (every 16th row of each read's walk), plain LF walks to the '$' (K2) -- the paths for shards too large for
+        # 4 bytes per row; answers compared with the tables'
+        try:
+            Qs = min(Q, 4_000_000)
+            o = out[0]
+            modes = {}
+            ref_hits = None
+            for every, name in ((1, "read_index_table"), (16, "sampled_every_16"), (0, "walk_to_terminator")):
+                t0 = time.time()
+                if every != args.locate_every or name != "read_index_table":
+                    S.seal(args.read_len + 28, every)
+                seal_t = time.time() - t0
+                inf = S.info
+                S.query_dev(dq, k, Qs, False, MAX_HITS, o["counts"], o["off"], o["hits"], caps[0], o["carr"], d_total, stream)
+                torch.cuda.synchronize()
+                nh_ = int(d_total.item())
+                S.read_stats(reset=True)
+                S.enable_timing(True)
+                for _ in range(3):
+                    flush.fill_(1)
+                    S.query_dev(dq, k, Qs, False, MAX_HITS, o["counts"], o["off"], o["hits"], caps[0], o["carr"], d_total, stream)
+                ms_, _ = S.read_timing()
+                S.enable_timing(False)
+                _, wsteps, _ = S.read_stats(reset=True)
+                got = o["hits"][:nh_].clone()
+                same = True if ref_hits is None else bool(torch.equal(got, ref_hits))
+                if ref_hits is None:
+                    ref_hits = got
+                modes[name] = {"locate_ms": ms_["locate"] / 3, "hit_rows_per_s": nh_ / (ms_["locate"] / 3e3), "hits": nh_,
+                               "lf_steps_per_hit": wsteps / 3 / max(nh_, 1), "table_bytes": int(inf.table_bytes) if every == 1 else
+                               int(inf.index_bytes) - base_index_bytes, "seal_seconds": round(seal_t, 2),
+                               "equals_read_index_table": same}
+            side["locate_modes_first_4M_kmers"] = modes
+            del ref_hits, got
+        except Exception as ex:
+            print(f"locate-mode side measurement failed: {ex}", file=sys.stderr)
+        # the population's shards leave HBM next: building configs[1] (a 1.08 G-symbol suffix sort) needs the room
         S.close()
         for ent in data["shards"].values():
             if "gpu" in ent:

@@ -113,9 +113,9 @@ int rs_index_set_dense(rs_index* ix, int on);
  * stay uncovered and are walked at query time as before).  Rebuilt by rs_index_set_tail_emulation. */
 int rs_index_build_locate_table(rs_index* ix, uint32_t max_read_len);
 /* The same, sampled: entries only for the rows reached after a multiple of `every` bases of a read's walk (a
- * marker bit per row and a popcount directory address them), so a hit row is walked fewer than `every` steps
- * instead of to the '$'.  n (1/8 + 1/64 + 8/every) bytes: 0.64 bytes per symbol at every = 16.  every = 1 is
- * the full table. */
+ * 16-byte record per 64 rows holds their marker bits and the number of entries before them), so a hit row is walked
+ * fewer than `every` steps instead of to the '$'.  n (1/4 + 8/every) bytes: 0.75 bytes per symbol at every = 16.
+ * every = 1 is the full table. */
 int rs_index_build_locate_samples(rs_index* ix, uint32_t max_read_len, uint32_t every);
 int rs_index_drop_locate_table(rs_index* ix);
 /* Work counters for the *_dev calls (kept on the device, off by default): executed updateInterval

@@ -147,28 +147,30 @@ static int build_locate(rs_index* ix, uint32_t max_len, uint32_t every) {
     if (alloc(&ix->d_loc, n) != cudaSuccess) return bail("out of device memory");
     if (rs_build_locate_table(ix->dev, max_len, ix->d_loc, ix->d_loc_fin, st) != cudaSuccess) return bail("build failed");
   } else {
-    const uint64_t nwords = (n + 63) / 64, ngroups = (nwords + 7) / 8;
-    if (alloc(&ix->d_loc_mark, nwords) != cudaSuccess || alloc(&ix->d_loc_rank, ngroups + 1) != cudaSuccess)
-      return bail("out of device memory");
-    uint64_t* d_counts = nullptr;
+    const uint64_t nwords = (n + 63) / 64;
+    if (alloc(&ix->d_loc_mark, 2 * nwords) != cudaSuccess) return bail("out of device memory");
+    uint64_t *d_counts = nullptr, *d_before = nullptr;
     void* d_scan = nullptr;
     size_t scan_bytes = 0;
-    if (rs_scan_bytes(ngroups, &scan_bytes) != cudaSuccess || cudaMalloc((void**)&d_counts, (ngroups + 1) * 8) != cudaSuccess ||
-        cudaMalloc(&d_scan, scan_bytes ? scan_bytes : 8) != cudaSuccess) {
+    if (rs_scan_bytes(nwords, &scan_bytes) != cudaSuccess || cudaMalloc((void**)&d_counts, (nwords + 1) * 8) != cudaSuccess ||
+        cudaMalloc((void**)&d_before, (nwords + 1) * 8) != cudaSuccess || cudaMalloc(&d_scan, scan_bytes ? scan_bytes : 8) != cudaSuccess) {
       if (d_counts) cudaFree(d_counts);
+      if (d_before) cudaFree(d_before);
       return bail("out of device memory");
     }
     uint64_t nsamples = 0;
     cudaError_t e = rs_locate_mark(ix->dev, max_len, every, ix->d_loc_mark, ix->d_loc_fin, st);
     if (e == cudaSuccess) e = rs_locate_mark_counts(ix->d_loc_mark, n, d_counts, st);
-    if (e == cudaSuccess) e = rs_exclusive_scan(d_counts, ix->d_loc_rank, ngroups, d_scan, scan_bytes, st);
-    if (e == cudaSuccess) e = cudaMemcpyAsync(&nsamples, ix->d_loc_rank + ngroups, 8, cudaMemcpyDeviceToHost, st);
+    if (e == cudaSuccess) e = rs_exclusive_scan(d_counts, d_before, nwords, d_scan, scan_bytes, st);
+    if (e == cudaSuccess) e = rs_locate_mark_ranks(ix->d_loc_mark, n, d_before, st);
+    if (e == cudaSuccess) e = cudaMemcpyAsync(&nsamples, d_before + nwords, 8, cudaMemcpyDeviceToHost, st);
     if (e == cudaSuccess) e = cudaStreamSynchronize(st);
     cudaFree(d_counts);
+    cudaFree(d_before);
     cudaFree(d_scan);
     if (e != cudaSuccess) return bail(cudaGetErrorString(e));
     if (alloc(&ix->d_loc, nsamples) != cudaSuccess) return bail("out of device memory");
-    if (rs_locate_fill(ix->dev, max_len, every, ix->d_loc_mark, ix->d_loc_rank, ix->d_loc, nsamples, st) != cudaSuccess)
+    if (rs_locate_fill(ix->dev, max_len, every, ix->d_loc_mark, ix->d_loc, nsamples, st) != cudaSuccess)
       return bail("build failed");
   }
   if (cudaStreamSynchronize(st) != cudaSuccess) return bail("build failed");

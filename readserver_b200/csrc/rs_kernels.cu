@@ -577,16 +577,20 @@ __global__ void __launch_bounds__(RS_THREADS)
 }
 
 /* ---- sampled locate table ---- */
+/* One 16-byte record per 64 rows: {marker bits, sampled rows before the word}.  A walk step fetches the record of its
+ * row together with the row's rank block; when the row is sampled the record alone gives the slot of its entry
+ * (round 1 kept the bits and a popcount directory per 512 rows apart: up to eight more words on every sampled row). */
 /* pass 1: mark the rows every `every` symbols along each read's walk; fin as in the full table */
 __global__ void __launch_bounds__(RS_THREADS, RS_K2_BLOCKS_BUILD)
     k_mark_locate(const __grid_constant__ rs_index_dev ix, uint32_t max_len, uint32_t every,
-                  unsigned long long* __restrict__ mark, uint64_t* __restrict__ fin) {
+                  ulonglong2* __restrict__ rec, uint64_t* __restrict__ fin) {
   const uint64_t stride = (uint64_t)gridDim.x * RS_THREADS;
   for (uint64_t i = (uint64_t)blockIdx.x * RS_THREADS + threadIdx.x; i < ix.num_strings; i += stride) {
     uint64_t idx = i;
     uint32_t s = 0;
     while (true) {
-      if (s % every == 0 && idx < ix.n) atomicOr(mark + (idx >> 6), 1ull << (idx & 63));
+      if (s % every == 0 && idx < ix.n)
+        atomicOr(reinterpret_cast<unsigned long long*>(&rec[idx >> 6].x), 1ull << (idx & 63));
       uint64_t nxt;
       const uint32_t sym = rs_lf_step(ix, idx, &nxt);
       idx = nxt;
@@ -602,33 +606,30 @@ __global__ void __launch_bounds__(RS_THREADS, RS_K2_BLOCKS_BUILD)
   }
 }
 
-/* set bits of each 512-row group */
-__global__ void k_mark_counts(const uint64_t* __restrict__ mark, uint64_t ngroups, uint64_t nwords,
-                              uint64_t* __restrict__ counts) {
-  const uint64_t g = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (g >= ngroups) return;
-  uint64_t c = 0;
-  for (uint32_t w = 0; w < 8 && g * 8 + w < nwords; ++w) c += __popcll(mark[g * 8 + w]);
-  counts[g] = c;
+/* set bits of each word (input of the scan that yields the records' second halves) */
+__global__ void k_mark_counts(const ulonglong2* __restrict__ rec, uint64_t nwords, uint64_t* __restrict__ counts) {
+  const uint64_t w = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (w < nwords) counts[w] = __popcll(rec[w].x);
+}
+__global__ void k_mark_ranks(ulonglong2* __restrict__ rec, uint64_t nwords, const uint64_t* __restrict__ before) {
+  const uint64_t w = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (w < nwords) rec[w].y = before[w];
 }
 
-__device__ __forceinline__ uint64_t rs_sample_slot(const uint64_t* __restrict__ mark, const uint64_t* __restrict__ rank,
-                                                   uint64_t row) {
-  uint64_t slot = rank[row >> 9];
-  for (uint64_t w = (row >> 9) << 3; w < (row >> 6); ++w) slot += __popcll(mark[w]);
-  return slot + __popcll(mark[row >> 6] & ((1ull << (row & 63)) - 1));
+__device__ __forceinline__ uint64_t rs_sample_slot(const ulonglong2 r, uint64_t row) {
+  return r.y + __popcll(r.x & ((1ull << (row & 63)) - 1));
 }
 
 /* pass 2: the same walks again, filling the entries of the sampled rows */
 __global__ void __launch_bounds__(RS_THREADS, RS_K2_BLOCKS_BUILD)
     k_fill_locate(const __grid_constant__ rs_index_dev ix, uint32_t max_len, uint32_t every,
-                  const uint64_t* __restrict__ mark, const uint64_t* __restrict__ rank, uint64_t* __restrict__ loc) {
+                  const ulonglong2* __restrict__ rec, uint64_t* __restrict__ loc) {
   const uint64_t stride = (uint64_t)gridDim.x * RS_THREADS;
   for (uint64_t i = (uint64_t)blockIdx.x * RS_THREADS + threadIdx.x; i < ix.num_strings; i += stride) {
     uint64_t idx = i;
     uint32_t s = 0;
     while (true) {
-      if (s % every == 0 && idx < ix.n) loc[rs_sample_slot(mark, rank, idx)] = (i << 24) | s;
+      if (s % every == 0 && idx < ix.n) loc[rs_sample_slot(rec[idx >> 6], idx)] = (i << 24) | s;
       uint64_t nxt;
       const uint32_t sym = rs_lf_step(ix, idx, &nxt);
       idx = nxt;
@@ -637,27 +638,56 @@ __global__ void __launch_bounds__(RS_THREADS, RS_K2_BLOCKS_BUILD)
   }
 }
 
-/* K2 with the sampled table: follow the walk until a sampled row (or the '$') */
+/* K2 with the sampled table: follow the walk until a sampled row (or the '$').  Rows are handed out from a counter
+ * as in K1 (a warp takes as many as it has idle lanes), so the lanes stay busy although walks end after 0 .. every - 1
+ * steps. */
 __global__ void __launch_bounds__(RS_THREADS, RS_K2_BLOCKS_BUILD)
     k_locate_sampled(const __grid_constant__ rs_index_dev ix, const uint64_t* __restrict__ rows, uint64_t n,
                      uint32_t max_steps, uint64_t* __restrict__ lexrank, uint32_t* __restrict__ steps,
                      const uint64_t* __restrict__ sai, uint64_t* __restrict__ read_index,
-                     unsigned long long* __restrict__ stats, const uint64_t* __restrict__ n_dev) {
+                     unsigned long long* __restrict__ stats, const uint64_t* __restrict__ n_dev,
+                     unsigned long long* __restrict__ ticket) {
   if (n_dev && *n_dev < n) n = *n_dev; /* item count left on the device by an earlier kernel (rs_pop.cu) */
-  const uint64_t stride = (uint64_t)gridDim.x * RS_THREADS;
+  const ulonglong2* __restrict__ rec = reinterpret_cast<const ulonglong2*>(ix.loc_mark);
+  const uint32_t lane = threadIdx.x & 31u;
   unsigned long long lf_steps = 0;
-  for (uint64_t i = (uint64_t)blockIdx.x * RS_THREADS + threadIdx.x; i < n; i += stride) {
-    uint64_t idx = rows[i];
-    uint64_t term = ~0ull;
-    uint32_t nsteps = 0xFFFFFFFFu, s = 0;
-    while (true) {
-      /* the marker word and the blocks of the LF step are fetched together: the step is wasted on a sampled row,
-       * but the two reads do not wait for each other on the others */
-      const uint64_t mw = idx < ix.n ? __ldg(ix.loc_mark + (idx >> 6)) : 0;
+  uint64_t i = 0, idx = 0;
+  uint32_t s = 0;
+  bool active = false, exhausted = false;
+  while (true) {
+    const uint32_t idle = __ballot_sync(RS_FULL, !active);
+    if (idle == RS_FULL || __popc(idle) >= RS_REFILL_MIN) {
+      if (!exhausted) {
+        const int leader = __ffs((int)idle) - 1;
+        unsigned long long base = 0;
+        if ((int)lane == leader) base = atomicAdd(ticket, (unsigned long long)__popc(idle));
+        base = __shfl_sync(RS_FULL, base, leader);
+        if (base >= n) exhausted = true;
+        if (!active && !exhausted) {
+          i = base + (uint64_t)__popc(idle & ((1u << lane) - 1u));
+          if (i < n) {
+            idx = rows[i];
+            s = 0;
+            active = true;
+          }
+        }
+      }
+      if (__all_sync(RS_FULL, !active)) {
+        if (exhausted) break;
+        continue;
+      }
+    }
+    if (active) {
+      /* the record and the block of the LF step are fetched together: the step is wasted on a sampled row, but the
+       * two reads do not wait for each other on the others */
+      const ulonglong2 r = idx < ix.n ? __ldg(rec + (idx >> 6)) : make_ulonglong2(0, 0);
       uint64_t nxt;
       const uint32_t sym = rs_lf_step(ix, idx, &nxt);
-      if ((mw >> (idx & 63)) & 1ull) {
-        const uint64_t e = __ldg(ix.loc + rs_sample_slot(ix.loc_mark, ix.loc_rank, idx));
+      bool done = false;
+      uint64_t term = ~0ull;
+      uint32_t nsteps = 0xFFFFFFFFu;
+      if ((r.x >> (idx & 63)) & 1ull) {
+        const uint64_t e = __ldg(ix.loc + rs_sample_slot(r, idx));
         const uint64_t f = e != ~0ull ? __ldg(ix.loc_fin + (e >> 24)) : ~0ull;
         if (f != ~0ull) {
           const uint64_t total = (uint64_t)s + ((f & RS_LOC_STEP_MASK) - (e & RS_LOC_STEP_MASK));
@@ -665,21 +695,27 @@ __global__ void __launch_bounds__(RS_THREADS, RS_K2_BLOCKS_BUILD)
             term = f >> 24;
             nsteps = (uint32_t)total;
           }
-          break;
+          done = true;
         }
       }
-      ++lf_steps;
-      idx = nxt;
-      if (sym == 0) {
-        term = idx;
-        nsteps = s;
-        break;
+      if (!done) {
+        ++lf_steps;
+        idx = nxt;
+        if (sym == 0) {
+          term = idx;
+          nsteps = s;
+          done = true;
+        } else if (++s > max_steps) {
+          done = true;
+        }
       }
-      if (++s > max_steps) break;
+      if (done) {
+        if (lexrank) lexrank[i] = term;
+        if (steps) steps[i] = nsteps;
+        if (read_index) read_index[i] = (term != ~0ull && term < ix.num_strings) ? sai[term] : ~0ull;
+        active = false;
+      }
     }
-    if (lexrank) lexrank[i] = term;
-    if (steps) steps[i] = nsteps;
-    if (read_index) read_index[i] = (term != ~0ull && term < ix.num_strings) ? sai[term] : ~0ull;
   }
   if (stats && lf_steps) atomicAdd(stats + 1, lf_steps);
 }
@@ -694,23 +730,39 @@ __global__ void __launch_bounds__(RS_THREADS, RS_K2_BLOCKS)
     k_extract_prefix(const __grid_constant__ rs_index_dev ix, const uint64_t* __restrict__ rows, uint64_t n,
                      uint32_t max_steps, uint64_t* __restrict__ lexrank, uint32_t* __restrict__ steps,
                      const uint64_t* __restrict__ sai, uint64_t* __restrict__ read_index, uint8_t* __restrict__ bases,
-                     unsigned long long* __restrict__ stats, const uint64_t* __restrict__ n_dev) {
+                     unsigned long long* __restrict__ stats, const uint64_t* __restrict__ n_dev,
+                     unsigned long long* __restrict__ ticket) {
   if (n_dev && *n_dev < n) n = *n_dev;
-  const uint64_t stride = (uint64_t)gridDim.x * RS_THREADS;
+  const uint32_t lane = threadIdx.x & 31u;
   unsigned long long lf_steps = 0;
-  uint64_t next_i = (uint64_t)blockIdx.x * RS_THREADS + threadIdx.x;
   uint64_t i = 0, idx = 0;
   uint32_t s = 0;
-  bool active = false;
+  bool active = false, exhausted = false;
   while (true) {
-    if (!active && next_i < n) {
-      i = next_i;
-      next_i += stride;
-      idx = rows[i];
-      s = 0;
-      active = true;
+    /* rows are handed out from one counter, a warp taking as many as it has idle lanes (walks are 1 .. read length
+     * steps long: with a fixed share of the rows per thread a warp ran until its slowest lane was done) */
+    const uint32_t idle = __ballot_sync(RS_FULL, !active);
+    if (idle == RS_FULL || __popc(idle) >= RS_REFILL_MIN) {
+      if (!exhausted) {
+        const int leader = __ffs((int)idle) - 1;
+        unsigned long long base = 0;
+        if ((int)lane == leader) base = atomicAdd(ticket, (unsigned long long)__popc(idle));
+        base = __shfl_sync(RS_FULL, base, leader);
+        if (base >= n) exhausted = true;
+        if (!active && !exhausted) {
+          i = base + (uint64_t)__popc(idle & ((1u << lane) - 1u));
+          if (i < n) {
+            idx = rows[i];
+            s = 0;
+            active = true;
+          }
+        }
+      }
+      if (__all_sync(RS_FULL, !active)) {
+        if (exhausted) break;
+        continue;
+      }
     }
-    if (__all_sync(RS_FULL, !active)) break;
     if (active) {
       uint64_t nxt;
       const uint32_t sym = rs_lf_step(ix, idx, &nxt);
@@ -986,14 +1038,19 @@ cudaError_t rs_launch_extract_prefix_n(const rs_index_dev& ix, const uint64_t* r
                                        uint32_t max_steps, const uint64_t* sai, uint64_t* read_index,
                                        unsigned long long* stats, cudaStream_t st) {
   if (!n) return cudaSuccess;
+  unsigned long long* ticket = nullptr;
+  if (!(ix.loc && ix.loc_every == 1)) {
+    const cudaError_t te = rs_ticket_take(1, &ticket, st);
+    if (te != cudaSuccess) return te;
+  }
   if (ix.loc && ix.loc_every > 1) {
-    RS_LAUNCH(k_locate_sampled, n, st, ix, rows, n, max_steps, nullptr, nullptr, sai, read_index, stats, n_dev);
+    RS_LAUNCH(k_locate_sampled, n, st, ix, rows, n, max_steps, nullptr, nullptr, sai, read_index, stats, n_dev, ticket);
   } else if (ix.loc) {
     uint64_t blocks = (n + RS_THREADS - 1) / RS_THREADS;
     if (blocks > 148 * 8) blocks = 148 * 8;
     k_locate_lookup<<<(unsigned)blocks, RS_THREADS, 0, st>>>(ix, rows, n, max_steps, nullptr, nullptr, sai, read_index, stats, n_dev);
   } else {
-    RS_LAUNCH(k_extract_prefix, n, st, ix, rows, n, max_steps, nullptr, nullptr, sai, read_index, nullptr, stats, n_dev);
+    RS_LAUNCH(k_extract_prefix, n, st, ix, rows, n, max_steps, nullptr, nullptr, sai, read_index, nullptr, stats, n_dev, ticket);
   }
   return cudaGetLastError();
 }
@@ -1003,8 +1060,13 @@ cudaError_t rs_launch_extract_prefix(const rs_index_dev& ix, const uint64_t* row
                                      uint8_t* bases, unsigned long long* stats, cudaStream_t st) {
   if (!n) return cudaSuccess;
   const uint64_t* none = nullptr;
+  unsigned long long* ticket = nullptr;
+  if (!(ix.loc && ix.loc_every == 1 && !bases)) {
+    const cudaError_t te = rs_ticket_take(1, &ticket, st);
+    if (te != cudaSuccess) return te;
+  }
   if (ix.loc && ix.loc_every > 1 && !bases) {
-    RS_LAUNCH(k_locate_sampled, n, st, ix, rows, n, max_steps, lexrank, steps, sai, read_index, stats, none);
+    RS_LAUNCH(k_locate_sampled, n, st, ix, rows, n, max_steps, lexrank, steps, sai, read_index, stats, none, ticket);
     return cudaGetLastError();
   }
   if (ix.loc && !bases) {
@@ -1013,42 +1075,47 @@ cudaError_t rs_launch_extract_prefix(const rs_index_dev& ix, const uint64_t* row
     k_locate_lookup<<<(unsigned)blocks, RS_THREADS, 0, st>>>(ix, rows, n, max_steps, lexrank, steps, sai, read_index, stats, none);
     return cudaGetLastError();
   }
-  RS_LAUNCH(k_extract_prefix, n, st, ix, rows, n, max_steps, lexrank, steps, sai, read_index, bases, stats, none);
+  RS_LAUNCH(k_extract_prefix, n, st, ix, rows, n, max_steps, lexrank, steps, sai, read_index, bases, stats, none, ticket);
   return cudaGetLastError();
 }
 
-/* sampled table, pass 1: mark[] (zeroed here) and fin[]; the caller sizes loc from the marks (rs_locate_marks_scan) */
-cudaError_t rs_locate_mark(const rs_index_dev& ix_in, uint32_t max_len, uint32_t every, uint64_t* mark, uint64_t* fin,
+/* sampled table, pass 1: records (zeroed here) and fin[]; the caller sizes loc from the marks */
+cudaError_t rs_locate_mark(const rs_index_dev& ix_in, uint32_t max_len, uint32_t every, uint64_t* rec, uint64_t* fin,
                            cudaStream_t st) {
   rs_index_dev ix = ix_in;
   ix.loc = nullptr;
   ix.loc_every = 0;
   cudaError_t e;
   const uint64_t nwords = (ix.n + 63) / 64;
-  if ((e = cudaMemsetAsync(mark, 0, nwords * 8, st)) != cudaSuccess) return e;
+  if ((e = cudaMemsetAsync(rec, 0, nwords * 16, st)) != cudaSuccess) return e;
   if ((e = cudaMemsetAsync(fin, 0xFF, (ix.num_strings ? ix.num_strings : 1) * 8, st)) != cudaSuccess) return e;
   if (!ix.num_strings) return cudaSuccess;
-  RS_LAUNCH(k_mark_locate, ix.num_strings, st, ix, max_len, every, reinterpret_cast<unsigned long long*>(mark), fin);
+  RS_LAUNCH(k_mark_locate, ix.num_strings, st, ix, max_len, every, reinterpret_cast<ulonglong2*>(rec), fin);
   return cudaGetLastError();
 }
 
-/* counts[g] = marked rows of group g (512 rows); the caller scans them into the rank directory */
-cudaError_t rs_locate_mark_counts(const uint64_t* mark, uint64_t n, uint64_t* counts, cudaStream_t st) {
-  const uint64_t nwords = (n + 63) / 64, ngroups = (nwords + 7) / 8;
-  k_mark_counts<<<(unsigned)((ngroups + 255) / 256), 256, 0, st>>>(mark, ngroups, nwords, counts);
+/* counts[w] = marked rows of word w; the caller scans them and hands the result to rs_locate_mark_ranks */
+cudaError_t rs_locate_mark_counts(const uint64_t* rec, uint64_t n, uint64_t* counts, cudaStream_t st) {
+  const uint64_t nwords = (n + 63) / 64;
+  k_mark_counts<<<(unsigned)((nwords + 255) / 256), 256, 0, st>>>(reinterpret_cast<const ulonglong2*>(rec), nwords, counts);
+  return cudaGetLastError();
+}
+cudaError_t rs_locate_mark_ranks(uint64_t* rec, uint64_t n, const uint64_t* before, cudaStream_t st) {
+  const uint64_t nwords = (n + 63) / 64;
+  k_mark_ranks<<<(unsigned)((nwords + 255) / 256), 256, 0, st>>>(reinterpret_cast<ulonglong2*>(rec), nwords, before);
   return cudaGetLastError();
 }
 
 /* sampled table, pass 2 */
-cudaError_t rs_locate_fill(const rs_index_dev& ix_in, uint32_t max_len, uint32_t every, const uint64_t* mark,
-                           const uint64_t* rank, uint64_t* loc, uint64_t nsamples, cudaStream_t st) {
+cudaError_t rs_locate_fill(const rs_index_dev& ix_in, uint32_t max_len, uint32_t every, const uint64_t* rec,
+                           uint64_t* loc, uint64_t nsamples, cudaStream_t st) {
   rs_index_dev ix = ix_in;
   ix.loc = nullptr;
   ix.loc_every = 0;
   cudaError_t e;
   if ((e = cudaMemsetAsync(loc, 0xFF, (nsamples ? nsamples : 1) * 8, st)) != cudaSuccess) return e;
   if (!ix.num_strings) return cudaSuccess;
-  RS_LAUNCH(k_fill_locate, ix.num_strings, st, ix, max_len, every, mark, rank, loc);
+  RS_LAUNCH(k_fill_locate, ix.num_strings, st, ix, max_len, every, reinterpret_cast<const ulonglong2*>(rec), loc);
   return cudaGetLastError();
 }
 

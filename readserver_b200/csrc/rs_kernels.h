@@ -51,10 +51,12 @@ cudaError_t rs_launch_extract_prefix_n(const rs_index_dev& ix, const uint64_t* r
 /* fills loc[n] and fin[num_strings] (rs_layout.h: locate table); walks are cut at max_len symbols */
 cudaError_t rs_build_locate_table(const rs_index_dev& ix, uint32_t max_len, uint64_t* loc, uint64_t* fin, cudaStream_t st);
 
-cudaError_t rs_locate_mark(const rs_index_dev& ix, uint32_t max_len, uint32_t every, uint64_t* mark, uint64_t* fin, cudaStream_t st);
-cudaError_t rs_locate_mark_counts(const uint64_t* mark, uint64_t n, uint64_t* counts, cudaStream_t st);
-cudaError_t rs_locate_fill(const rs_index_dev& ix, uint32_t max_len, uint32_t every, const uint64_t* mark, const uint64_t* rank,
-                           uint64_t* loc, uint64_t nsamples, cudaStream_t st);
+/* sampled locate table: rec = one 16-byte record per 64 rows {marker bits, sampled rows before the word} */
+cudaError_t rs_locate_mark(const rs_index_dev& ix, uint32_t max_len, uint32_t every, uint64_t* rec, uint64_t* fin, cudaStream_t st);
+cudaError_t rs_locate_mark_counts(const uint64_t* rec, uint64_t n, uint64_t* counts, cudaStream_t st);
+cudaError_t rs_locate_mark_ranks(uint64_t* rec, uint64_t n, const uint64_t* before, cudaStream_t st);
+cudaError_t rs_locate_fill(const rs_index_dev& ix, uint32_t max_len, uint32_t every, const uint64_t* rec, uint64_t* loc,
+                           uint64_t nsamples, cudaStream_t st);
 
 cudaError_t rs_launch_occ_at(const rs_index_dev& ix, const uint8_t* syms, const uint64_t* cnt, uint64_t n, uint64_t* out,
                              cudaStream_t st);

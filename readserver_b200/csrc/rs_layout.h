@@ -92,9 +92,11 @@ typedef struct rs_index_dev {
   const uint64_t* loc;
   const uint64_t* loc_fin;
   /* Sampled variant (loc_every > 1): loc holds entries only for the rows reached after a multiple of loc_every
-   * symbols of a walk (the start rows included), in row order; loc_mark has one bit per row (set = sampled),
-   * loc_rank[k] = set bits before row 512 k.  A row's walk is followed until it meets a sampled row or its end:
-   * fewer than loc_every LF steps.  n (1/8 + 1/64 + 8/loc_every) bytes instead of 8 n. */
+   * symbols of a walk (the start rows included), in row order.  loc_mark = one 16-byte record per 64 rows:
+   * {bit i = row 64 w + i is sampled, number of sampled rows before row 64 w}, so the record a walk step fetches to
+   * learn whether its row is sampled also gives the slot of the row's entry.  A row's walk is followed until it meets
+   * a sampled row or its end: fewer than loc_every LF steps.  n (1/4 + 8/loc_every) bytes instead of 8 n.
+   * (loc_rank is unused since the records carry the ranks.) */
   const uint64_t* loc_mark;
   const uint64_t* loc_rank;
   uint32_t loc_every; /* 0: no table, 1: full table, > 1: sampled */

@@ -607,6 +607,11 @@ int rs_shardset_seal(rs_shardset* set, uint32_t max_read_len, uint32_t locate_ev
         if (rc != RS_STATUS_OK) return rc;
       }
     }
+  } else {
+    for (rs_index* ix : set->shards) { /* plain walks: a table an earlier seal left on a shard must not answer */
+      const int rc = rs_index_drop_locate_table(ix);
+      if (rc != RS_STATUS_OK) return rc;
+    }
   }
 
   /* device pointer tables */
