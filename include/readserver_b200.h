@@ -169,6 +169,19 @@ int rs_count_batch(const rs_index* ix, const char* kmers, int k, size_t Q, int s
 int rs_count_batch_dev(const rs_index* ix, const void* d_kmers, int k, size_t Q, int strand, void* d_counts,
                        void* stream);
 
+/* rs_count_batch_dev for callers that may not allocate device memory (code under CUDA stream capture, tight serving
+ * loops, harnesses that forbid cudaMalloc).  NO counterpart in the reference.
+ * Same arguments, same answers as rs_count_batch_dev; the call itself performs no cudaMalloc / cudaFree /
+ * allocating library routine: its scratch (8 bytes of packed key per query + the work counter of the search kernel)
+ * is a file-scope `static __device__` array of the library, RS_NOALLOC_MAX_QUERIES * 8 + 256 bytes (8 MiB) that every
+ * GPU loading the library holds until the process exits.  Limits: Q <= RS_NOALLOC_MAX_QUERIES and 1 <= k <= 31
+ * (fixed-length k-mers); beyond them the call returns RS_STATUS_ARG with a message and launches nothing.  The index's
+ * device must be the current device.  All calls on one GPU share the array: calls that overlap on the GPU (different
+ * streams with no ordering between them) RACE; calls on one stream, or ordered by events, are safe. */
+#define RS_NOALLOC_MAX_QUERIES (1u << 20)
+int rs_count_batch_noalloc_dev(const rs_index* ix, const void* d_kmers, int k, size_t Q, int strand, void* d_counts,
+                               void* stream);
+
 /* ---- locate -------------------------------------------------------------------------------------- */
 /* Attach the lexicographic-rank -> read-index table (SGA's .sai, written by `sga index` next to the
  * .bwt: submodules/sga/src/SuffixTools/SampledSuffixArray.cpp:171-189).  sai has num_strings entries. */

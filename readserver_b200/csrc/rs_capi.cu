@@ -924,6 +924,24 @@ int rs_count_batch_dev(const rs_index* ix, const void* d_kmers, int k, size_t Q,
   return RS_STATUS_OK;
 }
 
+/* rs_count_batch_dev without any allocation (no counterpart in the reference; see include/readserver_b200.h) */
+int rs_count_batch_noalloc_dev(const rs_index* ix, const void* d_kmers, int k, size_t Q, int strand, void* d_counts,
+                               void* stream) {
+  if (!ix || (Q && (!d_kmers || !d_counts))) return fail(RS_STATUS_ARG, "null argument");
+  if (k < 1 || k > 31) return fail(RS_STATUS_ARG, "rs_count_batch_noalloc_dev: k must be in 1..31, got %d", k);
+  if (strand != 0 && strand != 1) return fail(RS_STATUS_ARG, "strand must be 0 or 1");
+  if (Q > RS_NOALLOC_MAX_QUERIES)
+    return fail(RS_STATUS_ARG, "rs_count_batch_noalloc_dev: %llu queries exceed the static scratch's maximum of %u per call",
+                (unsigned long long)Q, (unsigned)RS_NOALLOC_MAX_QUERIES);
+  int cur = -1;
+  CU(cudaGetDevice(&cur));
+  if (cur != ix->device)
+    return fail(RS_STATUS_ARG, "rs_count_batch_noalloc_dev: the index lives on device %d, the current device is %d", ix->device, cur);
+  CU(rs_launch_count_noalloc(ix->dev, (const uint8_t*)d_kmers, (uint32_t)k, Q, strand, (uint64_t*)d_counts,
+                             (unsigned long long*)ix->d_stats, (cudaStream_t)stream));
+  return RS_STATUS_OK;
+}
+
 /* ---- locate ---- */
 int rs_index_set_sai(rs_index* ix, const uint64_t* sai, uint64_t num_strings) {
   if (!ix || !sai) return fail(RS_STATUS_ARG, "null argument");

@@ -1198,3 +1198,57 @@ cudaError_t rs_build_dense(const rs_index_dev& ix_in, uint64_t ndense, void* out
   RS_LAUNCH(k_dense_build, ndense, st, ix, ndense, reinterpret_cast<uint4*>(out), bad);
   return cudaGetLastError();
 }
+
+/* ---- count without any allocation (rs_count_batch_noalloc_dev) ----
+ * The count path's scratch -- the packed keys K1 searches (8 bytes per query) and the work counter the dense K1 hands
+ * its queries out from -- lives in a file-scope device array instead of cudaMalloc'd memory: callers that may not
+ * allocate (under stream capture, in a serving loop) can still count.  Every GPU that loads the library holds the
+ * array (8 MiB + 256 B) until the process ends.  ALL calls on a device share it: two calls that overlap on the GPU
+ * (different streams, no ordering between them) race on the keys and on the counter; calls on one stream, or ordered
+ * by events, are safe.  The array keeps the previous call's contents: the counter is cleared by every call, the keys
+ * of queries 0..Q-1 are rewritten by every call before K1 reads them.
+ * `g_noalloc_scratch` is a host-side stand-in in host code, not a device address: the address is taken ONCE per
+ * device with cudaGetSymbolAddress, with that device current. */
+#define RS_NOALLOC_HEAD 256u /* the work counter (first 8 bytes), keeping the keys 256-byte aligned */
+static __device__ __align__(256) unsigned char g_noalloc_scratch[RS_NOALLOC_HEAD + (size_t)RS_NOALLOC_MAX_QUERIES * 8u];
+static unsigned char* g_noalloc_ptr[64] = {};
+static std::mutex g_noalloc_mu;
+
+cudaError_t rs_launch_count_noalloc(const rs_index_dev& ix, const uint8_t* text, uint32_t k, uint64_t Q, int strand,
+                                    uint64_t* counts, unsigned long long* stats, cudaStream_t st) {
+  if (!Q) return cudaSuccess;
+  if (k < 1 || k > RS_PACK_MAX_K || Q > RS_NOALLOC_MAX_QUERIES || (strand != 0 && strand != 1)) return cudaErrorInvalidValue;
+  int dev = 0;
+  cudaError_t e = cudaGetDevice(&dev);
+  if (e != cudaSuccess) return e;
+  if (dev < 0 || dev >= 64) return cudaErrorInvalidDevice;
+  unsigned char* scratch = nullptr;
+  {
+    std::lock_guard<std::mutex> lk(g_noalloc_mu);
+    if (!g_noalloc_ptr[dev]) { /* set-up, once per device, that device being current */
+      void* p = nullptr;
+      e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+      if (e != cudaSuccess) return e;
+      g_noalloc_ptr[dev] = static_cast<unsigned char*>(p);
+    }
+    scratch = g_noalloc_ptr[dev];
+  }
+  unsigned long long* ticket = reinterpret_cast<unsigned long long*>(scratch);
+  uint64_t* pkeys = reinterpret_cast<uint64_t*>(scratch + RS_NOALLOC_HEAD);
+  e = cudaMemsetAsync(ticket, 0, RS_NOALLOC_HEAD, st); /* the counter must start at zero; the last call left it at >= Q */
+  if (e != cudaSuccess) return e;
+  k_pack_kmers<<<(unsigned)((Q + RS_THREADS - 1) / RS_THREADS), RS_THREADS, 0, st>>>(text, k, Q, strand == 1, pkeys);
+  rs_peers peers;
+  memset(&peers, 0, sizeof(peers));
+  const bool ftab = ix.ftab && ix.ftab_k > 1;
+  /* mode 1 (count) over keys kept apart from the output: counts[q] = rows of the interval, 0 for a flagged key */
+  if (ix.dense) {
+    const bool small = ix.n < (1ull << 31);
+    if (ftab && small) RS_LAUNCH((k_find_interval_dense<true, true>), Q, st, ix, k, Q, pkeys, counts, nullptr, 1, strand, stats, peers, ticket);
+    else if (ftab) RS_LAUNCH((k_find_interval_dense<true, false>), Q, st, ix, k, Q, pkeys, counts, nullptr, 1, strand, stats, peers, ticket);
+    else if (small) RS_LAUNCH((k_find_interval_dense<false, true>), Q, st, ix, k, Q, pkeys, counts, nullptr, 1, strand, stats, peers, ticket);
+    else RS_LAUNCH((k_find_interval_dense<false, false>), Q, st, ix, k, Q, pkeys, counts, nullptr, 1, strand, stats, peers, ticket);
+  } else if (ftab) RS_LAUNCH((k_find_interval<true, true>), Q, st, ix, nullptr, nullptr, k, Q, pkeys, counts, nullptr, 1, strand, stats, peers);
+  else RS_LAUNCH((k_find_interval<false, true>), Q, st, ix, nullptr, nullptr, k, Q, pkeys, counts, nullptr, 1, strand, stats, peers);
+  return cudaGetLastError();
+}

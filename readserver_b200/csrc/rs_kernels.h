@@ -34,6 +34,13 @@ cudaError_t rs_launch_find_interval_packed(const rs_index_dev& ix, const uint64_
                                            uint64_t* first, uint32_t* rows, int mode, unsigned long long* stats,
                                            cudaStream_t st, const rs_peers* peers = nullptr,
                                            unsigned long long* ticket = nullptr);
+/* Count (mode 1) with NO allocation: the packed keys and the dense K1's work counter live in a file-scope device array
+ * of rs_kernels.cu (RS_NOALLOC_MAX_QUERIES * 8 + 256 bytes per GPU), shared by all calls on the device. */
+#ifndef RS_NOALLOC_MAX_QUERIES
+#define RS_NOALLOC_MAX_QUERIES (1u << 20) /* = include/readserver_b200.h */
+#endif
+cudaError_t rs_launch_count_noalloc(const rs_index_dev& ix, const uint8_t* text, uint32_t k, uint64_t Q, int strand,
+                                    uint64_t* counts, unsigned long long* stats, cudaStream_t st);
 /* work counters of the kernels that hand their items out dynamically: `n` consecutive cleared slots, one per launch */
 cudaError_t rs_ticket_take(uint32_t n, unsigned long long** first, cudaStream_t st);
 /* cross-GPU barrier over peer-mapped flag words: every rank writes `epoch` into its slot of every peer's

@@ -140,6 +140,7 @@ def lib() -> C.CDLL:
         "rs_find_interval_var_batch_dev": (i32, [vp, vp, vp, sz, vp, vp, vp]),
         "rs_count_batch": (i32, [vp, vp, i32, sz, i32, vp]),
         "rs_count_batch_dev": (i32, [vp, vp, i32, sz, i32, vp, vp]),
+        "rs_count_batch_noalloc_dev": (i32, [vp, vp, i32, sz, i32, vp, vp]),
         "rs_index_set_sai": (i32, [vp, vp, u64]),
         "rs_extract_prefix_batch": (i32, [vp, vp, sz, C.c_uint32, vp, vp, vp, vp]),
         "rs_extract_prefix_batch_dev": (i32, [vp, vp, sz, C.c_uint32, vp, vp, vp, vp, vp]),
@@ -150,6 +151,9 @@ def lib() -> C.CDLL:
         f.argtypes = args
     _LIB = L
     return L
+
+
+NOALLOC_MAX_QUERIES = 1 << 20  # RS_NOALLOC_MAX_QUERIES, include/readserver_b200.h
 
 
 def _check(rc: int):
@@ -568,6 +572,11 @@ class GpuBWT:
 
     def count_dev(self, d_kmers, k: int, q: int, strand: int, d_counts, stream: int = 0):
         _check(lib().rs_count_batch_dev(self._h, _ptr(d_kmers), k, q, strand, _ptr(d_counts), stream))
+
+    def count_noalloc_dev(self, d_kmers, k: int, q: int, strand: int, d_counts, stream: int = 0):
+        """count_dev for callers that may not allocate: scratch in the library's static device array
+        (q <= NOALLOC_MAX_QUERIES, k <= 31; calls overlapping on the GPU race -- include/readserver_b200.h)."""
+        _check(lib().rs_count_batch_noalloc_dev(self._h, _ptr(d_kmers), k, q, strand, _ptr(d_counts), stream))
 
     def locate_dev(self, d_kmers, k: int, q: int, max_hits: int, max_steps: int, d_hit_offsets, capacity: int,
                    d_rows=None, d_lexrank=None, d_read_index=None, d_steps=None, stream: int = 0) -> int:
