@@ -155,7 +155,9 @@ __global__ void k_pop_advance(const uint64_t* __restrict__ local, uint64_t nq, u
   if (total) *total = *base;
 }
 
-/* extractPrefix from one row of shard `v` (rows the read-index table does not cover): as K2 walks it */
+/* extractPrefix from one row of shard `v` (rows the read-index table does not cover): as K2 walks it.  A copy per
+ * instantiation of the gather kernel: ptxas 12.9 crashes on one out-of-line function called from several of them. */
+template <uint32_t G>
 __device__ __noinline__ uint64_t rs_pop_walk_one(const rs_index_dev* __restrict__ views, uint32_t s,
                                                  const uint64_t* const* __restrict__ sais, uint64_t row,
                                                  uint32_t max_steps) {
@@ -227,14 +229,32 @@ __global__ void k_pop_owner_slots(const __grid_constant__ rs_pop_peers P, const 
 #ifndef RS_GATHER_BLOCKS
 #define RS_GATHER_BLOCKS 4 /* resident CTAs per SM: the kernel waits on memory, occupancy is its parallelism */
 #endif
+/* OR over the lanes of a query's group */
+template <uint32_t G>
+__device__ __forceinline__ uint32_t rs_group_or(uint32_t gm, uint32_t v) {
+  if constexpr (G == 32) {
+    return __reduce_or_sync(RS_FULL, v);
+  } else {
+#pragma unroll
+    for (int d = (int)G / 2; d >= 1; d >>= 1) v |= __shfl_xor_sync(gm, v, d, G);
+    return v;
+  }
+}
+/* G lanes per query (a power of two, 8..32): a rank that holds few shards (8 of the 64 on each of 8 GPUs) would leave
+ * most lanes of a whole warp without a shard -- and the kernel's memory-level parallelism is its lanes with a load in
+ * flight; with G = 8 a warp works on four queries at once.  Groups of one warp run independently (disjoint masks). */
+template <uint32_t G>
 __global__ void __launch_bounds__(256, RS_GATHER_BLOCKS)
     k_pop_gather(const __grid_constant__ rs_pop_tables T, const __grid_constant__ rs_pop_peers P,
                  const uint64_t* __restrict__ keys, uint32_t k, const uint64_t* __restrict__ lo,
                  const uint32_t* __restrict__ cnt, uint64_t C, uint64_t q0, uint64_t nq, uint64_t max_hits,
                  const uint64_t* __restrict__ slot, uint64_t capacity, int want_carriers) {
-  const uint32_t lane = threadIdx.x & 31;
-  const uint64_t warps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
-  for (uint64_t q = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5; q < nq; q += warps) {
+  const uint32_t wlane = threadIdx.x & 31;
+  const uint32_t lane = wlane & (G - 1u);                 /* lane within the query's group */
+  const uint32_t gshift = wlane & ~(G - 1u);              /* the group's first lane in the warp */
+  const uint32_t GM = G == 32 ? RS_FULL : (((1u << (G & 31u)) - 1u) << gshift); /* the group's lanes */
+  const uint64_t groups = ((uint64_t)gridDim.x * blockDim.x) / G;
+  for (uint64_t q = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) / G; q < nq; q += groups) {
     const uint32_t owner = P.world > 1 ? rs_owner_of(keys[q], k, false, P.world) : 0u;
     uint64_t* __restrict__ hits = P.hits[owner];
     uint64_t off = slot[q0 + q];
@@ -244,17 +264,17 @@ __global__ void __launch_bounds__(256, RS_GATHER_BLOCKS)
      * the rate of the random-access probe); ld.global.cg instead of the L1 path made it slower (82 vs 73 ms).
      * A k-mer of a read set at 30x hits a handful of rows in most of the shards: the lanes take one shard each
      * (32 independent chains of loads in flight per warp), a warp scan lays their rows out in shard order. */
-    for (uint32_t s0 = 0; s0 < T.nshards; s0 += 32) {
+    for (uint32_t s0 = 0; s0 < T.nshards; s0 += G) {
       const uint32_t s = s0 + lane;
       uint64_t c = s < T.nshards ? cnt[(uint64_t)s * C + q] : 0;
       if (c > max_hits) c = max_hits;
       uint64_t incl = c;
 #pragma unroll
-      for (int d = 1; d < 32; d <<= 1) {
-        const uint64_t t = __shfl_up_sync(RS_FULL, incl, d);
+      for (int d = 1; d < (int)G; d <<= 1) {
+        const uint64_t t = __shfl_up_sync(GM, incl, d, G);
         if ((int)lane >= d) incl += t;
       }
-      const uint64_t total = __shfl_sync(RS_FULL, incl, 31);
+      const uint64_t total = __shfl_sync(GM, incl, G - 1, G);
       if (total == 0) continue;
       const uint64_t mine = off + incl - c; /* where this lane's shard starts in the query's list */
       const uint64_t first = c ? lo[(uint64_t)s * C + q] : 0;
@@ -264,7 +284,7 @@ __global__ void __launch_bounds__(256, RS_GATHER_BLOCKS)
         const uint64_t tag = T.tag[s];
         for (uint32_t j = 0; j < (uint32_t)c; ++j) {
           uint64_t r = rid[first + j];
-          if (r == RS_RID_NONE) r = rs_pop_walk_one(T.views, s, T.sai, first + j, T.max_steps);
+          if (r == RS_RID_NONE) r = rs_pop_walk_one<G>(T.views, s, T.sai, first + j, T.max_steps);
           if (mine + j < capacity) hits[mine + j] = r == ~0ull ? ~0ull : (tag | r);
           if (want_carriers && sets && r != ~0ull) {
             const uint4 v = __ldg(sets + r);
@@ -275,20 +295,20 @@ __global__ void __launch_bounds__(256, RS_GATHER_BLOCKS)
           }
         }
       }
-      /* long intervals (a repeat, a short k): the whole warp reads the rows of one shard, coalesced */
-      uint32_t big = __ballot_sync(RS_FULL, c > RS_GATHER_LANE_ROWS);
+      /* long intervals (a repeat, a short k): the whole group reads the rows of one shard, coalesced */
+      uint32_t big = __ballot_sync(GM, c > RS_GATHER_LANE_ROWS) >> gshift;
       while (big) {
         const int src = __ffs((int)big) - 1;
         big &= big - 1;
-        const uint64_t bc = __shfl_sync(RS_FULL, c, src), bfirst = __shfl_sync(RS_FULL, first, src),
-                       bmine = __shfl_sync(RS_FULL, mine, src);
+        const uint64_t bc = __shfl_sync(GM, c, src, G), bfirst = __shfl_sync(GM, first, src, G),
+                       bmine = __shfl_sync(GM, mine, src, G);
         const uint32_t bs = s0 + (uint32_t)src;
         const uint32_t* __restrict__ rid = T.rid[bs];
         const uint4* __restrict__ sets = T.sets[bs];
         const uint64_t tag = T.tag[bs];
-        for (uint64_t j = lane; j < bc; j += 32) {
+        for (uint64_t j = lane; j < bc; j += G) {
           uint64_t r = rid[bfirst + j];
-          if (r == RS_RID_NONE) r = rs_pop_walk_one(T.views, bs, T.sai, bfirst + j, T.max_steps);
+          if (r == RS_RID_NONE) r = rs_pop_walk_one<G>(T.views, bs, T.sai, bfirst + j, T.max_steps);
           if (bmine + j < capacity) hits[bmine + j] = r == ~0ull ? ~0ull : (tag | r);
           if (want_carriers && sets && r != ~0ull) {
             const uint4 v = __ldg(sets + r);
@@ -302,10 +322,10 @@ __global__ void __launch_bounds__(256, RS_GATHER_BLOCKS)
       off += total;
     }
     if (want_carriers) {
-      b0 = __reduce_or_sync(RS_FULL, b0);
-      b1 = __reduce_or_sync(RS_FULL, b1);
-      b2 = __reduce_or_sync(RS_FULL, b2);
-      b3 = __reduce_or_sync(RS_FULL, b3);
+      b0 = rs_group_or<G>(GM, b0);
+      b1 = rs_group_or<G>(GM, b1);
+      b2 = rs_group_or<G>(GM, b2);
+      b3 = rs_group_or<G>(GM, b3);
       uint32_t* dst = P.carr[owner] + (q0 + q) * 4;
       if (P.world == 1) {
         if (lane == 0) *reinterpret_cast<uint4*>(dst) = make_uint4(b0, b1, b2, b3);
@@ -991,8 +1011,11 @@ static int pop_run(rs_shardset* set, rs_popcomm* comm, const void* d_kmers, int 
     const uint64_t* slot = P.slot[multi ? comm->rank : 0];
     StageTimer tm_locate(set, st, RS_POP_STAGE_LOCATE, table ? 1 : 5 * S + 1);
     if (table) {
-      k_pop_gather<<<grid_for(nq * 32, 256, 148 * 2 * RS_GATHER_BLOCKS), 256, 0, st>>>(set->tab, P, keys + q0, (uint32_t)k, lo, cnt, C, q0, nq, max_hits,
-                                                                 slot, capacity, (want_carr && set->have_sets) ? 1 : 0);
+      const int wc = (want_carr && set->have_sets) ? 1 : 0;
+      const int gg = 148 * 2 * RS_GATHER_BLOCKS;
+      if (S > 16) k_pop_gather<32><<<grid_for(nq * 32, 256, gg), 256, 0, st>>>(set->tab, P, keys + q0, (uint32_t)k, lo, cnt, C, q0, nq, max_hits, slot, capacity, wc);
+      else if (S > 8) k_pop_gather<16><<<grid_for(nq * 16, 256, gg), 256, 0, st>>>(set->tab, P, keys + q0, (uint32_t)k, lo, cnt, C, q0, nq, max_hits, slot, capacity, wc);
+      else k_pop_gather<8><<<grid_for(nq * 8, 256, gg), 256, 0, st>>>(set->tab, P, keys + q0, (uint32_t)k, lo, cnt, C, q0, nq, max_hits, slot, capacity, wc);
       CU(cudaGetLastError());
       if (want_carr && !set->have_sets) {
         k_pop_carriers<<<grid_for(nq * 32, 256, 148 * 8), 256, 8 * set->words * 4, st>>>(set->tab, d_hit_offsets + q0, nq, d_hits, capacity,

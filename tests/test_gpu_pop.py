@@ -305,6 +305,25 @@ def test_shard_set_order_ids_chunks_and_bad_bytes(popcase, engine, monkeypatch):
         assert rc == 9 and tot.value == want[1][-1] and np.array_equal(off, want[1]) and np.array_equal(hits, want[2][:10])
 
 
+@pytest.mark.parametrize("nshards", [3, 7, 13, 16, 17])
+def test_shard_set_of_few_shards(nshards, popcase, engine):
+    """A rank of a multi-GPU job holds a few of the 64 shards: the gather kernel then works on several queries per warp
+    (8 or 16 lanes each).  Long k-mers (a few rows per shard: one lane per shard) and short ones (intervals of many rows:
+    the whole group reads one shard's rows)."""
+    order = [(5 * s + 2) % 64 for s in range(nshards)]
+    with engine.ShardSet() as S:
+        for s in order:
+            S.add(popcase.gpu[s], s)
+        S.seal(popcase.read_len + 28, 1)
+        for k, nq, max_hits in ((31, 3001, 1 << 20), (9, 700, 1 << 20), (9, 700, 11)):
+            q = np.ascontiguousarray(popcase.queries[:nq, :k])
+            want = popcase.expected(q, max_hits, shard_order=order)
+            got = S.query(q, k, max_hits=max_hits, carriers=True)
+            assert np.array_equal(got["counts"], want[0]) and np.array_equal(got["hit_offsets"], want[1]), (k, max_hits)
+            assert np.array_equal(got["hits"], want[2]) and np.array_equal(got["carriers"], want[3]), (k, max_hits)
+        assert int(want[0].max()) > 8 * nshards  # the short k-mers do have long intervals
+
+
 def test_shard_set_under_the_reference_tail_behaviour(datasets, engine):
     """A single shard whose tail region is NOT empty ('small': walks into it are cut or wander): the read-index table
     leaves those rows uncovered and the pipeline walks them, ending where K2 and the oracle end."""
