@@ -537,6 +537,11 @@ def run_ours(args):
     if world > 1:
         dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
     total_ms = float(total_ms.item())
+    stage_by_rank = None
+    if world > 1:  # every rank's stage times: the step ends at the slowest rank's last barrier
+        per = [None] * world
+        dist.all_gather_object(per, {s_: round(v / args.steps, 3) for s_, v in stage_ms.items()})
+        stage_by_rank = per
 
     # ---- N > 1: the fanned-in answers against the ranks' own answers, gathered with torch.distributed ----
     fan_in_ok = None
@@ -718,6 +723,7 @@ def run_ours(args):
             "avg_launch_ms": stage_ms["search"] / k1_launches,
             "k1_share_of_step": stage_ms["search"] / max(sum(step_ms), 1e-9),
             "stage_ms_per_step": {s: v / args.steps for s, v in stage_ms.items()},
+            **({"stage_ms_per_step_by_rank": stage_by_rank} if stage_by_rank else {}),
             "note": "one launch = the whole batch against ONE shard, whose rank blocks (70 MB) and suffix table stay largely "
                     "L2-resident for the launch: the achieved figure is served by L2 + HBM together, `traffic` (ncu) says how "
                     "much of it HBM carried (DESIGN.md 6)",

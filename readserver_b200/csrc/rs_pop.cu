@@ -229,53 +229,56 @@ __global__ void k_pop_owner_slots(const __grid_constant__ rs_pop_peers P, const 
 #ifndef RS_GATHER_BLOCKS
 #define RS_GATHER_BLOCKS 4 /* resident CTAs per SM: the kernel waits on memory, occupancy is its parallelism */
 #endif
-/* OR over the lanes of a query's group */
+/* OR over the G lanes of a query's group (every lane of the warp takes part) */
 template <uint32_t G>
-__device__ __forceinline__ uint32_t rs_group_or(uint32_t gm, uint32_t v) {
+__device__ __forceinline__ uint32_t rs_group_or(uint32_t v) {
   if constexpr (G == 32) {
     return __reduce_or_sync(RS_FULL, v);
   } else {
 #pragma unroll
-    for (int d = (int)G / 2; d >= 1; d >>= 1) v |= __shfl_xor_sync(gm, v, d, G);
+    for (int d = (int)G / 2; d >= 1; d >>= 1) v |= __shfl_xor_sync(RS_FULL, v, d, G);
     return v;
   }
 }
-/* G lanes per query (a power of two, 8..32): a rank that holds few shards (8 of the 64 on each of 8 GPUs) would leave
- * most lanes of a whole warp without a shard -- and the kernel's memory-level parallelism is its lanes with a load in
- * flight; with G = 8 a warp works on four queries at once.  Groups of one warp run independently (disjoint masks). */
+/* G lanes per query (a power of two, 1..32), 32 / G queries per warp, the lanes of a group taking one shard each, G
+ * shards per round.  The kernel waits on memory and its parallelism is the lanes that have a load in flight: a rank that
+ * holds few shards (8 or 9 of the 64 on each of 8 GPUs) would leave most lanes of a warp-per-query kernel without a
+ * shard, so the host picks the largest G that keeps >= 85 % of the lane slots on a shard (rs_gather_lanes).  All groups
+ * of a warp run the same trips (a group past the batch's end carries zero counts), so the warp stays converged and an
+ * interval of many rows is read by all 32 lanes whichever group it belongs to. */
 template <uint32_t G>
 __global__ void __launch_bounds__(256, RS_GATHER_BLOCKS)
     k_pop_gather(const __grid_constant__ rs_pop_tables T, const __grid_constant__ rs_pop_peers P,
                  const uint64_t* __restrict__ keys, uint32_t k, const uint64_t* __restrict__ lo,
                  const uint32_t* __restrict__ cnt, uint64_t C, uint64_t q0, uint64_t nq, uint64_t max_hits,
                  const uint64_t* __restrict__ slot, uint64_t capacity, int want_carriers) {
+  constexpr uint32_t QW = 32u / G; /* queries per warp */
   const uint32_t wlane = threadIdx.x & 31;
-  const uint32_t lane = wlane & (G - 1u);                 /* lane within the query's group */
-  const uint32_t gshift = wlane & ~(G - 1u);              /* the group's first lane in the warp */
-  const uint32_t GM = G == 32 ? RS_FULL : (((1u << (G & 31u)) - 1u) << gshift); /* the group's lanes */
-  const uint64_t groups = ((uint64_t)gridDim.x * blockDim.x) / G;
-  for (uint64_t q = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) / G; q < nq; q += groups) {
-    const uint32_t owner = P.world > 1 ? rs_owner_of(keys[q], k, false, P.world) : 0u;
+  const uint32_t lane = wlane & (G - 1u); /* lane within the query's group */
+  const uint64_t warps = ((uint64_t)gridDim.x * blockDim.x) >> 5;
+  for (uint64_t qb = (((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5) * QW; qb < nq; qb += warps * QW) {
+    const uint64_t q = qb + wlane / G;
+    const bool valid = q < nq;
+    const uint32_t owner = (valid && P.world > 1) ? rs_owner_of(keys[q], k, false, P.world) : 0u;
     uint64_t* __restrict__ hits = P.hits[owner];
-    uint64_t off = slot[q0 + q];
+    uint64_t off = valid ? slot[q0 + q] : 0;
     uint32_t b0 = 0, b1 = 0, b2 = 0, b3 = 0;
     /* The table reads below are 4 and 16 bytes at random addresses, and HBM delivers whole 128-byte lines for them
      * (ncu on configs[2]: 247 GB of DRAM reads per 10 M-query step for 790 M hits = 1.9 G line fetches at 26 G lines/s,
      * the rate of the random-access probe); ld.global.cg instead of the L1 path made it slower (82 vs 73 ms).
      * A k-mer of a read set at 30x hits a handful of rows in most of the shards: the lanes take one shard each
-     * (32 independent chains of loads in flight per warp), a warp scan lays their rows out in shard order. */
+     * (32 independent chains of loads in flight per warp), a scan over the group lays their rows out in shard order. */
     for (uint32_t s0 = 0; s0 < T.nshards; s0 += G) {
       const uint32_t s = s0 + lane;
-      uint64_t c = s < T.nshards ? cnt[(uint64_t)s * C + q] : 0;
+      uint64_t c = (valid && s < T.nshards) ? cnt[(uint64_t)s * C + q] : 0;
       if (c > max_hits) c = max_hits;
       uint64_t incl = c;
 #pragma unroll
       for (int d = 1; d < (int)G; d <<= 1) {
-        const uint64_t t = __shfl_up_sync(GM, incl, d, G);
+        const uint64_t t = __shfl_up_sync(RS_FULL, incl, d, G);
         if ((int)lane >= d) incl += t;
       }
-      const uint64_t total = __shfl_sync(GM, incl, G - 1, G);
-      if (total == 0) continue;
+      const uint64_t total = __shfl_sync(RS_FULL, incl, G - 1, G);
       const uint64_t mine = off + incl - c; /* where this lane's shard starts in the query's list */
       const uint64_t first = c ? lo[(uint64_t)s * C + q] : 0;
       if (c && c <= RS_GATHER_LANE_ROWS) {
@@ -295,46 +298,74 @@ __global__ void __launch_bounds__(256, RS_GATHER_BLOCKS)
           }
         }
       }
-      /* long intervals (a repeat, a short k): the whole group reads the rows of one shard, coalesced */
-      uint32_t big = __ballot_sync(GM, c > RS_GATHER_LANE_ROWS) >> gshift;
+      /* long intervals (a repeat, a short k): the whole warp reads the rows of one shard, coalesced */
+      uint32_t big = __ballot_sync(RS_FULL, c > RS_GATHER_LANE_ROWS);
       while (big) {
         const int src = __ffs((int)big) - 1;
         big &= big - 1;
-        const uint64_t bc = __shfl_sync(GM, c, src, G), bfirst = __shfl_sync(GM, first, src, G),
-                       bmine = __shfl_sync(GM, mine, src, G);
-        const uint32_t bs = s0 + (uint32_t)src;
+        const uint64_t bc = __shfl_sync(RS_FULL, c, src), bfirst = __shfl_sync(RS_FULL, first, src),
+                       bmine = __shfl_sync(RS_FULL, mine, src);
+        const uint32_t bs = __shfl_sync(RS_FULL, s, src);
+        uint64_t* __restrict__ bhits = P.hits[__shfl_sync(RS_FULL, owner, src)];
         const uint32_t* __restrict__ rid = T.rid[bs];
         const uint4* __restrict__ sets = T.sets[bs];
         const uint64_t tag = T.tag[bs];
-        for (uint64_t j = lane; j < bc; j += G) {
+        uint32_t t0 = 0, t1 = 0, t2 = 0, t3 = 0;
+        for (uint64_t j = wlane; j < bc; j += 32) {
           uint64_t r = rid[bfirst + j];
           if (r == RS_RID_NONE) r = rs_pop_walk_one<G>(T.views, bs, T.sai, bfirst + j, T.max_steps);
-          if (bmine + j < capacity) hits[bmine + j] = r == ~0ull ? ~0ull : (tag | r);
+          if (bmine + j < capacity) bhits[bmine + j] = r == ~0ull ? ~0ull : (tag | r);
           if (want_carriers && sets && r != ~0ull) {
             const uint4 v = __ldg(sets + r);
-            b0 |= v.x;
-            b1 |= v.y;
-            b2 |= v.z;
-            b3 |= v.w;
+            t0 |= v.x;
+            t1 |= v.y;
+            t2 |= v.z;
+            t3 |= v.w;
+          }
+        }
+        if (want_carriers) { /* the set goes to the query of the lane the interval came from */
+          t0 = __reduce_or_sync(RS_FULL, t0);
+          t1 = __reduce_or_sync(RS_FULL, t1);
+          t2 = __reduce_or_sync(RS_FULL, t2);
+          t3 = __reduce_or_sync(RS_FULL, t3);
+          if ((int)wlane == src) {
+            b0 |= t0;
+            b1 |= t1;
+            b2 |= t2;
+            b3 |= t3;
           }
         }
       }
       off += total;
     }
     if (want_carriers) {
-      b0 = rs_group_or<G>(GM, b0);
-      b1 = rs_group_or<G>(GM, b1);
-      b2 = rs_group_or<G>(GM, b2);
-      b3 = rs_group_or<G>(GM, b3);
-      uint32_t* dst = P.carr[owner] + (q0 + q) * 4;
-      if (P.world == 1) {
-        if (lane == 0) *reinterpret_cast<uint4*>(dst) = make_uint4(b0, b1, b2, b3);
-      } else if (lane < 4) { /* several ranks contribute to one bitmap (cleared by its owner before the step) */
-        const uint32_t v = lane == 0 ? b0 : lane == 1 ? b1 : lane == 2 ? b2 : b3;
-        if (v) atomicOr(dst + lane, v);
+      b0 = rs_group_or<G>(b0);
+      b1 = rs_group_or<G>(b1);
+      b2 = rs_group_or<G>(b2);
+      b3 = rs_group_or<G>(b3);
+      if (valid) {
+        uint32_t* dst = P.carr[owner] + (q0 + q) * 4;
+        if (P.world == 1) {
+          if (lane == 0) *reinterpret_cast<uint4*>(dst) = make_uint4(b0, b1, b2, b3);
+        } else { /* several ranks contribute to one bitmap (cleared by its owner before the step) */
+          for (uint32_t w = lane; w < 4; w += G) {
+            const uint32_t v = w == 0 ? b0 : w == 1 ? b1 : w == 2 ? b2 : b3;
+            if (v) atomicOr(dst + w, v);
+          }
+        }
       }
     }
   }
+}
+
+/* lanes per query for a rank holding S shards: the largest power of two that keeps >= 85 % of the lane slots of a round
+ * on a shard (S = 64, 32: 32; 16: 16; 8, 7: 8; 21, 22: 8; 9: 2; 1 lane always qualifies) */
+static uint32_t rs_gather_lanes(uint32_t S) {
+  for (uint32_t g = 32; g > 1; g >>= 1) {
+    const uint32_t slots = (S + g - 1) / g * g;
+    if ((uint64_t)S * 100 >= (uint64_t)slots * 85) return g;
+  }
+  return 1;
 }
 
 /* ---- without the read-index table: per shard, rows -> walk -> scatter ---- */
@@ -442,6 +473,7 @@ struct rs_shardset {
   uint64_t* h_marks = nullptr;
   uint64_t* d_stats = nullptr; /* executed updateInterval steps / LF steps of the set's calls (bench.py) */
   uint64_t chunk = 1u << 20;
+  uint32_t gather_lanes = 32; /* lanes per query in the gather kernel (rs_gather_lanes; RS_B200_GATHER_LANES forces) */
   bool chunk_forced = false; /* RS_B200_POP_CHUNK given */
   /* stage timing (bench.py: which kernel a step's time goes to): events recorded on the call's stream around the
    * stages of every chunk, read back -- and summed per stage -- by rs_shardset_read_timing */
@@ -678,6 +710,11 @@ int rs_shardset_seal(rs_shardset* set, uint32_t max_read_len, uint32_t locate_ev
   T.views = (const rs_index_dev*)put(views.data(), S * sizeof(rs_index_dev), 16);
   CU(cudaMemcpyAsync(set->d_tabmem, host.data(), bytes, cudaMemcpyHostToDevice, st));
   CU(cudaStreamSynchronize(st));
+  set->gather_lanes = rs_gather_lanes((uint32_t)set->shards.size());
+  if (const char* e = getenv("RS_B200_GATHER_LANES")) { /* experiments and tests: 1, 2, 4, 8, 16 or 32 */
+    const long v = atol(e);
+    if (v >= 1 && v <= 32 && (v & (v - 1)) == 0) set->gather_lanes = (uint32_t)v;
+  }
   set->sealed = true;
   return RS_STATUS_OK;
 }
@@ -1013,9 +1050,17 @@ static int pop_run(rs_shardset* set, rs_popcomm* comm, const void* d_kmers, int 
     if (table) {
       const int wc = (want_carr && set->have_sets) ? 1 : 0;
       const int gg = 148 * 2 * RS_GATHER_BLOCKS;
-      if (S > 16) k_pop_gather<32><<<grid_for(nq * 32, 256, gg), 256, 0, st>>>(set->tab, P, keys + q0, (uint32_t)k, lo, cnt, C, q0, nq, max_hits, slot, capacity, wc);
-      else if (S > 8) k_pop_gather<16><<<grid_for(nq * 16, 256, gg), 256, 0, st>>>(set->tab, P, keys + q0, (uint32_t)k, lo, cnt, C, q0, nq, max_hits, slot, capacity, wc);
-      else k_pop_gather<8><<<grid_for(nq * 8, 256, gg), 256, 0, st>>>(set->tab, P, keys + q0, (uint32_t)k, lo, cnt, C, q0, nq, max_hits, slot, capacity, wc);
+#define RS_GATHER(G) \
+  k_pop_gather<G><<<grid_for(nq * G, 256, gg), 256, 0, st>>>(set->tab, P, keys + q0, (uint32_t)k, lo, cnt, C, q0, nq, max_hits, slot, capacity, wc)
+      switch (set->gather_lanes) {
+        case 32: RS_GATHER(32); break;
+        case 16: RS_GATHER(16); break;
+        case 8: RS_GATHER(8); break;
+        case 4: RS_GATHER(4); break;
+        case 2: RS_GATHER(2); break;
+        default: RS_GATHER(1); break;
+      }
+#undef RS_GATHER
       CU(cudaGetLastError());
       if (want_carr && !set->have_sets) {
         k_pop_carriers<<<grid_for(nq * 32, 256, 148 * 8), 256, 8 * set->words * 4, st>>>(set->tab, d_hit_offsets + q0, nq, d_hits, capacity,

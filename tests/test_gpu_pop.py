@@ -305,11 +305,14 @@ def test_shard_set_order_ids_chunks_and_bad_bytes(popcase, engine, monkeypatch):
         assert rc == 9 and tot.value == want[1][-1] and np.array_equal(off, want[1]) and np.array_equal(hits, want[2][:10])
 
 
-@pytest.mark.parametrize("nshards", [3, 7, 13, 16, 17])
-def test_shard_set_of_few_shards(nshards, popcase, engine):
+@pytest.mark.parametrize("nshards,lanes", [(3, None), (7, None), (9, None), (13, None), (16, None), (17, None), (22, None),
+                                           (13, 1), (13, 4), (7, 32), (40, 16), (5, 2)])
+def test_shard_set_of_few_shards(nshards, lanes, popcase, engine, monkeypatch):
     """A rank of a multi-GPU job holds a few of the 64 shards: the gather kernel then works on several queries per warp
-    (8 or 16 lanes each).  Long k-mers (a few rows per shard: one lane per shard) and short ones (intervals of many rows:
-    the whole group reads one shard's rows)."""
+    (1..16 lanes each, picked from the number of shards; forced here as well).  Long k-mers (a few rows per shard: one
+    lane per shard) and short ones (intervals of many rows: the whole warp reads one shard's rows)."""
+    if lanes is not None:
+        monkeypatch.setenv("RS_B200_GATHER_LANES", str(lanes))
     order = [(5 * s + 2) % 64 for s in range(nshards)]
     with engine.ShardSet() as S:
         for s in order:
