@@ -40,6 +40,7 @@
  * region -- or the row is not on any read's walk)
  * ---------------------------------------------------------------------------------------------- */
 #define RS_RID_NONE 0xFFFFFFFFu
+#define RS_RID_FAIL 0xFFFFFFFEu /* pass 3 walked from the row: the walk ends nowhere (the hit is reported as 2^64-1) */
 
 /* pass 1: one walker per read from the row of its terminator (row i belongs to read i in builder input order);
  * every row it passes is stamped with i; term[i] = where the walk ended (lexicographic rank of the read) */
@@ -87,10 +88,39 @@ __global__ void k_rid_resolve(uint32_t* __restrict__ rid, uint64_t n, const uint
     uint32_t out = RS_RID_NONE;
     if (t < num_strings) {
       const uint64_t ri = sai[t];
-      if (ri < RS_RID_NONE) out = (uint32_t)ri;
+      if (ri < RS_RID_FAIL) out = (uint32_t)ri;
     }
     rid[r] = out;
   }
+}
+
+/* pass 3: the rows passes 1-2 left open (inside the reference's tail region walks join, get cut or wander, so a row
+ * there may be on no read's walk) are walked once here, exactly as the query-time fallback walks them
+ * (rs_pop_walk_one), and their answer is stored: a batch then never pays a 100-step walk by one lane while the
+ * other lanes of its warp wait (configs[2]: three of the 64 shards have such rows; the ranks holding them took 9-12 ms
+ * for the locate stage, the others 7.3).  A read index that does not fit the table stays RS_RID_NONE (walked per query). */
+__global__ void __launch_bounds__(256)
+    k_rid_fill(const __grid_constant__ rs_index_dev ix, const uint64_t* __restrict__ sai, uint32_t max_steps,
+               uint32_t* __restrict__ rid, unsigned long long* __restrict__ nfilled) {
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  uint32_t mine = 0;
+  for (uint64_t r = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; r < ix.n; r += stride) {
+    if (rid[r] != RS_RID_NONE) continue;
+    uint64_t idx = r, res = ~0ull;
+    for (uint32_t st = 0; st <= max_steps; ++st) {
+      uint64_t nxt;
+      const uint32_t sym = rs_lf_step(ix, idx, &nxt);
+      idx = nxt;
+      if (sym == 0) {
+        res = idx < ix.num_strings ? sai[idx] : ~0ull;
+        break;
+      }
+    }
+    if (res == ~0ull) rid[r] = RS_RID_FAIL;
+    else if (res < RS_RID_FAIL) rid[r] = (uint32_t)res;
+    ++mine;
+  }
+  if (nfilled && mine) atomicAdd(nfilled, (unsigned long long)mine);
 }
 
 /* per-read sample-set bitmaps (<= 128 samples): bit s of read r's 16 bytes = sample s carries the read */
@@ -288,6 +318,7 @@ __global__ void __launch_bounds__(256, RS_GATHER_BLOCKS)
         for (uint32_t j = 0; j < (uint32_t)c; ++j) {
           uint64_t r = rid[first + j];
           if (r == RS_RID_NONE) r = rs_pop_walk_one<G>(T.views, s, T.sai, first + j, T.max_steps);
+          else if (r == RS_RID_FAIL) r = ~0ull;
           if (mine + j < capacity) hits[mine + j] = r == ~0ull ? ~0ull : (tag | r);
           if (want_carriers && sets && r != ~0ull) {
             const uint4 v = __ldg(sets + r);
@@ -314,6 +345,7 @@ __global__ void __launch_bounds__(256, RS_GATHER_BLOCKS)
         for (uint64_t j = wlane; j < bc; j += 32) {
           uint64_t r = rid[bfirst + j];
           if (r == RS_RID_NONE) r = rs_pop_walk_one<G>(T.views, bs, T.sai, bfirst + j, T.max_steps);
+          else if (r == RS_RID_FAIL) r = ~0ull;
           if (bmine + j < capacity) bhits[bmine + j] = r == ~0ull ? ~0ull : (tag | r);
           if (want_carriers && sets && r != ~0ull) {
             const uint4 v = __ldg(sets + r);
@@ -641,6 +673,8 @@ int rs_shardset_seal(rs_shardset* set, uint32_t max_read_len, uint32_t locate_ev
         cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, set->device);
         k_rid_walk<<<grid_for(ns, RS_THREADS, sms * std::max(per_sm, 1)), RS_THREADS, 0, st>>>(v, max_read_len, set->d_rid[i], d_term);
         k_rid_resolve<<<grid_for(n, 256, 148 * 16), 256, 0, st>>>(set->d_rid[i], n, d_term, ix->d_sai, ns);
+        if (!getenv("RS_B200_NO_RID_FILL")) /* (tests compare the table with and without pass 3) */
+          k_rid_fill<<<grid_for(n, 256, 148 * 8), 256, 0, st>>>(v, ix->d_sai, max_read_len, set->d_rid[i], nullptr);
       }
       CU(cudaGetLastError());
       CU(cudaFreeAsync(d_term, st));

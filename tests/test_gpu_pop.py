@@ -327,9 +327,13 @@ def test_shard_set_of_few_shards(nshards, lanes, popcase, engine, monkeypatch):
         assert int(want[0].max()) > 8 * nshards  # the short k-mers do have long intervals
 
 
-def test_shard_set_under_the_reference_tail_behaviour(datasets, engine):
-    """A single shard whose tail region is NOT empty ('small': walks into it are cut or wander): the read-index table
-    leaves those rows uncovered and the pipeline walks them, ending where K2 and the oracle end."""
+@pytest.mark.parametrize("fill", [True, False])
+def test_shard_set_under_the_reference_tail_behaviour(fill, datasets, engine, monkeypatch):
+    """A single shard whose tail region is NOT empty ('small': walks into it are cut or wander): the reads' walks leave
+    those rows of the read-index table open; the seal walks them once (fill) or the pipeline walks them per query
+    (RS_B200_NO_RID_FILL), ending where K2 and the oracle end either way."""
+    if not fill:
+        monkeypatch.setenv("RS_B200_NO_RID_FILL", "1")
     case, P = datasets.case("small"), datasets.port("small")
     q = case.queries(4000, 20, seed=9)
     with engine.GpuBWT(runs=case.runs, num_strings=case.num_strings, num_symbols=case.num_symbols) as B:
