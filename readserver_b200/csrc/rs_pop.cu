@@ -158,13 +158,16 @@ __global__ void k_pop_revcomp(const uint64_t* __restrict__ in, uint32_t k, uint6
 
 /* per query of the chunk: population count and number of hits to report */
 __global__ void k_pop_totals(const uint32_t* __restrict__ cnt, uint32_t S, uint64_t C, uint64_t nq, uint64_t max_hits,
-                             uint64_t* __restrict__ counts, uint64_t* __restrict__ nhits, uint32_t* __restrict__ seg) {
+                             uint64_t* __restrict__ counts, uint64_t* __restrict__ nhits, uint32_t* __restrict__ seg,
+                             uint32_t* __restrict__ pass_off, uint32_t pass_shards) {
   const uint64_t q = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (q >= nq) return;
   uint64_t tot = 0, h = 0;
   for (uint32_t s = 0; s < S; ++s) {
     const uint64_t c = cnt[(uint64_t)s * C + q];
     if (seg) seg[(uint64_t)s * C + q] = (uint32_t)h; /* where shard s's hits start inside the query's slot */
+    /* ... and where the shards of a gather pass start (k_pop_gather runs pass by pass) */
+    if (pass_off && s % pass_shards == 0) pass_off[(uint64_t)(s / pass_shards) * C + q] = h > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)h;
     tot += c;
     h += c < max_hits ? c : max_hits;
   }
@@ -213,12 +216,13 @@ __device__ __forceinline__ uint32_t rs_owner_of(uint64_t pk, uint32_t k, bool, u
  * hits stored into the owner's per-rank table -- both straight into the owner's memory over NVLink */
 __global__ void k_pop_totals_comm(const __grid_constant__ rs_pop_peers P, const uint64_t* __restrict__ keys, uint32_t k,
                                   const uint32_t* __restrict__ cnt, uint32_t S, uint64_t C, uint64_t q0, uint64_t nq,
-                                  uint64_t max_hits, int want_hits) {
+                                  uint64_t max_hits, int want_hits, uint32_t* __restrict__ pass_off, uint32_t pass_shards) {
   const uint64_t q = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (q >= nq) return;
   uint64_t tot = 0, h = 0;
   for (uint32_t s = 0; s < S; ++s) {
     const uint64_t c = cnt[(uint64_t)s * C + q];
+    if (pass_off && s % pass_shards == 0) pass_off[(uint64_t)(s / pass_shards) * C + q] = h > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)h;
     tot += c;
     h += c < max_hits ? c : max_hits;
   }
@@ -255,6 +259,9 @@ __global__ void k_pop_owner_slots(const __grid_constant__ rs_pop_peers P, const 
  * the hit reads' sample sets when carrier sets are wanted (W = 4 words of 32 samples).  The hits go to the rank that
  * owns the query (P.world > 1: over NVLink peer memory, at the slot the owner assigned to this rank -- locate and the
  * fan-in of the hit lists, server.cpp:184-197, are one kernel), the sample set is OR-ed into the owner's bitmap. */
+#ifndef RS_POP_PASS_BYTES
+#define RS_POP_PASS_BYTES (32ull << 20)
+#endif
 #define RS_GATHER_LANE_ROWS 8u /* intervals up to this many rows are read by one lane; longer ones by the whole warp */
 #ifndef RS_GATHER_BLOCKS
 #define RS_GATHER_BLOCKS 4 /* resident CTAs per SM: the kernel waits on memory, occupancy is its parallelism */
@@ -281,7 +288,8 @@ __global__ void __launch_bounds__(256, RS_GATHER_BLOCKS)
     k_pop_gather(const __grid_constant__ rs_pop_tables T, const __grid_constant__ rs_pop_peers P,
                  const uint64_t* __restrict__ keys, uint32_t k, const uint64_t* __restrict__ lo,
                  const uint32_t* __restrict__ cnt, uint64_t C, uint64_t q0, uint64_t nq, uint64_t max_hits,
-                 const uint64_t* __restrict__ slot, uint64_t capacity, int want_carriers) {
+                 const uint64_t* __restrict__ slot, uint64_t capacity, int want_carriers, uint32_t s_begin,
+                 uint32_t s_end, const uint32_t* __restrict__ pass_off) {
   constexpr uint32_t QW = 32u / G; /* queries per warp */
   const uint32_t wlane = threadIdx.x & 31;
   const uint32_t lane = wlane & (G - 1u); /* lane within the query's group */
@@ -291,16 +299,16 @@ __global__ void __launch_bounds__(256, RS_GATHER_BLOCKS)
     const bool valid = q < nq;
     const uint32_t owner = (valid && P.world > 1) ? rs_owner_of(keys[q], k, false, P.world) : 0u;
     uint64_t* __restrict__ hits = P.hits[owner];
-    uint64_t off = valid ? slot[q0 + q] : 0;
+    uint64_t off = valid ? slot[q0 + q] + (pass_off ? (uint64_t)pass_off[q] : 0ull) : 0;
     uint32_t b0 = 0, b1 = 0, b2 = 0, b3 = 0;
     /* The table reads below are 4 and 16 bytes at random addresses, and HBM delivers whole 128-byte lines for them
      * (ncu on configs[2]: 247 GB of DRAM reads per 10 M-query step for 790 M hits = 1.9 G line fetches at 26 G lines/s,
      * the rate of the random-access probe); ld.global.cg instead of the L1 path made it slower (82 vs 73 ms).
      * A k-mer of a read set at 30x hits a handful of rows in most of the shards: the lanes take one shard each
      * (32 independent chains of loads in flight per warp), a scan over the group lays their rows out in shard order. */
-    for (uint32_t s0 = 0; s0 < T.nshards; s0 += G) {
+    for (uint32_t s0 = s_begin; s0 < s_end; s0 += G) {
       const uint32_t s = s0 + lane;
-      uint64_t c = (valid && s < T.nshards) ? cnt[(uint64_t)s * C + q] : 0;
+      uint64_t c = (valid && s < s_end) ? cnt[(uint64_t)s * C + q] : 0;
       if (c > max_hits) c = max_hits;
       uint64_t incl = c;
 #pragma unroll
@@ -377,7 +385,7 @@ __global__ void __launch_bounds__(256, RS_GATHER_BLOCKS)
       b3 = rs_group_or<G>(b3);
       if (valid) {
         uint32_t* dst = P.carr[owner] + (q0 + q) * 4;
-        if (P.world == 1) {
+        if (P.world == 1 && s_begin == 0) { /* the first pass stores, the others add */
           if (lane == 0) *reinterpret_cast<uint4*>(dst) = make_uint4(b0, b1, b2, b3);
         } else { /* several ranks contribute to one bitmap (cleared by its owner before the step) */
           for (uint32_t w = lane; w < 4; w += G) {
@@ -497,7 +505,7 @@ struct rs_shardset {
   /* per-call scratch, grown on demand; calls on one set are serialised */
   std::mutex mu;
   cudaStream_t stream = nullptr;
-  Scratch s_packed, s_lo, s_cnt, s_seg, s_nh, s_loc, s_scan, s_base, s_rows, s_dst, s_ri, s_in, s_lcnt;
+  Scratch s_pass, s_packed, s_lo, s_cnt, s_seg, s_nh, s_loc, s_scan, s_base, s_rows, s_dst, s_ri, s_in, s_lcnt;
   /* host-pointer calls: device-side result buffers, the copy-out stream, per-sub-batch events and hit-list marks */
   Scratch s_hc, s_ho, s_hh, s_hw, s_hm;
   cudaStream_t copy_stream = nullptr;
@@ -506,6 +514,7 @@ struct rs_shardset {
   uint64_t* d_stats = nullptr; /* executed updateInterval steps / LF steps of the set's calls (bench.py) */
   uint64_t chunk = 1u << 20;
   uint32_t gather_lanes = 32; /* lanes per query in the gather kernel (rs_gather_lanes; RS_B200_GATHER_LANES forces) */
+  uint32_t pass_shards = 0;   /* shards per gather pass (0 = all in one): a pass's sample-set tables fit L2 */
   bool chunk_forced = false; /* RS_B200_POP_CHUNK given */
   /* stage timing (bench.py: which kernel a step's time goes to): events recorded on the call's stream around the
    * stages of every chunk, read back -- and summed per stage -- by rs_shardset_read_timing */
@@ -602,7 +611,7 @@ void rs_shardset_destroy(rs_shardset* set) {
   cudaSetDevice(set->device);
   if (set->stream) cudaStreamSynchronize(set->stream);
   free_tables(set);
-  Scratch* all[] = {&set->s_packed, &set->s_lo, &set->s_cnt, &set->s_seg, &set->s_nh, &set->s_loc, &set->s_scan,
+  Scratch* all[] = {&set->s_pass, &set->s_packed, &set->s_lo, &set->s_cnt, &set->s_seg, &set->s_nh, &set->s_loc, &set->s_scan,
                     &set->s_base, &set->s_rows, &set->s_dst, &set->s_ri, &set->s_in, &set->s_lcnt,
                     &set->s_hc, &set->s_ho, &set->s_hh, &set->s_hw, &set->s_hm};
   for (Scratch* s : all) s->release();
@@ -744,7 +753,23 @@ int rs_shardset_seal(rs_shardset* set, uint32_t max_read_len, uint32_t locate_ev
   T.views = (const rs_index_dev*)put(views.data(), S * sizeof(rs_index_dev), 16);
   CU(cudaMemcpyAsync(set->d_tabmem, host.data(), bytes, cudaMemcpyHostToDevice, st));
   CU(cudaStreamSynchronize(st));
-  set->gather_lanes = rs_gather_lanes((uint32_t)set->shards.size());
+  /* Gather passes: the per-read sample-set tables are read at random (one 16-byte set per hit); when a rank's tables
+   * exceed what L2 keeps (configs[2] on one GPU: 177 MB over 64 shards) the gather runs over a few shards at a time so
+   * that a pass's tables stay L2-resident (RS_POP_PASS_BYTES; 8 shards = 22 MB there).  Power-of-two shard counts keep
+   * the lanes of a group on a shard each. */
+  set->pass_shards = 0;
+  if (set->have_sets && S > 8) {
+    uint64_t set_bytes = 0;
+    for (rs_index* ix : set->shards) set_bytes += ix->dev.num_strings * sizeof(uint4);
+    uint64_t budget = RS_POP_PASS_BYTES;
+    if (const char* e = getenv("RS_B200_POP_PASS_BYTES")) budget = (uint64_t)atoll(e); /* 0: one pass */
+    if (budget && set_bytes > budget) {
+      uint32_t ps = 32;
+      while (ps > 8 && set_bytes * ps / S > budget) ps >>= 1;
+      if (ps < S) set->pass_shards = ps;
+    }
+  }
+  set->gather_lanes = rs_gather_lanes(set->pass_shards ? set->pass_shards : (uint32_t)set->shards.size());
   if (const char* e = getenv("RS_B200_GATHER_LANES")) { /* experiments and tests: 1, 2, 4, 8, 16 or 32 */
     const long v = atol(e);
     if (v >= 1 && v <= 32 && (v & (v - 1)) == 0) set->gather_lanes = (uint32_t)v;
@@ -1010,6 +1035,10 @@ static int pop_run(rs_shardset* set, rs_popcomm* comm, const void* d_kmers, int 
   CU(rs_scan_bytes(C, &scan_bytes));
   CU(set->s_scan.need(scan_bytes ? scan_bytes : 8));
   if (want_hits && !table) CU(set->s_seg.need((size_t)S * C * 4));
+  const uint32_t pass_shards = (table && want_hits && d_carriers && set->pass_shards) ? set->pass_shards : 0;
+  const uint32_t npass = pass_shards ? (S + pass_shards - 1) / pass_shards : 1;
+  if (pass_shards) CU(set->s_pass.need((size_t)npass * C * 4));
+  uint32_t* pass_off = pass_shards ? (uint32_t*)set->s_pass.p : nullptr;
   uint64_t* lo = (uint64_t*)set->s_lo.p;
   uint32_t* cnt = (uint32_t*)set->s_cnt.p;
   uint64_t* nh = (uint64_t*)set->s_nh.p;
@@ -1052,10 +1081,10 @@ static int pop_run(rs_shardset* set, rs_popcomm* comm, const void* d_kmers, int 
     {
       StageTimer tm(set, st, RS_POP_STAGE_OFFSETS, want_hits ? 4 : 1);
       if (!multi) {
-        k_pop_totals<<<gq, 256, 0, st>>>(cnt, S, C, nq, max_hits, d_counts + q0, nh, seg);
+        k_pop_totals<<<gq, 256, 0, st>>>(cnt, S, C, nq, max_hits, d_counts + q0, nh, seg, pass_off, pass_shards);
       } else {
-        if (seg) k_pop_totals<<<gq, 256, 0, st>>>(cnt, S, C, nq, max_hits, loc /* unused sums */, nh, seg);
-        k_pop_totals_comm<<<gq, 256, 0, st>>>(P, keys + q0, (uint32_t)k, cnt, S, C, q0, nq, max_hits, want_hits ? 1 : 0);
+        if (seg) k_pop_totals<<<gq, 256, 0, st>>>(cnt, S, C, nq, max_hits, loc /* unused sums */, nh, seg, nullptr, 0);
+        k_pop_totals_comm<<<gq, 256, 0, st>>>(P, keys + q0, (uint32_t)k, cnt, S, C, q0, nq, max_hits, want_hits ? 1 : 0, pass_off, pass_shards);
       }
       CU(cudaGetLastError());
       if (!want_hits) continue;
@@ -1080,19 +1109,23 @@ static int pop_run(rs_shardset* set, rs_popcomm* comm, const void* d_kmers, int 
       continue;
     }
     const uint64_t* slot = P.slot[multi ? comm->rank : 0];
-    StageTimer tm_locate(set, st, RS_POP_STAGE_LOCATE, table ? 1 : 5 * S + 1);
+    StageTimer tm_locate(set, st, RS_POP_STAGE_LOCATE, table ? npass : 5 * S + 1);
     if (table) {
       const int wc = (want_carr && set->have_sets) ? 1 : 0;
       const int gg = 148 * 2 * RS_GATHER_BLOCKS;
-#define RS_GATHER(G) \
-  k_pop_gather<G><<<grid_for(nq * G, 256, gg), 256, 0, st>>>(set->tab, P, keys + q0, (uint32_t)k, lo, cnt, C, q0, nq, max_hits, slot, capacity, wc)
-      switch (set->gather_lanes) {
-        case 32: RS_GATHER(32); break;
-        case 16: RS_GATHER(16); break;
-        case 8: RS_GATHER(8); break;
-        case 4: RS_GATHER(4); break;
-        case 2: RS_GATHER(2); break;
-        default: RS_GATHER(1); break;
+#define RS_GATHER(G)                                                                                                       \
+  k_pop_gather<G><<<grid_for(nq * G, 256, gg), 256, 0, st>>>(set->tab, P, keys + q0, (uint32_t)k, lo, cnt, C, q0, nq, max_hits, \
+                                                             slot, capacity, wc, sb, se, pass_off ? pass_off + (size_t)ps * C : nullptr)
+      for (uint32_t ps = 0; ps < npass; ++ps) {
+        const uint32_t sb = pass_shards ? ps * pass_shards : 0, se = pass_shards ? std::min<uint32_t>(S, sb + pass_shards) : S;
+        switch (set->gather_lanes) {
+          case 32: RS_GATHER(32); break;
+          case 16: RS_GATHER(16); break;
+          case 8: RS_GATHER(8); break;
+          case 4: RS_GATHER(4); break;
+          case 2: RS_GATHER(2); break;
+          default: RS_GATHER(1); break;
+        }
       }
 #undef RS_GATHER
       CU(cudaGetLastError());

@@ -305,14 +305,18 @@ def test_shard_set_order_ids_chunks_and_bad_bytes(popcase, engine, monkeypatch):
         assert rc == 9 and tot.value == want[1][-1] and np.array_equal(off, want[1]) and np.array_equal(hits, want[2][:10])
 
 
-@pytest.mark.parametrize("nshards,lanes", [(3, None), (7, None), (9, None), (13, None), (16, None), (17, None), (22, None),
-                                           (13, 1), (13, 4), (7, 32), (40, 16), (5, 2)])
-def test_shard_set_of_few_shards(nshards, lanes, popcase, engine, monkeypatch):
+@pytest.mark.parametrize("nshards,lanes,pass_bytes", [
+    (3, None, None), (7, None, None), (9, None, None), (13, None, None), (16, None, None), (17, None, None), (22, None, None),
+    (13, 1, None), (13, 4, None), (7, 32, None), (40, 16, None), (5, 2, None),
+    (64, None, 1), (22, None, 1), (40, 4, 30000), (64, None, 0)])
+def test_shard_set_of_few_shards(nshards, lanes, pass_bytes, popcase, engine, monkeypatch):
     """A rank of a multi-GPU job holds a few of the 64 shards: the gather kernel then works on several queries per warp
     (1..16 lanes each, picked from the number of shards; forced here as well).  Long k-mers (a few rows per shard: one
     lane per shard) and short ones (intervals of many rows: the whole warp reads one shard's rows)."""
     if lanes is not None:
         monkeypatch.setenv("RS_B200_GATHER_LANES", str(lanes))
+    if pass_bytes is not None:  # the gather in passes of 8..32 shards whose sample-set tables fit this many bytes
+        monkeypatch.setenv("RS_B200_POP_PASS_BYTES", str(pass_bytes))
     order = [(5 * s + 2) % 64 for s in range(nshards)]
     with engine.ShardSet() as S:
         for s in order:
