@@ -259,6 +259,9 @@ __global__ void k_pop_owner_slots(const __grid_constant__ rs_pop_peers P, const 
  * the hit reads' sample sets when carrier sets are wanted (W = 4 words of 32 samples).  The hits go to the rank that
  * owns the query (P.world > 1: over NVLink peer memory, at the slot the owner assigned to this rank -- locate and the
  * fan-in of the hit lists, server.cpp:184-197, are one kernel), the sample set is OR-ed into the owner's bitmap. */
+#ifndef RS_POP_SHARD_MAJOR_MIN
+#define RS_POP_SHARD_MAJOR_MIN (1u << 17) /* queries per chunk from which the gather runs shard by shard */
+#endif
 #ifndef RS_POP_PASS_BYTES
 #define RS_POP_PASS_BYTES (32ull << 20)
 #endif
@@ -398,6 +401,149 @@ __global__ void __launch_bounds__(256, RS_GATHER_BLOCKS)
   }
 }
 
+/* Shard-major gather: ONE shard per launch, one lane per query.  The shard's read-index table (4 B per row: 70 MB on
+ * configs[2]) and its sample sets (3 MB) stay in L2 for the launch -- as the shard's rank blocks do for K1 -- so a hit
+ * costs an L2 sector instead of a 128-byte line from HBM; what streams from HBM is the launch's 28 bytes per query
+ * (count, first row, offsets), read coalesced.  A query's hits of this shard go to slot[q] + seg[q] (seg: the hits of
+ * the shards before this one, from k_pop_totals); its sample set is OR-ed into the chunk's bitmap by the lane that
+ * owns the query (launches follow each other on the stream: no atomics).  Intervals of many rows are read by the whole
+ * warp. */
+#ifndef RS_GATHER_SHARD_BLOCKS
+#define RS_GATHER_SHARD_BLOCKS 4
+#endif
+__global__ void __launch_bounds__(256, RS_GATHER_SHARD_BLOCKS)
+    k_pop_gather_shard(const __grid_constant__ rs_pop_tables T, const __grid_constant__ rs_pop_peers P, uint32_t s,
+                       const uint64_t* __restrict__ keys, uint32_t k, const uint64_t* __restrict__ lo_s,
+                       const uint32_t* __restrict__ cnt_s, const uint32_t* __restrict__ seg_s, uint64_t q0, uint64_t nq,
+                       uint64_t max_hits, const uint64_t* __restrict__ slot, uint64_t capacity, uint4* __restrict__ carr) {
+  const uint32_t wlane = threadIdx.x & 31;
+  const uint64_t nthreads = (uint64_t)gridDim.x * blockDim.x;
+  const uint32_t* __restrict__ rid = T.rid[s];
+  const uint4* __restrict__ sets = carr ? T.sets[s] : nullptr;
+  const uint64_t tag = T.tag[s];
+  const bool multi = P.world > 1;
+  /* the trip's streamed inputs are loaded one trip ahead (coalesced, whether or not the query has rows here): the
+   * dependent part of a trip is then two loads deep (row -> read index -> sample set), not four */
+  uint64_t qb = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) & ~31ull; /* warp-uniform */
+  uint64_t q = qb + wlane;
+  uint32_t nc = q < nq ? cnt_s[q] : 0;
+  uint64_t nfirst = q < nq ? lo_s[q] : 0, nmine = q < nq ? slot[q0 + q] + seg_s[q] : 0, nkey = (multi && q < nq) ? keys[q] : 0;
+  for (; qb < nq; qb += nthreads) {
+    q = qb + wlane;
+    uint64_t c = nc;
+    const uint64_t first = nfirst, mine = nmine, key = nkey;
+    {
+      const uint64_t qn = q + nthreads;
+      const bool in = qn < nq;
+      nc = in ? cnt_s[qn] : 0;
+      nfirst = in ? lo_s[qn] : 0;
+      nmine = in ? slot[q0 + qn] + seg_s[qn] : 0;
+      nkey = (multi && in) ? keys[qn] : 0;
+    }
+    if (c > max_hits) c = max_hits;
+    if (!__any_sync(RS_FULL, c != 0)) continue;
+    const uint32_t owner = (c && multi) ? rs_owner_of(key, k, false, P.world) : 0u;
+    uint64_t* __restrict__ hits = P.hits[owner];
+    uint32_t b0 = 0, b1 = 0, b2 = 0, b3 = 0;
+    bool open_rows = false;
+    if (c && c <= RS_GATHER_LANE_ROWS) {
+      for (uint32_t j0 = 0; j0 < (uint32_t)c; j0 += 4) { /* four rows at a time: their loads are in flight together */
+        uint32_t r4[4];
+#pragma unroll
+        for (uint32_t i = 0; i < 4; ++i) r4[i] = j0 + i < (uint32_t)c ? rid[first + j0 + i] : RS_RID_FAIL;
+        uint64_t r8[4];
+        uint4 v4[4];
+#pragma unroll
+        for (uint32_t i = 0; i < 4; ++i) {
+          r8[i] = r4[i] >= RS_RID_FAIL ? ~0ull : (uint64_t)r4[i];
+          open_rows |= r4[i] == RS_RID_NONE; /* redone below */
+          v4[i] = make_uint4(0, 0, 0, 0);
+          if (sets && r8[i] != ~0ull) v4[i] = __ldg(sets + r8[i]);
+        }
+#pragma unroll
+        for (uint32_t i = 0; i < 4; ++i) {
+          if (j0 + i < (uint32_t)c && mine + j0 + i < capacity) hits[mine + j0 + i] = r8[i] == ~0ull ? ~0ull : (tag | r8[i]);
+          b0 |= v4[i].x;
+          b1 |= v4[i].y;
+          b2 |= v4[i].z;
+          b3 |= v4[i].w;
+        }
+      }
+    }
+    if (open_rows) { /* rows the table leaves to a walk (a read index that does not fit it): rare, kept out of the loop above */
+      for (uint32_t j = 0; j < (uint32_t)c; ++j) {
+        if (rid[first + j] != RS_RID_NONE) continue;
+        const uint64_t r = rs_pop_walk_one<0>(T.views, s, T.sai, first + j, T.max_steps);
+        if (r == ~0ull) continue;
+        if (mine + j < capacity) hits[mine + j] = tag | r;
+        if (sets) {
+          const uint4 v = __ldg(sets + r);
+          b0 |= v.x;
+          b1 |= v.y;
+          b2 |= v.z;
+          b3 |= v.w;
+        }
+      }
+    }
+    uint32_t big = __ballot_sync(RS_FULL, c > RS_GATHER_LANE_ROWS);
+    while (big) {
+      const int src = __ffs((int)big) - 1;
+      big &= big - 1;
+      const uint64_t bc = __shfl_sync(RS_FULL, c, src), bfirst = __shfl_sync(RS_FULL, first, src),
+                     bmine = __shfl_sync(RS_FULL, mine, src);
+      uint64_t* __restrict__ bhits = P.hits[__shfl_sync(RS_FULL, owner, src)];
+      uint32_t t0 = 0, t1 = 0, t2 = 0, t3 = 0;
+      for (uint64_t j = wlane; j < bc; j += 32) {
+        uint64_t r = rid[bfirst + j];
+        if (r == RS_RID_NONE) r = rs_pop_walk_one<0>(T.views, s, T.sai, bfirst + j, T.max_steps);
+        else if (r == RS_RID_FAIL) r = ~0ull;
+        if (bmine + j < capacity) bhits[bmine + j] = r == ~0ull ? ~0ull : (tag | r);
+        if (sets && r != ~0ull) {
+          const uint4 v = __ldg(sets + r);
+          t0 |= v.x;
+          t1 |= v.y;
+          t2 |= v.z;
+          t3 |= v.w;
+        }
+      }
+      if (sets) {
+        t0 = __reduce_or_sync(RS_FULL, t0);
+        t1 = __reduce_or_sync(RS_FULL, t1);
+        t2 = __reduce_or_sync(RS_FULL, t2);
+        t3 = __reduce_or_sync(RS_FULL, t3);
+        if ((int)wlane == src) {
+          b0 |= t0;
+          b1 |= t1;
+          b2 |= t2;
+          b3 |= t3;
+        }
+      }
+    }
+    if (b0 | b1 | b2 | b3) {
+      uint4 v = carr[q];
+      v.x |= b0;
+      v.y |= b1;
+      v.z |= b2;
+      v.w |= b3;
+      carr[q] = v;
+    }
+  }
+}
+
+/* several GPUs: the chunk's locally united sample sets are OR-ed into the owners' bitmaps (cleared by them before the step) */
+__global__ void k_pop_carr_send(const __grid_constant__ rs_pop_peers P, const uint64_t* __restrict__ keys, uint32_t k,
+                                uint64_t q0, uint64_t nq, const uint4* __restrict__ carr) {
+  const uint64_t q = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (q >= nq) return;
+  const uint4 v = carr[q];
+  if (!(v.x | v.y | v.z | v.w)) return;
+  uint32_t* dst = P.carr[rs_owner_of(keys[q], k, false, P.world)] + (q0 + q) * 4;
+  if (v.x) atomicOr(dst + 0, v.x);
+  if (v.y) atomicOr(dst + 1, v.y);
+  if (v.z) atomicOr(dst + 2, v.z);
+  if (v.w) atomicOr(dst + 3, v.w);
+}
+
 /* lanes per query for a rank holding S shards: the largest power of two that keeps >= 85 % of the lane slots of a round
  * on a shard (S = 64, 32: 32; 16: 16; 8, 7: 8; 21, 22: 8; 9: 2; 1 lane always qualifies) */
 static uint32_t rs_gather_lanes(uint32_t S) {
@@ -505,7 +651,7 @@ struct rs_shardset {
   /* per-call scratch, grown on demand; calls on one set are serialised */
   std::mutex mu;
   cudaStream_t stream = nullptr;
-  Scratch s_pass, s_packed, s_lo, s_cnt, s_seg, s_nh, s_loc, s_scan, s_base, s_rows, s_dst, s_ri, s_in, s_lcnt;
+  Scratch s_carrl, s_pass, s_packed, s_lo, s_cnt, s_seg, s_nh, s_loc, s_scan, s_base, s_rows, s_dst, s_ri, s_in, s_lcnt;
   /* host-pointer calls: device-side result buffers, the copy-out stream, per-sub-batch events and hit-list marks */
   Scratch s_hc, s_ho, s_hh, s_hw, s_hm;
   cudaStream_t copy_stream = nullptr;
@@ -514,6 +660,7 @@ struct rs_shardset {
   uint64_t* d_stats = nullptr; /* executed updateInterval steps / LF steps of the set's calls (bench.py) */
   uint64_t chunk = 1u << 20;
   uint32_t gather_lanes = 32; /* lanes per query in the gather kernel (rs_gather_lanes; RS_B200_GATHER_LANES forces) */
+  int gather_mode = 0;        /* 0: by batch size; 1: query-major passes (k_pop_gather); 2: shard-major (k_pop_gather_shard) */
   uint32_t pass_shards = 0;   /* shards per gather pass (0 = all in one): a pass's sample-set tables fit L2 */
   bool chunk_forced = false; /* RS_B200_POP_CHUNK given */
   /* stage timing (bench.py: which kernel a step's time goes to): events recorded on the call's stream around the
@@ -611,7 +758,7 @@ void rs_shardset_destroy(rs_shardset* set) {
   cudaSetDevice(set->device);
   if (set->stream) cudaStreamSynchronize(set->stream);
   free_tables(set);
-  Scratch* all[] = {&set->s_pass, &set->s_packed, &set->s_lo, &set->s_cnt, &set->s_seg, &set->s_nh, &set->s_loc, &set->s_scan,
+  Scratch* all[] = {&set->s_carrl, &set->s_pass, &set->s_packed, &set->s_lo, &set->s_cnt, &set->s_seg, &set->s_nh, &set->s_loc, &set->s_scan,
                     &set->s_base, &set->s_rows, &set->s_dst, &set->s_ri, &set->s_in, &set->s_lcnt,
                     &set->s_hc, &set->s_ho, &set->s_hh, &set->s_hw, &set->s_hm};
   for (Scratch* s : all) s->release();
@@ -770,6 +917,8 @@ int rs_shardset_seal(rs_shardset* set, uint32_t max_read_len, uint32_t locate_ev
     }
   }
   set->gather_lanes = rs_gather_lanes(set->pass_shards ? set->pass_shards : (uint32_t)set->shards.size());
+  set->gather_mode = 0;
+  if (const char* e = getenv("RS_B200_GATHER_MODE")) set->gather_mode = !strcmp(e, "shard") ? 2 : !strcmp(e, "query") ? 1 : 0;
   if (const char* e = getenv("RS_B200_GATHER_LANES")) { /* experiments and tests: 1, 2, 4, 8, 16 or 32 */
     const long v = atol(e);
     if (v >= 1 && v <= 32 && (v & (v - 1)) == 0) set->gather_lanes = (uint32_t)v;
@@ -1034,8 +1183,12 @@ static int pop_run(rs_shardset* set, rs_popcomm* comm, const void* d_kmers, int 
   size_t scan_bytes = 0;
   CU(rs_scan_bytes(C, &scan_bytes));
   CU(set->s_scan.need(scan_bytes ? scan_bytes : 8));
-  if (want_hits && !table) CU(set->s_seg.need((size_t)S * C * 4));
-  const uint32_t pass_shards = (table && want_hits && d_carriers && set->pass_shards) ? set->pass_shards : 0;
+  /* large chunks: the gather goes shard by shard (tables L2-resident per launch); small ones: one launch, query-major */
+  const bool shard_major = table && want_hits && capacity && (!d_carriers || set->have_sets) &&
+                           (set->gather_mode == 2 || (set->gather_mode == 0 && C >= RS_POP_SHARD_MAJOR_MIN));
+  if (want_hits && (!table || shard_major)) CU(set->s_seg.need((size_t)S * C * 4));
+  if (shard_major && d_carriers && multi) CU(set->s_carrl.need(C * 16));
+  const uint32_t pass_shards = (table && !shard_major && want_hits && d_carriers && set->pass_shards) ? set->pass_shards : 0;
   const uint32_t npass = pass_shards ? (S + pass_shards - 1) / pass_shards : 1;
   if (pass_shards) CU(set->s_pass.need((size_t)npass * C * 4));
   uint32_t* pass_off = pass_shards ? (uint32_t*)set->s_pass.p : nullptr;
@@ -1044,7 +1197,7 @@ static int pop_run(rs_shardset* set, rs_popcomm* comm, const void* d_kmers, int 
   uint64_t* nh = (uint64_t*)set->s_nh.p;
   uint64_t* loc = (uint64_t*)set->s_loc.p;
   uint64_t* base = (uint64_t*)set->s_base.p;
-  uint32_t* seg = (want_hits && !table) ? (uint32_t*)set->s_seg.p : nullptr;
+  uint32_t* seg = (want_hits && (!table || shard_major)) ? (uint32_t*)set->s_seg.p : nullptr;
   /* where results go: own buffers (one GPU) or every rank's, through peer memory */
   rs_pop_peers P;
   if (multi) {
@@ -1109,8 +1262,20 @@ static int pop_run(rs_shardset* set, rs_popcomm* comm, const void* d_kmers, int 
       continue;
     }
     const uint64_t* slot = P.slot[multi ? comm->rank : 0];
-    StageTimer tm_locate(set, st, RS_POP_STAGE_LOCATE, table ? npass : 5 * S + 1);
-    if (table) {
+    StageTimer tm_locate(set, st, RS_POP_STAGE_LOCATE, shard_major ? S + 1 : table ? npass : 5 * S + 1);
+    if (shard_major) {
+      uint4* carr = nullptr;
+      if (want_carr) { /* the chunk's sets start empty: the launches OR into them */
+        carr = multi ? (uint4*)set->s_carrl.p : reinterpret_cast<uint4*>(d_carriers + q0 * 4);
+        CU(cudaMemsetAsync(carr, 0, nq * 16, st));
+      }
+      const int gs = grid_for(nq, 256, 148 * RS_GATHER_BLOCKS);
+      for (uint32_t sh = 0; sh < S; ++sh)
+        k_pop_gather_shard<<<gs, 256, 0, st>>>(set->tab, P, sh, keys + q0, (uint32_t)k, lo + (uint64_t)sh * C, cnt + (uint64_t)sh * C,
+                                               seg + (uint64_t)sh * C, q0, nq, max_hits, slot, capacity, carr);
+      if (carr && multi) k_pop_carr_send<<<gq, 256, 0, st>>>(P, keys + q0, (uint32_t)k, q0, nq, carr);
+      CU(cudaGetLastError());
+    } else if (table) {
       const int wc = (want_carr && set->have_sets) ? 1 : 0;
       const int gg = 148 * 2 * RS_GATHER_BLOCKS;
 #define RS_GATHER(G)                                                                                                       \

@@ -204,8 +204,10 @@ def popcase(engine):
     c.close()
 
 
-@pytest.mark.parametrize("locate_every", [1, 8, 0])
-def test_shard_set_count_locate_carriers_match_per_shard_oracles(locate_every, popcase, engine):
+@pytest.mark.parametrize("locate_every,mode", [(1, "query"), (1, "shard"), (8, None), (0, None)])
+def test_shard_set_count_locate_carriers_match_per_shard_oracles(locate_every, mode, popcase, engine, monkeypatch):
+    if mode:
+        monkeypatch.setenv("RS_B200_GATHER_MODE", mode)
     q = popcase.queries
     with engine.ShardSet() as S:
         for s, b in enumerate(popcase.gpu):
@@ -308,14 +310,17 @@ def test_shard_set_order_ids_chunks_and_bad_bytes(popcase, engine, monkeypatch):
 @pytest.mark.parametrize("nshards,lanes,pass_bytes", [
     (3, None, None), (7, None, None), (9, None, None), (13, None, None), (16, None, None), (17, None, None), (22, None, None),
     (13, 1, None), (13, 4, None), (7, 32, None), (40, 16, None), (5, 2, None),
-    (64, None, 1), (22, None, 1), (40, 4, 30000), (64, None, 0)])
+    (64, None, 1), (22, None, 1), (40, 4, 30000), (64, None, 0),
+    (64, None, "shard"), (9, None, "shard"), (1, None, "shard")])
 def test_shard_set_of_few_shards(nshards, lanes, pass_bytes, popcase, engine, monkeypatch):
     """A rank of a multi-GPU job holds a few of the 64 shards: the gather kernel then works on several queries per warp
     (1..16 lanes each, picked from the number of shards; forced here as well).  Long k-mers (a few rows per shard: one
     lane per shard) and short ones (intervals of many rows: the whole warp reads one shard's rows)."""
     if lanes is not None:
         monkeypatch.setenv("RS_B200_GATHER_LANES", str(lanes))
-    if pass_bytes is not None:  # the gather in passes of 8..32 shards whose sample-set tables fit this many bytes
+    if pass_bytes == "shard":   # the gather shard by shard, one lane per query (what large batches get)
+        monkeypatch.setenv("RS_B200_GATHER_MODE", "shard")
+    elif pass_bytes is not None:  # the gather in passes of 8..32 shards whose sample-set tables fit this many bytes
         monkeypatch.setenv("RS_B200_POP_PASS_BYTES", str(pass_bytes))
     order = [(5 * s + 2) % 64 for s in range(nshards)]
     with engine.ShardSet() as S:
@@ -338,6 +343,7 @@ def test_shard_set_under_the_reference_tail_behaviour(fill, datasets, engine, mo
     (RS_B200_NO_RID_FILL), ending where K2 and the oracle end either way."""
     if not fill:
         monkeypatch.setenv("RS_B200_NO_RID_FILL", "1")
+        monkeypatch.setenv("RS_B200_GATHER_MODE", "shard")   # (the walk fallback of the shard-major kernel)
     case, P = datasets.case("small"), datasets.port("small")
     q = case.queries(4000, 20, seed=9)
     with engine.GpuBWT(runs=case.runs, num_strings=case.num_strings, num_symbols=case.num_symbols) as B:
@@ -373,8 +379,8 @@ def test_shard_set_argument_errors(popcase, engine):
             S.query(np.zeros((2, 40), dtype=np.uint8) + 65, 40)   # k > 31
 
 
-@pytest.mark.parametrize("locate_every,world", [(1, 3), (0, 2)])
-def test_multi_rank_fan_in_through_peer_memory(locate_every, world):
+@pytest.mark.parametrize("locate_every,world,mode", [(1, 3, "query"), (1, 2, "shard"), (0, 2, None)])
+def test_multi_rank_fan_in_through_peer_memory(locate_every, world, mode):
     """The whole multi-GPU protocol with `world` PROCESSES (tests/pop_worker.py): CUDA IPC mapping of every rank's result
     buffers, counts added into the owner's buffer, hit numbers, slots assigned by the owner, read indices written into
     the owner's list, sample sets OR-ed into the owner's bitmap, flag barriers in between.  The ranks use GPU
@@ -389,7 +395,7 @@ def test_multi_rank_fan_in_through_peer_memory(locate_every, world):
     procs = []
     for r in range(world):
         env = dict(os.environ, RANK=str(r), WORLD_SIZE=str(world), MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port),
-                   RS_B200_POP_CHUNK="1024")
+                   RS_B200_POP_CHUNK="1024", **({"RS_B200_GATHER_MODE": mode} if mode else {}))
         procs.append(subprocess.Popen([sys.executable, os.path.join(common.ROOT, "tests", "pop_worker.py"), str(locate_every)],
                                       env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True))
     outs = []
