@@ -74,6 +74,9 @@ cudaError_t rs_launch_extract_postfix(const rs_index_dev& ix, const uint64_t* ro
 cudaError_t rs_build_dense(const rs_index_dev& ix, uint64_t ndense, void* out, unsigned int* bad, cudaStream_t st);
 
 /* rs_pipeline.cu */
+cudaError_t rs_sort_pairs_bytes(uint64_t n, size_t* bytes);
+cudaError_t rs_sort_pairs(const uint64_t* keys_in, uint64_t* keys_out, const uint32_t* vals_in, uint32_t* vals_out,
+                          uint64_t n, int end_bit, void* tmp, size_t tmp_bytes, cudaStream_t st);
 cudaError_t rs_scan_bytes(uint64_t n, size_t* bytes);
 cudaError_t rs_exclusive_scan(const uint64_t* counts, uint64_t* offsets, uint64_t n, void* tmp, size_t tmp_bytes,
                               cudaStream_t st);

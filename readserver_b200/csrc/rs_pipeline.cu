@@ -6,6 +6,7 @@
  */
 #include "rs_kernels.h"
 
+#include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
 
 /* counts[q] = rows of interval q, capped at max_hits (count_reads' count, service.cpp:304) */
@@ -41,6 +42,19 @@ cudaError_t rs_scan_bytes(uint64_t n, size_t* bytes) {
 cudaError_t rs_exclusive_scan(const uint64_t* counts, uint64_t* offsets, uint64_t n, void* tmp, size_t tmp_bytes,
                               cudaStream_t st) {
   return cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, counts, offsets, n + 1, st);
+}
+
+/* (key, value) pairs sorted by bits [0, end_bit) of the key: the shard set sorts a batch's packed k-mers (first base
+ * most significant = the order of their BWT intervals) so that the locate stage reads each read-index table in
+ * ascending row order */
+cudaError_t rs_sort_pairs_bytes(uint64_t n, size_t* bytes) {
+  *bytes = 0;
+  return cub::DeviceRadixSort::SortPairs(nullptr, *bytes, (const uint64_t*)nullptr, (uint64_t*)nullptr,
+                                         (const uint32_t*)nullptr, (uint32_t*)nullptr, n, 0, 64);
+}
+cudaError_t rs_sort_pairs(const uint64_t* keys_in, uint64_t* keys_out, const uint32_t* vals_in, uint32_t* vals_out,
+                          uint64_t n, int end_bit, void* tmp, size_t tmp_bytes, cudaStream_t st) {
+  return cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys_in, keys_out, vals_in, vals_out, n, 0, end_bit, st);
 }
 
 cudaError_t rs_launch_hit_counts(const uint64_t* lower, const uint64_t* upper, uint64_t Q, uint64_t max_hits,

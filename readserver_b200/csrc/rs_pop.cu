@@ -159,7 +159,7 @@ __global__ void k_pop_revcomp(const uint64_t* __restrict__ in, uint32_t k, uint6
 /* per query of the chunk: population count and number of hits to report */
 __global__ void k_pop_totals(const uint32_t* __restrict__ cnt, uint32_t S, uint64_t C, uint64_t nq, uint64_t max_hits,
                              uint64_t* __restrict__ counts, uint64_t* __restrict__ nhits, uint32_t* __restrict__ seg,
-                             uint32_t* __restrict__ pass_off, uint32_t pass_shards) {
+                             uint32_t* __restrict__ pass_off, uint32_t pass_shards, const uint32_t* __restrict__ perm) {
   const uint64_t q = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (q >= nq) return;
   uint64_t tot = 0, h = 0;
@@ -171,8 +171,9 @@ __global__ void k_pop_totals(const uint32_t* __restrict__ cnt, uint32_t S, uint6
     tot += c;
     h += c < max_hits ? c : max_hits;
   }
-  counts[q] = tot;
-  nhits[q] = h;
+  const uint64_t qo = perm ? perm[q] : q; /* sorted batch: the answers go to the query's place in the caller's order */
+  counts[qo] = tot;
+  nhits[qo] = h;
 }
 
 /* hit_offsets[q] = base + local offset; the running base advances by the chunk's hits */
@@ -216,7 +217,8 @@ __device__ __forceinline__ uint32_t rs_owner_of(uint64_t pk, uint32_t k, bool, u
  * hits stored into the owner's per-rank table -- both straight into the owner's memory over NVLink */
 __global__ void k_pop_totals_comm(const __grid_constant__ rs_pop_peers P, const uint64_t* __restrict__ keys, uint32_t k,
                                   const uint32_t* __restrict__ cnt, uint32_t S, uint64_t C, uint64_t q0, uint64_t nq,
-                                  uint64_t max_hits, int want_hits, uint32_t* __restrict__ pass_off, uint32_t pass_shards) {
+                                  uint64_t max_hits, int want_hits, uint32_t* __restrict__ pass_off, uint32_t pass_shards,
+                                  const uint32_t* __restrict__ perm) {
   const uint64_t q = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (q >= nq) return;
   uint64_t tot = 0, h = 0;
@@ -227,8 +229,9 @@ __global__ void k_pop_totals_comm(const __grid_constant__ rs_pop_peers P, const 
     h += c < max_hits ? c : max_hits;
   }
   const uint32_t owner = rs_owner_of(keys[q], k, false, P.world);
-  if (tot) atomicAdd(reinterpret_cast<unsigned long long*>(P.counts[owner]) + q0 + q, (unsigned long long)tot);
-  if (want_hits) P.rankh[owner][(uint64_t)P.rank * P.maxq + q0 + q] = h > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)h;
+  const uint64_t qo = q0 + (perm ? perm[q] : q);
+  if (tot) atomicAdd(reinterpret_cast<unsigned long long*>(P.counts[owner]) + qo, (unsigned long long)tot);
+  if (want_hits) P.rankh[owner][(uint64_t)P.rank * P.maxq + qo] = h > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)h;
 }
 
 /* owner: hits of each query it owns, summed over the source ranks (0 for the queries of other owners) */
@@ -532,16 +535,33 @@ __global__ void __launch_bounds__(256, RS_GATHER_SHARD_BLOCKS)
 
 /* several GPUs: the chunk's locally united sample sets are OR-ed into the owners' bitmaps (cleared by them before the step) */
 __global__ void k_pop_carr_send(const __grid_constant__ rs_pop_peers P, const uint64_t* __restrict__ keys, uint32_t k,
-                                uint64_t q0, uint64_t nq, const uint4* __restrict__ carr) {
+                                uint64_t q0, uint64_t nq, const uint4* __restrict__ carr, const uint32_t* __restrict__ perm) {
   const uint64_t q = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (q >= nq) return;
   const uint4 v = carr[q];
   if (!(v.x | v.y | v.z | v.w)) return;
-  uint32_t* dst = P.carr[rs_owner_of(keys[q], k, false, P.world)] + (q0 + q) * 4;
+  uint32_t* dst = P.carr[rs_owner_of(keys[q], k, false, P.world)] + (q0 + (perm ? perm[q] : q)) * 4;
   if (v.x) atomicOr(dst + 0, v.x);
   if (v.y) atomicOr(dst + 1, v.y);
   if (v.z) atomicOr(dst + 2, v.z);
   if (v.w) atomicOr(dst + 3, v.w);
+}
+
+/* sorted batch: 0, 1, 2, ... (the values the sort carries along); where each sorted query's hits start; the sample
+ * sets back in the caller's order */
+__global__ void k_pop_iota(uint32_t* __restrict__ out, uint64_t n) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = (uint32_t)i;
+}
+__global__ void k_pop_slot_sorted(const uint64_t* __restrict__ slot, const uint32_t* __restrict__ perm, uint64_t n,
+                                  uint64_t* __restrict__ out) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = slot[perm[i]];
+}
+__global__ void k_pop_carr_unsort(const uint4* __restrict__ carr, const uint32_t* __restrict__ perm, uint64_t n,
+                                  uint4* __restrict__ out) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[perm[i]] = carr[i];
 }
 
 /* lanes per query for a rank holding S shards: the largest power of two that keeps >= 85 % of the lane slots of a round
@@ -651,7 +671,7 @@ struct rs_shardset {
   /* per-call scratch, grown on demand; calls on one set are serialised */
   std::mutex mu;
   cudaStream_t stream = nullptr;
-  Scratch s_carrl, s_pass, s_packed, s_lo, s_cnt, s_seg, s_nh, s_loc, s_scan, s_base, s_rows, s_dst, s_ri, s_in, s_lcnt;
+  Scratch s_sort, s_skeys, s_perm, s_iota, s_sslot, s_carrl, s_pass, s_packed, s_lo, s_cnt, s_seg, s_nh, s_loc, s_scan, s_base, s_rows, s_dst, s_ri, s_in, s_lcnt;
   /* host-pointer calls: device-side result buffers, the copy-out stream, per-sub-batch events and hit-list marks */
   Scratch s_hc, s_ho, s_hh, s_hw, s_hm;
   cudaStream_t copy_stream = nullptr;
@@ -660,6 +680,7 @@ struct rs_shardset {
   uint64_t* d_stats = nullptr; /* executed updateInterval steps / LF steps of the set's calls (bench.py) */
   uint64_t chunk = 1u << 20;
   uint32_t gather_lanes = 32; /* lanes per query in the gather kernel (rs_gather_lanes; RS_B200_GATHER_LANES forces) */
+  bool sort_batches = true;   /* RS_B200_POP_SORT=0 turns the sorted batch off */
   int gather_mode = 0;        /* 0: by batch size; 1: query-major passes (k_pop_gather); 2: shard-major (k_pop_gather_shard) */
   uint32_t pass_shards = 0;   /* shards per gather pass (0 = all in one): a pass's sample-set tables fit L2 */
   bool chunk_forced = false; /* RS_B200_POP_CHUNK given */
@@ -758,7 +779,7 @@ void rs_shardset_destroy(rs_shardset* set) {
   cudaSetDevice(set->device);
   if (set->stream) cudaStreamSynchronize(set->stream);
   free_tables(set);
-  Scratch* all[] = {&set->s_carrl, &set->s_pass, &set->s_packed, &set->s_lo, &set->s_cnt, &set->s_seg, &set->s_nh, &set->s_loc, &set->s_scan,
+  Scratch* all[] = {&set->s_sort, &set->s_skeys, &set->s_perm, &set->s_iota, &set->s_sslot, &set->s_carrl, &set->s_pass, &set->s_packed, &set->s_lo, &set->s_cnt, &set->s_seg, &set->s_nh, &set->s_loc, &set->s_scan,
                     &set->s_base, &set->s_rows, &set->s_dst, &set->s_ri, &set->s_in, &set->s_lcnt,
                     &set->s_hc, &set->s_ho, &set->s_hh, &set->s_hw, &set->s_hm};
   for (Scratch* s : all) s->release();
@@ -917,6 +938,8 @@ int rs_shardset_seal(rs_shardset* set, uint32_t max_read_len, uint32_t locate_ev
     }
   }
   set->gather_lanes = rs_gather_lanes(set->pass_shards ? set->pass_shards : (uint32_t)set->shards.size());
+  set->sort_batches = true;
+  if (const char* e = getenv("RS_B200_POP_SORT")) set->sort_batches = atoi(e) != 0;
   set->gather_mode = 0;
   if (const char* e = getenv("RS_B200_GATHER_MODE")) set->gather_mode = !strcmp(e, "shard") ? 2 : !strcmp(e, "query") ? 1 : 0;
   if (const char* e = getenv("RS_B200_GATHER_LANES")) { /* experiments and tests: 1, 2, 4, 8, 16 or 32 */
@@ -1187,7 +1210,31 @@ static int pop_run(rs_shardset* set, rs_popcomm* comm, const void* d_kmers, int 
   const bool shard_major = table && want_hits && capacity && (!d_carriers || set->have_sets) &&
                            (set->gather_mode == 2 || (set->gather_mode == 0 && C >= RS_POP_SHARD_MAJOR_MIN));
   if (want_hits && (!table || shard_major)) CU(set->s_seg.need((size_t)S * C * 4));
-  if (shard_major && d_carriers && multi) CU(set->s_carrl.need(C * 16));
+  /* Sorted batch (a shard-major gather over the whole batch in one chunk): the packed k-mers are sorted -- first base
+   * most significant, which is the order of their intervals in every shard's BWT -- and searched in that order, so the
+   * gather of a shard reads its read-index table in ascending row order (streaming instead of one DRAM line per hit)
+   * and neighbouring lanes of K1 end in neighbouring blocks.  Answers go to the queries' places in the caller's order
+   * through the permutation the sort carries along. */
+  const bool sorted = shard_major && set->sort_batches && Q <= C && Q > 1 && Q < (1ull << 32);
+  if (shard_major && d_carriers && (multi || sorted)) CU(set->s_carrl.need(C * 16));
+  const uint32_t* perm = nullptr;
+  const uint64_t* ksearch = keys; /* what K1 and the gather index by position in their launch */
+  if (sorted) {
+    size_t sort_bytes = 0;
+    CU(rs_sort_pairs_bytes(Q, &sort_bytes));
+    CU(set->s_sort.need(sort_bytes ? sort_bytes : 8));
+    CU(set->s_skeys.need(Q * 8));
+    CU(set->s_perm.need(Q * 4));
+    CU(set->s_iota.need(Q * 4));
+    CU(set->s_sslot.need(Q * 8));
+    StageTimer tm(set, st, RS_POP_STAGE_PACK, 2);
+    k_pop_iota<<<(unsigned)((Q + 255) / 256), 256, 0, st>>>((uint32_t*)set->s_iota.p, Q);
+    CU(cudaGetLastError());
+    CU(rs_sort_pairs(keys, (uint64_t*)set->s_skeys.p, (const uint32_t*)set->s_iota.p, (uint32_t*)set->s_perm.p, Q, 2 * k,
+                     set->s_sort.p, sort_bytes, st));
+    perm = (const uint32_t*)set->s_perm.p;
+    ksearch = (const uint64_t*)set->s_skeys.p;
+  }
   const uint32_t pass_shards = (table && !shard_major && want_hits && d_carriers && set->pass_shards) ? set->pass_shards : 0;
   const uint32_t npass = pass_shards ? (S + pass_shards - 1) / pass_shards : 1;
   if (pass_shards) CU(set->s_pass.need((size_t)npass * C * 4));
@@ -1228,16 +1275,17 @@ static int pop_run(rs_shardset* set, rs_popcomm* comm, const void* d_kmers, int 
       CU(rs_ticket_take(S, &tickets, st));
       StageTimer tm(set, st, RS_POP_STAGE_SEARCH, S);
       for (uint32_t s = 0; s < S; ++s)
-        CU(rs_launch_find_interval_packed(set->shards[s]->dev, keys + q0, (uint32_t)k, nq, lo + (uint64_t)s * C,
+        CU(rs_launch_find_interval_packed(set->shards[s]->dev, ksearch + q0, (uint32_t)k, nq, lo + (uint64_t)s * C,
                                           cnt + (uint64_t)s * C, 4, (unsigned long long*)set->d_stats, st, nullptr, tickets + s));
     }
     {
       StageTimer tm(set, st, RS_POP_STAGE_OFFSETS, want_hits ? 4 : 1);
       if (!multi) {
-        k_pop_totals<<<gq, 256, 0, st>>>(cnt, S, C, nq, max_hits, d_counts + q0, nh, seg, pass_off, pass_shards);
+        k_pop_totals<<<gq, 256, 0, st>>>(cnt, S, C, nq, max_hits, d_counts + q0, nh, seg, pass_off, pass_shards, perm);
       } else {
-        if (seg) k_pop_totals<<<gq, 256, 0, st>>>(cnt, S, C, nq, max_hits, loc /* unused sums */, nh, seg, nullptr, 0);
-        k_pop_totals_comm<<<gq, 256, 0, st>>>(P, keys + q0, (uint32_t)k, cnt, S, C, q0, nq, max_hits, want_hits ? 1 : 0, pass_off, pass_shards);
+        if (seg) k_pop_totals<<<gq, 256, 0, st>>>(cnt, S, C, nq, max_hits, loc /* unused sums */, nh, seg, nullptr, 0, nullptr);
+        k_pop_totals_comm<<<gq, 256, 0, st>>>(P, ksearch + q0, (uint32_t)k, cnt, S, C, q0, nq, max_hits, want_hits ? 1 : 0, pass_off,
+                                              pass_shards, perm);
       }
       CU(cudaGetLastError());
       if (!want_hits) continue;
@@ -1262,18 +1310,23 @@ static int pop_run(rs_shardset* set, rs_popcomm* comm, const void* d_kmers, int 
       continue;
     }
     const uint64_t* slot = P.slot[multi ? comm->rank : 0];
-    StageTimer tm_locate(set, st, RS_POP_STAGE_LOCATE, shard_major ? S + 1 : table ? npass : 5 * S + 1);
+    StageTimer tm_locate(set, st, RS_POP_STAGE_LOCATE, shard_major ? S + 3 : table ? npass : 5 * S + 1);
     if (shard_major) {
       uint4* carr = nullptr;
       if (want_carr) { /* the chunk's sets start empty: the launches OR into them */
-        carr = multi ? (uint4*)set->s_carrl.p : reinterpret_cast<uint4*>(d_carriers + q0 * 4);
+        carr = (multi || sorted) ? (uint4*)set->s_carrl.p : reinterpret_cast<uint4*>(d_carriers + q0 * 4);
         CU(cudaMemsetAsync(carr, 0, nq * 16, st));
+      }
+      if (sorted) { /* q0 = 0: where the hits of the i-th query in sorted order start */
+        k_pop_slot_sorted<<<gq, 256, 0, st>>>(slot, perm, nq, (uint64_t*)set->s_sslot.p);
+        slot = (const uint64_t*)set->s_sslot.p;
       }
       const int gs = grid_for(nq, 256, 148 * RS_GATHER_BLOCKS);
       for (uint32_t sh = 0; sh < S; ++sh)
-        k_pop_gather_shard<<<gs, 256, 0, st>>>(set->tab, P, sh, keys + q0, (uint32_t)k, lo + (uint64_t)sh * C, cnt + (uint64_t)sh * C,
+        k_pop_gather_shard<<<gs, 256, 0, st>>>(set->tab, P, sh, ksearch + q0, (uint32_t)k, lo + (uint64_t)sh * C, cnt + (uint64_t)sh * C,
                                                seg + (uint64_t)sh * C, q0, nq, max_hits, slot, capacity, carr);
-      if (carr && multi) k_pop_carr_send<<<gq, 256, 0, st>>>(P, keys + q0, (uint32_t)k, q0, nq, carr);
+      if (carr && multi) k_pop_carr_send<<<gq, 256, 0, st>>>(P, ksearch + q0, (uint32_t)k, q0, nq, carr, perm);
+      else if (carr && sorted) k_pop_carr_unsort<<<gq, 256, 0, st>>>(carr, perm, nq, reinterpret_cast<uint4*>(d_carriers));
       CU(cudaGetLastError());
     } else if (table) {
       const int wc = (want_carr && set->have_sets) ? 1 : 0;

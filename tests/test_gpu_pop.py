@@ -311,15 +311,17 @@ def test_shard_set_order_ids_chunks_and_bad_bytes(popcase, engine, monkeypatch):
     (3, None, None), (7, None, None), (9, None, None), (13, None, None), (16, None, None), (17, None, None), (22, None, None),
     (13, 1, None), (13, 4, None), (7, 32, None), (40, 16, None), (5, 2, None),
     (64, None, 1), (22, None, 1), (40, 4, 30000), (64, None, 0),
-    (64, None, "shard"), (9, None, "shard"), (1, None, "shard")])
+    (64, None, "shard"), (9, None, "shard"), (1, None, "shard"), (64, None, "shard-unsorted")])
 def test_shard_set_of_few_shards(nshards, lanes, pass_bytes, popcase, engine, monkeypatch):
     """A rank of a multi-GPU job holds a few of the 64 shards: the gather kernel then works on several queries per warp
     (1..16 lanes each, picked from the number of shards; forced here as well).  Long k-mers (a few rows per shard: one
     lane per shard) and short ones (intervals of many rows: the whole warp reads one shard's rows)."""
     if lanes is not None:
         monkeypatch.setenv("RS_B200_GATHER_LANES", str(lanes))
-    if pass_bytes == "shard":   # the gather shard by shard, one lane per query (what large batches get)
-        monkeypatch.setenv("RS_B200_GATHER_MODE", "shard")
+    if pass_bytes in ("shard", "shard-unsorted"):   # the gather shard by shard, one lane per query, over the sorted batch
+        monkeypatch.setenv("RS_B200_GATHER_MODE", "shard")   # (what large batches get)
+        if pass_bytes == "shard-unsorted":
+            monkeypatch.setenv("RS_B200_POP_SORT", "0")
     elif pass_bytes is not None:  # the gather in passes of 8..32 shards whose sample-set tables fit this many bytes
         monkeypatch.setenv("RS_B200_POP_PASS_BYTES", str(pass_bytes))
     order = [(5 * s + 2) % 64 for s in range(nshards)]
@@ -379,8 +381,9 @@ def test_shard_set_argument_errors(popcase, engine):
             S.query(np.zeros((2, 40), dtype=np.uint8) + 65, 40)   # k > 31
 
 
-@pytest.mark.parametrize("locate_every,world,mode", [(1, 3, "query"), (1, 2, "shard"), (0, 2, None)])
-def test_multi_rank_fan_in_through_peer_memory(locate_every, world, mode):
+@pytest.mark.parametrize("locate_every,world,mode,chunk", [(1, 3, "query", "1024"), (1, 2, "shard", "1024"),
+                                                          (1, 3, "shard", None), (0, 2, None, "1024")])
+def test_multi_rank_fan_in_through_peer_memory(locate_every, world, mode, chunk):
     """The whole multi-GPU protocol with `world` PROCESSES (tests/pop_worker.py): CUDA IPC mapping of every rank's result
     buffers, counts added into the owner's buffer, hit numbers, slots assigned by the owner, read indices written into
     the owner's list, sample sets OR-ed into the owner's bitmap, flag barriers in between.  The ranks use GPU
@@ -395,7 +398,8 @@ def test_multi_rank_fan_in_through_peer_memory(locate_every, world, mode):
     procs = []
     for r in range(world):
         env = dict(os.environ, RANK=str(r), WORLD_SIZE=str(world), MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port),
-                   RS_B200_POP_CHUNK="1024", **({"RS_B200_GATHER_MODE": mode} if mode else {}))
+                   **({"RS_B200_POP_CHUNK": chunk} if chunk else {}),   # None: one chunk, so the batch is sorted
+                   **({"RS_B200_GATHER_MODE": mode} if mode else {}))
         procs.append(subprocess.Popen([sys.executable, os.path.join(common.ROOT, "tests", "pop_worker.py"), str(locate_every)],
                                       env=env, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True))
     outs = []
