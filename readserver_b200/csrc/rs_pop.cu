@@ -404,13 +404,36 @@ __global__ void __launch_bounds__(256, RS_GATHER_BLOCKS)
   }
 }
 
-/* Shard-major gather: ONE shard per launch, one lane per query.  The shard's read-index table (4 B per row: 70 MB on
- * configs[2]) and its sample sets (3 MB) stay in L2 for the launch -- as the shard's rank blocks do for K1 -- so a hit
- * costs an L2 sector instead of a 128-byte line from HBM; what streams from HBM is the launch's 28 bytes per query
- * (count, first row, offsets), read coalesced.  A query's hits of this shard go to slot[q] + seg[q] (seg: the hits of
- * the shards before this one, from k_pop_totals); its sample set is OR-ed into the chunk's bitmap by the lane that
- * owns the query (launches follow each other on the stream: no atomics).  Intervals of many rows are read by the whole
- * warp. */
+/* cold path of the shard-major gather: the rows of this lane's interval that the table leaves to a walk */
+__device__ __noinline__ void rs_gather_open_rows(const rs_pop_tables& T, uint32_t s, const uint32_t* __restrict__ rid,
+                                                 const uint4* __restrict__ sets, uint64_t tag, uint32_t c, uint64_t first,
+                                                 uint64_t* __restrict__ dst, uint32_t* bm) {
+  for (uint32_t j = 0; j < c; ++j) {
+    if (rid[first + j] != RS_RID_NONE) continue;
+    const uint64_t r = rs_pop_walk_one<0>(T.views, s, T.sai, first + j, T.max_steps);
+    if (r == ~0ull) continue; /* the hot loop stored 2^64-1 */
+    dst[j] = tag | r;
+    if (sets) {
+      const uint4 v = __ldg(sets + r);
+      bm[0] |= v.x;
+      bm[1] |= v.y;
+      bm[2] |= v.z;
+      bm[3] |= v.w;
+    }
+  }
+}
+
+/* Shard-major gather: ONE shard per launch.  A warp takes 32 consecutive queries of the (sorted) chunk per trip: their
+ * counts, first rows and destinations are read coalesced (28 bytes per query, streamed), then the rows of all 32
+ * intervals together are dealt out to the lanes -- hit h of the trip to lane h mod 32, its query found by a search
+ * over the warp's running sum in shared memory -- so a trip costs ceil(hits / 32) rounds of
+ * row -> read index -> sample set -> store, whatever the split of the hits over the queries (one lane per query ran
+ * as many rounds as the longest interval of the 32, with the other lanes masked: ncu showed 13 of 32 lanes active and
+ * 414 warp instructions per trip).  An interval of a million rows is simply 31 k rounds of coalesced reads.  A query's
+ * hits of this shard go to slot[q] + seg[q] (seg: the hits of the shards before this one, from k_pop_totals); sample
+ * sets are OR-ed per query in shared memory, then into the chunk's bitmap by the lane that owns the query (launches
+ * follow each other on the stream: no global atomics).  With a sorted batch the rows of successive queries ascend, so
+ * the read-index table streams through L2 once per launch. */
 #ifndef RS_GATHER_SHARD_BLOCKS
 #define RS_GATHER_SHARD_BLOCKS 4
 #endif
@@ -419,117 +442,94 @@ __global__ void __launch_bounds__(256, RS_GATHER_SHARD_BLOCKS)
                        const uint64_t* __restrict__ keys, uint32_t k, const uint64_t* __restrict__ lo_s,
                        const uint32_t* __restrict__ cnt_s, const uint32_t* __restrict__ seg_s, uint64_t q0, uint64_t nq,
                        uint64_t max_hits, const uint64_t* __restrict__ slot, uint64_t capacity, uint4* __restrict__ carr) {
-  const uint32_t wlane = threadIdx.x & 31;
+  __shared__ uint64_t sh_incl[8][32];  /* running sum of the trip's counts */
+  __shared__ uint64_t sh_first[8][32]; /* first row of each query's interval */
+  __shared__ uint64_t sh_dst[8][32];   /* address of each query's first hit in its owner's list */
+  __shared__ uint32_t sh_bm[8][32][4]; /* sample sets of the trip's queries */
+  const uint32_t wlane = threadIdx.x & 31, w = threadIdx.x >> 5;
   const uint64_t nthreads = (uint64_t)gridDim.x * blockDim.x;
   const uint32_t* __restrict__ rid = T.rid[s];
   const uint4* __restrict__ sets = carr ? T.sets[s] : nullptr;
   const uint64_t tag = T.tag[s];
   const bool multi = P.world > 1;
-  /* the trip's streamed inputs are loaded one trip ahead (coalesced, whether or not the query has rows here): the
-   * dependent part of a trip is then two loads deep (row -> read index -> sample set), not four */
-  uint64_t qb = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) & ~31ull; /* warp-uniform */
-  uint64_t q = qb + wlane;
-  uint32_t nc = q < nq ? cnt_s[q] : 0;
-  uint64_t nfirst = q < nq ? lo_s[q] : 0, nmine = q < nq ? slot[q0 + q] + seg_s[q] : 0, nkey = (multi && q < nq) ? keys[q] : 0;
-  for (; qb < nq; qb += nthreads) {
-    q = qb + wlane;
-    uint64_t c = nc;
-    const uint64_t first = nfirst, mine = nmine, key = nkey;
-    {
-      const uint64_t qn = q + nthreads;
-      const bool in = qn < nq;
-      nc = in ? cnt_s[qn] : 0;
-      nfirst = in ? lo_s[qn] : 0;
-      nmine = in ? slot[q0 + qn] + seg_s[qn] : 0;
-      nkey = (multi && in) ? keys[qn] : 0;
-    }
+  for (uint64_t qb = ((uint64_t)blockIdx.x * blockDim.x + threadIdx.x) & ~31ull; qb < nq; qb += nthreads) { /* warp-uniform */
+    const uint64_t q = qb + wlane;
+    uint64_t c = q < nq ? cnt_s[q] : 0;
     if (c > max_hits) c = max_hits;
     if (!__any_sync(RS_FULL, c != 0)) continue;
-    const uint32_t owner = (c && multi) ? rs_owner_of(key, k, false, P.world) : 0u;
-    uint64_t* __restrict__ hits = P.hits[owner];
-    uint32_t b0 = 0, b1 = 0, b2 = 0, b3 = 0;
+    const uint64_t first = c ? lo_s[q] : 0;
+    const uint64_t mine = c ? slot[q0 + q] + seg_s[q] : 0;
+    const uint32_t owner = (c && multi) ? rs_owner_of(keys[q], k, false, P.world) : 0u;
+    if (mine >= capacity) c = 0;                       /* nothing of it can be reported */
+    else if (c > capacity - mine) c = capacity - mine; /* the list ends inside the interval */
+    uint64_t incl = c;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) {
+      const uint64_t t = __shfl_up_sync(RS_FULL, incl, d);
+      if ((int)wlane >= d) incl += t;
+    }
+    const uint64_t total = __shfl_sync(RS_FULL, incl, 31);
+    sh_incl[w][wlane] = incl;
+    sh_first[w][wlane] = first;
+    sh_dst[w][wlane] = (uint64_t)(uintptr_t)(P.hits[owner] + mine);
+    if (sets) *reinterpret_cast<uint4*>(sh_bm[w][wlane]) = make_uint4(0, 0, 0, 0);
+    __syncwarp();
     bool open_rows = false;
-    if (c && c <= RS_GATHER_LANE_ROWS) {
-      for (uint32_t j0 = 0; j0 < (uint32_t)c; j0 += 4) { /* four rows at a time: their loads are in flight together */
-        uint32_t r4[4];
+    for (uint64_t hb = 0; hb < total; hb += 32) {
+      const uint64_t h = hb + wlane;
+      const bool live = h < total;
+      uint32_t l = 0; /* the query hit h belongs to: the first whose running sum exceeds h */
+      uint4 sv = make_uint4(0, 0, 0, 0);
+      if (live) {
 #pragma unroll
-        for (uint32_t i = 0; i < 4; ++i) r4[i] = j0 + i < (uint32_t)c ? rid[first + j0 + i] : RS_RID_FAIL;
-        uint64_t r8[4];
-        uint4 v4[4];
-#pragma unroll
-        for (uint32_t i = 0; i < 4; ++i) {
-          r8[i] = r4[i] >= RS_RID_FAIL ? ~0ull : (uint64_t)r4[i];
-          open_rows |= r4[i] == RS_RID_NONE; /* redone below */
-          v4[i] = make_uint4(0, 0, 0, 0);
-          if (sets && r8[i] != ~0ull) v4[i] = __ldg(sets + r8[i]);
-        }
-#pragma unroll
-        for (uint32_t i = 0; i < 4; ++i) {
-          if (j0 + i < (uint32_t)c && mine + j0 + i < capacity) hits[mine + j0 + i] = r8[i] == ~0ull ? ~0ull : (tag | r8[i]);
-          b0 |= v4[i].x;
-          b1 |= v4[i].y;
-          b2 |= v4[i].z;
-          b3 |= v4[i].w;
-        }
-      }
-    }
-    if (open_rows) { /* rows the table leaves to a walk (a read index that does not fit it): rare, kept out of the loop above */
-      for (uint32_t j = 0; j < (uint32_t)c; ++j) {
-        if (rid[first + j] != RS_RID_NONE) continue;
-        const uint64_t r = rs_pop_walk_one<0>(T.views, s, T.sai, first + j, T.max_steps);
-        if (r == ~0ull) continue;
-        if (mine + j < capacity) hits[mine + j] = tag | r;
-        if (sets) {
-          const uint4 v = __ldg(sets + r);
-          b0 |= v.x;
-          b1 |= v.y;
-          b2 |= v.z;
-          b3 |= v.w;
-        }
-      }
-    }
-    uint32_t big = __ballot_sync(RS_FULL, c > RS_GATHER_LANE_ROWS);
-    while (big) {
-      const int src = __ffs((int)big) - 1;
-      big &= big - 1;
-      const uint64_t bc = __shfl_sync(RS_FULL, c, src), bfirst = __shfl_sync(RS_FULL, first, src),
-                     bmine = __shfl_sync(RS_FULL, mine, src);
-      uint64_t* __restrict__ bhits = P.hits[__shfl_sync(RS_FULL, owner, src)];
-      uint32_t t0 = 0, t1 = 0, t2 = 0, t3 = 0;
-      for (uint64_t j = wlane; j < bc; j += 32) {
-        uint64_t r = rid[bfirst + j];
-        if (r == RS_RID_NONE) r = rs_pop_walk_one<0>(T.views, s, T.sai, bfirst + j, T.max_steps);
-        else if (r == RS_RID_FAIL) r = ~0ull;
-        if (bmine + j < capacity) bhits[bmine + j] = r == ~0ull ? ~0ull : (tag | r);
-        if (sets && r != ~0ull) {
-          const uint4 v = __ldg(sets + r);
-          t0 |= v.x;
-          t1 |= v.y;
-          t2 |= v.z;
-          t3 |= v.w;
-        }
+        for (uint32_t step = 16; step; step >>= 1)
+          if (sh_incl[w][l + step - 1] <= h) l += step;
+        const uint64_t j = h - (l ? sh_incl[w][l - 1] : 0ull);
+        const uint32_t v = rid[sh_first[w][l] + j];
+        open_rows |= v == RS_RID_NONE; /* left to a walk: redone below */
+        reinterpret_cast<uint64_t*>((uintptr_t)sh_dst[w][l])[j] = v >= RS_RID_FAIL ? ~0ull : (tag | v);
+        if (sets && v < RS_RID_FAIL) sv = __ldg(sets + v);
       }
       if (sets) {
-        t0 = __reduce_or_sync(RS_FULL, t0);
-        t1 = __reduce_or_sync(RS_FULL, t1);
-        t2 = __reduce_or_sync(RS_FULL, t2);
-        t3 = __reduce_or_sync(RS_FULL, t3);
-        if ((int)wlane == src) {
-          b0 |= t0;
-          b1 |= t1;
-          b2 |= t2;
-          b3 |= t3;
+        __syncwarp();
+        const uint32_t l0 = __shfl_sync(RS_FULL, l, 0);
+        if (__all_sync(RS_FULL, !live || l == l0)) { /* one interval fills the round: one OR for the warp */
+          sv.x = __reduce_or_sync(RS_FULL, sv.x);
+          sv.y = __reduce_or_sync(RS_FULL, sv.y);
+          sv.z = __reduce_or_sync(RS_FULL, sv.z);
+          sv.w = __reduce_or_sync(RS_FULL, sv.w);
+          if (wlane == 0) {
+            sh_bm[w][l0][0] |= sv.x;
+            sh_bm[w][l0][1] |= sv.y;
+            sh_bm[w][l0][2] |= sv.z;
+            sh_bm[w][l0][3] |= sv.w;
+          }
+          __syncwarp();
+        } else {
+          if (sv.x) atomicOr(&sh_bm[w][l][0], sv.x);
+          if (sv.y) atomicOr(&sh_bm[w][l][1], sv.y);
+          if (sv.z) atomicOr(&sh_bm[w][l][2], sv.z);
+          if (sv.w) atomicOr(&sh_bm[w][l][3], sv.w);
         }
       }
     }
-    if (b0 | b1 | b2 | b3) {
-      uint4 v = carr[q];
-      v.x |= b0;
-      v.y |= b1;
-      v.z |= b2;
-      v.w |= b3;
-      carr[q] = v;
+    __syncwarp();
+    if (__any_sync(RS_FULL, open_rows)) /* rows whose read index does not fit the table: walked, one lane per query */
+      rs_gather_open_rows(T, s, rid, sets, tag, (uint32_t)c, first, reinterpret_cast<uint64_t*>((uintptr_t)sh_dst[w][wlane]),
+                          sh_bm[w][wlane]);
+    if (sets) {
+      __syncwarp();
+      const uint4 b = *reinterpret_cast<const uint4*>(sh_bm[w][wlane]);
+      if (b.x | b.y | b.z | b.w) {
+        uint4 v = carr[q];
+        v.x |= b.x;
+        v.y |= b.y;
+        v.z |= b.z;
+        v.w |= b.w;
+        carr[q] = v;
+      }
     }
+    __syncwarp(); /* the next trip rewrites the shared arrays */
   }
 }
 
