@@ -134,8 +134,13 @@ __device__ __forceinline__ void rs_emit(int mode, uint64_t* __restrict__ lower, 
     upper[q] = hi;
   } else if (mode == 4) { /* shard set (rs_pop.cu): first row and number of rows, 12 bytes per shard-query */
     const uint64_t cnt = hi >= lo ? hi - lo + 1 : 0;
+#ifndef RS_K1_NO_STREAM_OUT /* written once, read once by another kernel: not worth an L2 line the rank blocks could hold */
+    __stcs(reinterpret_cast<unsigned long long*>(lower) + q, (unsigned long long)lo);
+    __stcs(reinterpret_cast<uint32_t*>(upper) + q, cnt > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)cnt);
+#else
     lower[q] = lo;
     reinterpret_cast<uint32_t*>(upper)[q] = cnt > 0xFFFFFFFFull ? 0xFFFFFFFFu : (uint32_t)cnt;
+#endif
   } else {
     const uint64_t cnt = hi >= lo ? hi - lo + 1 : 0;
     if (mode == 1) lower[q] = cnt;
@@ -379,7 +384,8 @@ __global__ void __launch_bounds__(RS_THREADS, RS_K1D_BLOCKS)
               j = (int32_t)k - 2;
               if (FTAB && k >= ix.ftab_k) {
                 const uint32_t t = ix.ftab_k;
-                const ulonglong2 e = __ldg(reinterpret_cast<const ulonglong2*>(ix.ftab) + (pk & ((1ull << (2 * t)) - 1)));
+                ulonglong2 e;
+                rs_ftab_load(ix, pk & ((1ull << (2 * t)) - 1), (uint64_t*)&e.x, (uint64_t*)&e.y);
                 lo = (P)e.x;
                 hi = (P)e.y; /* 2^64-1 becomes NONE */
                 j = (int32_t)k - (int32_t)t - 1;

@@ -155,6 +155,27 @@ struct rs_dblk {
   uint32_t cnt[4], p0[4], p1[4], p2[4];
 };
 
+/* entry `idx` of the k-mer suffix table (lower, upper) */
+RS_HD void rs_ftab_load(const rs_index_dev& ix, uint64_t idx, uint64_t* lo, uint64_t* hi) {
+#if defined(__CUDA_ARCH__) && !defined(RS_FTAB_NO_EVICT_FIRST)
+  /* one look-up per query at a random place of a table several times the size of L2: its lines are not worth keeping
+   * (the eviction priority exists for 256-bit loads only: the entry's 32-byte sector is read, the entry picked) */
+  unsigned long long a, b, c, d;
+  asm("ld.global.nc.L2::evict_first.v4.u64 {%0,%1,%2,%3}, [%4];"
+      : "=l"(a), "=l"(b), "=l"(c), "=l"(d)
+      : "l"(__cvta_generic_to_global(reinterpret_cast<const uint8_t*>(ix.ftab) + (idx >> 1) * 32)));
+  *lo = (idx & 1) ? c : a;
+  *hi = (idx & 1) ? d : b;
+#elif defined(__CUDA_ARCH__)
+  const ulonglong2 e = __ldg(reinterpret_cast<const ulonglong2*>(ix.ftab) + idx);
+  *lo = e.x;
+  *hi = e.y;
+#else
+  *lo = ix.ftab[2 * idx];
+  *hi = ix.ftab[2 * idx + 1];
+#endif
+}
+
 RS_HD rs_dblk rs_load_dense(const rs_index_dev& ix, uint64_t b) {
   const uint8_t* p = reinterpret_cast<const uint8_t*>(ix.dense) + b * 64;
   rs_dblk k;
@@ -162,10 +183,15 @@ RS_HD rs_dblk rs_load_dense(const rs_index_dev& ix, uint64_t b) {
   /* two 256-bit loads (LDG.E.256 on sm_100a) instead of four 128-bit ones: every load instruction of a warp whose
    * lanes sit on different blocks costs one L1 tag look-up per lane, and K1 over dense blocks is bound by exactly
    * that (ncu: l1tex throughput 91 % with four loads per block) */
-  asm("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+#ifdef RS_DENSE_EVICT_LAST
+#define RS_DENSE_LD "ld.global.nc.L2::evict_last.v8.u32"
+#else
+#define RS_DENSE_LD "ld.global.nc.v8.u32"
+#endif
+  asm(RS_DENSE_LD " {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
       : "=r"(k.cnt[0]), "=r"(k.cnt[1]), "=r"(k.cnt[2]), "=r"(k.cnt[3]), "=r"(k.p0[0]), "=r"(k.p0[1]), "=r"(k.p0[2]), "=r"(k.p0[3])
       : "l"(__cvta_generic_to_global(p)));
-  asm("ld.global.nc.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
+  asm(RS_DENSE_LD " {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];"
       : "=r"(k.p1[0]), "=r"(k.p1[1]), "=r"(k.p1[2]), "=r"(k.p1[3]), "=r"(k.p2[0]), "=r"(k.p2[1]), "=r"(k.p2[2]), "=r"(k.p2[3])
       : "l"(__cvta_generic_to_global(p + 32)));
   return k;
