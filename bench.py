@@ -65,7 +65,9 @@ def parse():
     ap.add_argument("--cpu-seconds", type=float, default=15.0, help="target CPU time of the cpu_baseline sample")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-side", action="store_true", help="skip the side measurements (configs[1] count line, roofline probe)")
-    ap.add_argument("--workload", default="configs2", choices=["configs2", "configs4", "configs1"],
+    ap.add_argument("--c3-symbols", type=int, default=9_000_000_000, help="configs3: symbols per shard")
+    ap.add_argument("--c3-shards", type=int, default=NSHARDS, help="configs3: shards in the collection (64; fewer for trials)")
+    ap.add_argument("--workload", default="configs2", choices=["configs2", "configs4", "configs1", "configs3"],
                     help="configs2 (default, the metric's): 10 M 31-mers, forward strand.  configs4: variant-allele probes over "
                          "the same population -- --sites sites of its list, the reference- and the alternative-allele 31-mer "
                          "centred on each, both strands -> read indices -> carrier sets")
@@ -831,6 +833,279 @@ def run_ours(args):
 _REAL_STDOUT = sys.stdout
 
 
+# ------------------------------------------------------------------------------------------------
+# configs[3]: a run-level collection far larger than anything derivable from reads here
+# ------------------------------------------------------------------------------------------------
+def run_configs3(args):
+    """BASELINE.json configs[3] (SURVEY.md 8(d) "Config 4"): 64 shards drawn at the run level -- run symbol and length
+    following the table measured on a real configs[2]-style shard -- of --c3-symbols symbols each, 64 / N shards per GPU
+    (9e9 symbols = 9.6 GB of run blocks + rank blocks + tables per shard: 77 GB per GPU at N = 8); count + locate (LF
+    walks) of --queries 31-mers, 90 % of them read off the shards' own LF walks, answers fanned in to the k-mers'
+    owners over NVLink peer memory as in configs[2].  Parity: a slice shard of 1 % the size, same generator, loaded into
+    the reference's CPU code (oracle/_ref) and into the engine on rank 0."""
+    import torch
+    import torch.distributed as dist
+    rank, local_rank, world = dist_env()
+    assert torch.cuda.is_available(), "bench.py needs a CUDA device (there is no CPU path)"
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=torch.device(f"cuda:{local_rank}"))
+    torch.cuda.set_device(local_rank)
+    dev = f"cuda:{local_rank}"
+    from readserver_b200 import datagen as dg, engine, sharding
+    Q, k = args.queries, args.k
+    max_steps = args.read_len + 28
+    nshards = args.c3_shards
+
+    # the run table: one shard of a small population with configs[2]'s samples, coverage and read length
+    t0 = time.time()
+    pop = dg.make_population(2_000_000, args.samples, seed=4, device=dev)
+    keys, _ = dg.population_read_keys(pop, args.coverage, args.read_len, seed=41)
+    real = dg.build_population_shard(pop, keys, 0, args.read_len).built
+    table = dg.run_table(real.runs).cpu()
+    mean_run = float(real.num_symbols) / max(1, real.runs.numel())
+    del pop, keys, real
+    torch.cuda.empty_cache()
+
+    # this rank's shards
+    my_shards = [s for s in range(nshards) if s % world == rank]
+    gpu, sizes = {}, {}
+    for s in my_shards:
+        runs, nstr, nsym = dg.runlevel_shard(table, args.c3_symbols, seed=6000 + s, device=dev)
+        B = engine.GpuBWT(runs=runs, num_strings=nstr, num_symbols=nsym, device=local_rank)
+        B.set_sai(torch.arange(nstr, dtype=torch.int64, device=dev))
+        sizes[s] = dict(symbols=nsym, runs=int(runs.numel()), strings=nstr, hbm_bytes=int(B.info.hbm_bytes))
+        gpu[s] = B
+        del runs
+        torch.cuda.empty_cache()
+    torch.cuda.synchronize()
+    load_s = time.time() - t0
+
+    # queries: 90 % read off LF walks from random rows of the shards (every rank contributes its share), 10 % random
+    stream = torch.cuda.current_stream().cuda_stream
+    share = (int(0.9 * Q) + world - 1) // world
+    got = []
+    g = torch.Generator(device=dev)
+    g.manual_seed(500 + rank)
+    need, walk_len = share, 200
+    while need > 0:
+        for s in my_shards:
+            m = int(need / len(my_shards) / 0.55) + 1024
+            rows = torch.randint(0, sizes[s]["symbols"], (m,), generator=g, device=dev, dtype=torch.int64)
+            bases = torch.zeros((m, walk_len), dtype=torch.uint8, device=dev)
+            steps = torch.zeros(m, dtype=torch.int32, device=dev)
+            gpu[s].extract_prefix_dev(rows, m, walk_len, None, steps, None, bases, stream)
+            torch.cuda.synchronize()
+            ok = (steps >= k) & (steps <= walk_len)
+            idx = torch.nonzero(ok).squeeze(1)
+            st = steps[idx].to(torch.int64)
+            cols = (st - k).unsqueeze(1) + torch.arange(k, device=dev).unsqueeze(0)   # the k characters next to the row
+            got.append(torch.gather(bases[idx], 1, cols))
+            del rows, bases, steps
+        have = sum(int(x.shape[0]) for x in got)
+        need = share - have
+    present = torch.cat(got)[:share].contiguous()
+    del got
+    if world > 1:
+        parts = [torch.empty_like(present) for _ in range(world)]
+        dist.all_gather(parts, present)
+        present = torch.cat(parts)
+    present = present[: int(0.9 * Q)]
+    gq = torch.Generator(device=dev)
+    gq.manual_seed(77)
+    rnd = torch.tensor(list(b"ACGT"), dtype=torch.uint8, device=dev)[
+        torch.randint(0, 4, (Q - present.shape[0], k), generator=gq, device=dev)]
+    dq = torch.cat([present, rnd])
+    dq = dq[torch.randperm(Q, generator=gq, device=dev)].contiguous()   # the same batch on every rank
+    del present, rnd
+    torch.cuda.empty_cache()
+    # shard set (plain LF walks: the locate tables of shards this size take minutes to build), sizing pass, communicator
+    S = engine.ShardSet(local_rank)
+    for s_ in my_shards:
+        S.add(gpu[s_], s_)
+    info = S.seal(max_steps, 0)
+    S.enable_stats(True)
+    l_counts = torch.empty(Q, dtype=torch.int64, device=dev)
+    l_off = torch.empty(Q + 1, dtype=torch.int64, device=dev)
+    d_total = torch.zeros(1, dtype=torch.int64, device=dev)
+    S.query_dev(dq, k, Q, False, MAX_HITS, l_counts, l_off, None, 0, None, d_total, stream)
+    torch.cuda.synchronize()
+    local_hits = int(d_total.item())
+    th = torch.tensor([local_hits], dtype=torch.int64, device=dev)
+    if world > 1:
+        dist.all_reduce(th)
+    total_hits = int(th.item())
+    comm = None
+    if world > 1:
+        cap = int(total_hits / world * 1.3) + (1 << 20)
+        comm = sharding.connect_peers(engine.PopComm(local_rank, rank, world, Q, cap), dev)
+    else:
+        cap = max(total_hits, 1)
+        o_counts = torch.empty(Q, dtype=torch.int64, device=dev)
+        o_off = torch.empty(Q + 1, dtype=torch.int64, device=dev)
+        o_hits = torch.empty(cap, dtype=torch.int64, device=dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)
+
+    def step():
+        if world > 1:
+            comm.query_dev(S, dq, k, Q, False, MAX_HITS, True, False, stream)
+        else:
+            S.query_dev(dq, k, Q, False, MAX_HITS, o_counts, o_off, o_hits, cap, None, d_total, stream)
+
+    for _ in range(max(3, args.warmup)):
+        step()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+        assert not comm.timed_out(), "peer barrier timed out"
+    S.read_stats(reset=True)
+    S.enable_timing(True)
+    clocks = ClockSampler(local_rank)
+    clocks.start()
+    evs = []
+    for _ in range(args.steps):
+        flush.fill_(1)
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        step()
+        e1.record()
+        evs.append((e0, e1))
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    clk = clocks.stop()
+    stage_ms, stage_launches = S.read_timing()
+    S.enable_timing(False)
+    interval_steps, walk_steps, block_loads = S.read_stats(reset=True)
+    tms = torch.tensor([sum(a.elapsed_time(b) for a, b in evs)], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+    total_ms = float(tms.item())
+
+    # checks at full size: what the owners hold = the sum of the ranks' own answers; the k-mers read off the walks are found
+    if world > 1:
+        res = comm.results(Q, dev)
+        own = torch.from_numpy(sharding.owner_of(dq.cpu().numpy(), world)).to(dev) == rank
+        sums = l_counts.clone()
+        dist.all_reduce(sums)
+        hsum = (l_off[1:] - l_off[:-1]).clone()
+        dist.all_reduce(hsum)
+        ok = bool(torch.equal(res["counts"][:Q][own], sums[own]))
+        ro = res["hit_offsets"][: Q + 1]
+        ok = ok and bool(torch.equal((ro[1:] - ro[:-1])[own], hsum[own]))
+        okt = torch.tensor([int(ok)], device=dev)
+        dist.all_reduce(okt, op=dist.ReduceOp.MIN)
+        fan_in_ok = bool(okt.item())
+        found = int((sums > 0).sum().item())
+        index_bytes = torch.tensor([int(info.index_bytes)], dtype=torch.int64, device=dev)
+        allb = [torch.zeros_like(index_bytes) for _ in range(world)]
+        dist.all_gather(allb, index_bytes)
+        index_bytes_by_rank = [int(x.item()) for x in allb]
+        per = [None] * world
+        dist.all_gather_object(per, {s_: round(v / args.steps, 3) for s_, v in stage_ms.items()})
+    else:
+        fan_in_ok = None
+        found = int((o_counts > 0).sum().item())
+        assert torch.equal(o_counts, l_counts)
+        index_bytes_by_rank = [int(info.index_bytes)]
+        per = None
+    assert fan_in_ok is not False, "results fanned in through peer memory differ from the ranks' own answers"
+    # parity slice (rank 0): a shard of 1 % the size from the same generator, in the reference's CPU code and in the engine
+    slice_line = None
+    if rank == 0 and not args.no_cpu_baseline:
+        import oracle
+        nsl = max(2_000_000, args.c3_symbols // 100)
+        runs, nstr, nsym = dg.runlevel_shard(table, nsl, seed=6999, device=dev)
+        with tempfile.TemporaryDirectory() as d:
+            path = os.path.join(d, "slice.bwt")
+            dg.write_bwt(path, runs.cpu(), nstr, nsym)
+            ref = oracle.open_best(path)
+        Bs = engine.GpuBWT(runs=runs, num_strings=nstr, num_symbols=nsym, device=local_rank)
+        Bs.set_sai(torch.arange(nstr, dtype=torch.int64, device=dev))
+        m = 200_000
+        rows = torch.randint(0, nsym, (m,), generator=g, device=dev, dtype=torch.int64)
+        bases = torch.zeros((m, 200), dtype=torch.uint8, device=dev)
+        steps = torch.zeros(m, dtype=torch.int32, device=dev)
+        Bs.extract_prefix_dev(rows, m, 200, None, steps, None, bases, stream)
+        torch.cuda.synchronize()
+        idx = torch.nonzero((steps >= k) & (steps <= 200)).squeeze(1)[:50_000]
+        cols = (steps[idx].to(torch.int64) - k).unsqueeze(1) + torch.arange(k, device=dev).unsqueeze(0)
+        qs = torch.cat([torch.gather(bases[idx], 1, cols), dq[:50_000]]).cpu().numpy()
+        with engine.ShardSet(local_rank) as Ss:
+            Ss.add(Bs, 0)
+            Ss.seal(max_steps, 0)
+            got = Ss.query(qs, k, max_hits=MAX_HITS)
+        nthreads = os.cpu_count() or 1
+        lo, up = ref.find_interval_batch(qs, k, nthreads=nthreads)
+        secs = ref.last_seconds
+        c = np.where(up >= lo, np.minimum(up - lo + 1, MAX_HITS), 0).astype(np.int64)
+        rws = (np.repeat(lo, c) + (np.arange(int(c.sum()), dtype=np.int64) - np.repeat(np.cumsum(c) - c, c)).astype(np.uint64))
+        lex, _, _, _ = ref.locate_batch(rws.astype(np.uint64), nthreads=nthreads, prefix=True, postfix=False, max_steps=max_steps)
+        secs += ref.last_seconds
+        want_hits = np.where(lex < nstr, lex, np.iinfo(np.uint64).max)   # shard id 0, .sai = identity
+        slice_line = {
+            "symbols": nsym, "runs": int(runs.numel()), "queries": int(qs.shape[0]), "hits": int(c.sum()),
+            "counts_equal": bool(np.array_equal(got["counts"], c.astype(np.uint64))),
+            "read_indices_equal": bool(np.array_equal(got["hits"], want_hits)),
+            "reference": {"kind": ref.kind, "queries_per_s": qs.shape[0] / max(secs, 1e-9), "threads": nthreads}}
+        assert slice_line["counts_equal"] and slice_line["read_indices_equal"], slice_line
+        Bs.close()
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    peak, peak_src = hbm_peak()
+    k1_s = stage_ms["search"] / 1e3
+    achieved = block_loads * BYTES_PER_RANK / max(k1_s, 1e-12) / 1e9
+    tot_sym = sum(v["symbols"] for v in sizes.values())
+    line = {
+        "metric": "31-mer count+locate queries/s (findInterval + LF-walk locate over 64 run-level shards)",
+        "value": Q * args.steps / (total_ms / 1e3), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "warmup": max(3, args.warmup), "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "u64", "data": "synthetic",
+        "config": {
+            "workload": (f"configs[3]: {nshards} shards drawn at the run level (symbol and length of each run from the table of a "
+                         f"real shard: {args.samples} diploid samples x {args.coverage:g}x of {args.read_len}-bp reads), "
+                         f"{args.c3_symbols / 1e9:g} G symbols per shard, {nshards // world} shards per GPU; {Q} {k}-mers (90% read "
+                         f"off the shards' LF walks), count + locate by LF walk (<= {max_steps} steps), answers fanned in to the "
+                         f"k-mers' owners"),
+            "k": k, "queries_per_step": Q, "shards": nshards, "shards_on_rank0": len(my_shards),
+            "symbols_on_rank0": tot_sym, "runs_on_rank0": sum(v["runs"] for v in sizes.values()),
+            "mean_run_length_of_the_real_shard": mean_run,
+            "index_hbm_bytes_by_rank": index_bytes_by_rank, "index_hbm_bytes_total": sum(index_bytes_by_rank),
+            "generate_and_load_seconds_rank0": round(load_s, 1), "hits_per_step": total_hits, "kmers_found": found,
+            "chunk_queries": int(info.chunk_queries),
+            "l2": "index per GPU far larger than the 126 MB L2 (a shard's rank blocks alone are 4.5 GB); 256 MiB written "
+                  "between timed steps (untimed)",
+            "timing": "CUDA events around each step on the launching stream, summed; max over ranks; ranks aligned with a "
+                      "barrier before each step",
+            "collective": "fused into the pipeline's kernels over NVLink peer memory (counts added into the owner's buffer, "
+                          "hit numbers -> owner assigns slots -> read indices written into the owner's list)" if world > 1 else "none",
+            "fan_in_equals_ranks_own_answers": fan_in_ok, "parity_slice": slice_line},
+        "roofline": {
+            "bound": "hbm", "kernel": "k_find_interval_dense (K1), one launch per shard", "achieved": achieved, "peak": peak,
+            "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+            "algorithmic_bytes": "64-byte rank blocks K1 had to read x 64 B (counted on the device)",
+            "blocks_per_launch": block_loads / max(1, stage_launches["search"]),
+            "stage_ms_per_step": {s_: v / args.steps for s_, v in stage_ms.items()},
+            **({"stage_ms_per_step_by_rank": per} if per else {}),
+            "lf_steps_per_step": walk_steps / args.steps},
+        "e2e": None, "gpu_launches": int(sum(stage_launches.values()) / max(1, args.steps)), "clocks": clk,
+        "cpu_baseline": ({"value": slice_line["reference"]["queries_per_s"], "unit": UNIT, "cores": slice_line["reference"]["threads"],
+                          "kind": slice_line["reference"]["kind"],
+                          "sample": f"{slice_line['queries']} k-mers, count + locate, against the parity slice shard "
+                                    f"({slice_line['symbols']} symbols): ONE shard of 1 % the size, not the collection"}
+                         if slice_line else None),
+    }
+    print(json.dumps(line), file=_REAL_STDOUT, flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
 def main():
     args = parse()
     # libraries (NCCL's version banner, torchrun notices) must not share stdout with the ONE JSON line
@@ -845,6 +1120,8 @@ def main():
         print(json.dumps(side_configs1(args, engine, "cuda:0", 0, flush)), file=_REAL_STDOUT, flush=True)
     elif args.impl == "reference":
         run_reference(args)
+    elif args.workload == "configs3":
+        run_configs3(args)
     else:
         run_ours(args)
 

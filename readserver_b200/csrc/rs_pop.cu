@@ -1477,7 +1477,9 @@ int rs_pop_query(rs_shardset* set, const void* kmers, int k, size_t Q, int packe
   uint64_t *d_hits = (hit_offsets && capacity) ? (uint64_t*)set->s_hh.p : nullptr, *d_marks = (uint64_t*)set->s_hm.p;
   uint32_t* d_carr = carriers ? (uint32_t*)set->s_hw.p : nullptr;
   /* sub-batches: about 2.5 M queries each, at most RS_POP_MAX_SUB */
-  size_t nsub = (Q + 2500000 - 1) / 2500000;
+  size_t sub_queries = 2500000;
+  if (const char* e = getenv("RS_B200_POP_SUB")) sub_queries = (size_t)std::max<long long>(1000, atoll(e)); /* experiments */
+  size_t nsub = (Q + sub_queries - 1) / sub_queries;
   if (nsub > RS_POP_MAX_SUB) nsub = RS_POP_MAX_SUB;
   if (!hit_offsets) nsub = 1;
   const size_t per = (Q + nsub - 1) / nsub;

@@ -502,3 +502,41 @@ def site_probe_kmers(pop: Population, n_sites: int, k: int, seed: int):
     alt[:, half] = pop.site_alt[pick]
     lut = torch.from_numpy(ASCII.copy()).to(dev)
     return lut[ref.long()], lut[alt.long()], pick
+
+
+# ------------------------------------------------------------------------------------------------
+# run-level collections (BASELINE.json configs[3]): BWTs far too large to derive from reads here are drawn
+# directly as SGA run bytes, run symbol and run length following a table measured on a real shard
+# ------------------------------------------------------------------------------------------------
+def run_table(runs: torch.Tensor) -> torch.Tensor:
+    """[5, 32] float64: how many runs of each symbol ($ACGT) have each length (1..31) in the run bytes `runs`."""
+    r = runs.to(torch.int64)
+    return torch.bincount((r >> 5) * 32 + (r & 31), minlength=160)[:160].reshape(5, 32).to(torch.float64)
+
+
+def runlevel_shard(table: torch.Tensor, num_symbols: int, seed: int, device="cuda", chunk: int = 1 << 27):
+    """Run bytes of a BWT of about `num_symbols` symbols whose (symbol, length) pairs are drawn independently from
+    `table` (run_table of a real shard).  Returns (runs uint8 [R] on `device`, num_strings, num_symbols): the number of
+    strings is the number of '$' drawn, as in a real BWT.  Not the BWT of any read set -- LF walks still end at a '$'
+    (geometrically distributed lengths) -- which is all the count and locate kernels need (Config 4)."""
+    g = torch.Generator(device=device)
+    g.manual_seed(seed)
+    p = (table / table.sum()).reshape(-1).to(device)
+    cdf = torch.cumsum(p, 0).to(torch.float32)
+    mean_len = float((table * torch.arange(32, dtype=torch.float64)).sum() / table.sum())
+    total = int(num_symbols / mean_len)
+    out = torch.empty(total, dtype=torch.uint8, device=device)
+    nsym = nstr = 0
+    for a in range(0, total, chunk):
+        n = min(chunk, total - a)
+        u = torch.rand(n, generator=g, device=device)
+        cell = torch.searchsorted(cdf, u).clamp_(max=159)          # index into the [5, 32] table
+        ln = cell & 31
+        bad = ln == 0                                              # (a zero-length cell has probability 0; rounding)
+        cell = torch.where(bad, torch.full_like(cell, 1 * 32 + 1), cell)
+        ln = cell & 31
+        out[a:a + n] = cell.to(torch.uint8)                        # sym << 5 | len == cell
+        nsym += int(ln.sum())
+        nstr += int(ln[(cell >> 5) == 0].sum())
+        del u, cell, ln, bad
+    return out, nstr, nsym
