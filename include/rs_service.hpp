@@ -157,6 +157,9 @@ class CountBatcher {
 // stored beside each code are sent as c and l (:1338-1342), else 0.  One Reply per strand, forward first, bytes as
 // QueryTask serialises them.  Tile matches are emitted in tile order along the query: the reference iterates an
 // unordered_set there, so its order among them is unspecified.
+// KmerMatch requests (KmerTask, service.cpp:851-990) ride the same batches: the tiles get_tiles(q, k, s) cuts are
+// searched as find_reads searches them, their reads united (a set of read strings in the reference: reported once each,
+// here in the order the tiles find them), and answered as count (the set's size), reads or all.
 class QueryBatcher {
  public:
   QueryBatcher(const GpuBWT* bwt, const std::map<std::string, std::string>* code_to_name, int size_of_sample,
@@ -174,8 +177,15 @@ class QueryBatcher {
   }
   bool push(const std::string& bytes) { return push(bytes.data(), bytes.size()); }
   bool push(wire::Request& r) {
-    if (r.t != wire::ExactMatch || r.rt == wire::Count || r.q.empty()) return false;
-    pending_.push_back(Item{std::move(r.q), r.rt});
+    if (r.q.empty()) return false;
+    if (r.t == wire::ExactMatch) {
+      if (r.rt == wire::Count) return false;  // CountBatcher's
+    } else if (r.t == wire::KmerMatch) {
+      if (r.k <= 0 || r.s < 0) return false;  // (k = 0 makes get_tiles cut empty tiles: left to the caller)
+    } else {
+      return false;
+    }
+    pending_.push_back(Item{std::move(r.q), r.rt, r.t, (size_t)r.k, (size_t)r.s});
     window_.on_push(pending_.size());
     return true;
   }
@@ -217,23 +227,38 @@ class QueryBatcher {
         out.push_back(Piece{strings.size() - 1, 2});
       }
     };
+    auto plan_find_reads = [&](std::vector<Piece>& out, const std::string& w) {  // find_reads (service.cpp:714-797)
+      const size_t sz = w.size();
+      if (sz < min_len_) {
+        strings.push_back(w);
+        out.push_back(Piece{strings.size() - 1, 0});
+      } else if (sz < max_read_) {
+        if (sz != min_len_) add_tiles(out, w, min_len_);
+        if (acgt(w)) {  // query() answers nothing for other bytes (query.cpp:90)
+          strings.push_back(w);
+          out.push_back(Piece{strings.size() - 1, 1});
+        }
+      } else {
+        add_tiles(out, w, max_read_);
+        if (min_len_ != max_read_) add_tiles(out, w, min_len_);
+      }
+    };
     for (size_t i = 0; i < n; ++i)
       for (int rev = 0; rev < 2; ++rev) {
-        const std::string w = rev ? rev_comp(pending_[i].q) : pending_[i].q;
+        const Item& it = pending_[i];
+        const std::string w = rev ? rev_comp(it.q) : it.q;
         std::vector<Piece>& out = plan[2 * i + rev];
-        const size_t sz = w.size();
-        if (sz < min_len_) {
-          strings.push_back(w);
-          out.push_back(Piece{strings.size() - 1, 0});
-        } else if (sz < max_read_) {
-          if (sz != min_len_) add_tiles(out, w, min_len_);
-          if (acgt(w)) {  // query() answers nothing for other bytes (query.cpp:90)
-            strings.push_back(w);
-            out.push_back(Piece{strings.size() - 1, 1});
+        if (it.t == wire::KmerMatch) {
+          // find_kmer_reads (service.cpp:466-502): find_reads of every tile get_tiles(w, k, skip) cuts (:232-246) that
+          // holds nothing but ACGT (:477); the reads of all tiles are united below
+          std::set<std::string> seen;
+          for (size_t at = 0; w.size() >= it.k && at + it.k <= w.size(); at += it.s + 1) {
+            const std::string tile = w.substr(at, it.k);
+            if (!seen.insert(tile).second || !acgt(tile)) continue;
+            plan_find_reads(out, tile);
           }
         } else {
-          add_tiles(out, w, max_read_);
-          if (min_len_ != max_read_) add_tiles(out, w, min_len_);
+          plan_find_reads(out, w);
         }
       }
     const std::vector<BWTInterval> ivs = findIntervalBatch(bwt_, strings);
@@ -269,8 +294,18 @@ class QueryBatcher {
           for (uint64_t h = b; h < start; ++h) hits[j].push_back(h);
         }
       }
+    // KmerTask keeps a SET of read strings (service.cpp:889): a read found through several tiles is reported once
+    for (size_t i = 0; i < n; ++i)
+      if (pending_[i].t == wire::KmerMatch)
+        for (int rev = 0; rev < 2; ++rev) {
+          std::set<std::string> seen;
+          std::vector<uint64_t> kept;
+          for (uint64_t h : hits[2 * i + rev])
+            if (seen.insert(pre[h] + post[h]).second) kept.push_back(h);
+          hits[2 * i + rev].swap(kept);
+        }
     bool want_samples = false;
-    for (size_t i = 0; i < n; ++i) want_samples |= pending_[i].rt != wire::Reads;
+    for (size_t i = 0; i < n; ++i) want_samples |= pending_[i].rt != wire::Reads && pending_[i].rt != wire::Count;
     std::vector<uint64_t> soff(rows.size() + 1, 0);
     std::vector<uint8_t> codes, meta;
     if (want_samples && !rows.empty()) {
@@ -287,10 +322,13 @@ class QueryBatcher {
     for (size_t i = 0; i < n; ++i)
       for (int rev = 0; rev < 2; ++rev) {
         const size_t j = 2 * i + rev;
-        if (pending_[i].rt == wire::Reads) {
+        const int32_t type = pending_[i].t;
+        if (pending_[i].rt == wire::Count) {  // KmerMatch only: the size of the set (service.cpp:893-902)
+          send(wire::encode_reply_count(type, pending_[i].q, rev != 0, hits[j].size()));
+        } else if (pending_[i].rt == wire::Reads) {
           std::vector<std::string> reads;
           for (uint64_t h : hits[j]) reads.push_back(pre[h] + post[h]);
-          send(wire::encode_reply_reads(wire::ExactMatch, pending_[i].q, rev != 0, reads));
+          send(wire::encode_reply_reads(type, pending_[i].q, rev != 0, reads));
         } else {
           std::vector<wire::ResultAll> out;
           for (uint64_t h : hits[j]) {
@@ -309,7 +347,7 @@ class QueryBatcher {
             }
             out.push_back(one);
           }
-          send(wire::encode_reply_all(wire::ExactMatch, pending_[i].q, rev != 0, out, pending_[i].rt));
+          send(wire::encode_reply_all(type, pending_[i].q, rev != 0, out, pending_[i].rt));
         }
       }
     pending_.clear();
@@ -319,7 +357,8 @@ class QueryBatcher {
  private:
   struct Item {
     std::string q;
-    int32_t rt;
+    int32_t rt, t;  // return type; ExactMatch or KmerMatch
+    size_t k, s;    // KmerMatch: tile length and skip
   };
   const GpuBWT* bwt_;
   const std::map<std::string, std::string>* hash_;
@@ -328,6 +367,169 @@ class QueryBatcher {
   uint32_t max_len_;
   bool meta_;
   std::string suffix_;
+  BatchWindow window_;
+  std::vector<Item> pending_;
+};
+
+// SiteMatch requests (GtTask::run, service.cpp:993-1212), batched.  Per request and strand: the query, position and
+// alternative allele are oriented and the window cut as :1024-1037 does; the windows of a batch go through
+// rs_gt_reads_batch (the tile loop over find_gt_reads, :1044-1072) -> read indices -> read strings from the packed read
+// table (GpuBWT::loadReadsFile); every read is offered to `align` -- the reference's align_gt_read (ksw.c, host code
+// that stays the reference's: bool(read, window, pos, alt, isalt)) -- and the accepted ones are answered as count,
+// reads or all (:1121-1199).  The reference keeps the reads in an unordered_set; here they come in read-index order.
+// A request whose window the reference itself cannot process (pos beyond the window: it prints an error, :1041-1043;
+// a substr past the end or a window shorter than a tile: it throws or never returns) gets the reply head alone.
+// Needs the .sai (setSai) and the read table.
+template <class Aligner>
+class SiteBatcher {
+ public:
+  SiteBatcher(const GpuBWT* bwt, const std::map<std::string, std::string>* code_to_name, int size_of_sample, Aligner align,
+              size_t max_read_length = 100, size_t max_pending = (size_t)1 << 12, uint32_t max_len = 256,
+              bool has_other_meta_data = false, uint64_t max_interval_size = 10000,
+              std::chrono::microseconds window = std::chrono::microseconds(2000))
+      : bwt_(bwt), hash_(code_to_name), sos_(size_of_sample), align_(align), max_read_(max_read_length),
+        max_pending_(max_pending), max_len_(max_len), meta_(has_other_meta_data), max_iv_(max_interval_size),
+        window_(max_pending, window) {}
+
+  bool push(const std::string& bytes) {
+    wire::Request r;
+    return wire::decode_request(bytes.data(), bytes.size(), r) && push(r);
+  }
+  bool push(wire::Request& r) {
+    if (r.t != wire::SiteMatch || r.q.empty() || r.k <= 0 || r.s < 0) return false;
+    pending_.push_back(Item{std::move(r.q), std::move(r.a), r.rt, (size_t)r.p, (size_t)r.k, (size_t)r.s, r.isalt == 1});
+    window_.on_push(pending_.size());
+    return true;
+  }
+  size_t pending() const { return pending_.size(); }
+  bool full() const { return pending_.size() >= max_pending_; }
+  bool due() const { return window_.due(pending_.size()); }
+  const BatchWindow& window() const { return window_; }
+
+  template <class Send>
+  size_t flush(Send&& send) {
+    const size_t n = pending_.size();
+    window_.on_flush();
+    if (!n) return 0;
+    struct Cut {
+      std::string w, alt;
+      size_t pos;
+      bool bad;
+    };
+    std::vector<Cut> cuts(2 * n);
+    std::map<std::pair<size_t, size_t>, std::vector<size_t> > groups;  // (k, s) -> cuts searched together
+    for (size_t i = 0; i < n; ++i)
+      for (int rev = 0; rev < 2; ++rev) {
+        const Item& it = pending_[i];
+        Cut& c = cuts[2 * i + rev];
+        c.w = it.q;
+        c.alt = it.a;
+        c.pos = it.p;
+        c.bad = false;
+        if (rev) {  // service.cpp:1024-1028
+          c.w = QueryBatcher::rev_comp(it.q);
+          c.pos = c.w.size() - it.p + 1;
+          c.alt = QueryBatcher::rev_comp(it.a);
+        }
+        if (c.pos <= max_read_) {  // :1030-1036
+          c.w = c.w.substr(0, max_read_ + c.pos - 1);
+        } else if (c.pos - max_read_ > c.w.size()) {
+          c.bad = true;  // substr would throw
+        } else {
+          c.w = c.w.substr(c.pos - max_read_, max_read_ * 2 - 1);
+          c.pos = max_read_;
+        }
+        if (c.pos > c.w.size() || c.w.size() < it.k) c.bad = true;
+        if (!c.bad) groups[std::make_pair(it.k, it.s)].push_back(2 * i + rev);
+      }
+    std::vector<std::vector<uint64_t> > found(2 * n);
+    for (const auto& g : groups) {
+      std::vector<std::string> ws;
+      std::vector<uint64_t> pos;
+      for (size_t j : g.second) {
+        ws.push_back(cuts[j].w);
+        pos.push_back(cuts[j].pos);
+      }
+      std::vector<uint32_t> flags;
+      const std::vector<std::vector<uint64_t> > ri = findGtReadsBatch(bwt_, ws, pos, g.first.first, g.first.second, max_iv_, &flags);
+      for (size_t x = 0; x < g.second.size(); ++x) {
+        if (flags[x]) cuts[g.second[x]].bad = true;  // a tile on which the reference throws or hangs
+        else found[g.second[x]] = ri[x];
+      }
+    }
+    for (size_t i = 0; i < n; ++i)
+      for (int rev = 0; rev < 2; ++rev) {
+        const size_t j = 2 * i + rev;
+        const Item& it = pending_[i];
+        const Cut& c = cuts[j];
+        if (c.bad) {
+          std::string head;
+          wire::reply_head(head, wire::SiteMatch, it.rt, it.q);
+          send(head);
+          continue;
+        }
+        const std::vector<std::string> reads = readsBatch(bwt_, found[j], max_len_);
+        std::vector<std::string> kept;
+        std::vector<uint64_t> kept_index;
+        for (size_t h = 0; h < reads.size(); ++h)
+          if (align_(reads[h], c.w, c.pos, c.alt, it.isalt)) {
+            kept.push_back(reads[h]);
+            kept_index.push_back(found[j][h]);
+          }
+        if (it.rt == wire::Count) {
+          send(wire::encode_reply_count(wire::SiteMatch, it.q, rev != 0, kept.size()));
+        } else if (it.rt == wire::Reads) {
+          send(wire::encode_reply_reads(wire::SiteMatch, it.q, rev != 0, kept));
+        } else {
+          std::vector<uint64_t> soff(kept.size() + 1, 0);
+          std::vector<uint8_t> codes(1), meta;
+          if (!kept.empty()) {
+            int rc = rs_samples_meta_batch(bwt_->handle(), kept_index.data(), kept.size(), soff.data(), 0, codes.data(), nullptr);
+            if (rc == RS_STATUS_CAPACITY) {
+              codes.resize((size_t)soff[kept.size()] * sos_ + 1);
+              if (meta_) meta.resize((size_t)soff[kept.size()] * 2 + 1);
+              rc = rs_samples_meta_batch(bwt_->handle(), kept_index.data(), kept.size(), soff.data(), soff[kept.size()],
+                                         codes.data(), meta_ ? meta.data() : nullptr);
+            }
+            check(rc);
+          }
+          std::vector<wire::ResultAll> out(kept.size());
+          for (size_t h = 0; h < kept.size(); ++h) {
+            out[h].r = kept[h];
+            for (uint64_t x = soff[h]; x < soff[h + 1]; ++x) {
+              wire::ReadInfo info;
+              const std::map<std::string, std::string>::const_iterator f =
+                  hash_->find(std::string((const char*)&codes[(size_t)x * sos_], (size_t)sos_));
+              if (f != hash_->end()) info.g = f->second;
+              if (meta_) {
+                info.c = (int32_t)(signed char)meta[(size_t)x * 2] - 33;
+                info.l = (int32_t)(signed char)meta[(size_t)x * 2 + 1] - 33;
+              }
+              out[h].s.push_back(info);
+            }
+          }
+          send(wire::encode_reply_all(wire::SiteMatch, it.q, rev != 0, out, it.rt));
+        }
+      }
+    pending_.clear();
+    return 2 * n;
+  }
+
+ private:
+  struct Item {
+    std::string q, a;
+    int32_t rt;
+    size_t p, k, s;
+    bool isalt;
+  };
+  const GpuBWT* bwt_;
+  const std::map<std::string, std::string>* hash_;
+  int sos_;
+  Aligner align_;
+  size_t max_read_, max_pending_;
+  uint32_t max_len_;
+  bool meta_;
+  uint64_t max_iv_;
   BatchWindow window_;
   std::vector<Item> pending_;
 };
@@ -341,10 +543,10 @@ class QueryBatcher {
 //     bool stopped();                                                  // the reference loops forever
 //   };
 //
-// Count requests and ExactMatch queries are batched (windows above) and answered on the GPU; KmerMatch and SiteMatch
-// requests -- whose k-mer / seed stages are rs_tile_intervals_batch / rs_gt_reads_batch, and whose reply assembly
-// needs the Smith-Waterman aligner that stays on the host -- are handed to `other`, as are bytes that do not parse
-// (the reference prints "unrecognised request type").
+// Count requests, ExactMatch and KmerMatch queries are batched (windows above) and answered on the GPU; SiteMatch
+// requests -- whose seed stage is rs_gt_reads_batch and whose reply assembly needs the Smith-Waterman aligner that
+// stays on the host -- are handed to `other`, as are bytes that do not parse (the reference prints "unrecognised
+// request type").
 template <class Transport, class Other>
 class Worker {
  public:

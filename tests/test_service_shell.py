@@ -274,22 +274,118 @@ def test_worker_loop_on_a_demo_shaped_script(meta, suffix, tmp_path):
                             info.g = names[val[c:c + sos]]
                             info.c, info.l = (val[c + sos] - 33, val[c + sos + 1] - 33) if meta else (0, 0)
                 want.append(("push", r.SerializeToString().hex()))
-    # not the batchers': k-mer match, site match, garbage
-    others = [M["Request"](t=3, rt=2, q=qs[4], k=31, s=0).SerializeToString().hex(),
-              M["Request"](t=4, rt=3, q=qs[5], k=31, s=7, p=40).SerializeToString().hex(), "ff"]
+    # k-mer match (KmerTask, service.cpp:851-990): the reads of all tiles, each once; count = how many
+    for q, kk, ss in ((qs[4], 31, 0), (qs[2], 31, 0), (qs[11], 40, 7), (full[2][:50] + "N" + full[2][51:90], 20, 3), (qs[15], 9, 0)):
+        for rt in (1, 2, 3):
+            reqs.append(M["Request"](t=3, rt=rt, q=q, k=kk, s=ss).SerializeToString().hex())
+            for rev in (False, True):
+                s = q[::-1].translate(COMP) if rev else q
+                hits, seen, tiles_seen = [], set(), set()
+                for at in range(0, len(s) - kk + 1, ss + 1):
+                    tile = s[at:at + kk]
+                    if tile in tiles_seen or any(c not in "ACGT" for c in tile):
+                        continue
+                    tiles_seen.add(tile)
+                    for rd, ri in _find_reads(P, gold.reads, index_of, tile, suffix, 73, 100):
+                        if rd not in seen:
+                            seen.add(rd)
+                            hits.append((rd, ri))
+                r = M["Reply"]()
+                r.rt, r.t, r.q = 3, rt, q
+                if rt == 1:
+                    (r.c.revcomp_matches if rev else r.c.forward_matches).c = len(hits)
+                elif rt == 2:
+                    r.r.SetInParent()
+                    for rd, _ in hits:
+                        (r.r.revcomp_matches if rev else r.r.forward_matches).add().r = rd
+                else:
+                    r.a.SetInParent()
+                    for rd, ri in hits:
+                        one = (r.a.revcomp_matches if rev else r.a.forward_matches).add()
+                        one.r = rd
+                        val = kept[ri]
+                        stride = sos + (2 if meta else 0)
+                        for c in range(0, len(val), stride):
+                            info = one.s.add()
+                            info.g = names[val[c:c + sos]]
+                            info.c, info.l = (val[c + sos] - 33, val[c + sos + 1] - 33) if meta else (0, 0)
+                want.append(("push", r.SerializeToString().hex()))
+    kmer_hits = sum(len(M["Reply"].FromString(bytes.fromhex(h)).r.forward_matches) for s_, h in want
+                    if M["Reply"].FromString(bytes.fromhex(h)).rt == 3)
+    assert kmer_hits > 10
+    # site match (GtTask, service.cpp:993-1212): window cut around p, seeds by find_gt_reads (oracle/gt.py, pinned on the
+    # reference's own), the aligner a stand-in predicate (the same in tests/cpp/worker_test.cpp), count / reads / all
+    from oracle import gt as ogt
+    site_reqs = [(g[3000:3260], 130, "A", 0, 31, 7), (g[8000:8150], 40, "ACG", 1, 31, 7), (g[500:700], 190, "T", 0, 20, 3),
+                 (g[100:180], 300, "A", 0, 31, 7), ("ACGT", 2, "A", 0, 31, 7), (full[30] + g[9000:9100], 100, "G", 1, 31, 0)]
+    site_hits = 0
+    for q, p_, a, isalt, kk, ss in site_reqs:
+        for rt in (1, 2, 3):
+            reqs.append(M["Request"](t=4, rt=rt, q=q, k=kk, s=ss, p=p_, a=a, isalt=isalt).SerializeToString().hex())
+            for rev in (False, True):
+                w, pos, alt = q, p_, a
+                if rev:
+                    w, pos, alt = q[::-1].translate(COMP), len(q) - p_ + 1, a[::-1].translate(COMP)
+                bad = pos < 0
+                if not bad and pos <= 100:
+                    w = w[:100 + pos - 1]
+                elif not bad and pos - 100 > len(w):
+                    bad = True
+                elif not bad:
+                    w, pos = w[pos - 100: pos - 100 + 199], 100
+                bad = bad or pos > len(w) or len(w) < kk
+                r = M["Reply"]()
+                r.rt, r.t, r.q = 4, rt, q
+                if not bad:
+                    idx, undefined = ogt.gt_task_reads(P, w, pos, kk, ss, 10000)
+                    bad = bool(undefined)
+                if not bad:
+                    keep = [ri for ri in idx
+                            if (len(gold.reads[ri]) + ord(gold.reads[ri][len(gold.reads[ri]) // 2]) + len(w) + pos + len(alt) + isalt) % 3]
+                    site_hits += len(keep)
+                    if rt == 1:
+                        (r.c.revcomp_matches if rev else r.c.forward_matches).c = len(keep)
+                    elif rt == 2:
+                        r.r.SetInParent()
+                        for ri in keep:
+                            (r.r.revcomp_matches if rev else r.r.forward_matches).add().r = gold.reads[ri]
+                    else:
+                        r.a.SetInParent()
+                        for ri in keep:
+                            one = (r.a.revcomp_matches if rev else r.a.forward_matches).add()
+                            one.r = gold.reads[ri]
+                            val = kept[ri]
+                            stride = sos + (2 if meta else 0)
+                            for c in range(0, len(val), stride):
+                                info = one.s.add()
+                                info.g = names[val[c:c + sos]]
+                                info.c, info.l = (val[c + sos] - 33, val[c + sos + 1] - 33) if meta else (0, 0)
+                want.append(("site", r.SerializeToString().hex()))
+    assert site_hits > 30
+    # nobody's: garbage, a k-mer request without k, a site request without k
+    others = [M["Request"](t=3, rt=2, q=qs[4], s=0).SerializeToString().hex(),
+              M["Request"](t=4, rt=3, q=qs[5], s=7, p=40).SerializeToString().hex(), "ff"]
     reqs[5:5] = others[:1]
     reqs += others[1:]
     f = tmp_path / "req.hex"
     f.write_text("\n".join(reqs) + "\n")
-    out = subprocess.run([exe, str(cfg), str(f), etl], check=True, capture_output=True, text=True).stdout.splitlines()
+    sai = tmp_path / "shard.sai"
+    np.asarray(gold.sai, dtype=np.uint64).tofile(sai)
+    out = subprocess.run([exe, str(cfg), str(f), etl, str(sai)], check=True, capture_output=True, text=True).stdout.splitlines()
     assert out[-1] == f"sent {len(want)}"
     got_other = [l.split(" ", 1)[1] for l in out if l.startswith("other ")]
     assert got_other == others
     # replies of one sink and one kind arrive in request order; batches of the two kinds interleave by their windows
     got = [tuple(l.split(" ", 1)) for l in out[:-1] if not l.startswith("other ")]
+    # (the count batcher answers ExactMatch counts, the query batcher everything about reads and all of KmerMatch)
+    def is_site(h):
+        return M["Reply"].FromString(bytes.fromhex(h)).rt == 4
+    assert [h for s_, h in got if s_ == "push" and is_site(h)] == [h for s_, h in want if s_ == "site"]
+    got = [(s_, h) for s_, h in got if not is_site(h)]
     for sink, is_count in (("count", True), ("push", True), ("push", False)):
         def kind(h):
-            return M["Reply"].FromString(bytes.fromhex(h)).HasField("c")
+            m = M["Reply"].FromString(bytes.fromhex(h))
+            return m.HasField("c") and m.rt != 3
         g_ = [h for s_, h in got if s_ == sink and kind(h) == is_count]
         w_ = [h for s_, h in want if s_ == sink and kind(h) == is_count]
         assert g_ == w_, (sink, is_count)
