@@ -686,9 +686,9 @@ def run_ours(args):
     getocc = 2.0 * interval_steps
     achieved = block_loads * BYTES_PER_RANK / max(k1_s, 1e-12) / 1e9
     traffic, traffic_src = committed_traffic("r2_k1_traffic.json") if args.workload == "configs2" and world == 1 else (None, None)
-    chunks = (Q + int(info.chunk_queries) - 1) // int(info.chunk_queries)
-    ours_per_step = len(strands) * (1 + chunks * (len(my_shards) + 4 + (1 if args.locate_every == 1 else 4 * len(my_shards) + 1))
-                                    + (chunks * 2 + 2 + chunks * 3 if world > 1 else 0))
+    # this library's own kernel launches inside the timed steps, as the pipeline counted them stage by stage
+    # (rs_shardset_read_timing; CUB's sort and scan kernels are not included)
+    ours_launches = int(sum(stage_launches.values()))
     hits_all = sum(total_hits.values())
     line = {
         "metric": METRIC if args.workload == "configs2" else
@@ -735,7 +735,7 @@ def run_ours(args):
                 "api": "rs_pop_query (host pointers, pinned): k-mers in, counts + hit offsets + hits + carrier sets out; the "
                        "copy-out of one sub-batch overlaps the kernels of the next" if world == 1
                 else "per rank: batch H2D, rs_pop_query_comm_dev, the owned answers D2H"},
-        "gpu_launches": args.steps * ours_per_step,
+        "gpu_launches": ours_launches,
         "clocks": clk,
     }
     if want_cpu:

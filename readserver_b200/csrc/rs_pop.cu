@@ -1227,7 +1227,7 @@ static int pop_run(rs_shardset* set, rs_popcomm* comm, const void* d_kmers, int 
     CU(set->s_perm.need(Q * 4));
     CU(set->s_iota.need(Q * 4));
     CU(set->s_sslot.need(Q * 8));
-    StageTimer tm(set, st, RS_POP_STAGE_PACK, 2);
+    StageTimer tm(set, st, RS_POP_STAGE_PACK, 1); /* launches counted are this library's own kernels (not CUB's) */
     k_pop_iota<<<(unsigned)((Q + 255) / 256), 256, 0, st>>>((uint32_t*)set->s_iota.p, Q);
     CU(cudaGetLastError());
     CU(rs_sort_pairs(keys, (uint64_t*)set->s_skeys.p, (const uint32_t*)set->s_iota.p, (uint32_t*)set->s_perm.p, Q, 2 * k,
@@ -1279,7 +1279,7 @@ static int pop_run(rs_shardset* set, rs_popcomm* comm, const void* d_kmers, int 
                                           cnt + (uint64_t)s * C, 4, (unsigned long long*)set->d_stats, st, nullptr, tickets + s));
     }
     {
-      StageTimer tm(set, st, RS_POP_STAGE_OFFSETS, want_hits ? 4 : 1);
+      StageTimer tm(set, st, RS_POP_STAGE_OFFSETS, (want_hits ? 3 : 1) + (multi ? (want_hits ? 5 : 1) : 0));
       if (!multi) {
         k_pop_totals<<<gq, 256, 0, st>>>(cnt, S, C, nq, max_hits, d_counts + q0, nh, seg, pass_off, pass_shards, perm);
       } else {
