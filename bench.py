@@ -602,7 +602,10 @@ def run_ours(args):
         dt = np.uint64 if world == 1 else np.int64
         a1, p1 = pinned_array(engine, Q * 8, dt, (Q,))
         a2, p2 = pinned_array(engine, (Q + 1) * 8, dt, (Q + 1,))
-        a3, p3 = pinned_array(engine, cap * 8, dt, (cap,))
+        if world == 1:   # the hit list travels as 5 bytes per hit (rs_pop_query_hits40)
+            a3, p3 = pinned_array(engine, cap * 5, np.uint8, (cap * 5,))
+        else:
+            a3, p3 = pinned_array(engine, cap * 8, dt, (cap,))
         a4, p4 = pinned_array(engine, Q * W * 4, np.uint32 if world == 1 else np.int32, (Q, W))
         host[sd] = dict(counts=a1, off=a2, hits=a3, carr=a4)
         keep_alive += [p1, p2, p3, p4]
@@ -611,10 +614,10 @@ def run_ours(args):
         def e2e_call():
             for sd in strands:
                 h = host[sd]
-                rc = L.rs_pop_query(S._h, hq.ctypes.data, k, Q, 0, sd, MAX_HITS, h["counts"].ctypes.data, h["off"].ctypes.data,
-                                    h["hits"].ctypes.data, caps[sd], h["carr"].ctypes.data, C.byref(tot))
+                rc = L.rs_pop_query_hits40(S._h, hq.ctypes.data, k, Q, 0, sd, MAX_HITS, h["counts"].ctypes.data, h["off"].ctypes.data,
+                                           h["hits"].ctypes.data, caps[sd], h["carr"].ctypes.data, C.byref(tot))
                 assert rc == 0, rc
-        d2h = sum(Q * 8 + (Q + 1) * 8 + total_hits[sd] * 8 + Q * W * 4 + 8 for sd in strands)
+        d2h = sum(Q * 8 + (Q + 1) * 8 + total_hits[sd] * 5 + Q * W * 4 + 8 for sd in strands)
     else:
         # every rank: batch in, the pipeline with its fan-in, the answers of the k-mers it owns out
         t_hq = torch.from_numpy(hq)
@@ -662,7 +665,11 @@ def run_ours(args):
             assert np.array_equal(h["off"], o["off"].cpu().numpy().view(np.uint64))
             assert np.array_equal(h["carr"], o["carr"].cpu().numpy().view(np.uint32))
             n = int(h["off"][Q])
-            assert n == total_hits[sd] and np.array_equal(h["hits"][:n], o["hits"][:n].cpu().numpy().view(np.uint64))
+            assert n == total_hits[sd]
+            for a in range(0, n, 1 << 24):   # the 5-byte list, widened piece by piece, against the device path's
+                b = min(n, a + (1 << 24))
+                assert np.array_equal(engine.unpack_hits40(h["hits"][5 * a: 5 * b], b - a),
+                                      o["hits"][a:b].cpu().numpy().view(np.uint64))
 
     side = None
     if world == 1 and not args.no_side:
@@ -732,7 +739,8 @@ def run_ours(args):
         },
         "e2e": {"value": Q * e2e_steps / e2e_s, "unit": UNIT, "h2d_bytes_per_step": (world if world > 1 else 1) * Q * k,
                 "d2h_bytes_per_step": d2h, "steps": e2e_steps,
-                "api": "rs_pop_query (host pointers, pinned): k-mers in, counts + hit offsets + hits + carrier sets out; the "
+                "api": "rs_pop_query_hits40 (host pointers, pinned): k-mers in, counts + hit offsets + hits (5 bytes each: shard "
+                       "id << 32 | read index) + carrier sets out; the "
                        "copy-out of one sub-batch overlaps the kernels of the next" if world == 1
                 else "per rank: batch H2D, rs_pop_query_comm_dev, the owned answers D2H"},
         "gpu_launches": ours_launches,
@@ -753,7 +761,7 @@ def run_ours(args):
             h = host[sd]
             he = int(h["off"][n])
             c = {"population_counts": bool(np.array_equal(h["counts"][:n], w_counts)),
-                 "hit_lists_read_index": bool(np.array_equal(h["off"][: n + 1], w_off) and np.array_equal(h["hits"][:he], w_hits)),
+                 "hit_lists_read_index": bool(np.array_equal(h["off"][: n + 1], w_off) and np.array_equal(engine.unpack_hits40(h["hits"], he), w_hits)),
                  "sample_sets": bool(np.array_equal(h["carr"][:n], w_carr)), "hits_checked": he,
                  "postfix_walk_vs_prefix_walk_read_index": post}
             all_ok &= c["population_counts"] and c["hit_lists_read_index"] and c["sample_sets"]

@@ -361,6 +361,13 @@ int rs_pop_query_dev(rs_shardset* set, const void* d_kmers, int k, size_t Q, int
 int rs_pop_query(rs_shardset* set, const void* kmers, int k, size_t Q, int packed, int strand, uint64_t max_hits,
                  uint64_t* counts, uint64_t* hit_offsets, uint64_t* hits, uint64_t capacity, uint32_t* carriers,
                  uint64_t* total_hits);
+/* rs_pop_query with the hit list in 5 bytes per hit instead of 8 (the list is most of what the call copies to the
+ * host: 790 M hits per 10 M 31-mers on BASELINE configs[2]): hit i = the 40-bit little-endian value at hits40 + 5 * i,
+ * shard id << 32 | read index; 2^40 - 1 where rs_pop_query reports 2^64 - 1.  hits40 holds 5 * capacity bytes.
+ * RS_STATUS_TOO_LARGE when a shard id >= 255 or a read index >= 2^32 occurs (the answers other than the list are valid). */
+int rs_pop_query_hits40(rs_shardset* set, const void* kmers, int k, size_t Q, int packed, int strand, uint64_t max_hits,
+                        uint64_t* counts, uint64_t* hit_offsets, uint8_t* hits40, uint64_t capacity, uint32_t* carriers,
+                        uint64_t* total_hits);
 
 /* ---- population queries across the GPUs of one box ---------------------------------------------------------
  * One process per GPU, each with a shard set over the shards it holds.  Every rank runs the whole batch on its set;

@@ -564,6 +564,49 @@ __global__ void k_pop_carr_unsort(const uint4* __restrict__ carr, const uint32_t
   if (i < n) out[perm[i]] = carr[i];
 }
 
+/* hits [begin, end) of the list as 40-bit values (rs_pop_query_hits40): shard id << 32 | read index, little-endian,
+ * 5 bytes each; 2^40 - 1 = no read.  Eight hits = five 64-bit words: a thread packs one aligned group of eight, the
+ * groups the range cuts are written byte by byte.  *bad is set when a shard id >= 255 or a read index >= 2^32 appears. */
+__global__ void k_pop_pack40(const uint64_t* __restrict__ hits, const uint64_t* __restrict__ begin_dev,
+                             const uint64_t* __restrict__ end_dev, uint64_t capacity, uint8_t* __restrict__ out,
+                             uint32_t* __restrict__ bad) {
+  const uint64_t b = begin_dev ? (*begin_dev < capacity ? *begin_dev : capacity) : 0;
+  const uint64_t e = *end_dev < capacity ? *end_dev : capacity;
+  const uint64_t g0 = b / 8, g1 = (e + 7) / 8;
+  const uint64_t stride = (uint64_t)gridDim.x * blockDim.x;
+  bool any_bad = false;
+  for (uint64_t g = g0 + (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; g < g1; g += stride) {
+    const uint64_t h0 = g * 8;
+    uint64_t v[8];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const uint64_t at = h0 + i;
+      uint64_t h = (at >= b && at < e) ? hits[at] : 0;
+      if (h == ~0ull) h = (1ull << 40) - 1;
+      else {
+        any_bad |= (h >> 40) >= 255u || ((h >> 32) & 0xFFu) != 0;
+        h = ((h >> 40) << 32) | (h & 0xFFFFFFFFull);
+      }
+      v[i] = h;
+    }
+    if (h0 >= b && h0 + 8 <= e) {
+      uint64_t* o = reinterpret_cast<uint64_t*>(out + h0 * 5); /* 40 bytes, 8-byte aligned */
+      o[0] = v[0] | (v[1] << 40);
+      o[1] = (v[1] >> 24) | (v[2] << 16) | (v[3] << 56);
+      o[2] = (v[3] >> 8) | (v[4] << 32);
+      o[3] = (v[4] >> 32) | (v[5] << 8) | (v[6] << 48);
+      o[4] = (v[6] >> 16) | (v[7] << 24);
+    } else {
+      for (int i = 0; i < 8; ++i) {
+        const uint64_t at = h0 + i;
+        if (at < b || at >= e) continue;
+        for (int x = 0; x < 5; ++x) out[at * 5 + x] = (uint8_t)(v[i] >> (8 * x));
+      }
+    }
+  }
+  if (any_bad) *bad = 1u;
+}
+
 /* lanes per query for a rank holding S shards: the largest power of two that keeps >= 85 % of the lane slots of a round
  * on a shard (S = 64, 32: 32; 16: 16; 8, 7: 8; 21, 22: 8; 9: 2; 1 lane always qualifies) */
 static uint32_t rs_gather_lanes(uint32_t S) {
@@ -673,7 +716,7 @@ struct rs_shardset {
   cudaStream_t stream = nullptr;
   Scratch s_sort, s_skeys, s_perm, s_iota, s_sslot, s_carrl, s_pass, s_packed, s_lo, s_cnt, s_seg, s_nh, s_loc, s_scan, s_base, s_rows, s_dst, s_ri, s_in, s_lcnt;
   /* host-pointer calls: device-side result buffers, the copy-out stream, per-sub-batch events and hit-list marks */
-  Scratch s_hc, s_ho, s_hh, s_hw, s_hm;
+  Scratch s_hc, s_ho, s_hh, s_hw, s_hm, s_h40;
   cudaStream_t copy_stream = nullptr;
   cudaEvent_t ev_sub[RS_POP_MAX_SUB] = {};
   uint64_t* h_marks = nullptr;
@@ -781,7 +824,7 @@ void rs_shardset_destroy(rs_shardset* set) {
   free_tables(set);
   Scratch* all[] = {&set->s_sort, &set->s_skeys, &set->s_perm, &set->s_iota, &set->s_sslot, &set->s_carrl, &set->s_pass, &set->s_packed, &set->s_lo, &set->s_cnt, &set->s_seg, &set->s_nh, &set->s_loc, &set->s_scan,
                     &set->s_base, &set->s_rows, &set->s_dst, &set->s_ri, &set->s_in, &set->s_lcnt,
-                    &set->s_hc, &set->s_ho, &set->s_hh, &set->s_hw, &set->s_hm};
+                    &set->s_hc, &set->s_ho, &set->s_hh, &set->s_hw, &set->s_hm, &set->s_h40};
   for (Scratch* s : all) s->release();
   if (set->copy_stream) cudaStreamDestroy(set->copy_stream);
   if (set->h_marks) cudaFreeHost(set->h_marks);
@@ -1446,9 +1489,11 @@ int rs_pop_query_dev(rs_shardset* set, const void* d_kmers, int k, size_t Q, int
 /* host buffers (pinned or not): the batch goes through the pipeline in a few sub-batches so that the copy-out of one
  * (its slice of counts, offsets, carrier sets and -- the bulk -- its hits) overlaps the kernels of the next;
  * RS_STATUS_CAPACITY when hits were dropped */
-int rs_pop_query(rs_shardset* set, const void* kmers, int k, size_t Q, int packed, int strand, uint64_t max_hits,
-                 uint64_t* counts, uint64_t* hit_offsets, uint64_t* hits, uint64_t capacity, uint32_t* carriers,
-                 uint64_t* total_hits) {
+static int pop_query_host(rs_shardset* set, const void* kmers, int k, size_t Q, int packed, int strand, uint64_t max_hits,
+                          uint64_t* counts, uint64_t* hit_offsets, void* hits_out, int hit_bytes, uint64_t capacity,
+                          uint32_t* carriers, uint64_t* total_hits) {
+  uint64_t* hits = static_cast<uint64_t*>(hits_out);       /* hit_bytes == 8 */
+  uint8_t* hits40 = static_cast<uint8_t*>(hits_out);       /* hit_bytes == 5 */
   const int rc = pop_check(set, kmers, k, Q, strand, counts, hit_offsets, hits, capacity, carriers);
   if (rc != RS_STATUS_OK) return rc;
   if (total_hits) *total_hits = 0;
@@ -1472,6 +1517,14 @@ int rs_pop_query(rs_shardset* set, const void* kmers, int k, size_t Q, int packe
   CU(set->s_ho.need((Q + 1) * 8));
   CU(set->s_hm.need(RS_POP_MAX_SUB * 8));
   if (hit_offsets && capacity) CU(set->s_hh.need(capacity * 8));
+  uint8_t* d_h40 = nullptr;
+  uint32_t* d_bad = nullptr;
+  if (hit_bytes == 5 && hit_offsets && capacity) {
+    CU(set->s_h40.need(capacity * 5 + 64));
+    d_h40 = (uint8_t*)set->s_h40.p + 8;                     /* the flag word, then the 8-byte aligned list */
+    d_bad = (uint32_t*)set->s_h40.p;
+    CU(cudaMemsetAsync(d_bad, 0, 8, st));
+  }
   if (carriers) CU(set->s_hw.need(Q * W * 4));
   uint64_t *d_counts = (uint64_t*)set->s_hc.p, *d_off = hit_offsets ? (uint64_t*)set->s_ho.p : nullptr;
   uint64_t *d_hits = (hit_offsets && capacity) ? (uint64_t*)set->s_hh.p : nullptr, *d_marks = (uint64_t*)set->s_hm.p;
@@ -1495,7 +1548,10 @@ int rs_pop_query(rs_shardset* set, const void* kmers, int k, size_t Q, int packe
       CU(cudaMemcpyAsync(hit_offsets + q0, d_off + q0, (nq + (q0 + nq == Q ? 1 : 0)) * 8, cudaMemcpyDeviceToHost, cs));
       if (carriers) CU(cudaMemcpyAsync(carriers + q0 * W, d_carr + q0 * W, nq * W * 4, cudaMemcpyDeviceToHost, cs));
       const uint64_t upto = end < capacity ? end : capacity;
-      if (hits && upto > copied) CU(cudaMemcpyAsync(hits + copied, d_hits + copied, (upto - copied) * 8, cudaMemcpyDeviceToHost, cs));
+      if (hits && upto > copied) {
+        if (d_h40) CU(cudaMemcpyAsync(hits40 + copied * 5, d_h40 + copied * 5, (upto - copied) * 5, cudaMemcpyDeviceToHost, cs));
+        else CU(cudaMemcpyAsync(hits + copied, d_hits + copied, (upto - copied) * 8, cudaMemcpyDeviceToHost, cs));
+      }
       if (upto > copied) copied = upto;
     }
     return RS_STATUS_OK;
@@ -1505,6 +1561,10 @@ int rs_pop_query(rs_shardset* set, const void* kmers, int k, size_t Q, int packe
     status = pop_run(set, nullptr, (const uint8_t*)set->s_in.p + q0 * unit, k, nq, packed, strand, max_hits, d_counts + q0,
                      d_off ? d_off + q0 : nullptr, d_hits, capacity, d_carr ? d_carr + q0 * W : nullptr, d_marks + b, st, b > 0);
     if (status != RS_STATUS_OK) break;
+    if (d_h40) { /* this sub-batch's stretch of the list in the 5-byte form */
+      k_pop_pack40<<<148 * 8, 256, 0, st>>>(d_hits, b ? d_marks + b - 1 : nullptr, d_marks + b, capacity, d_h40, d_bad);
+      CU(cudaGetLastError());
+    }
     /* the hit list's length so far, to the host; the copy stream may start on this sub-batch once it is there */
     CU(cudaMemcpyAsync(&set->h_marks[b], d_marks + b, 8, cudaMemcpyDeviceToHost, st));
     CU(cudaEventRecord(set->ev_sub[b], st));
@@ -1521,5 +1581,22 @@ int rs_pop_query(rs_shardset* set, const void* kmers, int k, size_t Q, int packe
   if (hit_offsets && total > capacity)
     return fail(RS_STATUS_CAPACITY, "%llu hits do not fit the %llu provided", (unsigned long long)total,
                 (unsigned long long)capacity);
+  if (d_bad) {
+    uint32_t bad = 0;
+    CU(cudaMemcpy(&bad, d_bad, 4, cudaMemcpyDeviceToHost));
+    if (bad) return fail(RS_STATUS_TOO_LARGE, "a hit does not fit 40 bits (shard id >= 255 or read index >= 2^32): use rs_pop_query");
+  }
   return RS_STATUS_OK;
+}
+
+int rs_pop_query(rs_shardset* set, const void* kmers, int k, size_t Q, int packed, int strand, uint64_t max_hits,
+                 uint64_t* counts, uint64_t* hit_offsets, uint64_t* hits, uint64_t capacity, uint32_t* carriers,
+                 uint64_t* total_hits) {
+  return pop_query_host(set, kmers, k, Q, packed, strand, max_hits, counts, hit_offsets, hits, 8, capacity, carriers, total_hits);
+}
+
+int rs_pop_query_hits40(rs_shardset* set, const void* kmers, int k, size_t Q, int packed, int strand, uint64_t max_hits,
+                        uint64_t* counts, uint64_t* hit_offsets, uint8_t* hits40, uint64_t capacity, uint32_t* carriers,
+                        uint64_t* total_hits) {
+  return pop_query_host(set, kmers, k, Q, packed, strand, max_hits, counts, hit_offsets, hits40, 5, capacity, carriers, total_hits);
 }

@@ -91,6 +91,7 @@ def lib() -> C.CDLL:
         "rs_popcomm_error": (i32, [vp, C.POINTER(i32)]),
         "rs_pop_query_dev": (i32, [vp, vp, i32, sz, i32, i32, u64, vp, vp, vp, u64, vp, vp, vp]),
         "rs_pop_query": (i32, [vp, vp, i32, sz, i32, i32, u64, vp, vp, vp, u64, vp, C.POINTER(u64)]),
+        "rs_pop_query_hits40": (i32, [vp, vp, i32, sz, i32, i32, u64, vp, vp, vp, u64, vp, C.POINTER(u64)]),
         "rs_index_close": (None, [vp]),
         "rs_index_get_info": (i32, [vp, C.POINTER(Info)]),
         "rs_index_set_tail_emulation": (i32, [vp, i32]),
@@ -154,6 +155,15 @@ def lib() -> C.CDLL:
 
 
 NOALLOC_MAX_QUERIES = 1 << 20  # RS_NOALLOC_MAX_QUERIES, include/readserver_b200.h
+
+
+def unpack_hits40(raw: np.ndarray, n: int) -> np.ndarray:
+    """The first n hits of an rs_pop_query_hits40 list (5 bytes each) in rs_pop_query's 64-bit form."""
+    b = np.ascontiguousarray(raw[: 5 * n], dtype=np.uint8).reshape(n, 5).astype(np.uint64)
+    v = b[:, 0] | (b[:, 1] << np.uint64(8)) | (b[:, 2] << np.uint64(16)) | (b[:, 3] << np.uint64(24)) | (b[:, 4] << np.uint64(32))
+    out = ((v >> np.uint64(32)) << np.uint64(40)) | (v & np.uint64(0xFFFFFFFF))
+    out[v == np.uint64((1 << 40) - 1)] = np.iinfo(np.uint64).max
+    return out
 
 
 def _check(rc: int):
@@ -646,8 +656,9 @@ class ShardSet:
                                       _ptr(d_hits), capacity, _ptr(d_carriers), _ptr(d_total), stream))
 
     def query(self, kmers, k: int | None = None, max_hits: int = 1 << 20, locate: bool = True, carriers: bool = False,
-              packed: bool = False, strand: int = 0):
-        """Host arrays in, host arrays out: dict(counts, hit_offsets, hits, carriers)."""
+              packed: bool = False, strand: int = 0, hits40: bool = False):
+        """Host arrays in, host arrays out: dict(counts, hit_offsets, hits, carriers).  hits40: the list travels as 5
+        bytes per hit (rs_pop_query_hits40) and is widened here."""
         if packed:
             kmers = np.ascontiguousarray(kmers, dtype=np.uint64)
             q = kmers.size
@@ -671,11 +682,17 @@ class ShardSet:
         if rc not in (0, 9):
             _check(rc)
         cap = int(tot.value)
-        hits = np.zeros(max(cap, 1), dtype=np.uint64)
         W = int(self.info.carrier_words)
         carr = np.zeros((q, W), dtype=np.uint32) if carriers else None
-        _check(L.rs_pop_query(self._h, kmers.ctypes.data, k, q, int(packed), strand, max_hits, counts.ctypes.data, off.ctypes.data,
-                              hits.ctypes.data, cap, _ptr(carr), C.byref(tot)))
+        if hits40:
+            raw = np.zeros(5 * max(cap, 1), dtype=np.uint8)
+            _check(L.rs_pop_query_hits40(self._h, kmers.ctypes.data, k, q, int(packed), strand, max_hits, counts.ctypes.data,
+                                         off.ctypes.data, raw.ctypes.data, cap, _ptr(carr), C.byref(tot)))
+            hits = unpack_hits40(raw, cap)
+        else:
+            hits = np.zeros(max(cap, 1), dtype=np.uint64)
+            _check(L.rs_pop_query(self._h, kmers.ctypes.data, k, q, int(packed), strand, max_hits, counts.ctypes.data, off.ctypes.data,
+                                  hits.ctypes.data, cap, _ptr(carr), C.byref(tot)))
         out.update(hit_offsets=off, hits=hits[:cap])
         if carriers:
             out["carriers"] = carr

@@ -32,3 +32,24 @@ def test_our_arm_needs_a_device():
     r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), *TINY], capture_output=True, text=True,
                        timeout=600, cwd=ROOT)
     assert r.returncode != 0 and "CUDA" in r.stderr
+
+
+import pytest
+
+
+@pytest.mark.gpu
+def test_configs3_workload_at_trial_size():
+    """bench.py --workload configs3 (run-level collection) on a few small shards: one JSON line, every planted k-mer
+    found, the parity slice equal to the CPU oracle."""
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--workload", "configs3", "--c3-symbols", "3000000",
+                        "--c3-shards", "4", "--queries", "20000", "--steps", "2", "--warmup", "1"],
+                       capture_output=True, text=True, timeout=900, cwd=ROOT)
+    assert r.returncode == 0, r.stderr[-3000:]
+    lines = [l for l in r.stdout.splitlines() if l.strip()]
+    assert len(lines) == 1, lines
+    d = json.loads(lines[0])
+    assert d["config"]["workload"].startswith("configs[3]") and d["value"] > 0 and d["gpu_launches"] > 0
+    assert d["config"]["kmers_found"] >= 18000 and d["config"]["shards_on_rank0"] == 4
+    s = d["config"]["parity_slice"]
+    assert s["counts_equal"] and s["read_indices_equal"] and s["hits"] > 1000
+    assert d["roofline"]["frac"] > 0 and d["cpu_baseline"]["value"] > 0

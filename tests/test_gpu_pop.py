@@ -224,6 +224,9 @@ def test_shard_set_count_locate_carriers_match_per_shard_oracles(locate_every, m
         # shards of this size have depth-2 trees: the reference loses most matches to its tail behaviour (SURVEY.md Q1:
         # initInterval's getOcc(b, n-1) is short), and so must we; the exact-rank test below sees all of them
         assert int(want[0].sum()) > q.shape[0]
+        # the 5-byte hit list of rs_pop_query_hits40 widens to the same list (2^40 - 1 <-> 2^64 - 1)
+        got40 = S.query(q, 31, max_hits=3, carriers=True, hits40=True)
+        assert all(np.array_equal(got[k], got40[k]) for k in got)
         # packed queries give the same answers; count-only call
         got2 = S.query(engine.pack_kmers(q), 31, packed=True, max_hits=3, carriers=True)
         assert all(np.array_equal(got[k], got2[k]) for k in got)
@@ -336,6 +339,32 @@ def test_shard_set_of_few_shards(nshards, lanes, pass_bytes, popcase, engine, mo
             assert np.array_equal(got["counts"], want[0]) and np.array_equal(got["hit_offsets"], want[1]), (k, max_hits)
             assert np.array_equal(got["hits"], want[2]) and np.array_equal(got["carriers"], want[3]), (k, max_hits)
         assert int(want[0].max()) > 8 * nshards  # the short k-mers do have long intervals
+
+
+def test_hits40_sub_batches_and_limits(popcase, engine, monkeypatch):
+    """rs_pop_query_hits40: stretches of the list packed sub-batch by sub-batch (boundaries that cut a group of eight
+    hits), cut-off walks as 2^40 - 1, shard ids that do not fit refused."""
+    monkeypatch.setenv("RS_B200_POP_SUB", "1000")
+    q = popcase.queries[:5003]
+    with engine.ShardSet() as S:
+        for s, b in enumerate(popcase.gpu):
+            S.add(b, s)
+        S.seal(popcase.read_len + 28, 1)
+        a, b_ = S.query(q, 31, carriers=True), S.query(q, 31, carriers=True, hits40=True)
+        assert all(np.array_equal(a[k], b_[k]) for k in a) and a["hits"].size > 5000
+    with engine.ShardSet() as S:          # plain walks bounded at 3 steps: most hits come back as "no read"
+        for s, b in enumerate(popcase.gpu[:5]):
+            S.add(b, s)
+        S.seal(3, 0)
+        a, b_ = S.query(q, 31), S.query(q, 31, hits40=True)
+        assert np.array_equal(a["hits"], b_["hits"]) and int((a["hits"] == U64MAX).sum()) > 100
+    with engine.ShardSet() as S:
+        S.add(popcase.gpu[0], 300)        # a shard id the 40-bit form cannot carry
+        S.seal(popcase.read_len + 28, 1)
+        assert S.query(q, 31)["hits"].size > 0
+        with pytest.raises(engine.RsError) as e:
+            S.query(q, 31, hits40=True)
+        assert e.value.status == 7 or "40 bits" in str(e.value)
 
 
 @pytest.mark.parametrize("fill", [True, False])

@@ -78,3 +78,29 @@ def test_site_probes_differ_at_the_centre_only():
     for i in range(50):
         p = int(pop.site_pos[pick[i]])
         assert np.array_equal(ref[i].numpy(), g[p - 15:p + 16])
+
+
+def test_runlevel_shard_follows_the_run_table():
+    """configs[3]'s generator: run bytes drawn from a (symbol, length) table; the table of the output matches the input's
+    proportions, the counts it returns are those of the bytes, and the bytes load into the oracle as a BWT."""
+    import torch
+    from readserver_b200 import datagen as dg
+    import oracle
+    t = torch.zeros(5, 32, dtype=torch.float64)
+    t[0, 1], t[0, 2] = 40, 2
+    for c in range(1, 5):
+        for ln, w in ((1, 300), (2, 180), (3, 120), (7, 40), (31, 5)):
+            t[c, ln] = w * (1 + 0.1 * c)
+    runs, nstr, nsym = dg.runlevel_shard(t, 3_000_000, seed=11, device="cpu", chunk=250_000)
+    r = runs.numpy()
+    assert int((r & 31).min()) >= 1 and int((r >> 5).max()) <= 4
+    assert nsym == int((r & 31).astype(np.int64).sum()) and abs(nsym - 3_000_000) < 30_000
+    assert nstr == int((r[(r >> 5) == 0] & 31).astype(np.int64).sum()) > 0
+    got = dg.run_table(runs)
+    assert float(((got / got.sum() - t / t.sum()).abs()).max()) < 2e-3
+    again, nstr2, nsym2 = dg.runlevel_shard(t, 3_000_000, seed=11, device="cpu", chunk=250_000)
+    assert torch.equal(again, runs) and (nstr2, nsym2) == (nstr, nsym)          # deterministic per seed
+    P = oracle.PortIndex(runs=r, num_strings=nstr, num_symbols=nsym)              # a BWT the oracle accepts
+    assert P.bwlen == nsym
+    lo, up = P.find_interval("ACG")
+    assert up >= lo
