@@ -1249,9 +1249,12 @@ static int pop_run(rs_shardset* set, rs_popcomm* comm, const void* d_kmers, int 
   size_t scan_bytes = 0;
   CU(rs_scan_bytes(C, &scan_bytes));
   CU(set->s_scan.need(scan_bytes ? scan_bytes : 8));
-  /* large chunks: the gather goes shard by shard (tables L2-resident per launch); small ones: one launch, query-major */
+  /* large chunks on one GPU: the gather goes shard by shard over the sorted batch; small ones: one launch, query-major.
+   * Across GPUs the query-major kernel stays: it writes a query's hits of this rank as one contiguous piece of the
+   * owner's list, where the shard-major kernel sends every 8-byte hit over NVLink on its own (8 GPUs, configs[2]:
+   * 7.5 ms against 570 ms for the stage); RS_B200_GATHER_MODE=shard still forces it (tests). */
   const bool shard_major = table && want_hits && capacity && (!d_carriers || set->have_sets) &&
-                           (set->gather_mode == 2 || (set->gather_mode == 0 && C >= RS_POP_SHARD_MAJOR_MIN));
+                           (set->gather_mode == 2 || (set->gather_mode == 0 && !multi && C >= RS_POP_SHARD_MAJOR_MIN));
   if (want_hits && (!table || shard_major)) CU(set->s_seg.need((size_t)S * C * 4));
   /* Sorted batch (a shard-major gather over the whole batch in one chunk): the packed k-mers are sorted -- first base
    * most significant, which is the order of their intervals in every shard's BWT -- and searched in that order, so the
@@ -1529,8 +1532,11 @@ static int pop_query_host(rs_shardset* set, const void* kmers, int k, size_t Q, 
   uint64_t *d_counts = (uint64_t*)set->s_hc.p, *d_off = hit_offsets ? (uint64_t*)set->s_ho.p : nullptr;
   uint64_t *d_hits = (hit_offsets && capacity) ? (uint64_t*)set->s_hh.p : nullptr, *d_marks = (uint64_t*)set->s_hm.p;
   uint32_t* d_carr = carriers ? (uint32_t*)set->s_hw.p : nullptr;
-  /* sub-batches: about 2.5 M queries each, at most RS_POP_MAX_SUB */
-  size_t sub_queries = 2500000;
+  /* sub-batches of up to 16 M queries (they bound the device-side result buffers of very large batches), at most
+   * RS_POP_MAX_SUB.  Smaller ones, whose copy-out overlaps the next one's kernels, measured slower on configs[2]: every
+   * sub-batch streams all shards' rank blocks and tables through L2 again (10 M 31-mers, 5-byte hits: 1 sub-batch
+   * 43.7 M q/s, 4 sub-batches 39.7 M q/s) */
+  size_t sub_queries = (size_t)1 << 24;
   if (const char* e = getenv("RS_B200_POP_SUB")) sub_queries = (size_t)std::max<long long>(1000, atoll(e)); /* experiments */
   size_t nsub = (Q + sub_queries - 1) / sub_queries;
   if (nsub > RS_POP_MAX_SUB) nsub = RS_POP_MAX_SUB;
