@@ -712,6 +712,10 @@ def run_ours(args):
             "sample_codes": data["totals"]["codes"], "reads_dropped_for_q2": data["totals"]["dropped"],
             "index_hbm_bytes_rank0": int(info.index_bytes), "table_hbm_bytes_rank0": int(info.table_bytes),
             "chunk_queries": int(info.chunk_queries), "carrier_words": W,
+            "pipeline": ("batch sorted by packed k-mer, K1 per shard, shard-major gather (one shard per launch, rows dealt out to lanes)"
+                         if world == 1 and args.locate_every == 1 and Q >= (1 << 17) and Q <= int(info.chunk_queries) else
+                         "K1 per shard, query-major gather (lanes per query by the rank's shard count)" if args.locate_every == 1 else
+                         "K1 per shard, per-shard walks"),
             "l2": "working set (index + tables) far larger than the 126 MB L2; 256 MiB written between timed steps (untimed)",
             "timing": "CUDA events around each step on the launching stream, summed; max over ranks"
                       + ("; ranks aligned with a barrier before each step" if world > 1 else ""),
