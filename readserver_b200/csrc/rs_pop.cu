@@ -553,6 +553,18 @@ __global__ void k_pop_iota(uint32_t* __restrict__ out, uint64_t n) {
   const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) out[i] = (uint32_t)i;
 }
+/* sort keys of a batch whose answers are to become final range by range of the caller's order: the range (i / per) above
+ * the 2k bits of the k-mer; and the batch's keys in the sorted order (the sort keys drop the flag bit) */
+__global__ void k_pop_range_keys(const uint64_t* __restrict__ keys, uint64_t n, uint64_t per, uint32_t bits,
+                                 uint64_t* __restrict__ out) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = ((i / per) << bits) | (keys[i] & ((1ull << bits) - 1));
+}
+__global__ void k_pop_keys_sorted(const uint64_t* __restrict__ keys, const uint32_t* __restrict__ perm, uint64_t n,
+                                  uint64_t* __restrict__ out) {
+  const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) out[i] = keys[perm[i]];
+}
 __global__ void k_pop_slot_sorted(const uint64_t* __restrict__ slot, const uint32_t* __restrict__ perm, uint64_t n,
                                   uint64_t* __restrict__ out) {
   const uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
@@ -714,7 +726,7 @@ struct rs_shardset {
   /* per-call scratch, grown on demand; calls on one set are serialised */
   std::mutex mu;
   cudaStream_t stream = nullptr;
-  Scratch s_sort, s_skeys, s_perm, s_iota, s_sslot, s_carrl, s_pass, s_packed, s_lo, s_cnt, s_seg, s_nh, s_loc, s_scan, s_base, s_rows, s_dst, s_ri, s_in, s_lcnt;
+  Scratch s_ckeys, s_sort, s_skeys, s_perm, s_iota, s_sslot, s_carrl, s_pass, s_packed, s_lo, s_cnt, s_seg, s_nh, s_loc, s_scan, s_base, s_rows, s_dst, s_ri, s_in, s_lcnt;
   /* host-pointer calls: device-side result buffers, the copy-out stream, per-sub-batch events and hit-list marks */
   Scratch s_hc, s_ho, s_hh, s_hw, s_hm, s_h40;
   cudaStream_t copy_stream = nullptr;
@@ -822,7 +834,7 @@ void rs_shardset_destroy(rs_shardset* set) {
   cudaSetDevice(set->device);
   if (set->stream) cudaStreamSynchronize(set->stream);
   free_tables(set);
-  Scratch* all[] = {&set->s_sort, &set->s_skeys, &set->s_perm, &set->s_iota, &set->s_sslot, &set->s_carrl, &set->s_pass, &set->s_packed, &set->s_lo, &set->s_cnt, &set->s_seg, &set->s_nh, &set->s_loc, &set->s_scan,
+  Scratch* all[] = {&set->s_ckeys, &set->s_sort, &set->s_skeys, &set->s_perm, &set->s_iota, &set->s_sslot, &set->s_carrl, &set->s_pass, &set->s_packed, &set->s_lo, &set->s_cnt, &set->s_seg, &set->s_nh, &set->s_loc, &set->s_scan,
                     &set->s_base, &set->s_rows, &set->s_dst, &set->s_ri, &set->s_in, &set->s_lcnt,
                     &set->s_hc, &set->s_ho, &set->s_hh, &set->s_hw, &set->s_hm, &set->s_h40};
   for (Scratch* s : all) s->release();
@@ -1212,10 +1224,24 @@ static int comm_barrier(rs_popcomm* c, cudaStream_t st) {
   return RS_STATUS_OK;
 }
 
+/* Host-pointer calls: the batch's answers become final range by range of the CALLER's order, so that the copy-out of a
+ * range runs while the gather works on the next one.  The batch is then sorted by (range, k-mer): K1 and the offsets
+ * see one batch, the shard-major gather runs range after range (its rows still ascend within a range). */
+#define RS_POP_MAX_RANGES 4
+struct PopProgress {
+  uint32_t ranges = 1;                 /* wanted; pop_run stores what it used */
+  uint64_t per = 0;                    /* queries per range (pop_run) */
+  cudaEvent_t ev_marks = nullptr;      /* recorded once h_marks is on its way */
+  cudaEvent_t ev_range[RS_POP_MAX_RANGES] = {};
+  uint64_t* h_marks = nullptr;         /* pinned, ranges + 1: hit offsets at the range boundaries */
+  uint8_t* d_h40 = nullptr;            /* the list in 5 bytes per hit as well (k_pop_pack40), or null */
+  uint32_t* d_bad = nullptr;
+};
+
 /* the pipeline proper; everything on `st`, no host synchronisation */
 static int pop_run(rs_shardset* set, rs_popcomm* comm, const void* d_kmers, int k, size_t Q, int packed, int strand, uint64_t max_hits,
                    uint64_t* d_counts, uint64_t* d_hit_offsets, uint64_t* d_hits, uint64_t capacity, uint32_t* d_carriers,
-                   uint64_t* d_total, cudaStream_t st, bool keep_base = false) {
+                   uint64_t* d_total, cudaStream_t st, bool keep_base = false, PopProgress* prog = nullptr) {
   const uint32_t S = (uint32_t)set->shards.size();
   /* chunk: as many queries as the per-shard interval scratch (12 bytes per shard and query) may take; long launches
    * keep every lane busy (the batch is handed out dynamically) and a shard's index hot in L2 */
@@ -1265,6 +1291,9 @@ static int pop_run(rs_shardset* set, rs_popcomm* comm, const void* d_kmers, int 
   if (shard_major && d_carriers && (multi || sorted)) CU(set->s_carrl.need(C * 16));
   const uint32_t* perm = nullptr;
   const uint64_t* ksearch = keys; /* what K1 and the gather index by position in their launch */
+  /* ranges of the caller's order that become final one after the other (host-pointer calls, PopProgress) */
+  const uint32_t R = (prog && sorted && Q >= RS_POP_MAX_RANGES) ? std::min<uint32_t>(std::max<uint32_t>(prog->ranges, 1u), RS_POP_MAX_RANGES) : 1u;
+  const uint64_t per = (Q + R - 1) / R;
   if (sorted) {
     size_t sort_bytes = 0;
     CU(rs_sort_pairs_bytes(Q, &sort_bytes));
@@ -1274,12 +1303,27 @@ static int pop_run(rs_shardset* set, rs_popcomm* comm, const void* d_kmers, int 
     CU(set->s_iota.need(Q * 4));
     CU(set->s_sslot.need(Q * 8));
     StageTimer tm(set, st, RS_POP_STAGE_PACK, 1); /* launches counted are this library's own kernels (not CUB's) */
-    k_pop_iota<<<(unsigned)((Q + 255) / 256), 256, 0, st>>>((uint32_t*)set->s_iota.p, Q);
+    const unsigned gQ = (unsigned)((Q + 255) / 256);
+    k_pop_iota<<<gQ, 256, 0, st>>>((uint32_t*)set->s_iota.p, Q);
     CU(cudaGetLastError());
-    CU(rs_sort_pairs(keys, (uint64_t*)set->s_skeys.p, (const uint32_t*)set->s_iota.p, (uint32_t*)set->s_perm.p, Q, 2 * k,
-                     set->s_sort.p, sort_bytes, st));
+    if (R > 1) { /* (range, k-mer) order */
+      CU(set->s_ckeys.need(Q * 16));
+      uint64_t* ck = (uint64_t*)set->s_ckeys.p;
+      k_pop_range_keys<<<gQ, 256, 0, st>>>(keys, Q, per, 2u * (uint32_t)k, ck);
+      CU(rs_sort_pairs(ck, ck + Q, (const uint32_t*)set->s_iota.p, (uint32_t*)set->s_perm.p, Q, 2 * k + 2, set->s_sort.p,
+                       sort_bytes, st));
+      k_pop_keys_sorted<<<gQ, 256, 0, st>>>(keys, (const uint32_t*)set->s_perm.p, Q, (uint64_t*)set->s_skeys.p);
+      CU(cudaGetLastError());
+    } else {
+      CU(rs_sort_pairs(keys, (uint64_t*)set->s_skeys.p, (const uint32_t*)set->s_iota.p, (uint32_t*)set->s_perm.p, Q, 2 * k,
+                       set->s_sort.p, sort_bytes, st));
+    }
     perm = (const uint32_t*)set->s_perm.p;
     ksearch = (const uint64_t*)set->s_skeys.p;
+  }
+  if (prog) {
+    prog->ranges = R;
+    prog->per = per;
   }
   const uint32_t pass_shards = (table && !shard_major && want_hits && d_carriers && set->pass_shards) ? set->pass_shards : 0;
   const uint32_t npass = pass_shards ? (S + pass_shards - 1) / pass_shards : 1;
@@ -1344,6 +1388,11 @@ static int pop_run(rs_shardset* set, rs_popcomm* comm, const void* d_kmers, int 
       k_pop_add_base<<<(unsigned)((nq + 256) / 256), 256, 0, st>>>(loc, nq, base, d_hit_offsets + q0);
       k_pop_advance<<<1, 1, 0, st>>>(loc, nq, base, q0 + nq == Q ? d_hit_offsets + Q : nullptr, q0 + nq == Q ? d_total : nullptr);
       CU(cudaGetLastError());
+      if (prog && R > 1) { /* the list's extent per range, on its way to the host while the gather runs */
+        for (uint32_t r = 0; r <= R; ++r)
+          CU(cudaMemcpyAsync(&prog->h_marks[r], d_hit_offsets + std::min<uint64_t>((uint64_t)r * per, Q), 8, cudaMemcpyDeviceToHost, st));
+        CU(cudaEventRecord(prog->ev_marks, st));
+      }
       if (multi) {
         k_pop_owner_slots<<<gq, 256, 0, st>>>(P, keys + q0, (uint32_t)k, q0, nq, d_hit_offsets);
         CU(cudaGetLastError());
@@ -1367,13 +1416,30 @@ static int pop_run(rs_shardset* set, rs_popcomm* comm, const void* d_kmers, int 
         k_pop_slot_sorted<<<gq, 256, 0, st>>>(slot, perm, nq, (uint64_t*)set->s_sslot.p);
         slot = (const uint64_t*)set->s_sslot.p;
       }
-      const int gs = grid_for(nq, 256, 148 * RS_GATHER_BLOCKS);
-      for (uint32_t sh = 0; sh < S; ++sh)
-        k_pop_gather_shard<<<gs, 256, 0, st>>>(set->tab, P, sh, ksearch + q0, (uint32_t)k, lo + (uint64_t)sh * C, cnt + (uint64_t)sh * C,
-                                               seg + (uint64_t)sh * C, q0, nq, max_hits, slot, capacity, carr);
-      if (carr && multi) k_pop_carr_send<<<gq, 256, 0, st>>>(P, ksearch + q0, (uint32_t)k, q0, nq, carr, perm);
-      else if (carr && sorted) k_pop_carr_unsort<<<gq, 256, 0, st>>>(carr, perm, nq, reinterpret_cast<uint4*>(d_carriers));
-      CU(cudaGetLastError());
+      if (R > 1) { /* sorted by (range, k-mer), q0 = 0: range after range, each final when its last launch ends */
+        for (uint32_t r = 0; r < R; ++r) {
+          const uint64_t a = std::min<uint64_t>((uint64_t)r * per, Q), b = std::min<uint64_t>(a + per, Q), n = b - a;
+          if (n) {
+            const int gs = grid_for(n, 256, 148 * RS_GATHER_BLOCKS);
+            for (uint32_t sh = 0; sh < S; ++sh)
+              k_pop_gather_shard<<<gs, 256, 0, st>>>(set->tab, P, sh, ksearch + a, (uint32_t)k, lo + (uint64_t)sh * C + a,
+                                                     cnt + (uint64_t)sh * C + a, seg + (uint64_t)sh * C + a, 0, n, max_hits,
+                                                     slot + a, capacity, carr ? carr + a : nullptr);
+            if (carr) k_pop_carr_unsort<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(carr + a, perm + a, n, reinterpret_cast<uint4*>(d_carriers));
+            if (prog->d_h40) k_pop_pack40<<<148 * 4, 256, 0, st>>>(d_hits, d_hit_offsets + a, d_hit_offsets + b, capacity, prog->d_h40, prog->d_bad);
+            CU(cudaGetLastError());
+          }
+          CU(cudaEventRecord(prog->ev_range[r], st));
+        }
+      } else {
+        const int gs = grid_for(nq, 256, 148 * RS_GATHER_BLOCKS);
+        for (uint32_t sh = 0; sh < S; ++sh)
+          k_pop_gather_shard<<<gs, 256, 0, st>>>(set->tab, P, sh, ksearch + q0, (uint32_t)k, lo + (uint64_t)sh * C, cnt + (uint64_t)sh * C,
+                                                 seg + (uint64_t)sh * C, q0, nq, max_hits, slot, capacity, carr);
+        if (carr && multi) k_pop_carr_send<<<gq, 256, 0, st>>>(P, ksearch + q0, (uint32_t)k, q0, nq, carr, perm);
+        else if (carr && sorted) k_pop_carr_unsort<<<gq, 256, 0, st>>>(carr, perm, nq, reinterpret_cast<uint4*>(d_carriers));
+        CU(cudaGetLastError());
+      }
     } else if (table) {
       const int wc = (want_carr && set->have_sets) ? 1 : 0;
       const int gg = 148 * 2 * RS_GATHER_BLOCKS;
@@ -1433,6 +1499,18 @@ static int pop_run(rs_shardset* set, rs_popcomm* comm, const void* d_kmers, int 
   if (multi) {
     const int rc = comm_barrier(comm, st); /* every rank's adds, hits and bitmaps have landed */
     if (rc != RS_STATUS_OK) return rc;
+  }
+  if (prog && R == 1) { /* one range: everything is final here */
+    if (want_hits) {
+      if (prog->d_h40 && capacity) {
+        k_pop_pack40<<<148 * 8, 256, 0, st>>>(d_hits, d_hit_offsets, d_hit_offsets + Q, capacity, prog->d_h40, prog->d_bad);
+        CU(cudaGetLastError());
+      }
+      CU(cudaMemcpyAsync(&prog->h_marks[0], d_hit_offsets, 8, cudaMemcpyDeviceToHost, st));
+      CU(cudaMemcpyAsync(&prog->h_marks[1], d_hit_offsets + Q, 8, cudaMemcpyDeviceToHost, st));
+    }
+    CU(cudaEventRecord(prog->ev_marks, st));
+    CU(cudaEventRecord(prog->ev_range[0], st));
   }
   return RS_STATUS_OK;
 }
@@ -1543,46 +1621,46 @@ static int pop_query_host(rs_shardset* set, const void* kmers, int k, size_t Q, 
   if (!hit_offsets) nsub = 1;
   const size_t per = (Q + nsub - 1) / nsub;
   CU(cudaMemcpyAsync(set->s_in.p, kmers, Q * unit, cudaMemcpyHostToDevice, st));
-  uint64_t copied = 0; /* hits already queued for copy-out */
+  /* Copy-out range by range of the caller's order: pop_run sorts a large batch by (range, k-mer) and gathers range after
+   * range, so a range's answers leave while the next one is gathered (RS_B200_POP_RANGES: 1..4, experiments) */
+  uint32_t want_ranges = (hit_offsets && capacity) ? RS_POP_MAX_RANGES : 1;
+  if (const char* e = getenv("RS_B200_POP_RANGES")) want_ranges = (uint32_t)std::min<long>(RS_POP_MAX_RANGES, std::max<long>(1, atol(e)));
+  uint64_t total = 0;
   int status = RS_STATUS_OK;
-  auto drain = [&](size_t b) -> int { /* sub-batch b is computed: queue its copy-out */
-    const size_t q0 = b * per, nq = std::min(per, Q - q0);
-    CU(cudaEventSynchronize(set->ev_sub[b]));
-    const uint64_t end = set->h_marks[b];
-    CU(cudaMemcpyAsync(counts + q0, d_counts + q0, nq * 8, cudaMemcpyDeviceToHost, cs));
-    if (hit_offsets) {
-      CU(cudaMemcpyAsync(hit_offsets + q0, d_off + q0, (nq + (q0 + nq == Q ? 1 : 0)) * 8, cudaMemcpyDeviceToHost, cs));
-      if (carriers) CU(cudaMemcpyAsync(carriers + q0 * W, d_carr + q0 * W, nq * W * 4, cudaMemcpyDeviceToHost, cs));
-      const uint64_t upto = end < capacity ? end : capacity;
-      if (hits && upto > copied) {
-        if (d_h40) CU(cudaMemcpyAsync(hits40 + copied * 5, d_h40 + copied * 5, (upto - copied) * 5, cudaMemcpyDeviceToHost, cs));
-        else CU(cudaMemcpyAsync(hits + copied, d_hits + copied, (upto - copied) * 8, cudaMemcpyDeviceToHost, cs));
-      }
-      if (upto > copied) copied = upto;
-    }
-    return RS_STATUS_OK;
-  };
   for (size_t b = 0; b < nsub && status == RS_STATUS_OK; ++b) {
     const size_t q0 = b * per, nq = std::min(per, Q - q0);
+    PopProgress pg;
+    pg.ranges = want_ranges;
+    pg.ev_marks = set->ev_sub[RS_POP_MAX_RANGES];
+    for (int r = 0; r < RS_POP_MAX_RANGES; ++r) pg.ev_range[r] = set->ev_sub[r];
+    pg.h_marks = set->h_marks;
+    pg.d_h40 = d_h40;
+    pg.d_bad = d_bad;
     status = pop_run(set, nullptr, (const uint8_t*)set->s_in.p + q0 * unit, k, nq, packed, strand, max_hits, d_counts + q0,
-                     d_off ? d_off + q0 : nullptr, d_hits, capacity, d_carr ? d_carr + q0 * W : nullptr, d_marks + b, st, b > 0);
+                     d_off ? d_off + q0 : nullptr, d_hits, capacity, d_carr ? d_carr + q0 * W : nullptr, d_marks + b, st, b > 0,
+                     &pg);
     if (status != RS_STATUS_OK) break;
-    if (d_h40) { /* this sub-batch's stretch of the list in the 5-byte form */
-      k_pop_pack40<<<148 * 8, 256, 0, st>>>(d_hits, b ? d_marks + b - 1 : nullptr, d_marks + b, capacity, d_h40, d_bad);
-      CU(cudaGetLastError());
+    CU(cudaEventSynchronize(pg.ev_marks)); /* the ranges' extents in the hit list are on the host */
+    for (uint32_t r = 0; r < pg.ranges; ++r) {
+      const size_t ra = std::min<size_t>((size_t)r * pg.per, nq), re = std::min<size_t>(ra + pg.per, nq);
+      CU(cudaStreamWaitEvent(cs, pg.ev_range[r], 0));
+      if (re == ra) continue;
+      CU(cudaMemcpyAsync(counts + q0 + ra, d_counts + q0 + ra, (re - ra) * 8, cudaMemcpyDeviceToHost, cs));
+      if (!hit_offsets) continue;
+      CU(cudaMemcpyAsync(hit_offsets + q0 + ra, d_off + q0 + ra, (re - ra + (q0 + re == Q ? 1 : 0)) * 8, cudaMemcpyDeviceToHost, cs));
+      if (carriers) CU(cudaMemcpyAsync(carriers + (q0 + ra) * W, d_carr + (q0 + ra) * W, (re - ra) * W * 4, cudaMemcpyDeviceToHost, cs));
+      const uint64_t hb = std::min<uint64_t>(set->h_marks[r], capacity), he = std::min<uint64_t>(set->h_marks[r + 1], capacity);
+      if (hits_out && he > hb) {
+        if (d_h40) CU(cudaMemcpyAsync(hits40 + hb * 5, d_h40 + hb * 5, (he - hb) * 5, cudaMemcpyDeviceToHost, cs));
+        else CU(cudaMemcpyAsync(hits + hb, d_hits + hb, (he - hb) * 8, cudaMemcpyDeviceToHost, cs));
+      }
     }
-    /* the hit list's length so far, to the host; the copy stream may start on this sub-batch once it is there */
-    CU(cudaMemcpyAsync(&set->h_marks[b], d_marks + b, 8, cudaMemcpyDeviceToHost, st));
-    CU(cudaEventRecord(set->ev_sub[b], st));
-    CU(cudaStreamWaitEvent(cs, set->ev_sub[b], 0));
-    if (b > 0) status = drain(b - 1); /* while sub-batch b runs */
+    if (hit_offsets) total = set->h_marks[pg.ranges];
   }
-  if (status == RS_STATUS_OK) status = drain(nsub - 1);
   cudaStreamSynchronize(st);
   const cudaError_t ce = cudaStreamSynchronize(cs);
   if (status != RS_STATUS_OK) return status;
   if (ce != cudaSuccess) return fail(RS_STATUS_CUDA, "copy-out: %s", cudaGetErrorString(ce));
-  const uint64_t total = hit_offsets ? set->h_marks[nsub - 1] : 0;
   if (total_hits) *total_hits = total;
   if (hit_offsets && total > capacity)
     return fail(RS_STATUS_CAPACITY, "%llu hits do not fit the %llu provided", (unsigned long long)total,
