@@ -745,7 +745,7 @@ def run_ours(args):
                 "d2h_bytes_per_step": d2h, "steps": e2e_steps,
                 "api": "rs_pop_query_hits40 (host pointers, pinned): k-mers in, counts + hit offsets + hits (5 bytes each: shard "
                        "id << 32 | read index) + carrier sets out; the "
-                       "copy-out of one sub-batch overlaps the kernels of the next" if world == 1
+                       "answers leave range by range of the batch while the gather works on the next range" if world == 1
                 else "per rank: batch H2D, rs_pop_query_comm_dev, the owned answers D2H"},
         "gpu_launches": ours_launches,
         "clocks": clk,

@@ -331,7 +331,10 @@ int rs_gt_reads_batch(const rs_index* ix, const char* text, const uint64_t* offs
  *     carriers[Q x W]     may be NULL.  Bit s of a k-mer's W 32-bit words = sample number s (0-based: code - 1,
  *                         create_samples_hash.cpp:41-50) carries at least one of its hit reads; W = carrier_words
  *                         of rs_shardset_get_info.  Needs the hit list.
- * The _dev call is asynchronous on `stream` and never synchronises; calls on one set are serialised. */
+ * The _dev call is asynchronous on `stream` and never synchronises; calls on one set are serialised.  The host-pointer
+ * calls copy the k-mers in, run the pipeline and copy the answers out -- range by range of the batch while the locate
+ * stage works on the next range (large batches are sorted by (range, k-mer) for that) -- and return when the answers
+ * are in the caller's buffers; pinned buffers (rs_host_alloc) make the copies asynchronous. */
 typedef struct rs_shardset rs_shardset;
 typedef struct rs_shardset_info {
   uint32_t num_shards, sealed, locate_every, max_read_len, num_samples, carrier_words;
