@@ -104,3 +104,21 @@ def test_runlevel_shard_follows_the_run_table():
     assert P.bwlen == nsym
     lo, up = P.find_interval("ACG")
     assert up >= lo
+
+
+def test_unpack_hits40_widens_the_five_byte_list():
+    """engine.unpack_hits40: the 5-byte hits of rs_pop_query_hits40 (shard id << 32 | read index, little-endian; 2^40 - 1 =
+    no read) in rs_pop_query's 64-bit form (shard id << 40 | read index; 2^64 - 1)."""
+    from readserver_b200 import engine
+    rng = np.random.default_rng(5)
+    shard = rng.integers(0, 255, 1000).astype(np.uint64)
+    ri = rng.integers(0, 1 << 32, 1000).astype(np.uint64)
+    v = (shard << np.uint64(32)) | ri
+    v[::37] = (1 << 40) - 1
+    raw = np.zeros(5 * 1000 + 3, dtype=np.uint8)
+    for x in range(5):
+        raw[x:5000:5] = ((v >> np.uint64(8 * x)) & np.uint64(255)).astype(np.uint8)
+    want = (shard << np.uint64(40)) | ri
+    want[::37] = np.iinfo(np.uint64).max
+    assert np.array_equal(engine.unpack_hits40(raw, 1000), want)
+    assert engine.unpack_hits40(raw, 0).size == 0
